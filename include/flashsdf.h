@@ -1,0 +1,223 @@
+/*
+ * flashsdf.h -- C ABI of libflashsdf, the B200 (sm_100a) implementation of the
+ * tracking hot path of the Julia package `Flash`
+ * (JuliaTagBot/point-cloud-signed-distance).
+ *
+ * The reference has no FFI of its own; its boundary is a set of Julia function
+ * signatures.  Every entry point below names the Julia interface it replaces
+ * (file:line under the reference tree).  The Julia-side `ccall` bindings are in
+ * INTEGRATION.md and point-cloud-signed-distance_b200/julia/FlashCUDA.jl.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; all host buffers are caller-owned; the ctx
+ *     owns device memory, its stream, events and (optionally) one NCCL communicator;
+ *   - doubles at the ABI (the reference is Float64 end to end, src/models.jl:25,
+ *     src/depthsensors.jl:16); fp32/fp64 mixing is internal to the kernels;
+ *   - row-major everywhere: X is [C][nx], grad is [C][nx], points are [N][3]
+ *     (the memory of a Julia Vector{SVector{3,Float64}});
+ *   - every call returns 0 on success or a negative flash_status; the message is
+ *     flash_last_error(ctx) (ctx may be NULL for creation failures).  Nothing
+ *     throws across the ABI and nothing calls exit();
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point
+ *     returns FLASH_ERR_NO_DEVICE.
+ *   - a ctx is single-caller (the reference is single-threaded); distinct ctxs are
+ *     independent.
+ */
+#ifndef FLASHSDF_H
+#define FLASHSDF_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FLASHSDF_ABI_VERSION 1
+
+typedef struct flash_ctx flash_ctx;
+
+typedef enum flash_status {
+  FLASH_OK = 0,
+  FLASH_ERR_INVALID = -1,    /* bad argument / malformed model description */
+  FLASH_ERR_NO_DEVICE = -2,  /* no usable CUDA device (there is no CPU path) */
+  FLASH_ERR_CUDA = -3,       /* a CUDA runtime call or kernel failed */
+  FLASH_ERR_TOO_LARGE = -4,  /* model exceeds a compiled-in kernel limit */
+  FLASH_ERR_STATE = -5,      /* call order (e.g. cost before points were set) */
+  FLASH_ERR_NCCL = -6,       /* NCCL missing or a collective failed */
+  FLASH_ERR_IO = -7          /* file ingestion failed */
+} flash_status;
+
+/* joint types: RigidBodyDynamics Fixed / Revolute(axis) / QuaternionFloating as used by
+ * src/models.jl:26 (Revolute), :79 and :106 (QuaternionFloating), load_urdf :167. */
+enum { FLASH_JOINT_FIXED = 0, FLASH_JOINT_REVOLUTE = 1, FLASH_JOINT_QUAT_FLOATING = 2 };
+
+/* surface kinds: the BodyGeometry hierarchy, src/Flash.jl:35-48 */
+enum { FLASH_SURF_CONVEX = 0, FLASH_SURF_RIGID_SKIN = 1, FLASH_SURF_DEFORMABLE_SKIN = 2 };
+
+/* how convex bodies are evaluated */
+enum { FLASH_SDF_EXACT = 0, FLASH_SDF_GRID = 1 };
+
+/*
+ * Flattened `Flash.Manipulator` (src/Flash.jl:62-65): a mechanism tree plus the ordered
+ * `surfaces` vector.  Bodies are the moving bodies in tree order (a parent always precedes its
+ * children; parent -1 is the world).  The configuration vector q concatenates the joints in body
+ * order: fixed 0 values, revolute 1 (angle), quaternion-floating 7 ([w x y z tx ty tz], the
+ * RigidBodyDynamics 0.0.2 layout).  The state vector is x = [q ; deformation_data]
+ * (src/gradientdescent.jl:9-17), deformation_data holding 3 values per surface point of every
+ * deformable skin, surfaces in order (src/Flash.jl:97-104).
+ *
+ * body transform:  T(body->world) = T(parent->world) * joint_to_parent * T_joint(q)
+ * (body_to_joint is the identity in every builder of src/models.jl and for URDF input).
+ *
+ * Points of all surfaces are stored CSR style in `points`:
+ *   convex surface s : points[point_offset[s] .. point_offset[s+1])  are the vertices, given in
+ *                      the surface frame; surface_frame[s] maps that frame into body
+ *                      surface_body[s] (the URDF visual origin, src/models.jl:154-164).  The body
+ *                      is the convex hull of the vertices (EnhancedGJK semantics, src/models.jl:152).
+ *   skin surface s   : the first n_surface_points[s] points are surface points (value 0), the
+ *                      remaining ones skeleton points (value -1), the concatenation order of
+ *                      src/Flash.jl:207-211; point_body[] gives the body each control point is
+ *                      expressed in (a skin may span bodies: two_link_arm, src/models.jl:27-68).
+ */
+typedef struct flash_model_desc {
+  int32_t abi_version;             /* FLASHSDF_ABI_VERSION */
+  int32_t n_bodies;
+  const int32_t* body_parent;      /* [n_bodies]      */
+  const int32_t* joint_type;       /* [n_bodies]      */
+  const double*  joint_axis;       /* [n_bodies][3]   revolute axis in the joint frame */
+  const double*  joint_to_parent;  /* [n_bodies][12]  row-major [R|t], frameBefore -> parent body */
+  int32_t n_surfaces;
+  const int32_t* surface_kind;     /* [n_surfaces]    */
+  const int32_t* surface_body;     /* [n_surfaces]    convex only (-1 = world) */
+  const double*  surface_frame;    /* [n_surfaces][12] convex only */
+  const int32_t* point_offset;     /* [n_surfaces+1]  */
+  const int32_t* n_surface_points; /* [n_surfaces]    */
+  const double*  points;           /* [n_points][3]   */
+  const int32_t* point_body;       /* [n_points]      skins only (-1 = world) */
+} flash_model_desc;
+
+/*
+ * Options.  The RBF switches exist because SpatialFields.jl (pinned 06046c2, REQUIRE.dev:23) is
+ * not in the reference tree: `InterpolatingSurface(points, values, XCubed(), true)`
+ * (src/Flash.jl:212) is restated as the cubic-RBF variational interpolant with a linear
+ * polynomial, divided by its gradient norm -- the only definition consistent with
+ * test/runtests.jl:17.  Defaults reproduce that.
+ */
+typedef struct flash_options {
+  int32_t abi_version;
+  int32_t device;                   /* CUDA device ordinal, -1 = current */
+  int32_t rbf_normalize_by_gradient;/* 1 (default): skin value = f/|grad f| ; 0: raw f */
+  int32_t rbf_polynomial_degree;    /* 1 (default): a0 + a.x ; 0: a0 only */
+  int32_t sdf_mode;                 /* FLASH_SDF_EXACT (default) or FLASH_SDF_GRID */
+  double  grid_spacing;             /* metres, grid mode; <=0 -> 0.004 */
+  double  grid_margin;              /* metres around each hull's AABB covered by its grid; <=0 -> 0.10 */
+  int32_t reserved[8];
+} flash_options;
+
+void flash_options_default(flash_options* opt);
+
+int flash_abi_version(void);
+const char* flash_last_error(const flash_ctx* ctx);
+
+/* `Manipulator(mechanism, surfaces)` from Flash.Models.* (src/models.jl:70,97,135,170,176):
+ * Julia builds the model, flattens it once, and keeps the ctx for the model's lifetime. */
+int flash_model_create(const flash_model_desc* desc, const flash_options* opt, flash_ctx** out);
+void flash_destroy(flash_ctx* ctx);
+
+/* num_positions / num_states (src/Flash.jl:90) and the surface count */
+int flash_num_positions(const flash_ctx* ctx);
+int flash_num_states(const flash_ctx* ctx);
+int flash_num_surfaces(const flash_ctx* ctx);
+
+/* `CostFunctor(manipulator, sensed_points)` (src/gradientdescent.jl:41-47) captures the frame's
+ * points once; so does this.  xyz is the memory of Vector{SVector{3,Float64}}.  Points are
+ * rounded to fp32 on upload (stated in DESIGN.md). */
+int flash_points_set(flash_ctx* ctx, const double* xyz, int64_t n);
+int flash_points_set_f32(flash_ctx* ctx, const float* xyz, int64_t n);
+/* zero-copy: a device buffer of n float4 {x,y,z,unused} that stays valid until replaced */
+int flash_points_set_device(flash_ctx* ctx, const void* device_float4, int64_t n);
+int64_t flash_num_points(const flash_ctx* ctx);
+
+/*
+ * The hot path.  Replaces `(f::CostFunctor)(x)` + ForwardDiff's chunked gradient
+ * (src/gradientdescent.jl:49-65, src/tracking.jl:16-21) for a batch of C candidate states:
+ *   cost[c]  = sum_p skin_c(p)^2 + w_def * sum |deformation|^2     (RAW, not divided by N:
+ *              src/tracking.jl:18-20 divides and calls the callback on the Julia side)
+ *   grad[c]  = d cost[c] / d X[c]   including the in-cost quaternion normalisation
+ *              (src/gradientdescent.jl:30) -- may be NULL
+ *   argmin   = [C][N] index into `surfaces` of the first minimum (src/Flash.jl:267) -- may be NULL
+ * With a communicator attached (flash_comm_init) the points of all ranks are summed with one
+ * ncclAllReduce before the gradient epilogue, so every rank returns the global cost/gradient.
+ */
+int flash_cost_grad(flash_ctx* ctx, const double* X, int32_t C, double w_def,
+                    double* cost, double* grad, int32_t* argmin);
+
+/* `Flash.skin(state)(x)` (src/Flash.jl:265-268) for n query points under one state x:
+ * dist[n] (and optionally the argmin surface index). */
+int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t n,
+                    double* dist, int32_t* argmin);
+
+/*
+ * `DepthSensors.raycast_depths` / `raycast_points` (src/depthsensors.jl:56-113).
+ * rays [R][3] are the SENSOR-frame unit rays (generateKinectRays, :10-30) in row-major order,
+ * cam[12] the row-major [R|t] sensor->world transform.  depths[R] receives the marching distance
+ * or NaN for a miss; hits (may be NULL) receives the world points of the non-NaN rays in ray
+ * order, *nhits their number.
+ */
+int flash_raycast(flash_ctx* ctx, const double* x, const double* rays, int64_t R,
+                  const double cam[12], double* depths, double* hits, int64_t* nhits);
+
+/* generateKinectRays(rows, cols, vertical_fov, horizontal_fov), src/depthsensors.jl:10-30;
+ * host-side helper writing rays[rows*cols][3] row-major (v outer, u inner). */
+int flash_kinect_rays(int32_t rows, int32_t cols, double vertical_fov, double horizontal_fov,
+                      double* rays);
+
+/*
+ * `estimate_state` with a NaiveSolver (src/tracking.jl:8-27) run as an on-device loop for a batch
+ * of C warm starts: per iteration g = grad(cost/N); stop when |g|_2 < grad_tol;
+ * step = -rate * g ./ precondition_divisors, rescaled to |step|_2 <= max_step; x += step.
+ * (The step rule is SimpleGradientDescent's, which is not in the reference tree -- inferred from
+ * the keyword names at src/tracking.jl:12-15 and examples/irb140.ipynb cell 9.)
+ * divisors may be NULL (all ones).  X is updated in place; cost_out[C] (may be NULL) receives
+ * the raw cost at the returned x; iters_out[C] (may be NULL) the iterations taken.
+ */
+typedef struct flash_solver_params {
+  double rate;
+  double max_step;
+  int32_t iteration_limit;
+  double gradient_convergence_tolerance; /* <=0: never stop early */
+  double deformation_cost_weight;        /* src/gradientdescent.jl:7, default 10 */
+} flash_solver_params;
+
+int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solver_params* p,
+                         const double* precondition_divisors, double* cost_out, int32_t* iters_out);
+
+/* ---- multi-GPU: one process per GPU, points sharded, one allreduce per call ---- */
+#define FLASH_NCCL_UNIQUE_ID_BYTES 128
+int flash_comm_unique_id(void* id128);             /* rank 0 creates, caller broadcasts */
+int flash_comm_init(flash_ctx* ctx, int32_t rank, int32_t world, const void* id128);
+int flash_comm_world(const flash_ctx* ctx);
+
+/* ---- measurement hooks (CUDA events on the ctx stream) ---- */
+typedef struct flash_timing {
+  float ms_prepare;    /* FK + RBF solve kernel            */
+  float ms_main;       /* cost/gradient accumulation kernel */
+  float ms_allreduce;  /* NCCL (0 without a communicator)   */
+  float ms_epilogue;   /* adjoint solve + joint projection  */
+  float ms_total;      /* first launch -> last kernel end   */
+  int32_t launches;    /* kernels launched by the last call */
+} flash_timing;
+int flash_profiling(flash_ctx* ctx, int32_t enable);
+int flash_last_timing(const flash_ctx* ctx, flash_timing* t);
+/* total kernels launched by this ctx since creation (bench.py's gpu_launches) */
+int64_t flash_launch_count(const flash_ctx* ctx);
+/* device properties the bench reports: SM count, clock (kHz), L2 bytes */
+int flash_device_info(const flash_ctx* ctx, int32_t* sm_count, int32_t* clock_khz, int64_t* l2_bytes);
+/* grid mode: max |grid - exact| sampled at bake time per surface (metres); -1 if not grid */
+int flash_grid_report(const flash_ctx* ctx, int32_t surface, int32_t dims[3], double* spacing,
+                      double* max_abs_err);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLASHSDF_H */

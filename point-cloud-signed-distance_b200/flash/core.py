@@ -1,0 +1,229 @@
+"""Mirror of src/Flash.jl: geometry types, Manipulator, ManipulatorState, skin."""
+import ctypes as C
+
+import numpy as np
+
+from ._desc import ABI_VERSION, Options, PackedModel, Timing, c_double_p, c_int32_p
+from . import _lib
+
+JOINT_FIXED, JOINT_REVOLUTE, JOINT_QUAT_FLOATING = 0, 1, 2
+SDF_EXACT, SDF_GRID = 0, 1
+_NQ = {JOINT_FIXED: 0, JOINT_REVOLUTE: 1, JOINT_QUAT_FLOATING: 7}
+
+
+class FlashError(RuntimeError):
+    pass
+
+
+def _identity34():
+    return np.hstack([np.eye(3), np.zeros((3, 1))])
+
+
+class Body:
+    """A moving body and the joint that attaches it to its parent (RigidBodyDynamics attach!)."""
+
+    def __init__(self, name, parent, joint_type, axis=(0.0, 0.0, 1.0), joint_to_parent=None):
+        self.name = name
+        self.parent = int(parent)
+        self.joint_type = int(joint_type)
+        self.axis = np.asarray(axis, float)
+        self.joint_to_parent = _identity34() if joint_to_parent is None else np.asarray(joint_to_parent, float).reshape(3, 4)
+
+
+class Mechanism:
+    def __init__(self, bodies=None):
+        self.bodies = list(bodies or [])
+
+    def num_positions(self):
+        return sum(_NQ[b.joint_type] for b in self.bodies)
+
+    def q_offsets(self):
+        offs, o = [], 0
+        for b in self.bodies:
+            offs.append(o)
+            o += _NQ[b.joint_type]
+        return offs
+
+    def zero_configuration(self):
+        q = np.zeros(self.num_positions())
+        for b, o in zip(self.bodies, self.q_offsets()):
+            if b.joint_type == JOINT_QUAT_FLOATING:
+                q[o] = 1.0
+        return q
+
+
+class BodyGeometry:  # src/Flash.jl:30
+    pass
+
+
+class InterpolatingGeometry(BodyGeometry):  # src/Flash.jl:33
+    def __init__(self, surface_points, skeleton_points):
+        # each point is (body_index, (x, y, z)) -- a Point3D in that body's frame
+        self.surface_points = [(int(b), tuple(map(float, p))) for b, p in surface_points]
+        self.skeleton_points = [(int(b), tuple(map(float, p))) for b, p in skeleton_points]
+
+
+class DeformableInterpolatingSkin(InterpolatingGeometry):  # src/Flash.jl:35-38
+    pass
+
+
+class RigidInterpolatingSkin(InterpolatingGeometry):  # src/Flash.jl:40-43
+    pass
+
+
+class ConvexGeometry(BodyGeometry):  # src/Flash.jl:45-48
+    def __init__(self, vertices, body, frame=None):
+        self.vertices = np.asarray(vertices, float).reshape(-1, 3)
+        self.body = int(body)
+        self.frame = _identity34() if frame is None else np.asarray(frame, float).reshape(3, 4)
+
+
+def num_deformations(x):  # src/Flash.jl:79-88
+    if isinstance(x, DeformableInterpolatingSkin):
+        return len(x.surface_points)
+    if isinstance(x, BodyGeometry):
+        return 0
+    return sum(num_deformations(s) for s in x.surfaces)
+
+
+class Manipulator:  # src/Flash.jl:62-65
+    def __init__(self, mechanism, surfaces):
+        self.mechanism = mechanism
+        self.surfaces = list(surfaces)
+        self._ctx = None
+        self._packed = None
+        self._options = dict(sdf_mode=SDF_EXACT, grid_spacing=0.0, grid_margin=0.0,
+                             rbf_normalize_by_gradient=1, rbf_polynomial_degree=1, device=-1)
+
+    def __repr__(self):  # src/Flash.jl:67
+        return "Manipulator with %d links and %d surfaces" % (len(self.mechanism.bodies) + 1, len(self.surfaces))
+
+    # ---- C-ABI context management
+    def set_options(self, **kw):
+        for k in kw:
+            if k not in self._options:
+                raise KeyError(k)
+        self._options.update(kw)
+        self.invalidate()
+
+    def invalidate(self):
+        if self._ctx is not None:
+            _lib.lib().flash_destroy(self._ctx)
+        self._ctx = None
+        self._packed = None
+
+    def packed(self):
+        if self._packed is None:
+            self._packed = PackedModel(self)
+        return self._packed
+
+    def ctx(self):
+        if self._ctx is None:
+            L = _lib.lib()
+            opt = Options()
+            L.flash_options_default(C.byref(opt))
+            for k, v in self._options.items():
+                if k in ("grid_spacing", "grid_margin"):
+                    if v > 0:
+                        setattr(opt, k, v)
+                else:
+                    setattr(opt, k, v)
+            out = C.c_void_p()
+            rc = L.flash_model_create(C.byref(self.packed().desc), C.byref(opt), C.byref(out))
+            if rc != 0:
+                msg = L.flash_last_error(None)
+                raise FlashError("flash_model_create failed (%d): %s" % (rc, msg.decode() if msg else "?"))
+            self._ctx = out
+        return self._ctx
+
+    def check(self, rc):
+        if rc != 0:
+            msg = _lib.lib().flash_last_error(self._ctx)
+            raise FlashError("libflashsdf error %d: %s" % (rc, msg.decode() if msg else "?"))
+
+    def last_timing(self):
+        t = Timing()
+        self.check(_lib.lib().flash_last_timing(self.ctx(), C.byref(t)))
+        return {k: getattr(t, k) for k, _ in Timing._fields_}
+
+    def __del__(self):
+        try:
+            self.invalidate()
+        except Exception:
+            pass
+
+
+def num_positions(manip):
+    return manip.mechanism.num_positions()
+
+
+def num_states(manip):  # src/Flash.jl:90
+    return num_positions(manip) + 3 * num_deformations(manip)
+
+
+class _MechanismState:
+    def __init__(self, mechanism):
+        self.mechanism = mechanism
+        self.q = mechanism.zero_configuration()
+
+
+class ManipulatorState:  # src/Flash.jl:71-125
+    def __init__(self, manipulator):
+        self.manipulator = manipulator
+        self.mechanism_state = _MechanismState(manipulator.mechanism)
+        self.deformation_data = np.zeros(3 * num_deformations(manipulator))
+        self.deformations = {}
+        off = 0
+        for s in manipulator.surfaces:
+            views = []
+            for _ in range(num_deformations(s)):
+                views.append(self.deformation_data[off:off + 3])
+                off += 3
+            self.deformations[s] = views
+
+
+def set_configuration_(state, joint_angles):  # set_configuration!, src/Flash.jl:127-129
+    q = np.asarray(joint_angles, float)
+    if q.shape != state.mechanism_state.q.shape:
+        raise ValueError("configuration has %d entries, expected %d" % (q.size, state.mechanism_state.q.size))
+    state.mechanism_state.q[:] = q
+
+
+def _flatten(state):
+    return np.concatenate([state.mechanism_state.q, state.deformation_data])
+
+
+class Skin:
+    """The closure returned by Flash.skin(state): x -> minimum(s(x) for s in all_surfaces)."""
+
+    def __init__(self, manipulator, x):
+        self.manipulator = manipulator
+        self.x = np.ascontiguousarray(x, dtype=np.float64)
+
+    def eval(self, points, return_argmin=False):
+        pts = np.ascontiguousarray(points, dtype=np.float64).reshape(-1, 3)
+        n = len(pts)
+        dist = np.empty(n)
+        arg = np.empty(n, dtype=np.int32)
+        m = self.manipulator
+        m.check(_lib.lib().flash_skin_eval(m.ctx(), self.x.ctypes.data_as(c_double_p), pts.ctypes.data_as(c_double_p), n,
+                                           dist.ctypes.data_as(c_double_p), arg.ctypes.data_as(c_int32_p)))
+        return (dist, arg) if return_argmin else dist
+
+    def __call__(self, point):
+        p = np.asarray(point, float)
+        if p.ndim == 1:
+            return float(self.eval(p.reshape(1, 3))[0])
+        return self.eval(p)
+
+
+def skin(state):  # src/Flash.jl:265-268
+    return Skin(state.manipulator, _flatten(state))
+
+
+def surface_points(state, surface):
+    """Body-frame control points of a skin including deformations (world transform is on device)."""
+    pts = np.array([p for _, p in surface.surface_points], float)
+    if isinstance(surface, DeformableInterpolatingSkin):
+        pts = pts + np.array(state.deformations[surface]).reshape(-1, 3)
+    return pts

@@ -1,0 +1,75 @@
+"""Mirror of src/gradientdescent.jl."""
+import numpy as np
+
+from ._desc import c_double_p, c_int32_p
+from . import _lib
+from .core import ManipulatorState, _flatten, num_states
+
+default_deformation_cost_weight = 10  # src/gradientdescent.jl:7
+
+
+def flatten(state):  # src/gradientdescent.jl:9-11
+    return _flatten(state)
+
+
+def unflatten_(state, data):  # unflatten!, src/gradientdescent.jl:13-17
+    data = np.asarray(data, float)
+    nq = state.mechanism_state.q.size
+    if data.size != nq + state.deformation_data.size:
+        raise ValueError("state vector has %d entries, expected %d" % (data.size, nq + state.deformation_data.size))
+    state.mechanism_state.q[:] = data[:nq]
+    state.deformation_data[:] = data[nq:]
+
+
+def cost(state, sensed_points, deformation_cost_weight=default_deformation_cost_weight):  # src/gradientdescent.jl:28-39
+    f = CostFunctor(state.manipulator, sensed_points)
+    return f(flatten(state), deformation_cost_weight=deformation_cost_weight)
+
+
+class CostFunctor:  # src/gradientdescent.jl:41-57
+    """cost = CostFunctor(manipulator, sensed_points); cost(x) -> raw cost (not divided by N).
+
+    The points are uploaded once (the functor captures them, as in the reference); every call is one
+    flash_cost_grad launch.  Batched forms (`batch`) evaluate C candidate states at once.
+    """
+
+    def __init__(self, manipulator, sensed_points):
+        self.manipulator = manipulator
+        pts = np.ascontiguousarray(sensed_points, dtype=np.float64).reshape(-1, 3)
+        self.sensed_points = pts
+        self.upload()
+
+    def upload(self):
+        m = self.manipulator
+        m.check(_lib.lib().flash_points_set(m.ctx(), self.sensed_points.ctypes.data_as(c_double_p), len(self.sensed_points)))
+
+    def batch(self, X, gradient=True, argmin=False, deformation_cost_weight=default_deformation_cost_weight):
+        m = self.manipulator
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        if X.ndim == 1:
+            X = X.reshape(1, -1)
+        nx = num_states(m)
+        if X.shape[1] != nx:
+            raise ValueError("state vector has %d entries, expected %d" % (X.shape[1], nx))
+        Cn = X.shape[0]
+        cost = np.empty(Cn)
+        grad = np.empty((Cn, nx)) if gradient else None
+        arg = np.empty((Cn, len(self.sensed_points)), dtype=np.int32) if argmin else None
+        m.check(_lib.lib().flash_cost_grad(
+            m.ctx(), X.ctypes.data_as(c_double_p), Cn, float(deformation_cost_weight),
+            cost.ctypes.data_as(c_double_p),
+            grad.ctypes.data_as(c_double_p) if gradient else None,
+            arg.ctypes.data_as(c_int32_p) if argmin else None))
+        return cost, grad, arg
+
+    def __call__(self, x, deformation_cost_weight=default_deformation_cost_weight):
+        c, _, _ = self.batch(x, gradient=False, deformation_cost_weight=deformation_cost_weight)
+        return float(c[0])
+
+
+def CostAndGradientFunctor(cost):  # src/gradientdescent.jl:59-65: (g, x) -> value, gradient written into g
+    def f(g, x):
+        c, grad, _ = cost.batch(x, gradient=True)
+        g[:] = grad[0]
+        return float(c[0])
+    return f
