@@ -1,0 +1,326 @@
+#!/usr/bin/env python
+"""bench.py -- point x configuration SDF cost+gradient evaluations per second (BASELINE.json metric).
+
+Workload (BASELINE.json configs[4], "K5"): the IRB140(floating base)+squishable+table scene of
+examples/irb_and_squishable.ipynb (63 states, 9 surfaces), 10,000,000 synthetic points uniform in the
+scene AABB [-0.5,1]x[-0.5,0.5]x[0.5,2], 64 candidate configurations (warm start + N(0,0.05)).
+One "step" = one flash_cost_grad call: cost[64] + grad[64][63] over all points.
+With N GPUs the POINTS are sharded across ranks (total work fixed -> "strong" scaling); each rank's
+partial accumulators are summed by one ncclAllReduce inside the library before the epilogue.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode exact|grid]
+
+--impl reference times the CPU oracle (the fp64 C++ restatement of the Julia reference; Julia 0.5 and
+its six un-vendored packages cannot run on this box) on a bounded sample of the same workload.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "point-cloud-signed-distance_b200"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "point_config_cost_grad_evals_per_sec"
+UNIT = "evals/s"
+SCENE_LO, SCENE_HI = np.array([-0.5, -0.5, 0.5]), np.array([1.0, 0.5, 2.0])
+
+
+def scene_model(flash):
+    return flash.models.irb_and_squishable()
+
+
+def scene_states(flash, m, n_configs, seed=5):
+    """Warm start of examples/irb_and_squishable.ipynb cell 6 + N(0, 0.05) perturbations."""
+    rng = np.random.default_rng(seed)
+    nx, nq = flash.num_states(m), flash.num_positions(m)
+    x0 = flash.gradientdescent.flatten(flash.ManipulatorState(m))
+    x0[4:7] = [0.0, 0.0, 0.75]            # irb floating base
+    x0[13 + 4:13 + 7] = [0.55, 0.45, 0.8]  # squishable
+    x0[20 + 4:20 + 7] = [0.4, 0.0, 0.6]    # table
+    X = np.repeat(x0[None], n_configs, 0)
+    X[1:, :nq] += 0.05 * rng.standard_normal((n_configs - 1, nq))
+    X[1:, nq:] += 0.005 * rng.standard_normal((n_configs - 1, nx - nq))
+    return X
+
+
+def scene_points(n, seed, out=None):
+    """fp32-representable points uniform in the scene AABB, generated in chunks."""
+    rng = np.random.default_rng(seed)
+    pts = np.empty((n, 3), np.float64) if out is None else out
+    for i in range(0, n, 1 << 20):
+        j = min(n, i + (1 << 20))
+        pts[i:j] = (SCENE_LO + (SCENE_HI - SCENE_LO) * rng.random((j - i, 3), dtype=np.float32)).astype(np.float32)
+    return pts
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            f = tempfile.NamedTemporaryFile(prefix="clocks_", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for line in open(self.path):
+            t = [v.strip() for v in line.split(",")]
+            if len(t) < 9:
+                continue
+            try:
+                sm.append(float(t[1])); mx.append(float(t[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), t[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.path)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)), "measured"
+    return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback"
+
+
+# -------------------------------------------------------------------------------------------------
+def cpu_leg(n_points, n_configs, steps, warmup, threads=None, method="dual", seed=11):
+    """Times the CPU oracle (reference-faithful chunked forward-mode gradient by default) on a bounded
+    sample of the bench workload.  Returns evals/s and a description."""
+    import flash
+    import oracle_lib as ol
+    m = scene_model(flash)
+    o = ol.Oracle(m, threads=threads)
+    X = scene_states(flash, m, max(n_configs, 2))[:n_configs]
+    pts = scene_points(n_points, seed)
+    for _ in range(warmup):
+        o.cost_grad(X[0], pts[: max(1000, n_points // 20)], mode=ol.GJK, method=method)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        for c in range(n_configs):
+            o.cost_grad(X[c], pts, mode=ol.GJK, method=method)
+    dt = time.perf_counter() - t0
+    return {"value": n_points * n_configs * steps / dt, "unit": UNIT, "cores": o.threads, "kind": "port",
+            "sample": "%d points x %d configs x %d steps of the same scene; oracle/ C++ fp64 port, %s gradient (%s), %d threads"
+                      % (n_points, n_configs, steps, "ForwardDiff-style chunked dual" if method == "dual" else "single-pass adjoint",
+                         "7 passes of Dual{9} for 63 states" if method == "dual" else "not the reference's algorithm", o.threads),
+            "seconds": dt}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    base = cpu_leg(args.ref_points, args.ref_configs, args.steps, min(args.warmup, 1))
+    line = {"metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * base["seconds"] / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "impl": "reference",
+            "config": {"workload": "K5: IRB140(floating)+squishable+table, 63 states, 9 surfaces; bounded sample of 10M points x 64 configs",
+                       "points": args.ref_points, "configs": args.ref_configs},
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "Julia 0.5 reference cannot run here (no julia, un-vendored deps); this is the oracle/ C++ port on the host cores"}
+    print(json.dumps(line), flush=True)
+
+
+# -------------------------------------------------------------------------------------------------
+def run_ours(args, rank, local_rank, world):
+    import torch
+    import flash
+    from flash import _lib
+    from flash._desc import Timing, c_double_p
+
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    L = _lib.lib()
+    m = scene_model(flash)
+    m.set_options(device=local_rank, sdf_mode=1 if args.mode == "grid" else 0, grid_spacing=args.grid_spacing)
+    ctx = m.ctx()
+    nx = flash.num_states(m)
+    Cn = args.configs
+    X = np.ascontiguousarray(scene_states(flash, m, Cn))
+
+    # shard the points: rank r owns [lo, hi)
+    N = args.points
+    lo, hi = (N * rank) // world, (N * (rank + 1)) // world
+    n_local = hi - lo
+    pin = torch.empty((n_local, 3), dtype=torch.float64, pin_memory=True)
+    pts = pin.numpy()
+    scene_points(n_local, 1000 + rank, out=pts)
+
+    if world > 1:
+        idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            raw = (C.c_ubyte * 128)()
+            m.check(L.flash_comm_unique_id(raw))
+            idbuf.copy_(torch.tensor(list(raw), dtype=torch.uint8))
+        dist.broadcast(idbuf, 0)
+        raw = (C.c_ubyte * 128)(*idbuf.cpu().tolist())
+        m.check(L.flash_comm_init(ctx, rank, world, raw))
+
+    cost = np.empty(Cn); grad = np.empty((Cn, nx))
+    pX, pc, pg, pp = X.ctypes.data_as(c_double_p), cost.ctypes.data_as(c_double_p), grad.ctypes.data_as(c_double_p), pts.ctypes.data_as(c_double_p)
+    m.check(L.flash_points_set(ctx, pp, n_local))
+    m.check(L.flash_profiling(ctx, 1))
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        m.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
+
+    def e2e_step():
+        m.check(L.flash_points_set(ctx, pp, n_local))
+        m.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    launches0 = L.flash_launch_count(ctx)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    t_steps, k_main, k_total = [], [], []
+    tm = Timing()
+    for _ in range(args.steps):
+        flush.zero_()
+        barrier()
+        t0 = time.perf_counter()
+        step()
+        torch.cuda.synchronize()
+        t_steps.append(time.perf_counter() - t0)
+        L.flash_last_timing(ctx, C.byref(tm))
+        k_main.append(tm.ms_main); k_total.append(tm.ms_total)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = L.flash_launch_count(ctx) - launches0
+    checksum = float(cost.sum())
+
+    # end-to-end: host (pinned) points -> device every step, results back on the host
+    for _ in range(1):
+        e2e_step()
+    t_e2e = []
+    for _ in range(args.steps):
+        flush.zero_()
+        barrier()
+        t0 = time.perf_counter()
+        e2e_step()
+        torch.cuda.synchronize()
+        t_e2e.append(time.perf_counter() - t0)
+    barrier()
+
+    tt = torch.tensor([sum(t_steps), sum(t_e2e), sum(k_main) / 1e3, sum(k_total) / 1e3], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    T, Te, Tk, Tkt = [float(v) for v in tt.cpu()]
+    units = float(N) * Cn * args.steps
+    if rank == 0:
+        peaks, peak_src = measured_peaks()
+        sm = C.c_int32(); khz = C.c_int32(); l2 = C.c_int64()
+        L.flash_device_info(ctx, C.byref(sm), C.byref(khz), C.byref(l2))
+        # algorithmic HBM bytes of the main kernel per launch: every point (float4, 16 B) is read once per
+        # config pass it is not L2-resident for; the algorithmic minimum is one read per launch per rank
+        # plus the per-config tables -- the kernel is ALU-bound, see DESIGN.md.
+        n_rank = (N + world - 1) // world
+        alg_bytes = 16.0 * n_rank + 8.0 * Cn * 400
+        kernel_s = Tk / args.steps
+        achieved = alg_bytes / kernel_s / 1e9
+        # ALU roofline (the binding one in exact mode): issue slots per second
+        fp32_peak = sm.value * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12
+        line = {
+            "metric": METRIC, "value": units / T, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": 1e3 * T / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32 distances / f64 RBF + accumulation", "data": "synthetic",
+            "config": {"workload": "K5: IRB140(floating)+squishable+table (63 states, 9 surfaces), %d points x %d configs, points sharded over %d GPU(s)" % (N, Cn, world),
+                       "points": N, "configs": Cn, "sdf_mode": args.mode, "l2": "L2 flushed (512 MiB memset) between timed steps; inputs %s L2" % ("exceed" if 16 * n_rank > l2.value else "fit"),
+                       "parallelism": "points sharded x%d, one ncclAllReduce of [C][%d] fp64 per step" % (world, 0)},
+            "device_ms_per_step": 1e3 * Tkt / args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
+                         "traffic": None, "peak_source": peak_src, "kernel": "cost_kernel<GRAD>", "kernel_ms": 1e3 * kernel_s,
+                         "note": "exact mode is ALU-bound (GJK + fp64 RBF), not HBM-bound: see alu"},
+            "alu": {"evals_per_sm_clock": (units / world / args.steps) / kernel_s / (sm.value * (clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)) * 1e6),
+                    "fp32_peak_tflops_nominal": fp32_peak},
+            "clocks": clocks,
+            "e2e": {"value": units / Te, "unit": UNIT, "h2d_bytes_per_step": int(n_local * 24 + X.nbytes), "d2h_bytes_per_step": int(cost.nbytes + grad.nbytes),
+                    "ms_per_step": 1e3 * Te / args.steps},
+            "gpu_launches": int(launches),
+            "checksum_cost_sum": checksum,
+        }
+        if args.cpu_baseline and world == 1:
+            base = cpu_leg(args.ref_points, args.ref_configs, 1, 1)
+            fast = cpu_leg(args.ref_points, args.ref_configs, 1, 0, method="adjoint")
+            base["adjoint_value"] = fast["value"]
+            base["adjoint_note"] = "same oracle, single-pass analytic gradient (not the reference's algorithm): best CPU algorithm on %d threads" % fast["cores"]
+            line["cpu_baseline"] = base
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="exact", choices=["exact", "grid"])
+    ap.add_argument("--points", type=int, default=10_000_000)
+    ap.add_argument("--configs", type=int, default=64)
+    ap.add_argument("--grid-spacing", type=float, default=0.004)
+    ap.add_argument("--ref-points", type=int, default=100_000)
+    ap.add_argument("--ref-configs", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under it so that there is one process per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus), "--master-addr", "127.0.0.1",
+               "--master-port", str(29500 + os.getpid() % 1000)] + sys.argv
+        sys.exit(subprocess.call(cmd))
+    run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,664 @@
+// flash_dev.h -- device-side data layout and per-point / per-config math of libflashsdf.
+//
+// Everything here is `__host__ __device__`: the CUDA kernels in flash_kernels.cuh are the only
+// product callers; the functions also compile with plain g++ so that tests/hostcheck can run the
+// SAME arithmetic on a CPU-only box against the oracle before GPU time is spent (test
+// infrastructure only -- the shipped library has no CPU path).
+//
+// Reference rows: A3 state layout, A4 quaternion normalisation, A5 cost, A6 min over
+// surfaces, A7 RBF skin, A8 convex signed distance.  Citations are /root/reference paths.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#define FLASH_HD __host__ __device__ __forceinline__
+#define FLASH_HDN __host__ __device__ __noinline__
+#else
+#define FLASH_HD inline
+#define FLASH_HDN inline
+#endif
+
+namespace flashdev {
+
+constexpr int MAX_BODIES = 32;
+constexpr int MAX_SURFACES = 32;
+constexpr int MAX_CONVEX = 24;
+constexpr int MAX_SKINS = 4;
+constexpr int MAX_SKIN_PTS = 64;           // control points per skin (two_link_arm has 46)
+constexpr int MAX_SKIN_M = MAX_SKIN_PTS + 4;
+constexpr int MAX_HULL_VERTS = 255;        // vertex ids are packed in 8 bits
+constexpr int GJK_MAX_ITER = 24;
+
+enum { JOINT_FIXED = 0, JOINT_REVOLUTE = 1, JOINT_QUAT = 2 };
+enum { SURF_CONVEX = 0, SURF_RIGID_SKIN = 1, SURF_DEFORMABLE_SKIN = 2 };
+
+struct F3 { float x, y, z; };
+struct F4 { float x, y, z, w; };
+struct D3 { double x, y, z; };
+struct XfD { double R[9]; double t[3]; };  // p_out = R p + t
+
+struct BodyC {
+  int parent, jtype, qoff, pad;
+  double axis[3];    // unit, joint frame
+  double j2p[12];    // row-major [R|t], frameBefore -> parent body
+};
+
+// per convex surface; the geometry frame is the surface frame re-centred on the hull centroid
+struct ConvexC {
+  int surface, body, nverts, nplanes;
+  int off_planes, off_tris, off_verts, pad;  // indices into the geometry blob (units: F4 / u32 / F4)
+  float lo[3], hi[3];                        // AABB of the vertices, geometry frame
+  float depth_bound, pad2;                   // >= max penetration depth
+  double frame[12];                          // geometry frame -> body frame
+  // grid mode (body-frame SDF grid): origin, spacing, dims, offset into the grid pool (floats)
+  float g_org[3]; float g_inv_h; int g_dim[3]; int g_on; long long g_off;
+};
+
+struct SkinC {
+  int surface, kind, npts, nsurf;
+  int deform_off;  // first deformation scalar (relative to x + nq), -1 if rigid
+  int M;           // npts + (poly_deg >= 1 ? 4 : 1)
+  int tab_off;     // config table: centres[3n], w[n], a0, a[3]      (doubles)
+  int acc_off;     // accumulators: gY[n+4], gC[3n]                  (doubles)
+  int aux_off;     // per-config aux: LU[M*M], piv[M]                (doubles)
+  int pt_off;      // into ModelC::skin_pt
+  int pad[2];
+};
+
+struct ModelC {
+  int n_bodies, n_surfaces, n_convex, n_skins;
+  int nq, nx, normalize, poly_deg;
+  int tab_len;   // doubles per config:   12*n_convex + sum(4n+4)
+  int acc_len;   // doubles per config:   1 + 6*n_convex + sum(4n+4)
+  int aux_len;   // doubles per config:   24*n_bodies + n_bodies + sum(M*M + M)
+  int geo_f4, geo_u32;  // blob sizes
+  int pad;
+  BodyC body[MAX_BODIES];
+  ConvexC cvx[MAX_CONVEX];
+  SkinC skin[MAX_SKINS];
+  int surf_kind[MAX_SURFACES];
+  int surf_slot[MAX_SURFACES];  // index into cvx[] or skin[]
+  double skin_pt[MAX_SKINS * MAX_SKIN_PTS][3];
+  int skin_pt_body[MAX_SKINS * MAX_SKIN_PTS];
+};
+
+// what the per-point code reads; copied to shared memory by every block of the main kernel
+struct HotModel {
+  int n_convex, n_skins, normalize, acc_len;
+  int tab_len, pad[3];
+  SkinC skin[MAX_SKINS];
+  ConvexC cvx[MAX_CONVEX];
+};
+
+// offsets inside the per-config aux block
+FLASH_HD int aux_X(const ModelC& M, int b) { return 12 * b; }
+FLASH_HD int aux_P(const ModelC& M, int b) { return 12 * M.n_bodies + 12 * b; }
+FLASH_HD int aux_qnorm(const ModelC& M, int b) { return 24 * M.n_bodies + b; }
+FLASH_HD int aux_skin0(const ModelC& M) { return 25 * M.n_bodies; }
+
+// ------------------------------------------------------------------ small algebra
+FLASH_HD F3 f3(float x, float y, float z) { F3 r; r.x = x; r.y = y; r.z = z; return r; }
+FLASH_HD F3 operator-(F3 a, F3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
+FLASH_HD F3 operator+(F3 a, F3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
+FLASH_HD F3 operator*(F3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
+FLASH_HD float dot(F3 a, F3 b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+FLASH_HD F3 cross(F3 a, F3 b) { return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+FLASH_HD F3 xyz(F4 a) { return f3(a.x, a.y, a.z); }
+FLASH_HD D3 d3(double x, double y, double z) { D3 r; r.x = x; r.y = y; r.z = z; return r; }
+FLASH_HD D3 operator-(D3 a, D3 b) { return d3(a.x - b.x, a.y - b.y, a.z - b.z); }
+FLASH_HD D3 operator+(D3 a, D3 b) { return d3(a.x + b.x, a.y + b.y, a.z + b.z); }
+FLASH_HD D3 operator*(D3 a, double s) { return d3(a.x * s, a.y * s, a.z * s); }
+FLASH_HD double dot(D3 a, D3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+FLASH_HD D3 cross(D3 a, D3 b) { return d3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+FLASH_HD D3 xf_rot(const double* X, D3 p) { return d3(X[0] * p.x + X[1] * p.y + X[2] * p.z, X[3] * p.x + X[4] * p.y + X[5] * p.z, X[6] * p.x + X[7] * p.y + X[8] * p.z); }
+FLASH_HD D3 xf_rotT(const double* X, D3 p) { return d3(X[0] * p.x + X[3] * p.y + X[6] * p.z, X[1] * p.x + X[4] * p.y + X[7] * p.z, X[2] * p.x + X[5] * p.y + X[8] * p.z); }
+FLASH_HD D3 xf_t(const double* X) { return d3(X[9], X[10], X[11]); }
+FLASH_HD D3 xf_apply(const double* X, D3 p) { return xf_rot(X, p) + xf_t(X); }
+// XfD stored flat as 12 doubles: R[0..8], t[9..11]
+FLASH_HD void xf_compose(const double* A, const double* B, double* C) {  // C = A*B (C may not alias)
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) C[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+  D3 t = xf_apply(A, d3(B[9], B[10], B[11]));
+  C[9] = t.x; C[10] = t.y; C[11] = t.z;
+}
+FLASH_HD void xf_from_rowmajor34(const double* m, double* X) {
+  for (int i = 0; i < 3; ++i) { X[3 * i] = m[4 * i]; X[3 * i + 1] = m[4 * i + 1]; X[3 * i + 2] = m[4 * i + 2]; X[9 + i] = m[4 * i + 3]; }
+}
+
+// ------------------------------------------------------------------ kinematics (row A3/A4/A10)
+// Joint transform of body b under the normalised configuration.  Revolute(axis) and
+// QuaternionFloating q=[w x y z tx ty tz] as in src/models.jl:26,79,106.
+FLASH_HD void joint_xf(const BodyC& B, const double* qn, double* J) {
+  for (int i = 0; i < 12; ++i) J[i] = 0;
+  J[0] = J[4] = J[8] = 1;
+  if (B.jtype == JOINT_REVOLUTE) {
+    double ax = B.axis[0], ay = B.axis[1], az = B.axis[2];
+    double s, c;
+#ifdef __CUDA_ARCH__
+    sincos(qn[B.qoff], &s, &c);
+#else
+    s = sin(qn[B.qoff]); c = cos(qn[B.qoff]);
+#endif
+    double C = 1.0 - c;
+    J[0] = c + C * ax * ax;      J[1] = C * ax * ay - s * az; J[2] = C * ax * az + s * ay;
+    J[3] = C * ay * ax + s * az; J[4] = c + C * ay * ay;      J[5] = C * ay * az - s * ax;
+    J[6] = C * az * ax - s * ay; J[7] = C * az * ay + s * ax; J[8] = c + C * az * az;
+  } else if (B.jtype == JOINT_QUAT) {
+    const double w = qn[B.qoff], x = qn[B.qoff + 1], y = qn[B.qoff + 2], z = qn[B.qoff + 3];
+    J[0] = 1 - 2 * (y * y + z * z); J[1] = 2 * (x * y - w * z);     J[2] = 2 * (x * z + w * y);
+    J[3] = 2 * (x * y + w * z);     J[4] = 1 - 2 * (x * x + z * z); J[5] = 2 * (y * z - w * x);
+    J[6] = 2 * (x * z - w * y);     J[7] = 2 * (y * z + w * x);     J[8] = 1 - 2 * (x * x + y * y);
+    J[9] = qn[B.qoff + 4]; J[10] = qn[B.qoff + 5]; J[11] = qn[B.qoff + 6];
+  }
+}
+
+// Forward kinematics for one configuration.  x is the RAW state; quaternions are normalised here
+// exactly where the reference does it (normalize!, src/gradientdescent.jl:19-30).  Writes into the
+// per-config aux block: X_b (body->world), P_b (joint frameBefore->world), |quat_b|.
+FLASH_HD void fk_config(const ModelC& M, const double* x, double* aux) {
+  double qn[7 * MAX_BODIES > 64 ? 64 : 7 * MAX_BODIES];  // nq <= 64 enforced at model creation
+  for (int k = 0; k < M.nq; ++k) qn[k] = x[k];
+  for (int b = 0; b < M.n_bodies; ++b) {
+    const BodyC& B = M.body[b];
+    double nrm = 1.0;
+    if (B.jtype == JOINT_QUAT) {
+      const double* q = x + B.qoff;
+      nrm = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+      for (int k = 0; k < 4; ++k) qn[B.qoff + k] = q[k] / nrm;
+    }
+    aux[aux_qnorm(M, b)] = nrm;
+  }
+  for (int b = 0; b < M.n_bodies; ++b) {
+    const BodyC& B = M.body[b];
+    double j2p[12], J[12];
+    xf_from_rowmajor34(B.j2p, j2p);
+    double* P = aux + aux_P(M, b);
+    if (B.parent >= 0) xf_compose(aux + aux_X(M, B.parent), j2p, P);
+    else for (int i = 0; i < 12; ++i) P[i] = j2p[i];
+    joint_xf(B, qn, J);
+    xf_compose(P, J, aux + aux_X(M, b));
+  }
+}
+
+// ------------------------------------------------------------------ LU (RBF system, row A7)
+// In-place LU with partial pivoting, row-major M x M.  `lane`/`nl` let a warp share the row
+// updates (nl = 1 on the host); WSYNC must be a warp barrier on the device.
+#ifdef __CUDA_ARCH__
+#define FLASH_WSYNC() __syncwarp()
+#else
+#define FLASH_WSYNC() ((void)0)
+#endif
+FLASH_HD int lu_factor(double* A, double* piv, int M, int lane, int nl) {
+  int ok = 1;
+  for (int k = 0; k < M; ++k) {
+    int p = k; double best = fabs(A[k * M + k]);
+    for (int i = k + 1; i < M; ++i) { double v = fabs(A[i * M + k]); if (v > best) { best = v; p = i; } }
+    if (best == 0.0) ok = 0;
+    FLASH_WSYNC();
+    if (p != k) for (int j = lane; j < M; j += nl) { double t = A[k * M + j]; A[k * M + j] = A[p * M + j]; A[p * M + j] = t; }
+    if (lane == 0) piv[k] = (double)p;
+    FLASH_WSYNC();
+    const double inv = 1.0 / A[k * M + k];
+    for (int i = k + 1 + lane; i < M; i += nl) {
+      const double f = A[i * M + k] * inv;
+      A[i * M + k] = f;
+      for (int j = k + 1; j < M; ++j) A[i * M + j] -= f * A[k * M + j];
+    }
+    FLASH_WSYNC();
+  }
+  return ok;
+}
+FLASH_HD void lu_solve(const double* LU, const double* piv, double* b, int M) {
+  for (int k = 0; k < M; ++k) { int p = (int)piv[k]; if (p != k) { double t = b[k]; b[k] = b[p]; b[p] = t; } }
+  for (int i = 1; i < M; ++i) { double s = b[i]; for (int j = 0; j < i; ++j) s -= LU[i * M + j] * b[j]; b[i] = s; }
+  for (int i = M - 1; i >= 0; --i) { double s = b[i]; for (int j = i + 1; j < M; ++j) s -= LU[i * M + j] * b[j]; b[i] = s / LU[i * M + i]; }
+}
+
+// Per-config preparation after fk_config: convex world->geometry transforms and, per skin, the
+// world control points (src/Flash.jl:152-205), the Turk-O'Brien system (InterpolatingSurface,
+// src/Flash.jl:212) factored in fp64, and its solution.  tab/aux are this config's blocks.
+FLASH_HD void prepare_convex(const ModelC& M, const double* aux, double* tab) {
+  for (int j = 0; j < M.n_convex; ++j) {
+    const ConvexC& C = M.cvx[j];
+    double S[12];
+    if (C.body >= 0) xf_compose(aux + aux_X(M, C.body), C.frame, S);
+    else for (int i = 0; i < 12; ++i) S[i] = C.frame[i];
+    double* T = tab + 12 * j;   // y = A x + b,  A = R^T, b = -R^T t
+    T[0] = S[0]; T[1] = S[3]; T[2] = S[6];
+    T[3] = S[1]; T[4] = S[4]; T[5] = S[7];
+    T[6] = S[2]; T[7] = S[5]; T[8] = S[8];
+    D3 b = xf_rotT(S, d3(S[9], S[10], S[11]));
+    T[9] = -b.x; T[10] = -b.y; T[11] = -b.z;
+  }
+}
+FLASH_HD void skin_centres(const ModelC& M, const SkinC& K, const double* x, const double* aux, double* tab) {
+  double* c = tab + K.tab_off;
+  for (int i = 0; i < K.npts; ++i) {
+    D3 p = d3(M.skin_pt[K.pt_off + i][0], M.skin_pt[K.pt_off + i][1], M.skin_pt[K.pt_off + i][2]);
+    if (K.kind == SURF_DEFORMABLE_SKIN && i < K.nsurf) {  // point + deformation in the body frame (src/Flash.jl:176-181)
+      const double* dd = x + M.nq + K.deform_off + 3 * i;
+      p = p + d3(dd[0], dd[1], dd[2]);
+    }
+    int b = M.skin_pt_body[K.pt_off + i];
+    if (b >= 0) p = xf_apply(aux + aux_X(M, b), p);
+    c[3 * i] = p.x; c[3 * i + 1] = p.y; c[3 * i + 2] = p.z;
+  }
+}
+FLASH_HD void skin_assemble(const ModelC& M, const SkinC& K, const double* tab, double* A, int lane, int nl) {
+  const double* c = tab + K.tab_off;
+  const int n = K.npts, Mm = K.M;
+  for (int e = lane; e < Mm * Mm; e += nl) {
+    int i = e / Mm, j = e % Mm;
+    double v = 0;
+    if (i < n && j < n) {
+      double dx = c[3 * i] - c[3 * j], dy = c[3 * i + 1] - c[3 * j + 1], dz = c[3 * i + 2] - c[3 * j + 2];
+      double r2 = dx * dx + dy * dy + dz * dz;
+      v = r2 * sqrt(r2);
+    } else if (i < n) v = (j == n) ? 1.0 : c[3 * i + (j - n - 1)];
+    else if (j < n) v = (i == n) ? 1.0 : c[3 * j + (i - n - 1)];
+    A[e] = v;
+  }
+}
+// rhs zeros(surface), -1 (skeleton) (src/Flash.jl:211); solution -> tab (w, a0, a)
+FLASH_HD void skin_solve(const ModelC& M, const SkinC& K, const double* LU, const double* piv, double* tab) {
+  double b[MAX_SKIN_M];
+  const int n = K.npts;
+  for (int i = 0; i < K.M; ++i) b[i] = (i < n && i >= K.nsurf) ? -1.0 : 0.0;
+  lu_solve(LU, piv, b, K.M);
+  double* w = tab + K.tab_off + 3 * n;
+  for (int i = 0; i < n; ++i) w[i] = b[i];
+  w[n] = b[n];
+  for (int k = 0; k < 3; ++k) w[n + 1 + k] = (K.M == n + 4) ? b[n + 1 + k] : 0.0;
+}
+
+// ------------------------------------------------------------------ convex signed distance (row A8)
+// Closest point to the ORIGIN on segment / triangle given in coordinates relative to the query
+// point (Ericson, Real-Time Collision Detection 5.1.2 / 5.1.5), with barycentric weights whose
+// exact zeros identify the supporting sub-simplex.
+FLASH_HD F3 seg_closest0(F3 a, F3 b, float& wa, float& wb) {
+  F3 ab = b - a;
+  float den = dot(ab, ab);
+  float t = den > 0.f ? -dot(a, ab) / den : 0.f;
+  if (t <= 0.f) { wa = 1.f; wb = 0.f; return a; }
+  if (t >= 1.f) { wa = 0.f; wb = 1.f; return b; }
+  wa = 1.f - t; wb = t;
+  return a + ab * t;
+}
+FLASH_HD F3 tri_closest0(F3 a, F3 b, F3 c, float& wa, float& wb, float& wc) {
+  F3 ab = b - a, ac = c - a;
+  float d1 = -dot(ab, a), d2 = -dot(ac, a);
+  if (d1 <= 0.f && d2 <= 0.f) { wa = 1.f; wb = 0.f; wc = 0.f; return a; }
+  float d3 = -dot(ab, b), d4 = -dot(ac, b);
+  if (d3 >= 0.f && d4 <= d3) { wa = 0.f; wb = 1.f; wc = 0.f; return b; }
+  float vc = d1 * d4 - d3 * d2;
+  if (vc <= 0.f && d1 >= 0.f && d3 <= 0.f) { float v = d1 / (d1 - d3); wa = 1.f - v; wb = v; wc = 0.f; return a + ab * v; }
+  float d5 = -dot(ab, c), d6 = -dot(ac, c);
+  if (d6 >= 0.f && d5 <= d6) { wa = 0.f; wb = 0.f; wc = 1.f; return c; }
+  float vb = d5 * d2 - d1 * d6;
+  if (vb <= 0.f && d2 >= 0.f && d6 <= 0.f) { float w = d2 / (d2 - d6); wa = 1.f - w; wb = 0.f; wc = w; return a + ac * w; }
+  float va = d3 * d6 - d5 * d4;
+  if (va <= 0.f && (d4 - d3) >= 0.f && (d5 - d6) >= 0.f) { float w = (d4 - d3) / ((d4 - d3) + (d5 - d6)); wa = 0.f; wb = 1.f - w; wc = w; return b + (c - b) * w; }
+  float den = va + vb + vc;
+  if (!(den > 0.f)) {  // degenerate (collinear) triangle: best of the three edges
+    float u0, u1, v0, v1, w0, w1;
+    F3 q0 = seg_closest0(a, b, u0, u1), q1 = seg_closest0(a, c, v0, v1), q2 = seg_closest0(b, c, w0, w1);
+    float e0 = dot(q0, q0), e1 = dot(q1, q1), e2 = dot(q2, q2);
+    if (e0 <= e1 && e0 <= e2) { wa = u0; wb = u1; wc = 0.f; return q0; }
+    if (e1 <= e2) { wa = v0; wb = 0.f; wc = v1; return q1; }
+    wa = 0.f; wb = w0; wc = w1; return q2;
+  }
+  float inv = 1.f / den;
+  float v = vb * inv, w = vc * inv;
+  wa = 1.f - v - w; wb = v; wc = w;
+  return a + ab * v + ac * w;
+}
+
+// GJK working simplex: up to three hull vertices (coordinates relative to the query point).
+struct Simplex { F3 a, b, c; int ia, ib, ic, ns; };
+FLASH_HD void simplex_push(Simplex& S, F3 p, int j) {
+  if (S.ns == 0) { S.a = p; S.ia = j; } else if (S.ns == 1) { S.b = p; S.ib = j; } else { S.c = p; S.ic = j; }
+  ++S.ns;
+}
+// keep the vertices with non-zero barycentric weight (at least one)
+FLASH_HD void simplex_from(Simplex& S, F3 p0, int j0, float u0, F3 p1, int j1, float u1, F3 p2, int j2, float u2) {
+  S.ns = 0;
+  if (u0 > 0.f) simplex_push(S, p0, j0);
+  if (u1 > 0.f) simplex_push(S, p1, j1);
+  if (u2 > 0.f) simplex_push(S, p2, j2);
+  if (S.ns == 0) simplex_push(S, p2, j2);
+}
+
+// Signed distance from y (geometry frame) to the convex hull given by its supporting planes and
+// vertices.  Inside (all plane distances <= 0): the largest plane distance, normal = that plane's.
+// Outside: exact Euclidean distance by GJK on the vertex set, started from a triangle of the
+// most-violated face (EnhancedGJK `gjk!` is the reference algorithm, src/Flash.jl:238-243; its
+// inside value is iteration-path dependent and replaced by the exact depth -- DESIGN.md).
+// nrm receives grad_y(distance).
+FLASH_HD float hull_sd(const F4* __restrict__ planes, const uint32_t* __restrict__ ptri, const F4* __restrict__ verts,
+                       int np, int nv, F3 y, F3& nrm) {
+  float D = -3.0e38f; int fs = 0;
+  for (int f = 0; f < np; ++f) {
+    F4 p = planes[f];
+    float s = fmaf(p.x, y.x, fmaf(p.y, y.y, fmaf(p.z, y.z, -p.w)));
+    if (s > D) { D = s; fs = f; }
+  }
+  if (D <= 0.f) { nrm = xyz(planes[fs]); return D; }
+  Simplex S;
+  F3 q;
+  {
+    uint32_t t = ptri[fs];
+    int j0 = t & 255, j1 = (t >> 8) & 255, j2 = (t >> 16) & 255;
+    F3 p0 = xyz(verts[j0]) - y, p1 = xyz(verts[j1]) - y, p2 = xyz(verts[j2]) - y;
+    float u0, u1, u2;
+    q = tri_closest0(p0, p1, p2, u0, u1, u2);
+    simplex_from(S, p0, j0, u0, p1, j1, u1, p2, j2, u2);
+  }
+  for (int it = 0; it < GJK_MAX_ITER; ++it) {
+    float dd = dot(q, q);
+    if (!(dd > 0.f)) break;
+    // support vertex towards the query point: minimise q.(v - y)  <=>  minimise q.v
+    float best = 3.0e38f; int iw = 0;
+    for (int v = 0; v < nv; ++v) {
+      F4 p = verts[v];
+      float s = fmaf(q.x, p.x, fmaf(q.y, p.y, q.z * p.z));
+      if (s < best) { best = s; iw = v; }
+    }
+    if (iw == S.ia || (S.ns > 1 && iw == S.ib) || (S.ns > 2 && iw == S.ic)) break;  // already supporting
+    F3 w = xyz(verts[iw]) - y;
+    if (dd - dot(q, w) <= 1e-7f * dd) break;                                          // no descent left
+    float u0, u1, u2;
+    if (S.ns == 1) {
+      q = seg_closest0(S.a, w, u0, u1);
+      simplex_from(S, S.a, S.ia, u0, w, iw, u1, w, iw, 0.f);
+    } else if (S.ns == 2) {
+      q = tri_closest0(S.a, S.b, w, u0, u1, u2);
+      simplex_from(S, S.a, S.ia, u0, S.b, S.ib, u1, w, iw, u2);
+    } else {
+      // tetrahedron (a,b,c,w): y is outside the hull, so the closest point lies on one of the
+      // three faces that contain the new vertex
+      float x0, x1, x2, y0, y1, y2, z0, z1, z2;
+      F3 q0 = tri_closest0(S.a, S.b, w, x0, x1, x2);
+      F3 q1 = tri_closest0(S.a, S.c, w, y0, y1, y2);
+      F3 q2 = tri_closest0(S.b, S.c, w, z0, z1, z2);
+      float e0 = dot(q0, q0), e1 = dot(q1, q1), e2 = dot(q2, q2);
+      Simplex T = S;
+      if (e0 <= e1 && e0 <= e2) { q = q0; simplex_from(S, T.a, T.ia, x0, T.b, T.ib, x1, w, iw, x2); }
+      else if (e1 <= e2) { q = q1; simplex_from(S, T.a, T.ia, y0, T.c, T.ic, y1, w, iw, y2); }
+      else { q = q2; simplex_from(S, T.b, T.ib, z0, T.c, T.ic, z1, w, iw, z2); }
+    }
+  }
+  float dd = dot(q, q);
+  if (!(dd > 0.f)) { nrm = xyz(planes[fs]); return D; }   // numerically on the surface
+#ifdef __CUDA_ARCH__
+  float inv = rsqrtf(dd);
+  inv = inv * (1.5f - 0.5f * dd * inv * inv);   // one Newton step: ~1 ulp
+#else
+  float inv = 1.0f / sqrtf(dd);
+#endif
+  nrm = q * (-inv);
+  return dd * inv;
+}
+
+// conservative lower bound of the signed distance from the AABB of the hull
+FLASH_HD float aabb_lower_bound(const float* lo, const float* hi, float depth_bound, F3 y) {
+  float dx = fmaxf(fmaxf(lo[0] - y.x, y.x - hi[0]), 0.f);
+  float dy = fmaxf(fmaxf(lo[1] - y.y, y.y - hi[1]), 0.f);
+  float dz = fmaxf(fmaxf(lo[2] - y.z, y.z - hi[2]), 0.f);
+  float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+  if (d2 > 0.f) return sqrtf(d2) * (1.f - 4e-6f) - 1e-7f;
+  return -depth_bound;
+}
+
+// world point -> geometry frame, fp64 FMA chain rounded once to fp32 (DESIGN.md "precision")
+FLASH_HD F3 to_geometry(const double* __restrict__ T, float px, float py, float pz) {
+  double x = px, y = py, z = pz;
+  double a = fma(T[0], x, fma(T[1], y, fma(T[2], z, T[9])));
+  double b = fma(T[3], x, fma(T[4], y, fma(T[5], z, T[10])));
+  double c = fma(T[6], x, fma(T[7], y, fma(T[8], z, T[11])));
+  return f3((float)a, (float)b, (float)c);
+}
+
+// trilinear sample of a body-frame SDF grid with analytic gradient, manual fp32 (no texture unit)
+FLASH_HD bool grid_sd(const ConvexC& C, const float* __restrict__ pool, F3 y, float& d, F3& nrm) {
+  float gx = (y.x - C.g_org[0]) * C.g_inv_h, gy = (y.y - C.g_org[1]) * C.g_inv_h, gz = (y.z - C.g_org[2]) * C.g_inv_h;
+  if (!(gx >= 0.f && gy >= 0.f && gz >= 0.f && gx < (float)(C.g_dim[0] - 1) && gy < (float)(C.g_dim[1] - 1) && gz < (float)(C.g_dim[2] - 1))) return false;
+  int ix = (int)gx, iy = (int)gy, iz = (int)gz;
+  float fx = gx - (float)ix, fy = gy - (float)iy, fz = gz - (float)iz;
+  const float* g = pool + C.g_off + ((long long)iz * C.g_dim[1] + iy) * C.g_dim[0] + ix;
+  const long long sy = C.g_dim[0], sz = (long long)C.g_dim[0] * C.g_dim[1];
+  float c000 = g[0], c100 = g[1], c010 = g[sy], c110 = g[sy + 1];
+  float c001 = g[sz], c101 = g[sz + 1], c011 = g[sz + sy], c111 = g[sz + sy + 1];
+  float c00 = fmaf(fx, c100 - c000, c000), c10 = fmaf(fx, c110 - c010, c010);
+  float c01 = fmaf(fx, c101 - c001, c001), c11 = fmaf(fx, c111 - c011, c011);
+  float c0 = fmaf(fy, c10 - c00, c00), c1 = fmaf(fy, c11 - c01, c01);
+  d = fmaf(fz, c1 - c0, c0);
+  // d/dx: interpolate the x-differences in y,z; likewise for y and z
+  float dx00 = c100 - c000, dx10 = c110 - c010, dx01 = c101 - c001, dx11 = c111 - c011;
+  float dx0 = fmaf(fy, dx10 - dx00, dx00), dx1 = fmaf(fy, dx11 - dx01, dx01);
+  float dy0 = c10 - c00, dy1 = c11 - c01;
+  nrm.x = fmaf(fz, dx1 - dx0, dx0) * C.g_inv_h;
+  nrm.y = fmaf(fz, dy1 - dy0, dy0) * C.g_inv_h;
+  nrm.z = (c1 - c0) * C.g_inv_h;
+  return true;
+}
+
+// ------------------------------------------------------------------ RBF skin value (row A7), fp64
+// f(x) = sum w_i |x-c_i|^3 + a0 + a.x ; returned value f/|grad f| (normalize) -- fp64 because the
+// cubic terms cancel to ~1e-4 of their magnitude.
+struct SkinEval { double s, f, ginv; D3 nh; };
+FLASH_HD double dsqrt_fast(double r2) {
+#ifdef __CUDA_ARCH__
+  // fp32 rsqrt seed + two fp64 Newton steps on 1/sqrt, then r = r2 * rinv with a final correction
+  if (r2 <= 0.0) return 0.0;
+  double y = (double)rsqrtf((float)r2);
+  y = y * (1.5 - 0.5 * r2 * y * y);
+  y = y * (1.5 - 0.5 * r2 * y * y);
+  double r = r2 * y;
+  return fma(fma(-r, r, r2), 0.5 * y, r);
+#else
+  return sqrt(r2);
+#endif
+}
+FLASH_HD SkinEval skin_eval(const double* __restrict__ c, const double* __restrict__ w, int n, bool normalize, double px, double py, double pz) {
+  double f = w[n] + w[n + 1] * px + w[n + 2] * py + w[n + 3] * pz;
+  double gx = w[n + 1], gy = w[n + 2], gz = w[n + 3];
+  for (int i = 0; i < n; ++i) {
+    double ux = px - c[3 * i], uy = py - c[3 * i + 1], uz = pz - c[3 * i + 2];
+    double r2 = fma(ux, ux, fma(uy, uy, uz * uz));
+    double r = dsqrt_fast(r2);
+    double wr = w[i] * r;
+    f = fma(wr, r2, f);
+    double k = 3.0 * wr;
+    gx = fma(k, ux, gx); gy = fma(k, uy, gy); gz = fma(k, uz, gz);
+  }
+  SkinEval e;
+  e.f = f;
+  if (!normalize) { e.s = f; e.ginv = 1.0; e.nh = d3(0, 0, 0); return e; }
+  double g2 = gx * gx + gy * gy + gz * gz;
+  double gi = 1.0 / sqrt(g2);
+  e.ginv = gi; e.s = f * gi; e.nh = d3(gx * gi, gy * gi, gz * gi);
+  return e;
+}
+
+// Adjoint contributions of ONE point (where this skin is the minimum) to centre i:
+// out[0] = d(s^2)/d w_i, out[1..3] = explicit d(s^2)/d c_i.  i == n is the polynomial pseudo-centre:
+// out[0] = d/d a0, out[1..3] = d/d a.   (derivation: DESIGN.md "RBF adjoint")
+FLASH_HD void skin_adjoint_term(const double* __restrict__ c, const double* __restrict__ w, int n, bool normalize, int i,
+                                double px, double py, double pz, double s, double ginv, D3 nh, double out[4]) {
+  const double beta = normalize ? 2.0 * s * ginv : 2.0 * s;  // raw mode: s holds f
+  const double sn = normalize ? s : 0.0;
+  if (i == n) {
+    out[0] = beta;
+    out[1] = beta * (px - sn * nh.x); out[2] = beta * (py - sn * nh.y); out[3] = beta * (pz - sn * nh.z);
+    return;
+  }
+  double ux = px - c[3 * i], uy = py - c[3 * i + 1], uz = pz - c[3 * i + 2];
+  double r2 = ux * ux + uy * uy + uz * uz;
+  double r = dsqrt_fast(r2);
+  double un = ux * nh.x + uy * nh.y + uz * nh.z;
+  out[0] = beta * (r * r2 - sn * 3.0 * r * un);
+  double wi = w[i];
+  double k1 = -3.0 * wi * r;                              // d f / d c_i          = k1 * u
+  double k2 = sn * wi * 3.0 * r;                          // -s * n.d(grad f)/dc_i = k2 * nh + k3 * u
+  double k3 = r > 0.0 ? sn * wi * 3.0 * un / r : 0.0;
+  out[1] = beta * ((k1 + k3) * ux + k2 * nh.x);
+  out[2] = beta * ((k1 + k3) * uy + k2 * nh.y);
+  out[3] = beta * ((k1 + k3) * uz + k2 * nh.z);
+}
+
+// ------------------------------------------------------------------ min over surfaces (row A6)
+struct GeoView {            // geometry blob (shared memory in the main kernel)
+  const F4* f4;             // planes and vertices
+  const uint32_t* u32;      // per-plane start triangle
+  const float* grid_pool;   // grid mode
+};
+
+struct PointEval {
+  float d;        // min over surfaces
+  int arg;        // surface index of the first minimum (src/Flash.jl:267)
+  int slot;       // cvx[] or skin[] slot of the winner
+  int is_skin;    // winner is an interpolating skin
+  F3 y, n;        // winner convex: point and distance gradient in the geometry frame
+  SkinEval sk;    // winner skin
+};
+
+FLASH_HD bool lex_less(float d, int s, float best, int arg) { return d < best || (d == best && s < arg); }
+
+// Evaluates skin(x) = min over all surfaces for one world point under one configuration.
+// `lb` is per-thread scratch of n_convex floats with stride lb_stride.
+// Convex bodies are culled with their AABB lower bound: a body is evaluated exactly only if its
+// bound can still beat the best value so far, which cannot change the min or the argmin.
+FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __restrict__ tab,
+                         float px, float py, float pz, float* lb, int lb_stride, bool use_grid, PointEval& out) {
+  const ConvexC* __restrict__ cvx = M.cvx;
+  float best = 3.0e38f; int arg = 0x7fffffff; int slot = -1; int is_skin = 0;
+  out.y = f3(0, 0, 0); out.n = f3(0, 0, 0);
+  out.sk.s = 0; out.sk.f = 0; out.sk.ginv = 0; out.sk.nh = d3(0, 0, 0);
+  for (int k = 0; k < M.n_skins; ++k) {
+    const SkinC& K = M.skin[k];
+    const double* c = tab + K.tab_off;
+    SkinEval e = skin_eval(c, c + 3 * K.npts, K.npts, M.normalize != 0, (double)px, (double)py, (double)pz);
+    float d = (float)e.s;
+    if (lex_less(d, K.surface, best, arg)) { best = d; arg = K.surface; slot = k; is_skin = 1; out.sk = e; }
+  }
+  const int nc = M.n_convex;
+  int j0 = -1; float lb0 = 3.0e38f;
+  for (int j = 0; j < nc; ++j) {
+    F3 y = to_geometry(tab + 12 * j, px, py, pz);
+    float l = aabb_lower_bound(cvx[j].lo, cvx[j].hi, cvx[j].depth_bound, y);
+    lb[j * lb_stride] = l;
+    if (l < lb0) { lb0 = l; j0 = j; }
+  }
+  // the most promising body first, then the rest in surface order
+  for (int jj = -1; jj < nc; ++jj) {
+    int j = jj < 0 ? j0 : jj;
+    if (j < 0 || (jj >= 0 && j == j0)) continue;
+    float l = lb[j * lb_stride];
+    const ConvexC& C = cvx[j];
+    if (l > best || (l == best && C.surface > arg)) continue;
+    F3 y = to_geometry(tab + 12 * j, px, py, pz);
+    F3 n; float d;
+    bool done = false;
+    if (use_grid && C.g_on) done = grid_sd(C, G.grid_pool, y, d, n);
+    if (!done) d = hull_sd(G.f4 + C.off_planes, G.u32 + C.off_tris, G.f4 + C.off_verts, C.nplanes, C.nverts, y, n);
+    if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
+  }
+  out.d = best; out.arg = arg; out.slot = slot; out.is_skin = is_skin;
+}
+
+// ------------------------------------------------------------------ epilogue (rows A2-A5 gradient)
+// acc: this config's accumulators after the sum over all points (and ranks).  Produces the raw cost
+// and d cost / d x, including the in-cost quaternion normalisation (src/gradientdescent.jl:30) and
+// the deformation regulariser (:33-37).  Serial; a few thousand flops per config.
+FLASH_HD void epilogue_config(const ModelC& M, const double* x, const double* tab, const double* aux, const double* acc,
+                              double w_def, double* scratch /* 6*n_bodies + MAX_SKIN_M */, double* cost, double* grad) {
+  const int nb = M.n_bodies;
+  double* F = scratch;            // [nb][3]
+  double* Mo = scratch + 3 * nb;  // [nb][3]
+  double* lam = scratch + 6 * nb; // [M]
+  for (int i = 0; i < 6 * nb; ++i) scratch[i] = 0;
+  if (grad) for (int k = 0; k < M.nx; ++k) grad[k] = 0;
+  double c = acc[0];
+  if (grad) {
+    // convex wrenches, accumulated in the geometry frame: f = sum g, tau = sum y x g, g = -2 d n
+    for (int j = 0; j < M.n_convex; ++j) {
+      const ConvexC& C = M.cvx[j];
+      if (C.body < 0) continue;
+      double S[12];
+      xf_compose(aux + aux_X(M, C.body), C.frame, S);
+      const double* a = acc + 1 + 6 * j;
+      D3 f = xf_rot(S, d3(a[0], a[1], a[2]));
+      D3 m = xf_rot(S, d3(a[3], a[4], a[5])) + cross(xf_t(S), f);
+      F[3 * C.body] += f.x; F[3 * C.body + 1] += f.y; F[3 * C.body + 2] += f.z;
+      Mo[3 * C.body] += m.x; Mo[3 * C.body + 1] += m.y; Mo[3 * C.body + 2] += m.z;
+    }
+    for (int k = 0; k < M.n_skins; ++k) {
+      const SkinC& K = M.skin[k];
+      const int n = K.npts, Mm = K.M;
+      const double* cc = tab + K.tab_off;
+      const double* w = cc + 3 * n;
+      const double* gY = acc + K.acc_off;
+      const double* gC = gY + n + 4;
+      const double* LU = aux + aux_skin0(M) + K.aux_off;
+      const double* piv = LU + Mm * Mm;
+      for (int i = 0; i < Mm; ++i) lam[i] = gY[i];
+      lu_solve(LU, piv, lam, Mm);   // symmetric system: A^-T gY = A^-1 gY
+      D3 la = Mm == n + 4 ? d3(lam[n + 1], lam[n + 2], lam[n + 3]) : d3(0, 0, 0);
+      D3 av = d3(w[n + 1], w[n + 2], w[n + 3]);
+      for (int i = 0; i < n; ++i) {
+        D3 ci = d3(cc[3 * i], cc[3 * i + 1], cc[3 * i + 2]);
+        D3 Gi = d3(gC[3 * i], gC[3 * i + 1], gC[3 * i + 2]);
+        for (int j = 0; j < n; ++j) {
+          D3 u = ci - d3(cc[3 * j], cc[3 * j + 1], cc[3 * j + 2]);
+          double r = sqrt(dot(u, u));
+          Gi = Gi - u * (3.0 * r * (lam[i] * w[j] + lam[j] * w[i]));
+        }
+        Gi = Gi - av * lam[i] - la * w[i];
+        int b = M.skin_pt_body[K.pt_off + i];
+        if (b >= 0) {
+          D3 m = cross(ci, Gi);
+          F[3 * b] += Gi.x; F[3 * b + 1] += Gi.y; F[3 * b + 2] += Gi.z;
+          Mo[3 * b] += m.x; Mo[3 * b + 1] += m.y; Mo[3 * b + 2] += m.z;
+        }
+        if (K.kind == SURF_DEFORMABLE_SKIN && i < K.nsurf) {
+          D3 gd = b >= 0 ? xf_rotT(aux + aux_X(M, b), Gi) : Gi;
+          double* o = grad + M.nq + K.deform_off + 3 * i;
+          o[0] += gd.x; o[1] += gd.y; o[2] += gd.z;
+        }
+      }
+    }
+    for (int b = nb - 1; b >= 0; --b) {  // subtree wrenches: children follow parents
+      int p = M.body[b].parent;
+      if (p >= 0) for (int k = 0; k < 3; ++k) { F[3 * p + k] += F[3 * b + k]; Mo[3 * p + k] += Mo[3 * b + k]; }
+    }
+    for (int b = 0; b < nb; ++b) {
+      const BodyC& B = M.body[b];
+      if (B.jtype == JOINT_FIXED) continue;
+      const double* P = aux + aux_P(M, b);
+      D3 Fb = d3(F[3 * b], F[3 * b + 1], F[3 * b + 2]), Mb = d3(Mo[3 * b], Mo[3 * b + 1], Mo[3 * b + 2]);
+      if (B.jtype == JOINT_REVOLUTE) {
+        D3 wv = xf_rot(P, d3(B.axis[0], B.axis[1], B.axis[2]));
+        grad[B.qoff] += dot(wv, Mb - cross(xf_t(P), Fb));
+      } else {
+        const double* Xb = aux + aux_X(M, b);
+        D3 Gp = xf_rotT(P, Mb - cross(xf_t(Xb), Fb));
+        D3 Fp = xf_rotT(P, Fb);
+        const double nrm = aux[aux_qnorm(M, b)];
+        const double* q = x + B.qoff;
+        const double qw = q[0] / nrm;
+        D3 v = d3(q[1] / nrm, q[2] / nrm, q[3] / nrm);
+        D3 gv = Gp * qw + cross(Gp, v);
+        const double inv = 2.0 / nrm;
+        grad[B.qoff] += -dot(Gp, v) * inv;
+        grad[B.qoff + 1] += gv.x * inv; grad[B.qoff + 2] += gv.y * inv; grad[B.qoff + 3] += gv.z * inv;
+        grad[B.qoff + 4] += Fp.x; grad[B.qoff + 5] += Fp.y; grad[B.qoff + 6] += Fp.z;
+      }
+    }
+  }
+  double reg = 0;
+  for (int k = M.nq; k < M.nx; ++k) { reg += x[k] * x[k]; if (grad) grad[k] += 2.0 * w_def * x[k]; }
+  *cost = c + w_def * reg;
+}
+
+}  // namespace flashdev

@@ -1,0 +1,470 @@
+// flash_kernels.cuh -- the CUDA kernels of libflashsdf (sm_100a).
+//
+//   prepare_kernel   one warp per config: FK, convex world->geometry transforms, RBF control points,
+//                    fp64 LU of the Turk-O'Brien system (rows A3, A4, A7, A10)
+//   cost_kernel      the hot loop (rows A5, A6, A7, A8): points x configs -> per-config accumulators
+//                    (cost, per-body wrenches, RBF adjoint sums); also serves skin_eval (DIST mode)
+//   epilogue_kernel  adjoint RBF solve + wrench -> joint-space gradient (replaces ForwardDiff's
+//                    ceil(nx/10) dual passes with one pass)
+//   raycast kernels  batched ray marching of the same field (row A9) + order-preserving compaction
+//   gd_step_kernel   NaiveSolver update for the on-device estimate_state loop (row F1)
+//   grid kernels     SDF grid baking / error sampling for FLASH_SDF_GRID
+//
+// Design notes (B200): tensor cores are not used (no dense contraction on this path).  Points are
+// read as coalesced float4; hull geometry, the config's transforms and RBF tables are staged in
+// shared memory once per block; reductions are warp shuffles -> per-warp shared accumulators ->
+// one fp64 atomicAdd per accumulator per block.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "flash_dev.h"
+
+namespace flashk {
+
+using namespace flashdev;
+
+constexpr int BLOCK = 256;
+constexpr int WARPS = BLOCK / 32;
+constexpr int QENT = 8;  // doubles per skin-queue entry: x y z s ginv nhx nhy nhz (slot in a side array)
+
+struct CostParams {
+  const HotModel* hot;
+  const F4* geo_f4;
+  const uint32_t* geo_u32;
+  const float* grid_pool;
+  int geo_f4_n, geo_u32_n;
+  const float4* pts;
+  long long n_pts;
+  const double* tab;   // [C][tab_len]
+  double* acc;         // [C][acc_len]
+  int32_t* argmin;     // [C][n_pts] or null
+  double* dist;        // [n_pts] (DIST mode, C == 1)
+  int pts_per_block;
+  int use_grid;
+};
+
+__host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
+
+// dynamic shared memory layout of cost_kernel / raycast_kernel
+struct SmemLayout {
+  size_t off_hot, off_f4, off_u32, off_tab, off_acc, off_lb, off_queue, off_qslot, total;
+};
+__host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, int tab_len, int acc_len, int n_convex, bool grad_skins) {
+  SmemLayout L;
+  size_t o = 0;
+  L.off_hot = o; o = align16(o + sizeof(HotModel));
+  L.off_f4 = o; o = align16(o + sizeof(F4) * (size_t)geo_f4_n);
+  L.off_u32 = o; o = align16(o + sizeof(uint32_t) * (size_t)geo_u32_n);
+  L.off_tab = o; o = align16(o + sizeof(double) * (size_t)tab_len);
+  L.off_acc = o; o = align16(o + sizeof(double) * (size_t)acc_len * WARPS);
+  L.off_lb = o; o = align16(o + sizeof(float) * (size_t)(n_convex > 0 ? n_convex : 1) * BLOCK);
+  L.off_queue = o; o = align16(o + (grad_skins ? sizeof(double) * QENT * 32 * WARPS : 0));
+  L.off_qslot = o; o = align16(o + (grad_skins ? sizeof(int) * 32 * WARPS : 0));
+  L.total = o;
+  return L;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) prepare_kernel(const ModelC* __restrict__ Mp, const double* __restrict__ X, double* __restrict__ tab_all,
+                                                      double* __restrict__ aux_all, int* __restrict__ status) {
+  const ModelC& M = *Mp;
+  const int c = blockIdx.x, lane = threadIdx.x;
+  const double* x = X + (size_t)c * M.nx;
+  double* tab = tab_all + (size_t)c * M.tab_len;
+  double* aux = aux_all + (size_t)c * M.aux_len;
+  if (lane == 0) {
+    fk_config(M, x, aux);
+    prepare_convex(M, aux, tab);
+    for (int k = 0; k < M.n_skins; ++k) skin_centres(M, M.skin[k], x, aux, tab);
+  }
+  __syncwarp();
+  for (int k = 0; k < M.n_skins; ++k) {
+    const SkinC& K = M.skin[k];
+    double* LU = aux + aux_skin0(M) + K.aux_off;
+    skin_assemble(M, K, tab, LU, lane, 32);
+    __syncwarp();
+    int ok = lu_factor(LU, LU + K.M * K.M, K.M, lane, 32);
+    if (!ok && lane == 0) atomicExch(status, 1);  // singular RBF system (coincident control points)
+    __syncwarp();
+    if (lane == 0) skin_solve(M, K, LU, LU + K.M * K.M, tab);
+    __syncwarp();
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// stage model + geometry + this config's table in shared memory
+__device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayout& L, const HotModel* hot, const F4* geo_f4, int nf4,
+                                            const uint32_t* geo_u32, int nu32, const double* tab, int tab_len) {
+  const int tid = threadIdx.x;
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(hot);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(smem + L.off_hot);
+    for (int i = tid; i < (int)(sizeof(HotModel) / 4); i += BLOCK) dst[i] = src[i];
+  }
+  {
+    const float4* src = reinterpret_cast<const float4*>(geo_f4);
+    float4* dst = reinterpret_cast<float4*>(smem + L.off_f4);
+    for (int i = tid; i < nf4; i += BLOCK) dst[i] = __ldg(src + i);
+  }
+  {
+    uint32_t* dst = reinterpret_cast<uint32_t*>(smem + L.off_u32);
+    for (int i = tid; i < nu32; i += BLOCK) dst[i] = __ldg(geo_u32 + i);
+  }
+  {
+    double* dst = reinterpret_cast<double*>(smem + L.off_tab);
+    for (int i = tid; i < tab_len; i += BLOCK) dst[i] = tab[i];
+  }
+}
+
+// GRAD: accumulate gradient terms; ARGMIN: write the argmin surface per point; DIST: write the
+// min distance per point (skin_eval entry) and skip all accumulation.
+template <bool GRAD, bool ARGMIN, bool DIST>
+__global__ void __launch_bounds__(BLOCK, 2) cost_kernel(const CostParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int c = blockIdx.x;
+  // every block re-derives the layout from the same numbers the host used
+  const HotModel* hot_g = p.hot;
+  const int tab_len = hot_g->tab_len, acc_len = hot_g->acc_len, n_convex = hot_g->n_convex;
+  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, tab_len, acc_len, n_convex, GRAD && hot_g->n_skins > 0);
+  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab + (size_t)c * tab_len, tab_len);
+  double* acc_w = reinterpret_cast<double*>(smem + L.off_acc) + (size_t)warp * acc_len;
+  if (!DIST) for (int i = lane; i < acc_len; i += 32) acc_w[i] = 0.0;
+  __syncthreads();
+  const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
+  GeoView G;
+  G.f4 = reinterpret_cast<const F4*>(smem + L.off_f4);
+  G.u32 = reinterpret_cast<const uint32_t*>(smem + L.off_u32);
+  G.grid_pool = p.grid_pool;
+  const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
+  float* lb = reinterpret_cast<float*>(smem + L.off_lb) + tid;
+  double* queue = reinterpret_cast<double*>(smem + L.off_queue) + (size_t)warp * 32 * QENT;
+  int* qslot = reinterpret_cast<int*>(smem + L.off_qslot) + warp * 32;
+
+  const long long tile0 = (long long)blockIdx.y * p.pts_per_block;
+  long long tile1 = tile0 + p.pts_per_block;
+  if (tile1 > p.n_pts) tile1 = p.n_pts;
+  double cost_local = 0.0;
+
+  for (long long base = tile0; base < tile1; base += BLOCK) {
+    const long long i = base + tid;
+    const bool valid = i < tile1;
+    PointEval e;
+    e.d = 0.f; e.arg = -1; e.slot = -1; e.is_skin = 0;
+    float px = 0.f, py = 0.f, pz = 0.f;
+    if (valid) {
+      const float4 P = __ldg(p.pts + i);
+      px = P.x; py = P.y; pz = P.z;
+      eval_point(H, G, tab, px, py, pz, lb, BLOCK, p.use_grid != 0, e);
+    }
+    if (DIST) {
+      if (valid) {
+        p.dist[i] = e.is_skin ? e.sk.s : (double)e.d;
+        if (ARGMIN) p.argmin[i] = e.arg;
+      }
+      continue;
+    }
+    if (ARGMIN && valid) p.argmin[(size_t)c * p.n_pts + i] = e.arg;
+    if (valid) { const double dv = e.is_skin ? e.sk.s : (double)e.d; cost_local = fma(dv, dv, cost_local); }
+    if (!GRAD) continue;
+
+    // ---- convex winners: per-body wrench in the geometry frame, g = -2 d n, tau = y x g
+    const bool isc = valid && !e.is_skin && e.slot >= 0;
+    unsigned remaining = __ballot_sync(0xffffffffu, isc);
+    while (remaining) {
+      const int leader = __ffs(remaining) - 1;
+      const int j = __shfl_sync(0xffffffffu, e.slot, leader);
+      const bool mine = isc && e.slot == j;
+      const unsigned m = __ballot_sync(0xffffffffu, mine);
+      const float g = mine ? -2.f * e.d : 0.f;
+      float v0 = g * e.n.x, v1 = g * e.n.y, v2 = g * e.n.z;
+      float t0 = e.y.y * v2 - e.y.z * v1, t1 = e.y.z * v0 - e.y.x * v2, t2 = e.y.x * v1 - e.y.y * v0;
+      v0 = warp_sum(v0); v1 = warp_sum(v1); v2 = warp_sum(v2);
+      t0 = warp_sum(t0); t1 = warp_sum(t1); t2 = warp_sum(t2);
+      if (lane == 0) {
+        double* a = acc_w + 1 + 6 * j;
+        a[0] += (double)v0; a[1] += (double)v1; a[2] += (double)v2;
+        a[3] += (double)t0; a[4] += (double)t1; a[5] += (double)t2;
+      }
+      remaining &= ~m;
+    }
+
+    // ---- skin winners: queue them per warp, then lanes = control points (no shuffles)
+    if (H.n_skins > 0) {
+      const bool iss = valid && e.is_skin;
+      const unsigned ms = __ballot_sync(0xffffffffu, iss);
+      if (ms) {
+        if (iss) {
+          const int pos = __popc(ms & ((1u << lane) - 1u));
+          double* q = queue + pos * QENT;
+          q[0] = (double)px; q[1] = (double)py; q[2] = (double)pz;
+          q[3] = e.sk.s; q[4] = e.sk.ginv; q[5] = e.sk.nh.x; q[6] = e.sk.nh.y; q[7] = e.sk.nh.z;
+          qslot[pos] = e.slot;
+        }
+        __syncwarp();
+        const int cnt = __popc(ms);
+        for (int k = 0; k < H.n_skins; ++k) {
+          const SkinC& K = H.skin[k];
+          const double* cc = tab + K.tab_off;
+          const int n = K.npts;
+          for (int ci = lane; ci <= n; ci += 32) {
+            double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+            for (int qe = 0; qe < cnt; ++qe) {
+              if (qslot[qe] != k) continue;
+              const double* q = queue + qe * QENT;
+              double o[4];
+              skin_adjoint_term(cc, cc + 3 * n, n, H.normalize != 0, ci, q[0], q[1], q[2], q[3], q[4], d3(q[5], q[6], q[7]), o);
+              a0 += o[0]; a1 += o[1]; a2 += o[2]; a3 += o[3];
+            }
+            double* gY = acc_w + K.acc_off;
+            if (ci < n) { gY[ci] += a0; double* gC = gY + n + 4 + 3 * ci; gC[0] += a1; gC[1] += a2; gC[2] += a3; }
+            else { gY[n] += a0; gY[n + 1] += a1; gY[n + 2] += a2; gY[n + 3] += a3; }
+          }
+        }
+        __syncwarp();
+      }
+    }
+  }
+  if (DIST) return;
+  cost_local = warp_sum(cost_local);
+  if (lane == 0) acc_w[0] += cost_local;
+  __syncthreads();
+  const double* acc_all = reinterpret_cast<const double*>(smem + L.off_acc);
+  const int nacc = GRAD ? acc_len : 1;
+  for (int l = tid; l < nacc; l += BLOCK) {
+    double s = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) s += acc_all[(size_t)w * acc_len + l];
+    if (s != 0.0) atomicAdd(p.acc + (size_t)c * acc_len + l, s);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) epilogue_kernel(const ModelC* __restrict__ Mp, const double* __restrict__ X, const double* __restrict__ tab_all,
+                                                       const double* __restrict__ aux_all, const double* __restrict__ acc_all, int C, double w_def,
+                                                       double* __restrict__ cost, double* __restrict__ grad /* may be null */) {
+  const ModelC& M = *Mp;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  // one thread per config; scratch in local memory (a few hundred doubles)
+  double scratch[6 * MAX_BODIES + MAX_SKIN_M];
+  epilogue_config(M, X + (size_t)c * M.nx, tab_all + (size_t)c * M.tab_len, aux_all + (size_t)c * M.aux_len, acc_all + (size_t)c * M.acc_len, w_def,
+                  scratch, cost + c, grad ? grad + (size_t)c * M.nx : nullptr);
+}
+
+// ------------------------------------------------------------------------------------------------
+// fp64 [n][3] (the memory of a Julia Vector{SVector{3,Float64}}) -> float4, rounded once
+__global__ void convert_points_f64(const double* __restrict__ src, float4* __restrict__ dst, long long n) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = make_float4((float)src[3 * i], (float)src[3 * i + 1], (float)src[3 * i + 2], 0.f);
+}
+__global__ void convert_points_f32(const float* __restrict__ src, float4* __restrict__ dst, long long n) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = make_float4(src[3 * i], src[3 * i + 1], src[3 * i + 2], 0.f);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Ray marching (doRaycast, src/depthsensors.jl:56-81): one thread per ray, march state in fp64, the
+// field evaluated by the same eval_point as the cost path.  rays are sensor-frame, cam = [R|t] rowmajor.
+struct RayParams {
+  const HotModel* hot;
+  const F4* geo_f4;
+  const uint32_t* geo_u32;
+  const float* grid_pool;
+  int geo_f4_n, geo_u32_n;
+  const double* tab;      // config 0
+  const double* rays;     // [R][3]
+  long long R;
+  double cam[12];
+  double* depths;         // [R], NaN = miss
+  int* block_hits;        // [gridDim.x]
+  int use_grid;
+};
+
+__device__ __forceinline__ double field_at(const HotModel& H, const GeoView& G, const double* tab, double ox, double oy, double oz,
+                                            double rx, double ry, double rz, double dist, float* lb, int use_grid) {
+  PointEval e;
+  eval_point(H, G, tab, (float)fma(dist, rx, ox), (float)fma(dist, ry, oy), (float)fma(dist, rz, oz), lb, BLOCK, use_grid != 0, e);
+  return e.is_skin ? e.sk.s : (double)e.d;
+}
+
+__global__ void __launch_bounds__(BLOCK, 2) raycast_kernel(const RayParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int tid = threadIdx.x;
+  const HotModel* hot_g = p.hot;
+  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, hot_g->tab_len, 0, hot_g->n_convex, false);
+  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab, hot_g->tab_len);
+  __syncthreads();
+  const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
+  GeoView G;
+  G.f4 = reinterpret_cast<const F4*>(smem + L.off_f4);
+  G.u32 = reinterpret_cast<const uint32_t*>(smem + L.off_u32);
+  G.grid_pool = p.grid_pool;
+  const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
+  float* lb = reinterpret_cast<float*>(smem + L.off_lb) + tid;
+  const long long i = (long long)blockIdx.x * BLOCK + tid;
+  bool hit = false;
+  if (i < p.R) {
+    // rays_in_world (:83-86) then normalize (:93)
+    double sx = p.rays[3 * i], sy = p.rays[3 * i + 1], sz = p.rays[3 * i + 2];
+    double rx = p.cam[0] * sx + p.cam[1] * sy + p.cam[2] * sz;
+    double ry = p.cam[4] * sx + p.cam[5] * sy + p.cam[6] * sz;
+    double rz = p.cam[8] * sx + p.cam[9] * sy + p.cam[10] * sz;
+    const double inv = 1.0 / sqrt(rx * rx + ry * ry + rz * rz);
+    rx *= inv; ry *= inv; rz *= inv;
+    const double ox = p.cam[3], oy = p.cam[7], oz = p.cam[11];
+    const double EPS = 1e-5, SAFE_RATE = 0.4;
+    double dist = 0.0, est = -1.0;
+    double last = field_at(H, G, tab, ox, oy, oz, rx, ry, rz, dist, lb, p.use_grid);
+    int k = 0;
+    while (fabs(last) > EPS && k < 60) {
+      double step = -last / est;
+      const double sg = step > 0 ? 1.0 : (step < 0 ? -1.0 : 0.0);
+      step = sg * fmin(SAFE_RATE, fabs(step));
+      dist += step;
+      const double v = field_at(H, G, tab, ox, oy, oz, rx, ry, rz, dist, lb, p.use_grid);
+      est = (v - last) / step;
+      last = v;
+      ++k;
+    }
+    // the reference re-evaluates the field at the final sample; `last` is that value
+    hit = !(fabs(last) > 1000 * EPS);
+    p.depths[i] = hit ? dist : __longlong_as_double(0x7ff8000000000000LL);
+  }
+  const int cnt = __syncthreads_count(hit);
+  if (tid == 0) p.block_hits[blockIdx.x] = cnt;
+}
+
+// exclusive scan of per-block hit counts (single block; nblocks up to a few thousand)
+__global__ void scan_blocks_kernel(int* __restrict__ counts, int n, long long* __restrict__ total) {
+  __shared__ int carry;
+  __shared__ int wsum[32];
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < n; base += blockDim.x) {
+    const int i = base + threadIdx.x;
+    int v = i < n ? counts[i] : 0;
+    int x = v;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) wsum[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      int s = lane < (int)(blockDim.x >> 5) ? wsum[lane] : 0;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
+      wsum[lane] = s;
+    }
+    __syncthreads();
+    const int prev = (w > 0 ? wsum[w - 1] : 0) + carry;
+    if (i < n) counts[i] = prev + x - v;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) carry = prev + x;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+
+// hits in ray order: sensor_tform(dist * normalize(sensor.rays[row, col])), src/depthsensors.jl:108
+__global__ void __launch_bounds__(BLOCK) compact_hits_kernel(const double* __restrict__ rays, const double* __restrict__ depths, long long R,
+                                                             const int* __restrict__ block_base, double* __restrict__ hits, float4* __restrict__ hits_f4,
+                                                             double c0, double c1, double c2, double c3, double c4, double c5, double c6, double c7,
+                                                             double c8, double c9, double c10, double c11) {
+  __shared__ int wbase[WARPS];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long long i = (long long)blockIdx.x * BLOCK + tid;
+  double d = i < R ? depths[i] : __longlong_as_double(0x7ff8000000000000LL);
+  const bool hit = d == d;
+  const unsigned m = __ballot_sync(0xffffffffu, hit);
+  if (lane == 0) wbase[warp] = __popc(m);
+  __syncthreads();
+  int base = block_base[blockIdx.x];
+  for (int w = 0; w < warp; ++w) base += wbase[w];
+  if (hit) {
+    const long long k = base + __popc(m & ((1u << lane) - 1u));
+    double sx = rays[3 * i], sy = rays[3 * i + 1], sz = rays[3 * i + 2];
+    const double s = d / sqrt(sx * sx + sy * sy + sz * sz);
+    sx *= s; sy *= s; sz *= s;
+    const double wx = c0 * sx + c1 * sy + c2 * sz + c3, wy = c4 * sx + c5 * sy + c6 * sz + c7, wz = c8 * sx + c9 * sy + c10 * sz + c11;
+    if (hits) { hits[3 * k] = wx; hits[3 * k + 1] = wy; hits[3 * k + 2] = wz; }
+    if (hits_f4) hits_f4[k] = make_float4((float)wx, (float)wy, (float)wz, 0.f);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// NaiveSolver step (see flash_estimate_state in flashsdf.h).  One thread block per config.
+__global__ void __launch_bounds__(128) gd_step_kernel(double* __restrict__ X, const double* __restrict__ grad, int nx, double inv_n, double rate, double max_step,
+                                                       double tol, const double* __restrict__ divisors, int* __restrict__ done, int* __restrict__ iters) {
+  __shared__ double red[128];
+  const int c = blockIdx.x, tid = threadIdx.x;
+  if (done[c]) return;
+  double* x = X + (size_t)c * nx;
+  const double* g = grad + (size_t)c * nx;
+  double gn = 0, sn = 0;
+  for (int k = tid; k < nx; k += blockDim.x) {
+    const double gk = g[k] * inv_n;
+    const double st = -rate * gk / (divisors ? divisors[k] : 1.0);
+    gn += gk * gk; sn += st * st;
+  }
+  red[tid] = gn; __syncthreads();
+  for (int o = 64; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
+  gn = red[0]; __syncthreads();
+  red[tid] = sn; __syncthreads();
+  for (int o = 64; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
+  sn = sqrt(red[0]);
+  if (tol > 0 && sqrt(gn) < tol) { if (tid == 0) done[c] = 1; return; }
+  const double sc = sn > max_step ? max_step / sn : 1.0;
+  for (int k = tid; k < nx; k += blockDim.x) x[k] += sc * (-rate * g[k] * inv_n / (divisors ? divisors[k] : 1.0));
+  if (tid == 0) iters[c] += 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// grid mode: bake the exact hull distance at every node of a geometry-frame grid
+__global__ void bake_grid_kernel(const HotModel* __restrict__ hot, const F4* __restrict__ geo_f4, const uint32_t* __restrict__ geo_u32, int j, float* __restrict__ pool) {
+  const ConvexC& C = hot->cvx[j];
+  const long long n = (long long)C.g_dim[0] * C.g_dim[1] * C.g_dim[2];
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int ix = (int)(i % C.g_dim[0]), iy = (int)((i / C.g_dim[0]) % C.g_dim[1]), iz = (int)(i / ((long long)C.g_dim[0] * C.g_dim[1]));
+  const float h = 1.0f / C.g_inv_h;
+  F3 y = f3(C.g_org[0] + ix * h, C.g_org[1] + iy * h, C.g_org[2] + iz * h);
+  F3 n3;
+  pool[C.g_off + i] = hull_sd(geo_f4 + C.off_planes, geo_u32 + C.off_tris, geo_f4 + C.off_verts, C.nplanes, C.nverts, y, n3);
+}
+// max |trilinear - exact| over cell centres (the worst place for trilinear interpolation)
+__global__ void grid_error_kernel(const HotModel* __restrict__ hot, const F4* __restrict__ geo_f4, const uint32_t* __restrict__ geo_u32, int j,
+                                  const float* __restrict__ pool, unsigned int* __restrict__ max_err_bits) {
+  const ConvexC& C = hot->cvx[j];
+  const int cx = C.g_dim[0] - 1, cy = C.g_dim[1] - 1, cz = C.g_dim[2] - 1;
+  const long long n = (long long)cx * cy * cz;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  float err = 0.f;
+  if (i < n) {
+    const int ix = (int)(i % cx), iy = (int)((i / cx) % cy), iz = (int)(i / ((long long)cx * cy));
+    const float h = 1.0f / C.g_inv_h;
+    F3 y = f3(C.g_org[0] + (ix + 0.5f) * h, C.g_org[1] + (iy + 0.5f) * h, C.g_org[2] + (iz + 0.5f) * h);
+    F3 n3, n4; float dg;
+    float de = hull_sd(geo_f4 + C.off_planes, geo_u32 + C.off_tris, geo_f4 + C.off_verts, C.nplanes, C.nverts, y, n3);
+    if (grid_sd(C, pool, y, dg, n4)) err = fabsf(dg - de);
+  }
+  err = fmaxf(err, __shfl_xor_sync(0xffffffffu, err, 16));
+  err = fmaxf(err, __shfl_xor_sync(0xffffffffu, err, 8));
+  err = fmaxf(err, __shfl_xor_sync(0xffffffffu, err, 4));
+  err = fmaxf(err, __shfl_xor_sync(0xffffffffu, err, 2));
+  err = fmaxf(err, __shfl_xor_sync(0xffffffffu, err, 1));
+  if ((threadIdx.x & 31) == 0 && err > 0.f) atomicMax(max_err_bits, __float_as_uint(err));
+}
+
+}  // namespace flashk

@@ -1,0 +1,637 @@
+// flashsdf.cu -- C ABI of libflashsdf (include/flashsdf.h): context, device memory, streams,
+// kernel launches, NCCL all-reduce.  There is no CPU compute path in this file or anywhere in the
+// library: without a CUDA device the compute entry points return FLASH_ERR_NO_DEVICE.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/flashsdf.h"
+#include "flash_host.h"
+#include "flash_kernels.cuh"
+
+using namespace flashdev;
+using namespace flashhost;
+using namespace flashk;
+
+// ------------------------------------------------------------------------------------------------
+// NCCL is resolved at run time (dlopen) so that single-GPU users -- the Julia host -- need no NCCL.
+namespace {
+typedef struct { char internal[128]; } nccl_uid;
+typedef void* nccl_comm;
+struct NcclApi {
+  void* handle = nullptr;
+  int (*GetUniqueId)(nccl_uid*) = nullptr;
+  int (*CommInitRank)(nccl_comm*, int, nccl_uid, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, nccl_comm, cudaStream_t) = nullptr;
+  int (*CommDestroy)(nccl_comm) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+bool load_nccl(std::string& err) {
+  if (g_nccl.handle) return true;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  void* h = nullptr;
+  for (const char* n : names) { h = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+  if (!h) { err = std::string("cannot dlopen libnccl.so.2: ") + dlerror(); return false; }
+  NcclApi a; a.handle = h;
+  a.GetUniqueId = (int (*)(nccl_uid*))dlsym(h, "ncclGetUniqueId");
+  a.CommInitRank = (int (*)(nccl_comm*, int, nccl_uid, int))dlsym(h, "ncclCommInitRank");
+  a.AllReduce = (int (*)(const void*, void*, size_t, int, int, nccl_comm, cudaStream_t))dlsym(h, "ncclAllReduce");
+  a.CommDestroy = (int (*)(nccl_comm))dlsym(h, "ncclCommDestroy");
+  a.GetErrorString = (const char* (*)(int))dlsym(h, "ncclGetErrorString");
+  if (!a.GetUniqueId || !a.CommInitRank || !a.AllReduce || !a.CommDestroy) { err = "libnccl.so.2 lacks required symbols"; return false; }
+  g_nccl = a;
+  return true;
+}
+constexpr int NCCL_FLOAT64 = 8, NCCL_SUM = 0;
+thread_local std::string g_create_err;
+}  // namespace
+
+struct flash_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  HostModel hm;
+  HotModel hot;
+  ModelC* d_model = nullptr;
+  HotModel* d_hot = nullptr;
+  F4* d_geo_f4 = nullptr;
+  uint32_t* d_geo_u32 = nullptr;
+  float* d_grid_pool = nullptr;
+  size_t grid_pool_floats = 0;
+  std::vector<double> grid_err;  // per convex slot
+  bool use_grid = false;
+  // points
+  float4* d_pts = nullptr; long long n_pts = 0; long long cap_pts = 0; bool pts_external = false; bool pts_set = false;
+  void* d_stage = nullptr; size_t cap_stage = 0;
+  // per-batch state
+  int cap_C = 0;
+  double *d_X = nullptr, *d_tab = nullptr, *d_aux = nullptr, *d_acc = nullptr, *d_cost = nullptr, *d_grad = nullptr, *d_div = nullptr;
+  int *d_status = nullptr, *d_done = nullptr, *d_iters = nullptr;
+  double* h_pin = nullptr; size_t cap_pin = 0;  // pinned staging for X / cost / grad
+  int32_t* d_argmin = nullptr; size_t cap_argmin = 0;
+  // query scratch (skin_eval / raycast)
+  double* d_qd = nullptr; size_t cap_qd = 0;
+  int* d_qi = nullptr; size_t cap_qi = 0;
+  // comm
+  nccl_comm comm = nullptr; int rank = 0, world = 1;
+  // measurement
+  bool profiling = false;
+  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  flash_timing last = {0, 0, 0, 0, 0, 0};
+  long long launches = 0;
+  int sm_count = 0, clock_khz = 0; long long l2_bytes = 0; int smem_optin = 0;
+  std::string err;
+};
+
+namespace {
+
+#define CU(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                               \
+      return FLASH_ERR_CUDA;                                                                       \
+    }                                                                                              \
+  } while (0)
+
+int fail(flash_ctx* ctx, int code, const std::string& msg) {
+  if (ctx) ctx->err = msg; else g_create_err = msg;
+  return code;
+}
+
+template <class T>
+int ensure(flash_ctx* ctx, T*& p, size_t& cap, size_t need) {
+  if (need <= cap) return 0;
+  if (p) CU(cudaFree(p));
+  p = nullptr; cap = 0;
+  size_t want = need + need / 8;
+  CU(cudaMalloc((void**)&p, want * sizeof(T)));
+  cap = want;
+  return 0;
+}
+
+int ensure_batch(flash_ctx* ctx, int C) {
+  if (C <= ctx->cap_C) return 0;
+  const ModelC& M = ctx->hm.M;
+  double** ptrs[] = {&ctx->d_X, &ctx->d_tab, &ctx->d_aux, &ctx->d_acc, &ctx->d_cost, &ctx->d_grad};
+  for (auto pp : ptrs) if (*pp) { CU(cudaFree(*pp)); *pp = nullptr; }
+  if (ctx->d_done) { CU(cudaFree(ctx->d_done)); ctx->d_done = nullptr; }
+  if (ctx->d_iters) { CU(cudaFree(ctx->d_iters)); ctx->d_iters = nullptr; }
+  if (ctx->h_pin) { CU(cudaFreeHost(ctx->h_pin)); ctx->h_pin = nullptr; }
+  ctx->cap_C = 0;
+  const size_t c = (size_t)C;
+  CU(cudaMalloc((void**)&ctx->d_X, c * M.nx * sizeof(double)));
+  CU(cudaMalloc((void**)&ctx->d_tab, c * std::max(M.tab_len, 1) * sizeof(double)));
+  CU(cudaMalloc((void**)&ctx->d_aux, c * std::max(M.aux_len, 1) * sizeof(double)));
+  CU(cudaMalloc((void**)&ctx->d_acc, c * M.acc_len * sizeof(double)));
+  CU(cudaMalloc((void**)&ctx->d_cost, c * sizeof(double)));
+  CU(cudaMalloc((void**)&ctx->d_grad, c * M.nx * sizeof(double)));
+  CU(cudaMalloc((void**)&ctx->d_done, c * sizeof(int)));
+  CU(cudaMalloc((void**)&ctx->d_iters, c * sizeof(int)));
+  ctx->cap_pin = c * (2 * (size_t)M.nx + 2);
+  CU(cudaHostAlloc((void**)&ctx->h_pin, ctx->cap_pin * sizeof(double), cudaHostAllocDefault));
+  ctx->cap_C = C;
+  return 0;
+}
+
+SmemLayout cost_layout(const flash_ctx* ctx, bool grad) {
+  const ModelC& M = ctx->hm.M;
+  return smem_layout(M.geo_f4, M.geo_u32, M.tab_len, M.acc_len, M.n_convex, grad && M.n_skins > 0);
+}
+
+template <bool G, bool A, bool D>
+int launch_cost_t(flash_ctx* ctx, const CostParams& p, int C, int tiles, size_t smem) {
+  auto k = cost_kernel<G, A, D>;
+  if (smem > 48 * 1024) CU(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  dim3 grid((unsigned)C, (unsigned)tiles);
+  k<<<grid, BLOCK, smem, ctx->stream>>>(p);
+  CU(cudaGetLastError());
+  ctx->launches++; ctx->last.launches++;
+  return 0;
+}
+
+// points per block: enough blocks for >= ~4 waves, at most 4096 points, at least one batch
+int choose_tile(const flash_ctx* ctx, long long n, int C) {
+  const long long target_blocks = (long long)ctx->sm_count * 2 * 4;
+  long long ppb = (n * C + target_blocks - 1) / target_blocks;
+  ppb = ((ppb + BLOCK - 1) / BLOCK) * BLOCK;
+  if (ppb < BLOCK) ppb = BLOCK;
+  if (ppb > 4096) ppb = 4096;
+  while ((n + ppb - 1) / ppb > 65535) ppb *= 2;
+  return (int)ppb;
+}
+
+int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin) {
+  const ModelC& M = ctx->hm.M;
+  CostParams p;
+  p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
+  p.geo_f4_n = M.geo_f4; p.geo_u32_n = M.geo_u32;
+  p.pts = ctx->d_pts; p.n_pts = ctx->n_pts; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = d_argmin; p.dist = nullptr;
+  p.pts_per_block = choose_tile(ctx, ctx->n_pts, C);
+  p.use_grid = ctx->use_grid ? 1 : 0;
+  if (ctx->n_pts == 0) return 0;
+  const int tiles = (int)((ctx->n_pts + p.pts_per_block - 1) / p.pts_per_block);
+  const size_t smem = cost_layout(ctx, grad).total;
+  if (smem > (size_t)ctx->smem_optin) return fail(ctx, FLASH_ERR_TOO_LARGE, "model geometry does not fit in shared memory (" + std::to_string(smem) + " bytes)");
+  if (grad) return d_argmin ? launch_cost_t<true, true, false>(ctx, p, C, tiles, smem) : launch_cost_t<true, false, false>(ctx, p, C, tiles, smem);
+  return d_argmin ? launch_cost_t<false, true, false>(ctx, p, C, tiles, smem) : launch_cost_t<false, false, false>(ctx, p, C, tiles, smem);
+}
+
+int run_prepare(flash_ctx* ctx, int C) {
+  prepare_kernel<<<C, 32, 0, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_status);
+  CU(cudaGetLastError());
+  ctx->launches++; ctx->last.launches++;
+  return 0;
+}
+
+int run_epilogue(flash_ctx* ctx, int C, double w_def, bool grad) {
+  epilogue_kernel<<<(C + 31) / 32, 32, 0, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, C, w_def, ctx->d_cost, grad ? ctx->d_grad : nullptr);
+  CU(cudaGetLastError());
+  ctx->launches++; ctx->last.launches++;
+  return 0;
+}
+
+int run_allreduce(flash_ctx* ctx, int C) {
+  if (!ctx->comm) return 0;
+  int rc = g_nccl.AllReduce(ctx->d_acc, ctx->d_acc, (size_t)C * ctx->hm.M.acc_len, NCCL_FLOAT64, NCCL_SUM, ctx->comm, ctx->stream);
+  if (rc != 0) return fail(ctx, FLASH_ERR_NCCL, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
+  return 0;
+}
+
+// prepare -> main -> (allreduce) -> epilogue on the ctx stream, X already on the device
+int pipeline(flash_ctx* ctx, int C, double w_def, bool grad, int32_t* d_argmin) {
+  const ModelC& M = ctx->hm.M;
+  int rc;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[0], ctx->stream));
+  CU(cudaMemsetAsync(ctx->d_acc, 0, (size_t)C * M.acc_len * sizeof(double), ctx->stream));
+  if ((rc = run_prepare(ctx, C))) return rc;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[1], ctx->stream));
+  if ((rc = run_cost(ctx, C, grad, d_argmin))) return rc;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
+  if ((rc = run_allreduce(ctx, C))) return rc;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[3], ctx->stream));
+  if ((rc = run_epilogue(ctx, C, w_def, grad))) return rc;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[4], ctx->stream));
+  return 0;
+}
+
+int collect_timing(flash_ctx* ctx) {
+  if (!ctx->profiling) return 0;
+  CU(cudaEventSynchronize(ctx->ev[4]));
+  CU(cudaEventElapsedTime(&ctx->last.ms_prepare, ctx->ev[0], ctx->ev[1]));
+  CU(cudaEventElapsedTime(&ctx->last.ms_main, ctx->ev[1], ctx->ev[2]));
+  CU(cudaEventElapsedTime(&ctx->last.ms_allreduce, ctx->ev[2], ctx->ev[3]));
+  CU(cudaEventElapsedTime(&ctx->last.ms_epilogue, ctx->ev[3], ctx->ev[4]));
+  CU(cudaEventElapsedTime(&ctx->last.ms_total, ctx->ev[0], ctx->ev[4]));
+  return 0;
+}
+
+int check_status(flash_ctx* ctx) {
+  int st = 0;
+  CU(cudaMemcpyAsync(&st, ctx->d_status, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (st != 0) {
+    CU(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), ctx->stream));
+    return fail(ctx, FLASH_ERR_INVALID, "singular RBF system (coincident skin control points)");
+  }
+  return 0;
+}
+
+// grid mode: allocate + bake body-frame SDF grids for every convex surface
+int bake_grids(flash_ctx* ctx) {
+  ModelC& M = ctx->hm.M;
+  const double h = ctx->hm.opt.grid_spacing, margin = ctx->hm.opt.grid_margin;
+  size_t total = 0;
+  for (int j = 0; j < M.n_convex; ++j) {
+    ConvexC& C = M.cvx[j];
+    long long cells = 1;
+    for (int k = 0; k < 3; ++k) {
+      C.g_org[k] = (float)(C.lo[k] - margin);
+      C.g_dim[k] = (int)std::ceil((C.hi[k] - C.lo[k] + 2 * margin) / h) + 1;
+      cells *= C.g_dim[k];
+    }
+    if (cells > (1ll << 31)) return fail(ctx, FLASH_ERR_TOO_LARGE, "SDF grid too large; increase grid_spacing");
+    C.g_inv_h = (float)(1.0 / h);
+    C.g_off = (long long)total;
+    C.g_on = 1;
+    total += (size_t)cells;
+  }
+  if (total * sizeof(float) > (size_t)64 << 30) return fail(ctx, FLASH_ERR_TOO_LARGE, "SDF grids exceed 64 GiB; increase grid_spacing");
+  CU(cudaMalloc((void**)&ctx->d_grid_pool, std::max<size_t>(total, 1) * sizeof(float)));
+  ctx->grid_pool_floats = total;
+  make_hot(M, ctx->hot);
+  CU(cudaMemcpy(ctx->d_model, &M, sizeof(ModelC), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(ctx->d_hot, &ctx->hot, sizeof(HotModel), cudaMemcpyHostToDevice));
+  unsigned int* d_err = nullptr;
+  CU(cudaMalloc((void**)&d_err, sizeof(unsigned int) * std::max(M.n_convex, 1)));
+  CU(cudaMemset(d_err, 0, sizeof(unsigned int) * std::max(M.n_convex, 1)));
+  for (int j = 0; j < M.n_convex; ++j) {
+    const ConvexC& C = M.cvx[j];
+    long long n = (long long)C.g_dim[0] * C.g_dim[1] * C.g_dim[2];
+    bake_grid_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_hot, ctx->d_geo_f4, ctx->d_geo_u32, j, ctx->d_grid_pool);
+    CU(cudaGetLastError());
+    long long nc = (long long)(C.g_dim[0] - 1) * (C.g_dim[1] - 1) * (C.g_dim[2] - 1);
+    grid_error_kernel<<<(unsigned)((nc + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_hot, ctx->d_geo_f4, ctx->d_geo_u32, j, ctx->d_grid_pool, d_err + j);
+    CU(cudaGetLastError());
+    ctx->launches += 2;
+  }
+  std::vector<unsigned int> bits(std::max(M.n_convex, 1));
+  CU(cudaMemcpyAsync(bits.data(), d_err, sizeof(unsigned int) * bits.size(), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  CU(cudaFree(d_err));
+  ctx->grid_err.assign(M.n_convex, 0.0);
+  for (int j = 0; j < M.n_convex; ++j) { float f; std::memcpy(&f, &bits[j], 4); ctx->grid_err[j] = f; }
+  ctx->use_grid = true;
+  return 0;
+}
+
+}  // namespace
+
+// ================================================================================================
+extern "C" {
+
+void flash_options_default(flash_options* opt) { if (opt) options_default(opt); }
+int flash_abi_version(void) { return FLASHSDF_ABI_VERSION; }
+const char* flash_last_error(const flash_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int flash_model_create(const flash_model_desc* desc, const flash_options* opt, flash_ctx** out) {
+  if (!out) return fail(nullptr, FLASH_ERR_INVALID, "null out pointer");
+  *out = nullptr;
+  flash_ctx* ctx = new flash_ctx;
+  std::string err;
+  if (!build_model(desc, opt, ctx->hm, err)) { delete ctx; return fail(nullptr, FLASH_ERR_INVALID, err); }
+  make_hot(ctx->hm.M, ctx->hot);
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    delete ctx;
+    return fail(nullptr, FLASH_ERR_NO_DEVICE, std::string("no CUDA device (libflashsdf has no CPU path): ") + cudaGetErrorString(e));
+  }
+  int dev = ctx->hm.opt.device;
+  if (dev < 0) { if (cudaGetDevice(&dev) != cudaSuccess) dev = 0; }
+  if (dev >= ndev) { delete ctx; return fail(nullptr, FLASH_ERR_INVALID, "device ordinal out of range"); }
+  ctx->device = dev;
+  auto bail = [&](int rc) { g_create_err = ctx->err; flash_destroy(ctx); return rc; };
+#define CUC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_); return bail(FLASH_ERR_CUDA); } } while (0)
+  CUC(cudaSetDevice(dev));
+  cudaDeviceProp prop;
+  CUC(cudaGetDeviceProperties(&prop, dev));
+  ctx->sm_count = prop.multiProcessorCount; ctx->l2_bytes = prop.l2CacheSize; ctx->smem_optin = (int)prop.sharedMemPerBlockOptin;
+  int khz = 0; cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev); ctx->clock_khz = khz;
+  CUC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  for (auto& ev : ctx->ev) CUC(cudaEventCreate(&ev));
+  const ModelC& M = ctx->hm.M;
+  CUC(cudaMalloc((void**)&ctx->d_model, sizeof(ModelC)));
+  CUC(cudaMalloc((void**)&ctx->d_hot, sizeof(HotModel)));
+  CUC(cudaMalloc((void**)&ctx->d_geo_f4, std::max<size_t>(M.geo_f4, 1) * sizeof(F4)));
+  CUC(cudaMalloc((void**)&ctx->d_geo_u32, std::max<size_t>(M.geo_u32, 1) * sizeof(uint32_t)));
+  CUC(cudaMalloc((void**)&ctx->d_status, sizeof(int)));
+  CUC(cudaMemset(ctx->d_status, 0, sizeof(int)));
+  CUC(cudaMemcpy(ctx->d_model, &M, sizeof(ModelC), cudaMemcpyHostToDevice));
+  CUC(cudaMemcpy(ctx->d_hot, &ctx->hot, sizeof(HotModel), cudaMemcpyHostToDevice));
+  if (M.geo_f4) CUC(cudaMemcpy(ctx->d_geo_f4, ctx->hm.geo_f4.data(), M.geo_f4 * sizeof(F4), cudaMemcpyHostToDevice));
+  if (M.geo_u32) CUC(cudaMemcpy(ctx->d_geo_u32, ctx->hm.geo_u32.data(), M.geo_u32 * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  const size_t smem = cost_layout(ctx, true).total;
+  if (smem > (size_t)ctx->smem_optin) { ctx->err = "model geometry does not fit in shared memory (" + std::to_string(smem) + " bytes)"; return bail(FLASH_ERR_TOO_LARGE); }
+  if (ctx->hm.opt.sdf_mode == FLASH_SDF_GRID) { int rc = bake_grids(ctx); if (rc) return bail(rc); }
+#undef CUC
+  *out = ctx;
+  return FLASH_OK;
+}
+
+void flash_destroy(flash_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
+  void* frees[] = {ctx->d_model, ctx->d_hot, ctx->d_geo_f4, ctx->d_geo_u32, ctx->d_grid_pool, ctx->pts_external ? nullptr : (void*)ctx->d_pts, ctx->d_stage,
+                   ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, ctx->d_cost, ctx->d_grad, ctx->d_div, ctx->d_status, ctx->d_done, ctx->d_iters,
+                   ctx->d_argmin, ctx->d_qd, ctx->d_qi};
+  for (void* p : frees) if (p) cudaFree(p);
+  if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
+  for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+int flash_num_positions(const flash_ctx* ctx) { return ctx ? ctx->hm.M.nq : FLASH_ERR_INVALID; }
+int flash_num_states(const flash_ctx* ctx) { return ctx ? ctx->hm.M.nx : FLASH_ERR_INVALID; }
+int flash_num_surfaces(const flash_ctx* ctx) { return ctx ? ctx->hm.M.n_surfaces : FLASH_ERR_INVALID; }
+int64_t flash_num_points(const flash_ctx* ctx) { return ctx ? ctx->n_pts : FLASH_ERR_INVALID; }
+
+static int points_alloc(flash_ctx* ctx, int64_t n) {
+  if (ctx->pts_external) { ctx->d_pts = nullptr; ctx->cap_pts = 0; ctx->pts_external = false; }
+  if (n > ctx->cap_pts) {
+    if (ctx->d_pts) CU(cudaFree(ctx->d_pts));
+    ctx->d_pts = nullptr; ctx->cap_pts = 0;
+    CU(cudaMalloc((void**)&ctx->d_pts, (size_t)std::max<int64_t>(n, 1) * sizeof(float4)));
+    ctx->cap_pts = n;
+  }
+  return 0;
+}
+
+int flash_points_set(flash_ctx* ctx, const double* xyz, int64_t n) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set: bad arguments");
+  CU(cudaSetDevice(ctx->device));
+  int rc = points_alloc(ctx, n); if (rc) return rc;
+  if (n > 0) {
+    const size_t bytes = (size_t)n * 3 * sizeof(double);
+    if (bytes > ctx->cap_stage) { if (ctx->d_stage) CU(cudaFree(ctx->d_stage)); ctx->d_stage = nullptr; ctx->cap_stage = 0; CU(cudaMalloc(&ctx->d_stage, bytes)); ctx->cap_stage = bytes; }
+    CU(cudaMemcpyAsync(ctx->d_stage, xyz, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    convert_points_f64<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>((const double*)ctx->d_stage, ctx->d_pts, n);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    CU(cudaStreamSynchronize(ctx->stream));  // the caller may reuse xyz as soon as we return
+  }
+  ctx->n_pts = n; ctx->pts_set = true;
+  return FLASH_OK;
+}
+
+int flash_points_set_f32(flash_ctx* ctx, const float* xyz, int64_t n) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_f32: bad arguments");
+  CU(cudaSetDevice(ctx->device));
+  int rc = points_alloc(ctx, n); if (rc) return rc;
+  if (n > 0) {
+    const size_t bytes = (size_t)n * 3 * sizeof(float);
+    if (bytes > ctx->cap_stage) { if (ctx->d_stage) CU(cudaFree(ctx->d_stage)); ctx->d_stage = nullptr; ctx->cap_stage = 0; CU(cudaMalloc(&ctx->d_stage, bytes)); ctx->cap_stage = bytes; }
+    CU(cudaMemcpyAsync(ctx->d_stage, xyz, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    convert_points_f32<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>((const float*)ctx->d_stage, ctx->d_pts, n);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    CU(cudaStreamSynchronize(ctx->stream));
+  }
+  ctx->n_pts = n; ctx->pts_set = true;
+  return FLASH_OK;
+}
+
+int flash_points_set_device(flash_ctx* ctx, const void* device_float4, int64_t n) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (n < 0 || (n > 0 && !device_float4)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_device: bad arguments");
+  if (((uintptr_t)device_float4 & 15) != 0) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_device: pointer must be 16-byte aligned");
+  CU(cudaSetDevice(ctx->device));
+  if (!ctx->pts_external && ctx->d_pts) CU(cudaFree(ctx->d_pts));
+  ctx->d_pts = (float4*)device_float4; ctx->cap_pts = 0; ctx->pts_external = true;
+  ctx->n_pts = n; ctx->pts_set = true;
+  return FLASH_OK;
+}
+
+int flash_cost_grad(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad, int32_t* argmin) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!X || C < 1 || !cost) return fail(ctx, FLASH_ERR_INVALID, "flash_cost_grad: bad arguments");
+  if (!ctx->pts_set) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad: call flash_points_set first");
+  const ModelC& M = ctx->hm.M;
+  CU(cudaSetDevice(ctx->device));
+  int rc = ensure_batch(ctx, C); if (rc) return rc;
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
+  const size_t nX = (size_t)C * M.nx;
+  std::memcpy(ctx->h_pin, X, nX * sizeof(double));
+  CU(cudaMemcpyAsync(ctx->d_X, ctx->h_pin, nX * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  int32_t* d_arg = nullptr;
+  if (argmin) {
+    rc = ensure(ctx, ctx->d_argmin, ctx->cap_argmin, (size_t)C * (size_t)std::max<long long>(ctx->n_pts, 1)); if (rc) return rc;
+    d_arg = ctx->d_argmin;
+  }
+  rc = pipeline(ctx, C, w_def, grad != nullptr, d_arg); if (rc) return rc;
+  double* h_cost = ctx->h_pin + nX;
+  double* h_grad = h_cost + C;
+  CU(cudaMemcpyAsync(h_cost, ctx->d_cost, (size_t)C * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  if (grad) CU(cudaMemcpyAsync(h_grad, ctx->d_grad, nX * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  if (argmin && ctx->n_pts > 0) CU(cudaMemcpyAsync(argmin, d_arg, (size_t)C * ctx->n_pts * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  rc = check_status(ctx); if (rc) return rc;   // synchronises the stream
+  std::memcpy(cost, h_cost, (size_t)C * sizeof(double));
+  if (grad) std::memcpy(grad, h_grad, nX * sizeof(double));
+  return collect_timing(ctx);
+}
+
+int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t n, double* dist, int32_t* argmin) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!x || n < 0 || (n > 0 && (!xyz || !dist))) return fail(ctx, FLASH_ERR_INVALID, "flash_skin_eval: bad arguments");
+  if (n == 0) return FLASH_OK;
+  const ModelC& M = ctx->hm.M;
+  CU(cudaSetDevice(ctx->device));
+  int rc = ensure_batch(ctx, 1); if (rc) return rc;
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
+  CU(cudaMemcpyAsync(ctx->d_X, x, (size_t)M.nx * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  if ((rc = run_prepare(ctx, 1))) return rc;
+  // query points: [n][3] doubles -> float4 (own scratch; the frame's points stay untouched)
+  // scratch layout in doubles: xyz[3n] | pad to even | float4[n] (2 doubles each) | dist[n]
+  const size_t off_f4 = ((size_t)n * 3 + 1) & ~(size_t)1, off_dist = off_f4 + 2 * (size_t)n;
+  rc = ensure(ctx, ctx->d_qd, ctx->cap_qd, off_dist + (size_t)n); if (rc) return rc;
+  rc = ensure(ctx, ctx->d_qi, ctx->cap_qi, (size_t)n); if (rc) return rc;
+  double* d_xyz = ctx->d_qd; float4* d_f4 = (float4*)(ctx->d_qd + off_f4); double* d_dist = ctx->d_qd + off_dist;
+  CU(cudaMemcpyAsync(d_xyz, xyz, (size_t)n * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  convert_points_f64<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_xyz, d_f4, n);
+  CU(cudaGetLastError());
+  ctx->launches++; ctx->last.launches++;
+  CostParams p;
+  p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
+  p.geo_f4_n = M.geo_f4; p.geo_u32_n = M.geo_u32;
+  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist;
+  p.pts_per_block = choose_tile(ctx, n, 1); p.use_grid = ctx->use_grid ? 1 : 0;
+  const int tiles = (int)((n + p.pts_per_block - 1) / p.pts_per_block);
+  const size_t smem = cost_layout(ctx, false).total;
+  if ((rc = launch_cost_t<false, true, true>(ctx, p, 1, tiles, smem))) return rc;
+  CU(cudaMemcpyAsync(dist, d_dist, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  if (argmin) CU(cudaMemcpyAsync(argmin, ctx->d_qi, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  return check_status(ctx);
+}
+
+int flash_kinect_rays(int32_t rows, int32_t cols, double vertical_fov, double horizontal_fov, double* rays) {
+  if (rows < 1 || cols < 1 || !rays) return FLASH_ERR_INVALID;
+  kinect_rays(rows, cols, vertical_fov, horizontal_fov, rays);
+  return FLASH_OK;
+}
+
+int flash_raycast(flash_ctx* ctx, const double* x, const double* rays, int64_t R, const double cam[12], double* depths, double* hits, int64_t* nhits) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!x || R < 0 || !cam || (R > 0 && (!rays || !depths))) return fail(ctx, FLASH_ERR_INVALID, "flash_raycast: bad arguments");
+  if (nhits) *nhits = 0;
+  if (R == 0) return FLASH_OK;
+  const ModelC& M = ctx->hm.M;
+  CU(cudaSetDevice(ctx->device));
+  int rc = ensure_batch(ctx, 1); if (rc) return rc;
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
+  CU(cudaMemcpyAsync(ctx->d_X, x, (size_t)M.nx * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  if ((rc = run_prepare(ctx, 1))) return rc;
+  const int nblocks = (int)((R + BLOCK - 1) / BLOCK);
+  // scratch: rays[3R] | depths[R] | hits[3R] | total(1)
+  rc = ensure(ctx, ctx->d_qd, ctx->cap_qd, (size_t)R * 7 + 2); if (rc) return rc;
+  rc = ensure(ctx, ctx->d_qi, ctx->cap_qi, (size_t)nblocks + 2); if (rc) return rc;
+  double* d_rays = ctx->d_qd; double* d_depths = d_rays + 3 * R; double* d_hits = d_depths + R; long long* d_total = (long long*)(d_hits + 3 * R);
+  CU(cudaMemcpyAsync(d_rays, rays, (size_t)R * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  RayParams p;
+  p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
+  p.geo_f4_n = M.geo_f4; p.geo_u32_n = M.geo_u32; p.tab = ctx->d_tab; p.rays = d_rays; p.R = R;
+  for (int i = 0; i < 12; ++i) p.cam[i] = cam[i];
+  p.depths = d_depths; p.block_hits = ctx->d_qi; p.use_grid = ctx->use_grid ? 1 : 0;
+  const size_t smem = smem_layout(M.geo_f4, M.geo_u32, M.tab_len, 0, M.n_convex, false).total;
+  if (smem > 48 * 1024) CU(cudaFuncSetAttribute(raycast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[1], ctx->stream));
+  raycast_kernel<<<nblocks, BLOCK, smem, ctx->stream>>>(p);
+  CU(cudaGetLastError());
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
+  scan_blocks_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->d_qi, nblocks, d_total);
+  CU(cudaGetLastError());
+  compact_hits_kernel<<<nblocks, BLOCK, 0, ctx->stream>>>(d_rays, d_depths, R, ctx->d_qi, d_hits, nullptr, cam[0], cam[1], cam[2], cam[3], cam[4], cam[5], cam[6],
+                                                          cam[7], cam[8], cam[9], cam[10], cam[11]);
+  CU(cudaGetLastError());
+  ctx->launches += 3; ctx->last.launches += 3;
+  long long total = 0;
+  CU(cudaMemcpyAsync(depths, d_depths, (size_t)R * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaMemcpyAsync(&total, d_total, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
+  rc = check_status(ctx); if (rc) return rc;
+  if (hits && total > 0) { CU(cudaMemcpyAsync(hits, d_hits, (size_t)total * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream)); CU(cudaStreamSynchronize(ctx->stream)); }
+  if (nhits) *nhits = total;
+  if (ctx->profiling) { CU(cudaEventElapsedTime(&ctx->last.ms_main, ctx->ev[1], ctx->ev[2])); ctx->last.ms_total = ctx->last.ms_main; }
+  return FLASH_OK;
+}
+
+int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solver_params* sp, const double* divisors, double* cost_out, int32_t* iters_out) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!X || C < 1 || !sp || sp->iteration_limit < 0) return fail(ctx, FLASH_ERR_INVALID, "flash_estimate_state: bad arguments");
+  if (!ctx->pts_set) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: call flash_points_set first");
+  const ModelC& M = ctx->hm.M;
+  CU(cudaSetDevice(ctx->device));
+  int rc = ensure_batch(ctx, C); if (rc) return rc;
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
+  const size_t nX = (size_t)C * M.nx;
+  std::memcpy(ctx->h_pin, X, nX * sizeof(double));
+  CU(cudaMemcpyAsync(ctx->d_X, ctx->h_pin, nX * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaMemsetAsync(ctx->d_done, 0, (size_t)C * sizeof(int), ctx->stream));
+  CU(cudaMemsetAsync(ctx->d_iters, 0, (size_t)C * sizeof(int), ctx->stream));
+  if (divisors) {
+    if (!ctx->d_div) CU(cudaMalloc((void**)&ctx->d_div, (size_t)M.nx * sizeof(double)));
+    CU(cudaMemcpyAsync(ctx->d_div, divisors, (size_t)M.nx * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  }
+  // total point count across ranks (the reference divides by length(sensed_points), src/tracking.jl:20)
+  double n_total = (double)ctx->n_pts;
+  if (ctx->comm) {
+    double* d_n = ctx->d_cost;  // scratch
+    CU(cudaMemcpyAsync(d_n, &n_total, sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    int nrc = g_nccl.AllReduce(d_n, d_n, 1, NCCL_FLOAT64, NCCL_SUM, ctx->comm, ctx->stream);
+    if (nrc != 0) return fail(ctx, FLASH_ERR_NCCL, "ncclAllReduce(point count) failed");
+    CU(cudaMemcpyAsync(&n_total, d_n, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+  }
+  const bool prof = ctx->profiling; ctx->profiling = false;
+  cudaEvent_t e0 = ctx->ev[0], e1 = ctx->ev[4];
+  if (prof) CU(cudaEventRecord(e0, ctx->stream));
+  for (int it = 0; it < sp->iteration_limit; ++it) {
+    if ((rc = pipeline(ctx, C, sp->deformation_cost_weight, true, nullptr))) { ctx->profiling = prof; return rc; }
+    gd_step_kernel<<<C, 128, 0, ctx->stream>>>(ctx->d_X, ctx->d_grad, M.nx, n_total > 0 ? 1.0 / n_total : 0.0, sp->rate, sp->max_step,
+                                               sp->gradient_convergence_tolerance, divisors ? ctx->d_div : nullptr, ctx->d_done, ctx->d_iters);
+    CU(cudaGetLastError());
+    ctx->launches++; ctx->last.launches++;
+  }
+  if (cost_out) { if ((rc = pipeline(ctx, C, sp->deformation_cost_weight, false, nullptr))) { ctx->profiling = prof; return rc; } }
+  if (prof) CU(cudaEventRecord(e1, ctx->stream));
+  ctx->profiling = prof;
+  double* h_cost = ctx->h_pin + nX;
+  CU(cudaMemcpyAsync(ctx->h_pin, ctx->d_X, nX * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  if (cost_out) CU(cudaMemcpyAsync(h_cost, ctx->d_cost, (size_t)C * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  if (iters_out) CU(cudaMemcpyAsync(iters_out, ctx->d_iters, (size_t)C * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  rc = check_status(ctx); if (rc) return rc;
+  std::memcpy(X, ctx->h_pin, nX * sizeof(double));
+  if (cost_out) std::memcpy(cost_out, h_cost, (size_t)C * sizeof(double));
+  if (prof) CU(cudaEventElapsedTime(&ctx->last.ms_total, e0, e1));
+  return FLASH_OK;
+}
+
+// ---- multi-GPU
+int flash_comm_unique_id(void* id128) {
+  std::string err;
+  if (!id128) return FLASH_ERR_INVALID;
+  if (!load_nccl(err)) { g_create_err = err; return FLASH_ERR_NCCL; }
+  nccl_uid id;
+  int rc = g_nccl.GetUniqueId(&id);
+  if (rc != 0) { g_create_err = "ncclGetUniqueId failed"; return FLASH_ERR_NCCL; }
+  std::memcpy(id128, &id, sizeof id);
+  return FLASH_OK;
+}
+
+int flash_comm_init(flash_ctx* ctx, int32_t rank, int32_t world, const void* id128) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (world < 1 || rank < 0 || rank >= world || !id128) return fail(ctx, FLASH_ERR_INVALID, "flash_comm_init: bad arguments");
+  std::string err;
+  if (!load_nccl(err)) return fail(ctx, FLASH_ERR_NCCL, err);
+  CU(cudaSetDevice(ctx->device));
+  nccl_uid id; std::memcpy(&id, id128, sizeof id);
+  if (ctx->comm) { g_nccl.CommDestroy(ctx->comm); ctx->comm = nullptr; }
+  int rc = g_nccl.CommInitRank(&ctx->comm, world, id, rank);
+  if (rc != 0) { ctx->comm = nullptr; return fail(ctx, FLASH_ERR_NCCL, std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error")); }
+  ctx->rank = rank; ctx->world = world;
+  return FLASH_OK;
+}
+
+int flash_comm_world(const flash_ctx* ctx) { return ctx ? ctx->world : FLASH_ERR_INVALID; }
+
+// ---- measurement
+int flash_profiling(flash_ctx* ctx, int32_t enable) { if (!ctx) return FLASH_ERR_INVALID; ctx->profiling = enable != 0; return FLASH_OK; }
+int flash_last_timing(const flash_ctx* ctx, flash_timing* t) { if (!ctx || !t) return FLASH_ERR_INVALID; *t = ctx->last; return FLASH_OK; }
+int64_t flash_launch_count(const flash_ctx* ctx) { return ctx ? ctx->launches : FLASH_ERR_INVALID; }
+int flash_device_info(const flash_ctx* ctx, int32_t* sm_count, int32_t* clock_khz, int64_t* l2_bytes) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (sm_count) *sm_count = ctx->sm_count;
+  if (clock_khz) *clock_khz = ctx->clock_khz;
+  if (l2_bytes) *l2_bytes = ctx->l2_bytes;
+  return FLASH_OK;
+}
+int flash_grid_report(const flash_ctx* ctx, int32_t surface, int32_t dims[3], double* spacing, double* max_abs_err) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  const ModelC& M = ctx->hm.M;
+  if (surface < 0 || surface >= M.n_surfaces || M.surf_kind[surface] != SURF_CONVEX || !ctx->use_grid) return FLASH_ERR_INVALID;
+  const ConvexC& C = M.cvx[M.surf_slot[surface]];
+  if (dims) for (int k = 0; k < 3; ++k) dims[k] = C.g_dim[k];
+  if (spacing) *spacing = 1.0 / C.g_inv_h;
+  if (max_abs_err) *max_abs_err = ctx->grid_err[M.surf_slot[surface]];
+  return FLASH_OK;
+}
+
+}  // extern "C"

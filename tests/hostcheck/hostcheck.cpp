@@ -1,0 +1,108 @@
+// hostcheck.cpp -- TEST INFRASTRUCTURE.  Compiles the product's __host__ __device__ math
+// (csrc/flash_dev.h, csrc/flash_host.h) with g++ and replays, serially, exactly what the CUDA
+// kernels do per config and per point, so the formulas can be checked against the oracle on a box
+// without a GPU.  Never linked into libflashsdf.so; the product has no CPU path.
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../point-cloud-signed-distance_b200/csrc/flash_host.h"
+
+using namespace flashdev;
+using namespace flashhost;
+
+struct HC { HostModel hm; HotModel hot; };
+static thread_local std::string g_err;
+
+extern "C" {
+
+const char* hc_last_error() { return g_err.c_str(); }
+
+void* hc_model_create(const flash_model_desc* d, const flash_options* o) {
+  HC* h = new HC;
+  if (!build_model(d, o, h->hm, g_err)) { delete h; return nullptr; }
+  make_hot(h->hm.M, h->hot);
+  return h;
+}
+void hc_model_destroy(void* p) { delete (HC*)p; }
+
+// out: nx, nq, tab_len, acc_len, aux_len, n_convex, n_skins
+void hc_info(void* p, int* out) {
+  ModelC& M = ((HC*)p)->hm.M;
+  out[0] = M.nx; out[1] = M.nq; out[2] = M.tab_len; out[3] = M.acc_len; out[4] = M.aux_len; out[5] = M.n_convex; out[6] = M.n_skins;
+}
+void hc_convex_info(void* p, int j, int* nverts, int* nplanes, float* lo, float* hi, float* depth_bound) {
+  ConvexC& C = ((HC*)p)->hm.M.cvx[j];
+  *nverts = C.nverts; *nplanes = C.nplanes; *depth_bound = C.depth_bound;
+  for (int k = 0; k < 3; ++k) { lo[k] = C.lo[k]; hi[k] = C.hi[k]; }
+}
+
+// prepare kernel, one config
+void hc_prepare(void* p, const double* x, double* tab, double* aux) {
+  ModelC& M = ((HC*)p)->hm.M;
+  fk_config(M, x, aux);
+  prepare_convex(M, aux, tab);
+  for (int k = 0; k < M.n_skins; ++k) {
+    const SkinC& K = M.skin[k];
+    skin_centres(M, K, x, aux, tab);
+    double* LU = aux + aux_skin0(M) + K.aux_off;
+    skin_assemble(M, K, tab, LU, 0, 1);
+    lu_factor(LU, LU + K.M * K.M, K.M, 0, 1);
+    skin_solve(M, K, LU, LU + K.M * K.M, tab);
+  }
+}
+
+// main kernel, one config, serial over points; fp32 contributions for convex winners (as the warp
+// shuffles carry them), fp64 for skins, fp64 accumulation
+void hc_accumulate(void* p, const double* tab, const float* pts, long long n, int use_grid, double* acc, double* dist, int* argmin) {
+  HC* h = (HC*)p;
+  const HotModel& H = h->hot;
+  GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
+  float lb[MAX_CONVEX];
+  for (long long i = 0; i < n; ++i) {
+    PointEval e;
+    eval_point(H, G, tab, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], lb, 1, use_grid != 0, e);
+    double dv = e.is_skin ? e.sk.s : (double)e.d;
+    if (dist) dist[i] = dv;
+    if (argmin) argmin[i] = e.arg;
+    if (!acc) continue;
+    acc[0] += dv * dv;
+    if (!e.is_skin) {
+      float g = -2.f * e.d;
+      float v0 = g * e.n.x, v1 = g * e.n.y, v2 = g * e.n.z;
+      float t0 = e.y.y * v2 - e.y.z * v1, t1 = e.y.z * v0 - e.y.x * v2, t2 = e.y.x * v1 - e.y.y * v0;
+      double* a = acc + 1 + 6 * e.slot;
+      a[0] += v0; a[1] += v1; a[2] += v2; a[3] += t0; a[4] += t1; a[5] += t2;
+    } else {
+      const SkinC& K = H.skin[e.slot];
+      const double* c = tab + K.tab_off;
+      double* gY = acc + K.acc_off; double* gC = gY + K.npts + 4;
+      for (int ci = 0; ci <= K.npts; ++ci) {
+        double o[4];
+        skin_adjoint_term(c, c + 3 * K.npts, K.npts, H.normalize != 0, ci, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], e.sk.s, e.sk.ginv, e.sk.nh, o);
+        if (ci < K.npts) { gY[ci] += o[0]; gC[3 * ci] += o[1]; gC[3 * ci + 1] += o[2]; gC[3 * ci + 2] += o[3]; }
+        else { gY[ci] += o[0]; gY[ci + 1] += o[1]; gY[ci + 2] += o[2]; gY[ci + 3] += o[3]; }
+      }
+    }
+  }
+}
+
+void hc_epilogue(void* p, const double* x, const double* tab, const double* aux, const double* acc, double w_def, double* cost, double* grad) {
+  ModelC& M = ((HC*)p)->hm.M;
+  std::vector<double> scratch(6 * MAX_BODIES + MAX_SKIN_M);
+  epilogue_config(M, x, tab, aux, acc, w_def, scratch.data(), cost, grad);
+}
+
+// signed distance of geometry-frame points y[n][3] to convex slot j
+void hc_hull_sd(void* p, int j, const float* y, long long n, float* d, float* nrm) {
+  HC* h = (HC*)p;
+  const ConvexC& C = h->hm.M.cvx[j];
+  const F4* f4 = h->hm.geo_f4.data(); const uint32_t* u32 = h->hm.geo_u32.data();
+  for (long long i = 0; i < n; ++i) {
+    F3 nn;
+    d[i] = hull_sd(f4 + C.off_planes, u32 + C.off_tris, f4 + C.off_verts, C.nplanes, C.nverts, f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]), nn);
+    nrm[3 * i] = nn.x; nrm[3 * i + 1] = nn.y; nrm[3 * i + 2] = nn.z;
+  }
+}
+
+}  // extern "C"
