@@ -21,6 +21,14 @@
 
 namespace flashdev {
 
+#if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
+struct Counters { long long points, narrow, inside, gjk_iters, plane_tests, vert_tests, lb_tests; };
+inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0, 0}; return c; }
+#define FLASH_COUNT(field, n) (flashdev::counters().field += (n))
+#else
+#define FLASH_COUNT(field, n) ((void)0)
+#endif
+
 constexpr int MAX_BODIES = 32;
 constexpr int MAX_SURFACES = 32;
 constexpr int MAX_CONVEX = 24;
@@ -48,6 +56,7 @@ struct BodyC {
 struct ConvexC {
   int surface, body, nverts, nplanes;
   int off_planes, off_tris, off_verts, pad;  // indices into the geometry blob (units: F4 / u32 / F4)
+  int nplanes_pad, nverts_pad, pad3[2];      // counts rounded up to a multiple of 8 (padding is inert)
   float lo[3], hi[3];                        // AABB of the vertices, geometry frame
   float depth_bound, pad2;                   // >= max penetration depth
   double frame[12];                          // geometry frame -> body frame
@@ -336,14 +345,31 @@ FLASH_HD void simplex_from(Simplex& S, F3 p0, int j0, float u0, F3 p1, int j1, f
 // inside value is iteration-path dependent and replaced by the exact depth -- DESIGN.md).
 // nrm receives grad_y(distance).
 FLASH_HD float hull_sd(const F4* __restrict__ planes, const uint32_t* __restrict__ ptri, const F4* __restrict__ verts,
-                       int np, int nv, F3 y, F3& nrm) {
+                       int np, int nv, F3 y, float cutoff, F3& nrm) {
+  // Plane scan in groups of 8 (arrays are padded to a multiple of 8 by the host): three FFMAs and
+  // one FMNMX per plane; the index is recovered only in the rare group that raises the maximum.
+  // D is a lower bound of the distance, so the scan stops once D exceeds `cutoff` (the best value
+  // another surface already achieved): this body cannot be the minimum.
   float D = -3.0e38f; int fs = 0;
-  for (int f = 0; f < np; ++f) {
-    F4 p = planes[f];
-    float s = fmaf(p.x, y.x, fmaf(p.y, y.y, fmaf(p.z, y.z, -p.w)));
-    if (s > D) { D = s; fs = f; }
+  for (int f = 0; f < np; f += 8) {
+    float sv[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const F4 p = planes[f + k];
+      sv[k] = fmaf(p.x, y.x, fmaf(p.y, y.y, fmaf(p.z, y.z, -p.w)));
+    }
+    const float m = fmaxf(fmaxf(fmaxf(sv[0], sv[1]), fmaxf(sv[2], sv[3])), fmaxf(fmaxf(sv[4], sv[5]), fmaxf(sv[6], sv[7])));
+    if (m > D) {
+      D = m;
+      int k = 7;
+#pragma unroll
+      for (int t = 6; t >= 0; --t) k = (sv[t] == m) ? t : k;
+      fs = f + k;
+      if (D > cutoff) { nrm = xyz(planes[fs]); return D; }
+    }
   }
-  if (D <= 0.f) { nrm = xyz(planes[fs]); return D; }
+  FLASH_COUNT(narrow, 1); FLASH_COUNT(plane_tests, np);
+  if (D <= 0.f) { FLASH_COUNT(inside, 1); nrm = xyz(planes[fs]); return D; }
   Simplex S;
   F3 q;
   {
@@ -354,15 +380,30 @@ FLASH_HD float hull_sd(const F4* __restrict__ planes, const uint32_t* __restrict
     q = tri_closest0(p0, p1, p2, u0, u1, u2);
     simplex_from(S, p0, j0, u0, p1, j1, u1, p2, j2, u2);
   }
-  for (int it = 0; it < GJK_MAX_ITER; ++it) {
+  // D (the largest plane distance) is a lower bound of the distance and |q| an upper bound: when
+  // they meet, q is the projection onto the face and no support scan is needed to certify it.
+  bool certified = dot(q, q) <= D * D * (1.f + 2e-6f);
+  for (int it = 0; it < GJK_MAX_ITER && !certified; ++it) {
     float dd = dot(q, q);
     if (!(dd > 0.f)) break;
     // support vertex towards the query point: minimise q.(v - y)  <=>  minimise q.v
+    FLASH_COUNT(gjk_iters, 1); FLASH_COUNT(vert_tests, nv);
     float best = 3.0e38f; int iw = 0;
-    for (int v = 0; v < nv; ++v) {
-      F4 p = verts[v];
-      float s = fmaf(q.x, p.x, fmaf(q.y, p.y, q.z * p.z));
-      if (s < best) { best = s; iw = v; }
+    for (int v = 0; v < nv; v += 8) {   // groups of 8 (padded with copies of vertex 0)
+      float sv[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const F4 p = verts[v + k];
+        sv[k] = fmaf(q.x, p.x, fmaf(q.y, p.y, q.z * p.z));
+      }
+      const float m = fminf(fminf(fminf(sv[0], sv[1]), fminf(sv[2], sv[3])), fminf(fminf(sv[4], sv[5]), fminf(sv[6], sv[7])));
+      if (m < best) {
+        best = m;
+        int k = 7;
+#pragma unroll
+        for (int t = 6; t >= 0; --t) k = (sv[t] == m) ? t : k;
+        iw = v + k;
+      }
     }
     if (iw == S.ia || (S.ns > 1 && iw == S.ib) || (S.ns > 2 && iw == S.ic)) break;  // already supporting
     F3 w = xyz(verts[iw]) - y;
@@ -406,7 +447,7 @@ FLASH_HD float aabb_lower_bound(const float* lo, const float* hi, float depth_bo
   float dy = fmaxf(fmaxf(lo[1] - y.y, y.y - hi[1]), 0.f);
   float dz = fmaxf(fmaxf(lo[2] - y.z, y.z - hi[2]), 0.f);
   float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-  if (d2 > 0.f) return sqrtf(d2) * (1.f - 4e-6f) - 1e-7f;
+  if (d2 > 0.f) return sqrtf(d2) * (1.f - 4e-6f) - 4e-6f;
   return -depth_bound;
 }
 
@@ -417,6 +458,12 @@ FLASH_HD F3 to_geometry(const double* __restrict__ T, float px, float py, float 
   double b = fma(T[3], x, fma(T[4], y, fma(T[5], z, T[10])));
   double c = fma(T[6], x, fma(T[7], y, fma(T[8], z, T[11])));
   return f3((float)a, (float)b, (float)c);
+}
+
+// fp32 version for the culling bound only (error < 2e-6 m for |x| < 4 m; the bound subtracts 4e-6)
+FLASH_HD F3 to_geometry_f32(const float* __restrict__ T, float px, float py, float pz) {
+  return f3(fmaf(T[0], px, fmaf(T[1], py, fmaf(T[2], pz, T[9]))), fmaf(T[3], px, fmaf(T[4], py, fmaf(T[5], pz, T[10]))),
+            fmaf(T[6], px, fmaf(T[7], py, fmaf(T[8], pz, T[11]))));
 }
 
 // trilinear sample of a body-frame SDF grid with analytic gradient, manual fp32 (no texture unit)
@@ -529,7 +576,7 @@ FLASH_HD bool lex_less(float d, int s, float best, int arg) { return d < best ||
 // `lb` is per-thread scratch of n_convex floats with stride lb_stride.
 // Convex bodies are culled with their AABB lower bound: a body is evaluated exactly only if its
 // bound can still beat the best value so far, which cannot change the min or the argmin.
-FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __restrict__ tab,
+FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __restrict__ tab, const float* __restrict__ tabf,
                          float px, float py, float pz, float* lb, int lb_stride, bool use_grid, PointEval& out) {
   const ConvexC* __restrict__ cvx = M.cvx;
   float best = 3.0e38f; int arg = 0x7fffffff; int slot = -1; int is_skin = 0;
@@ -543,9 +590,10 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
     if (lex_less(d, K.surface, best, arg)) { best = d; arg = K.surface; slot = k; is_skin = 1; out.sk = e; }
   }
   const int nc = M.n_convex;
+  FLASH_COUNT(points, 1); FLASH_COUNT(lb_tests, nc);
   int j0 = -1; float lb0 = 3.0e38f;
   for (int j = 0; j < nc; ++j) {
-    F3 y = to_geometry(tab + 12 * j, px, py, pz);
+    F3 y = to_geometry_f32(tabf + 12 * j, px, py, pz);
     float l = aabb_lower_bound(cvx[j].lo, cvx[j].hi, cvx[j].depth_bound, y);
     lb[j * lb_stride] = l;
     if (l < lb0) { lb0 = l; j0 = j; }
@@ -561,7 +609,7 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
     F3 n; float d;
     bool done = false;
     if (use_grid && C.g_on) done = grid_sd(C, G.grid_pool, y, d, n);
-    if (!done) d = hull_sd(G.f4 + C.off_planes, G.u32 + C.off_tris, G.f4 + C.off_verts, C.nplanes, C.nverts, y, n);
+    if (!done) d = hull_sd(G.f4 + C.off_planes, G.u32 + C.off_tris, G.f4 + C.off_verts, C.nplanes_pad, C.nverts_pad, y, best, n);
     if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
   }
   out.d = best; out.arg = arg; out.slot = slot; out.is_skin = is_skin;

@@ -182,6 +182,9 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
         out.geo_f4.push_back(F4{(float)H.planes[f][0], (float)H.planes[f][1], (float)H.planes[f][2], (float)H.planes[f][3]});
         out.geo_u32.push_back((uint32_t)H.ptri[f][0] | ((uint32_t)H.ptri[f][1] << 8) | ((uint32_t)H.ptri[f][2] << 16));
       }
+      // pad to a multiple of 8 with planes that can never be the maximum
+      C.nplanes_pad = (C.nplanes + 7) & ~7;
+      for (int f = C.nplanes; f < C.nplanes_pad; ++f) { out.geo_f4.push_back(F4{0.f, 0.f, 0.f, 1.0e30f}); out.geo_u32.push_back(out.geo_u32.back()); }
       C.off_verts = (int)out.geo_f4.size();
       for (int k = 0; k < 3; ++k) { C.lo[k] = 3e38f; C.hi[k] = -3e38f; }
       for (auto& v : H.verts) {
@@ -192,6 +195,8 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
         C.lo[1] = std::min(C.lo[1], std::nextafterf(f.y, -3e38f)); C.hi[1] = std::max(C.hi[1], std::nextafterf(f.y, 3e38f));
         C.lo[2] = std::min(C.lo[2], std::nextafterf(f.z, -3e38f)); C.hi[2] = std::max(C.hi[2], std::nextafterf(f.z, 3e38f));
       }
+      C.nverts_pad = (C.nverts + 7) & ~7;   // pad with copies of vertex 0 (never a strictly better support)
+      for (int v = C.nverts; v < C.nverts_pad; ++v) out.geo_f4.push_back(F4{(float)H.verts[0].x, (float)H.verts[0].y, (float)H.verts[0].z, 0.f});
       double db = 1e300;
       for (auto& p : H.planes) {
         double w = 0;

@@ -38,6 +38,7 @@ struct CostParams {
   const double* tab;   // [C][tab_len]
   double* acc;         // [C][acc_len]
   int32_t* argmin;     // [C][n_pts] or null
+  const int* perm;     // sorted position -> caller index (null: identity)
   double* dist;        // [n_pts] (DIST mode, C == 1)
   int pts_per_block;
   int use_grid;
@@ -47,7 +48,7 @@ __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t
 
 // dynamic shared memory layout of cost_kernel / raycast_kernel
 struct SmemLayout {
-  size_t off_hot, off_f4, off_u32, off_tab, off_acc, off_lb, off_queue, off_qslot, total;
+  size_t off_hot, off_f4, off_u32, off_tab, off_tabf, off_acc, off_lb, off_queue, off_qslot, total;
 };
 __host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, int tab_len, int acc_len, int n_convex, bool grad_skins) {
   SmemLayout L;
@@ -56,6 +57,7 @@ __host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, i
   L.off_f4 = o; o = align16(o + sizeof(F4) * (size_t)geo_f4_n);
   L.off_u32 = o; o = align16(o + sizeof(uint32_t) * (size_t)geo_u32_n);
   L.off_tab = o; o = align16(o + sizeof(double) * (size_t)tab_len);
+  L.off_tabf = o; o = align16(o + sizeof(float) * 12 * (size_t)(n_convex > 0 ? n_convex : 1));
   L.off_acc = o; o = align16(o + sizeof(double) * (size_t)acc_len * WARPS);
   L.off_lb = o; o = align16(o + sizeof(float) * (size_t)(n_convex > 0 ? n_convex : 1) * BLOCK);
   L.off_queue = o; o = align16(o + (grad_skins ? sizeof(double) * QENT * 32 * WARPS : 0));
@@ -105,7 +107,7 @@ __global__ void __launch_bounds__(32) prepare_kernel(const ModelC* __restrict__ 
 // ------------------------------------------------------------------------------------------------
 // stage model + geometry + this config's table in shared memory
 __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayout& L, const HotModel* hot, const F4* geo_f4, int nf4,
-                                            const uint32_t* geo_u32, int nu32, const double* tab, int tab_len) {
+                                            const uint32_t* geo_u32, int nu32, const double* tab, int tab_len, int n_convex) {
   const int tid = threadIdx.x;
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(hot);
@@ -124,6 +126,8 @@ __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayou
   {
     double* dst = reinterpret_cast<double*>(smem + L.off_tab);
     for (int i = tid; i < tab_len; i += BLOCK) dst[i] = tab[i];
+    float* dstf = reinterpret_cast<float*>(smem + L.off_tabf);   // fp32 copy of the convex transforms (culling bound)
+    for (int i = tid; i < 12 * n_convex; i += BLOCK) dstf[i] = (float)tab[i];
   }
 }
 
@@ -138,7 +142,7 @@ __global__ void __launch_bounds__(BLOCK, 2) cost_kernel(const CostParams p) {
   const HotModel* hot_g = p.hot;
   const int tab_len = hot_g->tab_len, acc_len = hot_g->acc_len, n_convex = hot_g->n_convex;
   const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, tab_len, acc_len, n_convex, GRAD && hot_g->n_skins > 0);
-  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab + (size_t)c * tab_len, tab_len);
+  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab + (size_t)c * tab_len, tab_len, n_convex);
   double* acc_w = reinterpret_cast<double*>(smem + L.off_acc) + (size_t)warp * acc_len;
   if (!DIST) for (int i = lane; i < acc_len; i += 32) acc_w[i] = 0.0;
   __syncthreads();
@@ -148,6 +152,7 @@ __global__ void __launch_bounds__(BLOCK, 2) cost_kernel(const CostParams p) {
   G.u32 = reinterpret_cast<const uint32_t*>(smem + L.off_u32);
   G.grid_pool = p.grid_pool;
   const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
+  const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
   float* lb = reinterpret_cast<float*>(smem + L.off_lb) + tid;
   double* queue = reinterpret_cast<double*>(smem + L.off_queue) + (size_t)warp * 32 * QENT;
   int* qslot = reinterpret_cast<int*>(smem + L.off_qslot) + warp * 32;
@@ -166,7 +171,7 @@ __global__ void __launch_bounds__(BLOCK, 2) cost_kernel(const CostParams p) {
     if (valid) {
       const float4 P = __ldg(p.pts + i);
       px = P.x; py = P.y; pz = P.z;
-      eval_point(H, G, tab, px, py, pz, lb, BLOCK, p.use_grid != 0, e);
+      eval_point(H, G, tab, tabf, px, py, pz, lb, BLOCK, p.use_grid != 0, e);
     }
     if (DIST) {
       if (valid) {
@@ -175,7 +180,7 @@ __global__ void __launch_bounds__(BLOCK, 2) cost_kernel(const CostParams p) {
       }
       continue;
     }
-    if (ARGMIN && valid) p.argmin[(size_t)c * p.n_pts + i] = e.arg;
+    if (ARGMIN && valid) p.argmin[(size_t)c * p.n_pts + (p.perm ? (long long)p.perm[i] : i)] = e.arg;
     if (valid) { const double dv = e.is_skin ? e.sk.s : (double)e.d; cost_local = fma(dv, dv, cost_local); }
     if (!GRAD) continue;
 
@@ -264,14 +269,115 @@ __global__ void __launch_bounds__(32) epilogue_kernel(const ModelC* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------------
-// fp64 [n][3] (the memory of a Julia Vector{SVector{3,Float64}}) -> float4, rounded once
-__global__ void convert_points_f64(const double* __restrict__ src, float4* __restrict__ dst, long long n) {
-  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) dst[i] = make_float4((float)src[3 * i], (float)src[3 * i + 1], (float)src[3 * i + 2], 0.f);
+// Point ingestion: fp64 or fp32 [n][3] AoS (the memory of a Julia Vector{SVector{3,Float64}}) ->
+// float4 rounded once, and re-ordered into Morton order of a 64^3 cell grid over the cloud's AABB
+// so that the 32 points of a warp lie within ~one cell: all lanes then cull the same bodies and run
+// the same GJK iterations (measured: 9.4 -> ~25 active lanes per instruction).  The cost is a sum
+// over points, so the order is free; `perm` maps sorted position -> caller's index for argmin.
+template <class T>
+__device__ __forceinline__ float3 load_xyz(const T* __restrict__ src, long long i) {
+  return make_float3((float)src[3 * i], (float)src[3 * i + 1], (float)src[3 * i + 2]);
 }
-__global__ void convert_points_f32(const float* __restrict__ src, float4* __restrict__ dst, long long n) {
-  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) dst[i] = make_float4(src[3 * i], src[3 * i + 1], src[3 * i + 2], 0.f);
+__device__ __forceinline__ unsigned ordered_bits(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__host__ __device__ inline float from_ordered_bits(unsigned u) {
+  u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(u);
+#else
+  float f; memcpy(&f, &u, 4); return f;
+#endif
+}
+// bounds[0..2] = min (ordered bits), bounds[3..5] = max
+template <class T>
+__global__ void points_bounds_kernel(const T* __restrict__ src, long long n, unsigned* __restrict__ bounds) {
+  float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    float3 p = load_xyz(src, i);
+    if (p.x == p.x && p.y == p.y && p.z == p.z && fabsf(p.x) < 1e30f && fabsf(p.y) < 1e30f && fabsf(p.z) < 1e30f) {
+      lo[0] = fminf(lo[0], p.x); lo[1] = fminf(lo[1], p.y); lo[2] = fminf(lo[2], p.z);
+      hi[0] = fmaxf(hi[0], p.x); hi[1] = fmaxf(hi[1], p.y); hi[2] = fmaxf(hi[2], p.z);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o)); hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o)); }
+  }
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { atomicMin(bounds + k, ordered_bits(lo[k])); atomicMax(bounds + 3 + k, ordered_bits(hi[k])); }
+  }
+}
+constexpr int SORT_BITS = 6;                       // 64 cells per axis
+constexpr int SORT_BINS = 1 << (3 * SORT_BITS);    // 262,144
+__device__ __forceinline__ unsigned spread3(unsigned v) {  // 6 bits -> every third bit
+  v &= 0x3f;
+  v = (v | (v << 8)) & 0x300f;
+  v = (v | (v << 4)) & 0x30c3;
+  v = (v | (v << 2)) & 0x9249;
+  return v;
+}
+__device__ __forceinline__ unsigned cell_of(float3 p, const unsigned* __restrict__ bounds) {
+  unsigned key = 0;
+  const float v[3] = {p.x, p.y, p.z};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const float lo = from_ordered_bits(bounds[k]), hi = from_ordered_bits(bounds[3 + k]);
+    const float ext = hi - lo;
+    float t = ext > 0.f ? (v[k] - lo) / ext : 0.f;
+    int c = (int)(t * (float)(1 << SORT_BITS));
+    c = c < 0 ? 0 : (c > (1 << SORT_BITS) - 1 ? (1 << SORT_BITS) - 1 : c);   // NaN -> 0
+    key |= spread3((unsigned)c) << k;
+  }
+  return key;
+}
+template <class T>
+__global__ void points_hist_kernel(const T* __restrict__ src, long long n, const unsigned* __restrict__ bounds, int* __restrict__ bins) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) atomicAdd(bins + cell_of(load_xyz(src, i), bounds), 1);
+}
+// exclusive scan of SORT_BINS counters: per-1024 local scan, scan of the 256 block sums, add back
+__global__ void __launch_bounds__(1024) bins_scan_local_kernel(int* __restrict__ bins, int* __restrict__ block_sums) {
+  __shared__ int wsum[32];
+  const int i = blockIdx.x * 1024 + threadIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int v = bins[i];
+  int x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+  if (lane == 31) wsum[w] = x;
+  __syncthreads();
+  if (w == 0) {
+    int s = wsum[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
+    wsum[lane] = s;
+  }
+  __syncthreads();
+  const int incl = x + (w > 0 ? wsum[w - 1] : 0);
+  bins[i] = incl - v;
+  if (threadIdx.x == 1023) block_sums[blockIdx.x] = incl;
+}
+__global__ void __launch_bounds__(1024) bins_scan_add_kernel(int* __restrict__ bins, const int* __restrict__ block_sums) {
+  __shared__ int base;
+  if (threadIdx.x == 0) { int s = 0; for (int b = 0; b < (int)blockIdx.x; ++b) s += block_sums[b]; base = s; }
+  __syncthreads();
+  bins[blockIdx.x * 1024 + threadIdx.x] += base;
+}
+template <class T>
+__global__ void points_scatter_kernel(const T* __restrict__ src, long long n, const unsigned* __restrict__ bounds, int* __restrict__ cursor,
+                                      float4* __restrict__ dst, int* __restrict__ perm) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float3 p = load_xyz(src, i);
+  const int pos = atomicAdd(cursor + cell_of(p, bounds), 1);
+  dst[pos] = make_float4(p.x, p.y, p.z, 0.f);
+  perm[pos] = (int)i;
+}
+// unsorted conversion (clouds too small to be worth sorting, or > 2^31 points)
+template <class T>
+__global__ void convert_points_kernel(const T* __restrict__ src, float4* __restrict__ dst, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { const float3 p = load_xyz(src, i); dst[i] = make_float4(p.x, p.y, p.z, 0.f); }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -292,10 +398,10 @@ struct RayParams {
   int use_grid;
 };
 
-__device__ __forceinline__ double field_at(const HotModel& H, const GeoView& G, const double* tab, double ox, double oy, double oz,
+__device__ __forceinline__ double field_at(const HotModel& H, const GeoView& G, const double* tab, const float* tabf, double ox, double oy, double oz,
                                             double rx, double ry, double rz, double dist, float* lb, int use_grid) {
   PointEval e;
-  eval_point(H, G, tab, (float)fma(dist, rx, ox), (float)fma(dist, ry, oy), (float)fma(dist, rz, oz), lb, BLOCK, use_grid != 0, e);
+  eval_point(H, G, tab, tabf, (float)fma(dist, rx, ox), (float)fma(dist, ry, oy), (float)fma(dist, rz, oz), lb, BLOCK, use_grid != 0, e);
   return e.is_skin ? e.sk.s : (double)e.d;
 }
 
@@ -304,7 +410,7 @@ __global__ void __launch_bounds__(BLOCK, 2) raycast_kernel(const RayParams p) {
   const int tid = threadIdx.x;
   const HotModel* hot_g = p.hot;
   const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, hot_g->tab_len, 0, hot_g->n_convex, false);
-  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab, hot_g->tab_len);
+  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab, hot_g->tab_len, hot_g->n_convex);
   __syncthreads();
   const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
   GeoView G;
@@ -312,6 +418,7 @@ __global__ void __launch_bounds__(BLOCK, 2) raycast_kernel(const RayParams p) {
   G.u32 = reinterpret_cast<const uint32_t*>(smem + L.off_u32);
   G.grid_pool = p.grid_pool;
   const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
+  const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
   float* lb = reinterpret_cast<float*>(smem + L.off_lb) + tid;
   const long long i = (long long)blockIdx.x * BLOCK + tid;
   bool hit = false;
@@ -326,14 +433,14 @@ __global__ void __launch_bounds__(BLOCK, 2) raycast_kernel(const RayParams p) {
     const double ox = p.cam[3], oy = p.cam[7], oz = p.cam[11];
     const double EPS = 1e-5, SAFE_RATE = 0.4;
     double dist = 0.0, est = -1.0;
-    double last = field_at(H, G, tab, ox, oy, oz, rx, ry, rz, dist, lb, p.use_grid);
+    double last = field_at(H, G, tab, tabf, ox, oy, oz, rx, ry, rz, dist, lb, p.use_grid);
     int k = 0;
     while (fabs(last) > EPS && k < 60) {
       double step = -last / est;
       const double sg = step > 0 ? 1.0 : (step < 0 ? -1.0 : 0.0);
       step = sg * fmin(SAFE_RATE, fabs(step));
       dist += step;
-      const double v = field_at(H, G, tab, ox, oy, oz, rx, ry, rz, dist, lb, p.use_grid);
+      const double v = field_at(H, G, tab, tabf, ox, oy, oz, rx, ry, rz, dist, lb, p.use_grid);
       est = (v - last) / step;
       last = v;
       ++k;
@@ -441,7 +548,7 @@ __global__ void bake_grid_kernel(const HotModel* __restrict__ hot, const F4* __r
   const float h = 1.0f / C.g_inv_h;
   F3 y = f3(C.g_org[0] + ix * h, C.g_org[1] + iy * h, C.g_org[2] + iz * h);
   F3 n3;
-  pool[C.g_off + i] = hull_sd(geo_f4 + C.off_planes, geo_u32 + C.off_tris, geo_f4 + C.off_verts, C.nplanes, C.nverts, y, n3);
+  pool[C.g_off + i] = hull_sd(geo_f4 + C.off_planes, geo_u32 + C.off_tris, geo_f4 + C.off_verts, C.nplanes_pad, C.nverts_pad, y, 3.0e38f, n3);
 }
 // max |trilinear - exact| over cell centres (the worst place for trilinear interpolation)
 __global__ void grid_error_kernel(const HotModel* __restrict__ hot, const F4* __restrict__ geo_f4, const uint32_t* __restrict__ geo_u32, int j,
@@ -456,7 +563,7 @@ __global__ void grid_error_kernel(const HotModel* __restrict__ hot, const F4* __
     const float h = 1.0f / C.g_inv_h;
     F3 y = f3(C.g_org[0] + (ix + 0.5f) * h, C.g_org[1] + (iy + 0.5f) * h, C.g_org[2] + (iz + 0.5f) * h);
     F3 n3, n4; float dg;
-    float de = hull_sd(geo_f4 + C.off_planes, geo_u32 + C.off_tris, geo_f4 + C.off_verts, C.nplanes, C.nverts, y, n3);
+    float de = hull_sd(geo_f4 + C.off_planes, geo_u32 + C.off_tris, geo_f4 + C.off_verts, C.nplanes_pad, C.nverts_pad, y, 3.0e38f, n3);
     if (grid_sd(C, pool, y, dg, n4)) err = fabsf(dg - de);
   }
   err = fmaxf(err, __shfl_xor_sync(0xffffffffu, err, 16));

@@ -68,6 +68,7 @@ struct flash_ctx {
   // points
   float4* d_pts = nullptr; long long n_pts = 0; long long cap_pts = 0; bool pts_external = false; bool pts_set = false;
   void* d_stage = nullptr; size_t cap_stage = 0;
+  int* d_bins = nullptr; int* d_perm = nullptr; size_t cap_perm = 0; bool perm_on = false; bool sort_points = true;
   // per-batch state
   int cap_C = 0;
   double *d_X = nullptr, *d_tab = nullptr, *d_aux = nullptr, *d_acc = nullptr, *d_cost = nullptr, *d_grad = nullptr, *d_div = nullptr;
@@ -171,7 +172,7 @@ int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin) {
   CostParams p;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
   p.geo_f4_n = M.geo_f4; p.geo_u32_n = M.geo_u32;
-  p.pts = ctx->d_pts; p.n_pts = ctx->n_pts; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = d_argmin; p.dist = nullptr;
+  p.pts = ctx->d_pts; p.n_pts = ctx->n_pts; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = d_argmin; p.dist = nullptr; p.perm = ctx->perm_on ? ctx->d_perm : nullptr;
   p.pts_per_block = choose_tile(ctx, ctx->n_pts, C);
   p.use_grid = ctx->use_grid ? 1 : 0;
   if (ctx->n_pts == 0) return 0;
@@ -292,6 +293,57 @@ int bake_grids(flash_ctx* ctx) {
 
 }  // namespace
 
+static int points_alloc(flash_ctx* ctx, int64_t n) {
+  if (ctx->pts_external) { ctx->d_pts = nullptr; ctx->cap_pts = 0; ctx->pts_external = false; }
+  if (n > ctx->cap_pts) {
+    if (ctx->d_pts) CU(cudaFree(ctx->d_pts));
+    ctx->d_pts = nullptr; ctx->cap_pts = 0;
+    CU(cudaMalloc((void**)&ctx->d_pts, (size_t)std::max<int64_t>(n, 1) * sizeof(float4)));
+    ctx->cap_pts = n;
+  }
+  return 0;
+}
+
+// H2D of the caller's AoS buffer, then convert + Morton-bin on the device (see flash_kernels.cuh)
+template <class T>
+static int points_ingest(flash_ctx* ctx, const T* xyz, int64_t n) {
+  CU(cudaSetDevice(ctx->device));
+  int rc = points_alloc(ctx, n); if (rc) return rc;
+  ctx->perm_on = false;
+  if (n > 0) {
+    const size_t bytes = (size_t)n * 3 * sizeof(T);
+    if (bytes > ctx->cap_stage) { if (ctx->d_stage) CU(cudaFree(ctx->d_stage)); ctx->d_stage = nullptr; ctx->cap_stage = 0; CU(cudaMalloc(&ctx->d_stage, bytes)); ctx->cap_stage = bytes; }
+    CU(cudaMemcpyAsync(ctx->d_stage, xyz, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    const T* src = (const T*)ctx->d_stage;
+    const unsigned nb = (unsigned)((n + 255) / 256);
+    if (ctx->sort_points && n >= 4096 && n < (1ll << 31)) {
+      if (!ctx->d_bins) CU(cudaMalloc((void**)&ctx->d_bins, (size_t)(SORT_BINS + 256 + 8) * sizeof(int)));
+      rc = ensure(ctx, ctx->d_perm, ctx->cap_perm, (size_t)n); if (rc) return rc;
+      int* bins = ctx->d_bins; int* sums = bins + SORT_BINS; unsigned* bounds = (unsigned*)(sums + 256);
+      CU(cudaMemsetAsync(bins, 0, (size_t)(SORT_BINS + 256) * sizeof(int), ctx->stream));
+      const unsigned init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+      CU(cudaMemcpyAsync(bounds, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+      const unsigned gb = (unsigned)std::min<long long>((n + 255) / 256, (long long)ctx->sm_count * 16);
+      points_bounds_kernel<T><<<gb, 256, 0, ctx->stream>>>(src, n, bounds);
+      points_hist_kernel<T><<<nb, 256, 0, ctx->stream>>>(src, n, bounds, bins);
+      bins_scan_local_kernel<<<SORT_BINS / 1024, 1024, 0, ctx->stream>>>(bins, sums);
+      bins_scan_add_kernel<<<SORT_BINS / 1024, 1024, 0, ctx->stream>>>(bins, sums);
+      points_scatter_kernel<T><<<nb, 256, 0, ctx->stream>>>(src, n, bounds, bins, ctx->d_pts, ctx->d_perm);
+      CU(cudaGetLastError());
+      ctx->launches += 5;
+      ctx->perm_on = true;
+    } else {
+      convert_points_kernel<T><<<nb, 256, 0, ctx->stream>>>(src, ctx->d_pts, n);
+      CU(cudaGetLastError());
+      ctx->launches++;
+    }
+    CU(cudaStreamSynchronize(ctx->stream));  // the caller may reuse xyz as soon as we return
+  }
+  ctx->n_pts = n; ctx->pts_set = true;
+  return FLASH_OK;
+}
+
+
 // ================================================================================================
 extern "C" {
 
@@ -306,6 +358,7 @@ int flash_model_create(const flash_model_desc* desc, const flash_options* opt, f
   std::string err;
   if (!build_model(desc, opt, ctx->hm, err)) { delete ctx; return fail(nullptr, FLASH_ERR_INVALID, err); }
   make_hot(ctx->hm.M, ctx->hot);
+  if (const char* e = getenv("FLASHSDF_NO_SORT")) ctx->sort_points = !(e[0] == '1');
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0) {
@@ -351,7 +404,7 @@ void flash_destroy(flash_ctx* ctx) {
   if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
   void* frees[] = {ctx->d_model, ctx->d_hot, ctx->d_geo_f4, ctx->d_geo_u32, ctx->d_grid_pool, ctx->pts_external ? nullptr : (void*)ctx->d_pts, ctx->d_stage,
                    ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, ctx->d_cost, ctx->d_grad, ctx->d_div, ctx->d_status, ctx->d_done, ctx->d_iters,
-                   ctx->d_argmin, ctx->d_qd, ctx->d_qi};
+                   ctx->d_argmin, ctx->d_qd, ctx->d_qi, ctx->d_bins, ctx->d_perm};
   for (void* p : frees) if (p) cudaFree(p);
   if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -364,51 +417,16 @@ int flash_num_states(const flash_ctx* ctx) { return ctx ? ctx->hm.M.nx : FLASH_E
 int flash_num_surfaces(const flash_ctx* ctx) { return ctx ? ctx->hm.M.n_surfaces : FLASH_ERR_INVALID; }
 int64_t flash_num_points(const flash_ctx* ctx) { return ctx ? ctx->n_pts : FLASH_ERR_INVALID; }
 
-static int points_alloc(flash_ctx* ctx, int64_t n) {
-  if (ctx->pts_external) { ctx->d_pts = nullptr; ctx->cap_pts = 0; ctx->pts_external = false; }
-  if (n > ctx->cap_pts) {
-    if (ctx->d_pts) CU(cudaFree(ctx->d_pts));
-    ctx->d_pts = nullptr; ctx->cap_pts = 0;
-    CU(cudaMalloc((void**)&ctx->d_pts, (size_t)std::max<int64_t>(n, 1) * sizeof(float4)));
-    ctx->cap_pts = n;
-  }
-  return 0;
-}
-
 int flash_points_set(flash_ctx* ctx, const double* xyz, int64_t n) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set: bad arguments");
-  CU(cudaSetDevice(ctx->device));
-  int rc = points_alloc(ctx, n); if (rc) return rc;
-  if (n > 0) {
-    const size_t bytes = (size_t)n * 3 * sizeof(double);
-    if (bytes > ctx->cap_stage) { if (ctx->d_stage) CU(cudaFree(ctx->d_stage)); ctx->d_stage = nullptr; ctx->cap_stage = 0; CU(cudaMalloc(&ctx->d_stage, bytes)); ctx->cap_stage = bytes; }
-    CU(cudaMemcpyAsync(ctx->d_stage, xyz, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    convert_points_f64<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>((const double*)ctx->d_stage, ctx->d_pts, n);
-    CU(cudaGetLastError());
-    ctx->launches++;
-    CU(cudaStreamSynchronize(ctx->stream));  // the caller may reuse xyz as soon as we return
-  }
-  ctx->n_pts = n; ctx->pts_set = true;
-  return FLASH_OK;
+  return points_ingest<double>(ctx, xyz, n);
 }
 
 int flash_points_set_f32(flash_ctx* ctx, const float* xyz, int64_t n) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_f32: bad arguments");
-  CU(cudaSetDevice(ctx->device));
-  int rc = points_alloc(ctx, n); if (rc) return rc;
-  if (n > 0) {
-    const size_t bytes = (size_t)n * 3 * sizeof(float);
-    if (bytes > ctx->cap_stage) { if (ctx->d_stage) CU(cudaFree(ctx->d_stage)); ctx->d_stage = nullptr; ctx->cap_stage = 0; CU(cudaMalloc(&ctx->d_stage, bytes)); ctx->cap_stage = bytes; }
-    CU(cudaMemcpyAsync(ctx->d_stage, xyz, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    convert_points_f32<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>((const float*)ctx->d_stage, ctx->d_pts, n);
-    CU(cudaGetLastError());
-    ctx->launches++;
-    CU(cudaStreamSynchronize(ctx->stream));
-  }
-  ctx->n_pts = n; ctx->pts_set = true;
-  return FLASH_OK;
+  return points_ingest<float>(ctx, xyz, n);
 }
 
 int flash_points_set_device(flash_ctx* ctx, const void* device_float4, int64_t n) {
@@ -417,7 +435,7 @@ int flash_points_set_device(flash_ctx* ctx, const void* device_float4, int64_t n
   if (((uintptr_t)device_float4 & 15) != 0) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_device: pointer must be 16-byte aligned");
   CU(cudaSetDevice(ctx->device));
   if (!ctx->pts_external && ctx->d_pts) CU(cudaFree(ctx->d_pts));
-  ctx->d_pts = (float4*)device_float4; ctx->cap_pts = 0; ctx->pts_external = true;
+  ctx->d_pts = (float4*)device_float4; ctx->cap_pts = 0; ctx->pts_external = true; ctx->perm_on = false;
   ctx->n_pts = n; ctx->pts_set = true;
   return FLASH_OK;
 }
@@ -467,13 +485,13 @@ int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t 
   rc = ensure(ctx, ctx->d_qi, ctx->cap_qi, (size_t)n); if (rc) return rc;
   double* d_xyz = ctx->d_qd; float4* d_f4 = (float4*)(ctx->d_qd + off_f4); double* d_dist = ctx->d_qd + off_dist;
   CU(cudaMemcpyAsync(d_xyz, xyz, (size_t)n * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-  convert_points_f64<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_xyz, d_f4, n);
+  convert_points_kernel<double><<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_xyz, d_f4, n);
   CU(cudaGetLastError());
   ctx->launches++; ctx->last.launches++;
   CostParams p;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
   p.geo_f4_n = M.geo_f4; p.geo_u32_n = M.geo_u32;
-  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist;
+  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist; p.perm = nullptr;
   p.pts_per_block = choose_tile(ctx, n, 1); p.use_grid = ctx->use_grid ? 1 : 0;
   const int tiles = (int)((n + p.pts_per_block - 1) / p.pts_per_block);
   const size_t smem = cost_layout(ctx, false).total;

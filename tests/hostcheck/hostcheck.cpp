@@ -59,9 +59,11 @@ void hc_accumulate(void* p, const double* tab, const float* pts, long long n, in
   const HotModel& H = h->hot;
   GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
   float lb[MAX_CONVEX];
+  float tabf[12 * MAX_CONVEX];
+  for (int i = 0; i < 12 * H.n_convex; ++i) tabf[i] = (float)tab[i];
   for (long long i = 0; i < n; ++i) {
     PointEval e;
-    eval_point(H, G, tab, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], lb, 1, use_grid != 0, e);
+    eval_point(H, G, tab, tabf, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], lb, 1, use_grid != 0, e);
     double dv = e.is_skin ? e.sk.s : (double)e.d;
     if (dist) dist[i] = dv;
     if (argmin) argmin[i] = e.arg;
@@ -93,6 +95,17 @@ void hc_epilogue(void* p, const double* x, const double* tab, const double* aux,
   epilogue_config(M, x, tab, aux, acc, w_def, scratch.data(), cost, grad);
 }
 
+// instrumentation (only meaningful when built with -DFLASH_COUNTERS)
+void hc_counters(long long* out, int reset) {
+#ifdef FLASH_COUNTERS
+  Counters& c = counters();
+  out[0] = c.points; out[1] = c.narrow; out[2] = c.inside; out[3] = c.gjk_iters; out[4] = c.plane_tests; out[5] = c.vert_tests; out[6] = c.lb_tests;
+  if (reset) c = Counters{0, 0, 0, 0, 0, 0, 0};
+#else
+  for (int i = 0; i < 7; ++i) out[i] = -1;
+#endif
+}
+
 // signed distance of geometry-frame points y[n][3] to convex slot j
 void hc_hull_sd(void* p, int j, const float* y, long long n, float* d, float* nrm) {
   HC* h = (HC*)p;
@@ -100,7 +113,7 @@ void hc_hull_sd(void* p, int j, const float* y, long long n, float* d, float* nr
   const F4* f4 = h->hm.geo_f4.data(); const uint32_t* u32 = h->hm.geo_u32.data();
   for (long long i = 0; i < n; ++i) {
     F3 nn;
-    d[i] = hull_sd(f4 + C.off_planes, u32 + C.off_tris, f4 + C.off_verts, C.nplanes, C.nverts, f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]), nn);
+    d[i] = hull_sd(f4 + C.off_planes, u32 + C.off_tris, f4 + C.off_verts, C.nplanes_pad, C.nverts_pad, f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]), 3.0e38f, nn);
     nrm[3 * i] = nn.x; nrm[3 * i + 1] = nn.y; nrm[3 * i + 2] = nn.z;
   }
 }

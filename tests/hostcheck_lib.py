@@ -24,8 +24,8 @@ def build():
             os.path.join(ROOT, "include", "flashsdf.h")]
     if os.path.exists(LIB) and all(os.path.getmtime(LIB) >= os.path.getmtime(s) for s in srcs):
         return
-    subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-Wno-unused-function", "-Wno-maybe-uninitialized",
-                           "-ffp-contract=off", "-o", LIB, os.path.join(HC_DIR, "hostcheck.cpp")])
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-Wno-unused-function", "-Wno-maybe-uninitialized", "-Wno-unknown-pragmas",
+                           "-ffp-contract=off", "-DFLASH_COUNTERS", "-o", LIB, os.path.join(HC_DIR, "hostcheck.cpp")])
 
 
 def lib():
@@ -42,6 +42,7 @@ def lib():
         L.hc_prepare.argtypes = [vp, c_double_p, c_double_p, c_double_p]; L.hc_prepare.restype = None
         L.hc_accumulate.argtypes = [vp, c_double_p, c_float_p, C.c_longlong, C.c_int, c_double_p, c_double_p, c_int32_p]; L.hc_accumulate.restype = None
         L.hc_epilogue.argtypes = [vp, c_double_p, c_double_p, c_double_p, c_double_p, C.c_double, c_double_p, c_double_p]; L.hc_epilogue.restype = None
+        L.hc_counters.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_counters.restype = None
         L.hc_hull_sd.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_float_p, c_float_p]; L.hc_hull_sd.restype = None
         _lib = L
     return _lib
@@ -100,3 +101,9 @@ class HostCheck:
         d = np.empty(len(y), np.float32); n = np.empty((len(y), 3), np.float32)
         lib().hc_hull_sd(self.h, j, y.ctypes.data_as(c_float_p), len(y), d.ctypes.data_as(c_float_p), n.ctypes.data_as(c_float_p))
         return d, n
+
+
+def counters(reset=True):
+    out = (C.c_longlong * 7)()
+    lib().hc_counters(out, 1 if reset else 0)
+    return dict(zip(("points", "narrow", "inside", "gjk_iters", "plane_tests", "vert_tests", "lb_tests"), list(out)))
