@@ -217,6 +217,13 @@ int flash_device_info(const flash_ctx* ctx, int32_t* sm_count, int32_t* clock_kh
 int flash_grid_report(const flash_ctx* ctx, int32_t surface, int32_t dims[3], double* spacing,
                       double* max_abs_err);
 
+/* grid mode: copies surface's grid (x fastest, then y, then z; dims from flash_grid_report) and its
+ * origin in the geometry frame (the surface frame re-centred on the hull centroid, returned as the
+ * row-major [R|t] geometry->body transform) so that a caller can re-evaluate the same trilinear
+ * formula -- the parity definition of grid mode. */
+int flash_grid_download(const flash_ctx* ctx, int32_t surface, double origin[3], double geometry_to_body[12],
+                        float* values);
+
 #ifdef __cplusplus
 }
 #endif

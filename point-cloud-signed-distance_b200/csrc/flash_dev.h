@@ -380,9 +380,10 @@ FLASH_HD float hull_sd(const F4* __restrict__ planes, const uint32_t* __restrict
     q = tri_closest0(p0, p1, p2, u0, u1, u2);
     simplex_from(S, p0, j0, u0, p1, j1, u1, p2, j2, u2);
   }
-  // D (the largest plane distance) is a lower bound of the distance and |q| an upper bound: when
-  // they meet, q is the projection onto the face and no support scan is needed to certify it.
-  bool certified = dot(q, q) <= D * D * (1.f + 2e-6f);
+  // If the closest point of the start triangle is in its interior, it is the orthogonal projection of
+  // y onto the supporting plane fs and lies on the hull: it IS the closest point (no tolerance
+  // involved), so the support scan that would merely certify it is skipped.
+  const bool certified = S.ns == 3;
   for (int it = 0; it < GJK_MAX_ITER && !certified; ++it) {
     float dd = dot(q, q);
     if (!(dd > 0.f)) break;
@@ -496,13 +497,11 @@ FLASH_HD bool grid_sd(const ConvexC& C, const float* __restrict__ pool, F3 y, fl
 struct SkinEval { double s, f, ginv; D3 nh; };
 FLASH_HD double dsqrt_fast(double r2) {
 #ifdef __CUDA_ARCH__
-  // fp32 rsqrt seed + two fp64 Newton steps on 1/sqrt, then r = r2 * rinv with a final correction
-  if (r2 <= 0.0) return 0.0;
-  double y = (double)rsqrtf((float)r2);
-  y = y * (1.5 - 0.5 * r2 * y * y);
-  y = y * (1.5 - 0.5 * r2 * y * y);
-  double r = r2 * y;
-  return fma(fma(-r, r, r2), 0.5 * y, r);
+  // fp32 rsqrt seed (rel. error 2^-22) + one fp64 Newton step on 1/sqrt: rel. error 1.5*(2^-22)^2 =
+  // 8.5e-14, far below the 1e-10 the RBF sums need; r2 == 0 gives exactly 0.
+  double y = (double)rsqrtf(fmaxf((float)r2, 1e-30f));
+  y = y * fma(-0.5 * r2, y * y, 1.5);
+  return r2 * y;
 #else
   return sqrt(r2);
 #endif

@@ -652,4 +652,19 @@ int flash_grid_report(const flash_ctx* ctx, int32_t surface, int32_t dims[3], do
   return FLASH_OK;
 }
 
+int flash_grid_download(const flash_ctx* ctx, int32_t surface, double origin[3], double geometry_to_body[12], float* values) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  const ModelC& M = ctx->hm.M;
+  if (surface < 0 || surface >= M.n_surfaces || M.surf_kind[surface] != SURF_CONVEX || !ctx->use_grid) return FLASH_ERR_INVALID;
+  const ConvexC& C = M.cvx[M.surf_slot[surface]];
+  if (origin) for (int k = 0; k < 3; ++k) origin[k] = C.g_org[k];
+  if (geometry_to_body) for (int i = 0; i < 3; ++i) { for (int j = 0; j < 3; ++j) geometry_to_body[4 * i + j] = C.frame[3 * i + j]; geometry_to_body[4 * i + 3] = C.frame[9 + i]; }
+  if (values) {
+    const size_t n = (size_t)C.g_dim[0] * C.g_dim[1] * C.g_dim[2];
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return FLASH_ERR_CUDA;
+    if (cudaMemcpy(values, ctx->d_grid_pool + C.g_off, n * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess) return FLASH_ERR_CUDA;
+  }
+  return FLASH_OK;
+}
+
 }  // extern "C"

@@ -146,6 +146,19 @@ class Manipulator:  # src/Flash.jl:62-65
         self.check(_lib.lib().flash_last_timing(self.ctx(), C.byref(t)))
         return {k: getattr(t, k) for k, _ in Timing._fields_}
 
+    def grid_report(self, surface):
+        """grid mode: (dims, spacing, max |trilinear - exact| sampled at cell centres) of a convex surface."""
+        dims = (C.c_int32 * 3)(); sp = C.c_double(); err = C.c_double()
+        self.check(_lib.lib().flash_grid_report(self.ctx(), surface, dims, C.byref(sp), C.byref(err)))
+        return tuple(dims), sp.value, err.value
+
+    def grid_download(self, surface):
+        dims, sp, _ = self.grid_report(surface)
+        org = np.zeros(3); g2b = np.zeros(12); vals = np.empty(dims[2] * dims[1] * dims[0], np.float32)
+        self.check(_lib.lib().flash_grid_download(self.ctx(), surface, org.ctypes.data_as(c_double_p), g2b.ctypes.data_as(c_double_p),
+                                                  vals.ctypes.data_as(C.POINTER(C.c_float))))
+        return vals.reshape(dims[2], dims[1], dims[0]), org, sp, g2b.reshape(3, 4)
+
     def __del__(self):
         try:
             self.invalidate()

@@ -141,3 +141,190 @@ def test_errors_are_reported_not_thrown_across_abi():
         bad = flash.models.beanbag()
         bad.surfaces[0].surface_points[0] = bad.surfaces[0].surface_points[1]  # coincident control points
         flash.gradientdescent.CostFunctor(bad, np.ones((4, 3)))(flash.gradientdescent.flatten(flash.ManipulatorState(bad)))
+
+
+# ------------------------------------------------------------------ golden vectors through the CUDA path
+import os
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_v1.npz"))
+BUILDERS = {"two_link_arm": flash.models.two_link_arm, "beanbag": flash.models.beanbag, "squishable": flash.models.squishable,
+            "irb140": flash.models.irb140, "irb_and_squishable": flash.models.irb_and_squishable}
+
+
+@pytest.mark.parametrize("name", sorted(BUILDERS))
+def test_golden_vectors_on_gpu(name):
+    m = BUILDERS[name]()
+    x, pts = GOLD[name + "/x"], GOLD[name + "/pts"]
+    c, g, a = flash.gradientdescent.CostFunctor(m, pts).batch(x, argmin=True)
+    assert abs(c[0] - float(GOLD[name + "/cost"])) <= RTOL * float(GOLD[name + "/cost"])
+    gg = GOLD[name + "/grad"]
+    assert np.abs(g[0] - gg).max() <= RTOL * np.abs(gg).max()
+    per = GOLD[name + "/per_surface"]
+    for i in np.nonzero(a[0] != GOLD[name + "/argmin"])[0]:
+        s = np.sort(per[i]); assert s[1] - s[0] < 2e-6
+
+
+def test_points_f32_and_device_entry_points():
+    import ctypes as C
+    import torch
+    from flash import _lib
+    rng = np.random.default_rng(9)
+    m = flash.models.irb140()
+    X = rng.uniform(-1, 1, (2, 6))
+    pts = _points(rng, 50000, [-0.6, -0.7, -0.2], [0.9, 0.7, 1.1])
+    f = flash.gradientdescent.CostFunctor(m, pts)
+    ref = f.batch(X, argmin=True)
+    L = _lib.lib()
+    p32 = np.ascontiguousarray(pts, np.float32)
+    m.check(L.flash_points_set_f32(m.ctx(), p32.ctypes.data_as(C.POINTER(C.c_float)), len(p32)))
+    got = f.batch(X, argmin=True)
+    assert np.allclose(got[0], ref[0], rtol=1e-9) and np.abs(got[1] - ref[1]).max() <= 1e-6 * np.abs(ref[1]).max() and (got[2] == ref[2]).all()
+    d4 = torch.zeros((len(pts), 4), dtype=torch.float32, device="cuda")
+    d4[:, :3] = torch.from_numpy(p32).cuda()
+    torch.cuda.synchronize()
+    m.check(L.flash_points_set_device(m.ctx(), C.c_void_p(d4.data_ptr()), len(pts)))
+    got = f.batch(X, argmin=True)          # caller's order, no binning
+    assert np.allclose(got[0], ref[0], rtol=1e-9) and np.abs(got[1] - ref[1]).max() <= 1e-6 * np.abs(ref[1]).max() and (got[2] == ref[2]).all()
+
+
+def test_k3_real_kinect_cloud():
+    """examples/squishable.ipynb: the 25,571-point real cloud (fixture tests/golden/squishable_unsquished_xyz.npy)."""
+    pts = np.load(os.path.join(os.path.dirname(__file__), "golden", "squishable_unsquished_xyz.npy")).astype(np.float64)
+    m = flash.models.squishable()
+    x = flash.gradientdescent.flatten(flash.ManipulatorState(m))
+    x[4:7] = pts.mean(0)
+    X = np.stack([x, x + 0.01])
+    _compare(m, X, pts)
+
+
+# ------------------------------------------------------------------ depth rendering (row A9)
+def _raycast_case(m, x, sensor, cam):
+    st = flash.ManipulatorState(m)
+    flash.gradientdescent.unflatten_(st, x)
+    skin = flash.skin(st)
+    depths = flash.depthsensors.raycast_depths(skin, sensor, cam)
+    hits = flash.depthsensors.raycast_points(skin, sensor, cam)
+    do, ho = ol.Oracle(m).raycast(x, sensor.rays.reshape(-1, 3), cam, mode=ol.GJK)
+    d = depths.reshape(-1)
+    both = np.isfinite(d) & np.isfinite(do)
+    flips = (np.isfinite(d) != np.isfinite(do)).sum()
+    assert flips <= max(2, int(0.01 * np.isfinite(do).sum())), flips      # silhouette rays may flip hit/miss
+    # both marches stop anywhere inside |field| <= 1e-5 (src/depthsensors.jl:57,64): depths agree to that band / slope
+    assert np.abs(d[both] - do[both]).max() < 2e-4
+    assert np.median(np.abs(d[both] - do[both])) < 2e-5
+    assert len(hits) == np.isfinite(d).sum()
+    # hits are in ray order and lie on the rays
+    idx = np.nonzero(np.isfinite(d))[0]
+    w = (cam[:, :3] @ (sensor.rays.reshape(-1, 3)[idx] * d[idx, None]).T).T + cam[:, 3]
+    assert np.allclose(w, hits, atol=1e-9)
+    return both.sum()
+
+
+def test_raycast_two_link_arm_k1():
+    m = flash.models.two_link_arm()
+    sensor = flash.depthsensors.Kinect(41, 41)
+    cam = flash.depthsensors.affine((0, 0, 4), (1, 0, 0), np.pi)          # examples/manipulator.ipynb cell 2
+    assert _raycast_case(m, np.array([np.pi, 1.3]), sensor, cam) > 20
+
+
+def test_raycast_irb140():
+    m = flash.models.irb140()
+    sensor = flash.depthsensors.Kinect(120, 160)
+    cam = flash.depthsensors.affine((0, 1.5, 0.5), (1, 0, 0), np.pi / 2)  # examples/irb140.ipynb cell 4
+    assert _raycast_case(m, np.zeros(6), sensor, cam) > 500
+
+
+def test_raycast_then_track_squishable():
+    """examples/deformable_manipulator.ipynb flow on the squishable: render a deformed state, start
+    from the identity pose, run estimate_state; host loop and on-device loop agree."""
+    rng = np.random.default_rng(11)
+    m = flash.models.squishable()
+    true = flash.ManipulatorState(m)
+    true.mechanism_state.q[4:7] = [0.1, -0.05, 0.08]
+    true.deformation_data[:] = 0.03 * (rng.random(36) - 0.5)
+    sensor = flash.depthsensors.Kinect(80, 80)
+    cam = flash.depthsensors.affine((0, 0, 2), (1, 0, 0), np.pi)
+    pts = flash.depthsensors.raycast(true, sensor, cam)
+    assert len(pts) > 100
+    x0 = flash.gradientdescent.flatten(flash.ManipulatorState(m))
+    div = np.r_[np.ones(7), 1e-3 * np.ones(36)]                            # examples/squishable.ipynb cell 9
+    solver = flash.tracking.NaiveSolver(43, rate=0.01, max_step=0.1, iteration_limit=20, precondition_divisors=div)
+    trace = []
+    xh = flash.tracking.estimate_state(m, pts, x0, callback=lambda x, c: trace.append(c), solver=solver)
+    xd = flash.tracking.estimate_state(m, pts, x0, solver=solver, on_device=True)
+    assert len(trace) == 20 and trace[-1] < trace[0]
+    assert np.abs(xh - xd).max() < 1e-6 * max(1.0, np.abs(xh).max())
+    xo, co, it = ol.Oracle(m).estimate_state(x0, pts, rate=0.01, max_step=0.1, iteration_limit=20, divisors=div, mode=ol.GJK)
+    assert np.abs(xh - xo).max() < 1e-4                                    # 20 iterations of a 1e-5-accurate gradient
+
+
+def test_on_device_estimate_state_batched_with_tolerance():
+    rng = np.random.default_rng(12)
+    m = flash.models.irb140()
+    true = np.zeros(6)
+    st = flash.ManipulatorState(m)
+    sensor = flash.depthsensors.Kinect(60, 80)
+    cam = flash.depthsensors.affine((0, 1.5, 0.5), (1, 0, 0), np.pi / 2)
+    pts = flash.depthsensors.raycast(st, sensor, cam)
+    import ctypes as C
+    from flash import _lib
+    from flash._desc import SolverParams, c_double_p, c_int32_p
+    f = flash.gradientdescent.CostFunctor(m, pts)
+    X = true + 0.2 * rng.standard_normal((4, 6))
+    X0 = X.copy()
+    sp = SolverParams(20.0, 0.5, 40, 1e-4, 10.0)                            # examples/irb140.ipynb cell 9
+    cost = np.zeros(4); iters = np.zeros(4, np.int32)
+    m.check(_lib.lib().flash_estimate_state(m.ctx(), X.ctypes.data_as(c_double_p), 4, C.byref(sp), None, cost.ctypes.data_as(c_double_p), iters.ctypes.data_as(c_int32_p)))
+    c0, _, _ = f.batch(X0, gradient=False)
+    assert (cost < c0).all() and (iters > 0).all() and (iters <= 40).all()
+    c1, _, _ = f.batch(X, gradient=False)
+    assert np.allclose(c1, cost, rtol=1e-9)
+
+
+# ------------------------------------------------------------------ grid mode (north_star's gather design)
+def _trilinear_f64(vals, org, h, y):
+    g = (y - org) / h
+    i = np.floor(g).astype(int); f = g - i
+    def at(dx, dy, dz):
+        return vals[i[:, 2] + dz, i[:, 1] + dy, i[:, 0] + dx].astype(np.float64)
+    c00 = at(0, 0, 0) * (1 - f[:, 0]) + at(1, 0, 0) * f[:, 0]; c10 = at(0, 1, 0) * (1 - f[:, 0]) + at(1, 1, 0) * f[:, 0]
+    c01 = at(0, 0, 1) * (1 - f[:, 0]) + at(1, 0, 1) * f[:, 0]; c11 = at(0, 1, 1) * (1 - f[:, 0]) + at(1, 1, 1) * f[:, 0]
+    c0 = c00 * (1 - f[:, 1]) + c10 * f[:, 1]; c1 = c01 * (1 - f[:, 1]) + c11 * f[:, 1]
+    return c0 * (1 - f[:, 2]) + c1 * f[:, 2]
+
+
+def test_grid_mode_matches_same_grid_in_fp64_and_reports_deviation():
+    """Grid-mode parity: the kernel's manual fp32 trilinear lookup == the same trilinear formula in
+    fp64 on the same (downloaded) grid; its deviation from the exact SDF is bounded by the bake report."""
+    rng = np.random.default_rng(13)
+    m = flash.models.table()
+    m.set_options(sdf_mode=1, grid_spacing=0.005, grid_margin=0.1)
+    vals, org, h, g2b = m.grid_download(0)
+    dims, sp, err = m.grid_report(0)
+    assert vals.shape == (dims[2], dims[1], dims[0]) and np.isclose(sp, 0.005) and 0 < err < 0.005
+    x = np.array([1.0, 0, 0, 0, 0, 0, 0])                       # identity pose: world == body == geometry + centroid
+    pts = _points(rng, 20000, [-0.33, -0.33, -0.13], [0.33, 0.33, 0.13])
+    st = flash.ManipulatorState(m)
+    d_grid = flash.skin(st).eval(pts)
+    y = pts - g2b[:, 3]
+    ref = _trilinear_f64(vals, org, h, y)
+    assert np.abs(d_grid - ref).max() < 2e-6
+    exact = flash.models.table()
+    d_exact = flash.skin(flash.ManipulatorState(exact)).eval(pts)
+    assert np.abs(d_grid - d_exact).max() <= err * 1.5 + 1e-6
+    far = _points(rng, 1000, [0.6, 0.6, 0.6], [0.9, 0.9, 0.9])  # outside the grid: falls back to the exact path
+    assert np.abs(flash.skin(st).eval(far) - flash.skin(flash.ManipulatorState(exact)).eval(far)).max() < 1e-6
+
+
+def test_grid_mode_cost_close_to_exact_on_combined_scene():
+    rng = np.random.default_rng(14)
+    mg, me = flash.models.irb_and_squishable(), flash.models.irb_and_squishable()
+    mg.set_options(sdf_mode=1, grid_spacing=0.004)
+    x0 = flash.gradientdescent.flatten(flash.ManipulatorState(me))
+    x0[4:7] = [0.0, 0.0, 0.75]; x0[17:20] = [0.55, 0.45, 0.8]; x0[24:27] = [0.4, 0.0, 0.6]
+    X = np.stack([x0, x0 + np.r_[0.03 * rng.standard_normal(27), np.zeros(36)]])
+    pts = _points(rng, 40000, [-0.5, -0.5, 0.5], [1.0, 0.5, 2.0])
+    cg, gg, ag = flash.gradientdescent.CostFunctor(mg, pts).batch(X, argmin=True)
+    ce, ge, ae = flash.gradientdescent.CostFunctor(me, pts).batch(X, argmin=True)
+    assert np.abs(cg - ce).max() <= 2e-3 * np.abs(ce).max()
+    assert np.abs(gg - ge).max() <= 2e-2 * np.abs(ge).max()
+    assert (ag != ae).mean() < 5e-3

@@ -1,0 +1,103 @@
+"""CPU tests of the PRODUCT's __host__ __device__ math (csrc/flash_dev.h, csrc/flash_host.h) compiled
+with g++ and replayed serially by tests/hostcheck -- the same formulas the CUDA kernels execute --
+against the oracle.  (The CUDA path itself is tested in test_gpu_parity.py.)"""
+import os
+
+import numpy as np
+import pytest
+
+import flash
+import hostcheck_lib as hl
+import oracle_lib as ol
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "golden_v1.npz"))
+BUILDERS = {"two_link_arm": flash.models.two_link_arm, "beanbag": flash.models.beanbag, "squishable": flash.models.squishable,
+            "irb140": flash.models.irb140, "irb_and_squishable": flash.models.irb_and_squishable}
+
+
+@pytest.mark.parametrize("name", sorted(BUILDERS))
+def test_kernel_math_matches_golden(name):
+    h = hl.HostCheck(BUILDERS[name]())
+    x, pts = GOLD[name + "/x"], GOLD[name + "/pts"]
+    c, g, dist, arg = h.cost_grad(x, pts)
+    assert abs(c - float(GOLD[name + "/cost"])) <= 1e-5 * abs(float(GOLD[name + "/cost"]))
+    gg = GOLD[name + "/grad"]
+    assert np.abs(g - gg).max() <= 1e-5 * np.abs(gg).max()
+    per = GOLD[name + "/per_surface"]
+    assert np.abs(dist - per.min(1)).max() < 2e-6
+    bad = np.nonzero(arg != GOLD[name + "/argmin"])[0]
+    for i in bad:  # only exact-tie flips within fp32 rounding are tolerated
+        s = np.sort(per[i]); assert s[1] - s[0] < 2e-6
+
+
+def test_kernel_math_large_random_scene():
+    rng = np.random.default_rng(3)
+    m = flash.models.irb_and_squishable()
+    h, o = hl.HostCheck(m), ol.Oracle(m)
+    x = GOLD["irb_and_squishable/x"]
+    pts = rng.uniform([-0.8, -0.8, -0.3], [1.0, 0.8, 1.2], (30000, 3)).astype(np.float32).astype(np.float64)
+    c, g, dist, arg = h.cost_grad(x, pts)
+    co, go = o.cost_grad(x, pts, method="adjoint", mode=ol.GJK)
+    do, ao = o.skin(x, pts, mode=ol.GJK, argmin=True)
+    assert abs(c - co) <= 1e-6 * co and np.abs(g - go).max() <= 1e-6 * np.abs(go).max()
+    assert np.abs(dist - do).max() < 2e-6 and (arg != ao).sum() <= 3
+
+
+def test_hull_builder_agrees_with_oracle_hull():
+    m = flash.models.irb_and_squishable()
+    h, o = hl.HostCheck(m), ol.Oracle(m)
+    conv = [s for s in range(9) if s != 7]
+    for j, s in enumerate(conv):
+        nv, npl, lo, hi, depth = h.convex_info(j)
+        onv, onp, _ = o.hull_info(s)
+        assert (nv, npl) == (onv, onp)
+        assert (hi > lo).all() and depth > 0
+
+
+def test_hull_sd_exact_on_box_and_lower_bound_property():
+    m = flash.models.table()
+    h = hl.HostCheck(m)
+    rng = np.random.default_rng(5)
+    y = rng.uniform(-0.6, 0.6, (5000, 3)).astype(np.float32)
+    d, n = h.hull_sd(0, y)
+    hw = np.array([0.25, 0.25, 0.05])
+    q = np.abs(y.astype(np.float64)) - hw
+    ref = np.linalg.norm(np.maximum(q, 0), axis=1) + np.minimum(q.max(1), 0)
+    assert np.abs(d - ref).max() < 2e-7
+    assert np.allclose(np.linalg.norm(n, axis=1), 1.0, atol=1e-5)
+    # finite-difference check of the returned gradient away from the medial axis / edges
+    eps = 1e-3
+    for k in range(3):
+        e = np.zeros(3, np.float32); e[k] = eps
+        dp, _ = h.hull_sd(0, y + e); dm, _ = h.hull_sd(0, y - e)
+        fd = (dp.astype(np.float64) - dm) / (2 * eps)
+        ok = np.abs(fd - n[:, k]) < 5e-2
+        assert ok.mean() > 0.97
+
+
+def test_linear_in_points_and_shardable():
+    """acc(A u B) = acc(A) + acc(B): the property the multi-GPU sharding relies on."""
+    m = flash.models.irb_and_squishable()
+    h = hl.HostCheck(m)
+    x, pts = GOLD["irb_and_squishable/x"], GOLD["irb_and_squishable/pts"]
+    tab, aux = h.prepare(x)
+    a, _, _ = h.accumulate(tab, pts)
+    a1, _, _ = h.accumulate(tab, pts[:100]); a2, _, _ = h.accumulate(tab, pts[100:])
+    assert np.allclose(a, a1 + a2, rtol=1e-12, atol=1e-12)
+
+
+def test_model_validation_errors():
+    import ctypes as C
+    from flash._desc import PackedModel
+    m = flash.models.table()
+    m.surfaces[0].vertices = m.surfaces[0].vertices[:3]       # not a volume
+    with pytest.raises(RuntimeError, match="at least 4"):
+        hl.HostCheck(m)
+    m2 = flash.models.two_link_arm()
+    m2.mechanism.bodies[0].parent = 1                         # not parents-first
+    with pytest.raises(RuntimeError, match="parents-first"):
+        hl.HostCheck(m2)
+    m3 = flash.models.beanbag()
+    p = PackedModel(m3); p.desc.abi_version = 99
+    assert not hl.lib().hc_model_create(C.byref(p.desc), None)
+    assert b"abi_version" in hl.lib().hc_last_error()

@@ -1,0 +1,44 @@
+"""Summarise an .ncu-rep (read on the CPU box): key raw metrics + hottest CUDA source lines."""
+import csv
+import subprocess
+import sys
+
+rep = sys.argv[1]
+top = int(sys.argv[2]) if len(sys.argv) > 2 else 30
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(raw.splitlines()))
+hdr, units = rows[0], rows[1]
+keys = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "lts__t_bytes.sum", "launch__registers_per_thread", "launch__grid_size",
+        "launch__shared_mem_per_block_dynamic", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "smsp__thread_inst_executed_per_inst_executed.ratio", "smsp__inst_executed.sum", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+        "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio", "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio", "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio", "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_not_selected_per_issue_active.ratio", "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+        "smsp__warps_eligible.avg.per_cycle_active", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"]
+for r in rows[2:]:
+    name = r[hdr.index("Kernel Name")] if "Kernel Name" in hdr else "?"
+    print("== kernel:", name[:100])
+    for k in keys:
+        if k in hdr:
+            i = hdr.index(k)
+            print("  %-85s %s %s" % (k, r[i], units[i]))
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
+cur, stats = None, []
+for r in csv.reader(src.splitlines()):
+    if len(r) >= 2 and r[0] == "File Path":
+        cur = r[1].split("/")[-1]
+    elif len(r) > 8 and r[0].isdigit():
+        try:
+            stats.append((cur, int(r[0]), r[1].strip()[:95], int(r[6] or 0), int(r[7] or 0), int(r[8] or 0)))
+        except ValueError:
+            pass
+tot = sum(s[3] for s in stats) or 1
+toti = sum(s[4] for s in stats) or 1
+print("== hottest source lines (stall samples %%, instructions %%, active threads per instruction); total samples %d, warp instructions %d" % (tot, toti))
+for s in sorted(stats, key=lambda s: -s[3])[:top]:
+    print("%s:%4d samp %5.1f%% inst %5.1f%% thr/inst %5.1f | %s" % (s[0], s[1], 100 * s[3] / tot, 100 * s[4] / toti, s[5] / max(s[4], 1), s[2]))
