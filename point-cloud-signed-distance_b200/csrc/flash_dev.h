@@ -453,8 +453,7 @@ FLASH_HD float aabb_lower_bound(const float* lo, const float* hi, float depth_bo
 }
 
 // world point -> geometry frame, fp64 FMA chain rounded once to fp32 (DESIGN.md "precision")
-FLASH_HD F3 to_geometry(const double* __restrict__ T, float px, float py, float pz) {
-  double x = px, y = py, z = pz;
+FLASH_HD F3 to_geometry(const double* __restrict__ T, double x, double y, double z) {
   double a = fma(T[0], x, fma(T[1], y, fma(T[2], z, T[9])));
   double b = fma(T[3], x, fma(T[4], y, fma(T[5], z, T[10])));
   double c = fma(T[6], x, fma(T[7], y, fma(T[8], z, T[11])));
@@ -575,8 +574,10 @@ FLASH_HD bool lex_less(float d, int s, float best, int arg) { return d < best ||
 // `lb` is per-thread scratch of n_convex floats with stride lb_stride.
 // Convex bodies are culled with their AABB lower bound: a body is evaluated exactly only if its
 // bound can still beat the best value so far, which cannot change the min or the argmin.
+// The point is passed in fp64: the cost path feeds fp32 points (exact in fp64), the ray marcher its
+// fp64 sample positions.
 FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __restrict__ tab, const float* __restrict__ tabf,
-                         float px, float py, float pz, float* lb, int lb_stride, bool use_grid, PointEval& out) {
+                         double px, double py, double pz, float* lb, int lb_stride, bool use_grid, PointEval& out) {
   const ConvexC* __restrict__ cvx = M.cvx;
   float best = 3.0e38f; int arg = 0x7fffffff; int slot = -1; int is_skin = 0;
   out.y = f3(0, 0, 0); out.n = f3(0, 0, 0);
@@ -584,7 +585,7 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
   for (int k = 0; k < M.n_skins; ++k) {
     const SkinC& K = M.skin[k];
     const double* c = tab + K.tab_off;
-    SkinEval e = skin_eval(c, c + 3 * K.npts, K.npts, M.normalize != 0, (double)px, (double)py, (double)pz);
+    SkinEval e = skin_eval(c, c + 3 * K.npts, K.npts, M.normalize != 0, px, py, pz);
     float d = (float)e.s;
     if (lex_less(d, K.surface, best, arg)) { best = d; arg = K.surface; slot = k; is_skin = 1; out.sk = e; }
   }
@@ -592,7 +593,7 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
   FLASH_COUNT(points, 1); FLASH_COUNT(lb_tests, nc);
   int j0 = -1; float lb0 = 3.0e38f;
   for (int j = 0; j < nc; ++j) {
-    F3 y = to_geometry_f32(tabf + 12 * j, px, py, pz);
+    F3 y = to_geometry_f32(tabf + 12 * j, (float)px, (float)py, (float)pz);
     float l = aabb_lower_bound(cvx[j].lo, cvx[j].hi, cvx[j].depth_bound, y);
     lb[j * lb_stride] = l;
     if (l < lb0) { lb0 = l; j0 = j; }

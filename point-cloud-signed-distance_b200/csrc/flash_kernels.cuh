@@ -167,11 +167,12 @@ __global__ void __launch_bounds__(BLOCK, 2) cost_kernel(const CostParams p) {
     const bool valid = i < tile1;
     PointEval e;
     e.d = 0.f; e.arg = -1; e.slot = -1; e.is_skin = 0;
+    e.y = f3(0.f, 0.f, 0.f); e.n = f3(0.f, 0.f, 0.f);   // lanes past the tile end must contribute exact zeros
     float px = 0.f, py = 0.f, pz = 0.f;
     if (valid) {
       const float4 P = __ldg(p.pts + i);
       px = P.x; py = P.y; pz = P.z;
-      eval_point(H, G, tab, tabf, px, py, pz, lb, BLOCK, p.use_grid != 0, e);
+      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, lb, BLOCK, p.use_grid != 0, e);
     }
     if (DIST) {
       if (valid) {
@@ -192,9 +193,9 @@ __global__ void __launch_bounds__(BLOCK, 2) cost_kernel(const CostParams p) {
       const int j = __shfl_sync(0xffffffffu, e.slot, leader);
       const bool mine = isc && e.slot == j;
       const unsigned m = __ballot_sync(0xffffffffu, mine);
-      const float g = mine ? -2.f * e.d : 0.f;
-      float v0 = g * e.n.x, v1 = g * e.n.y, v2 = g * e.n.z;
-      float t0 = e.y.y * v2 - e.y.z * v1, t1 = e.y.z * v0 - e.y.x * v2, t2 = e.y.x * v1 - e.y.y * v0;
+      const float g = -2.f * e.d;
+      float v0 = mine ? g * e.n.x : 0.f, v1 = mine ? g * e.n.y : 0.f, v2 = mine ? g * e.n.z : 0.f;
+      float t0 = mine ? e.y.y * v2 - e.y.z * v1 : 0.f, t1 = mine ? e.y.z * v0 - e.y.x * v2 : 0.f, t2 = mine ? e.y.x * v1 - e.y.y * v0 : 0.f;
       v0 = warp_sum(v0); v1 = warp_sum(v1); v2 = warp_sum(v2);
       t0 = warp_sum(t0); t1 = warp_sum(t1); t2 = warp_sum(t2);
       if (lane == 0) {
@@ -401,7 +402,7 @@ struct RayParams {
 __device__ __forceinline__ double field_at(const HotModel& H, const GeoView& G, const double* tab, const float* tabf, double ox, double oy, double oz,
                                             double rx, double ry, double rz, double dist, float* lb, int use_grid) {
   PointEval e;
-  eval_point(H, G, tab, tabf, (float)fma(dist, rx, ox), (float)fma(dist, ry, oy), (float)fma(dist, rz, oz), lb, BLOCK, use_grid != 0, e);
+  eval_point(H, G, tab, tabf, fma(dist, rx, ox), fma(dist, ry, oy), fma(dist, rz, oz), lb, BLOCK, use_grid != 0, e);
   return e.is_skin ? e.sk.s : (double)e.d;
 }
 

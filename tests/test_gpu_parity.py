@@ -198,24 +198,39 @@ def test_k3_real_kinect_cloud():
 
 # ------------------------------------------------------------------ depth rendering (row A9)
 def _raycast_case(m, x, sensor, cam):
+    """GPU ray marcher vs the oracle's.  doRaycast (src/depthsensors.jl:56-81) is a secant iteration
+    that either converges onto the surface (|field| <= 1e-5) or, for rays that pass within ~1 cm of
+    a silhouette, wanders for 60 iterations and is accepted iff its last sample has |field| <= 1e-2.
+    The first kind is well defined and must match; the second kind is chaotic (a 1e-7 difference in
+    one field value changes where it ends), so hit/miss flips are accepted only there."""
     st = flash.ManipulatorState(m)
     flash.gradientdescent.unflatten_(st, x)
     skin = flash.skin(st)
     depths = flash.depthsensors.raycast_depths(skin, sensor, cam)
     hits = flash.depthsensors.raycast_points(skin, sensor, cam)
-    do, ho = ol.Oracle(m).raycast(x, sensor.rays.reshape(-1, 3), cam, mode=ol.GJK)
+    o = ol.Oracle(m)
+    rays = sensor.rays.reshape(-1, 3)
+    do, ho = o.raycast(x, rays, cam, mode=ol.GJK)
     d = depths.reshape(-1)
-    both = np.isfinite(d) & np.isfinite(do)
-    flips = (np.isfinite(d) != np.isfinite(do)).sum()
-    assert flips <= max(2, int(0.01 * np.isfinite(do).sum())), flips      # silhouette rays may flip hit/miss
-    # both marches stop anywhere inside |field| <= 1e-5 (src/depthsensors.jl:57,64): depths agree to that band / slope
-    assert np.abs(d[both] - do[both]).max() < 2e-4
-    assert np.median(np.abs(d[both] - do[both])) < 2e-5
-    assert len(hits) == np.isfinite(d).sum()
+    hit_g, hit_o = np.isfinite(d), np.isfinite(do)
+    assert len(hits) == hit_g.sum()
     # hits are in ray order and lie on the rays
-    idx = np.nonzero(np.isfinite(d))[0]
-    w = (cam[:, :3] @ (sensor.rays.reshape(-1, 3)[idx] * d[idx, None]).T).T + cam[:, 3]
+    idx = np.nonzero(hit_g)[0]
+    w = (cam[:, :3] @ (rays[idx] * d[idx, None]).T).T + cam[:, 3]
     assert np.allclose(w, hits, atol=1e-9)
+    f_g = np.full(len(d), np.inf); f_g[hit_g] = np.abs(o.skin(x, hits, mode=ol.GJK))
+    f_o = np.full(len(d), np.inf); f_o[hit_o] = np.abs(o.skin(x, ho, mode=ol.GJK))
+    assert f_g[hit_g].max() < 1.1e-2                      # every hit passes the 1000*EPS acceptance test
+    conv_o, conv_g = f_o <= 1.5e-5, f_g <= 3e-5           # converged marches
+    assert hit_g[conv_o].all() and hit_o[conv_g].all()     # no flips on well-defined rays
+    both = conv_o & conv_g
+    diff = np.abs(d[both] - do[both])
+    # converged marches stop anywhere inside the 1e-5 band: depths agree to band/slope; a ray with two
+    # crossings a few cm apart can settle on the other one (<= 1%)
+    assert (diff > 2e-4).sum() <= max(1, int(0.01 * both.sum())), (diff > 2e-4).sum()
+    assert np.median(diff) < 2e-5
+    flips = (hit_g != hit_o).sum()
+    assert flips <= 0.05 * hit_o.sum()
     return both.sum()
 
 
