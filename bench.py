@@ -52,13 +52,21 @@ def scene_states(flash, m, n_configs, seed=5):
     return X
 
 
-def scene_points(n, seed, out=None):
-    """fp32-representable points uniform in the scene AABB, generated in chunks."""
-    rng = np.random.default_rng(seed)
+CHUNK = 1 << 20
+
+
+def scene_points(lo, hi, seed=1000, out=None):
+    """Points [lo, hi) of the global seeded cloud: fp32-representable, uniform in the scene AABB.  Chunk k
+    (2^20 points) is drawn from its own generator (seed, k), so every rank count sees the same cloud."""
+    n = hi - lo
     pts = np.empty((n, 3), np.float64) if out is None else out
-    for i in range(0, n, 1 << 20):
-        j = min(n, i + (1 << 20))
-        pts[i:j] = (SCENE_LO + (SCENE_HI - SCENE_LO) * rng.random((j - i, 3), dtype=np.float32)).astype(np.float32)
+    k0, k1 = lo // CHUNK, (hi + CHUNK - 1) // CHUNK
+    for k in range(k0, max(k1, k0 + (1 if n else 0))):
+        rng = np.random.default_rng([seed, k])
+        chunk = (SCENE_LO + (SCENE_HI - SCENE_LO) * rng.random((CHUNK, 3), dtype=np.float32)).astype(np.float32)
+        a, b = max(lo, k * CHUNK), min(hi, (k + 1) * CHUNK)
+        if b > a:
+            pts[a - lo:b - lo] = chunk[a - k * CHUNK:b - k * CHUNK]
     return pts
 
 
@@ -122,7 +130,7 @@ def cpu_leg(n_points, n_configs, steps, warmup, threads=None, method="dual", see
     m = scene_model(flash)
     o = ol.Oracle(m, threads=threads)
     X = scene_states(flash, m, max(n_configs, 2))[:n_configs]
-    pts = scene_points(n_points, seed)
+    pts = scene_points(0, n_points, seed)
     for _ in range(warmup):
         o.cost_grad(X[0], pts[: max(1000, n_points // 20)], mode=ol.GJK, method=method)
     t0 = time.perf_counter()
@@ -171,6 +179,8 @@ def run_ours(args, rank, local_rank, world):
     m.set_options(device=local_rank, sdf_mode=1 if args.mode == "grid" else 0, grid_spacing=args.grid_spacing)
     ctx = m.ctx()
     nx = flash.num_states(m)
+    acc_len = 1 + 6 * sum(isinstance(s_, flash.ConvexGeometry) for s_ in m.surfaces) + sum(
+        4 * (len(s_.surface_points) + len(s_.skeleton_points)) + 4 for s_ in m.surfaces if not isinstance(s_, flash.ConvexGeometry))
     Cn = args.configs
     X = np.ascontiguousarray(scene_states(flash, m, Cn))
 
@@ -180,7 +190,7 @@ def run_ours(args, rank, local_rank, world):
     n_local = hi - lo
     pin = torch.empty((n_local, 3), dtype=torch.float64, pin_memory=True)
     pts = pin.numpy()
-    scene_points(n_local, 1000 + rank, out=pts)
+    scene_points(lo, hi, out=pts)
 
     if world > 1:
         idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -269,7 +279,7 @@ def run_ours(args, rank, local_rank, world):
             "dtype": "f32 distances / f64 RBF + accumulation", "data": "synthetic",
             "config": {"workload": "K5: IRB140(floating)+squishable+table (63 states, 9 surfaces), %d points x %d configs, points sharded over %d GPU(s)" % (N, Cn, world),
                        "points": N, "configs": Cn, "sdf_mode": args.mode, "l2": "L2 flushed (512 MiB memset) between timed steps; inputs %s L2" % ("exceed" if 16 * n_rank > l2.value else "fit"),
-                       "parallelism": "points sharded x%d, one ncclAllReduce of [C][%d] fp64 per step" % (world, 0)},
+                       "parallelism": "points sharded x%d, one ncclAllReduce of [%d][%d] fp64 per step" % (world, Cn, acc_len)},
             "device_ms_per_step": 1e3 * Tkt / args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                          "traffic": None, "peak_source": peak_src, "kernel": "cost_kernel<GRAD>", "kernel_ms": 1e3 * kernel_s,
@@ -282,6 +292,9 @@ def run_ours(args, rank, local_rank, world):
             "gpu_launches": int(launches),
             "checksum_cost_sum": checksum,
         }
+        if world == 1 and args.extras:
+            line["grid_mode"] = grid_leg(args, flash, L, X, pts, n_local, cost.copy(), flush)
+            line["tracking"] = tracking_leg(flash, L)
         if args.cpu_baseline and world == 1:
             base = cpu_leg(args.ref_points, args.ref_configs, 1, 1)
             fast = cpu_leg(args.ref_points, args.ref_configs, 1, 0, method="adjoint")
@@ -294,6 +307,80 @@ def run_ours(args, rank, local_rank, world):
         dist.destroy_process_group()
 
 
+def grid_leg(args, flash, L, X, pts, n_local, cost_exact, flush):
+    """Same workload with FLASH_SDF_GRID (hull distances from baked body-frame grids, manual fp32
+    trilinear): reported beside the exact-mode headline together with its deviation from it."""
+    import torch
+    from flash._desc import Timing, c_double_p
+    mg = scene_model(flash)
+    mg.set_options(sdf_mode=1, grid_spacing=args.grid_spacing)
+    ctx = mg.ctx()
+    Cn, nx = X.shape
+    cost = np.empty(Cn); grad = np.empty((Cn, nx))
+    pX, pc, pg = X.ctypes.data_as(c_double_p), cost.ctypes.data_as(c_double_p), grad.ctypes.data_as(c_double_p)
+    mg.check(L.flash_points_set(ctx, pts.ctypes.data_as(c_double_p), n_local))
+    mg.check(L.flash_profiling(ctx, 1))
+    for _ in range(3):
+        mg.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
+    ts, km = [], []
+    tm = Timing()
+    for _ in range(args.steps):
+        flush.zero_(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        mg.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
+        ts.append(time.perf_counter() - t0)
+        L.flash_last_timing(ctx, C.byref(tm)); km.append(tm.ms_main)
+    errs = [mg.grid_report(s)[2] for s in range(len(mg.surfaces)) if isinstance(mg.surfaces[s], flash.ConvexGeometry)]
+    dims = [mg.grid_report(s)[0] for s in range(len(mg.surfaces)) if isinstance(mg.surfaces[s], flash.ConvexGeometry)]
+    nodes = int(sum(d[0] * d[1] * d[2] for d in dims))
+    out = {"value": float(n_local) * Cn * args.steps / sum(ts), "unit": UNIT, "ms_per_step": 1e3 * sum(ts) / args.steps, "kernel_ms": float(np.mean(km)),
+           "grid_spacing_m": args.grid_spacing, "grid_nodes": nodes, "grid_bytes": 4 * nodes,
+           "max_abs_err_vs_exact_sdf_m": float(max(errs)), "cost_rel_dev_vs_exact_mode": float(np.abs(cost - cost_exact).max() / np.abs(cost_exact).max()),
+           "note": "approximate mode (trilinear SDF grids for the convex bodies; RBF skin stays analytic fp64); parity is defined on the same grid, see DESIGN.md"}
+    mg.invalidate()
+    return out
+
+
+def tracking_leg(flash, L):
+    """K3 (BASELINE.json configs[2]): squishable tracking, whole NaiveSolver loop on the device
+    (rate 0.01, max_step 0.1, 50 iterations, divisors [1x7, 1e-3x36]: examples/squishable.ipynb cell 9)."""
+    from flash._desc import SolverParams, c_double_p
+    out = {}
+    m = flash.models.squishable()
+    rng = np.random.default_rng(3)
+    true = flash.ManipulatorState(m)
+    true.mechanism_state.q[4:7] = [0.05, -0.03, 0.04]
+    true.deformation_data[:] = 0.03 * (rng.random(36) - 0.5)
+    sensor = flash.depthsensors.Kinect(480, 640)
+    cam = flash.depthsensors.affine((0, 0, 1.2), (1, 0, 0), np.pi)
+    t0 = time.perf_counter()
+    pts = flash.depthsensors.raycast(true, sensor, cam)
+    t_ray = time.perf_counter() - t0
+    clouds = {"k3_synthetic_640x480_raycast": pts}
+    real = os.path.join(ROOT, "tests", "golden", "squishable_unsquished_xyz.npy")
+    if os.path.exists(real):
+        clouds["k3_real_kinect_cloud"] = np.load(real).astype(np.float64)
+    div = np.r_[np.ones(7), 1e-3 * np.ones(36)]
+    sp = SolverParams(0.01, 0.1, 50, 0.0, 10.0)
+    for name, cloud in clouds.items():
+        f = flash.gradientdescent.CostFunctor(m, cloud)
+        x0 = flash.gradientdescent.flatten(flash.ManipulatorState(m))
+        x0[4:7] = cloud.mean(0) if name.startswith("k3_real") else 0.0
+        c0 = f(x0)
+        times = []
+        for _ in range(4):
+            X = x0.reshape(1, -1).copy(); cost = np.zeros(1)
+            t0 = time.perf_counter()
+            m.check(L.flash_estimate_state(m.ctx(), X.ctypes.data_as(c_double_p), 1, C.byref(sp), div.ctypes.data_as(c_double_p), cost.ctypes.data_as(c_double_p), None))
+            times.append(time.perf_counter() - t0)
+        t = min(times[1:])
+        out[name] = {"points": int(len(cloud)), "iterations": 50, "ms_per_frame": 1e3 * t, "frames_per_sec": 1.0 / t,
+                     "evals_per_sec": len(cloud) * 51 / t, "cost_start": float(c0), "cost_end": float(cost[0])}
+    out["raycast_640x480"] = {"rays": 480 * 640, "hits": int(len(pts)), "ms": 1e3 * t_ray, "note": "first call, includes allocation and H2D/D2H of rays, depths and hits"}
+    out["reference_published"] = "8.083 s per estimate_state on the real cloud (examples/squishable.ipynb:328; Julia 0.5, 1 thread, with drawing callback)"
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -304,9 +391,10 @@ def main():
     ap.add_argument("--points", type=int, default=10_000_000)
     ap.add_argument("--configs", type=int, default=64)
     ap.add_argument("--grid-spacing", type=float, default=0.004)
-    ap.add_argument("--ref-points", type=int, default=100_000)
-    ap.add_argument("--ref-configs", type=int, default=2)
+    ap.add_argument("--ref-points", type=int, default=1_000_000)
+    ap.add_argument("--ref-configs", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
+    ap.add_argument("--no-extras", dest="extras", action="store_false", help="skip the grid-mode and K3 tracking legs (N=1 only)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

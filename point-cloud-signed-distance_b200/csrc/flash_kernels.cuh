@@ -133,8 +133,11 @@ __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayou
 
 // GRAD: accumulate gradient terms; ARGMIN: write the argmin surface per point; DIST: write the
 // min distance per point (skin_eval entry) and skip all accumulation.
+#ifndef FLASH_MINB
+#define FLASH_MINB 3
+#endif
 template <bool GRAD, bool ARGMIN, bool DIST>
-__global__ void __launch_bounds__(BLOCK, 2) cost_kernel(const CostParams p) {
+__global__ void __launch_bounds__(BLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int c = blockIdx.x;

@@ -8,7 +8,7 @@ import os
 from ._desc import ModelDesc, Options, SolverParams, Timing, c_double_p, c_int32_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libflashsdf.so")
+LIB_PATH = os.environ.get("FLASHSDF_LIB") or os.path.join(os.path.dirname(_HERE), "lib", "libflashsdf.so")
 
 # every symbol include/flashsdf.h declares
 SYMBOLS = [
