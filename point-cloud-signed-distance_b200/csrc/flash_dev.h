@@ -55,10 +55,10 @@ struct BodyC {
 // per convex surface; the geometry frame is the surface frame re-centred on the hull centroid
 struct ConvexC {
   int surface, body, nverts, nplanes;
-  int off_planes, off_tris, off_verts, pad;  // indices into the geometry blob (units: F4 / u32 / F4)
+  int off_planes, off_tris, off_verts, off_vz;  // indices into the geometry blob (units: F4 / u32 / F4 / F4)
   int nplanes_pad, nverts_pad, pad3[2];      // counts rounded up to a multiple of 8 (padding is inert)
   float lo[3], hi[3];                        // AABB of the vertices, geometry frame
-  float depth_bound, pad2;                   // >= max penetration depth
+  float depth_bound, r_in;                   // >= max penetration depth; <= inradius about the geometry origin
   double frame[12];                          // geometry frame -> body frame
   // grid mode (body-frame SDF grid): origin, spacing, dims, offset into the grid pool (floats)
   float g_org[3]; float g_inv_h; int g_dim[3]; int g_on; long long g_off;
@@ -338,26 +338,84 @@ FLASH_HD void simplex_from(Simplex& S, F3 p0, int j0, float u0, F3 p1, int j1, f
   if (S.ns == 0) simplex_push(S, p2, j2);
 }
 
+// ---- geometry blob layout (per hull), chosen so that the scans run on packed fp32 FMAs (FFMA2, sm_100):
+//   planes, pair k = planes 2k, 2k+1:  F4 {nx0, nx1, ny0, ny1}, F4 {nz0, nz1, -o0, -o1}
+//   vertices, pair k:                  F4 {x0, x1, y0, y1} (VA) and float2 {z0, z1} (VZ, a flat float array)
+// counts are padded to a multiple of 8; padding planes can never be the maximum, padding vertices are
+// copies of vertex 0 (never a strictly better support).
+struct HullView { const F4* planes; const uint32_t* ptri; const F4* va; const float* vz; int np, nv; };
+FLASH_HD F3 plane_normal(const F4* P, int f) { const float* a = reinterpret_cast<const float*>(P + (f & ~1)); const int h = f & 1; return f3(a[h], a[2 + h], a[4 + h]); }
+FLASH_HD F3 vert_at(const HullView& V, int j) { const float* a = reinterpret_cast<const float*>(V.va + (j >> 1)); const int h = j & 1; return f3(a[h], a[2 + h], V.vz[j]); }
+
+// eight plane distances n.y - o / eight support values q.v; the device versions issue one FFMA2 per
+// two lanes of work, the host versions are the same fused multiply-adds one at a time (bit-identical).
+#ifdef __CUDA_ARCH__
+__device__ __forceinline__ unsigned long long pk2(float lo, float hi) { unsigned long long r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk2(unsigned long long v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r;
+}
+__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) {
+  unsigned long long r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r;
+}
+#endif
+FLASH_HD void planes8(const F4* __restrict__ P, F3 y, float sv[8]) {
+#ifdef __CUDA_ARCH__
+  const unsigned long long yx = pk2(y.x, y.x), yy = pk2(y.y, y.y), yz = pk2(y.z, y.z);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const F4 a = P[2 * k], b = P[2 * k + 1];
+    unsigned long long r = fma2(pk2(b.x, b.y), yz, pk2(b.z, b.w));
+    r = fma2(pk2(a.z, a.w), yy, r);
+    r = fma2(pk2(a.x, a.y), yx, r);
+    upk2(r, sv[2 * k], sv[2 * k + 1]);
+  }
+#else
+  for (int k = 0; k < 4; ++k) {
+    const F4 a = P[2 * k], b = P[2 * k + 1];
+    sv[2 * k] = fmaf(a.x, y.x, fmaf(a.z, y.y, fmaf(b.x, y.z, b.z)));
+    sv[2 * k + 1] = fmaf(a.y, y.x, fmaf(a.w, y.y, fmaf(b.y, y.z, b.w)));
+  }
+#endif
+}
+FLASH_HD void verts8(const F4* __restrict__ VA, const float* __restrict__ VZ, F3 q, float sv[8]) {
+#ifdef __CUDA_ARCH__
+  const unsigned long long qx = pk2(q.x, q.x), qy = pk2(q.y, q.y), qz = pk2(q.z, q.z);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const F4 a = VA[k];
+    const float2 z = *reinterpret_cast<const float2*>(VZ + 2 * k);
+    unsigned long long r = mul2(pk2(z.x, z.y), qz);
+    r = fma2(pk2(a.z, a.w), qy, r);
+    r = fma2(pk2(a.x, a.y), qx, r);
+    upk2(r, sv[2 * k], sv[2 * k + 1]);
+  }
+#else
+  for (int k = 0; k < 4; ++k) {
+    const F4 a = VA[k];
+    sv[2 * k] = fmaf(q.x, a.x, fmaf(q.y, a.z, q.z * VZ[2 * k]));
+    sv[2 * k + 1] = fmaf(q.x, a.y, fmaf(q.y, a.w, q.z * VZ[2 * k + 1]));
+  }
+#endif
+}
+
 // Signed distance from y (geometry frame) to the convex hull given by its supporting planes and
 // vertices.  Inside (all plane distances <= 0): the largest plane distance, normal = that plane's.
 // Outside: exact Euclidean distance by GJK on the vertex set, started from a triangle of the
 // most-violated face (EnhancedGJK `gjk!` is the reference algorithm, src/Flash.jl:238-243; its
 // inside value is iteration-path dependent and replaced by the exact depth -- DESIGN.md).
 // nrm receives grad_y(distance).
-FLASH_HD float hull_sd(const F4* __restrict__ planes, const uint32_t* __restrict__ ptri, const F4* __restrict__ verts,
-                       int np, int nv, F3 y, float cutoff, F3& nrm) {
-  // Plane scan in groups of 8 (arrays are padded to a multiple of 8 by the host): three FFMAs and
-  // one FMNMX per plane; the index is recovered only in the rare group that raises the maximum.
-  // D is a lower bound of the distance, so the scan stops once D exceeds `cutoff` (the best value
-  // another surface already achieved): this body cannot be the minimum.
+FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
+  const F4* __restrict__ planes = V.planes;
+  const int np = V.np, nv = V.nv;
+  // Plane scan in groups of 8: 12 FFMA2 and a 3-input max tree per group; the index is recovered only
+  // in the rare group that raises the maximum.  D is a lower bound of the distance, so the scan stops
+  // once D exceeds `cutoff` (the best value another surface already achieved): this body cannot be
+  // the minimum.
   float D = -3.0e38f; int fs = 0;
   for (int f = 0; f < np; f += 8) {
     float sv[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const F4 p = planes[f + k];
-      sv[k] = fmaf(p.x, y.x, fmaf(p.y, y.y, fmaf(p.z, y.z, -p.w)));
-    }
+    planes8(planes + f, y, sv);
     const float m = fmaxf(fmaxf(fmaxf(sv[0], sv[1]), fmaxf(sv[2], sv[3])), fmaxf(fmaxf(sv[4], sv[5]), fmaxf(sv[6], sv[7])));
     if (m > D) {
       D = m;
@@ -365,17 +423,17 @@ FLASH_HD float hull_sd(const F4* __restrict__ planes, const uint32_t* __restrict
 #pragma unroll
       for (int t = 6; t >= 0; --t) k = (sv[t] == m) ? t : k;
       fs = f + k;
-      if (D > cutoff) { nrm = xyz(planes[fs]); return D; }
+      if (D > cutoff) { nrm = plane_normal(planes, fs); return D; }
     }
   }
   FLASH_COUNT(narrow, 1); FLASH_COUNT(plane_tests, np);
-  if (D <= 0.f) { FLASH_COUNT(inside, 1); nrm = xyz(planes[fs]); return D; }
+  if (D <= 0.f) { FLASH_COUNT(inside, 1); nrm = plane_normal(planes, fs); return D; }
   Simplex S;
   F3 q;
   {
-    uint32_t t = ptri[fs];
+    uint32_t t = V.ptri[fs];
     int j0 = t & 255, j1 = (t >> 8) & 255, j2 = (t >> 16) & 255;
-    F3 p0 = xyz(verts[j0]) - y, p1 = xyz(verts[j1]) - y, p2 = xyz(verts[j2]) - y;
+    F3 p0 = vert_at(V, j0) - y, p1 = vert_at(V, j1) - y, p2 = vert_at(V, j2) - y;
     float u0, u1, u2;
     q = tri_closest0(p0, p1, p2, u0, u1, u2);
     simplex_from(S, p0, j0, u0, p1, j1, u1, p2, j2, u2);
@@ -392,11 +450,7 @@ FLASH_HD float hull_sd(const F4* __restrict__ planes, const uint32_t* __restrict
     float best = 3.0e38f; int iw = 0;
     for (int v = 0; v < nv; v += 8) {   // groups of 8 (padded with copies of vertex 0)
       float sv[8];
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const F4 p = verts[v + k];
-        sv[k] = fmaf(q.x, p.x, fmaf(q.y, p.y, q.z * p.z));
-      }
+      verts8(V.va + (v >> 1), V.vz + v, q, sv);
       const float m = fminf(fminf(fminf(sv[0], sv[1]), fminf(sv[2], sv[3])), fminf(fminf(sv[4], sv[5]), fminf(sv[6], sv[7])));
       if (m < best) {
         best = m;
@@ -407,7 +461,7 @@ FLASH_HD float hull_sd(const F4* __restrict__ planes, const uint32_t* __restrict
       }
     }
     if (iw == S.ia || (S.ns > 1 && iw == S.ib) || (S.ns > 2 && iw == S.ic)) break;  // already supporting
-    F3 w = xyz(verts[iw]) - y;
+    F3 w = vert_at(V, iw) - y;
     if (dd - dot(q, w) <= 1e-7f * dd) break;                                          // no descent left
     float u0, u1, u2;
     if (S.ns == 1) {
@@ -431,7 +485,7 @@ FLASH_HD float hull_sd(const F4* __restrict__ planes, const uint32_t* __restrict
     }
   }
   float dd = dot(q, q);
-  if (!(dd > 0.f)) { nrm = xyz(planes[fs]); return D; }   // numerically on the surface
+  if (!(dd > 0.f)) { nrm = plane_normal(planes, fs); return D; }   // numerically on the surface
 #ifdef __CUDA_ARCH__
   float inv = rsqrtf(dd);
   inv = inv * (1.5f - 0.5f * dd * inv * inv);   // one Newton step: ~1 ulp
@@ -554,10 +608,16 @@ FLASH_HD void skin_adjoint_term(const double* __restrict__ c, const double* __re
 
 // ------------------------------------------------------------------ min over surfaces (row A6)
 struct GeoView {            // geometry blob (shared memory in the main kernel)
-  const F4* f4;             // planes and vertices
+  const F4* f4;             // plane pairs, vertex pairs
   const uint32_t* u32;      // per-plane start triangle
   const float* grid_pool;   // grid mode
 };
+FLASH_HD HullView hull_view(const GeoView& G, const ConvexC& C) {
+  HullView V;
+  V.planes = G.f4 + C.off_planes; V.ptri = G.u32 + C.off_tris; V.va = G.f4 + C.off_verts;
+  V.vz = reinterpret_cast<const float*>(G.f4 + C.off_vz); V.np = C.nplanes_pad; V.nv = C.nverts_pad;
+  return V;
+}
 
 struct PointEval {
   float d;        // min over surfaces
@@ -570,14 +630,43 @@ struct PointEval {
 
 FLASH_HD bool lex_less(float d, int s, float best, int arg) { return d < best || (d == best && s < arg); }
 
+// Bounds of hull j's signed distance over the ball B(centre, rho) of world points (the 32 Morton-
+// neighbouring points one warp evaluates together).  The distance is 1-Lipschitz, so
+//   d(y) >= aabb_lower_bound(centre) - rho   and   d(y) <= |centre - hull centroid| - inradius + rho.
+// T is the fp32 copy of the world->geometry transform (error < 2e-6 m for |x| < 4 m; both bounds carry
+// that margin), the geometry origin is the hull centroid.
+FLASH_HD void hull_ball_bounds(const ConvexC& C, const float* __restrict__ T, float cx, float cy, float cz, float rho, float& lb, float& ub) {
+  const F3 y = to_geometry_f32(T, cx, cy, cz);
+  const float r = rho * (1.f + 1e-6f);
+  lb = aabb_lower_bound(C.lo, C.hi, C.depth_bound, y) - r - 4e-6f;
+  ub = sqrtf(dot(y, y)) * (1.f + 4e-6f) + 8e-6f - C.r_in + r;
+}
+// Hulls that can be the minimum for SOME point of the ball: lb_j <= min_k ub_k.  A culled hull is
+// strictly farther than hull argmin(ub) at every point of the ball, so neither the min nor the argmin
+// (first minimum) changes.  `first` = the most promising candidate (smallest lower bound).
+FLASH_HD unsigned group_candidates(const HotModel& M, const float* __restrict__ tabf, float cx, float cy, float cz, float rho, int& first) {
+  float lb[MAX_CONVEX];
+  float min_ub = 3.0e38f;
+  for (int j = 0; j < M.n_convex; ++j) {
+    float ub;
+    hull_ball_bounds(M.cvx[j], tabf + 12 * j, cx, cy, cz, rho, lb[j], ub);
+    min_ub = fminf(min_ub, ub);
+  }
+  unsigned mask = 0; float lb0 = 3.0e38f; first = -1;
+  for (int j = 0; j < M.n_convex; ++j)
+    if (lb[j] <= min_ub) { mask |= 1u << j; if (lb[j] < lb0) { lb0 = lb[j]; first = j; } }
+  return mask;
+}
+
 // Evaluates skin(x) = min over all surfaces for one world point under one configuration.
-// `lb` is per-thread scratch of n_convex floats with stride lb_stride.
-// Convex bodies are culled with their AABB lower bound: a body is evaluated exactly only if its
-// bound can still beat the best value so far, which cannot change the min or the argmin.
+// `cand` = bit mask of the convex slots to consider (group_candidates, or all ones), `first` = the
+// slot to evaluate first (-1: chosen here from the per-point bounds).  Within the candidates a body is
+// evaluated exactly only if its per-point AABB lower bound can still beat the best value so far,
+// which cannot change the min or the argmin.
 // The point is passed in fp64: the cost path feeds fp32 points (exact in fp64), the ray marcher its
 // fp64 sample positions.
 FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __restrict__ tab, const float* __restrict__ tabf,
-                         double px, double py, double pz, float* lb, int lb_stride, bool use_grid, PointEval& out) {
+                         double px, double py, double pz, unsigned cand, int first, bool use_grid, PointEval& out) {
   const ConvexC* __restrict__ cvx = M.cvx;
   float best = 3.0e38f; int arg = 0x7fffffff; int slot = -1; int is_skin = 0;
   out.y = f3(0, 0, 0); out.n = f3(0, 0, 0);
@@ -590,27 +679,47 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
     if (lex_less(d, K.surface, best, arg)) { best = d; arg = K.surface; slot = k; is_skin = 1; out.sk = e; }
   }
   const int nc = M.n_convex;
-  FLASH_COUNT(points, 1); FLASH_COUNT(lb_tests, nc);
-  int j0 = -1; float lb0 = 3.0e38f;
-  for (int j = 0; j < nc; ++j) {
-    F3 y = to_geometry_f32(tabf + 12 * j, (float)px, (float)py, (float)pz);
-    float l = aabb_lower_bound(cvx[j].lo, cvx[j].hi, cvx[j].depth_bound, y);
-    lb[j * lb_stride] = l;
-    if (l < lb0) { lb0 = l; j0 = j; }
+  const float fx = (float)px, fy = (float)py, fz = (float)pz;
+  FLASH_COUNT(points, 1);
+  if (first < 0) {   // no group information: the most promising body by the per-point bound
+    float lb0 = 3.0e38f;
+    for (int j = 0; j < nc; ++j) {
+      if (!((cand >> j) & 1u)) continue;
+      FLASH_COUNT(lb_tests, 1);
+      const float l = aabb_lower_bound(cvx[j].lo, cvx[j].hi, cvx[j].depth_bound, to_geometry_f32(tabf + 12 * j, fx, fy, fz));
+      if (l < lb0) { lb0 = l; first = j; }
+    }
   }
-  // the most promising body first, then the rest in surface order
-  for (int jj = -1; jj < nc; ++jj) {
-    int j = jj < 0 ? j0 : jj;
-    if (j < 0 || (jj >= 0 && j == j0)) continue;
-    float l = lb[j * lb_stride];
+  // `first`, then the remaining candidates in surface order
+  const bool single = (cand & (cand - 1u)) == 0u;
+  unsigned rest = first >= 0 ? (cand & ~(1u << first)) : cand;
+  int j = first;
+  while (true) {
+    if (j < 0) {
+      if (!rest) break;
+#ifdef __CUDA_ARCH__
+      j = __ffs(rest) - 1;
+#else
+      j = __builtin_ctz(rest);
+#endif
+      rest &= rest - 1u;
+    }
     const ConvexC& C = cvx[j];
-    if (l > best || (l == best && C.surface > arg)) continue;
-    F3 y = to_geometry(tab + 12 * j, px, py, pz);
-    F3 n; float d;
-    bool done = false;
-    if (use_grid && C.g_on) done = grid_sd(C, G.grid_pool, y, d, n);
-    if (!done) d = hull_sd(G.f4 + C.off_planes, G.u32 + C.off_tris, G.f4 + C.off_verts, C.nplanes_pad, C.nverts_pad, y, best, n);
-    if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
+    bool skip = false;
+    if (!single) {
+      FLASH_COUNT(lb_tests, 1);
+      const float l = aabb_lower_bound(C.lo, C.hi, C.depth_bound, to_geometry_f32(tabf + 12 * j, fx, fy, fz));
+      skip = l > best || (l == best && C.surface > arg);
+    }
+    if (!skip) {
+      F3 y = to_geometry(tab + 12 * j, px, py, pz);
+      F3 n; float d;
+      bool done = false;
+      if (use_grid && C.g_on) done = grid_sd(C, G.grid_pool, y, d, n);
+      if (!done) d = hull_sd(hull_view(G, C), y, best, n);
+      if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
+    }
+    j = -1;
   }
   out.d = best; out.arg = arg; out.slot = slot; out.is_skin = is_skin;
 }

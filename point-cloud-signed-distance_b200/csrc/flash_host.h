@@ -178,25 +178,42 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
       if (!build_hull(pts, H, err)) { err = "surface " + std::to_string(s) + ": " + err; return false; }
       C.nverts = (int)H.verts.size(); C.nplanes = (int)H.planes.size();
       C.off_planes = (int)out.geo_f4.size(); C.off_tris = (int)out.geo_u32.size();
-      for (size_t f = 0; f < H.planes.size(); ++f) {
-        out.geo_f4.push_back(F4{(float)H.planes[f][0], (float)H.planes[f][1], (float)H.planes[f][2], (float)H.planes[f][3]});
-        out.geo_u32.push_back((uint32_t)H.ptri[f][0] | ((uint32_t)H.ptri[f][1] << 8) | ((uint32_t)H.ptri[f][2] << 16));
-      }
-      // pad to a multiple of 8 with planes that can never be the maximum
+      // planes: padded to a multiple of 8 with planes that can never be the maximum, stored as pairs
+      // {nx0,nx1,ny0,ny1}{nz0,nz1,-o0,-o1} for the packed-FMA scan (flash_dev.h "geometry blob layout")
       C.nplanes_pad = (C.nplanes + 7) & ~7;
-      for (int f = C.nplanes; f < C.nplanes_pad; ++f) { out.geo_f4.push_back(F4{0.f, 0.f, 0.f, 1.0e30f}); out.geo_u32.push_back(out.geo_u32.back()); }
-      C.off_verts = (int)out.geo_f4.size();
+      {
+        std::vector<std::array<float, 4>> pl;
+        for (size_t f = 0; f < H.planes.size(); ++f) {
+          pl.push_back({(float)H.planes[f][0], (float)H.planes[f][1], (float)H.planes[f][2], -(float)H.planes[f][3]});
+          out.geo_u32.push_back((uint32_t)H.ptri[f][0] | ((uint32_t)H.ptri[f][1] << 8) | ((uint32_t)H.ptri[f][2] << 16));
+        }
+        for (int f = C.nplanes; f < C.nplanes_pad; ++f) { pl.push_back({0.f, 0.f, 0.f, -1.0e30f}); out.geo_u32.push_back(out.geo_u32.back()); }
+        for (int f = 0; f < C.nplanes_pad; f += 2) {
+          out.geo_f4.push_back(F4{pl[f][0], pl[f + 1][0], pl[f][1], pl[f + 1][1]});
+          out.geo_f4.push_back(F4{pl[f][2], pl[f + 1][2], pl[f][3], pl[f + 1][3]});
+        }
+      }
+      // vertices: padded with copies of vertex 0 (never a strictly better support); pairs {x0,x1,y0,y1}
+      // followed by the flat z array
+      C.nverts_pad = (C.nverts + 7) & ~7;
+      std::vector<std::array<float, 3>> vf;
       for (int k = 0; k < 3; ++k) { C.lo[k] = 3e38f; C.hi[k] = -3e38f; }
       for (auto& v : H.verts) {
-        F4 f = F4{(float)v.x, (float)v.y, (float)v.z, 0.f};
-        out.geo_f4.push_back(f);
+        std::array<float, 3> f = {(float)v.x, (float)v.y, (float)v.z};
+        vf.push_back(f);
         // bounds must contain the fp32 vertices (nextafter outward)
-        C.lo[0] = std::min(C.lo[0], std::nextafterf(f.x, -3e38f)); C.hi[0] = std::max(C.hi[0], std::nextafterf(f.x, 3e38f));
-        C.lo[1] = std::min(C.lo[1], std::nextafterf(f.y, -3e38f)); C.hi[1] = std::max(C.hi[1], std::nextafterf(f.y, 3e38f));
-        C.lo[2] = std::min(C.lo[2], std::nextafterf(f.z, -3e38f)); C.hi[2] = std::max(C.hi[2], std::nextafterf(f.z, 3e38f));
+        for (int k = 0; k < 3; ++k) { C.lo[k] = std::min(C.lo[k], std::nextafterf(f[k], -3e38f)); C.hi[k] = std::max(C.hi[k], std::nextafterf(f[k], 3e38f)); }
       }
-      C.nverts_pad = (C.nverts + 7) & ~7;   // pad with copies of vertex 0 (never a strictly better support)
-      for (int v = C.nverts; v < C.nverts_pad; ++v) out.geo_f4.push_back(F4{(float)H.verts[0].x, (float)H.verts[0].y, (float)H.verts[0].z, 0.f});
+      for (int v = C.nverts; v < C.nverts_pad; ++v) vf.push_back(vf[0]);
+      C.off_verts = (int)out.geo_f4.size();
+      for (int v = 0; v < C.nverts_pad; v += 2) out.geo_f4.push_back(F4{vf[v][0], vf[v + 1][0], vf[v][1], vf[v + 1][1]});
+      C.off_vz = (int)out.geo_f4.size();
+      for (int v = 0; v < C.nverts_pad; v += 4) out.geo_f4.push_back(F4{vf[v][2], vf[v + 1][2], vf[v + 2][2], vf[v + 3][2]});
+      {
+        double rin = 1e300;   // the geometry origin is the vertex centroid: strictly inside
+        for (auto& p : H.planes) rin = std::min(rin, p[3]);
+        C.r_in = (float)std::max(0.0, rin * (1.0 - 1e-6) - 1e-7);
+      }
       double db = 1e300;
       for (auto& p : H.planes) {
         double w = 0;

@@ -39,6 +39,7 @@ struct CostParams {
   double* acc;         // [C][acc_len]
   int32_t* argmin;     // [C][n_pts] or null
   const int* perm;     // sorted position -> caller index (null: identity)
+  const float4* grp;   // per 32 consecutive points: bounding ball {cx, cy, cz, rho} (null: no group culling)
   double* dist;        // [n_pts] (DIST mode, C == 1)
   int pts_per_block;
   int use_grid;
@@ -48,7 +49,7 @@ __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t
 
 // dynamic shared memory layout of cost_kernel / raycast_kernel
 struct SmemLayout {
-  size_t off_hot, off_f4, off_u32, off_tab, off_tabf, off_acc, off_lb, off_queue, off_qslot, total;
+  size_t off_hot, off_f4, off_u32, off_tab, off_tabf, off_acc, off_queue, off_qslot, total;
 };
 __host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, int tab_len, int acc_len, int n_convex, bool grad_skins) {
   SmemLayout L;
@@ -59,12 +60,15 @@ __host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, i
   L.off_tab = o; o = align16(o + sizeof(double) * (size_t)tab_len);
   L.off_tabf = o; o = align16(o + sizeof(float) * 12 * (size_t)(n_convex > 0 ? n_convex : 1));
   L.off_acc = o; o = align16(o + sizeof(double) * (size_t)acc_len * WARPS);
-  L.off_lb = o; o = align16(o + sizeof(float) * (size_t)(n_convex > 0 ? n_convex : 1) * BLOCK);
   L.off_queue = o; o = align16(o + (grad_skins ? sizeof(double) * QENT * 32 * WARPS : 0));
   L.off_qslot = o; o = align16(o + (grad_skins ? sizeof(int) * 32 * WARPS : 0));
   L.total = o;
   return L;
 }
+
+// monotone float <-> int maps, so that REDUX.MIN (integer) reduces floats
+__device__ __forceinline__ int ordered_int(float f) { const int i = __float_as_int(f); return i ^ ((i >> 31) & 0x7fffffff); }
+__device__ __forceinline__ float from_ordered_int(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -156,10 +160,10 @@ __global__ void __launch_bounds__(BLOCK, FLASH_MINB) cost_kernel(const CostParam
   G.grid_pool = p.grid_pool;
   const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
   const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
-  float* lb = reinterpret_cast<float*>(smem + L.off_lb) + tid;
   double* queue = reinterpret_cast<double*>(smem + L.off_queue) + (size_t)warp * 32 * QENT;
   int* qslot = reinterpret_cast<int*>(smem + L.off_qslot) + warp * 32;
 
+  const unsigned all_convex = n_convex >= 32 ? 0xffffffffu : ((1u << n_convex) - 1u);
   const long long tile0 = (long long)blockIdx.y * p.pts_per_block;
   long long tile1 = tile0 + p.pts_per_block;
   if (tile1 > p.n_pts) tile1 = p.n_pts;
@@ -172,10 +176,22 @@ __global__ void __launch_bounds__(BLOCK, FLASH_MINB) cost_kernel(const CostParam
     e.d = 0.f; e.arg = -1; e.slot = -1; e.is_skin = 0;
     e.y = f3(0.f, 0.f, 0.f); e.n = f3(0.f, 0.f, 0.f);   // lanes past the tile end must contribute exact zeros
     float px = 0.f, py = 0.f, pz = 0.f;
+    // hulls that can be the minimum for some point of this warp's 32 Morton neighbours: lane j bounds hull j
+    unsigned cand = all_convex; int first = -1;
+    if (!DIST && p.grp != nullptr && n_convex > 1) {
+      const float4 gb = __ldg(p.grp + ((base + warp * 32) >> 5));
+      float lbv = 3.0e38f, ubv = 3.0e38f;
+      if (lane < n_convex) hull_ball_bounds(H.cvx[lane], tabf + 12 * lane, gb.x, gb.y, gb.z, gb.w, lbv, ubv);
+      const float min_ub = from_ordered_int(__reduce_min_sync(0xffffffffu, ordered_int(ubv)));
+      const bool is_cand = lane < n_convex && lbv <= min_ub;
+      cand = __ballot_sync(0xffffffffu, is_cand);
+      first = __reduce_min_sync(0xffffffffu, is_cand ? ((ordered_int(lbv) & ~31) | lane) : 0x7fffffff) & 31;
+      if (cand == 0u) { cand = all_convex; first = -1; }   // only with non-finite bounds
+    }
     if (valid) {
       const float4 P = __ldg(p.pts + i);
       px = P.x; py = P.y; pz = P.z;
-      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, lb, BLOCK, p.use_grid != 0, e);
+      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, cand, first, p.use_grid != 0, e);
     }
     if (DIST) {
       if (valid) {
@@ -377,6 +393,27 @@ __global__ void points_scatter_kernel(const T* __restrict__ src, long long n, co
   dst[pos] = make_float4(p.x, p.y, p.z, 0.f);
   perm[pos] = (int)i;
 }
+// bounding ball of every 32 consecutive (Morton-neighbouring) points: one warp per group
+__global__ void __launch_bounds__(256) points_groups_kernel(const float4* __restrict__ pts, long long n, float4* __restrict__ grp) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long g = i >> 5;
+  if (g * 32 >= n) return;
+  float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+  if (i < n) { const float4 p = __ldg(pts + i); lo[0] = hi[0] = p.x; lo[1] = hi[1] = p.y; lo[2] = hi[2] = p.z; }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o)); hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o)); }
+  }
+  if ((threadIdx.x & 31) == 0) {
+    const float cx = 0.5f * (lo[0] + hi[0]), cy = 0.5f * (lo[1] + hi[1]), cz = 0.5f * (lo[2] + hi[2]);
+    const float ex = fmaxf(hi[0] - cx, cx - lo[0]), ey = fmaxf(hi[1] - cy, cy - lo[1]), ez = fmaxf(hi[2] - cz, cz - lo[2]);
+    float rho = sqrtf(ex * ex + ey * ey + ez * ez) * (1.f + 1e-6f) + 1e-30f;
+    float4 o = make_float4(cx, cy, cz, rho);
+    if (!(rho < 3e37f) || !(fabsf(cx) < 3e37f) || !(fabsf(cy) < 3e37f) || !(fabsf(cz) < 3e37f)) o = make_float4(0.f, 0.f, 0.f, 1e30f);  // NaN / inf: no culling
+    grp[g] = o;
+  }
+}
 // unsorted conversion (clouds too small to be worth sorting, or > 2^31 points)
 template <class T>
 __global__ void convert_points_kernel(const T* __restrict__ src, float4* __restrict__ dst, long long n) {
@@ -403,9 +440,9 @@ struct RayParams {
 };
 
 __device__ __forceinline__ double field_at(const HotModel& H, const GeoView& G, const double* tab, const float* tabf, double ox, double oy, double oz,
-                                            double rx, double ry, double rz, double dist, float* lb, int use_grid) {
+                                            double rx, double ry, double rz, double dist, unsigned cand, int use_grid) {
   PointEval e;
-  eval_point(H, G, tab, tabf, fma(dist, rx, ox), fma(dist, ry, oy), fma(dist, rz, oz), lb, BLOCK, use_grid != 0, e);
+  eval_point(H, G, tab, tabf, fma(dist, rx, ox), fma(dist, ry, oy), fma(dist, rz, oz), cand, -1, use_grid != 0, e);
   return e.is_skin ? e.sk.s : (double)e.d;
 }
 
@@ -423,7 +460,7 @@ __global__ void __launch_bounds__(BLOCK, 2) raycast_kernel(const RayParams p) {
   G.grid_pool = p.grid_pool;
   const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
   const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
-  float* lb = reinterpret_cast<float*>(smem + L.off_lb) + tid;
+  const unsigned cand = H.n_convex >= 32 ? 0xffffffffu : ((1u << H.n_convex) - 1u);
   const long long i = (long long)blockIdx.x * BLOCK + tid;
   bool hit = false;
   if (i < p.R) {
@@ -437,14 +474,14 @@ __global__ void __launch_bounds__(BLOCK, 2) raycast_kernel(const RayParams p) {
     const double ox = p.cam[3], oy = p.cam[7], oz = p.cam[11];
     const double EPS = 1e-5, SAFE_RATE = 0.4;
     double dist = 0.0, est = -1.0;
-    double last = field_at(H, G, tab, tabf, ox, oy, oz, rx, ry, rz, dist, lb, p.use_grid);
+    double last = field_at(H, G, tab, tabf, ox, oy, oz, rx, ry, rz, dist, cand, p.use_grid);
     int k = 0;
     while (fabs(last) > EPS && k < 60) {
       double step = -last / est;
       const double sg = step > 0 ? 1.0 : (step < 0 ? -1.0 : 0.0);
       step = sg * fmin(SAFE_RATE, fabs(step));
       dist += step;
-      const double v = field_at(H, G, tab, tabf, ox, oy, oz, rx, ry, rz, dist, lb, p.use_grid);
+      const double v = field_at(H, G, tab, tabf, ox, oy, oz, rx, ry, rz, dist, cand, p.use_grid);
       est = (v - last) / step;
       last = v;
       ++k;
@@ -552,7 +589,8 @@ __global__ void bake_grid_kernel(const HotModel* __restrict__ hot, const F4* __r
   const float h = 1.0f / C.g_inv_h;
   F3 y = f3(C.g_org[0] + ix * h, C.g_org[1] + iy * h, C.g_org[2] + iz * h);
   F3 n3;
-  pool[C.g_off + i] = hull_sd(geo_f4 + C.off_planes, geo_u32 + C.off_tris, geo_f4 + C.off_verts, C.nplanes_pad, C.nverts_pad, y, 3.0e38f, n3);
+  GeoView G; G.f4 = geo_f4; G.u32 = geo_u32; G.grid_pool = nullptr;
+  pool[C.g_off + i] = hull_sd(hull_view(G, C), y, 3.0e38f, n3);
 }
 // max |trilinear - exact| over cell centres (the worst place for trilinear interpolation)
 __global__ void grid_error_kernel(const HotModel* __restrict__ hot, const F4* __restrict__ geo_f4, const uint32_t* __restrict__ geo_u32, int j,
@@ -567,7 +605,8 @@ __global__ void grid_error_kernel(const HotModel* __restrict__ hot, const F4* __
     const float h = 1.0f / C.g_inv_h;
     F3 y = f3(C.g_org[0] + (ix + 0.5f) * h, C.g_org[1] + (iy + 0.5f) * h, C.g_org[2] + (iz + 0.5f) * h);
     F3 n3, n4; float dg;
-    float de = hull_sd(geo_f4 + C.off_planes, geo_u32 + C.off_tris, geo_f4 + C.off_verts, C.nplanes_pad, C.nverts_pad, y, 3.0e38f, n3);
+    GeoView G; G.f4 = geo_f4; G.u32 = geo_u32; G.grid_pool = nullptr;
+    float de = hull_sd(hull_view(G, C), y, 3.0e38f, n3);
     if (grid_sd(C, pool, y, dg, n4)) err = fabsf(dg - de);
   }
   err = fmaxf(err, __shfl_xor_sync(0xffffffffu, err, 16));

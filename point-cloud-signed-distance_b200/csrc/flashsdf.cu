@@ -69,6 +69,7 @@ struct flash_ctx {
   float4* d_pts = nullptr; long long n_pts = 0; long long cap_pts = 0; bool pts_external = false; bool pts_set = false;
   void* d_stage = nullptr; size_t cap_stage = 0;
   int* d_bins = nullptr; int* d_perm = nullptr; size_t cap_perm = 0; bool perm_on = false; bool sort_points = true;
+  float4* d_grp = nullptr; size_t cap_grp = 0; bool grp_on = false; bool group_cull = true;
   // per-batch state
   int cap_C = 0;
   double *d_X = nullptr, *d_tab = nullptr, *d_aux = nullptr, *d_acc = nullptr, *d_cost = nullptr, *d_grad = nullptr, *d_div = nullptr;
@@ -173,6 +174,7 @@ int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin) {
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
   p.geo_f4_n = M.geo_f4; p.geo_u32_n = M.geo_u32;
   p.pts = ctx->d_pts; p.n_pts = ctx->n_pts; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = d_argmin; p.dist = nullptr; p.perm = ctx->perm_on ? ctx->d_perm : nullptr;
+  p.grp = ctx->grp_on && ctx->group_cull ? ctx->d_grp : nullptr;
   p.pts_per_block = choose_tile(ctx, ctx->n_pts, C);
   p.use_grid = ctx->use_grid ? 1 : 0;
   if (ctx->n_pts == 0) return 0;
@@ -293,6 +295,19 @@ int bake_grids(flash_ctx* ctx) {
 
 }  // namespace
 
+// bounding balls of the 32-point groups the main kernel's warps evaluate together
+static int points_groups(flash_ctx* ctx) {
+  ctx->grp_on = false;
+  const long long n = ctx->n_pts;
+  if (n <= 0) return 0;
+  int rc = ensure(ctx, ctx->d_grp, ctx->cap_grp, (size_t)((n + 31) / 32)); if (rc) return rc;
+  points_groups_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_pts, n, ctx->d_grp);
+  CU(cudaGetLastError());
+  ctx->launches++;
+  ctx->grp_on = true;
+  return 0;
+}
+
 static int points_alloc(flash_ctx* ctx, int64_t n) {
   if (ctx->pts_external) { ctx->d_pts = nullptr; ctx->cap_pts = 0; ctx->pts_external = false; }
   if (n > ctx->cap_pts) {
@@ -309,7 +324,7 @@ template <class T>
 static int points_ingest(flash_ctx* ctx, const T* xyz, int64_t n) {
   CU(cudaSetDevice(ctx->device));
   int rc = points_alloc(ctx, n); if (rc) return rc;
-  ctx->perm_on = false;
+  ctx->perm_on = false; ctx->grp_on = false;
   if (n > 0) {
     const size_t bytes = (size_t)n * 3 * sizeof(T);
     if (bytes > ctx->cap_stage) { if (ctx->d_stage) CU(cudaFree(ctx->d_stage)); ctx->d_stage = nullptr; ctx->cap_stage = 0; CU(cudaMalloc(&ctx->d_stage, bytes)); ctx->cap_stage = bytes; }
@@ -337,6 +352,8 @@ static int points_ingest(flash_ctx* ctx, const T* xyz, int64_t n) {
       CU(cudaGetLastError());
       ctx->launches++;
     }
+    ctx->n_pts = n;
+    rc = points_groups(ctx); if (rc) return rc;
     CU(cudaStreamSynchronize(ctx->stream));  // the caller may reuse xyz as soon as we return
   }
   ctx->n_pts = n; ctx->pts_set = true;
@@ -359,6 +376,7 @@ int flash_model_create(const flash_model_desc* desc, const flash_options* opt, f
   if (!build_model(desc, opt, ctx->hm, err)) { delete ctx; return fail(nullptr, FLASH_ERR_INVALID, err); }
   make_hot(ctx->hm.M, ctx->hot);
   if (const char* e = getenv("FLASHSDF_NO_SORT")) ctx->sort_points = !(e[0] == '1');
+  if (const char* e = getenv("FLASHSDF_NO_GROUP_CULL")) ctx->group_cull = !(e[0] == '1');
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0) {
@@ -404,7 +422,7 @@ void flash_destroy(flash_ctx* ctx) {
   if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
   void* frees[] = {ctx->d_model, ctx->d_hot, ctx->d_geo_f4, ctx->d_geo_u32, ctx->d_grid_pool, ctx->pts_external ? nullptr : (void*)ctx->d_pts, ctx->d_stage,
                    ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, ctx->d_cost, ctx->d_grad, ctx->d_div, ctx->d_status, ctx->d_done, ctx->d_iters,
-                   ctx->d_argmin, ctx->d_qd, ctx->d_qi, ctx->d_bins, ctx->d_perm};
+                   ctx->d_argmin, ctx->d_qd, ctx->d_qi, ctx->d_bins, ctx->d_perm, ctx->d_grp};
   for (void* p : frees) if (p) cudaFree(p);
   if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
@@ -437,7 +455,7 @@ int flash_points_set_device(flash_ctx* ctx, const void* device_float4, int64_t n
   if (!ctx->pts_external && ctx->d_pts) CU(cudaFree(ctx->d_pts));
   ctx->d_pts = (float4*)device_float4; ctx->cap_pts = 0; ctx->pts_external = true; ctx->perm_on = false;
   ctx->n_pts = n; ctx->pts_set = true;
-  return FLASH_OK;
+  return points_groups(ctx);
 }
 
 int flash_cost_grad(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad, int32_t* argmin) {
@@ -491,7 +509,7 @@ int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t 
   CostParams p;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
   p.geo_f4_n = M.geo_f4; p.geo_u32_n = M.geo_u32;
-  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist; p.perm = nullptr;
+  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr;
   p.pts_per_block = choose_tile(ctx, n, 1); p.use_grid = ctx->use_grid ? 1 : 0;
   const int tiles = (int)((n + p.pts_per_block - 1) / p.pts_per_block);
   const size_t smem = cost_layout(ctx, false).total;

@@ -12,6 +12,8 @@ using namespace flashdev;
 using namespace flashhost;
 
 struct HC { HostModel hm; HotModel hot; };
+static int g_group_cull = 1;            // replay the warp-level hull culling of cost_kernel
+static long long g_cand_total = 0, g_groups = 0;
 static thread_local std::string g_err;
 
 extern "C" {
@@ -58,12 +60,24 @@ void hc_accumulate(void* p, const double* tab, const float* pts, long long n, in
   HC* h = (HC*)p;
   const HotModel& H = h->hot;
   GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
-  float lb[MAX_CONVEX];
   float tabf[12 * MAX_CONVEX];
   for (int i = 0; i < 12 * H.n_convex; ++i) tabf[i] = (float)tab[i];
+  const unsigned all_convex = H.n_convex >= 32 ? 0xffffffffu : ((1u << H.n_convex) - 1u);
+  unsigned cand = all_convex; int first = -1;
   for (long long i = 0; i < n; ++i) {
+    if (g_group_cull && (i & 31) == 0 && H.n_convex > 1) {
+      // the warp's 32 points: bounding ball as points_groups_kernel computes it, then the candidate hulls
+      float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+      for (long long k = i; k < n && k < i + 32; ++k)
+        for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], pts[3 * k + a]); hi[a] = fmaxf(hi[a], pts[3 * k + a]); }
+      const float cx = 0.5f * (lo[0] + hi[0]), cy = 0.5f * (lo[1] + hi[1]), cz = 0.5f * (lo[2] + hi[2]);
+      const float ex = fmaxf(hi[0] - cx, cx - lo[0]), ey = fmaxf(hi[1] - cy, cy - lo[1]), ez = fmaxf(hi[2] - cz, cz - lo[2]);
+      const float rho = sqrtf(ex * ex + ey * ey + ez * ez) * (1.f + 1e-6f) + 1e-30f;
+      cand = group_candidates(H, tabf, cx, cy, cz, rho, first);
+      g_cand_total += __builtin_popcount(cand); g_groups += 1;
+    }
     PointEval e;
-    eval_point(H, G, tab, tabf, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], lb, 1, use_grid != 0, e);
+    eval_point(H, G, tab, tabf, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], cand, first, use_grid != 0, e);
     double dv = e.is_skin ? e.sk.s : (double)e.d;
     if (dist) dist[i] = dv;
     if (argmin) argmin[i] = e.arg;
@@ -95,6 +109,10 @@ void hc_epilogue(void* p, const double* x, const double* tab, const double* aux,
   epilogue_config(M, x, tab, aux, acc, w_def, scratch.data(), cost, grad);
 }
 
+void hc_set_group_cull(int on) { g_group_cull = on; }
+// out: candidate hulls summed over groups, groups
+void hc_group_stats(long long* out, int reset) { out[0] = g_cand_total; out[1] = g_groups; if (reset) { g_cand_total = 0; g_groups = 0; } }
+
 // instrumentation (only meaningful when built with -DFLASH_COUNTERS)
 void hc_counters(long long* out, int reset) {
 #ifdef FLASH_COUNTERS
@@ -110,10 +128,10 @@ void hc_counters(long long* out, int reset) {
 void hc_hull_sd(void* p, int j, const float* y, long long n, float* d, float* nrm) {
   HC* h = (HC*)p;
   const ConvexC& C = h->hm.M.cvx[j];
-  const F4* f4 = h->hm.geo_f4.data(); const uint32_t* u32 = h->hm.geo_u32.data();
+  GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
   for (long long i = 0; i < n; ++i) {
     F3 nn;
-    d[i] = hull_sd(f4 + C.off_planes, u32 + C.off_tris, f4 + C.off_verts, C.nplanes_pad, C.nverts_pad, f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]), 3.0e38f, nn);
+    d[i] = hull_sd(hull_view(G, C), f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]), 3.0e38f, nn);
     nrm[3 * i] = nn.x; nrm[3 * i + 1] = nn.y; nrm[3 * i + 2] = nn.z;
   }
 }
