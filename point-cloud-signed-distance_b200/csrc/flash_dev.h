@@ -22,8 +22,8 @@
 namespace flashdev {
 
 #if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
-struct Counters { long long points, narrow, inside, gjk_iters, plane_tests, vert_tests, lb_tests; };
-inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0, 0}; return c; }
+struct Counters { long long points, narrow, inside, gjk_iters, plane_tests, vert_tests, lb_tests, skin64; };
+inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0, 0, 0}; return c; }
 #define FLASH_COUNT(field, n) (flashdev::counters().field += (n))
 #else
 #define FLASH_COUNT(field, n) ((void)0)
@@ -72,7 +72,8 @@ struct SkinC {
   int acc_off;     // accumulators: gY[n+4], gC[3n]                  (doubles)
   int aux_off;     // per-config aux: LU[M*M], piv[M]                (doubles)
   int pt_off;      // into ModelC::skin_pt
-  int pad[2];
+  int tabf_off;    // fp32 table (floats): {cx,cy,cz,3w}[n], {a0,ax,ay,az}   (certified pre-filter)
+  int pad;
 };
 
 struct ModelC {
@@ -82,7 +83,7 @@ struct ModelC {
   int acc_len;   // doubles per config:   1 + 6*n_convex + sum(4n+4)
   int aux_len;   // doubles per config:   24*n_bodies + n_bodies + sum(M*M + M)
   int geo_f4, geo_u32;  // blob sizes
-  int pad;
+  int tabf_len;  // floats per config of the fp32 side table: 12*n_convex (padded to 4) + sum(4n+4)
   BodyC body[MAX_BODIES];
   ConvexC cvx[MAX_CONVEX];
   SkinC skin[MAX_SKINS];
@@ -95,7 +96,7 @@ struct ModelC {
 // what the per-point code reads; copied to shared memory by every block of the main kernel
 struct HotModel {
   int n_convex, n_skins, normalize, acc_len;
-  int tab_len, pad[3];
+  int tab_len, tabf_len, pad[2];
   SkinC skin[MAX_SKINS];
   ConvexC cvx[MAX_CONVEX];
 };
@@ -360,7 +361,7 @@ __device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigne
 }
 #endif
 FLASH_HD void planes8(const F4* __restrict__ P, F3 y, float sv[8]) {
-#ifdef __CUDA_ARCH__
+#if defined(__CUDA_ARCH__) && !defined(FLASH_NO_FFMA2)
   const unsigned long long yx = pk2(y.x, y.x), yy = pk2(y.y, y.y), yz = pk2(y.z, y.z);
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -379,7 +380,7 @@ FLASH_HD void planes8(const F4* __restrict__ P, F3 y, float sv[8]) {
 #endif
 }
 FLASH_HD void verts8(const F4* __restrict__ VA, const float* __restrict__ VZ, F3 q, float sv[8]) {
-#ifdef __CUDA_ARCH__
+#if defined(__CUDA_ARCH__) && !defined(FLASH_NO_FFMA2)
   const unsigned long long qx = pk2(q.x, q.x), qy = pk2(q.y, q.y), qz = pk2(q.z, q.z);
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -423,7 +424,7 @@ FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
 #pragma unroll
       for (int t = 6; t >= 0; --t) k = (sv[t] == m) ? t : k;
       fs = f + k;
-      if (D > cutoff) { nrm = plane_normal(planes, fs); return D; }
+      if (D > cutoff) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }   // cannot be the minimum: never a candidate value
     }
   }
   FLASH_COUNT(narrow, 1); FLASH_COUNT(plane_tests, np);
@@ -548,18 +549,26 @@ FLASH_HD bool grid_sd(const ConvexC& C, const float* __restrict__ pool, F3 y, fl
 // f(x) = sum w_i |x-c_i|^3 + a0 + a.x ; returned value f/|grad f| (normalize) -- fp64 because the
 // cubic terms cancel to ~1e-4 of their magnitude.
 struct SkinEval { double s, f, ginv; D3 nh; };
+// 1/sqrt(r2) and sqrt(r2) in fp64 from an fp32 rsqrt seed (rel. error 2^-22) + one fp64 Newton step:
+// rel. error 1.5*(2^-22)^2 = 8.5e-14, far below the 1e-10 the RBF sums need; r2 == 0 gives r = 0 and a
+// finite (huge) inverse that only ever multiplies an exact zero.
+FLASH_HD double drsqrt_fast(double r2) {
+#ifdef __CUDA_ARCH__
+  double y = (double)rsqrtf(fmaxf((float)r2, 1e-30f));
+  return y * fma(-0.5 * r2, y * y, 1.5);
+#else
+  return r2 > 0.0 ? 1.0 / sqrt(r2) : 1e15;
+#endif
+}
 FLASH_HD double dsqrt_fast(double r2) {
 #ifdef __CUDA_ARCH__
-  // fp32 rsqrt seed (rel. error 2^-22) + one fp64 Newton step on 1/sqrt: rel. error 1.5*(2^-22)^2 =
-  // 8.5e-14, far below the 1e-10 the RBF sums need; r2 == 0 gives exactly 0.
-  double y = (double)rsqrtf(fmaxf((float)r2, 1e-30f));
-  y = y * fma(-0.5 * r2, y * y, 1.5);
-  return r2 * y;
+  return r2 * drsqrt_fast(r2);
 #else
   return sqrt(r2);
 #endif
 }
 FLASH_HD SkinEval skin_eval(const double* __restrict__ c, const double* __restrict__ w, int n, bool normalize, double px, double py, double pz) {
+  FLASH_COUNT(skin64, 1);
   double f = w[n] + w[n + 1] * px + w[n + 2] * py + w[n + 3] * pz;
   double gx = w[n + 1], gy = w[n + 2], gz = w[n + 3];
   for (int i = 0; i < n; ++i) {
@@ -575,9 +584,76 @@ FLASH_HD SkinEval skin_eval(const double* __restrict__ c, const double* __restri
   e.f = f;
   if (!normalize) { e.s = f; e.ginv = 1.0; e.nh = d3(0, 0, 0); return e; }
   double g2 = gx * gx + gy * gy + gz * gz;
+#ifdef __CUDA_ARCH__
+  double gi = drsqrt_fast(g2);
+  gi = gi * fma(-0.5 * g2, gi * gi, 1.5);   // second Newton step: full fp64 accuracy for the value itself
+#else
   double gi = 1.0 / sqrt(g2);
+#endif
   e.ginv = gi; e.s = f * gi; e.nh = d3(gx * gi, gy * gi, gz * gi);
   return e;
+}
+
+// Certified fp32 interval [lo, hi] for the skin value of one point (pre-filter of the min over
+// surfaces: the fp64 evaluation above is needed only where the skin can be the minimum).
+// cw = fp32 side table {cx,cy,cz,3w}[n], {a0,ax,ay,az} (tabf_fill).  Error model: inputs are rounded
+// to fp32 (centres: eps*|c|, with |c| <= |p| + r), every operation adds eps relative; each cubic term
+// 3w r^3 therefore carries at most ~16 eps |3w| r^2 (r + |p|_1), each gradient term 3w r u at most
+// ~12 eps |3w| r (r + |p|_1), and the n-term sums add n*eps of the absolute sum.  K below is that
+// bound with a factor >2 of slack; eps = 2^-23.
+struct SkinBound { float lo, hi; };
+FLASH_HD SkinBound skin_bound_f32(const float* __restrict__ cw, int n, bool normalize, float px, float py, float pz) {
+  const float p1 = fabsf(px) + fabsf(py) + fabsf(pz);
+  float f3 = 0.f, gx = 0.f, gy = 0.f, gz = 0.f, A = 0.f, B = 0.f;   // f3 = 3 * sum w r^3
+  for (int i = 0; i < n; ++i) {
+    const float ux = px - cw[4 * i], uy = py - cw[4 * i + 1], uz = pz - cw[4 * i + 2], w3 = cw[4 * i + 3];
+    const float r2 = fmaf(ux, ux, fmaf(uy, uy, uz * uz));
+#ifdef __CUDA_ARCH__
+    const float r = r2 * rsqrtf(fmaxf(r2, 1e-30f));
+#else
+    const float r = sqrtf(r2);
+#endif
+    const float wr = w3 * r;
+    f3 = fmaf(wr, r2, f3);
+    gx = fmaf(wr, ux, gx); gy = fmaf(wr, uy, gy); gz = fmaf(wr, uz, gz);
+    const float t = fabsf(wr) * (r + p1);
+    B += t;
+    A = fmaf(t, r, A);
+  }
+  const float* a = cw + 4 * n;
+  const float third = 1.0f / 3.0f;
+  const float f = fmaf(f3, third, fmaf(a[1], px, fmaf(a[2], py, fmaf(a[3], pz, a[0]))));
+  const float K = 1.1920929e-7f * (float)(2 * n + 40);
+  const float pa = fabsf(a[0]) + fabsf(a[1] * px) + fabsf(a[2] * py) + fabsf(a[3] * pz);
+  const float Ef = K * (A * third + pa) + 1e-30f;
+  SkinBound o;
+  if (!normalize) { o.lo = f - Ef - fabsf(f) * 1e-6f; o.hi = f + Ef + fabsf(f) * 1e-6f; return o; }
+  gx += a[1]; gy += a[2]; gz += a[3];
+  const float gn = sqrtf(fmaf(gx, gx, fmaf(gy, gy, gz * gz)));
+  const float Eg = 2.f * K * (B + fabsf(a[1]) + fabsf(a[2]) + fabsf(a[3])) + 1e-30f;
+  const float g_lo = gn * (1.f - 1e-6f) - Eg, g_hi = gn * (1.f + 1e-6f) + Eg;
+  const float f_lo = f - Ef, f_hi = f + Ef;
+  o.lo = -3.0e38f; o.hi = 3.0e38f;
+  if (g_lo > 0.f) {
+    if (f_lo > 0.f) { o.lo = (f_lo / g_hi) * (1.f - 1e-6f); o.hi = (f_hi / g_lo) * (1.f + 1e-6f); }
+    else if (f_hi < 0.f) { o.lo = (f_lo / g_lo) * (1.f + 1e-6f); o.hi = (f_hi / g_hi) * (1.f - 1e-6f); }
+    else { o.lo = (f_lo / g_lo) * (1.f + 1e-6f) - 1e-30f; o.hi = (f_hi / g_lo) * (1.f + 1e-6f) + 1e-30f; }
+  }
+  return o;
+}
+// fp32 side table of one config: hull transforms (12 floats each) and the skin tables above
+FLASH_HD void tabf_fill(const HotModel& H, const double* __restrict__ tab, float* __restrict__ tabf, int tid, int nthreads) {
+  for (int i = tid; i < 12 * H.n_convex; i += nthreads) tabf[i] = (float)tab[i];
+  for (int k = 0; k < H.n_skins; ++k) {
+    const SkinC& K = H.skin[k];
+    const double* c = tab + K.tab_off;
+    const double* w = c + 3 * K.npts;
+    float* dst = tabf + K.tabf_off;
+    for (int e = tid; e < 4 * (K.npts + 1); e += nthreads) {
+      const int i = e >> 2, a = e & 3;
+      dst[e] = i < K.npts ? (a < 3 ? (float)c[3 * i + a] : (float)(3.0 * w[i])) : (float)w[K.npts + a];
+    }
+  }
 }
 
 // Adjoint contributions of ONE point (where this skin is the minimum) to centre i:
@@ -594,13 +670,14 @@ FLASH_HD void skin_adjoint_term(const double* __restrict__ c, const double* __re
   }
   double ux = px - c[3 * i], uy = py - c[3 * i + 1], uz = pz - c[3 * i + 2];
   double r2 = ux * ux + uy * uy + uz * uz;
-  double r = dsqrt_fast(r2);
+  double ri = drsqrt_fast(r2);
+  double r = r2 * ri;
   double un = ux * nh.x + uy * nh.y + uz * nh.z;
   out[0] = beta * (r * r2 - sn * 3.0 * r * un);
   double wi = w[i];
   double k1 = -3.0 * wi * r;                              // d f / d c_i          = k1 * u
   double k2 = sn * wi * 3.0 * r;                          // -s * n.d(grad f)/dc_i = k2 * nh + k3 * u
-  double k3 = r > 0.0 ? sn * wi * 3.0 * un / r : 0.0;
+  double k3 = r2 > 0.0 ? sn * wi * 3.0 * un * ri : 0.0;
   out[1] = beta * ((k1 + k3) * ux + k2 * nh.x);
   out[2] = beta * ((k1 + k3) * uy + k2 * nh.y);
   out[3] = beta * ((k1 + k3) * uz + k2 * nh.z);
@@ -666,20 +743,34 @@ FLASH_HD unsigned group_candidates(const HotModel& M, const float* __restrict__ 
 // The point is passed in fp64: the cost path feeds fp32 points (exact in fp64), the ray marcher its
 // fp64 sample positions.
 FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __restrict__ tab, const float* __restrict__ tabf,
-                         double px, double py, double pz, unsigned cand, int first, bool use_grid, PointEval& out) {
+                         double px, double py, double pz, unsigned cand, int first, bool use_grid, bool fp32_point, PointEval& out) {
   const ConvexC* __restrict__ cvx = M.cvx;
   float best = 3.0e38f; int arg = 0x7fffffff; int slot = -1; int is_skin = 0;
   out.y = f3(0, 0, 0); out.n = f3(0, 0, 0);
   out.sk.s = 0; out.sk.f = 0; out.sk.ginv = 0; out.sk.nh = d3(0, 0, 0);
-  for (int k = 0; k < M.n_skins; ++k) {
-    const SkinC& K = M.skin[k];
-    const double* c = tab + K.tab_off;
-    SkinEval e = skin_eval(c, c + 3 * K.npts, K.npts, M.normalize != 0, px, py, pz);
-    float d = (float)e.s;
-    if (lex_less(d, K.surface, best, arg)) { best = d; arg = K.surface; slot = k; is_skin = 1; out.sk = e; }
-  }
   const int nc = M.n_convex;
   const float fx = (float)px, fy = (float)py, fz = (float)pz;
+  // Skins.  With convex bodies in the model the fp64 evaluation is deferred: a certified fp32 interval
+  // [lo, hi] of each skin's value is enough to (a) give the hull scans a cutoff (hi) and (b) decide
+  // afterwards whether the skin can still be the minimum (lo <= best hull); only then is it evaluated
+  // in fp64.  The point must be fp32-representable for the interval to be valid (cost path); the ray
+  // marcher passes fp64 sample positions and evaluates the skins directly.
+  const bool defer = nc > 0 && fp32_point;
+  float s_lo[MAX_SKINS];
+  float cut = 3.0e38f;   // an upper bound of the final minimum that no surface index is attached to
+  for (int k = 0; k < M.n_skins; ++k) {
+    const SkinC& K = M.skin[k];
+    if (defer) {
+      const SkinBound sb = skin_bound_f32(tabf + K.tabf_off, K.npts, M.normalize != 0, fx, fy, fz);
+      s_lo[k] = sb.lo;
+      cut = fminf(cut, sb.hi);
+    } else {
+      const double* c = tab + K.tab_off;
+      SkinEval e = skin_eval(c, c + 3 * K.npts, K.npts, M.normalize != 0, px, py, pz);
+      float d = (float)e.s;
+      if (lex_less(d, K.surface, best, arg)) { best = d; arg = K.surface; slot = k; is_skin = 1; out.sk = e; }
+    }
+  }
   FLASH_COUNT(points, 1);
   if (first < 0) {   // no group information: the most promising body by the per-point bound
     float lb0 = 3.0e38f;
@@ -709,17 +800,27 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
     if (!single) {
       FLASH_COUNT(lb_tests, 1);
       const float l = aabb_lower_bound(C.lo, C.hi, C.depth_bound, to_geometry_f32(tabf + 12 * j, fx, fy, fz));
-      skip = l > best || (l == best && C.surface > arg);
+      skip = l > best || (l == best && C.surface > arg) || l > cut;
     }
     if (!skip) {
       F3 y = to_geometry(tab + 12 * j, px, py, pz);
       F3 n; float d;
       bool done = false;
       if (use_grid && C.g_on) done = grid_sd(C, G.grid_pool, y, d, n);
-      if (!done) d = hull_sd(hull_view(G, C), y, best, n);
+      if (!done) d = hull_sd(hull_view(G, C), y, fminf(best, cut), n);
       if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
     }
     j = -1;
+  }
+  if (defer) {
+    for (int k = 0; k < M.n_skins; ++k) {
+      if (s_lo[k] > best) continue;   // certified: this skin is strictly above the best hull
+      const SkinC& K = M.skin[k];
+      const double* c = tab + K.tab_off;
+      SkinEval e = skin_eval(c, c + 3 * K.npts, K.npts, M.normalize != 0, px, py, pz);
+      float d = (float)e.s;
+      if (lex_less(d, K.surface, best, arg)) { best = d; arg = K.surface; slot = k; is_skin = 1; out.sk = e; }
+    }
   }
   out.d = best; out.arg = arg; out.slot = slot; out.is_skin = is_skin;
 }

@@ -155,12 +155,12 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
   }
   if (qoff > 64) { err = "more than 64 configuration variables"; return false; }
   M.nq = qoff;
-  int ndef = 0, tab = 0, acc = 1, auxs = 0, ptoff = 0;
+  int ndef = 0, tab = 0, acc = 1, auxs = 0, ptoff = 0, tabf = 0;
   // first pass: count convex surfaces so that the table offsets of skins follow them
   int ncv = 0;
   for (int s = 0; s < d->n_surfaces; ++s) if (d->surface_kind[s] == FLASH_SURF_CONVEX) ++ncv;
   if (ncv > MAX_CONVEX) { err = "too many convex surfaces (max 24)"; return false; }
-  tab = 12 * ncv; acc = 1 + 6 * ncv;
+  tab = 12 * ncv; acc = 1 + 6 * ncv; tabf = (12 * ncv + 3) & ~3;
   for (int s = 0; s < d->n_surfaces; ++s) {
     const int kind = d->surface_kind[s];
     const int p0 = d->point_offset[s], p1 = d->point_offset[s + 1];
@@ -242,6 +242,7 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
       K.acc_off = acc; acc += 4 * K.npts + 4;
       K.aux_off = auxs; auxs += K.M * K.M + K.M;
       K.pt_off = ptoff; ptoff += K.npts;
+      K.tabf_off = tabf; tabf += 4 * K.npts + 4;
       for (int p = p0; p < p1; ++p) {
         int b = d->point_body[p];
         if (b < -1 || b >= d->n_bodies) { err = "skin control point on unknown body"; return false; }
@@ -251,14 +252,14 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
     } else { err = "unknown surface kind"; return false; }
   }
   M.nx = M.nq + 3 * ndef;
-  M.tab_len = tab; M.acc_len = acc; M.aux_len = 25 * M.n_bodies + auxs;
+  M.tab_len = tab; M.acc_len = acc; M.aux_len = 25 * M.n_bodies + auxs; M.tabf_len = tabf;
   M.geo_f4 = (int)out.geo_f4.size(); M.geo_u32 = (int)out.geo_u32.size();
   return true;
 }
 
 inline void make_hot(const ModelC& M, HotModel& H) {
   std::memset(&H, 0, sizeof H);
-  H.n_convex = M.n_convex; H.n_skins = M.n_skins; H.normalize = M.normalize; H.acc_len = M.acc_len; H.tab_len = M.tab_len;
+  H.n_convex = M.n_convex; H.n_skins = M.n_skins; H.normalize = M.normalize; H.acc_len = M.acc_len; H.tab_len = M.tab_len; H.tabf_len = M.tabf_len;
   for (int k = 0; k < MAX_SKINS; ++k) H.skin[k] = M.skin[k];
   for (int j = 0; j < MAX_CONVEX; ++j) H.cvx[j] = M.cvx[j];
 }

@@ -51,14 +51,14 @@ __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t
 struct SmemLayout {
   size_t off_hot, off_f4, off_u32, off_tab, off_tabf, off_acc, off_queue, off_qslot, total;
 };
-__host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, int tab_len, int acc_len, int n_convex, bool grad_skins) {
+__host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, int tab_len, int acc_len, int tabf_len, bool grad_skins) {
   SmemLayout L;
   size_t o = 0;
   L.off_hot = o; o = align16(o + sizeof(HotModel));
   L.off_f4 = o; o = align16(o + sizeof(F4) * (size_t)geo_f4_n);
   L.off_u32 = o; o = align16(o + sizeof(uint32_t) * (size_t)geo_u32_n);
   L.off_tab = o; o = align16(o + sizeof(double) * (size_t)tab_len);
-  L.off_tabf = o; o = align16(o + sizeof(float) * 12 * (size_t)(n_convex > 0 ? n_convex : 1));
+  L.off_tabf = o; o = align16(o + sizeof(float) * (size_t)(tabf_len > 0 ? tabf_len : 4));
   L.off_acc = o; o = align16(o + sizeof(double) * (size_t)acc_len * WARPS);
   L.off_queue = o; o = align16(o + (grad_skins ? sizeof(double) * QENT * 32 * WARPS : 0));
   L.off_qslot = o; o = align16(o + (grad_skins ? sizeof(int) * 32 * WARPS : 0));
@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(32) prepare_kernel(const ModelC* __restrict__ 
 // ------------------------------------------------------------------------------------------------
 // stage model + geometry + this config's table in shared memory
 __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayout& L, const HotModel* hot, const F4* geo_f4, int nf4,
-                                            const uint32_t* geo_u32, int nu32, const double* tab, int tab_len, int n_convex) {
+                                            const uint32_t* geo_u32, int nu32, const double* tab, int tab_len) {
   const int tid = threadIdx.x;
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(hot);
@@ -130,8 +130,8 @@ __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayou
   {
     double* dst = reinterpret_cast<double*>(smem + L.off_tab);
     for (int i = tid; i < tab_len; i += BLOCK) dst[i] = tab[i];
-    float* dstf = reinterpret_cast<float*>(smem + L.off_tabf);   // fp32 copy of the convex transforms (culling bound)
-    for (int i = tid; i < 12 * n_convex; i += BLOCK) dstf[i] = (float)tab[i];
+    // fp32 side table: hull transforms (culling bounds) and the skins' pre-filter tables
+    tabf_fill(*hot, tab, reinterpret_cast<float*>(smem + L.off_tabf), tid, BLOCK);
   }
 }
 
@@ -148,8 +148,8 @@ __global__ void __launch_bounds__(BLOCK, FLASH_MINB) cost_kernel(const CostParam
   // every block re-derives the layout from the same numbers the host used
   const HotModel* hot_g = p.hot;
   const int tab_len = hot_g->tab_len, acc_len = hot_g->acc_len, n_convex = hot_g->n_convex;
-  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, tab_len, acc_len, n_convex, GRAD && hot_g->n_skins > 0);
-  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab + (size_t)c * tab_len, tab_len, n_convex);
+  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, tab_len, acc_len, hot_g->tabf_len, GRAD && hot_g->n_skins > 0);
+  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab + (size_t)c * tab_len, tab_len);
   double* acc_w = reinterpret_cast<double*>(smem + L.off_acc) + (size_t)warp * acc_len;
   if (!DIST) for (int i = lane; i < acc_len; i += 32) acc_w[i] = 0.0;
   __syncthreads();
@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(BLOCK, FLASH_MINB) cost_kernel(const CostParam
     if (valid) {
       const float4 P = __ldg(p.pts + i);
       px = P.x; py = P.y; pz = P.z;
-      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, cand, first, p.use_grid != 0, e);
+      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, cand, first, p.use_grid != 0, true, e);
     }
     if (DIST) {
       if (valid) {
@@ -243,18 +243,32 @@ __global__ void __launch_bounds__(BLOCK, FLASH_MINB) cost_kernel(const CostParam
           const SkinC& K = H.skin[k];
           const double* cc = tab + K.tab_off;
           const int n = K.npts;
-          for (int ci = lane; ci <= n; ci += 32) {
+          // sub-warps of G lanes (G = smallest power of two >= n+1, at most 32) each take one queued
+          // point at a time; lane % G is the control point (n = the polynomial pseudo-centre)
+          int G = 32;
+          while ((G >> 1) > n) G >>= 1;
+          const int ci0 = lane & (G - 1), sub = lane / G, E = 32 / G;
+          for (int cb = 0; cb <= n; cb += G) {
+            const int ci = cb + ci0;
             double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-            for (int qe = 0; qe < cnt; ++qe) {
-              if (qslot[qe] != k) continue;
-              const double* q = queue + qe * QENT;
-              double o[4];
-              skin_adjoint_term(cc, cc + 3 * n, n, H.normalize != 0, ci, q[0], q[1], q[2], q[3], q[4], d3(q[5], q[6], q[7]), o);
-              a0 += o[0]; a1 += o[1]; a2 += o[2]; a3 += o[3];
+            if (ci <= n) {
+              for (int qe = sub; qe < cnt; qe += E) {
+                if (qslot[qe] != k) continue;
+                const double* q = queue + qe * QENT;
+                double o[4];
+                skin_adjoint_term(cc, cc + 3 * n, n, H.normalize != 0, ci, q[0], q[1], q[2], q[3], q[4], d3(q[5], q[6], q[7]), o);
+                a0 += o[0]; a1 += o[1]; a2 += o[2]; a3 += o[3];
+              }
             }
-            double* gY = acc_w + K.acc_off;
-            if (ci < n) { gY[ci] += a0; double* gC = gY + n + 4 + 3 * ci; gC[0] += a1; gC[1] += a2; gC[2] += a3; }
-            else { gY[n] += a0; gY[n + 1] += a1; gY[n + 2] += a2; gY[n + 3] += a3; }
+            for (int o = G; o < 32; o <<= 1) {
+              a0 += __shfl_xor_sync(0xffffffffu, a0, o); a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+              a2 += __shfl_xor_sync(0xffffffffu, a2, o); a3 += __shfl_xor_sync(0xffffffffu, a3, o);
+            }
+            if (sub == 0 && ci <= n) {
+              double* gY = acc_w + K.acc_off;
+              if (ci < n) { gY[ci] += a0; double* gC = gY + n + 4 + 3 * ci; gC[0] += a1; gC[1] += a2; gC[2] += a3; }
+              else { gY[n] += a0; gY[n + 1] += a1; gY[n + 2] += a2; gY[n + 3] += a3; }
+            }
           }
         }
         __syncwarp();
@@ -442,7 +456,7 @@ struct RayParams {
 __device__ __forceinline__ double field_at(const HotModel& H, const GeoView& G, const double* tab, const float* tabf, double ox, double oy, double oz,
                                             double rx, double ry, double rz, double dist, unsigned cand, int use_grid) {
   PointEval e;
-  eval_point(H, G, tab, tabf, fma(dist, rx, ox), fma(dist, ry, oy), fma(dist, rz, oz), cand, -1, use_grid != 0, e);
+  eval_point(H, G, tab, tabf, fma(dist, rx, ox), fma(dist, ry, oy), fma(dist, rz, oz), cand, -1, use_grid != 0, false, e);
   return e.is_skin ? e.sk.s : (double)e.d;
 }
 
@@ -450,8 +464,8 @@ __global__ void __launch_bounds__(BLOCK, 2) raycast_kernel(const RayParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x;
   const HotModel* hot_g = p.hot;
-  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, hot_g->tab_len, 0, hot_g->n_convex, false);
-  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab, hot_g->tab_len, hot_g->n_convex);
+  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, hot_g->tab_len, 0, hot_g->tabf_len, false);
+  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab, hot_g->tab_len);
   __syncthreads();
   const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
   GeoView G;

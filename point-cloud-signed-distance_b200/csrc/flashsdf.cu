@@ -143,7 +143,7 @@ int ensure_batch(flash_ctx* ctx, int C) {
 
 SmemLayout cost_layout(const flash_ctx* ctx, bool grad) {
   const ModelC& M = ctx->hm.M;
-  return smem_layout(M.geo_f4, M.geo_u32, M.tab_len, M.acc_len, M.n_convex, grad && M.n_skins > 0);
+  return smem_layout(M.geo_f4, M.geo_u32, M.tab_len, M.acc_len, M.tabf_len, grad && M.n_skins > 0);
 }
 
 template <bool G, bool A, bool D>
@@ -547,7 +547,7 @@ int flash_raycast(flash_ctx* ctx, const double* x, const double* rays, int64_t R
   p.geo_f4_n = M.geo_f4; p.geo_u32_n = M.geo_u32; p.tab = ctx->d_tab; p.rays = d_rays; p.R = R;
   for (int i = 0; i < 12; ++i) p.cam[i] = cam[i];
   p.depths = d_depths; p.block_hits = ctx->d_qi; p.use_grid = ctx->use_grid ? 1 : 0;
-  const size_t smem = smem_layout(M.geo_f4, M.geo_u32, M.tab_len, 0, M.n_convex, false).total;
+  const size_t smem = smem_layout(M.geo_f4, M.geo_u32, M.tab_len, 0, M.tabf_len, false).total;
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(raycast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[1], ctx->stream));
   raycast_kernel<<<nblocks, BLOCK, smem, ctx->stream>>>(p);

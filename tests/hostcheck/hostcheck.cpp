@@ -60,8 +60,9 @@ void hc_accumulate(void* p, const double* tab, const float* pts, long long n, in
   HC* h = (HC*)p;
   const HotModel& H = h->hot;
   GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
-  float tabf[12 * MAX_CONVEX];
-  for (int i = 0; i < 12 * H.n_convex; ++i) tabf[i] = (float)tab[i];
+  std::vector<float> tabf_v(H.tabf_len + 4);
+  float* tabf = tabf_v.data();
+  tabf_fill(H, tab, tabf, 0, 1);
   const unsigned all_convex = H.n_convex >= 32 ? 0xffffffffu : ((1u << H.n_convex) - 1u);
   unsigned cand = all_convex; int first = -1;
   for (long long i = 0; i < n; ++i) {
@@ -77,7 +78,7 @@ void hc_accumulate(void* p, const double* tab, const float* pts, long long n, in
       g_cand_total += __builtin_popcount(cand); g_groups += 1;
     }
     PointEval e;
-    eval_point(H, G, tab, tabf, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], cand, first, use_grid != 0, e);
+    eval_point(H, G, tab, tabf, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], cand, first, use_grid != 0, true, e);
     double dv = e.is_skin ? e.sk.s : (double)e.d;
     if (dist) dist[i] = dv;
     if (argmin) argmin[i] = e.arg;
@@ -117,11 +118,26 @@ void hc_group_stats(long long* out, int reset) { out[0] = g_cand_total; out[1] =
 void hc_counters(long long* out, int reset) {
 #ifdef FLASH_COUNTERS
   Counters& c = counters();
-  out[0] = c.points; out[1] = c.narrow; out[2] = c.inside; out[3] = c.gjk_iters; out[4] = c.plane_tests; out[5] = c.vert_tests; out[6] = c.lb_tests;
-  if (reset) c = Counters{0, 0, 0, 0, 0, 0, 0};
+  out[0] = c.points; out[1] = c.narrow; out[2] = c.inside; out[3] = c.gjk_iters; out[4] = c.plane_tests; out[5] = c.vert_tests; out[6] = c.lb_tests; out[7] = c.skin64;
+  if (reset) c = Counters{0, 0, 0, 0, 0, 0, 0, 0};
 #else
-  for (int i = 0; i < 7; ++i) out[i] = -1;
+  for (int i = 0; i < 8; ++i) out[i] = -1;
 #endif
+}
+
+// certified fp32 interval of skin slot k's value (skin_bound_f32) next to the fp64 value (skin_eval)
+void hc_skin_bound(void* p, int k, const double* tab, const float* pts, long long n, float* lo, float* hi, double* s64) {
+  HC* h = (HC*)p;
+  const HotModel& H = h->hot;
+  const SkinC& K = H.skin[k];
+  std::vector<float> tabf(H.tabf_len + 4);
+  tabf_fill(H, tab, tabf.data(), 0, 1);
+  const double* c = tab + K.tab_off;
+  for (long long i = 0; i < n; ++i) {
+    SkinBound b = skin_bound_f32(tabf.data() + K.tabf_off, K.npts, H.normalize != 0, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]);
+    lo[i] = b.lo; hi[i] = b.hi;
+    s64[i] = skin_eval(c, c + 3 * K.npts, K.npts, H.normalize != 0, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]).s;
+  }
 }
 
 // signed distance of geometry-frame points y[n][3] to convex slot j

@@ -44,6 +44,9 @@ def lib():
         L.hc_epilogue.argtypes = [vp, c_double_p, c_double_p, c_double_p, c_double_p, C.c_double, c_double_p, c_double_p]; L.hc_epilogue.restype = None
         L.hc_counters.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_counters.restype = None
         L.hc_hull_sd.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_float_p, c_float_p]; L.hc_hull_sd.restype = None
+        L.hc_skin_bound.argtypes = [vp, C.c_int, c_double_p, c_float_p, C.c_longlong, c_float_p, c_float_p, c_double_p]; L.hc_skin_bound.restype = None
+        L.hc_set_group_cull.argtypes = [C.c_int]; L.hc_set_group_cull.restype = None
+        L.hc_group_stats.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_group_stats.restype = None
         _lib = L
     return _lib
 
@@ -96,6 +99,13 @@ class HostCheck:
         lib().hc_convex_info(self.h, j, C.byref(nv), C.byref(npl), lo.ctypes.data_as(c_float_p), hi.ctypes.data_as(c_float_p), C.byref(db))
         return nv.value, npl.value, lo, hi, db.value
 
+    def skin_bound(self, k, tab, pts):
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 3)
+        lo = np.empty(len(pts), np.float32); hi = np.empty(len(pts), np.float32); s = np.empty(len(pts))
+        lib().hc_skin_bound(self.h, k, tab.ctypes.data_as(c_double_p), pts.ctypes.data_as(c_float_p), len(pts), lo.ctypes.data_as(c_float_p),
+                            hi.ctypes.data_as(c_float_p), s.ctypes.data_as(c_double_p))
+        return lo, hi, s
+
     def hull_sd(self, j, y):
         y = np.ascontiguousarray(y, np.float32).reshape(-1, 3)
         d = np.empty(len(y), np.float32); n = np.empty((len(y), 3), np.float32)
@@ -104,6 +114,16 @@ class HostCheck:
 
 
 def counters(reset=True):
-    out = (C.c_longlong * 7)()
+    out = (C.c_longlong * 8)()
     lib().hc_counters(out, 1 if reset else 0)
-    return dict(zip(("points", "narrow", "inside", "gjk_iters", "plane_tests", "vert_tests", "lb_tests"), list(out)))
+    return dict(zip(("points", "narrow", "inside", "gjk_iters", "plane_tests", "vert_tests", "lb_tests", "skin64"), list(out)))
+
+
+def set_group_cull(on):
+    lib().hc_set_group_cull(1 if on else 0)
+
+
+def group_stats(reset=True):
+    out = (C.c_longlong * 2)()
+    lib().hc_group_stats(out, 1 if reset else 0)
+    return {"candidates": out[0], "groups": out[1]}
