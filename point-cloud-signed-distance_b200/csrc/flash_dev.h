@@ -42,7 +42,7 @@ enum { JOINT_FIXED = 0, JOINT_REVOLUTE = 1, JOINT_QUAT = 2 };
 enum { SURF_CONVEX = 0, SURF_RIGID_SKIN = 1, SURF_DEFORMABLE_SKIN = 2 };
 
 struct F3 { float x, y, z; };
-struct F4 { float x, y, z, w; };
+struct alignas(16) F4 { float x, y, z, w; };
 struct D3 { double x, y, z; };
 struct XfD { double R[9]; double t[3]; };  // p_out = R p + t
 
@@ -106,6 +106,15 @@ FLASH_HD int aux_X(const ModelC& M, int b) { return 12 * b; }
 FLASH_HD int aux_P(const ModelC& M, int b) { return 12 * M.n_bodies + 12 * b; }
 FLASH_HD int aux_qnorm(const ModelC& M, int b) { return 24 * M.n_bodies + b; }
 FLASH_HD int aux_skin0(const ModelC& M) { return 25 * M.n_bodies; }
+
+// approximate 1/sqrt(x) for normal x > 0: one MUFU.RSQ (rel. error 2^-22), no denormal fix-up code
+FLASH_HD float rsqrt_fast(float x) {
+#ifdef __CUDA_ARCH__
+  float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r;
+#else
+  return 1.0f / sqrtf(x);
+#endif
+}
 
 // ------------------------------------------------------------------ small algebra
 FLASH_HD F3 f3(float x, float y, float z) { F3 r; r.x = x; r.y = y; r.z = z; return r; }
@@ -413,19 +422,23 @@ FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
   // in the rare group that raises the maximum.  D is a lower bound of the distance, so the scan stops
   // once D exceeds `cutoff` (the best value another surface already achieved): this body cannot be
   // the minimum.
-  float D = -3.0e38f; int fs = 0;
+  float D = -3.0e38f; int fg = 0;
   for (int f = 0; f < np; f += 8) {
     float sv[8];
     planes8(planes + f, y, sv);
     const float m = fmaxf(fmaxf(fmaxf(sv[0], sv[1]), fmaxf(sv[2], sv[3])), fmaxf(fmaxf(sv[4], sv[5]), fmaxf(sv[6], sv[7])));
-    if (m > D) {
-      D = m;
-      int k = 7;
+    fg = m > D ? f : fg;      // first group that attains the maximum
+    D = fmaxf(D, m);
+    if (D > cutoff) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }   // cannot be the minimum: never a candidate value
+  }
+  int fs;
+  {                           // index inside the winning group: recomputed once instead of tracked per group
+    float sv[8];
+    planes8(planes + fg, y, sv);
+    int k = 7;
 #pragma unroll
-      for (int t = 6; t >= 0; --t) k = (sv[t] == m) ? t : k;
-      fs = f + k;
-      if (D > cutoff) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }   // cannot be the minimum: never a candidate value
-    }
+    for (int t = 6; t >= 0; --t) k = (sv[t] == D) ? t : k;
+    fs = fg + k;
   }
   FLASH_COUNT(narrow, 1); FLASH_COUNT(plane_tests, np);
   if (D <= 0.f) { FLASH_COUNT(inside, 1); nrm = plane_normal(planes, fs); return D; }
@@ -448,18 +461,22 @@ FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
     if (!(dd > 0.f)) break;
     // support vertex towards the query point: minimise q.(v - y)  <=>  minimise q.v
     FLASH_COUNT(gjk_iters, 1); FLASH_COUNT(vert_tests, nv);
-    float best = 3.0e38f; int iw = 0;
+    float best = 3.0e38f; int vg = 0;
     for (int v = 0; v < nv; v += 8) {   // groups of 8 (padded with copies of vertex 0)
       float sv[8];
       verts8(V.va + (v >> 1), V.vz + v, q, sv);
       const float m = fminf(fminf(fminf(sv[0], sv[1]), fminf(sv[2], sv[3])), fminf(fminf(sv[4], sv[5]), fminf(sv[6], sv[7])));
-      if (m < best) {
-        best = m;
-        int k = 7;
+      vg = m < best ? v : vg;
+      best = fminf(best, m);
+    }
+    int iw;
+    {
+      float sv[8];
+      verts8(V.va + (vg >> 1), V.vz + vg, q, sv);
+      int k = 7;
 #pragma unroll
-        for (int t = 6; t >= 0; --t) k = (sv[t] == m) ? t : k;
-        iw = v + k;
-      }
+      for (int t = 6; t >= 0; --t) k = (sv[t] == best) ? t : k;
+      iw = vg + k;
     }
     if (iw == S.ia || (S.ns > 1 && iw == S.ib) || (S.ns > 2 && iw == S.ic)) break;  // already supporting
     F3 w = vert_at(V, iw) - y;
@@ -503,7 +520,7 @@ FLASH_HD float aabb_lower_bound(const float* lo, const float* hi, float depth_bo
   float dy = fmaxf(fmaxf(lo[1] - y.y, y.y - hi[1]), 0.f);
   float dz = fmaxf(fmaxf(lo[2] - y.z, y.z - hi[2]), 0.f);
   float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
-  if (d2 > 0.f) return sqrtf(d2) * (1.f - 4e-6f) - 4e-6f;
+  if (d2 > 0.f) return (d2 * rsqrt_fast(fmaxf(d2, 1e-30f))) * (1.f - 4e-6f) - 4e-6f;
   return -depth_bound;
 }
 
@@ -554,7 +571,7 @@ struct SkinEval { double s, f, ginv; D3 nh; };
 // finite (huge) inverse that only ever multiplies an exact zero.
 FLASH_HD double drsqrt_fast(double r2) {
 #ifdef __CUDA_ARCH__
-  double y = (double)rsqrtf(fmaxf((float)r2, 1e-30f));
+  double y = (double)rsqrt_fast(fmaxf((float)r2, 1e-30f));
   return y * fma(-0.5 * r2, y * y, 1.5);
 #else
   return r2 > 0.0 ? 1.0 / sqrt(r2) : 1e15;
@@ -606,10 +623,11 @@ FLASH_HD SkinBound skin_bound_f32(const float* __restrict__ cw, int n, bool norm
   const float p1 = fabsf(px) + fabsf(py) + fabsf(pz);
   float f3 = 0.f, gx = 0.f, gy = 0.f, gz = 0.f, A = 0.f, B = 0.f;   // f3 = 3 * sum w r^3
   for (int i = 0; i < n; ++i) {
-    const float ux = px - cw[4 * i], uy = py - cw[4 * i + 1], uz = pz - cw[4 * i + 2], w3 = cw[4 * i + 3];
+    const F4 cc = reinterpret_cast<const F4*>(cw)[i];   // 16-byte aligned: one LDS.128
+    const float ux = px - cc.x, uy = py - cc.y, uz = pz - cc.z, w3 = cc.w;
     const float r2 = fmaf(ux, ux, fmaf(uy, uy, uz * uz));
 #ifdef __CUDA_ARCH__
-    const float r = r2 * rsqrtf(fmaxf(r2, 1e-30f));
+    const float r = r2 * rsqrt_fast(fmaxf(r2, 1e-30f));
 #else
     const float r = sqrtf(r2);
 #endif
