@@ -237,8 +237,8 @@ FLASH_HD void lu_solve(const double* LU, const double* piv, double* b, int M) {
 // Per-config preparation after fk_config: convex world->geometry transforms and, per skin, the
 // world control points (src/Flash.jl:152-205), the Turk-O'Brien system (InterpolatingSurface,
 // src/Flash.jl:212) factored in fp64, and its solution.  tab/aux are this config's blocks.
-FLASH_HD void prepare_convex(const ModelC& M, const double* aux, double* tab) {
-  for (int j = 0; j < M.n_convex; ++j) {
+FLASH_HD void prepare_convex_one(const ModelC& M, int j, const double* aux, double* tab) {
+  {
     const ConvexC& C = M.cvx[j];
     double S[12];
     if (C.body >= 0) xf_compose(aux + aux_X(M, C.body), C.frame, S);
@@ -251,16 +251,24 @@ FLASH_HD void prepare_convex(const ModelC& M, const double* aux, double* tab) {
     T[9] = -b.x; T[10] = -b.y; T[11] = -b.z;
   }
 }
+FLASH_HD void prepare_convex(const ModelC& M, const double* aux, double* tab) {
+  for (int j = 0; j < M.n_convex; ++j) prepare_convex_one(M, j, aux, tab);
+}
+// world position of control point i of skin K (src/Flash.jl:152-205)
+FLASH_HD D3 skin_centre_one(const ModelC& M, const SkinC& K, int i, const double* x, const double* aux) {
+  D3 p = d3(M.skin_pt[K.pt_off + i][0], M.skin_pt[K.pt_off + i][1], M.skin_pt[K.pt_off + i][2]);
+  if (K.kind == SURF_DEFORMABLE_SKIN && i < K.nsurf) {  // point + deformation in the body frame (src/Flash.jl:176-181)
+    const double* dd = x + M.nq + K.deform_off + 3 * i;
+    p = p + d3(dd[0], dd[1], dd[2]);
+  }
+  const int b = M.skin_pt_body[K.pt_off + i];
+  if (b >= 0) p = xf_apply(aux + aux_X(M, b), p);
+  return p;
+}
 FLASH_HD void skin_centres(const ModelC& M, const SkinC& K, const double* x, const double* aux, double* tab) {
   double* c = tab + K.tab_off;
   for (int i = 0; i < K.npts; ++i) {
-    D3 p = d3(M.skin_pt[K.pt_off + i][0], M.skin_pt[K.pt_off + i][1], M.skin_pt[K.pt_off + i][2]);
-    if (K.kind == SURF_DEFORMABLE_SKIN && i < K.nsurf) {  // point + deformation in the body frame (src/Flash.jl:176-181)
-      const double* dd = x + M.nq + K.deform_off + 3 * i;
-      p = p + d3(dd[0], dd[1], dd[2]);
-    }
-    int b = M.skin_pt_body[K.pt_off + i];
-    if (b >= 0) p = xf_apply(aux + aux_X(M, b), p);
+    const D3 p = skin_centre_one(M, K, i, x, aux);
     c[3 * i] = p.x; c[3 * i + 1] = p.y; c[3 * i + 2] = p.z;
   }
 }
@@ -415,95 +423,96 @@ FLASH_HD void verts8(const F4* __restrict__ VA, const float* __restrict__ VZ, F3
 // most-violated face (EnhancedGJK `gjk!` is the reference algorithm, src/Flash.jl:238-243; its
 // inside value is iteration-path dependent and replaced by the exact depth -- DESIGN.md).
 // nrm receives grad_y(distance).
-FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
+//
+// The function is split into the two scans (plane maximum, support vertex) and the per-point pieces
+// between them, because the main kernel runs the scans warp-cooperatively (lanes = planes / vertices,
+// flash_kernels.cuh hull_sd_warp) around the SAME per-point pieces; this serial composition is what
+// the ray marcher, skin_eval, grid baking and the host replay use.
+
+// [region: plane scan] largest plane distance D and the lowest plane index attaining it.  Returns false
+// (and leaves fs undefined) as soon as D exceeds `cutoff`: D is a lower bound of the distance.
+FLASH_HD bool hull_plane_scan(const HullView& V, F3 y, float cutoff, float& D_out, int& fs_out) {
   const F4* __restrict__ planes = V.planes;
-  const int np = V.np, nv = V.nv;
-  // Plane scan in groups of 8: 12 FFMA2 and a 3-input max tree per group; the index is recovered only
-  // in the rare group that raises the maximum.  D is a lower bound of the distance, so the scan stops
-  // once D exceeds `cutoff` (the best value another surface already achieved): this body cannot be
-  // the minimum.
   float D = -3.0e38f; int fg = 0;
-  for (int f = 0; f < np; f += 8) {
+  int f = 0;
+  for (; f < V.np; f += 8) {
     float sv[8];
     planes8(planes + f, y, sv);
     const float m = fmaxf(fmaxf(fmaxf(sv[0], sv[1]), fmaxf(sv[2], sv[3])), fmaxf(fmaxf(sv[4], sv[5]), fmaxf(sv[6], sv[7])));
-    fg = m > D ? f : fg;      // first group that attains the maximum
+    fg = m > D ? f : fg;
     D = fmaxf(D, m);
-    if (D > cutoff) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }   // cannot be the minimum: never a candidate value
+    if (D > cutoff) { D_out = D; return false; }
   }
-  int fs;
-  {                           // index inside the winning group: recomputed once instead of tracked per group
+  float sv[8];                // index inside the winning group: recomputed once instead of tracked per group
+  planes8(planes + fg, y, sv);
+  int k = 7;
+#pragma unroll
+  for (int t = 6; t >= 0; --t) k = (sv[t] == D) ? t : k;
+  D_out = D; fs_out = fg + k;
+  return true;
+}
+// [region: support scan] lowest vertex index minimising q.v
+FLASH_HD int hull_support_scan(const HullView& V, F3 q) {
+  float best = 3.0e38f; int vg = 0;
+  for (int v = 0; v < V.nv; v += 8) {   // groups of 8 (padded with copies of vertex 0)
     float sv[8];
-    planes8(planes + fg, y, sv);
-    int k = 7;
+    verts8(V.va + (v >> 1), V.vz + v, q, sv);
+    const float m = fminf(fminf(fminf(sv[0], sv[1]), fminf(sv[2], sv[3])), fminf(fminf(sv[4], sv[5]), fminf(sv[6], sv[7])));
+    vg = m < best ? v : vg;
+    best = fminf(best, m);
+  }
+  float sv[8];
+  verts8(V.va + (vg >> 1), V.vz + vg, q, sv);
+  int k = 7;
 #pragma unroll
-    for (int t = 6; t >= 0; --t) k = (sv[t] == D) ? t : k;
-    fs = fg + k;
+  for (int t = 6; t >= 0; --t) k = (sv[t] == best) ? t : k;
+  return vg + k;
+}
+// [region: start triangle] closest point of face fs's triangle; true = it is interior to the triangle,
+// i.e. the orthogonal projection of y onto the supporting plane, which lies on the hull: it IS the
+// closest point (no tolerance involved) and no support scan is needed to certify it.
+FLASH_HD bool hull_gjk_start(const HullView& V, F3 y, int fs, Simplex& S, F3& q) {
+  const uint32_t t = V.ptri[fs];
+  const int j0 = t & 255, j1 = (t >> 8) & 255, j2 = (t >> 16) & 255;
+  F3 p0 = vert_at(V, j0) - y, p1 = vert_at(V, j1) - y, p2 = vert_at(V, j2) - y;
+  float u0, u1, u2;
+  q = tri_closest0(p0, p1, p2, u0, u1, u2);
+  simplex_from(S, p0, j0, u0, p1, j1, u1, p2, j2, u2);
+  return S.ns == 3;
+}
+// [region: simplex update] one GJK step after the support scan returned vertex iw for direction q.
+// Returns false when q is already the closest point (iw supports the simplex / no descent left).
+FLASH_HD bool hull_gjk_update(const HullView& V, F3 y, int iw, Simplex& S, F3& q) {
+  if (iw == S.ia || (S.ns > 1 && iw == S.ib) || (S.ns > 2 && iw == S.ic)) return false;  // already supporting
+  const float dd = dot(q, q);
+  F3 w = vert_at(V, iw) - y;
+  if (dd - dot(q, w) <= 1e-7f * dd) return false;                                          // no descent left
+  float u0, u1, u2;
+  if (S.ns == 1) {
+    q = seg_closest0(S.a, w, u0, u1);
+    simplex_from(S, S.a, S.ia, u0, w, iw, u1, w, iw, 0.f);
+  } else if (S.ns == 2) {
+    q = tri_closest0(S.a, S.b, w, u0, u1, u2);
+    simplex_from(S, S.a, S.ia, u0, S.b, S.ib, u1, w, iw, u2);
+  } else {
+    // tetrahedron (a,b,c,w): y is outside the hull, so the closest point lies on one of the
+    // three faces that contain the new vertex
+    float x0, x1, x2, y0, y1, y2, z0, z1, z2;
+    F3 q0 = tri_closest0(S.a, S.b, w, x0, x1, x2);
+    F3 q1 = tri_closest0(S.a, S.c, w, y0, y1, y2);
+    F3 q2 = tri_closest0(S.b, S.c, w, z0, z1, z2);
+    float e0 = dot(q0, q0), e1 = dot(q1, q1), e2 = dot(q2, q2);
+    Simplex T = S;
+    if (e0 <= e1 && e0 <= e2) { q = q0; simplex_from(S, T.a, T.ia, x0, T.b, T.ib, x1, w, iw, x2); }
+    else if (e1 <= e2) { q = q1; simplex_from(S, T.a, T.ia, y0, T.c, T.ic, y1, w, iw, y2); }
+    else { q = q2; simplex_from(S, T.b, T.ib, z0, T.c, T.ic, z1, w, iw, z2); }
   }
-  FLASH_COUNT(narrow, 1); FLASH_COUNT(plane_tests, np);
-  if (D <= 0.f) { FLASH_COUNT(inside, 1); nrm = plane_normal(planes, fs); return D; }
-  Simplex S;
-  F3 q;
-  {
-    uint32_t t = V.ptri[fs];
-    int j0 = t & 255, j1 = (t >> 8) & 255, j2 = (t >> 16) & 255;
-    F3 p0 = vert_at(V, j0) - y, p1 = vert_at(V, j1) - y, p2 = vert_at(V, j2) - y;
-    float u0, u1, u2;
-    q = tri_closest0(p0, p1, p2, u0, u1, u2);
-    simplex_from(S, p0, j0, u0, p1, j1, u1, p2, j2, u2);
-  }
-  // If the closest point of the start triangle is in its interior, it is the orthogonal projection of
-  // y onto the supporting plane fs and lies on the hull: it IS the closest point (no tolerance
-  // involved), so the support scan that would merely certify it is skipped.
-  const bool certified = S.ns == 3;
-  for (int it = 0; it < GJK_MAX_ITER && !certified; ++it) {
-    float dd = dot(q, q);
-    if (!(dd > 0.f)) break;
-    // support vertex towards the query point: minimise q.(v - y)  <=>  minimise q.v
-    FLASH_COUNT(gjk_iters, 1); FLASH_COUNT(vert_tests, nv);
-    float best = 3.0e38f; int vg = 0;
-    for (int v = 0; v < nv; v += 8) {   // groups of 8 (padded with copies of vertex 0)
-      float sv[8];
-      verts8(V.va + (v >> 1), V.vz + v, q, sv);
-      const float m = fminf(fminf(fminf(sv[0], sv[1]), fminf(sv[2], sv[3])), fminf(fminf(sv[4], sv[5]), fminf(sv[6], sv[7])));
-      vg = m < best ? v : vg;
-      best = fminf(best, m);
-    }
-    int iw;
-    {
-      float sv[8];
-      verts8(V.va + (vg >> 1), V.vz + vg, q, sv);
-      int k = 7;
-#pragma unroll
-      for (int t = 6; t >= 0; --t) k = (sv[t] == best) ? t : k;
-      iw = vg + k;
-    }
-    if (iw == S.ia || (S.ns > 1 && iw == S.ib) || (S.ns > 2 && iw == S.ic)) break;  // already supporting
-    F3 w = vert_at(V, iw) - y;
-    if (dd - dot(q, w) <= 1e-7f * dd) break;                                          // no descent left
-    float u0, u1, u2;
-    if (S.ns == 1) {
-      q = seg_closest0(S.a, w, u0, u1);
-      simplex_from(S, S.a, S.ia, u0, w, iw, u1, w, iw, 0.f);
-    } else if (S.ns == 2) {
-      q = tri_closest0(S.a, S.b, w, u0, u1, u2);
-      simplex_from(S, S.a, S.ia, u0, S.b, S.ib, u1, w, iw, u2);
-    } else {
-      // tetrahedron (a,b,c,w): y is outside the hull, so the closest point lies on one of the
-      // three faces that contain the new vertex
-      float x0, x1, x2, y0, y1, y2, z0, z1, z2;
-      F3 q0 = tri_closest0(S.a, S.b, w, x0, x1, x2);
-      F3 q1 = tri_closest0(S.a, S.c, w, y0, y1, y2);
-      F3 q2 = tri_closest0(S.b, S.c, w, z0, z1, z2);
-      float e0 = dot(q0, q0), e1 = dot(q1, q1), e2 = dot(q2, q2);
-      Simplex T = S;
-      if (e0 <= e1 && e0 <= e2) { q = q0; simplex_from(S, T.a, T.ia, x0, T.b, T.ib, x1, w, iw, x2); }
-      else if (e1 <= e2) { q = q1; simplex_from(S, T.a, T.ia, y0, T.c, T.ic, y1, w, iw, y2); }
-      else { q = q2; simplex_from(S, T.b, T.ib, z0, T.c, T.ic, z1, w, iw, z2); }
-    }
-  }
-  float dd = dot(q, q);
-  if (!(dd > 0.f)) { nrm = plane_normal(planes, fs); return D; }   // numerically on the surface
+  return true;
+}
+// distance and its gradient from the converged q (closest point - y)
+FLASH_HD float hull_gjk_finish(const HullView& V, F3 q, float D, int fs, F3& nrm) {
+  const float dd = dot(q, q);
+  if (!(dd > 0.f)) { nrm = plane_normal(V.planes, fs); return D; }   // numerically on the surface
 #ifdef __CUDA_ARCH__
   float inv = rsqrtf(dd);
   inv = inv * (1.5f - 0.5f * dd * inv * inv);   // one Newton step: ~1 ulp
@@ -512,6 +521,24 @@ FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
 #endif
   nrm = q * (-inv);
   return dd * inv;
+}
+
+FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
+  float D; int fs = 0;
+  if (!hull_plane_scan(V, y, cutoff, D, fs)) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }   // cannot be the minimum: never a candidate value
+  FLASH_COUNT(narrow, 1); FLASH_COUNT(plane_tests, V.np);
+  if (D <= 0.f) { FLASH_COUNT(inside, 1); nrm = plane_normal(V.planes, fs); return D; }
+  Simplex S;
+  F3 q;
+  const bool certified = hull_gjk_start(V, y, fs, S, q);
+  for (int it = 0; it < GJK_MAX_ITER && !certified; ++it) {
+    if (!(dot(q, q) > 0.f)) break;
+    // support vertex towards the query point: minimise q.(v - y)  <=>  minimise q.v
+    FLASH_COUNT(gjk_iters, 1); FLASH_COUNT(vert_tests, V.nv);
+    const int iw = hull_support_scan(V, q);
+    if (!hull_gjk_update(V, y, iw, S, q)) break;
+  }
+  return hull_gjk_finish(V, q, D, fs, nrm);
 }
 
 // conservative lower bound of the signed distance from the AABB of the hull

@@ -23,7 +23,10 @@ namespace flashk {
 
 using namespace flashdev;
 
-constexpr int BLOCK = 256;
+#ifndef FLASH_BLOCK
+#define FLASH_BLOCK 256
+#endif
+constexpr int BLOCK = FLASH_BLOCK;
 constexpr int WARPS = BLOCK / 32;
 constexpr int QENT = 8;  // doubles per skin-queue entry: x y z s ginv nhx nhy nhz (slot in a side array)
 
@@ -82,28 +85,108 @@ __device__ __forceinline__ double warp_sum(double v) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// One warp per config.  Everything that is iterated over (the RBF matrix, the control points) lives in
+// shared memory: the serial version of this kernel spent 35 us chasing dependent global loads through
+// a 17 x 17 triangular solve.  The Turk-O'Brien system is INVERTED (in-place Gauss-Jordan with partial
+// pivoting, rows over lanes) and the inverse kept in `aux`: weights and, in the epilogue, the adjoint
+// solve are then lane-parallel matrix-vector products (the system is symmetric).
+__host__ __device__ inline size_t prepare_smem_doubles(const ModelC& M) {
+  size_t need = 8;
+  for (int k = 0; k < M.n_skins; ++k) {
+    const size_t m = (size_t)M.skin[k].M, n = (size_t)M.skin[k].npts;
+    const size_t v = m * m + 3 * n + 2 * m;
+    if (v > need) need = v;
+  }
+  return need;
+}
 __global__ void __launch_bounds__(32) prepare_kernel(const ModelC* __restrict__ Mp, const double* __restrict__ X, double* __restrict__ tab_all,
-                                                      double* __restrict__ aux_all, int* __restrict__ status) {
+                                                      double* __restrict__ aux_all, double* __restrict__ acc_all, int* __restrict__ status) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  double* sm = reinterpret_cast<double*>(smem);
   const ModelC& M = *Mp;
   const int c = blockIdx.x, lane = threadIdx.x;
   const double* x = X + (size_t)c * M.nx;
   double* tab = tab_all + (size_t)c * M.tab_len;
   double* aux = aux_all + (size_t)c * M.aux_len;
-  if (lane == 0) {
-    fk_config(M, x, aux);
-    prepare_convex(M, aux, tab);
-    for (int k = 0; k < M.n_skins; ++k) skin_centres(M, M.skin[k], x, aux, tab);
-  }
+  if (acc_all) for (int i = lane; i < M.acc_len; i += 32) acc_all[(size_t)c * M.acc_len + i] = 0.0;   // replaces a memset node
+  if (lane == 0) fk_config(M, x, aux);
   __syncwarp();
+  for (int j = lane; j < M.n_convex; j += 32) prepare_convex_one(M, j, aux, tab);
   for (int k = 0; k < M.n_skins; ++k) {
     const SkinC& K = M.skin[k];
-    double* LU = aux + aux_skin0(M) + K.aux_off;
-    skin_assemble(M, K, tab, LU, lane, 32);
+    const int n = K.npts, Mm = K.M;
+    double* A = sm;                 // [Mm][Mm]
+    double* cs = A + Mm * Mm;       // [n][3]
+    double* piv = cs + 3 * n;       // [Mm]
+    for (int i = lane; i < n; i += 32) {
+      const D3 p = skin_centre_one(M, K, i, x, aux);
+      cs[3 * i] = p.x; cs[3 * i + 1] = p.y; cs[3 * i + 2] = p.z;
+      double* ct = tab + K.tab_off + 3 * i;
+      ct[0] = p.x; ct[1] = p.y; ct[2] = p.z;
+    }
     __syncwarp();
-    int ok = lu_factor(LU, LU + K.M * K.M, K.M, lane, 32);
-    if (!ok && lane == 0) atomicExch(status, 1);  // singular RBF system (coincident control points)
+    for (int i = lane; i < Mm; i += 32)       // row i of [Phi Q; Q^T 0]
+      for (int j = 0; j < Mm; ++j) {
+        double v = 0;
+        if (i < n && j < n) {
+          const double dx = cs[3 * i] - cs[3 * j], dy = cs[3 * i + 1] - cs[3 * j + 1], dz = cs[3 * i + 2] - cs[3 * j + 2];
+          const double r2 = dx * dx + dy * dy + dz * dz;
+          v = r2 * sqrt(r2);
+        } else if (i < n) v = (j == n) ? 1.0 : cs[3 * i + (j - n - 1)];
+        else if (j < n) v = (i == n) ? 1.0 : cs[3 * j + (i - n - 1)];
+        A[i * Mm + j] = v;
+      }
     __syncwarp();
-    if (lane == 0) skin_solve(M, K, LU, LU + K.M * K.M, tab);
+    bool ok = true;
+    for (int kk = 0; kk < Mm; ++kk) {
+      // pivot: largest |A[i][kk]|, i >= kk (lowest row on ties, as the serial factorisation)
+      double best = -1.0; int bi = kk;
+      for (int i = kk + lane; i < Mm; i += 32) { const double v = fabs(A[i * Mm + kk]); if (v > best) { best = v; bi = i; } }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+      }
+      if (!(best > 0.0)) ok = false;
+      if (bi != kk) for (int j = lane; j < Mm; j += 32) { const double t = A[kk * Mm + j]; A[kk * Mm + j] = A[bi * Mm + j]; A[bi * Mm + j] = t; }
+      if (lane == 0) piv[kk] = (double)bi;
+      __syncwarp();
+      const double inv = 1.0 / A[kk * Mm + kk];
+      __syncwarp();
+      for (int j = lane; j < Mm; j += 32) A[kk * Mm + j] = (j == kk) ? inv : A[kk * Mm + j] * inv;
+      __syncwarp();
+      for (int i = lane; i < Mm; i += 32) {
+        if (i == kk) continue;
+        double* Ai = A + i * Mm;
+        const double* Ak = A + kk * Mm;
+        const double f = Ai[kk];
+        int j = 0;
+        for (; j + 4 <= Mm; j += 4) {   // loads first, then stores: the rows never alias (i != kk)
+          const double a0 = Ai[j], a1 = Ai[j + 1], a2 = Ai[j + 2], a3 = Ai[j + 3];
+          const double p0 = Ak[j], p1 = Ak[j + 1], p2 = Ak[j + 2], p3 = Ak[j + 3];
+          Ai[j] = fma(-f, p0, a0); Ai[j + 1] = fma(-f, p1, a1); Ai[j + 2] = fma(-f, p2, a2); Ai[j + 3] = fma(-f, p3, a3);
+        }
+        for (; j < Mm; ++j) Ai[j] = fma(-f, Ak[j], Ai[j]);
+        Ai[kk] = -f * inv;
+      }
+      __syncwarp();
+    }
+    for (int kk = Mm - 1; kk >= 0; --kk) {      // undo the row exchanges on the columns
+      const int pv = (int)piv[kk];
+      if (pv != kk) for (int i = lane; i < Mm; i += 32) { const double t = A[i * Mm + kk]; A[i * Mm + kk] = A[i * Mm + pv]; A[i * Mm + pv] = t; }
+      __syncwarp();
+    }
+    if (!ok && lane == 0) atomicExch(status, 1);   // singular RBF system (coincident control points)
+    // weights: rhs = 0 (surface), -1 (skeleton) (src/Flash.jl:211)  ->  w = -sum_{skeleton j} Ainv[:, j]
+    double* w = tab + K.tab_off + 3 * n;
+    for (int i = lane; i < Mm; i += 32) {
+      double sacc = 0;
+      for (int j = K.nsurf; j < n; ++j) sacc -= A[i * Mm + j];
+      w[i] = sacc;
+    }
+    if (Mm != n + 4) for (int i = lane; i < 3; i += 32) w[n + 1 + i] = 0.0;
+    double* Ainv = aux + aux_skin0(M) + K.aux_off;
+    for (int e = lane; e < Mm * Mm; e += 32) Ainv[e] = A[e];
     __syncwarp();
   }
 }
@@ -290,16 +373,134 @@ __global__ void __launch_bounds__(BLOCK, FLASH_MINB) cost_kernel(const CostParam
 }
 
 // ------------------------------------------------------------------------------------------------
+// One warp per config (after the all-reduce): the warp-parallel form of flashdev::epilogue_config, same
+// formulas.  lambda = A^-1 gY is a matrix-vector product with the inverse prepare_kernel kept (the
+// system is symmetric); control points, hulls and joints are spread over the lanes; per-body wrenches
+// are accumulated in shared memory.
+__host__ __device__ inline size_t epilogue_smem_doubles(const ModelC& M) {
+  size_t need = 8;
+  for (int k = 0; k < M.n_skins; ++k) {
+    const size_t m = (size_t)M.skin[k].M, n = (size_t)M.skin[k].npts;
+    const size_t v = m * m + 3 * n + 2 * m + 4;
+    if (v > need) need = v;
+  }
+  return need + 6 * MAX_BODIES;
+}
 __global__ void __launch_bounds__(32) epilogue_kernel(const ModelC* __restrict__ Mp, const double* __restrict__ X, const double* __restrict__ tab_all,
                                                        const double* __restrict__ aux_all, const double* __restrict__ acc_all, int C, double w_def,
-                                                       double* __restrict__ cost, double* __restrict__ grad /* may be null */) {
+                                                       double* __restrict__ cost, double* __restrict__ grad_all /* may be null */) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  double* F = reinterpret_cast<double*>(smem);   // [nb][3]
+  double* Mo = F + 3 * MAX_BODIES;               // [nb][3]
+  double* sk = Mo + 3 * MAX_BODIES;              // per-skin scratch
   const ModelC& M = *Mp;
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = blockIdx.x, lane = threadIdx.x;
   if (c >= C) return;
-  // one thread per config; scratch in local memory (a few hundred doubles)
-  double scratch[6 * MAX_BODIES + MAX_SKIN_M];
-  epilogue_config(M, X + (size_t)c * M.nx, tab_all + (size_t)c * M.tab_len, aux_all + (size_t)c * M.aux_len, acc_all + (size_t)c * M.acc_len, w_def,
-                  scratch, cost + c, grad ? grad + (size_t)c * M.nx : nullptr);
+  const double* x = X + (size_t)c * M.nx;
+  const double* tab = tab_all + (size_t)c * M.tab_len;
+  const double* aux = aux_all + (size_t)c * M.aux_len;
+  const double* acc = acc_all + (size_t)c * M.acc_len;
+  double* grad = grad_all ? grad_all + (size_t)c * M.nx : nullptr;
+  const int nb = M.n_bodies;
+  if (grad) {
+    for (int i = lane; i < 6 * MAX_BODIES; i += 32) F[i] = 0.0;
+    for (int k = lane; k < M.nx; k += 32) grad[k] = 0.0;
+    __syncwarp();
+    // convex wrenches, accumulated in the geometry frame: f = sum g, tau = sum y x g, g = -2 d n
+    for (int j = lane; j < M.n_convex; j += 32) {
+      const ConvexC& Cv = M.cvx[j];
+      if (Cv.body < 0) continue;
+      double S[12];
+      xf_compose(aux + aux_X(M, Cv.body), Cv.frame, S);
+      const double* a = acc + 1 + 6 * j;
+      const D3 f = xf_rot(S, d3(a[0], a[1], a[2]));
+      const D3 m = xf_rot(S, d3(a[3], a[4], a[5])) + cross(xf_t(S), f);
+      atomicAdd(F + 3 * Cv.body, f.x); atomicAdd(F + 3 * Cv.body + 1, f.y); atomicAdd(F + 3 * Cv.body + 2, f.z);
+      atomicAdd(Mo + 3 * Cv.body, m.x); atomicAdd(Mo + 3 * Cv.body + 1, m.y); atomicAdd(Mo + 3 * Cv.body + 2, m.z);
+    }
+    for (int k = 0; k < M.n_skins; ++k) {
+      const SkinC& K = M.skin[k];
+      const int n = K.npts, Mm = K.M;
+      double* Ainv = sk;               // [Mm][Mm]
+      double* cc = Ainv + Mm * Mm;     // [n][3]
+      double* w = cc + 3 * n;          // [n + 4]
+      double* lam = w + n + 4;         // [Mm]
+      const double* gY = acc + K.acc_off;
+      const double* gC = gY + n + 4;
+      __syncwarp();
+      {
+        const double* src = aux + aux_skin0(M) + K.aux_off;
+        for (int e = lane; e < Mm * Mm; e += 32) Ainv[e] = src[e];
+        const double* ct = tab + K.tab_off;
+        for (int e = lane; e < 4 * n + 4; e += 32) cc[e] = ct[e];   // centres then (w, a0, a): contiguous in tab
+      }
+      __syncwarp();
+      for (int i = lane; i < Mm; i += 32) {
+        double sacc = 0;
+        for (int j = 0; j < Mm; ++j) sacc = fma(Ainv[i * Mm + j], gY[j], sacc);
+        lam[i] = sacc;
+      }
+      __syncwarp();
+      const D3 la = Mm == n + 4 ? d3(lam[n + 1], lam[n + 2], lam[n + 3]) : d3(0, 0, 0);
+      const D3 av = d3(w[n + 1], w[n + 2], w[n + 3]);
+      for (int i = lane; i < n; i += 32) {
+        const D3 ci = d3(cc[3 * i], cc[3 * i + 1], cc[3 * i + 2]);
+        D3 Gi = d3(gC[3 * i], gC[3 * i + 1], gC[3 * i + 2]);
+        for (int j = 0; j < n; ++j) {
+          const D3 u = ci - d3(cc[3 * j], cc[3 * j + 1], cc[3 * j + 2]);
+          const double r = sqrt(dot(u, u));
+          Gi = Gi - u * (3.0 * r * (lam[i] * w[j] + lam[j] * w[i]));
+        }
+        Gi = Gi - av * lam[i] - la * w[i];
+        const int b = M.skin_pt_body[K.pt_off + i];
+        if (b >= 0) {
+          const D3 m = cross(ci, Gi);
+          atomicAdd(F + 3 * b, Gi.x); atomicAdd(F + 3 * b + 1, Gi.y); atomicAdd(F + 3 * b + 2, Gi.z);
+          atomicAdd(Mo + 3 * b, m.x); atomicAdd(Mo + 3 * b + 1, m.y); atomicAdd(Mo + 3 * b + 2, m.z);
+        }
+        if (K.kind == SURF_DEFORMABLE_SKIN && i < K.nsurf) {
+          const D3 gd = b >= 0 ? xf_rotT(aux + aux_X(M, b), Gi) : Gi;
+          double* o = grad + M.nq + K.deform_off + 3 * i;
+          o[0] += gd.x; o[1] += gd.y; o[2] += gd.z;
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0)
+      for (int b = nb - 1; b >= 0; --b) {  // subtree wrenches: children follow parents
+        const int p = M.body[b].parent;
+        if (p >= 0) for (int k = 0; k < 3; ++k) { F[3 * p + k] += F[3 * b + k]; Mo[3 * p + k] += Mo[3 * b + k]; }
+      }
+    __syncwarp();
+    for (int b = lane; b < nb; b += 32) {
+      const BodyC& B = M.body[b];
+      if (B.jtype == JOINT_FIXED) continue;
+      const double* P = aux + aux_P(M, b);
+      const D3 Fb = d3(F[3 * b], F[3 * b + 1], F[3 * b + 2]), Mb = d3(Mo[3 * b], Mo[3 * b + 1], Mo[3 * b + 2]);
+      if (B.jtype == JOINT_REVOLUTE) {
+        const D3 wv = xf_rot(P, d3(B.axis[0], B.axis[1], B.axis[2]));
+        grad[B.qoff] += dot(wv, Mb - cross(xf_t(P), Fb));
+      } else {
+        const double* Xb = aux + aux_X(M, b);
+        const D3 Gp = xf_rotT(P, Mb - cross(xf_t(Xb), Fb));
+        const D3 Fp = xf_rotT(P, Fb);
+        const double nrm = aux[aux_qnorm(M, b)];
+        const double* q = x + B.qoff;
+        const double qw = q[0] / nrm;
+        const D3 v = d3(q[1] / nrm, q[2] / nrm, q[3] / nrm);
+        const D3 gv = Gp * qw + cross(Gp, v);
+        const double inv = 2.0 / nrm;
+        grad[B.qoff] += -dot(Gp, v) * inv;
+        grad[B.qoff + 1] += gv.x * inv; grad[B.qoff + 2] += gv.y * inv; grad[B.qoff + 3] += gv.z * inv;
+        grad[B.qoff + 4] += Fp.x; grad[B.qoff + 5] += Fp.y; grad[B.qoff + 6] += Fp.z;
+      }
+    }
+    __syncwarp();
+  }
+  double reg = 0;
+  for (int k = M.nq + lane; k < M.nx; k += 32) { reg = fma(x[k], x[k], reg); if (grad) grad[k] += 2.0 * w_def * x[k]; }
+  reg = warp_sum(reg);
+  if (lane == 0) cost[c] = acc[0] + w_def * reg;
 }
 
 // ------------------------------------------------------------------------------------------------

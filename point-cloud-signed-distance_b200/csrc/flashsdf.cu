@@ -186,15 +186,19 @@ int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin) {
   return d_argmin ? launch_cost_t<false, true, false>(ctx, p, C, tiles, smem) : launch_cost_t<false, false, false>(ctx, p, C, tiles, smem);
 }
 
-int run_prepare(flash_ctx* ctx, int C) {
-  prepare_kernel<<<C, 32, 0, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_status);
+int run_prepare(flash_ctx* ctx, int C, bool zero_acc = false) {
+  const size_t smem = prepare_smem_doubles(ctx->hm.M) * sizeof(double);
+  if (smem > 48 * 1024) CU(cudaFuncSetAttribute(prepare_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  prepare_kernel<<<C, 32, smem, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, zero_acc ? ctx->d_acc : nullptr, ctx->d_status);
   CU(cudaGetLastError());
   ctx->launches++; ctx->last.launches++;
   return 0;
 }
 
 int run_epilogue(flash_ctx* ctx, int C, double w_def, bool grad) {
-  epilogue_kernel<<<(C + 31) / 32, 32, 0, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, C, w_def, ctx->d_cost, grad ? ctx->d_grad : nullptr);
+  const size_t smem = epilogue_smem_doubles(ctx->hm.M) * sizeof(double);
+  if (smem > 48 * 1024) CU(cudaFuncSetAttribute(epilogue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  epilogue_kernel<<<C, 32, smem, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, C, w_def, ctx->d_cost, grad ? ctx->d_grad : nullptr);
   CU(cudaGetLastError());
   ctx->launches++; ctx->last.launches++;
   return 0;
@@ -212,8 +216,7 @@ int pipeline(flash_ctx* ctx, int C, double w_def, bool grad, int32_t* d_argmin) 
   const ModelC& M = ctx->hm.M;
   int rc;
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[0], ctx->stream));
-  CU(cudaMemsetAsync(ctx->d_acc, 0, (size_t)C * M.acc_len * sizeof(double), ctx->stream));
-  if ((rc = run_prepare(ctx, C))) return rc;
+  if ((rc = run_prepare(ctx, C, true))) return rc;   // also zeroes the accumulators
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[1], ctx->stream));
   if ((rc = run_cost(ctx, C, grad, d_argmin))) return rc;
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
