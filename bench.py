@@ -268,9 +268,25 @@ def run_ours(args, rank, local_rank, world):
         # config pass it is not L2-resident for; the algorithmic minimum is one read per launch per rank
         # plus the per-config tables -- the kernel is ALU-bound, see DESIGN.md.
         n_rank = (N + world - 1) // world
-        alg_bytes = 16.0 * n_rank + 8.0 * Cn * 400
+        alg_bytes = 16.5 * n_rank + 8.0 * Cn * 400   # float4 point + 16 B bounding ball per 32 points
         kernel_s = Tk / args.steps
         achieved = alg_bytes / kernel_s / 1e9
+        # per-launch DRAM traffic and warp instructions from the committed ncu capture, scaled to this launch
+        ncu = {}
+        try:
+            ncu = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_constants.json")))
+        except Exception:
+            pass
+        traffic = None
+        issue = None
+        if ncu:
+            traffic = (ncu["dram_bytes_read"] + ncu["dram_bytes_write"]) * (n_rank / ncu["points"])
+            winst = ncu["warp_instructions"] * (n_rank * Cn) / (ncu["points"] * ncu["configs"])
+            sm_clock = (clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)) * 1e6
+            peak_issue = sm.value * 4 * sm_clock
+            issue = {"bound": "issue slots (4 warp-instructions/clk/SM)", "achieved": winst / kernel_s, "peak": peak_issue, "unit": "warp-instr/s",
+                     "frac": winst / kernel_s / peak_issue, "warp_instr_per_eval": ncu["warp_instructions"] / (ncu["points"] * ncu["configs"]),
+                     "source": "instruction count per evaluation from profiles/r01_cost_kernel_ncu_full.txt x this run's evaluations / this run's kernel time"}
         # ALU roofline (the binding one in exact mode): issue slots per second
         fp32_peak = sm.value * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12
         line = {
@@ -282,8 +298,9 @@ def run_ours(args, rank, local_rank, world):
                        "parallelism": "points sharded x%d, one ncclAllReduce of [%d][%d] fp64 per step" % (world, Cn, acc_len)},
             "device_ms_per_step": 1e3 * Tkt / args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                         "traffic": None, "peak_source": peak_src, "kernel": "cost_kernel<GRAD>", "kernel_ms": 1e3 * kernel_s,
+                         "traffic": traffic, "peak_source": peak_src, "kernel": "cost_kernel<GRAD>", "kernel_ms": 1e3 * kernel_s,
                          "note": "exact mode is ALU-bound (GJK + fp64 RBF), not HBM-bound: see alu"},
+            "issue_roofline": issue,
             "alu": {"evals_per_sm_clock": (units / world / args.steps) / kernel_s / (sm.value * (clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)) * 1e6),
                     "fp32_peak_tflops_nominal": fp32_peak},
             "clocks": clocks,

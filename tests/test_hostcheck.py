@@ -101,3 +101,69 @@ def test_model_validation_errors():
     p = PackedModel(m3); p.desc.abi_version = 99
     assert not hl.lib().hc_model_create(C.byref(p.desc), None)
     assert b"abi_version" in hl.lib().hc_last_error()
+
+
+def _morton_sorted(pts, bits=5):
+    """Order points as libflashsdf does at upload (Morton code of a 2^bits^3 cell grid over the AABB)."""
+    lo, hi = pts.min(0), pts.max(0)
+    cell = np.clip(((pts - lo) / np.maximum(hi - lo, 1e-30) * (1 << bits)).astype(np.int64), 0, (1 << bits) - 1)
+    key = np.zeros(len(pts), np.int64)
+    for b in range(bits):
+        for a in range(3):
+            key |= ((cell[:, a] >> b) & 1) << (3 * b + a)
+    return pts[np.argsort(key, kind="stable")]
+
+
+def test_warp_group_culling_changes_nothing_and_culls():
+    """The per-32-point bounding-ball culling of cost_kernel (group_candidates) must leave every
+    distance, argmin and accumulator bit-identical, and must actually remove hulls on a dense cloud."""
+    rng = np.random.default_rng(11)
+    m = flash.models.irb_and_squishable()
+    h = hl.HostCheck(m)
+    x = GOLD["irb_and_squishable/x"]
+    tab, _ = h.prepare(x)
+    # a dense slab (K5 density: ~6,700 points per litre) so that 32 Morton neighbours span ~2 cm
+    pts = rng.uniform([-0.4, -0.3, 0.0], [0.6, 0.3, 0.3], (1_200_000, 3)).astype(np.float32)
+    pts = _morton_sorted(pts, bits=6)[: 32 * 3000]
+    hl.set_group_cull(False)
+    a0, d0, g0 = h.accumulate(tab, pts)
+    hl.set_group_cull(True); hl.group_stats()
+    a1, d1, g1 = h.accumulate(tab, pts)
+    st = hl.group_stats()
+    assert np.array_equal(d0, d1) and np.array_equal(g0, g1) and np.array_equal(a0, a1)
+    assert st["groups"] == 3000 and st["candidates"] / st["groups"] < 5.0   # 8 hulls in the model
+
+
+@pytest.mark.parametrize("name", ["irb_and_squishable", "squishable", "two_link_arm", "beanbag"])
+def test_fp32_skin_interval_contains_fp64_value(name):
+    """skin_bound_f32 is a CERTIFIED interval: the pre-filter may only skip the fp64 evaluation when the
+    skin provably cannot be the minimum."""
+    rng = np.random.default_rng(2)
+    m = BUILDERS[name]()
+    h = hl.HostCheck(m)
+    x = GOLD[name + "/x"]
+    tab, _ = h.prepare(x)
+    centre = GOLD[name + "/pts"].mean(0)
+    for scale in (0.05, 0.3, 1.0, 3.0):
+        pts = (centre + scale * rng.standard_normal((50000, 3))).astype(np.float32)
+        lo, hi, s = h.skin_bound(0, tab, pts)
+        assert (lo <= s).all() and (s <= hi).all()
+    # and it is tight enough to be useful where it matters (points within ~1 m of the skin)
+    pts = (centre + 0.3 * rng.standard_normal((50000, 3))).astype(np.float32)
+    lo, hi, s = h.skin_bound(0, tab, pts)
+    assert np.median((hi - lo) / np.maximum(np.abs(s), 1e-9)) < 0.25
+
+
+def test_fp32_prefilter_defers_most_fp64_skin_evaluations():
+    rng = np.random.default_rng(4)
+    m = flash.models.irb_and_squishable()
+    h = hl.HostCheck(m)
+    x = GOLD["irb_and_squishable/x"]
+    tab, _ = h.prepare(x)
+    pts = rng.uniform([-0.8, -0.8, -0.3], [1.0, 0.8, 1.2], (20000, 3)).astype(np.float32)
+    hl.counters()
+    _, _, arg = h.accumulate(tab, pts)
+    c = hl.counters()
+    skin_surface = [i for i, s_ in enumerate(m.surfaces) if not isinstance(s_, flash.ConvexGeometry)][0]
+    winners = int((arg == skin_surface).sum())
+    assert winners <= c["skin64"] <= winners + 0.1 * len(pts)
