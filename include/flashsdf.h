@@ -224,6 +224,19 @@ int flash_grid_report(const flash_ctx* ctx, int32_t surface, int32_t dims[3], do
 int flash_grid_download(const flash_ctx* ctx, int32_t surface, double origin[3], double geometry_to_body[12],
                         float* values);
 
+/*
+ * Headless replacement of the skin drawing in `draw` (src/Flash.jl:297-329: per surface
+ * `contour_mesh(surface, lb, ub, 0.0, ...)` sent to a remote viewer): samples the field of `surface`
+ * (an index into the model's surfaces, or -1 for skin(state) = the min over all of them) on the
+ * regular grid lo + k*spacing (k = 0 .. ceil((hi-lo)/spacing)) in the world frame with the same
+ * evaluators as the cost path, and extracts the iso-surface {field = iso} by marching tetrahedra.
+ * triangles [cap][9] (may be NULL) receives up to cap triangles as three xyz vertices, oriented with the
+ * normal towards increasing field (outwards); *n_triangles the number found, which can exceed cap
+ * (call again with a larger buffer).  The triangle order is unspecified.
+ */
+int flash_contour_mesh(flash_ctx* ctx, const double* x, int32_t surface, const double lo[3], const double hi[3],
+                       double spacing, double iso, float* triangles, int64_t cap, int64_t* n_triangles);
+
 #ifdef __cplusplus
 }
 #endif

@@ -832,4 +832,115 @@ __global__ void grid_error_kernel(const HotModel* __restrict__ hot, const F4* __
   if ((threadIdx.x & 31) == 0 && err > 0.f) atomicMax(max_err_bits, __float_as_uint(err));
 }
 
+// ------------------------------------------------------------------------------------------------
+// Headless iso-surface extraction (row F4): what `draw` obtains from contour_mesh(surface, lb, ub, 0.0, ..)
+// (src/Flash.jl:318-326), written to a triangle buffer instead of a viewer.
+//   field_grid_kernel  samples one surface's field (or the min over all surfaces, surface < 0) at the nodes
+//                      of a regular world-frame grid with the SAME evaluators as the cost path
+//   march_tets_kernel  marching tetrahedra (6 per cell, no case table): 0-2 triangles per tetrahedron,
+//                      vertices by linear interpolation along the edges, oriented towards increasing field
+struct GridParams {
+  const HotModel* hot;
+  const F4* geo_f4;
+  const uint32_t* geo_u32;
+  int geo_f4_n, geo_u32_n;
+  const double* tab;      // config 0
+  double org[3]; double h; int dim[3];
+  int surface;            // surface index, or < 0 for skin(state) = min over all
+  float* field;           // [dim2][dim1][dim0]
+};
+__global__ void __launch_bounds__(BLOCK, 2) field_grid_kernel(const GridParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const HotModel* hot_g = p.hot;
+  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, hot_g->tab_len, 0, hot_g->tabf_len, false);
+  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab, hot_g->tab_len);
+  __syncthreads();
+  const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
+  GeoView G;
+  G.f4 = reinterpret_cast<const F4*>(smem + L.off_f4);
+  G.u32 = reinterpret_cast<const uint32_t*>(smem + L.off_u32);
+  G.grid_pool = nullptr;
+  const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
+  const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
+  const long long n = (long long)p.dim[0] * p.dim[1] * p.dim[2];
+  const long long i = (long long)blockIdx.x * BLOCK + threadIdx.x;
+  if (i >= n) return;
+  const int ix = (int)(i % p.dim[0]), iy = (int)((i / p.dim[0]) % p.dim[1]), iz = (int)(i / ((long long)p.dim[0] * p.dim[1]));
+  const double px = p.org[0] + ix * p.h, py = p.org[1] + iy * p.h, pz = p.org[2] + iz * p.h;
+  double v;
+  if (p.surface < 0) {
+    PointEval e;
+    const unsigned cand = H.n_convex >= 32 ? 0xffffffffu : ((1u << H.n_convex) - 1u);
+    eval_point(H, G, tab, tabf, px, py, pz, cand, -1, false, false, e);
+    v = e.is_skin ? e.sk.s : (double)e.d;
+  } else {
+    v = 3.0e38;
+    for (int k = 0; k < H.n_skins; ++k)
+      if (H.skin[k].surface == p.surface) {
+        const double* c = tab + H.skin[k].tab_off;
+        v = skin_eval(c, c + 3 * H.skin[k].npts, H.skin[k].npts, H.normalize != 0, px, py, pz).s;
+      }
+    for (int j = 0; j < H.n_convex; ++j)
+      if (H.cvx[j].surface == p.surface) { F3 nn; v = (double)hull_sd(hull_view(G, H.cvx[j]), to_geometry(tab + 12 * j, px, py, pz), 3.0e38f, nn); }
+  }
+  p.field[i] = (float)v;
+}
+
+struct MarchParams {
+  const float* field; double org[3]; double h; int dim[3]; float iso;
+  float* tris;                  // [cap][9] world-frame vertices, may be null (count only)
+  unsigned long long cap;
+  unsigned long long* count;    // triangles produced (may exceed cap: the caller re-runs with a larger buffer)
+};
+__device__ __forceinline__ void march_emit(const MarchParams& p, const float a[3], const float b[3], const float c[3], const float towards[3]) {
+  // orient: normal . (direction of increasing field) > 0
+  const float e1[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, e2[3] = {c[0] - a[0], c[1] - a[1], c[2] - a[2]};
+  const float nx = e1[1] * e2[2] - e1[2] * e2[1], ny = e1[2] * e2[0] - e1[0] * e2[2], nz = e1[0] * e2[1] - e1[1] * e2[0];
+  if (nx == 0.f && ny == 0.f && nz == 0.f) return;   // degenerate (iso value exactly on a node)
+  const bool flip = nx * towards[0] + ny * towards[1] + nz * towards[2] < 0.f;
+  const unsigned long long k = atomicAdd(p.count, 1ull);
+  if (p.tris == nullptr || k >= p.cap) return;
+  float* o = p.tris + 9 * k;
+  const float* v1 = flip ? c : b; const float* v2 = flip ? b : c;
+  o[0] = a[0]; o[1] = a[1]; o[2] = a[2]; o[3] = v1[0]; o[4] = v1[1]; o[5] = v1[2]; o[6] = v2[0]; o[7] = v2[1]; o[8] = v2[2];
+}
+__global__ void __launch_bounds__(256) march_tets_kernel(const MarchParams p) {
+  const int cx = p.dim[0] - 1, cy = p.dim[1] - 1, cz = p.dim[2] - 1;
+  const long long n = (long long)cx * cy * cz;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int ix = (int)(i % cx), iy = (int)((i / cx) % cy), iz = (int)(i / ((long long)cx * cy));
+  float val[8], pos[8][3];
+  bool any_in = false, any_out = false;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int dx = k & 1, dy = (k >> 1) & 1, dz = k >> 2;
+    val[k] = p.field[((long long)(iz + dz) * p.dim[1] + (iy + dy)) * p.dim[0] + (ix + dx)] - p.iso;
+    pos[k][0] = (float)(p.org[0] + (ix + dx) * p.h); pos[k][1] = (float)(p.org[1] + (iy + dy) * p.h); pos[k][2] = (float)(p.org[2] + (iz + dz) * p.h);
+    any_in |= val[k] < 0.f; any_out |= !(val[k] < 0.f);
+  }
+  if (!(any_in && any_out)) return;
+  // six tetrahedra around the main diagonal 0-7
+  const int tets[6][4] = {{0, 1, 3, 7}, {0, 3, 2, 7}, {0, 2, 6, 7}, {0, 6, 4, 7}, {0, 4, 5, 7}, {0, 5, 1, 7}};
+  for (int t = 0; t < 6; ++t) {
+    int in[4], out[4], ni = 0, no = 0;
+    for (int k = 0; k < 4; ++k) { const int v = tets[t][k]; if (val[v] < 0.f) in[ni++] = v; else out[no++] = v; }
+    if (ni == 0 || ni == 4) continue;
+    auto cut = [&](int a, int b, float* o) {   // a inside, b outside
+      const float w = val[a] / (val[a] - val[b]);
+      o[0] = pos[a][0] + w * (pos[b][0] - pos[a][0]); o[1] = pos[a][1] + w * (pos[b][1] - pos[a][1]); o[2] = pos[a][2] + w * (pos[b][2] - pos[a][2]);
+    };
+    float dir[3] = {0.f, 0.f, 0.f};            // mean outside corner - mean inside corner
+    for (int k = 0; k < no; ++k) for (int a = 0; a < 3; ++a) dir[a] += pos[out[k]][a] / no;
+    for (int k = 0; k < ni; ++k) for (int a = 0; a < 3; ++a) dir[a] -= pos[in[k]][a] / ni;
+    float q0[3], q1[3], q2[3], q3[3];
+    if (ni == 1) { cut(in[0], out[0], q0); cut(in[0], out[1], q1); cut(in[0], out[2], q2); march_emit(p, q0, q1, q2, dir); }
+    else if (ni == 3) { cut(in[0], out[0], q0); cut(in[1], out[0], q1); cut(in[2], out[0], q2); march_emit(p, q0, q1, q2, dir); }
+    else {  // 2-2: a quad
+      cut(in[0], out[0], q0); cut(in[0], out[1], q1); cut(in[1], out[1], q2); cut(in[1], out[0], q3);
+      march_emit(p, q0, q1, q2, dir); march_emit(p, q0, q2, q3, dir);
+    }
+  }
+}
+
 }  // namespace flashk

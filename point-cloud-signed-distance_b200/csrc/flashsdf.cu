@@ -213,7 +213,6 @@ int run_allreduce(flash_ctx* ctx, int C) {
 
 // prepare -> main -> (allreduce) -> epilogue on the ctx stream, X already on the device
 int pipeline(flash_ctx* ctx, int C, double w_def, bool grad, int32_t* d_argmin) {
-  const ModelC& M = ctx->hm.M;
   int rc;
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[0], ctx->stream));
   if ((rc = run_prepare(ctx, C, true))) return rc;   // also zeroes the accumulators
@@ -621,6 +620,58 @@ int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solve
   std::memcpy(X, ctx->h_pin, nX * sizeof(double));
   if (cost_out) std::memcpy(cost_out, h_cost, (size_t)C * sizeof(double));
   if (prof) CU(cudaEventElapsedTime(&ctx->last.ms_total, e0, e1));
+  return FLASH_OK;
+}
+
+int flash_contour_mesh(flash_ctx* ctx, const double* x, int32_t surface, const double lo[3], const double hi[3], double spacing, double iso,
+                       float* triangles, int64_t cap, int64_t* n_triangles) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  const ModelC& M = ctx->hm.M;
+  if (!x || !lo || !hi || !n_triangles || !(spacing > 0) || cap < 0 || surface >= M.n_surfaces)
+    return fail(ctx, FLASH_ERR_INVALID, "flash_contour_mesh: bad arguments");
+  *n_triangles = 0;
+  GridParams g;
+  long long nodes = 1;
+  for (int k = 0; k < 3; ++k) {
+    if (!(hi[k] > lo[k])) return fail(ctx, FLASH_ERR_INVALID, "flash_contour_mesh: empty region");
+    g.org[k] = lo[k];
+    const double cells = std::ceil((hi[k] - lo[k]) / spacing);
+    if (!(cells < 4096)) return fail(ctx, FLASH_ERR_TOO_LARGE, "flash_contour_mesh: more than 4096 cells per axis; increase spacing");
+    g.dim[k] = (int)cells + 1;
+    nodes *= g.dim[k];
+  }
+  if (nodes > (1ll << 30)) return fail(ctx, FLASH_ERR_TOO_LARGE, "flash_contour_mesh: more than 2^30 grid nodes; increase spacing");
+  CU(cudaSetDevice(ctx->device));
+  int rc = ensure_batch(ctx, 1); if (rc) return rc;
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
+  CU(cudaMemcpyAsync(ctx->d_X, x, (size_t)M.nx * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  if ((rc = run_prepare(ctx, 1))) return rc;
+  // scratch (in doubles): field[nodes] floats | counter | triangles[cap][9] floats
+  const size_t off_cnt = ((size_t)nodes + 1) / 2, off_tri = off_cnt + 1;
+  rc = ensure(ctx, ctx->d_qd, ctx->cap_qd, off_tri + ((size_t)cap * 9 + 1) / 2 + 1); if (rc) return rc;
+  float* d_field = (float*)ctx->d_qd;
+  unsigned long long* d_cnt = (unsigned long long*)(ctx->d_qd + off_cnt);
+  float* d_tri = (float*)(ctx->d_qd + off_tri);
+  g.hot = ctx->d_hot; g.geo_f4 = ctx->d_geo_f4; g.geo_u32 = ctx->d_geo_u32; g.geo_f4_n = M.geo_f4; g.geo_u32_n = M.geo_u32;
+  g.tab = ctx->d_tab; g.h = spacing; g.surface = surface; g.field = d_field;
+  const size_t smem = smem_layout(M.geo_f4, M.geo_u32, M.tab_len, 0, M.tabf_len, false).total;
+  if (smem > 48 * 1024) CU(cudaFuncSetAttribute(field_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  field_grid_kernel<<<(unsigned)((nodes + BLOCK - 1) / BLOCK), BLOCK, smem, ctx->stream>>>(g);
+  CU(cudaGetLastError());
+  CU(cudaMemsetAsync(d_cnt, 0, sizeof(unsigned long long), ctx->stream));
+  MarchParams mp;
+  mp.field = d_field; mp.h = spacing; mp.iso = (float)iso; mp.tris = (triangles && cap > 0) ? d_tri : nullptr; mp.cap = (unsigned long long)cap; mp.count = d_cnt;
+  for (int k = 0; k < 3; ++k) { mp.org[k] = lo[k]; mp.dim[k] = g.dim[k]; }
+  const long long cells = (long long)(g.dim[0] - 1) * (g.dim[1] - 1) * (g.dim[2] - 1);
+  march_tets_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, ctx->stream>>>(mp);
+  CU(cudaGetLastError());
+  ctx->launches += 2; ctx->last.launches += 2;
+  unsigned long long cnt = 0;
+  CU(cudaMemcpyAsync(&cnt, d_cnt, sizeof cnt, cudaMemcpyDeviceToHost, ctx->stream));
+  rc = check_status(ctx); if (rc) return rc;   // synchronises
+  *n_triangles = (int64_t)cnt;
+  const unsigned long long take = std::min<unsigned long long>(cnt, (unsigned long long)cap);
+  if (triangles && take > 0) CU(cudaMemcpy(triangles, d_tri, (size_t)take * 9 * sizeof(float), cudaMemcpyDeviceToHost));
   return FLASH_OK;
 }
 

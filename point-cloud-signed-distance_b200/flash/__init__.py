@@ -10,7 +10,7 @@ The Julia `ccall` shim a maintainer would add is julia/FlashCUDA.jl (see INTEGRA
 from .core import (  # noqa: F401
     BodyGeometry, ConvexGeometry, DeformableInterpolatingSkin, RigidInterpolatingSkin,
     Manipulator, ManipulatorState, Mechanism, Body, num_states, num_deformations, num_positions,
-    set_configuration_, skin, surface_points, FlashError,
+    set_configuration_, skin, surface_points, FlashError, drawing_region, contour_mesh, draw,
     JOINT_FIXED, JOINT_REVOLUTE, JOINT_QUAT_FLOATING,
 )
 from . import models, gradientdescent, tracking, depthsensors, depthdata  # noqa: F401

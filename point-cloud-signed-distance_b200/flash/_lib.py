@@ -18,7 +18,7 @@ SYMBOLS = [
     "flash_cost_grad", "flash_skin_eval", "flash_raycast", "flash_kinect_rays",
     "flash_estimate_state", "flash_comm_unique_id", "flash_comm_init", "flash_comm_world",
     "flash_profiling", "flash_last_timing", "flash_launch_count", "flash_device_info",
-    "flash_grid_report", "flash_grid_download",
+    "flash_grid_report", "flash_grid_download", "flash_contour_mesh",
 ]
 
 _lib = None
@@ -58,5 +58,7 @@ def lib():
     L.flash_device_info.argtypes = [vp, c_int32_p, c_int32_p, C.POINTER(C.c_int64)]
     L.flash_grid_report.argtypes = [vp, C.c_int32, c_int32_p, c_double_p, c_double_p]
     L.flash_grid_download.argtypes = [vp, C.c_int32, c_double_p, c_double_p, C.POINTER(C.c_float)]
+    L.flash_contour_mesh.argtypes = [vp, c_double_p, C.c_int32, c_double_p, c_double_p, C.c_double, C.c_double, C.POINTER(C.c_float), C.c_int64,
+                                     C.POINTER(C.c_int64)]
     _lib = L
     return L

@@ -240,3 +240,90 @@ def surface_points(state, surface):
     if isinstance(surface, DeformableInterpolatingSkin):
         pts = pts + np.array(state.deformations[surface]).reshape(-1, 3)
     return pts
+
+
+def _body_poses(mechanism, q):
+    """4x4 body->world transforms (host-side, only to place a drawing region around a few points)."""
+    X = []
+    for b, o in zip(mechanism.bodies, mechanism.q_offsets()):
+        J = np.eye(4)
+        if b.joint_type == JOINT_REVOLUTE:
+            a = b.axis / np.linalg.norm(b.axis)
+            K = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+            J[:3, :3] = np.eye(3) + np.sin(q[o]) * K + (1 - np.cos(q[o])) * (K @ K)
+        elif b.joint_type == JOINT_QUAT_FLOATING:
+            w, x, y, z = q[o:o + 4] / np.linalg.norm(q[o:o + 4])
+            J[:3, :3] = [[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                         [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                         [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]]
+            J[:3, 3] = q[o + 4:o + 7]
+        P = np.eye(4); P[:3, :] = b.joint_to_parent
+        T = (X[b.parent] if b.parent >= 0 else np.eye(4)) @ P @ J
+        X.append(T)
+    return X
+
+
+def drawing_region(state, surface):  # src/Flash.jl:270-295
+    """World-frame box the reference contours a surface in: the control points' AABB grown by half its
+    widths (skins), the hull's AABB grown by a tenth (convex).  Control points / hull vertices are posed
+    by one skin_eval-free FK on the host (a handful of points)."""
+    m = state.manipulator
+    X = _body_poses(m.mechanism, state.mechanism_state.q)
+    if isinstance(surface, ConvexGeometry):
+        T = X[surface.body] if surface.body >= 0 else np.eye(4)
+        F = np.eye(4); F[:3, :] = np.asarray(surface.frame, float).reshape(3, 4)
+        P = (T @ F @ np.c_[np.asarray(surface.vertices, float), np.ones(len(surface.vertices))].T).T[:, :3]
+        grow = 0.1
+    else:
+        pts = []
+        sp = surface_points(state, surface)
+        for (b, _), p in zip(surface.surface_points, sp):
+            pts.append((X[b] @ np.r_[p, 1.0])[:3] if b >= 0 else p)
+        for b, p in surface.skeleton_points:
+            pts.append((X[b] @ np.r_[np.asarray(p, float), 1.0])[:3] if b >= 0 else np.asarray(p, float))
+        P = np.array(pts)
+        grow = 0.5
+    lb, ub = P.min(0), P.max(0)
+    w = ub - lb
+    return lb - grow * w, ub + grow * w
+
+
+def contour_mesh(state, lower, upper, isosurface_value=0.0, resolution=0.1, surface=None):
+    """Iso-surface of one surface's field (or of skin(state) when surface is None) inside [lower, upper],
+    extracted on the device (flash_contour_mesh).  Returns triangles [T][3][3] (world frame)."""
+    m = state.manipulator
+    x = _flatten(state)
+    idx = -1 if surface is None else (surface if isinstance(surface, int) else m.surfaces.index(surface))
+    lo = np.ascontiguousarray(lower, float); hi = np.ascontiguousarray(upper, float)
+    n = C.c_int64(0)
+    L = _lib.lib()
+    fp = C.POINTER(C.c_float)
+    m.check(L.flash_contour_mesh(m.ctx(), x.ctypes.data_as(c_double_p), idx, lo.ctypes.data_as(c_double_p), hi.ctypes.data_as(c_double_p),
+                                 float(resolution), float(isosurface_value), None, 0, C.byref(n)))
+    tris = np.empty((max(n.value, 1), 3, 3), np.float32)
+    m.check(L.flash_contour_mesh(m.ctx(), x.ctypes.data_as(c_double_p), idx, lo.ctypes.data_as(c_double_p), hi.ctypes.data_as(c_double_p),
+                                 float(resolution), float(isosurface_value), tris.ctypes.data_as(fp), n.value, C.byref(n)))
+    return tris[: n.value]
+
+
+def draw(state, draw_skin=True, path=None, resolution=None):  # src/Flash.jl:297-329, headless
+    """The reference sends control points and one contour mesh per surface to a remote viewer (LCMGL /
+    DrakeVisualizer: unavailable on this box).  Here the same meshes are returned -- and written as a
+    Wavefront OBJ when `path` is given -- one group per surface."""
+    meshes = []
+    if draw_skin:
+        for s_ in state.manipulator.surfaces:
+            lb, ub = drawing_region(state, s_)
+            h = resolution if resolution else float(np.max(ub - lb)) / 40.0
+            meshes.append(contour_mesh(state, lb, ub, 0.0, h, surface=s_))
+    if path is not None:
+        with open(path, "w") as f:
+            base = 1
+            for k, t in enumerate(meshes):
+                f.write("g surface_%d\n" % k)
+                for v in t.reshape(-1, 3):
+                    f.write("v %.7g %.7g %.7g\n" % tuple(v))
+                for i in range(len(t)):
+                    f.write("f %d %d %d\n" % (base + 3 * i, base + 3 * i + 1, base + 3 * i + 2))
+                base += 3 * len(t)
+    return meshes

@@ -343,3 +343,46 @@ def test_grid_mode_cost_close_to_exact_on_combined_scene():
     assert np.abs(cg - ce).max() <= 2e-3 * np.abs(ce).max()
     assert np.abs(gg - ge).max() <= 2e-2 * np.abs(ge).max()
     assert (ag != ae).mean() < 5e-3
+
+
+def test_contour_mesh_lies_on_the_zero_level_set():
+    """Row F4: the headless replacement of draw()'s contour_mesh.  Every vertex of the extracted mesh must
+    be a zero of the ORACLE's field up to the linear-interpolation error of one cell, the mesh must be
+    closed (area check on the table box) and oriented outwards."""
+    m = flash.models.irb_and_squishable()
+    st = flash.ManipulatorState(m)
+    x = flash.gradientdescent.flatten(st)
+    o = ol.Oracle(m)
+    # (a) one convex surface: the table box 0.5 x 0.5 x 0.1
+    table = m.surfaces[8]
+    lb, ub = flash.drawing_region(st, table)
+    h = 0.01
+    tris = flash.contour_mesh(st, lb, ub, 0.0, h, surface=table)
+    assert len(tris) > 1000
+    v = tris.reshape(-1, 3).astype(np.float64)
+    per = o.surfaces(x, v, mode=ol.GJK)
+    assert np.abs(per[:, 8]).max() < 0.5 * h
+    e1, e2 = tris[:, 1] - tris[:, 0], tris[:, 2] - tris[:, 0]
+    nrm = np.cross(e1, e2)
+    area = 0.5 * np.linalg.norm(nrm, axis=1).sum()
+    assert abs(area - 2 * (0.5 * 0.5 + 2 * 0.5 * 0.1)) < 0.03 * area
+    cen = tris.mean(1) - v.mean(0)
+    assert ((nrm * cen).sum(1) > 0).mean() > 0.98          # outward orientation
+    # (b) the deformable skin alone, and (c) skin(state) = min over everything
+    sk = m.surfaces[7]
+    lb, ub = flash.drawing_region(st, sk)
+    t2 = flash.contour_mesh(st, lb, ub, 0.0, 0.01, surface=sk)
+    per = o.surfaces(x, t2.reshape(-1, 3).astype(np.float64), mode=ol.GJK)
+    assert len(t2) > 500 and np.abs(per[:, 7]).max() < 5e-3
+    t3 = flash.contour_mesh(st, [-0.6, -0.6, -0.1], [0.9, 0.6, 1.0], 0.0, 0.02)
+    d = o.skin(x, t3.reshape(-1, 3).astype(np.float64), mode=ol.GJK)
+    assert len(t3) > 2000 and np.abs(d).max() < 1e-2
+    # count-only call and a too-small buffer report the same total
+    import ctypes as C
+    from flash import _lib
+    from flash._desc import c_double_p
+    n = C.c_int64(0)
+    lo = np.array([-0.6, -0.6, -0.1]); hi = np.array([0.9, 0.6, 1.0])
+    m.check(_lib.lib().flash_contour_mesh(m.ctx(), x.ctypes.data_as(c_double_p), -1, lo.ctypes.data_as(c_double_p), hi.ctypes.data_as(c_double_p), 0.02, 0.0,
+                                          None, 0, C.byref(n)))
+    assert n.value == len(t3)
