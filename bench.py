@@ -312,6 +312,7 @@ def run_ours(args, rank, local_rank, world):
         if world == 1 and args.extras:
             line["grid_mode"] = grid_leg(args, flash, L, X, pts, n_local, cost.copy(), flush)
             line["tracking"] = tracking_leg(flash, L)
+            line["other_configs"] = configs_leg(flash, L, args.steps)
         if args.cpu_baseline and world == 1:
             base = cpu_leg(args.ref_points, args.ref_configs, 1, 1)
             fast = cpu_leg(args.ref_points, args.ref_configs, 1, 0, method="adjoint")
@@ -356,6 +357,83 @@ def grid_leg(args, flash, L, X, pts, n_local, cost_exact, flush):
            "note": "approximate mode (trilinear SDF grids for the convex bodies; RBF skin stays analytic fp64); parity is defined on the same grid, see DESIGN.md"}
     mg.invalidate()
     return out
+
+
+def frame_cloud(flash, state, cam, rows=480, cols=640, ground_z=0.0, far=3.0):
+    """A full Kinect frame (rows*cols points exactly): ray-cast hits on the model, misses replaced
+    by the ray's hit on the ground plane z = ground_z (or the point at `far` metres when it never lands)."""
+    sensor = flash.depthsensors.Kinect(rows, cols)
+    depths = flash.depthsensors.raycast_depths(flash.skin(state), sensor, cam).reshape(-1)
+    rays = sensor.rays.reshape(-1, 3) @ cam[:, :3].T
+    rays /= np.linalg.norm(rays, axis=1, keepdims=True)
+    org = cam[:, 3]
+    with np.errstate(divide="ignore", invalid="ignore"):
+        t_ground = (ground_z - org[2]) / rays[:, 2]
+    t_ground = np.where((t_ground > 0) & np.isfinite(t_ground) & (t_ground < 10.0), t_ground, far)
+    d = np.where(np.isnan(depths), t_ground, depths)
+    pts = org + d[:, None] * rays
+    return pts.astype(np.float32).astype(np.float64), int((~np.isnan(depths)).sum())
+
+
+def configs_leg(flash, L, steps):
+    """BASELINE.json configs[1] (K2) and configs[3] (K4) as SURVEY 8(d) defines them: depth frames of the
+    models themselves (points ON the surfaces -- the tracking regime, unlike K5's uniform cloud)."""
+    from flash._desc import Timing, c_double_p
+    out = {}
+    rng = np.random.default_rng(2)
+    # K2: IRB140, one 640x480 frame from (0, 1.5, 0.5) looking along -y, one candidate configuration
+    m = flash.models.irb140()
+    st = flash.ManipulatorState(m)
+    cam = flash.depthsensors.affine((0, 1.5, 0.5), (1, 0, 0), np.pi / 2)
+    pts, hits = frame_cloud(flash, st, cam)
+    X = rng.uniform(-np.pi / 2, np.pi / 2, (1, 6))
+    out["k2_irb140_one_frame_one_config"] = _time_batches(flash, L, m, [pts], X, steps, hits)
+    # K4: IRB140(floating)+squishable+table, 8 frames x 16 configs per frame
+    m4 = scene_model(flash)
+    X4 = scene_states(flash, m4, 16)
+    st4 = flash.ManipulatorState(m4)
+    frames = []
+    hits4 = 0
+    for k in range(8):
+        x = X4[0].copy()
+        x[:flash.num_positions(m4)] += 0.02 * rng.standard_normal(flash.num_positions(m4))
+        flash.gradientdescent.unflatten_(st4, x)
+        cam4 = flash.depthsensors.affine((0.3 + 0.05 * k, 1.8, 1.0), (1, 0, 0), np.pi / 2 + 0.25)
+        p, h = frame_cloud(flash, st4, cam4)
+        frames.append(p); hits4 += h
+    out["k4_combined_8_frames_x_16_configs"] = _time_batches(flash, L, m4, frames, X4, steps, hits4)
+    return out
+
+
+def _time_batches(flash, L, m, clouds, X, steps, hits):
+    import torch
+    from flash._desc import Timing, c_double_p
+    ctx = m.ctx()
+    Cn, nx = X.shape
+    X = np.ascontiguousarray(X)
+    cost = np.empty(Cn); grad = np.empty((Cn, nx))
+    pX, pc, pg = X.ctypes.data_as(c_double_p), cost.ctypes.data_as(c_double_p), grad.ctypes.data_as(c_double_p)
+    m.check(L.flash_profiling(ctx, 1))
+    tm = Timing()
+    def run():
+        k_ms = 0.0
+        for p in clouds:
+            m.check(L.flash_points_set(ctx, p.ctypes.data_as(c_double_p), len(p)))
+            m.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
+            L.flash_last_timing(ctx, C.byref(tm)); k_ms += tm.ms_total
+        return k_ms
+    for _ in range(2):
+        run()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter(); k = 0.0
+    for _ in range(steps):
+        k += run()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    n = sum(len(p) for p in clouds)
+    return {"points": n, "ray_hits_on_model": hits, "configs": Cn, "frames": len(clouds), "e2e_ms_per_batch": 1e3 * dt / steps,
+            "e2e_evals_per_sec": n * Cn * steps / dt, "device_ms_per_batch": k / steps, "device_evals_per_sec": n * Cn * steps / (k / 1e3),
+            "note": "e2e = flash_points_set (H2D + Morton binning) + flash_cost_grad per frame, host buffers; device = CUDA-event time of prepare+cost+epilogue"}
 
 
 def tracking_leg(flash, L):

@@ -175,30 +175,31 @@ FLASH_HD void joint_xf(const BodyC& B, const double* qn, double* J) {
 // Forward kinematics for one configuration.  x is the RAW state; quaternions are normalised here
 // exactly where the reference does it (normalize!, src/gradientdescent.jl:19-30).  Writes into the
 // per-config aux block: X_b (body->world), P_b (joint frameBefore->world), |quat_b|.
-FLASH_HD void fk_config(const ModelC& M, const double* x, double* aux) {
+FLASH_HD void fk_bodies(const BodyC* __restrict__ body, int nb, int nq, const double* x, double* aux) {
   double qn[7 * MAX_BODIES > 64 ? 64 : 7 * MAX_BODIES];  // nq <= 64 enforced at model creation
-  for (int k = 0; k < M.nq; ++k) qn[k] = x[k];
-  for (int b = 0; b < M.n_bodies; ++b) {
-    const BodyC& B = M.body[b];
+  for (int k = 0; k < nq; ++k) qn[k] = x[k];
+  for (int b = 0; b < nb; ++b) {
+    const BodyC& B = body[b];
     double nrm = 1.0;
     if (B.jtype == JOINT_QUAT) {
       const double* q = x + B.qoff;
       nrm = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
       for (int k = 0; k < 4; ++k) qn[B.qoff + k] = q[k] / nrm;
     }
-    aux[aux_qnorm(M, b)] = nrm;
+    aux[24 * nb + b] = nrm;
   }
-  for (int b = 0; b < M.n_bodies; ++b) {
-    const BodyC& B = M.body[b];
+  for (int b = 0; b < nb; ++b) {
+    const BodyC& B = body[b];
     double j2p[12], J[12];
     xf_from_rowmajor34(B.j2p, j2p);
-    double* P = aux + aux_P(M, b);
-    if (B.parent >= 0) xf_compose(aux + aux_X(M, B.parent), j2p, P);
+    double* P = aux + 12 * nb + 12 * b;
+    if (B.parent >= 0) xf_compose(aux + 12 * B.parent, j2p, P);
     else for (int i = 0; i < 12; ++i) P[i] = j2p[i];
     joint_xf(B, qn, J);
-    xf_compose(P, J, aux + aux_X(M, b));
+    xf_compose(P, J, aux + 12 * b);
   }
 }
+FLASH_HD void fk_config(const ModelC& M, const double* x, double* aux) { fk_bodies(M.body, M.n_bodies, M.nq, x, aux); }
 
 // ------------------------------------------------------------------ LU (RBF system, row A7)
 // In-place LU with partial pivoting, row-major M x M.  `lane`/`nl` let a warp share the row

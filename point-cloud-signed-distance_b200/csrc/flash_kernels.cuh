@@ -97,7 +97,8 @@ __host__ __device__ inline size_t prepare_smem_doubles(const ModelC& M) {
     const size_t v = m * m + 3 * n + 2 * m;
     if (v > need) need = v;
   }
-  return need;
+  const size_t fk = 25 * MAX_BODIES + 64 + (MAX_BODIES * sizeof(BodyC) + 7) / 8;   // FK staging (reused by the skins afterwards)
+  return need > fk ? need : fk;
 }
 __global__ void __launch_bounds__(32) prepare_kernel(const ModelC* __restrict__ Mp, const double* __restrict__ X, double* __restrict__ tab_all,
                                                       double* __restrict__ aux_all, double* __restrict__ acc_all, int* __restrict__ status) {
@@ -109,8 +110,25 @@ __global__ void __launch_bounds__(32) prepare_kernel(const ModelC* __restrict__ 
   double* tab = tab_all + (size_t)c * M.tab_len;
   double* aux = aux_all + (size_t)c * M.aux_len;
   if (acc_all) for (int i = lane; i < M.acc_len; i += 32) acc_all[(size_t)c * M.acc_len + i] = 0.0;   // replaces a memset node
-  if (lane == 0) fk_config(M, x, aux);
-  __syncwarp();
+  {
+    // forward kinematics is a serial chain: run it on lane 0 out of shared memory (bodies, x and the
+    // transforms staged by all lanes) instead of chasing dependent global loads
+    const int nb = M.n_bodies;
+    double* s_aux = sm;                                       // [25 nb]
+    double* s_x = s_aux + 25 * MAX_BODIES;                    // [nq <= 64]
+    BodyC* s_body = reinterpret_cast<BodyC*>(s_x + 64);       // [nb]
+    {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(M.body);
+      uint32_t* dst = reinterpret_cast<uint32_t*>(s_body);
+      for (int i = lane; i < (int)(nb * sizeof(BodyC) / 4); i += 32) dst[i] = src[i];
+      for (int i = lane; i < M.nq; i += 32) s_x[i] = x[i];
+    }
+    __syncwarp();
+    if (lane == 0) fk_bodies(s_body, nb, M.nq, s_x, s_aux);
+    __syncwarp();
+    for (int i = lane; i < 25 * nb; i += 32) aux[i] = s_aux[i];
+    __syncwarp();
+  }
   for (int j = lane; j < M.n_convex; j += 32) prepare_convex_one(M, j, aux, tab);
   for (int k = 0; k < M.n_skins; ++k) {
     const SkinC& K = M.skin[k];
