@@ -56,7 +56,8 @@ struct BodyC {
 struct ConvexC {
   int surface, body, nverts, nplanes;
   int off_planes, off_tris, off_verts, off_vz;  // indices into the geometry blob (units: F4 / u32 / F4 / F4)
-  int nplanes_pad, nverts_pad, pad3[2];      // counts rounded up to a multiple of 8 (padding is inert)
+  int nplanes_pad, nverts_pad;               // counts rounded up to a multiple of 8 (padding is inert)
+  int off_voff, off_vlist;                   // support direction map (u32 indices into the blob), see dir_cell()
   float lo[3], hi[3];                        // AABB of the vertices, geometry frame
   float depth_bound, r_in;                   // >= max penetration depth; <= inradius about the geometry origin
   double frame[12];                          // geometry frame -> body frame
@@ -357,12 +358,36 @@ FLASH_HD void simplex_from(Simplex& S, F3 p0, int j0, float u0, F3 p1, int j1, f
   if (S.ns == 0) simplex_push(S, p2, j2);
 }
 
+// ---- support direction map (per hull): a cube map of DIRMAP_R x DIRMAP_R cells per face over directions d.
+//   voff/vlist  (u16 offsets / u8 lists)  EVERY vertex that is the support vertex for SOME direction of
+//                      the cell (host: normal-cone / cell clipping with margins) -- the support query over
+//                      the list (2-3 vertices on the IRB140 hulls) is exact and replaces the 56-vertex scan.
+// (A face table of the same shape that replaced the 100-plane scan by one plane test was measured and
+//  dropped: the most-violated plane is a much better GJK start -- 1.0 vs 1.3 iterations per point, and the
+//  iterations, not the scan, are what costs)
+constexpr int DIRMAP_R = 8;
+constexpr int DIRMAP_CELLS = 6 * DIRMAP_R * DIRMAP_R;
+FLASH_HD int dir_cell(F3 d) {
+  const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+  int axis; float m, u, v;
+  if (ax >= ay && ax >= az) { axis = 0; m = d.x; u = d.y; v = d.z; }
+  else if (ay >= az) { axis = 1; m = d.y; u = d.z; v = d.x; }
+  else { axis = 2; m = d.z; u = d.x; v = d.y; }
+  const float inv = 1.0f / fmaxf(fabsf(m), 1e-30f);
+  // u/|m|, v/|m| in [-1, 1] -> cell
+  int iu = (int)((u * inv + 1.0f) * (0.5f * DIRMAP_R)), iv = (int)((v * inv + 1.0f) * (0.5f * DIRMAP_R));
+  iu = iu < 0 ? 0 : (iu > DIRMAP_R - 1 ? DIRMAP_R - 1 : iu);
+  iv = iv < 0 ? 0 : (iv > DIRMAP_R - 1 ? DIRMAP_R - 1 : iv);
+  return ((2 * axis + (m < 0.f ? 1 : 0)) * DIRMAP_R + iv) * DIRMAP_R + iu;
+}
+
 // ---- geometry blob layout (per hull), chosen so that the scans run on packed fp32 FMAs (FFMA2, sm_100):
 //   planes, pair k = planes 2k, 2k+1:  F4 {nx0, nx1, ny0, ny1}, F4 {nz0, nz1, -o0, -o1}
 //   vertices, pair k:                  F4 {x0, x1, y0, y1} (VA) and float2 {z0, z1} (VZ, a flat float array)
 // counts are padded to a multiple of 8; padding planes can never be the maximum, padding vertices are
 // copies of vertex 0 (never a strictly better support).
-struct HullView { const F4* planes; const uint32_t* ptri; const F4* va; const float* vz; int np, nv; };
+struct HullView { const F4* planes; const uint32_t* ptri; const F4* va; const float* vz; int np, nv;
+                  const unsigned short* voff; const unsigned char* vlist; };
 FLASH_HD F3 plane_normal(const F4* P, int f) { const float* a = reinterpret_cast<const float*>(P + (f & ~1)); const int h = f & 1; return f3(a[h], a[2 + h], a[4 + h]); }
 FLASH_HD F3 vert_at(const HullView& V, int j) { const float* a = reinterpret_cast<const float*>(V.va + (j >> 1)); const int h = j & 1; return f3(a[h], a[2 + h], V.vz[j]); }
 
@@ -469,6 +494,20 @@ FLASH_HD int hull_support_scan(const HullView& V, F3 q) {
   for (int t = 6; t >= 0; --t) k = (sv[t] == best) ? t : k;
   return vg + k;
 }
+// [region: support map] exact support vertex (lowest index minimising q.v) from the direction map: only
+// the vertices whose normal cone meets the cell of -q can be the support (host: build_dirmaps)
+FLASH_HD int hull_support_map(const HullView& V, F3 q) {
+  const int cell = dir_cell(f3(-q.x, -q.y, -q.z));
+  const int b = V.voff[cell], e = V.voff[cell + 1];
+  float best = 3.0e38f; int iw = 0;
+  for (int t = b; t < e; ++t) {       // lists are in increasing vertex order: strict < keeps the lowest index on ties
+    const int j = V.vlist[t];
+    const F3 p = vert_at(V, j);
+    const float sv = fmaf(q.x, p.x, fmaf(q.y, p.y, q.z * p.z));
+    if (sv < best) { best = sv; iw = j; }
+  }
+  return iw;
+}
 // [region: start triangle] closest point of face fs's triangle; true = it is interior to the triangle,
 // i.e. the orthogonal projection of y onto the supporting plane, which lies on the hull: it IS the
 // closest point (no tolerance involved) and no support scan is needed to certify it.
@@ -525,9 +564,10 @@ FLASH_HD float hull_gjk_finish(const HullView& V, F3 q, float D, int fs, F3& nrm
 }
 
 FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
-  float D; int fs = 0;
+  float D = 0.f; int fs = 0;
   if (!hull_plane_scan(V, y, cutoff, D, fs)) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }   // cannot be the minimum: never a candidate value
-  FLASH_COUNT(narrow, 1); FLASH_COUNT(plane_tests, V.np);
+  FLASH_COUNT(plane_tests, V.np);
+  FLASH_COUNT(narrow, 1);
   if (D <= 0.f) { FLASH_COUNT(inside, 1); nrm = plane_normal(V.planes, fs); return D; }
   Simplex S;
   F3 q;
@@ -535,8 +575,13 @@ FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
   for (int it = 0; it < GJK_MAX_ITER && !certified; ++it) {
     if (!(dot(q, q) > 0.f)) break;
     // support vertex towards the query point: minimise q.(v - y)  <=>  minimise q.v
-    FLASH_COUNT(gjk_iters, 1); FLASH_COUNT(vert_tests, V.nv);
+    FLASH_COUNT(gjk_iters, 1);
+#ifndef FLASH_NO_DIRMAP
+    const int iw = hull_support_map(V, q);
+#else
+    FLASH_COUNT(vert_tests, V.nv);
     const int iw = hull_support_scan(V, q);
+#endif
     if (!hull_gjk_update(V, y, iw, S, q)) break;
   }
   return hull_gjk_finish(V, q, D, fs, nrm);
@@ -739,6 +784,8 @@ FLASH_HD HullView hull_view(const GeoView& G, const ConvexC& C) {
   HullView V;
   V.planes = G.f4 + C.off_planes; V.ptri = G.u32 + C.off_tris; V.va = G.f4 + C.off_verts;
   V.vz = reinterpret_cast<const float*>(G.f4 + C.off_vz); V.np = C.nplanes_pad; V.nv = C.nverts_pad;
+  V.voff = reinterpret_cast<const unsigned short*>(G.u32 + C.off_voff);
+  V.vlist = reinterpret_cast<const unsigned char*>(G.u32 + C.off_vlist);
   return V;
 }
 

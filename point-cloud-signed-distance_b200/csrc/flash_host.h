@@ -109,6 +109,49 @@ inline bool build_hull(const std::vector<D3>& in, HullOut& H, std::string& err) 
   return true;
 }
 
+// Support direction map of one hull (flash_dev.h dir_cell): the exact support-candidate lists.  Vertex k is a candidate of a cell iff its normal cone
+// {d : d.(v_k - v_j) >= 0 for all j} meets the cell (grown by a margin that covers the fp32 cell
+// lookup on the device): the cell's quad in face coordinates is clipped by every half-plane
+// (Sutherland-Hodgman); what survives is the set of directions v_k supports.
+struct DirMaps { std::vector<unsigned short> voff; std::vector<unsigned char> vlist; };
+inline void build_dirmaps(const std::vector<std::array<float, 3>>& v, int nverts, DirMaps& out) {
+  const int R = DIRMAP_R;
+  out.voff.assign(DIRMAP_CELLS + 1, 0); out.vlist.clear();
+  double rout = 0;
+  for (int k = 0; k < nverts; ++k) rout = std::max(rout, std::sqrt((double)v[k][0] * v[k][0] + (double)v[k][1] * v[k][1] + (double)v[k][2] * v[k][2]));
+  const double margin = 2e-3, eps = 1e-9 * std::max(rout, 1e-30);
+  typedef std::array<double, 2> P2;
+  for (int face = 0; face < 6; ++face) {
+    const int ax = face / 2; const double sg = (face % 2 == 0) ? 1.0 : -1.0;
+    const int e1 = (ax + 1) % 3, e2 = (ax + 2) % 3;   // dir_cell: u = next axis, v = the one after
+    for (int iv = 0; iv < R; ++iv)
+      for (int iu = 0; iu < R; ++iu) {
+        const int cell = (face * R + iv) * R + iu;
+        const double u0 = -1.0 + 2.0 * iu / R - margin, u1 = -1.0 + 2.0 * (iu + 1) / R + margin;
+        const double v0 = -1.0 + 2.0 * iv / R - margin, v1 = -1.0 + 2.0 * (iv + 1) / R + margin;
+        for (int k = 0; k < nverts; ++k) {
+          std::vector<P2> poly = {{u0, v0}, {u1, v0}, {u1, v1}, {u0, v1}}, nxt;
+          for (int j = 0; j < nverts && !poly.empty(); ++j) {
+            if (j == k) continue;
+            const double w[3] = {(double)v[k][0] - v[j][0], (double)v[k][1] - v[j][1], (double)v[k][2] - v[j][2]};
+            const double a = w[e1], b = w[e2], c = sg * w[ax] + eps;   // keep a*u + b*v + c >= 0
+            nxt.clear();
+            const size_t n = poly.size();
+            for (size_t i = 0; i < n; ++i) {
+              const P2 p = poly[i], q = poly[(i + 1) % n];
+              const double fp = a * p[0] + b * p[1] + c, fq = a * q[0] + b * q[1] + c;
+              if (fp >= 0) nxt.push_back(p);
+              if ((fp >= 0) != (fq >= 0)) { const double t = fp / (fp - fq); nxt.push_back({p[0] + t * (q[0] - p[0]), p[1] + t * (q[1] - p[1])}); }
+            }
+            poly.swap(nxt);
+          }
+          if (!poly.empty()) out.vlist.push_back((unsigned char)k);
+        }
+        out.voff[cell + 1] = (unsigned short)out.vlist.size();
+      }
+  }
+}
+
 inline void options_default(flash_options* o) {
   std::memset(o, 0, sizeof *o);
   o->abi_version = FLASHSDF_ABI_VERSION;
@@ -209,6 +252,20 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
       for (int v = 0; v < C.nverts_pad; v += 2) out.geo_f4.push_back(F4{vf[v][0], vf[v + 1][0], vf[v][1], vf[v + 1][1]});
       C.off_vz = (int)out.geo_f4.size();
       for (int v = 0; v < C.nverts_pad; v += 4) out.geo_f4.push_back(F4{vf[v][2], vf[v + 1][2], vf[v + 2][2], vf[v + 3][2]});
+      {
+        // support direction map -> blob (u32 words): voff u16 | vlist bytes
+        DirMaps dm;
+        build_dirmaps(vf, C.nverts, dm);
+        auto push_bytes = [&](const void* src, size_t nbytes) {
+          const size_t words = (nbytes + 3) / 4, at = out.geo_u32.size();
+          out.geo_u32.resize(at + words, 0u);
+          std::memcpy(out.geo_u32.data() + at, src, nbytes);
+          return (int)at;
+        };
+        C.off_voff = push_bytes(dm.voff.data(), dm.voff.size() * sizeof(unsigned short));
+        if (dm.vlist.empty()) dm.vlist.push_back(0);
+        C.off_vlist = push_bytes(dm.vlist.data(), dm.vlist.size());
+      }
       {
         double rin = 1e300;   // the geometry origin is the vertex centroid: strictly inside
         for (auto& p : H.planes) rin = std::min(rin, p[3]);

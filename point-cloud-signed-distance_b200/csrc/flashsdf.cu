@@ -163,7 +163,7 @@ int choose_tile(const flash_ctx* ctx, long long n, int C) {
   long long ppb = (n * C + target_blocks - 1) / target_blocks;
   ppb = ((ppb + BLOCK - 1) / BLOCK) * BLOCK;
   if (ppb < BLOCK) ppb = BLOCK;
-  static const long long max_tile = [] { const char* e = getenv("FLASHSDF_TILE"); long long v = e ? atoll(e) : 0; return v >= BLOCK ? v : 4096ll; }();
+  static const long long max_tile = [] { const char* e = getenv("FLASHSDF_TILE"); long long v = e ? atoll(e) : 0; return v >= BLOCK ? v : 8192ll; }();
   if (ppb > max_tile) ppb = max_tile;
   while ((n + ppb - 1) / ppb > 65535) ppb *= 2;
   return (int)ppb;

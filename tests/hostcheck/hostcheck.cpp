@@ -140,6 +140,19 @@ void hc_skin_bound(void* p, int k, const double* tab, const float* pts, long lon
   }
 }
 
+// support vertex for directions q[n][3] of convex slot j: from the direction map and from the full scan
+void hc_support(void* p, int j, const float* q, long long n, int* iw_map, int* iw_scan, float* val_map, float* val_scan) {
+  HC* h = (HC*)p;
+  const ConvexC& C = h->hm.M.cvx[j];
+  GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
+  const HullView V = hull_view(G, C);
+  for (long long i = 0; i < n; ++i) {
+    const F3 d = f3(q[3 * i], q[3 * i + 1], q[3 * i + 2]);
+    iw_map[i] = hull_support_map(V, d); iw_scan[i] = hull_support_scan(V, d);
+    val_map[i] = dot(d, vert_at(V, iw_map[i])); val_scan[i] = dot(d, vert_at(V, iw_scan[i]));
+  }
+}
+
 // signed distance of geometry-frame points y[n][3] to convex slot j
 void hc_hull_sd(void* p, int j, const float* y, long long n, float* d, float* nrm) {
   HC* h = (HC*)p;

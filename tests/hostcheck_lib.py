@@ -45,6 +45,7 @@ def lib():
         L.hc_counters.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_counters.restype = None
         L.hc_hull_sd.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_float_p, c_float_p]; L.hc_hull_sd.restype = None
         L.hc_skin_bound.argtypes = [vp, C.c_int, c_double_p, c_float_p, C.c_longlong, c_float_p, c_float_p, c_double_p]; L.hc_skin_bound.restype = None
+        L.hc_support.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_int32_p, c_int32_p, c_float_p, c_float_p]; L.hc_support.restype = None
         L.hc_set_group_cull.argtypes = [C.c_int]; L.hc_set_group_cull.restype = None
         L.hc_group_stats.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_group_stats.restype = None
         _lib = L
@@ -105,6 +106,13 @@ class HostCheck:
         lib().hc_skin_bound(self.h, k, tab.ctypes.data_as(c_double_p), pts.ctypes.data_as(c_float_p), len(pts), lo.ctypes.data_as(c_float_p),
                             hi.ctypes.data_as(c_float_p), s.ctypes.data_as(c_double_p))
         return lo, hi, s
+
+    def support(self, j, q):
+        q = np.ascontiguousarray(q, np.float32).reshape(-1, 3)
+        im = np.empty(len(q), np.int32); isc = np.empty(len(q), np.int32); vm = np.empty(len(q), np.float32); vs = np.empty(len(q), np.float32)
+        lib().hc_support(self.h, j, q.ctypes.data_as(c_float_p), len(q), im.ctypes.data_as(c_int32_p), isc.ctypes.data_as(c_int32_p),
+                         vm.ctypes.data_as(c_float_p), vs.ctypes.data_as(c_float_p))
+        return im, isc, vm, vs
 
     def hull_sd(self, j, y):
         y = np.ascontiguousarray(y, np.float32).reshape(-1, 3)

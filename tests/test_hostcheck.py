@@ -167,3 +167,21 @@ def test_fp32_prefilter_defers_most_fp64_skin_evaluations():
     skin_surface = [i for i, s_ in enumerate(m.surfaces) if not isinstance(s_, flash.ConvexGeometry)][0]
     winners = int((arg == skin_surface).sum())
     assert winners <= c["skin64"] <= winners + 0.1 * len(pts)
+
+
+def test_support_direction_map_is_exact():
+    """The cube-map candidate lists must contain the true support vertex for EVERY direction (also on cell
+    borders and cube edges): the map query has to return the same support value as the 56-vertex scan."""
+    rng = np.random.default_rng(8)
+    m = flash.models.irb_and_squishable()
+    h = hl.HostCheck(m)
+    q = rng.standard_normal((200000, 3)).astype(np.float32)
+    # directions exactly on cell borders / cube edges / axes
+    g = np.linspace(-1, 1, 17)
+    U, V = np.meshgrid(g, g)
+    border = np.concatenate([np.stack([np.ones_like(U), U, V], -1).reshape(-1, 3)[:, p] * s for p in ([0, 1, 2], [1, 2, 0], [2, 0, 1]) for s in (1, -1)])
+    q = np.concatenate([q, border.astype(np.float32), np.eye(3, dtype=np.float32), -np.eye(3, dtype=np.float32)])
+    for j in range(h.n_convex):
+        im, isc, vm, vs = h.support(j, q)
+        assert np.array_equal(vm, vs), (j, np.abs(vm - vs).max())
+        assert (im == isc).mean() > 0.999      # differ only on exact ties
