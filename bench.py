@@ -286,7 +286,7 @@ def run_ours(args, rank, local_rank, world):
             peak_issue = sm.value * 4 * sm_clock
             issue = {"bound": "issue slots (4 warp-instructions/clk/SM)", "achieved": winst / kernel_s, "peak": peak_issue, "unit": "warp-instr/s",
                      "frac": winst / kernel_s / peak_issue, "warp_instr_per_eval": ncu["warp_instructions"] / (ncu["points"] * ncu["configs"]),
-                     "source": "instruction count per evaluation from profiles/r01_cost_kernel_ncu_full.txt x this run's evaluations / this run's kernel time"}
+                     "source": "instruction count per evaluation from profiles/r01_cost_kernel_ncu_full.txt (refreshed by tools/refresh_profiles.sh) x this run's evaluations / this run's kernel time"}
         # ALU roofline (the binding one in exact mode): issue slots per second
         fp32_peak = sm.value * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12
         line = {
