@@ -83,12 +83,25 @@ class ClockSampler:
         try:
             f = tempfile.NamedTemporaryFile(prefix="clocks_", suffix=".csv", delete=False)
             self.path = f.name
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=f, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
+            return
+        # nvidia-smi needs a few hundred ms to print its first line: wait for it so that even a 50 ms timed
+        # region (N=8) is bracketed by samples
+        t0 = time.perf_counter()
+        while time.perf_counter() - t0 < 5.0 and os.path.getsize(self.path) == 0:
+            time.sleep(0.02)
 
-    def stop(self):
+    def mark(self):
+        """number of samples taken so far (to tell the samples of the timed region from the warm-up's)"""
+        try:
+            return sum(1 for _ in open(self.path))
+        except Exception:
+            return 0
+
+    def stop(self, first=0):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -97,7 +110,9 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
-        for line in open(self.path):
+        for li, line in enumerate(open(self.path)):
+            if li < max(first - 1, 0):
+                continue
             t = [v.strip() for v in line.split(",")]
             if len(t) < 9:
                 continue
@@ -220,12 +235,13 @@ def run_ours(args, rank, local_rank, world):
         m.check(L.flash_points_set(ctx, pp, n_local))
         m.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
 
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()      # sampling starts before the warm-up and ends after the end-to-end loop
     for _ in range(max(args.warmup, 3)):
         step()
     launches0 = L.flash_launch_count(ctx)
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
+    first_sample = sampler.mark() if rank == 0 else 0
     t_steps, k_main, k_total = [], [], []
     tm = Timing()
     for _ in range(args.steps):
@@ -238,7 +254,6 @@ def run_ours(args, rank, local_rank, world):
         L.flash_last_timing(ctx, C.byref(tm))
         k_main.append(tm.ms_main); k_total.append(tm.ms_total)
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
     launches = L.flash_launch_count(ctx) - launches0
     checksum = float(cost.sum())
 
@@ -254,6 +269,7 @@ def run_ours(args, rank, local_rank, world):
         torch.cuda.synchronize()
         t_e2e.append(time.perf_counter() - t0)
     barrier()
+    clocks = sampler.stop(first_sample) if rank == 0 else None
 
     tt = torch.tensor([sum(t_steps), sum(t_e2e), sum(k_main) / 1e3, sum(k_total) / 1e3], dtype=torch.float64, device="cuda")
     if dist is not None:
@@ -355,6 +371,18 @@ def grid_leg(args, flash, L, X, pts, n_local, cost_exact, flush):
            "grid_spacing_m": args.grid_spacing, "grid_nodes": nodes, "grid_bytes": 4 * nodes,
            "max_abs_err_vs_exact_sdf_m": float(max(errs)), "cost_rel_dev_vs_exact_mode": float(np.abs(cost - cost_exact).max() / np.abs(cost_exact).max()),
            "note": "approximate mode (trilinear SDF grids for the convex bodies; RBF skin stays analytic fp64); parity is defined on the same grid, see DESIGN.md"}
+    # the north_star's gather roofline: measured on this GPU model by tools/microbench/l2_gather.cu (profiles/r01_l2_gather.json)
+    try:
+        gm = json.load(open(os.path.join(ROOT, "profiles", "r01_l2_gather.json")))["l2_48MiB"]
+        samples_per_eval = 1.2   # <= narrow-phase evaluations per point*config after culling (host replay counters: 1.11), each at most one 8-corner sample
+        ach = float(n_local) * Cn * samples_per_eval * 32.0 / (float(np.mean(km)) * 1e-3) / 1e9
+        out["gather_roofline"] = {"bound": "l2 gather (8 manual fp32 corner loads per trilinear sample, grids L2-resident)", "achieved": ach,
+                                  "peak": gm["trilerp8_warp_coherent"]["alg_gbs"], "unit": "GB/s", "frac": ach / gm["trilerp8_warp_coherent"]["alg_gbs"],
+                                  "peak_random_access": gm["trilerp8_random"]["alg_gbs"],
+                                  "note": "upper bound of the achieved gather rate (<= %.1f samples per evaluation x 32 B); peak = same access pattern alone on a 48 MiB grid, "
+                                          "Morton-coherent warps; the kernel is bound by culling + the RBF skin pre-filter, not by the gather (DESIGN.md 5)" % samples_per_eval}
+    except Exception:
+        pass
     mg.invalidate()
     return out
 
