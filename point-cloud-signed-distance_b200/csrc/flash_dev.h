@@ -58,6 +58,7 @@ struct ConvexC {
   int off_planes, off_tris, off_verts, off_vz;  // indices into the geometry blob (units: F4 / u32 / F4 / F4)
   int nplanes_pad, nverts_pad;               // counts rounded up to a multiple of 8 (padding is inert)
   int off_voff, off_vlist;                   // support direction map (u32 indices into the blob), see dir_cell()
+  int off_pgrp, pgrp_pad;                    // plane-group hint map (u32 index into the blob; u16 per direction cell), see hull_plane_hint()
   float lo[3], hi[3];                        // AABB of the vertices, geometry frame
   float depth_bound, r_in;                   // >= max penetration depth; <= inradius about the geometry origin
   double frame[12];                          // geometry frame -> body frame
@@ -368,17 +369,21 @@ FLASH_HD void simplex_from(Simplex& S, F3 p0, int j0, float u0, F3 p1, int j1, f
 constexpr int DIRMAP_R = 8;
 constexpr int DIRMAP_CELLS = 6 * DIRMAP_R * DIRMAP_R;
 FLASH_HD int dir_cell(F3 d) {
+  // branch-free: major axis by selects, one (approximate on the device: 2 ulp, far inside the margin the
+  // host grows every cell by) reciprocal, clamps in floating point
   const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-  int axis; float m, u, v;
-  if (ax >= ay && ax >= az) { axis = 0; m = d.x; u = d.y; v = d.z; }
-  else if (ay >= az) { axis = 1; m = d.y; u = d.z; v = d.x; }
-  else { axis = 2; m = d.z; u = d.x; v = d.y; }
-  const float inv = 1.0f / fmaxf(fabsf(m), 1e-30f);
-  // u/|m|, v/|m| in [-1, 1] -> cell
-  int iu = (int)((u * inv + 1.0f) * (0.5f * DIRMAP_R)), iv = (int)((v * inv + 1.0f) * (0.5f * DIRMAP_R));
-  iu = iu < 0 ? 0 : (iu > DIRMAP_R - 1 ? DIRMAP_R - 1 : iu);
-  iv = iv < 0 ? 0 : (iv > DIRMAP_R - 1 ? DIRMAP_R - 1 : iv);
-  return ((2 * axis + (m < 0.f ? 1 : 0)) * DIRMAP_R + iv) * DIRMAP_R + iu;
+  const bool X = ax >= ay && ax >= az, Y = !X && ay >= az;
+  const float m = X ? d.x : (Y ? d.y : d.z), u = X ? d.y : (Y ? d.z : d.x), v = X ? d.z : (Y ? d.x : d.y);
+  const int face = (X ? 0 : (Y ? 2 : 4)) + (m < 0.f ? 1 : 0);
+#ifdef __CUDA_ARCH__
+  const float inv = __fdividef(0.5f * DIRMAP_R, fmaxf(fabsf(m), 1e-30f));
+#else
+  const float inv = (0.5f * DIRMAP_R) / fmaxf(fabsf(m), 1e-30f);
+#endif
+  // (u/|m| + 1) R/2 in [0, R] -> cell
+  const float fu = fminf(fmaxf(fmaf(u, inv, 0.5f * DIRMAP_R), 0.f), DIRMAP_R - 0.5f);
+  const float fv = fminf(fmaxf(fmaf(v, inv, 0.5f * DIRMAP_R), 0.f), DIRMAP_R - 0.5f);
+  return (face * DIRMAP_R + (int)fv) * DIRMAP_R + (int)fu;
 }
 
 // ---- geometry blob layout (per hull), chosen so that the scans run on packed fp32 FMAs (FFMA2, sm_100):
@@ -387,7 +392,7 @@ FLASH_HD int dir_cell(F3 d) {
 // counts are padded to a multiple of 8; padding planes can never be the maximum, padding vertices are
 // copies of vertex 0 (never a strictly better support).
 struct HullView { const F4* planes; const uint32_t* ptri; const F4* va; const float* vz; int np, nv;
-                  const unsigned short* voff; const unsigned char* vlist; };
+                  const unsigned short* voff; const unsigned char* vlist; const unsigned short* pgrp; };
 FLASH_HD F3 plane_normal(const F4* P, int f) { const float* a = reinterpret_cast<const float*>(P + (f & ~1)); const int h = f & 1; return f3(a[h], a[2 + h], a[4 + h]); }
 FLASH_HD F3 vert_at(const HullView& V, int j) { const float* a = reinterpret_cast<const float*>(V.va + (j >> 1)); const int h = j & 1; return f3(a[h], a[2 + h], V.vz[j]); }
 
@@ -477,6 +482,41 @@ FLASH_HD bool hull_plane_scan(const HullView& V, F3 y, float cutoff, float& D_ou
   D_out = D; fs_out = fg + k;
   return true;
 }
+// [region: plane hint] The host clusters the planes into groups of 8 by normal direction and records,
+// per direction cell of y (geometry origin = hull centroid), the two groups that hold the most-violated
+// plane for (nearly) every OUTSIDE point of that cell (flash_host.h build_plane_hints: upper envelopes of
+// the plane distances along sampled rays).  The map is a HINT, never trusted for the result:
+//   * any plane with n.y - o > 0 proves y outside, and its distance is a lower bound of the true one
+//     (valid for the cutoff test and as the "certified face" shortcut of hull_gjk_start);
+//   * the distance itself comes from GJK, which terminates on its own exact criterion whatever face it
+//     started from (a missed most-violated plane costs an extra iteration, not accuracy);
+//   * if no hinted plane is violated the point is inside or the hint failed: the full scan decides.
+// Returns 0: D > cutoff (cannot be the minimum), 1: outside with (D, fs), 2: undecided.
+FLASH_HD float max8(const float sv[8]) { return fmaxf(fmaxf(fmaxf(sv[0], sv[1]), fmaxf(sv[2], sv[3])), fmaxf(fmaxf(sv[4], sv[5]), fmaxf(sv[6], sv[7]))); }
+FLASH_HD int hull_plane_hint(const HullView& V, F3 y, float cutoff, float& D_out, int& fs_out) {
+  const unsigned gg = V.pgrp[dir_cell(y)];
+  const int g0 = (int)(gg & 255u) * 8, g1 = (int)(gg >> 8) * 8;
+  float sv[8];
+  planes8(V.planes + g0, y, sv);
+  float D = max8(sv);
+  int gw = g0;
+  if (D > cutoff) { D_out = D; return 0; }        // most rejections need the first group only
+  if (g1 != g0) {
+    planes8(V.planes + g1, y, sv);
+    const float m = max8(sv);
+    gw = m > D ? g1 : g0;
+    D = fmaxf(D, m);
+    if (D > cutoff) { D_out = D; return 0; }
+  }
+  D_out = D;
+  if (!(D > 0.f)) return 2;
+  planes8(V.planes + gw, y, sv);                   // index inside the winning group: recomputed for the accepted points only
+  int k = 7;
+#pragma unroll
+  for (int t = 6; t >= 0; --t) k = (sv[t] == D) ? t : k;
+  fs_out = gw + k;
+  return 1;
+}
 // [region: support scan] lowest vertex index minimising q.v
 FLASH_HD int hull_support_scan(const HullView& V, F3 q) {
   float best = 3.0e38f; int vg = 0;
@@ -565,8 +605,18 @@ FLASH_HD float hull_gjk_finish(const HullView& V, F3 q, float D, int fs, F3& nrm
 
 FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
   float D = 0.f; int fs = 0;
+#ifndef FLASH_NO_PLANEHINT
+  const int hint = hull_plane_hint(V, y, cutoff, D, fs);
+  FLASH_COUNT(plane_tests, 16);
+  if (hint == 0) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }
+  if (hint == 2) {
+    FLASH_COUNT(plane_tests, V.np);
+    if (!hull_plane_scan(V, y, cutoff, D, fs)) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }
+  }
+#else
   if (!hull_plane_scan(V, y, cutoff, D, fs)) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }   // cannot be the minimum: never a candidate value
   FLASH_COUNT(plane_tests, V.np);
+#endif
   FLASH_COUNT(narrow, 1);
   if (D <= 0.f) { FLASH_COUNT(inside, 1); nrm = plane_normal(V.planes, fs); return D; }
   Simplex S;
@@ -786,6 +836,7 @@ FLASH_HD HullView hull_view(const GeoView& G, const ConvexC& C) {
   V.vz = reinterpret_cast<const float*>(G.f4 + C.off_vz); V.np = C.nplanes_pad; V.nv = C.nverts_pad;
   V.voff = reinterpret_cast<const unsigned short*>(G.u32 + C.off_voff);
   V.vlist = reinterpret_cast<const unsigned char*>(G.u32 + C.off_vlist);
+  V.pgrp = reinterpret_cast<const unsigned short*>(G.u32 + C.off_pgrp);
   return V;
 }
 

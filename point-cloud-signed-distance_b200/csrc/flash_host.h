@@ -152,6 +152,95 @@ inline void build_dirmaps(const std::vector<std::array<float, 3>>& v, int nverts
   }
 }
 
+// Plane groups for hull_plane_hint (flash_dev.h).  (1) The planes are clustered into groups of 8 by normal
+// direction (balanced k-means on the unit sphere, farthest-point seeds): `order` lists, slot by slot, the
+// plane stored there (-1 = inert padding); group g = slots [8g, 8g+8).
+inline void cluster_planes(const std::vector<std::array<double, 4>>& planes, std::vector<int>& order) {
+  const int n = (int)planes.size(), K = (n + 7) / 8;
+  std::vector<D3> nv(n), cen(K);
+  for (int f = 0; f < n; ++f) nv[f] = d3(planes[f][0], planes[f][1], planes[f][2]);
+  std::vector<int> grp(n, 0);
+  {  // farthest-point seeds
+    std::vector<double> best(n, -2.0);
+    int cur = 0;
+    for (int k = 0; k < K; ++k) {
+      cen[k] = nv[cur];
+      int nxt = 0; double lo = 3.0;
+      for (int f = 0; f < n; ++f) { best[f] = std::max(best[f], dot(nv[f], cen[k])); if (best[f] < lo) { lo = best[f]; nxt = f; } }
+      cur = nxt;
+    }
+  }
+  for (int it = 0; it < 12; ++it) {
+    // balanced assignment: (plane, centre) pairs by decreasing similarity, capacity 8 per centre
+    std::vector<std::array<double, 3>> pr;
+    pr.reserve((size_t)n * K);
+    for (int f = 0; f < n; ++f) for (int k = 0; k < K; ++k) pr.push_back({-dot(nv[f], cen[k]), (double)f, (double)k});
+    std::sort(pr.begin(), pr.end());
+    std::vector<int> cnt(K, 0); std::vector<char> done(n, 0);
+    for (auto& e : pr) {
+      const int f = (int)e[1], k = (int)e[2];
+      if (done[f] || cnt[k] >= 8) continue;
+      grp[f] = k; done[f] = 1; ++cnt[k];
+    }
+    for (int k = 0; k < K; ++k) {
+      D3 c = d3(0, 0, 0);
+      for (int f = 0; f < n; ++f) if (grp[f] == k) c = c + nv[f];
+      const double l = nrm(c);
+      if (l > 1e-12) cen[k] = c * (1.0 / l);
+    }
+  }
+  order.assign((size_t)8 * K, -1);
+  std::vector<int> fill(K, 0);
+  for (int f = 0; f < n; ++f) order[(size_t)8 * grp[f] + fill[grp[f]]++] = f;
+}
+// (2) Per direction cell: the two groups that most often hold the most-violated plane of an outside point
+// y = t d of the cell.  Along a ray the plane distances t (n_f.d) - o_f are lines in t; outside the hull
+// (t > t_exit) the most-violated plane runs through their upper envelope, which is walked exactly; every
+// plane on it is weighted by the log-length of its stretch (clipped to 20 t_exit).  5 x 5 rays per cell.
+inline void build_plane_hints(const std::vector<std::array<double, 4>>& planes, const std::vector<int>& order, std::vector<unsigned short>& pgrp) {
+  const int R = DIRMAP_R, n = (int)planes.size(), K = (int)order.size() / 8;
+  std::vector<int> grp_of(n, 0);
+  for (size_t s = 0; s < order.size(); ++s) if (order[s] >= 0) grp_of[order[s]] = (int)(s / 8);
+  pgrp.assign(DIRMAP_CELLS, 0);
+  std::vector<double> a(n), wgt(K);
+  for (int face = 0; face < 6; ++face) {
+    const int ax = face / 2; const double sg = (face % 2 == 0) ? 1.0 : -1.0;
+    const int e1 = (ax + 1) % 3, e2 = (ax + 2) % 3;
+    for (int iv = 0; iv < R; ++iv)
+      for (int iu = 0; iu < R; ++iu) {
+        std::fill(wgt.begin(), wgt.end(), 0.0);
+        for (int sv = 0; sv < 5; ++sv)
+          for (int su = 0; su < 5; ++su) {
+            double d[3];
+            d[ax] = sg; d[e1] = -1.0 + 2.0 * (iu + 0.05 + 0.225 * su) / R; d[e2] = -1.0 + 2.0 * (iv + 0.05 + 0.225 * sv) / R;
+            int f = -1; double t = 1e300;
+            for (int g = 0; g < n; ++g) {
+              a[g] = planes[g][0] * d[0] + planes[g][1] * d[1] + planes[g][2] * d[2];
+              if (a[g] > 0 && planes[g][3] / a[g] < t) { t = planes[g][3] / a[g]; f = g; }
+            }
+            if (f < 0) continue;
+            const double t_end = 20.0 * t;
+            for (int guard = 0; guard < n && t < t_end; ++guard) {
+              int nf = -1; double tn = t_end;
+              for (int g = 0; g < n; ++g) {
+                if (!(a[g] > a[f])) continue;
+                const double tc = (planes[g][3] - planes[f][3]) / (a[g] - a[f]);
+                if (tc < tn) { tn = tc; nf = g; }
+              }
+              wgt[grp_of[f]] += std::log(std::max(tn, t * (1 + 1e-12)) / t) + 1e-3;
+              if (nf < 0) break;
+              f = nf; t = std::max(tn, t);
+            }
+          }
+        int b0 = 0, b1 = -1;
+        for (int k = 1; k < K; ++k) if (wgt[k] > wgt[b0]) b0 = k;
+        for (int k = 0; k < K; ++k) if (k != b0 && wgt[k] > 0 && (b1 < 0 || wgt[k] > wgt[b1])) b1 = k;
+        if (b1 < 0) b1 = b0;
+        pgrp[(face * R + iv) * R + iu] = (unsigned short)(b0 | (b1 << 8));
+      }
+  }
+}
+
 inline void options_default(flash_options* o) {
   std::memset(o, 0, sizeof *o);
   o->abi_version = FLASHSDF_ABI_VERSION;
@@ -223,14 +312,26 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
       C.off_planes = (int)out.geo_f4.size(); C.off_tris = (int)out.geo_u32.size();
       // planes: padded to a multiple of 8 with planes that can never be the maximum, stored as pairs
       // {nx0,nx1,ny0,ny1}{nz0,nz1,-o0,-o1} for the packed-FMA scan (flash_dev.h "geometry blob layout")
-      C.nplanes_pad = (C.nplanes + 7) & ~7;
+      // slot order: groups of 8 planes with neighbouring normals (cluster_planes); padding slots are inert
+      std::vector<int> order;
+      std::vector<unsigned short> pgrp;
+      if (C.nplanes <= 8 * 255) {
+        cluster_planes(H.planes, order);
+        build_plane_hints(H.planes, order, pgrp);
+      } else {   // more groups than a byte can name: no hint (every cell points at group 0; the full scan decides)
+        for (int f = 0; f < ((C.nplanes + 7) & ~7); ++f) order.push_back(f < C.nplanes ? f : -1);
+        pgrp.assign(DIRMAP_CELLS, 0);
+      }
+      C.nplanes_pad = (int)order.size();
       {
         std::vector<std::array<float, 4>> pl;
-        for (size_t f = 0; f < H.planes.size(); ++f) {
+        uint32_t any_tri = (uint32_t)H.ptri[0][0] | ((uint32_t)H.ptri[0][1] << 8) | ((uint32_t)H.ptri[0][2] << 16);
+        for (int slot = 0; slot < C.nplanes_pad; ++slot) {
+          const int f = order[slot];
+          if (f < 0) { pl.push_back({0.f, 0.f, 0.f, -1.0e30f}); out.geo_u32.push_back(any_tri); continue; }
           pl.push_back({(float)H.planes[f][0], (float)H.planes[f][1], (float)H.planes[f][2], -(float)H.planes[f][3]});
           out.geo_u32.push_back((uint32_t)H.ptri[f][0] | ((uint32_t)H.ptri[f][1] << 8) | ((uint32_t)H.ptri[f][2] << 16));
         }
-        for (int f = C.nplanes; f < C.nplanes_pad; ++f) { pl.push_back({0.f, 0.f, 0.f, -1.0e30f}); out.geo_u32.push_back(out.geo_u32.back()); }
         for (int f = 0; f < C.nplanes_pad; f += 2) {
           out.geo_f4.push_back(F4{pl[f][0], pl[f + 1][0], pl[f][1], pl[f + 1][1]});
           out.geo_f4.push_back(F4{pl[f][2], pl[f + 1][2], pl[f][3], pl[f + 1][3]});
@@ -265,6 +366,8 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
         C.off_voff = push_bytes(dm.voff.data(), dm.voff.size() * sizeof(unsigned short));
         if (dm.vlist.empty()) dm.vlist.push_back(0);
         C.off_vlist = push_bytes(dm.vlist.data(), dm.vlist.size());
+        C.off_pgrp = push_bytes(pgrp.data(), pgrp.size() * sizeof(unsigned short));
+        C.pgrp_pad = 0;
       }
       {
         double rin = 1e300;   // the geometry origin is the vertex centroid: strictly inside
