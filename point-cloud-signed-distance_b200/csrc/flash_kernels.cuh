@@ -28,6 +28,15 @@ using namespace flashdev;
 #endif
 constexpr int BLOCK = FLASH_BLOCK;
 constexpr int WARPS = BLOCK / 32;
+// The cost kernel runs 384-thread blocks, 2 per SM (same 24 warps per SM as 3 x 256), with one block barrier per
+// batch: its ~6000-instruction straight-line body thrashes the instruction cache when the warps of an SM are
+// spread over many code positions (ncu: stall_no_instruction 2.4 per issue); two lock-stepped groups of 12
+// warps measured best (256 x 3 + barrier: 58.0 ms, 384 x 2: 56.6 ms, 768 x 1: 62.5 ms, no barrier: 62.5 ms on K5).
+#ifndef FLASH_CBLOCK
+#define FLASH_CBLOCK 384
+#endif
+constexpr int CBLOCK = FLASH_CBLOCK;
+constexpr int CWARPS = CBLOCK / 32;
 constexpr int QENT = 8;  // doubles per skin-queue entry: x y z s ginv nhx nhy nhz (slot in a side array)
 
 struct CostParams {
@@ -54,7 +63,7 @@ __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t
 struct SmemLayout {
   size_t off_hot, off_f4, off_u32, off_tab, off_tabf, off_acc, off_queue, off_qslot, total;
 };
-__host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, int tab_len, int acc_len, int tabf_len, bool grad_skins) {
+__host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, int tab_len, int acc_len, int tabf_len, bool grad_skins, int warps = WARPS) {
   SmemLayout L;
   size_t o = 0;
   L.off_hot = o; o = align16(o + sizeof(HotModel));
@@ -62,9 +71,9 @@ __host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, i
   L.off_u32 = o; o = align16(o + sizeof(uint32_t) * (size_t)geo_u32_n);
   L.off_tab = o; o = align16(o + sizeof(double) * (size_t)tab_len);
   L.off_tabf = o; o = align16(o + sizeof(float) * (size_t)(tabf_len > 0 ? tabf_len : 4));
-  L.off_acc = o; o = align16(o + sizeof(double) * (size_t)acc_len * WARPS);
-  L.off_queue = o; o = align16(o + (grad_skins ? sizeof(double) * QENT * 32 * WARPS : 0));
-  L.off_qslot = o; o = align16(o + (grad_skins ? sizeof(int) * 32 * WARPS : 0));
+  L.off_acc = o; o = align16(o + sizeof(double) * (size_t)acc_len * warps);
+  L.off_queue = o; o = align16(o + (grad_skins ? sizeof(double) * QENT * 32 * warps : 0));
+  L.off_qslot = o; o = align16(o + (grad_skins ? sizeof(int) * 32 * warps : 0));
   L.total = o;
   return L;
 }
@@ -212,45 +221,45 @@ __global__ void __launch_bounds__(32) prepare_kernel(const ModelC* __restrict__ 
 // ------------------------------------------------------------------------------------------------
 // stage model + geometry + this config's table in shared memory
 __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayout& L, const HotModel* hot, const F4* geo_f4, int nf4,
-                                            const uint32_t* geo_u32, int nu32, const double* tab, int tab_len) {
+                                            const uint32_t* geo_u32, int nu32, const double* tab, int tab_len, int nthreads = BLOCK) {
   const int tid = threadIdx.x;
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(hot);
     uint32_t* dst = reinterpret_cast<uint32_t*>(smem + L.off_hot);
-    for (int i = tid; i < (int)(sizeof(HotModel) / 4); i += BLOCK) dst[i] = src[i];
+    for (int i = tid; i < (int)(sizeof(HotModel) / 4); i += nthreads) dst[i] = src[i];
   }
   {
     const float4* src = reinterpret_cast<const float4*>(geo_f4);
     float4* dst = reinterpret_cast<float4*>(smem + L.off_f4);
-    for (int i = tid; i < nf4; i += BLOCK) dst[i] = __ldg(src + i);
+    for (int i = tid; i < nf4; i += nthreads) dst[i] = __ldg(src + i);
   }
   {
     uint32_t* dst = reinterpret_cast<uint32_t*>(smem + L.off_u32);
-    for (int i = tid; i < nu32; i += BLOCK) dst[i] = __ldg(geo_u32 + i);
+    for (int i = tid; i < nu32; i += nthreads) dst[i] = __ldg(geo_u32 + i);
   }
   {
     double* dst = reinterpret_cast<double*>(smem + L.off_tab);
-    for (int i = tid; i < tab_len; i += BLOCK) dst[i] = tab[i];
+    for (int i = tid; i < tab_len; i += nthreads) dst[i] = tab[i];
     // fp32 side table: hull transforms (culling bounds) and the skins' pre-filter tables
-    tabf_fill(*hot, tab, reinterpret_cast<float*>(smem + L.off_tabf), tid, BLOCK);
+    tabf_fill(*hot, tab, reinterpret_cast<float*>(smem + L.off_tabf), tid, nthreads);
   }
 }
 
 // GRAD: accumulate gradient terms; ARGMIN: write the argmin surface per point; DIST: write the
 // min distance per point (skin_eval entry) and skip all accumulation.
 #ifndef FLASH_MINB
-#define FLASH_MINB 3
+#define FLASH_MINB 2
 #endif
 template <bool GRAD, bool ARGMIN, bool DIST>
-__global__ void __launch_bounds__(BLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
+__global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int c = blockIdx.x;
   // every block re-derives the layout from the same numbers the host used
   const HotModel* hot_g = p.hot;
   const int tab_len = hot_g->tab_len, acc_len = hot_g->acc_len, n_convex = hot_g->n_convex;
-  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, tab_len, acc_len, hot_g->tabf_len, GRAD && hot_g->n_skins > 0);
-  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab + (size_t)c * tab_len, tab_len);
+  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, tab_len, acc_len, hot_g->tabf_len, GRAD && hot_g->n_skins > 0, CWARPS);
+  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab + (size_t)c * tab_len, tab_len, CBLOCK);
   double* acc_w = reinterpret_cast<double*>(smem + L.off_acc) + (size_t)warp * acc_len;
   if (!DIST) for (int i = lane; i < acc_len; i += 32) acc_w[i] = 0.0;
   __syncthreads();
@@ -270,7 +279,10 @@ __global__ void __launch_bounds__(BLOCK, FLASH_MINB) cost_kernel(const CostParam
   if (tile1 > p.n_pts) tile1 = p.n_pts;
   double cost_local = 0.0;
 
-  for (long long base = tile0; base < tile1; base += BLOCK) {
+  for (long long base = tile0; base < tile1; base += CBLOCK) {
+#ifndef FLASH_NO_BATCH_SYNC
+    __syncthreads();   // keep the block's warps in the same code region (instruction-cache locality, see CBLOCK)
+#endif
     const long long i = base + tid;
     const bool valid = i < tile1;
     PointEval e;
@@ -382,10 +394,10 @@ __global__ void __launch_bounds__(BLOCK, FLASH_MINB) cost_kernel(const CostParam
   __syncthreads();
   const double* acc_all = reinterpret_cast<const double*>(smem + L.off_acc);
   const int nacc = GRAD ? acc_len : 1;
-  for (int l = tid; l < nacc; l += BLOCK) {
+  for (int l = tid; l < nacc; l += CBLOCK) {
     double s = 0;
 #pragma unroll
-    for (int w = 0; w < WARPS; ++w) s += acc_all[(size_t)w * acc_len + l];
+    for (int w = 0; w < CWARPS; ++w) s += acc_all[(size_t)w * acc_len + l];
     if (s != 0.0) atomicAdd(p.acc + (size_t)c * acc_len + l, s);
   }
 }

@@ -143,7 +143,7 @@ int ensure_batch(flash_ctx* ctx, int C) {
 
 SmemLayout cost_layout(const flash_ctx* ctx, bool grad) {
   const ModelC& M = ctx->hm.M;
-  return smem_layout(M.geo_f4, M.geo_u32, M.tab_len, M.acc_len, M.tabf_len, grad && M.n_skins > 0);
+  return smem_layout(M.geo_f4, M.geo_u32, M.tab_len, M.acc_len, M.tabf_len, grad && M.n_skins > 0, CWARPS);
 }
 
 template <bool G, bool A, bool D>
@@ -151,7 +151,7 @@ int launch_cost_t(flash_ctx* ctx, const CostParams& p, int C, int tiles, size_t 
   auto k = cost_kernel<G, A, D>;
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)C, (unsigned)tiles);
-  k<<<grid, BLOCK, smem, ctx->stream>>>(p);
+  k<<<grid, CBLOCK, smem, ctx->stream>>>(p);
   CU(cudaGetLastError());
   ctx->launches++; ctx->last.launches++;
   return 0;
@@ -161,9 +161,9 @@ int launch_cost_t(flash_ctx* ctx, const CostParams& p, int C, int tiles, size_t 
 int choose_tile(const flash_ctx* ctx, long long n, int C) {
   const long long target_blocks = (long long)ctx->sm_count * 2 * 4;
   long long ppb = (n * C + target_blocks - 1) / target_blocks;
-  ppb = ((ppb + BLOCK - 1) / BLOCK) * BLOCK;
-  if (ppb < BLOCK) ppb = BLOCK;
-  static const long long max_tile = [] { const char* e = getenv("FLASHSDF_TILE"); long long v = e ? atoll(e) : 0; return v >= BLOCK ? v : 8192ll; }();
+  ppb = ((ppb + CBLOCK - 1) / CBLOCK) * CBLOCK;
+  if (ppb < CBLOCK) ppb = CBLOCK;
+  static const long long max_tile = [] { const char* e = getenv("FLASHSDF_TILE"); long long v = e ? atoll(e) : 0; return v >= CBLOCK ? v : (8192ll / CBLOCK) * CBLOCK; }();
   if (ppb > max_tile) ppb = max_tile;
   while ((n + ppb - 1) / ppb > 65535) ppb *= 2;
   return (int)ppb;

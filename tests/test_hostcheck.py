@@ -185,3 +185,33 @@ def test_support_direction_map_is_exact():
         im, isc, vm, vs = h.support(j, q)
         assert np.array_equal(vm, vs), (j, np.abs(vm - vs).max())
         assert (im == isc).mean() > 0.999      # differ only on exact ties
+
+
+def test_plane_hint_map_never_changes_the_distance():
+    """hull_plane_hint (flash_dev.h) only picks GJK's start face and rejects by a valid lower bound; the
+    distance must equal the oracle's brute-force point-polytope distance everywhere: hugging the surfaces
+    (ray-cast hits pushed out / in by 1 mm and 1 cm), mid range, and far outside the scene."""
+    rng = np.random.default_rng(12)
+    m = flash.models.irb_and_squishable()
+    h, o = hl.HostCheck(m), ol.Oracle(m)
+    x = GOLD["irb_and_squishable/x"]
+    base = rng.uniform([-0.8, -0.8, -0.3], [1.0, 0.8, 1.2], (6000, 3))
+    d0, _ = o.skin(x, base, mode=ol.BRUTE, argmin=True)
+    # walk the points onto the zero level set along a finite-difference gradient, then offset them
+    eps = 1e-4
+    g = np.stack([(o.skin(x, base + eps * e, mode=ol.BRUTE) - o.skin(x, base - eps * e, mode=ol.BRUTE)) / (2 * eps) for e in np.eye(3)], 1)
+    g /= np.maximum(np.linalg.norm(g, axis=1, keepdims=True), 1e-9)
+    near = np.concatenate([base - (d0 - off)[:, None] * g for off in (1e-3, -1e-3, 1e-2, -1e-2)])
+    far = rng.uniform(-1, 1, (6000, 3)) * np.array([8.0, 8.0, 8.0])
+    pts = np.concatenate([near, base, far]).astype(np.float32).astype(np.float64)
+    tab, _ = h.prepare(x)
+    hl.counters()
+    _, dist, arg = h.accumulate(tab, pts)
+    cn = hl.counters()
+    do, ao = o.skin(x, pts, mode=ol.BRUTE, argmin=True)
+    assert np.abs(dist - do).max() < 2e-6 * (1 + np.abs(do).max())
+    per = o.surfaces(x, pts, mode=ol.BRUTE)
+    for i in np.nonzero(arg != ao)[0]:
+        s = np.sort(per[i]); assert s[1] - s[0] < 4e-6
+    # and it does its job: far fewer plane tests than one full 100-plane scan per narrow-phase evaluation
+    assert cn["plane_tests"] < 45 * cn["narrow"]
