@@ -443,6 +443,14 @@ def _time_batches(flash, L, m, clouds, X, steps, hits):
     pX, pc, pg = X.ctypes.data_as(c_double_p), cost.ctypes.data_as(c_double_p), grad.ctypes.data_as(c_double_p)
     m.check(L.flash_profiling(ctx, 1))
     tm = Timing()
+    # frames live in pinned host memory, as the K5 leg's points do (bench contract: H2D from pinned memory)
+    keep = []
+    pinned = []
+    for p in clouds:
+        t = torch.empty(p.shape, dtype=torch.float64, pin_memory=True)
+        a = t.numpy(); a[:] = p
+        keep.append(t); pinned.append(a)
+    clouds = pinned
     def run():
         k_ms = 0.0
         for p in clouds:

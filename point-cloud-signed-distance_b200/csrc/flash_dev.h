@@ -109,6 +109,17 @@ FLASH_HD int aux_P(const ModelC& M, int b) { return 12 * M.n_bodies + 12 * b; }
 FLASH_HD int aux_qnorm(const ModelC& M, int b) { return 24 * M.n_bodies + b; }
 FLASH_HD int aux_skin0(const ModelC& M) { return 25 * M.n_bodies; }
 
+// unroll factor of the per-centre skin loops (the cost kernel is instruction-cache sensitive: flash_kernels.cuh CBLOCK)
+#define FLASH_PRAGMA_(x) _Pragma(#x)
+#define FLASH_PRAGMA(x) FLASH_PRAGMA_(x)
+#ifndef FLASH_SKIN_UNROLL
+#define FLASH_SKIN_UNROLL 2   // K5: 1 -> 57.2 ms, 2 -> 56.3 ms, compiler's choice (4) -> 56.7 ms
+#endif
+#if defined(__CUDA_ARCH__)
+#define FLASH_SKIN_LOOP FLASH_PRAGMA(unroll FLASH_SKIN_UNROLL)
+#else
+#define FLASH_SKIN_LOOP
+#endif
 // approximate 1/sqrt(x) for normal x > 0: one MUFU.RSQ (rel. error 2^-22), no denormal fix-up code
 FLASH_HD float rsqrt_fast(float x) {
 #ifdef __CUDA_ARCH__
@@ -721,6 +732,7 @@ FLASH_HD SkinEval skin_eval(const double* __restrict__ c, const double* __restri
   FLASH_COUNT(skin64, 1);
   double f = w[n] + w[n + 1] * px + w[n + 2] * py + w[n + 3] * pz;
   double gx = w[n + 1], gy = w[n + 2], gz = w[n + 3];
+FLASH_SKIN_LOOP
   for (int i = 0; i < n; ++i) {
     double ux = px - c[3 * i], uy = py - c[3 * i + 1], uz = pz - c[3 * i + 2];
     double r2 = fma(ux, ux, fma(uy, uy, uz * uz));
@@ -755,6 +767,7 @@ struct SkinBound { float lo, hi; };
 FLASH_HD SkinBound skin_bound_f32(const float* __restrict__ cw, int n, bool normalize, float px, float py, float pz) {
   const float p1 = fabsf(px) + fabsf(py) + fabsf(pz);
   float f3 = 0.f, gx = 0.f, gy = 0.f, gz = 0.f, A = 0.f, B = 0.f;   // f3 = 3 * sum w r^3
+FLASH_SKIN_LOOP
   for (int i = 0; i < n; ++i) {
     const F4 cc = reinterpret_cast<const F4*>(cw)[i];   // 16-byte aligned: one LDS.128
     const float ux = px - cc.x, uy = py - cc.y, uz = pz - cc.z, w3 = cc.w;

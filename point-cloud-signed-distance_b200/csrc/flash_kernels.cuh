@@ -7,7 +7,7 @@
 //   epilogue_kernel  adjoint RBF solve + wrench -> joint-space gradient (replaces ForwardDiff's
 //                    ceil(nx/10) dual passes with one pass)
 //   raycast kernels  batched ray marching of the same field (row A9) + order-preserving compaction
-//   gd_step_kernel   NaiveSolver update for the on-device estimate_state loop (row F1)
+//   iterate_kernel   epilogue + NaiveSolver update + next prepare for the on-device estimate_state loop (row F1)
 //   grid kernels     SDF grid baking / error sampling for FLASH_SDF_GRID
 //
 // Design notes (B200): tensor cores are not used (no dense contraction on this path).  Points are
@@ -103,25 +103,25 @@ __host__ __device__ inline size_t prepare_smem_doubles(const ModelC& M) {
   size_t need = 8;
   for (int k = 0; k < M.n_skins; ++k) {
     const size_t m = (size_t)M.skin[k].M, n = (size_t)M.skin[k].npts;
-    const size_t v = m * m + 3 * n + 2 * m;
+    const size_t v = m * m + 3 * n + 3 * m + 4;   // A, centres, pivots, pivot row, pivot column, 2 scratch
     if (v > need) need = v;
   }
   const size_t fk = 25 * MAX_BODIES + 64 + (MAX_BODIES * sizeof(BodyC) + 7) / 8;   // FK staging (reused by the skins afterwards)
   return need > fk ? need : fk;
 }
-__global__ void __launch_bounds__(32) prepare_kernel(const ModelC* __restrict__ Mp, const double* __restrict__ X, double* __restrict__ tab_all,
-                                                      double* __restrict__ aux_all, double* __restrict__ acc_all, int* __restrict__ status) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  double* sm = reinterpret_cast<double*>(smem);
-  const ModelC& M = *Mp;
-  const int c = blockIdx.x, lane = threadIdx.x;
-  const double* x = X + (size_t)c * M.nx;
-  double* tab = tab_all + (size_t)c * M.tab_len;
-  double* aux = aux_all + (size_t)c * M.aux_len;
-  if (acc_all) for (int i = lane; i < M.acc_len; i += 32) acc_all[(size_t)c * M.acc_len + i] = 0.0;   // replaces a memset node
+// One BLOCK of PREP_T threads prepares one config: x -> tab, aux; zeroes acc (may be null);
+// sm = prepare_smem_doubles() doubles.  The single-warp version spent 18.5 of its 26.5 us in the Gauss-Jordan
+// inversion of the 17 x 17 system (clock64 stamps, K3) and 5.5 us in 17 serial fp64 square roots per lane;
+// here every matrix element has its own thread: per pivot one warp-shuffle search, the pivot row (scaled) and
+// column are copied aside, then all elements update at once -- the same fma per element as before, so the
+// inverse is bit-identical.
+constexpr int PREP_T = 320;
+__device__ __forceinline__ void prepare_block(const ModelC& M, const double* x, double* tab, double* aux, double* acc, int* status, double* sm, int tid, int T) {
+  const int lane = tid & 31, warp = tid >> 5;
+  if (acc) for (int i = tid; i < M.acc_len; i += T) acc[i] = 0.0;   // replaces a memset node
   {
-    // forward kinematics is a serial chain: run it on lane 0 out of shared memory (bodies, x and the
-    // transforms staged by all lanes) instead of chasing dependent global loads
+    // forward kinematics is a serial chain: run it on thread 0 out of shared memory (bodies, x and the
+    // transforms staged by all threads) instead of chasing dependent global loads
     const int nb = M.n_bodies;
     double* s_aux = sm;                                       // [25 nb]
     double* s_x = s_aux + 25 * MAX_BODIES;                    // [nq <= 64]
@@ -129,93 +129,105 @@ __global__ void __launch_bounds__(32) prepare_kernel(const ModelC* __restrict__ 
     {
       const uint32_t* src = reinterpret_cast<const uint32_t*>(M.body);
       uint32_t* dst = reinterpret_cast<uint32_t*>(s_body);
-      for (int i = lane; i < (int)(nb * sizeof(BodyC) / 4); i += 32) dst[i] = src[i];
-      for (int i = lane; i < M.nq; i += 32) s_x[i] = x[i];
+      for (int i = tid; i < (int)(nb * sizeof(BodyC) / 4); i += T) dst[i] = src[i];
+      for (int i = tid; i < M.nq; i += T) s_x[i] = x[i];
     }
-    __syncwarp();
-    if (lane == 0) fk_bodies(s_body, nb, M.nq, s_x, s_aux);
-    __syncwarp();
-    for (int i = lane; i < 25 * nb; i += 32) aux[i] = s_aux[i];
-    __syncwarp();
+    __syncthreads();
+    if (tid == 0) fk_bodies(s_body, nb, M.nq, s_x, s_aux);
+    __syncthreads();
+    for (int i = tid; i < 25 * nb; i += T) aux[i] = s_aux[i];
+    __syncthreads();
   }
-  for (int j = lane; j < M.n_convex; j += 32) prepare_convex_one(M, j, aux, tab);
+  for (int j = tid; j < M.n_convex; j += T) prepare_convex_one(M, j, aux, tab);
   for (int k = 0; k < M.n_skins; ++k) {
     const SkinC& K = M.skin[k];
     const int n = K.npts, Mm = K.M;
     double* A = sm;                 // [Mm][Mm]
     double* cs = A + Mm * Mm;       // [n][3]
     double* piv = cs + 3 * n;       // [Mm]
-    for (int i = lane; i < n; i += 32) {
+    double* prow = piv + Mm;        // [Mm] pivot row, scaled
+    double* pcol = prow + Mm;       // [Mm] pivot column
+    double* scr = pcol + Mm;        // [2] pivot row index, |pivot|
+    for (int i = tid; i < n; i += T) {
       const D3 p = skin_centre_one(M, K, i, x, aux);
       cs[3 * i] = p.x; cs[3 * i + 1] = p.y; cs[3 * i + 2] = p.z;
       double* ct = tab + K.tab_off + 3 * i;
       ct[0] = p.x; ct[1] = p.y; ct[2] = p.z;
     }
-    __syncwarp();
-    for (int i = lane; i < Mm; i += 32)       // row i of [Phi Q; Q^T 0]
-      for (int j = 0; j < Mm; ++j) {
-        double v = 0;
-        if (i < n && j < n) {
-          const double dx = cs[3 * i] - cs[3 * j], dy = cs[3 * i + 1] - cs[3 * j + 1], dz = cs[3 * i + 2] - cs[3 * j + 2];
-          const double r2 = dx * dx + dy * dy + dz * dz;
-          v = r2 * sqrt(r2);
-        } else if (i < n) v = (j == n) ? 1.0 : cs[3 * i + (j - n - 1)];
-        else if (j < n) v = (i == n) ? 1.0 : cs[3 * j + (i - n - 1)];
-        A[i * Mm + j] = v;
-      }
-    __syncwarp();
+    __syncthreads();
+    for (int e = tid; e < Mm * Mm; e += T) {       // [Phi Q; Q^T 0]
+      const int i = e / Mm, j = e - i * Mm;
+      double v = 0;
+      if (i < n && j < n) {
+        const double dx = cs[3 * i] - cs[3 * j], dy = cs[3 * i + 1] - cs[3 * j + 1], dz = cs[3 * i + 2] - cs[3 * j + 2];
+        const double r2 = dx * dx + dy * dy + dz * dz;
+        v = r2 * sqrt(r2);
+      } else if (i < n) v = (j == n) ? 1.0 : cs[3 * i + (j - n - 1)];
+      else if (j < n) v = (i == n) ? 1.0 : cs[3 * j + (i - n - 1)];
+      A[e] = v;
+    }
+    __syncthreads();
     bool ok = true;
     for (int kk = 0; kk < Mm; ++kk) {
-      // pivot: largest |A[i][kk]|, i >= kk (lowest row on ties, as the serial factorisation)
-      double best = -1.0; int bi = kk;
-      for (int i = kk + lane; i < Mm; i += 32) { const double v = fabs(A[i * Mm + kk]); if (v > best) { best = v; bi = i; } }
+      if (warp == 0) {
+        // pivot: largest |A[i][kk]|, i >= kk (lowest row on ties, as the serial factorisation)
+        double best = -1.0; int bi = kk;
+        for (int i = kk + lane; i < Mm; i += 32) { const double v = fabs(A[i * Mm + kk]); if (v > best) { best = v; bi = i; } }
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const double ob = __shfl_xor_sync(0xffffffffu, best, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
-      }
-      if (!(best > 0.0)) ok = false;
-      if (bi != kk) for (int j = lane; j < Mm; j += 32) { const double t = A[kk * Mm + j]; A[kk * Mm + j] = A[bi * Mm + j]; A[bi * Mm + j] = t; }
-      if (lane == 0) piv[kk] = (double)bi;
-      __syncwarp();
-      const double inv = 1.0 / A[kk * Mm + kk];
-      __syncwarp();
-      for (int j = lane; j < Mm; j += 32) A[kk * Mm + j] = (j == kk) ? inv : A[kk * Mm + j] * inv;
-      __syncwarp();
-      for (int i = lane; i < Mm; i += 32) {
-        if (i == kk) continue;
-        double* Ai = A + i * Mm;
-        const double* Ak = A + kk * Mm;
-        const double f = Ai[kk];
-        int j = 0;
-        for (; j + 4 <= Mm; j += 4) {   // loads first, then stores: the rows never alias (i != kk)
-          const double a0 = Ai[j], a1 = Ai[j + 1], a2 = Ai[j + 2], a3 = Ai[j + 3];
-          const double p0 = Ak[j], p1 = Ak[j + 1], p2 = Ak[j + 2], p3 = Ak[j + 3];
-          Ai[j] = fma(-f, p0, a0); Ai[j + 1] = fma(-f, p1, a1); Ai[j + 2] = fma(-f, p2, a2); Ai[j + 3] = fma(-f, p3, a3);
+        for (int o = 16; o > 0; o >>= 1) {
+          const double ob = __shfl_xor_sync(0xffffffffu, best, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+          if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
         }
-        for (; j < Mm; ++j) Ai[j] = fma(-f, Ak[j], Ai[j]);
-        Ai[kk] = -f * inv;
+        if (lane == 0) { scr[0] = (double)bi; scr[1] = best; piv[kk] = (double)bi; }
       }
-      __syncwarp();
+      __syncthreads();
+      const int bi = (int)scr[0];
+      if (!(scr[1] > 0.0)) ok = false;
+      if (bi != kk) {   // block-uniform
+        for (int j = tid; j < Mm; j += T) { const double t = A[kk * Mm + j]; A[kk * Mm + j] = A[bi * Mm + j]; A[bi * Mm + j] = t; }
+        __syncthreads();
+      }
+      {
+        const double inv = 1.0 / A[kk * Mm + kk];
+        for (int j = tid; j < Mm; j += T) { prow[j] = (j == kk) ? inv : A[kk * Mm + j] * inv; pcol[j] = A[j * Mm + kk]; }
+        __syncthreads();
+        for (int e = tid; e < Mm * Mm; e += T) {
+          const int i = e / Mm, j = e - i * Mm;
+          const double f = pcol[i];
+          A[e] = (i == kk) ? prow[j] : ((j == kk) ? -f * inv : fma(-f, prow[j], A[e]));
+        }
+        __syncthreads();
+      }
     }
     for (int kk = Mm - 1; kk >= 0; --kk) {      // undo the row exchanges on the columns
       const int pv = (int)piv[kk];
-      if (pv != kk) for (int i = lane; i < Mm; i += 32) { const double t = A[i * Mm + kk]; A[i * Mm + kk] = A[i * Mm + pv]; A[i * Mm + pv] = t; }
-      __syncwarp();
+      if (pv != kk) {   // block-uniform
+        for (int i = tid; i < Mm; i += T) { const double t = A[i * Mm + kk]; A[i * Mm + kk] = A[i * Mm + pv]; A[i * Mm + pv] = t; }
+        __syncthreads();
+      }
     }
-    if (!ok && lane == 0) atomicExch(status, 1);   // singular RBF system (coincident control points)
+    if (!ok && tid == 0) atomicExch(status, 1);   // singular RBF system (coincident control points)
     // weights: rhs = 0 (surface), -1 (skeleton) (src/Flash.jl:211)  ->  w = -sum_{skeleton j} Ainv[:, j]
     double* w = tab + K.tab_off + 3 * n;
-    for (int i = lane; i < Mm; i += 32) {
+    for (int i = tid; i < Mm; i += T) {
       double sacc = 0;
       for (int j = K.nsurf; j < n; ++j) sacc -= A[i * Mm + j];
       w[i] = sacc;
     }
-    if (Mm != n + 4) for (int i = lane; i < 3; i += 32) w[n + 1 + i] = 0.0;
+    if (Mm != n + 4) for (int i = tid; i < 3; i += T) w[n + 1 + i] = 0.0;
     double* Ainv = aux + aux_skin0(M) + K.aux_off;
-    for (int e = lane; e < Mm * Mm; e += 32) Ainv[e] = A[e];
-    __syncwarp();
+    for (int e = tid; e < Mm * Mm; e += T) Ainv[e] = A[e];
+    __syncthreads();
   }
+}
+
+__global__ void __launch_bounds__(PREP_T) prepare_kernel(const ModelC* __restrict__ Mp, const double* __restrict__ X, double* __restrict__ tab_all,
+                                                      double* __restrict__ aux_all, double* __restrict__ acc_all, int* __restrict__ status) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const ModelC& M = *Mp;
+  const int c = blockIdx.x;
+  prepare_block(M, X + (size_t)c * M.nx, tab_all + (size_t)c * M.tab_len, aux_all + (size_t)c * M.aux_len,
+                acc_all ? acc_all + (size_t)c * M.acc_len : nullptr, status, reinterpret_cast<double*>(smem), threadIdx.x, PREP_T);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -281,6 +293,12 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
 
   for (long long base = tile0; base < tile1; base += CBLOCK) {
 #ifndef FLASH_NO_BATCH_SYNC
+#ifndef FLASH_SYNC_EVERY
+#define FLASH_SYNC_EVERY 2   // K5: every batch 56.2 ms, every 2nd 55.4, every 3rd 55.4
+#endif
+#if FLASH_SYNC_EVERY > 1
+    if ((((base - tile0) / CBLOCK) % FLASH_SYNC_EVERY) == 0)
+#endif
     __syncthreads();   // keep the block's warps in the same code region (instruction-cache locality, see CBLOCK)
 #endif
     const long long i = base + tid;
@@ -416,21 +434,13 @@ __host__ __device__ inline size_t epilogue_smem_doubles(const ModelC& M) {
   }
   return need + 6 * MAX_BODIES;
 }
-__global__ void __launch_bounds__(32) epilogue_kernel(const ModelC* __restrict__ Mp, const double* __restrict__ X, const double* __restrict__ tab_all,
-                                                       const double* __restrict__ aux_all, const double* __restrict__ acc_all, int C, double w_def,
-                                                       double* __restrict__ cost, double* __restrict__ grad_all /* may be null */) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  double* F = reinterpret_cast<double*>(smem);   // [nb][3]
+// one warp finishes one config: acc (summed over points and ranks) -> *cost_c and grad (may be null);
+// sm = epilogue_smem_doubles() doubles
+__device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, const double* tab, const double* aux, const double* acc, double w_def,
+                                              double* cost_c, double* grad, double* sm, int lane) {
+  double* F = sm;                                // [nb][3]
   double* Mo = F + 3 * MAX_BODIES;               // [nb][3]
   double* sk = Mo + 3 * MAX_BODIES;              // per-skin scratch
-  const ModelC& M = *Mp;
-  const int c = blockIdx.x, lane = threadIdx.x;
-  if (c >= C) return;
-  const double* x = X + (size_t)c * M.nx;
-  const double* tab = tab_all + (size_t)c * M.tab_len;
-  const double* aux = aux_all + (size_t)c * M.aux_len;
-  const double* acc = acc_all + (size_t)c * M.acc_len;
-  double* grad = grad_all ? grad_all + (size_t)c * M.nx : nullptr;
   const int nb = M.n_bodies;
   if (grad) {
     for (int i = lane; i < 6 * MAX_BODIES; i += 32) F[i] = 0.0;
@@ -530,7 +540,17 @@ __global__ void __launch_bounds__(32) epilogue_kernel(const ModelC* __restrict__
   double reg = 0;
   for (int k = M.nq + lane; k < M.nx; k += 32) { reg = fma(x[k], x[k], reg); if (grad) grad[k] += 2.0 * w_def * x[k]; }
   reg = warp_sum(reg);
-  if (lane == 0) cost[c] = acc[0] + w_def * reg;
+  if (lane == 0) *cost_c = acc[0] + w_def * reg;
+}
+__global__ void __launch_bounds__(32) epilogue_kernel(const ModelC* __restrict__ Mp, const double* __restrict__ X, const double* __restrict__ tab_all,
+                                                       const double* __restrict__ aux_all, const double* __restrict__ acc_all, int C, double w_def,
+                                                       double* __restrict__ cost, double* __restrict__ grad_all /* may be null */) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const ModelC& M = *Mp;
+  const int c = blockIdx.x;
+  if (c >= C) return;
+  epilogue_warp(M, X + (size_t)c * M.nx, tab_all + (size_t)c * M.tab_len, aux_all + (size_t)c * M.aux_len, acc_all + (size_t)c * M.acc_len, w_def,
+                cost + c, grad_all ? grad_all + (size_t)c * M.nx : nullptr, reinterpret_cast<double*>(smem), threadIdx.x);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -797,30 +817,46 @@ __global__ void __launch_bounds__(BLOCK) compact_hits_kernel(const double* __res
 }
 
 // ------------------------------------------------------------------------------------------------
-// NaiveSolver step (see flash_estimate_state in flashsdf.h).  One thread block per config.
-__global__ void __launch_bounds__(128) gd_step_kernel(double* __restrict__ X, const double* __restrict__ grad, int nx, double inv_n, double rate, double max_step,
-                                                       double tol, const double* __restrict__ divisors, int* __restrict__ done, int* __restrict__ iters) {
-  __shared__ double red[128];
-  const int c = blockIdx.x, tid = threadIdx.x;
-  if (done[c]) return;
-  double* x = X + (size_t)c * nx;
-  const double* g = grad + (size_t)c * nx;
-  double gn = 0, sn = 0;
-  for (int k = tid; k < nx; k += blockDim.x) {
-    const double gk = g[k] * inv_n;
-    const double st = -rate * gk / (divisors ? divisors[k] : 1.0);
-    gn += gk * gk; sn += st * st;
+// Tracking iteration tail in ONE launch, one block per config: epilogue (cost + gradient of the pass the cost
+// kernel just finished; warp 0) -> NaiveSolver step (flash_estimate_state in flashsdf.h; warp 0) -> prepare of
+// the NEXT pass (FK, RBF system, zeroed accumulators; all PREP_T threads).  A gradient-descent iteration is then
+// 2 launches (cost_kernel, this) instead of 4; the three single-warp kernels it replaces were 51 of the 68 us
+// of an iteration on K3.
+__global__ void __launch_bounds__(PREP_T) iterate_kernel(const ModelC* Mp, double* X, double* tab_all, double* aux_all, double* acc_all, int C, double w_def,
+                                                          double* cost, double* grad_all, double inv_n, double rate, double max_step, double tol,
+                                                          const double* divisors, int* done, int* iters, int* status) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  double* sm = reinterpret_cast<double*>(smem);
+  const ModelC& M = *Mp;
+  const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+  if (c >= C) return;
+  double* x = X + (size_t)c * M.nx;
+  double* tab = tab_all + (size_t)c * M.tab_len;
+  double* aux = aux_all + (size_t)c * M.aux_len;
+  double* acc = acc_all + (size_t)c * M.acc_len;
+  double* g = grad_all + (size_t)c * M.nx;
+  if (tid < 32) {
+    epilogue_warp(M, x, tab, aux, acc, w_def, cost + c, g, sm, lane);
+    __syncwarp();
+    if (!done[c]) {
+      const int nx = M.nx;
+      double gn = 0, sn = 0;
+      for (int k = lane; k < nx; k += 32) {
+        const double gk = g[k] * inv_n;
+        const double st = -rate * gk / (divisors ? divisors[k] : 1.0);
+        gn += gk * gk; sn += st * st;
+      }
+      gn = warp_sum(gn); sn = sqrt(warp_sum(sn));
+      if (tol > 0 && sqrt(gn) < tol) { if (lane == 0) done[c] = 1; }
+      else {
+        const double sc = sn > max_step ? max_step / sn : 1.0;
+        for (int k = lane; k < nx; k += 32) x[k] += sc * (-rate * g[k] * inv_n / (divisors ? divisors[k] : 1.0));
+        if (lane == 0) iters[c] += 1;
+      }
+    }
   }
-  red[tid] = gn; __syncthreads();
-  for (int o = 64; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
-  gn = red[0]; __syncthreads();
-  red[tid] = sn; __syncthreads();
-  for (int o = 64; o > 0; o >>= 1) { if (tid < o) red[tid] += red[tid + o]; __syncthreads(); }
-  sn = sqrt(red[0]);
-  if (tol > 0 && sqrt(gn) < tol) { if (tid == 0) done[c] = 1; return; }
-  const double sc = sn > max_step ? max_step / sn : 1.0;
-  for (int k = tid; k < nx; k += blockDim.x) x[k] += sc * (-rate * g[k] * inv_n / (divisors ? divisors[k] : 1.0));
-  if (tid == 0) iters[c] += 1;
+  __syncthreads();   // x, and the end of every read of tab / aux / acc, are visible to the whole block
+  prepare_block(M, x, tab, aux, acc, status, sm, tid, PREP_T);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -189,7 +189,7 @@ int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin) {
 int run_prepare(flash_ctx* ctx, int C, bool zero_acc = false) {
   const size_t smem = prepare_smem_doubles(ctx->hm.M) * sizeof(double);
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(prepare_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  prepare_kernel<<<C, 32, smem, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, zero_acc ? ctx->d_acc : nullptr, ctx->d_status);
+  prepare_kernel<<<C, PREP_T, smem, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, zero_acc ? ctx->d_acc : nullptr, ctx->d_status);
   CU(cudaGetLastError());
   ctx->launches++; ctx->last.launches++;
   return 0;
@@ -602,14 +602,21 @@ int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solve
   const bool prof = ctx->profiling; ctx->profiling = false;
   cudaEvent_t e0 = ctx->ev[0], e1 = ctx->ev[4];
   if (prof) CU(cudaEventRecord(e0, ctx->stream));
+  // per iteration: cost_kernel -> [allreduce] -> iterate_kernel (epilogue + NaiveSolver step + prepare of the next pass)
+  const size_t it_smem = std::max(prepare_smem_doubles(M), epilogue_smem_doubles(M)) * sizeof(double);
+  if (it_smem > 48 * 1024) CU(cudaFuncSetAttribute(iterate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)it_smem));
+  if ((rc = run_prepare(ctx, C, true))) { ctx->profiling = prof; return rc; }
   for (int it = 0; it < sp->iteration_limit; ++it) {
-    if ((rc = pipeline(ctx, C, sp->deformation_cost_weight, true, nullptr))) { ctx->profiling = prof; return rc; }
-    gd_step_kernel<<<C, 128, 0, ctx->stream>>>(ctx->d_X, ctx->d_grad, M.nx, n_total > 0 ? 1.0 / n_total : 0.0, sp->rate, sp->max_step,
-                                               sp->gradient_convergence_tolerance, divisors ? ctx->d_div : nullptr, ctx->d_done, ctx->d_iters);
+    if ((rc = run_cost(ctx, C, true, nullptr)) || (rc = run_allreduce(ctx, C))) { ctx->profiling = prof; return rc; }
+    iterate_kernel<<<C, PREP_T, it_smem, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, C, sp->deformation_cost_weight, ctx->d_cost,
+                                                    ctx->d_grad, n_total > 0 ? 1.0 / n_total : 0.0, sp->rate, sp->max_step, sp->gradient_convergence_tolerance,
+                                                    divisors ? ctx->d_div : nullptr, ctx->d_done, ctx->d_iters, ctx->d_status);
     CU(cudaGetLastError());
     ctx->launches++; ctx->last.launches++;
   }
-  if (cost_out) { if ((rc = pipeline(ctx, C, sp->deformation_cost_weight, false, nullptr))) { ctx->profiling = prof; return rc; } }
+  if (cost_out) {   // cost at the final state: the last iterate_kernel already prepared it
+    if ((rc = run_cost(ctx, C, false, nullptr)) || (rc = run_allreduce(ctx, C)) || (rc = run_epilogue(ctx, C, sp->deformation_cost_weight, false))) { ctx->profiling = prof; return rc; }
+  }
   if (prof) CU(cudaEventRecord(e1, ctx->stream));
   ctx->profiling = prof;
   double* h_cost = ctx->h_pin + nX;
