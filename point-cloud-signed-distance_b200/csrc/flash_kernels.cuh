@@ -155,8 +155,9 @@ __device__ __forceinline__ void prepare_block(const ModelC& M, const double* x, 
       ct[0] = p.x; ct[1] = p.y; ct[2] = p.z;
     }
     __syncthreads();
-    for (int e = tid; e < Mm * Mm; e += T) {       // [Phi Q; Q^T 0]
-      const int i = e / Mm, j = e - i * Mm;
+    const int i0 = tid / Mm, j0 = tid - i0 * Mm, di = T / Mm, dj = T - di * Mm;   // element (i, j) of this thread, and its stride
+    for (int e = tid, i = i0, j = j0; e < Mm * Mm; e += T, i += di, j += dj) {       // [Phi Q; Q^T 0]
+      if (j >= Mm) { j -= Mm; ++i; }
       double v = 0;
       if (i < n && j < n) {
         const double dx = cs[3 * i] - cs[3 * j], dy = cs[3 * i + 1] - cs[3 * j + 1], dz = cs[3 * i + 2] - cs[3 * j + 2];
@@ -191,8 +192,8 @@ __device__ __forceinline__ void prepare_block(const ModelC& M, const double* x, 
         const double inv = 1.0 / A[kk * Mm + kk];
         for (int j = tid; j < Mm; j += T) { prow[j] = (j == kk) ? inv : A[kk * Mm + j] * inv; pcol[j] = A[j * Mm + kk]; }
         __syncthreads();
-        for (int e = tid; e < Mm * Mm; e += T) {
-          const int i = e / Mm, j = e - i * Mm;
+        for (int e = tid, i = i0, j = j0; e < Mm * Mm; e += T, i += di, j += dj) {
+          if (j >= Mm) { j -= Mm; ++i; }
           const double f = pcol[i];
           A[e] = (i == kk) ? prow[j] : ((j == kk) ? -f * inv : fma(-f, prow[j], A[e]));
         }
@@ -483,26 +484,40 @@ __device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, 
       __syncwarp();
       const D3 la = Mm == n + 4 ? d3(lam[n + 1], lam[n + 2], lam[n + 3]) : d3(0, 0, 0);
       const D3 av = d3(w[n + 1], w[n + 2], w[n + 3]);
-      for (int i = lane; i < n; i += 32) {
-        const D3 ci = d3(cc[3 * i], cc[3 * i + 1], cc[3 * i + 2]);
-        D3 Gi = d3(gC[3 * i], gC[3 * i + 1], gC[3 * i + 2]);
-        for (int j = 0; j < n; ++j) {
-          const D3 u = ci - d3(cc[3 * j], cc[3 * j + 1], cc[3 * j + 2]);
-          const double r = sqrt(dot(u, u));
-          Gi = Gi - u * (3.0 * r * (lam[i] * w[j] + lam[j] * w[i]));
+      for (int i0 = 0; i0 < n; i0 += 32) {          // warp-uniform trip count: the wrench sums below are warp reductions
+        const int i = i0 + lane;
+        const bool on = i < n;
+        D3 ci = d3(0, 0, 0), Gi = d3(0, 0, 0);
+        int b = -1;
+        if (on) {
+          ci = d3(cc[3 * i], cc[3 * i + 1], cc[3 * i + 2]);
+          Gi = d3(gC[3 * i], gC[3 * i + 1], gC[3 * i + 2]);
+          for (int j = 0; j < n; ++j) {
+            const D3 u = ci - d3(cc[3 * j], cc[3 * j + 1], cc[3 * j + 2]);
+            const double r = sqrt(dot(u, u));
+            Gi = Gi - u * (3.0 * r * (lam[i] * w[j] + lam[j] * w[i]));
+          }
+          Gi = Gi - av * lam[i] - la * w[i];
+          b = M.skin_pt_body[K.pt_off + i];
+          if (K.kind == SURF_DEFORMABLE_SKIN && i < K.nsurf) {
+            const D3 gd = b >= 0 ? xf_rotT(aux + aux_X(M, b), Gi) : Gi;
+            double* o = grad + M.nq + K.deform_off + 3 * i;
+            o[0] += gd.x; o[1] += gd.y; o[2] += gd.z;
+          }
         }
-        Gi = Gi - av * lam[i] - la * w[i];
-        const int b = M.skin_pt_body[K.pt_off + i];
-        if (b >= 0) {
+        // per distinct body among the lanes: one shuffle reduction of (force, moment) instead of fp64 shared
+        // atomics (CAS loops; 13 lanes on one address cost 3 us of the 12.5 us epilogue on K3)
+        unsigned rest = __ballot_sync(0xffffffffu, on && b >= 0);
+        while (rest) {
+          const int bb = __shfl_sync(0xffffffffu, b, __ffs(rest) - 1);
+          const bool mine = on && b == bb;
           const D3 m = cross(ci, Gi);
-          atomicAdd(F + 3 * b, Gi.x); atomicAdd(F + 3 * b + 1, Gi.y); atomicAdd(F + 3 * b + 2, Gi.z);
-          atomicAdd(Mo + 3 * b, m.x); atomicAdd(Mo + 3 * b + 1, m.y); atomicAdd(Mo + 3 * b + 2, m.z);
+          const double fx = warp_sum(mine ? Gi.x : 0.0), fy = warp_sum(mine ? Gi.y : 0.0), fz = warp_sum(mine ? Gi.z : 0.0);
+          const double mx = warp_sum(mine ? m.x : 0.0), my = warp_sum(mine ? m.y : 0.0), mz = warp_sum(mine ? m.z : 0.0);
+          if (lane == 0) { F[3 * bb] += fx; F[3 * bb + 1] += fy; F[3 * bb + 2] += fz; Mo[3 * bb] += mx; Mo[3 * bb + 1] += my; Mo[3 * bb + 2] += mz; }
+          rest &= ~__ballot_sync(0xffffffffu, mine);
         }
-        if (K.kind == SURF_DEFORMABLE_SKIN && i < K.nsurf) {
-          const D3 gd = b >= 0 ? xf_rotT(aux + aux_X(M, b), Gi) : Gi;
-          double* o = grad + M.nq + K.deform_off + 3 * i;
-          o[0] += gd.x; o[1] += gd.y; o[2] += gd.z;
-        }
+        __syncwarp();
       }
     }
     __syncwarp();

@@ -159,6 +159,15 @@ int launch_cost_t(flash_ctx* ctx, const CostParams& p, int C, int tiles, size_t 
 
 // points per block: enough blocks for >= ~4 waves, at most 4096 points, at least one batch
 int choose_tile(const flash_ctx* ctx, long long n, int C) {
+  // small problems (tracking: one config, one depth frame): fewer full-size blocks than SMs would leave SMs idle
+  // while the others queue 12 warps on their fp64 pipe; spread the points over one block per SM instead, in whole
+  // warp groups of 32 (a block's last batch is then partial)
+  if ((n * C + CBLOCK - 1) / CBLOCK < 2ll * ctx->sm_count && n > 0) {
+    const long long tiles = std::max<long long>(1, ctx->sm_count / std::max(C, 1));
+    long long ppb = (n + tiles - 1) / tiles;
+    ppb = std::max<long long>(32, ((ppb + 31) / 32) * 32);
+    return (int)ppb;
+  }
   const long long target_blocks = (long long)ctx->sm_count * 2 * 4;
   long long ppb = (n * C + target_blocks - 1) / target_blocks;
   ppb = ((ppb + CBLOCK - 1) / CBLOCK) * CBLOCK;
