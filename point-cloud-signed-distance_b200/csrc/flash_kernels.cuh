@@ -116,8 +116,22 @@ __host__ __device__ inline size_t prepare_smem_doubles(const ModelC& M) {
 // column are copied aside, then all elements update at once -- the same fma per element as before, so the
 // inverse is bit-identical.
 constexpr int PREP_T = 320;
+// 1/x for the pivot candidates of the fast path: MUFU seed (2^-20) + two Newton steps (2^-40, then rounding-limited),
+// ~70 cycles instead of the ~350 of the IEEE division routine that every pivot step would wait for
+__device__ __forceinline__ double rcp_newton(double x) {
+  double y; asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  double e = fma(-x, y, 1.0); y = fma(y, e, y);
+  e = fma(-x, y, 1.0); y = fma(y, e, y);
+  return y;
+}
 __device__ __forceinline__ void prepare_block(const ModelC& M, const double* x, double* tab, double* aux, double* acc, int* status, double* sm, int tid, int T) {
   const int lane = tid & 31, warp = tid >> 5;
+#ifdef FLASH_ITER_TIMING
+  long long ts[8]; ts[0] = clock64();
+#define FLASH_TS(i) ts[i] = clock64()
+#else
+#define FLASH_TS(i) ((void)0)
+#endif
   if (acc) for (int i = tid; i < M.acc_len; i += T) acc[i] = 0.0;   // replaces a memset node
   {
     // forward kinematics is a serial chain: run it on thread 0 out of shared memory (bodies, x and the
@@ -133,8 +147,10 @@ __device__ __forceinline__ void prepare_block(const ModelC& M, const double* x, 
       for (int i = tid; i < M.nq; i += T) s_x[i] = x[i];
     }
     __syncthreads();
+    FLASH_TS(1);
     if (tid == 0) fk_bodies(s_body, nb, M.nq, s_x, s_aux);
     __syncthreads();
+    FLASH_TS(2);
     for (int i = tid; i < 25 * nb; i += T) aux[i] = s_aux[i];
     __syncthreads();
   }
@@ -168,45 +184,89 @@ __device__ __forceinline__ void prepare_block(const ModelC& M, const double* x, 
       A[e] = v;
     }
     __syncthreads();
+    FLASH_TS(3);
     bool ok = true;
-    for (int kk = 0; kk < Mm; ++kk) {
-      if (warp == 0) {
-        // pivot: largest |A[i][kk]|, i >= kk (lowest row on ties, as the serial factorisation)
-        double best = -1.0; int bi = kk;
-        for (int i = kk + lane; i < Mm; i += 32) { const double v = fabs(A[i * Mm + kk]); if (v > best) { best = v; bi = i; } }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-          const double ob = __shfl_xor_sync(0xffffffffu, best, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-          if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
-        }
-        if (lane == 0) { scr[0] = (double)bi; scr[1] = best; piv[kk] = (double)bi; }
-      }
+    if (Mm * Mm <= T) {
+      // Fast path (K3: 17 x 17 <= 320 threads): thread e owns element (i0, j0) in a register, the matrix in shared
+      // memory is only the exchange medium.  Per pivot TWO barriers: every thread scans the pivot column itself
+      // (broadcast loads, no shuffle search, no broadcast phase), the row exchange is done by addressing (row bi
+      // "holds" old row kk) instead of a swap phase, and the reciprocal of every pivot candidate was computed by
+      // the thread that produced it during the previous update, so no division sits on the critical path.
+      // Same operations on the same numbers as the generic path below except for the reciprocal (rcp_newton, ~1 ulp).
+      const bool act = tid < Mm * Mm;
+      const int i = i0, j = j0;
+      double* rcp = prow;                       // [Mm] reciprocals of the next pivot column (prow/pcol are unused here)
+      double a = act ? A[tid] : 0.0;
+      if (act && j == 0) rcp[i] = rcp_newton(a);
       __syncthreads();
-      const int bi = (int)scr[0];
-      if (!(scr[1] > 0.0)) ok = false;
-      if (bi != kk) {   // block-uniform
-        for (int j = tid; j < Mm; j += T) { const double t = A[kk * Mm + j]; A[kk * Mm + j] = A[bi * Mm + j]; A[bi * Mm + j] = t; }
+      for (int kk = 0; kk < Mm; ++kk) {
+        double best = -1.0; int bi = kk;
+#pragma unroll 4
+        for (int r = kk; r < Mm; ++r) { const double v = fabs(A[r * Mm + kk]); if (v > best) { best = v; bi = r; } }   // lowest row on ties
+        if (!(best > 0.0)) ok = false;
+        const double inv = rcp[bi];
+        if (tid == 0) piv[kk] = (double)bi;
+        double nv = 0.0;
+        if (act) {
+          const double pr = A[bi * Mm + j];
+          const double f = (i == bi) ? A[kk * Mm + kk] : A[i * Mm + kk];
+          const double own = (i == bi) ? A[kk * Mm + j] : a;
+          if (i == kk) nv = (j == kk) ? inv : pr * inv;
+          else nv = (j == kk) ? -f * inv : fma(-f, pr * inv, own);
+        }
+        __syncthreads();                         // every read of the old matrix is done
+        if (act) { A[tid] = nv; a = nv; if (j == kk + 1) rcp[i] = rcp_newton(nv); }
         __syncthreads();
       }
-      {
-        const double inv = 1.0 / A[kk * Mm + kk];
-        for (int j = tid; j < Mm; j += T) { prow[j] = (j == kk) ? inv : A[kk * Mm + j] * inv; pcol[j] = A[j * Mm + kk]; }
-        __syncthreads();
-        for (int e = tid, i = i0, j = j0; e < Mm * Mm; e += T, i += di, j += dj) {
-          if (j >= Mm) { j -= Mm; ++i; }
-          const double f = pcol[i];
-          A[e] = (i == kk) ? prow[j] : ((j == kk) ? -f * inv : fma(-f, prow[j], A[e]));
+      FLASH_TS(4);
+      // undo the row exchanges on the columns: the exchanges (kk, piv[kk]), kk = Mm-1 .. 0, move this thread's
+      // column to `pos`
+      int pos = j;
+      for (int kk = Mm - 1; kk >= 0; --kk) { const int pv = (int)piv[kk]; pos = (pos == kk) ? pv : ((pos == pv) ? kk : pos); }
+      if (act) A[i * Mm + pos] = a;              // a permutation of the columns: no two threads write one address
+      __syncthreads();
+    } else {
+      for (int kk = 0; kk < Mm; ++kk) {
+        if (warp == 0) {
+          // pivot: largest |A[i][kk]|, i >= kk (lowest row on ties, as the serial factorisation)
+          double best = -1.0; int bi = kk;
+          for (int i = kk + lane; i < Mm; i += 32) { const double v = fabs(A[i * Mm + kk]); if (v > best) { best = v; bi = i; } }
+  #pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            const double ob = __shfl_xor_sync(0xffffffffu, best, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+          }
+          if (lane == 0) { scr[0] = (double)bi; scr[1] = best; piv[kk] = (double)bi; }
         }
         __syncthreads();
+        const int bi = (int)scr[0];
+        if (!(scr[1] > 0.0)) ok = false;
+        if (bi != kk) {   // block-uniform
+          for (int j = tid; j < Mm; j += T) { const double t = A[kk * Mm + j]; A[kk * Mm + j] = A[bi * Mm + j]; A[bi * Mm + j] = t; }
+          __syncthreads();
+        }
+        {
+          const double inv = 1.0 / A[kk * Mm + kk];
+          for (int j = tid; j < Mm; j += T) { prow[j] = (j == kk) ? inv : A[kk * Mm + j] * inv; pcol[j] = A[j * Mm + kk]; }
+          __syncthreads();
+          for (int e = tid, i = i0, j = j0; e < Mm * Mm; e += T, i += di, j += dj) {
+            if (j >= Mm) { j -= Mm; ++i; }
+            const double f = pcol[i];
+            A[e] = (i == kk) ? prow[j] : ((j == kk) ? -f * inv : fma(-f, prow[j], A[e]));
+          }
+          __syncthreads();
+        }
+      }
+      FLASH_TS(4);
+      for (int kk = Mm - 1; kk >= 0; --kk) {      // undo the row exchanges on the columns
+        const int pv = (int)piv[kk];
+        if (pv != kk) {   // block-uniform
+          for (int i = tid; i < Mm; i += T) { const double t = A[i * Mm + kk]; A[i * Mm + kk] = A[i * Mm + pv]; A[i * Mm + pv] = t; }
+          __syncthreads();
+        }
       }
     }
-    for (int kk = Mm - 1; kk >= 0; --kk) {      // undo the row exchanges on the columns
-      const int pv = (int)piv[kk];
-      if (pv != kk) {   // block-uniform
-        for (int i = tid; i < Mm; i += T) { const double t = A[i * Mm + kk]; A[i * Mm + kk] = A[i * Mm + pv]; A[i * Mm + pv] = t; }
-        __syncthreads();
-      }
-    }
+    FLASH_TS(5);
     if (!ok && tid == 0) atomicExch(status, 1);   // singular RBF system (coincident control points)
     // weights: rhs = 0 (surface), -1 (skeleton) (src/Flash.jl:211)  ->  w = -sum_{skeleton j} Ainv[:, j]
     double* w = tab + K.tab_off + 3 * n;
@@ -219,6 +279,10 @@ __device__ __forceinline__ void prepare_block(const ModelC& M, const double* x, 
     double* Ainv = aux + aux_skin0(M) + K.aux_off;
     for (int e = tid; e < Mm * Mm; e += T) Ainv[e] = A[e];
     __syncthreads();
+    FLASH_TS(6);
+#ifdef FLASH_ITER_TIMING
+    if (tid == 0 && blockIdx.x == 0) printf("prepare_block cycles: stage %lld fk %lld centres+assemble %lld invert %lld unswap %lld store %lld\n", ts[1] - ts[0], ts[2] - ts[1], ts[3] - ts[2], ts[4] - ts[3], ts[5] - ts[4], ts[6] - ts[5]);
+#endif
   }
 }
 
@@ -850,9 +914,15 @@ __global__ void __launch_bounds__(PREP_T) iterate_kernel(const ModelC* Mp, doubl
   double* aux = aux_all + (size_t)c * M.aux_len;
   double* acc = acc_all + (size_t)c * M.acc_len;
   double* g = grad_all + (size_t)c * M.nx;
+#ifdef FLASH_ITER_TIMING
+  long long t0 = clock64(), t1 = 0, t2 = 0;
+#endif
   if (tid < 32) {
     epilogue_warp(M, x, tab, aux, acc, w_def, cost + c, g, sm, lane);
     __syncwarp();
+#ifdef FLASH_ITER_TIMING
+    t1 = clock64();
+#endif
     if (!done[c]) {
       const int nx = M.nx;
       double gn = 0, sn = 0;
@@ -870,8 +940,14 @@ __global__ void __launch_bounds__(PREP_T) iterate_kernel(const ModelC* Mp, doubl
       }
     }
   }
+#ifdef FLASH_ITER_TIMING
+  t2 = clock64();
+#endif
   __syncthreads();   // x, and the end of every read of tab / aux / acc, are visible to the whole block
   prepare_block(M, x, tab, aux, acc, status, sm, tid, PREP_T);
+#ifdef FLASH_ITER_TIMING
+  if (tid == 0 && c == 0 && iters[0] >= 20 && iters[0] < 23) printf("iterate_kernel cycles: epilogue %lld step %lld prepare %lld\n", t1 - t0, t2 - t1, clock64() - t2);
+#endif
 }
 
 // ------------------------------------------------------------------------------------------------
