@@ -1,7 +1,8 @@
 // flash_kernels.cuh -- the CUDA kernels of libflashsdf (sm_100a).
 //
-//   prepare_kernel   one warp per config: FK, convex world->geometry transforms, RBF control points,
-//                    fp64 LU of the Turk-O'Brien system (rows A3, A4, A7, A10)
+//   prepare_kernel   one 320-thread block per config: FK, convex world->geometry transforms, RBF control points,
+//                    fp64 Gauss-Jordan inverse of the Turk-O'Brien system, one thread per matrix element
+//                    (rows A3, A4, A7, A10)
 //   cost_kernel      the hot loop (rows A5, A6, A7, A8): points x configs -> per-config accumulators
 //                    (cost, per-body wrenches, RBF adjoint sums); also serves skin_eval (DIST mode)
 //   epilogue_kernel  adjoint RBF solve + wrench -> joint-space gradient (replaces ForwardDiff's
@@ -94,10 +95,10 @@ __device__ __forceinline__ double warp_sum(double v) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// One warp per config.  Everything that is iterated over (the RBF matrix, the control points) lives in
+// One block per config.  Everything that is iterated over (the RBF matrix, the control points) lives in
 // shared memory: the serial version of this kernel spent 35 us chasing dependent global loads through
 // a 17 x 17 triangular solve.  The Turk-O'Brien system is INVERTED (in-place Gauss-Jordan with partial
-// pivoting, rows over lanes) and the inverse kept in `aux`: weights and, in the epilogue, the adjoint
+// pivoting) and the inverse kept in `aux`: weights and, in the epilogue, the adjoint
 // solve are then lane-parallel matrix-vector products (the system is symmetric).
 __host__ __device__ inline size_t prepare_smem_doubles(const ModelC& M) {
   size_t need = 8;
@@ -374,7 +375,7 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     float px = 0.f, py = 0.f, pz = 0.f;
     // hulls that can be the minimum for some point of this warp's 32 Morton neighbours: lane j bounds hull j
     unsigned cand = all_convex; int first = -1;
-    if (!DIST && p.grp != nullptr && n_convex > 1) {
+    if (!DIST && p.grp != nullptr && n_convex > 1 && base + warp * 32 < tile1) {   // (a warp past the tile end has no points and no group)
       const float4 gb = __ldg(p.grp + ((base + warp * 32) >> 5));
       float lbv = 3.0e38f, ubv = 3.0e38f;
       if (lane < n_convex) hull_ball_bounds(H.cvx[lane], tabf + 12 * lane, gb.x, gb.y, gb.z, gb.w, lbv, ubv);
