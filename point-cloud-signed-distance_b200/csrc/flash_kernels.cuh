@@ -29,14 +29,23 @@ using namespace flashdev;
 #endif
 constexpr int BLOCK = FLASH_BLOCK;
 constexpr int WARPS = BLOCK / 32;
-// The cost kernel runs 384-thread blocks, 2 per SM (same 24 warps per SM as 3 x 256), with one block barrier per
-// batch: its ~6000-instruction straight-line body thrashes the instruction cache when the warps of an SM are
-// spread over many code positions (ncu: stall_no_instruction 2.4 per issue); two lock-stepped groups of 12
-// warps measured best (256 x 3 + barrier: 58.0 ms, 384 x 2: 56.6 ms, 768 x 1: 62.5 ms, no barrier: 62.5 ms on K5).
+// The cost kernel runs ONE 768-thread block per SM (24 warps, 80 registers) whose warps take groups of 32 points
+// from a block-wide counter.  History (K5, ms per launch): 256 x 3 static 62.5 -- its ~6000-instruction
+// straight-line body was instruction-fetch bound (ncu stall_no_instruction 2.4 per issue) and every block ended
+// with 7 warps waiting for the slowest; a block barrier per batch 58.0; 384 x 2 + barrier 56.6 (768 x 1 + barrier
+// 62.5: one barrier over 24 warps waits too long); barrier every 2nd batch 55.4; dynamic hand-out of the groups
+// with no barrier at all 54.2 (384 x 2), 16128-point tiles 53.5, 768 x 1 52.5 (640 x 1, 96 regs: 53.1; 512 x 1,
+// 120 regs, no spills: 55.4; 256 x 3: 57.0).
 #ifndef FLASH_CBLOCK
-#define FLASH_CBLOCK 384
+#define FLASH_CBLOCK 768
 #endif
 constexpr int CBLOCK = FLASH_CBLOCK;
+// groups of 32 points per barrier interval of the dynamic hand-out (cost_kernel); FLASH_STATIC_GROUPS = the static schedule
+#ifndef FLASH_STATIC_GROUPS
+#ifndef FLASH_DYN_GROUPS
+#define FLASH_DYN_GROUPS 1000000   // K5, ms per launch: 24 -> 55.6, 48 -> 55.1, 96 -> 54.7, 252 (= the whole 8064-point tile) -> 54.2; static 55.4-57.4
+#endif
+#endif
 constexpr int CWARPS = CBLOCK / 32;
 constexpr int QENT = 8;  // doubles per skin-queue entry: x y z s ginv nhx nhy nhz (slot in a side array)
 
@@ -326,7 +335,7 @@ __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayou
 // GRAD: accumulate gradient terms; ARGMIN: write the argmin surface per point; DIST: write the
 // min distance per point (skin_eval entry) and skip all accumulation.
 #ifndef FLASH_MINB
-#define FLASH_MINB 2
+#define FLASH_MINB 1
 #endif
 template <bool GRAD, bool ARGMIN, bool DIST>
 __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
@@ -339,6 +348,11 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, tab_len, acc_len, hot_g->tabf_len, GRAD && hot_g->n_skins > 0, CWARPS);
   stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab + (size_t)c * tab_len, tab_len, CBLOCK);
   double* acc_w = reinterpret_cast<double*>(smem + L.off_acc) + (size_t)warp * acc_len;
+#ifdef FLASH_DYN_GROUPS
+  __shared__ int s_next_v;
+  int* s_next = &s_next_v;
+  if (tid == 0) s_next_v = 0;
+#endif
   if (!DIST) for (int i = lane; i < acc_len; i += 32) acc_w[i] = 0.0;
   __syncthreads();
   const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
@@ -357,7 +371,25 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   if (tile1 > p.n_pts) tile1 = p.n_pts;
   double cost_local = 0.0;
 
+#ifdef FLASH_DYN_GROUPS
+  // Groups of 32 points are handed to the warps dynamically WITHIN an interval of FLASH_DYN_GROUPS groups; a block
+  // barrier separates the intervals and the hand-out evens out the warps' unequal work between two barriers.
+  // Measured best with ONE interval (no barrier after the first): the hand-out removes the end-of-block tail in
+  // which 11 warps waited for the slowest one, which is what the per-batch barrier of the static schedule was
+  // (expensively) bounding; see DESIGN.md 5.
+  const int ngroups = (int)((tile1 - tile0 + 31) >> 5);
+  int g = 0;
+  if (lane == 0) g = atomicAdd(s_next, 1);
+  g = __shfl_sync(0xffffffffu, g, 0);
+  for (int g_end = FLASH_DYN_GROUPS; ; g_end += FLASH_DYN_GROUPS) {
+    __syncthreads();
+    while (g < g_end && g < ngroups) {
+    const long long wbase = tile0 + (long long)g * 32;
+    if (lane == 0) g = atomicAdd(s_next, 1);
+    g = __shfl_sync(0xffffffffu, g, 0);
+#else
   for (long long base = tile0; base < tile1; base += CBLOCK) {
+    {
 #ifndef FLASH_NO_BATCH_SYNC
 #ifndef FLASH_SYNC_EVERY
 #define FLASH_SYNC_EVERY 2   // K5: every batch 56.2 ms, every 2nd 55.4, every 3rd 55.4
@@ -367,7 +399,9 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
 #endif
     __syncthreads();   // keep the block's warps in the same code region (instruction-cache locality, see CBLOCK)
 #endif
-    const long long i = base + tid;
+    const long long wbase = base + warp * 32;
+#endif
+    const long long i = wbase + lane;
     const bool valid = i < tile1;
     PointEval e;
     e.d = 0.f; e.arg = -1; e.slot = -1; e.is_skin = 0;
@@ -375,8 +409,8 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     float px = 0.f, py = 0.f, pz = 0.f;
     // hulls that can be the minimum for some point of this warp's 32 Morton neighbours: lane j bounds hull j
     unsigned cand = all_convex; int first = -1;
-    if (!DIST && p.grp != nullptr && n_convex > 1 && base + warp * 32 < tile1) {   // (a warp past the tile end has no points and no group)
-      const float4 gb = __ldg(p.grp + ((base + warp * 32) >> 5));
+    if (!DIST && p.grp != nullptr && n_convex > 1 && wbase < tile1) {   // (a warp past the tile end has no points and no group)
+      const float4 gb = __ldg(p.grp + (wbase >> 5));
       float lbv = 3.0e38f, ubv = 3.0e38f;
       if (lane < n_convex) hull_ball_bounds(H.cvx[lane], tabf + 12 * lane, gb.x, gb.y, gb.z, gb.w, lbv, ubv);
       const float min_ub = from_ordered_int(__reduce_min_sync(0xffffffffu, ordered_int(ubv)));
@@ -471,6 +505,10 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
         __syncwarp();
       }
     }
+    }
+#ifdef FLASH_DYN_GROUPS
+    if (g_end >= ngroups) break;
+#endif
   }
   if (DIST) return;
   cost_local = warp_sum(cost_local);
