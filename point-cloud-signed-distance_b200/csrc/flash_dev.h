@@ -22,8 +22,8 @@
 namespace flashdev {
 
 #if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
-struct Counters { long long points, narrow, inside, gjk_iters, plane_tests, vert_tests, lb_tests, skin64; };
-inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0, 0, 0}; return c; }
+struct Counters { long long points, narrow, inside, gjk_iters, plane_tests, vert_tests, lb_tests, skin64; unsigned exact_mask; };   // exact_mask: hulls whose narrow phase ran for the LAST point
+inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0, 0, 0, 0u}; return c; }
 #define FLASH_COUNT(field, n) (flashdev::counters().field += (n))
 #else
 #define FLASH_COUNT(field, n) ((void)0)
@@ -974,7 +974,13 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
       F3 n; float d;
       bool done = false;
       if (use_grid && C.g_on) done = grid_sd(C, G.grid_pool, y, d, n);
+#if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
+      const long long narrow0 = flashdev::counters().narrow;
+#endif
       if (!done) d = hull_sd(hull_view(G, C), y, fminf(best, cut), n);
+#if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
+      if (flashdev::counters().narrow != narrow0) flashdev::counters().exact_mask |= 1u << j;
+#endif
       if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
     }
     j = -1;

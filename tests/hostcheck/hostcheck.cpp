@@ -2,6 +2,7 @@
 // (csrc/flash_dev.h, csrc/flash_host.h) with g++ and replays, serially, exactly what the CUDA
 // kernels do per config and per point, so the formulas can be checked against the oracle on a box
 // without a GPU.  Never linked into libflashsdf.so; the product has no CPU path.
+#include <algorithm>
 #include <cstdio>
 #include <string>
 #include <vector>
@@ -13,7 +14,8 @@ using namespace flashhost;
 
 struct HC { HostModel hm; HotModel hot; };
 static int g_group_cull = 1;            // replay the warp-level hull culling of cost_kernel
-static long long g_cand_total = 0, g_groups = 0;
+static long long g_cand_total = 0, g_groups = 0, g_rounds_or = 0, g_rounds_max = 0;
+static unsigned g_or = 0; static int g_max = 0;
 static thread_local std::string g_err;
 
 extern "C" {
@@ -78,7 +80,16 @@ void hc_accumulate(void* p, const double* tab, const float* pts, long long n, in
       g_cand_total += __builtin_popcount(cand); g_groups += 1;
     }
     PointEval e;
+#ifdef FLASH_COUNTERS
+    counters().exact_mask = 0u;
+#endif
     eval_point(H, G, tab, tabf, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], cand, first, use_grid != 0, true, e);
+#ifdef FLASH_COUNTERS
+    // exact narrow-phase rounds a warp of 32 consecutive points executes: one per hull ANY lane evaluates (the
+    // kernel's candidate loop is warp-uniform) vs the most any single lane needs
+    g_or |= counters().exact_mask; g_max = std::max(g_max, __builtin_popcount(counters().exact_mask));
+    if ((i & 31) == 31 || i == n - 1) { g_rounds_or += __builtin_popcount(g_or); g_rounds_max += g_max; g_or = 0; g_max = 0; }
+#endif
     double dv = e.is_skin ? e.sk.s : (double)e.d;
     if (dist) dist[i] = dv;
     if (argmin) argmin[i] = e.arg;
@@ -113,6 +124,7 @@ void hc_epilogue(void* p, const double* x, const double* tab, const double* aux,
 void hc_set_group_cull(int on) { g_group_cull = on; }
 // out: candidate hulls summed over groups, groups
 void hc_group_stats(long long* out, int reset) { out[0] = g_cand_total; out[1] = g_groups; if (reset) { g_cand_total = 0; g_groups = 0; } }
+void hc_round_stats(long long* out, int reset) { out[0] = g_rounds_or; out[1] = g_rounds_max; if (reset) { g_rounds_or = 0; g_rounds_max = 0; } }
 
 // instrumentation (only meaningful when built with -DFLASH_COUNTERS)
 void hc_counters(long long* out, int reset) {
