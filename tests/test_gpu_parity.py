@@ -272,6 +272,25 @@ def test_raycast_then_track_squishable():
     assert np.abs(xh - xo).max() < 1e-4                                    # 20 iterations of a 1e-5-accurate gradient
 
 
+def test_on_device_estimate_state_two_link_k1():
+    """K1 (BASELINE configs[0]) through the on-device loop: the two-link arm's 50 x 50 RBF system takes the
+    generic (multi-element-per-thread) inversion path of iterate_kernel; host loop, device loop and the oracle's
+    loop must land on the same state (examples/manipulator.ipynb cell 13)."""
+    m = flash.models.two_link_arm()
+    cam = flash.depthsensors.affine((0, 0, 4), (1, 0, 0), np.pi)
+    x_true = np.array([np.pi, 1.3])
+    o = ol.Oracle(m)
+    _, pts = o.raycast(x_true, ol.kinect_rays(41, 41).reshape(-1, 3), cam)
+    x0 = x_true + np.array([0.3, -0.25])
+    solver = flash.tracking.NaiveSolver(2, rate=1.0, max_step=0.5, iteration_limit=30)
+    xh = flash.tracking.estimate_state(m, pts, x0, solver=solver)
+    xd = flash.tracking.estimate_state(m, pts, x0, solver=solver, on_device=True)
+    xo, co, it = o.estimate_state(x0, pts, rate=1.0, max_step=0.5, iteration_limit=30, mode=ol.GJK)
+    assert np.abs(xh - xd).max() < 1e-8
+    assert np.abs(xd - xo).max() < 1e-5
+    assert np.abs(xd - x_true).max() < 0.5 * np.abs(x0 - x_true).max()
+
+
 def test_on_device_estimate_state_batched_with_tolerance():
     rng = np.random.default_rng(12)
     m = flash.models.irb140()
