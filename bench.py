@@ -5,7 +5,8 @@ Workload (BASELINE.json configs[4], "K5"): the IRB140(floating base)+squishable+
 examples/irb_and_squishable.ipynb (63 states, 9 surfaces), 10,000,000 synthetic points uniform in the
 scene AABB [-0.5,1]x[-0.5,0.5]x[0.5,2], 64 candidate configurations (warm start + N(0,0.05)).
 One "step" = one flash_cost_grad call: cost[64] + grad[64][63] over all points.
-With N GPUs the POINTS are sharded across ranks (total work fixed -> "strong" scaling); each rank's
+With N GPUs the POINTS are sharded across ranks by interleaved x-slabs of the same global cloud (total work
+fixed -> "strong" scaling; scene_points); each rank's
 partial accumulators are summed by one ncclAllReduce inside the library before the epilogue.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode exact|grid]
@@ -52,21 +53,35 @@ def scene_states(flash, m, n_configs, seed=5):
     return X
 
 
-CHUNK = 1 << 20
+SLABS = 40   # divisible by 1, 2, 4, 8 (and 5, 10, 20)
 
 
-def scene_points(lo, hi, seed=1000, out=None):
-    """Points [lo, hi) of the global seeded cloud: fp32-representable, uniform in the scene AABB.  Chunk k
-    (2^20 points) is drawn from its own generator (seed, k), so every rank count sees the same cloud."""
-    n = hi - lo
-    pts = np.empty((n, 3), np.float64) if out is None else out
-    k0, k1 = lo // CHUNK, (hi + CHUNK - 1) // CHUNK
-    for k in range(k0, max(k1, k0 + (1 if n else 0))):
-        rng = np.random.default_rng([seed, k])
-        chunk = (SCENE_LO + (SCENE_HI - SCENE_LO) * rng.random((CHUNK, 3), dtype=np.float32)).astype(np.float32)
-        a, b = max(lo, k * CHUNK), min(hi, (k + 1) * CHUNK)
-        if b > a:
-            pts[a - lo:b - lo] = chunk[a - k * CHUNK:b - k * CHUNK]
+def slab_counts(n_total):
+    base, rem = divmod(n_total, SLABS)
+    return [base + (1 if s < rem else 0) for s in range(SLABS)]
+
+
+def scene_points(n_total, rank=0, world=1, seed=1000):
+    """The global seeded cloud of n_total points, fp32-representable and uniform in the scene AABB, generated as
+    SLABS equal-count slabs along x (stratified uniform sampling: slab s is uniform in its x-range, drawn from its
+    own generator (seed, s)), so that every rank count sees the SAME cloud.  Returns the points of `rank`:
+    the slabs s with s % world == rank -- a spatial domain decomposition (interleaved, so that every rank samples
+    the whole scene) that keeps a rank's points as dense as the full cloud; sharding a randomly ordered cloud by
+    index instead thins every shard to 1/world of the density and costs the kernel's warp-level culling
+    15 % at world = 8."""
+    counts = slab_counts(n_total)
+    mine = [s_ for s_ in range(SLABS) if s_ % world == rank]
+    pts = np.empty((sum(counts[s_] for s_ in mine), 3), np.float64)
+    at = 0
+    w = (SCENE_HI[0] - SCENE_LO[0]) / SLABS
+    for s_ in mine:
+        rng = np.random.default_rng([seed, s_])
+        u = rng.random((counts[s_], 3), dtype=np.float32)
+        lo = np.array([SCENE_LO[0] + s_ * w, SCENE_LO[1], SCENE_LO[2]])
+        ext = np.array([w, SCENE_HI[1] - SCENE_LO[1], SCENE_HI[2] - SCENE_LO[2]])
+        chunk = (lo + ext * u).astype(np.float32)
+        pts[at:at + counts[s_]] = chunk
+        at += counts[s_]
     return pts
 
 
@@ -145,7 +160,7 @@ def cpu_leg(n_points, n_configs, steps, warmup, threads=None, method="dual", see
     m = scene_model(flash)
     o = ol.Oracle(m, threads=threads)
     X = scene_states(flash, m, max(n_configs, 2))[:n_configs]
-    pts = scene_points(0, n_points, seed)
+    pts = scene_points(n_points, seed=seed)
     for _ in range(warmup):
         o.cost_grad(X[0], pts[: max(1000, n_points // 20)], mode=ol.GJK, method=method)
     t0 = time.perf_counter()
@@ -199,13 +214,14 @@ def run_ours(args, rank, local_rank, world):
     Cn = args.configs
     X = np.ascontiguousarray(scene_states(flash, m, Cn))
 
-    # shard the points: rank r owns [lo, hi)
+    # shard the points: rank r owns the x-slabs s with s % world == r of the global cloud (scene_points)
     N = args.points
-    lo, hi = (N * rank) // world, (N * (rank + 1)) // world
-    n_local = hi - lo
+    shard = scene_points(N, rank, world)
+    n_local = len(shard)
     pin = torch.empty((n_local, 3), dtype=torch.float64, pin_memory=True)
     pts = pin.numpy()
-    scene_points(lo, hi, out=pts)
+    pts[:] = shard
+    del shard
 
     if world > 1:
         idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
@@ -311,7 +327,7 @@ def run_ours(args, rank, local_rank, world):
             "dtype": "f32 distances / f64 RBF + accumulation", "data": "synthetic",
             "config": {"workload": "K5: IRB140(floating)+squishable+table (63 states, 9 surfaces), %d points x %d configs, points sharded over %d GPU(s)" % (N, Cn, world),
                        "points": N, "configs": Cn, "sdf_mode": args.mode, "l2": "L2 flushed (512 MiB memset) between timed steps; inputs %s L2" % ("exceed" if 16 * n_rank > l2.value else "fit"),
-                       "parallelism": "points sharded x%d, one ncclAllReduce of [%d][%d] fp64 per step" % (world, Cn, acc_len)},
+                       "parallelism": "points sharded x%d by interleaved x-slabs (40 slabs, rank r owns slabs r mod %d), one ncclAllReduce of [%d][%d] fp64 per step" % (world, world, Cn, acc_len)},
             "device_ms_per_step": 1e3 * Tkt / args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
                          "traffic": traffic, "peak_source": peak_src, "kernel": "cost_kernel<GRAD>", "kernel_ms": 1e3 * kernel_s,
