@@ -540,12 +540,30 @@ __host__ __device__ inline size_t epilogue_smem_doubles(const ModelC& M) {
 }
 // one warp finishes one config: acc (summed over points and ranks) -> *cost_c and grad (may be null);
 // sm = epilogue_smem_doubles() doubles
+// preloaded: the caller's whole block has already copied skin 0's inverse and table into `sm` (epilogue_preload)
+__device__ __forceinline__ void epilogue_preload(const ModelC& M, const double* tab, const double* aux, double* sm, int tid, int T) {
+  if (M.n_skins < 1) return;
+  const SkinC& K = M.skin[0];
+  const int n = K.npts, Mm = K.M;
+  double* Ainv = sm + 6 * MAX_BODIES;
+  double* cc = Ainv + Mm * Mm;
+  const double* src = aux + aux_skin0(M) + K.aux_off;
+  for (int e = tid; e < Mm * Mm; e += T) Ainv[e] = src[e];
+  const double* ct = tab + K.tab_off;
+  for (int e = tid; e < 4 * n + 4; e += T) cc[e] = ct[e];
+}
 __device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, const double* tab, const double* aux, const double* acc, double w_def,
-                                              double* cost_c, double* grad, double* sm, int lane) {
+                                              double* cost_c, double* grad, double* sm, int lane, bool preloaded = false) {
   double* F = sm;                                // [nb][3]
   double* Mo = F + 3 * MAX_BODIES;               // [nb][3]
   double* sk = Mo + 3 * MAX_BODIES;              // per-skin scratch
   const int nb = M.n_bodies;
+#ifdef FLASH_ITER_TIMING
+  long long es[8]; for (int q = 0; q < 8; ++q) es[q] = 0; es[0] = clock64();
+#define FLASH_ES(i) es[i] = clock64()
+#else
+#define FLASH_ES(i) ((void)0)
+#endif
   if (grad) {
     for (int i = lane; i < 6 * MAX_BODIES; i += 32) F[i] = 0.0;
     for (int k = lane; k < M.nx; k += 32) grad[k] = 0.0;
@@ -572,19 +590,21 @@ __device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, 
       const double* gY = acc + K.acc_off;
       const double* gC = gY + n + 4;
       __syncwarp();
-      {
+      if (!(preloaded && k == 0)) {
         const double* src = aux + aux_skin0(M) + K.aux_off;
         for (int e = lane; e < Mm * Mm; e += 32) Ainv[e] = src[e];
         const double* ct = tab + K.tab_off;
         for (int e = lane; e < 4 * n + 4; e += 32) cc[e] = ct[e];   // centres then (w, a0, a): contiguous in tab
       }
       __syncwarp();
+      FLASH_ES(1);
       for (int i = lane; i < Mm; i += 32) {
         double sacc = 0;
         for (int j = 0; j < Mm; ++j) sacc = fma(Ainv[i * Mm + j], gY[j], sacc);
         lam[i] = sacc;
       }
       __syncwarp();
+      FLASH_ES(2);
       const D3 la = Mm == n + 4 ? d3(lam[n + 1], lam[n + 2], lam[n + 3]) : d3(0, 0, 0);
       const D3 av = d3(w[n + 1], w[n + 2], w[n + 3]);
       for (int i0 = 0; i0 < n; i0 += 32) {          // warp-uniform trip count: the wrench sums below are warp reductions
@@ -597,7 +617,7 @@ __device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, 
           Gi = d3(gC[3 * i], gC[3 * i + 1], gC[3 * i + 2]);
           for (int j = 0; j < n; ++j) {
             const D3 u = ci - d3(cc[3 * j], cc[3 * j + 1], cc[3 * j + 2]);
-            const double r = sqrt(dot(u, u));
+            const double r = dsqrt_fast(dot(u, u));   // MUFU seed + Newton (8.5e-14 relative; 0 -> 0): the IEEE sqrt cost 400 cycles x n per lane
             Gi = Gi - u * (3.0 * r * (lam[i] * w[j] + lam[j] * w[i]));
           }
           Gi = Gi - av * lam[i] - la * w[i];
@@ -608,6 +628,7 @@ __device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, 
             o[0] += gd.x; o[1] += gd.y; o[2] += gd.z;
           }
         }
+        FLASH_ES(3);
         // per distinct body among the lanes: one shuffle reduction of (force, moment) instead of fp64 shared
         // atomics (CAS loops; 13 lanes on one address cost 3 us of the 12.5 us epilogue on K3)
         unsigned rest = __ballot_sync(0xffffffffu, on && b >= 0);
@@ -624,6 +645,7 @@ __device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, 
       }
     }
     __syncwarp();
+    FLASH_ES(4);
     if (lane == 0)
       for (int b = nb - 1; b >= 0; --b) {  // subtree wrenches: children follow parents
         const int p = M.body[b].parent;
@@ -644,10 +666,11 @@ __device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, 
         const D3 Fp = xf_rotT(P, Fb);
         const double nrm = aux[aux_qnorm(M, b)];
         const double* q = x + B.qoff;
-        const double qw = q[0] / nrm;
-        const D3 v = d3(q[1] / nrm, q[2] / nrm, q[3] / nrm);
+        const double rn = 1.0 / nrm;
+        const double qw = q[0] * rn;
+        const D3 v = d3(q[1] * rn, q[2] * rn, q[3] * rn);
         const D3 gv = Gp * qw + cross(Gp, v);
-        const double inv = 2.0 / nrm;
+        const double inv = 2.0 * rn;
         grad[B.qoff] += -dot(Gp, v) * inv;
         grad[B.qoff + 1] += gv.x * inv; grad[B.qoff + 2] += gv.y * inv; grad[B.qoff + 3] += gv.z * inv;
         grad[B.qoff + 4] += Fp.x; grad[B.qoff + 5] += Fp.y; grad[B.qoff + 6] += Fp.z;
@@ -655,10 +678,14 @@ __device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, 
     }
     __syncwarp();
   }
+  FLASH_ES(5);
   double reg = 0;
   for (int k = M.nq + lane; k < M.nx; k += 32) { reg = fma(x[k], x[k], reg); if (grad) grad[k] += 2.0 * w_def * x[k]; }
   reg = warp_sum(reg);
   if (lane == 0) *cost_c = acc[0] + w_def * reg;
+#ifdef FLASH_ITER_TIMING
+  if (lane == 0 && blockIdx.x == 0 && grad) printf("epilogue cycles: load %lld lambda %lld Gloop %lld reduce %lld bodies %lld reg %lld\n", es[1] - es[0], es[2] - es[1], es[3] - es[2], es[4] - es[3], es[5] - es[4], clock64() - es[5]);
+#endif
 }
 __global__ void __launch_bounds__(32) epilogue_kernel(const ModelC* __restrict__ Mp, const double* __restrict__ X, const double* __restrict__ tab_all,
                                                        const double* __restrict__ aux_all, const double* __restrict__ acc_all, int C, double w_def,
@@ -956,8 +983,10 @@ __global__ void __launch_bounds__(PREP_T) iterate_kernel(const ModelC* Mp, doubl
 #ifdef FLASH_ITER_TIMING
   long long t0 = clock64(), t1 = 0, t2 = 0;
 #endif
+  epilogue_preload(M, tab, aux, sm, tid, PREP_T);   // 320 threads fetch the first skin's inverse while nothing else runs
+  __syncthreads();
   if (tid < 32) {
-    epilogue_warp(M, x, tab, aux, acc, w_def, cost + c, g, sm, lane);
+    epilogue_warp(M, x, tab, aux, acc, w_def, cost + c, g, sm, lane, true);
     __syncwarp();
 #ifdef FLASH_ITER_TIMING
     t1 = clock64();
@@ -965,7 +994,19 @@ __global__ void __launch_bounds__(PREP_T) iterate_kernel(const ModelC* Mp, doubl
     if (!done[c]) {
       const int nx = M.nx;
       double gn = 0, sn = 0;
-      for (int k = lane; k < nx; k += 32) {
+      double stv[8];                       // this lane's step components (nx <= 256): divided once, applied below
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const int k = lane + 32 * q;
+        stv[q] = 0.0;
+        if (k < nx) {
+          const double gk = g[k] * inv_n;
+          const double st = -rate * gk / (divisors ? divisors[k] : 1.0);
+          stv[q] = st;
+          gn += gk * gk; sn += st * st;
+        }
+      }
+      for (int k = lane + 256; k < nx; k += 32) {   // states beyond the register window (up to 64 + 3 * 4 * 64)
         const double gk = g[k] * inv_n;
         const double st = -rate * gk / (divisors ? divisors[k] : 1.0);
         gn += gk * gk; sn += st * st;
@@ -974,7 +1015,9 @@ __global__ void __launch_bounds__(PREP_T) iterate_kernel(const ModelC* Mp, doubl
       if (tol > 0 && sqrt(gn) < tol) { if (lane == 0) done[c] = 1; }
       else {
         const double sc = sn > max_step ? max_step / sn : 1.0;
-        for (int k = lane; k < nx; k += 32) x[k] += sc * (-rate * g[k] * inv_n / (divisors ? divisors[k] : 1.0));
+#pragma unroll
+        for (int q = 0; q < 8; ++q) { const int k = lane + 32 * q; if (k < nx) x[k] += sc * stv[q]; }
+        for (int k = lane + 256; k < nx; k += 32) x[k] += sc * (-rate * g[k] * inv_n / (divisors ? divisors[k] : 1.0));
         if (lane == 0) iters[c] += 1;
       }
     }
