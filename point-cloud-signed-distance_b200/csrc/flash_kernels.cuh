@@ -210,7 +210,7 @@ __device__ __forceinline__ void prepare_block(const ModelC& M, const double* x, 
       if (act && j == 0) rcp[i] = rcp_newton(a);
       __syncthreads();
       for (int kk = 0; kk < Mm; ++kk) {
-        double best = -1.0; int bi = kk;
+        double best = -1.0; int bi = kk;   // (comparing the bit patterns as 64-bit integers instead: 5 % slower end to end)
 #pragma unroll 4
         for (int r = kk; r < Mm; ++r) { const double v = fabs(A[r * Mm + kk]); if (v > best) { best = v; bi = r; } }   // lowest row on ties
         if (!(best > 0.0)) ok = false;
