@@ -22,14 +22,16 @@ def _worker(rank, world, port, q):
     gold = np.load(os.path.join(HERE, "golden", "golden_v1.npz"))
     x, pts = gold["irb_and_squishable/x"], gold["irb_and_squishable/pts"]
     h = hl.HostCheck(flash.models.irb_and_squishable())
-    n = len(pts)
-    lo, hi = (n * rank) // world, (n * (rank + 1)) // world     # bench.py's shard rule
+    # bench.py's shard rule: the cloud is cut into x-slabs and rank r owns the slabs s with s % world == r
+    order = np.argsort(pts[:, 0], kind="stable")
+    slabs = np.array_split(order, 40)
+    mine = np.concatenate([slabs[s] for s in range(40) if s % world == rank])
     tab, aux = h.prepare(x)
-    acc, _, _ = h.accumulate(tab, pts[lo:hi])
+    acc, _, _ = h.accumulate(tab, pts[mine])
     t = torch.from_numpy(acc)
     dist.all_reduce(t)                                           # the one collective of the path
     cost, grad = h.epilogue(x, tab, aux, t.numpy())
-    q.put((rank, cost, grad, hi - lo))
+    q.put((rank, cost, grad, len(mine)))
     dist.destroy_process_group()
 
 
@@ -57,9 +59,26 @@ def test_sharded_points_allreduce_matches_single_rank():
 
 
 def test_shard_rule_covers_all_points_once():
-    for n in (0, 1, 7, 307200, 10_000_000):
+    """bench.scene_points: the union of the ranks' slabs is the N = 1 cloud (same points, every one once), the
+    shards are balanced, each shard spans the whole scene, and the cloud is uniform in the scene box."""
+    sys.path.insert(0, os.path.dirname(HERE))
+    import bench
+    key = lambda a: np.sort(a.view([("x", "f8"), ("y", "f8"), ("z", "f8")]).ravel())
+    for n in (0, 1, 7, 100_003):
+        whole = bench.scene_points(n)
+        assert whole.shape == (n, 3)
         for world in (1, 2, 4, 8):
-            spans = [((n * r) // world, (n * (r + 1)) // world) for r in range(world)]
-            assert spans[0][0] == 0 and spans[-1][1] == n
-            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
-            assert max(b - a for a, b in spans) - min(b - a for a, b in spans) <= 1
+            parts = [bench.scene_points(n, r, world) for r in range(world)]
+            assert sum(len(p) for p in parts) == n
+            if n:
+                assert np.array_equal(key(np.concatenate(parts)), key(whole))
+            if n > 1000:
+                sizes = [len(p) for p in parts]
+                assert max(sizes) - min(sizes) <= bench.SLABS // world + 1
+                for p in parts:      # interleaved slabs: every rank sees (nearly) the full x-extent of the scene
+                    assert p[:, 0].max() - p[:, 0].min() > 0.75 * (bench.SCENE_HI[0] - bench.SCENE_LO[0])
+    big = bench.scene_points(100_003)
+    assert (big >= bench.SCENE_LO).all() and (big <= bench.SCENE_HI).all()
+    assert np.array_equal(big, big.astype(np.float32).astype(np.float64))          # fp32-representable
+    h = np.histogram(big[:, 0], bins=10, range=(bench.SCENE_LO[0], bench.SCENE_HI[0]))[0]
+    assert h.max() - h.min() < 0.05 * h.mean()
