@@ -446,6 +446,26 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
       const float g = -2.f * e.d;
       float v0 = mine ? g * e.n.x : 0.f, v1 = mine ? g * e.n.y : 0.f, v2 = mine ? g * e.n.z : 0.f;
       float t0 = mine ? e.y.y * v2 - e.y.z * v1 : 0.f, t1 = mine ? e.y.z * v0 - e.y.x * v2 : 0.f, t2 = mine ? e.y.x * v1 - e.y.y * v0 : 0.f;
+#ifndef FLASH_NO_BUTTERFLY
+      {
+        // all six sums in ONE butterfly: each exchange step halves the number of values a lane still carries
+        // (4 + 2 + 1 + 1 + 1 = 9 shuffles instead of 6 x 5); lanes 4k .. 4k+3 end up with the total of value k
+        const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+        float k0 = b4 ? t1 : v0, k1 = b4 ? t2 : v1, k2 = b4 ? 0.f : v2, k3 = b4 ? 0.f : t0;      // keep {v0,v1,v2,t0} | {t1,t2,0,0}
+        const float s0 = b4 ? v0 : t1, s1 = b4 ? v1 : t2, s2 = b4 ? v2 : 0.f, s3 = b4 ? t0 : 0.f;
+        k0 += __shfl_xor_sync(0xffffffffu, s0, 16); k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+        k2 += __shfl_xor_sync(0xffffffffu, s2, 16); k3 += __shfl_xor_sync(0xffffffffu, s3, 16);
+        float h0 = b3 ? k2 : k0, h1 = b3 ? k3 : k1;
+        h0 += __shfl_xor_sync(0xffffffffu, b3 ? k0 : k2, 8); h1 += __shfl_xor_sync(0xffffffffu, b3 ? k1 : k3, 8);
+        float w = b2 ? h1 : h0;
+        w += __shfl_xor_sync(0xffffffffu, b2 ? h0 : h1, 4);
+        w += __shfl_xor_sync(0xffffffffu, w, 2);
+        w += __shfl_xor_sync(0xffffffffu, w, 1);
+        // value index of this lane: b4 ? (4,5,-,-) : (0,1,2,3), entry 2*b3 + b2
+        const int vi = (b4 ? 4 : 0) + (b3 ? 2 : 0) + (b2 ? 1 : 0);
+        if ((lane & 3) == 0 && vi < 6) acc_w[1 + 6 * j + vi] += (double)w;
+      }
+#else
       v0 = warp_sum(v0); v1 = warp_sum(v1); v2 = warp_sum(v2);
       t0 = warp_sum(t0); t1 = warp_sum(t1); t2 = warp_sum(t2);
       if (lane == 0) {
@@ -453,6 +473,7 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
         a[0] += (double)v0; a[1] += (double)v1; a[2] += (double)v2;
         a[3] += (double)t0; a[4] += (double)t1; a[5] += (double)t2;
       }
+#endif
       remaining &= ~m;
     }
 
