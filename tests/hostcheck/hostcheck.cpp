@@ -4,6 +4,7 @@
 // without a GPU.  Never linked into libflashsdf.so; the product has no CPU path.
 #include <algorithm>
 #include <cstdio>
+#include <cstring>
 #include <string>
 #include <vector>
 
@@ -39,6 +40,21 @@ void hc_convex_info(void* p, int j, int* nverts, int* nplanes, float* lo, float*
   ConvexC& C = ((HC*)p)->hm.M.cvx[j];
   *nverts = C.nverts; *nplanes = C.nplanes; *depth_bound = C.depth_bound;
   for (int k = 0; k < 3; ++k) { lo[k] = C.lo[k]; hi[k] = C.hi[k]; }
+}
+
+// plane slots of hull j: nplanes_pad floats[4] {nx, ny, nz, -o} (inert padding: n = 0, -o = -1e30) and the
+// hint map (DIRMAP_CELLS entries: group0 | group1 << 8)
+int hc_plane_table(void* p, int j, float* planes /* [nplanes_pad][4] or null */, unsigned short* pgrp /* [DIRMAP_CELLS] or null */) {
+  HC* h = (HC*)p;
+  const ConvexC& C = h->hm.M.cvx[j];
+  const F4* P = h->hm.geo_f4.data() + C.off_planes;
+  if (planes)
+    for (int f = 0; f < C.nplanes_pad; ++f) {
+      const float* a = reinterpret_cast<const float*>(P + (f & ~1)); const int hh = f & 1;
+      planes[4 * f] = a[hh]; planes[4 * f + 1] = a[2 + hh]; planes[4 * f + 2] = a[4 + hh]; planes[4 * f + 3] = a[6 + hh];
+    }
+  if (pgrp) std::memcpy(pgrp, h->hm.geo_u32.data() + C.off_pgrp, DIRMAP_CELLS * sizeof(unsigned short));
+  return C.nplanes_pad;
 }
 
 // prepare kernel, one config

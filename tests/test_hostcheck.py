@@ -215,3 +215,43 @@ def test_plane_hint_map_never_changes_the_distance():
         s = np.sort(per[i]); assert s[1] - s[0] < 4e-6
     # and it does its job: far fewer plane tests than one full 100-plane scan per narrow-phase evaluation
     assert cn["plane_tests"] < 45 * cn["narrow"]
+
+
+def test_plane_groups_and_hint_tables_are_well_formed():
+    """flash_host.h cluster_planes / build_plane_hints: every plane sits in exactly one slot, padding slots are
+    inert, the groups are tight clusters of normals, and every hint names existing groups; for a direction cell's
+    centre ray the most-violated plane just outside the hull and one hull radius away is in a hinted group."""
+    import ctypes as C
+    m = flash.models.irb_and_squishable()
+    h = hl.HostCheck(m)
+    L = hl.lib()
+    L.hc_plane_table.restype = C.c_int
+    L.hc_plane_table.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    R = 8
+    for j in range(h.n_convex):
+        nv, npl, lo, hi, depth = h.convex_info(j)
+        npad = L.hc_plane_table(h.h, j, None, None)
+        assert npad % 8 == 0 and npl <= npad < npl + 8 * ((npl + 7) // 8)
+        P = np.zeros((npad, 4), np.float32); G = np.zeros(6 * R * R, np.uint16)
+        L.hc_plane_table(h.h, j, P.ctypes.data, G.ctypes.data)
+        real = np.linalg.norm(P[:, :3], axis=1) > 0.5
+        assert real.sum() == npl and (P[~real, 3] < -1e29).all()
+        assert np.allclose(np.linalg.norm(P[real, :3], axis=1), 1.0, atol=1e-5) and (P[real, 3] < 0).all()   # -o < 0: centroid inside
+        ng = npad // 8
+        assert ((G & 255) < ng).all() and ((G >> 8) < ng).all()
+        if npl >= 32:   # clustered: normals of a group lie within a cap much smaller than the sphere
+            spread = [np.min(P[g * 8:(g + 1) * 8][real[g * 8:(g + 1) * 8], :3] @ P[g * 8:(g + 1) * 8][real[g * 8:(g + 1) * 8], :3].mean(0)) for g in range(ng) if real[g * 8:(g + 1) * 8].any()]
+            assert np.median(spread) > 0.6
+        # the cell centres of the +x face
+        hits = 0
+        for iv in range(R):
+            for iu in range(R):
+                d = np.array([1.0, -1 + (2 * iu + 1) / R, -1 + (2 * iv + 1) / R]); d /= np.linalg.norm(d)
+                a = P[:, :3].astype(np.float64) @ d
+                t_exit = np.min(np.where(real & (a > 0), -P[:, 3] / np.maximum(a, 1e-30), np.inf))
+                g = G[(0 * R + iv) * R + iu]
+                for scale in (1.05, 2.0):       # just outside the hull and one hull radius away, along the cell's centre ray
+                    y = scale * t_exit * d
+                    f = int(np.argmax(np.where(real, P[:, :3] @ y + P[:, 3], -np.inf)))
+                    hits += (f // 8) in (int(g & 255), int(g >> 8))
+        assert hits >= 0.75 * 2 * R * R      # a hint, not a guarantee: a miss costs a GJK iteration, never accuracy (83-100 % on these hulls)
