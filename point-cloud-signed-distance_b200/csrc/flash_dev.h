@@ -805,6 +805,59 @@ FLASH_SKIN_LOOP
   }
   return o;
 }
+// Certified lower bound of the skin value over the WHOLE ball |x - c| <= rho (group-level cull: a skin whose
+// bound exceeds the group's hull upper bound is the minimum for no point of the group, so the per-point
+// pre-filter above is skipped for all 32 points).  Third-order Taylor expansion at the ball centre with the
+// actual Hessian: for phi = r^3, grad = 3 r u, Hess = 3 (r I + u u^T / r), |D^3 phi [d,d,d]| <= 6 |d|^3 and
+// |D^3 phi [d,d,.]| <= 6 |d|^2, so with W3 = sum |3 w_i|
+//   f(x)      >= f(c) - |g| rho - |H|_F rho^2 / 2 - W3 rho^3 / 3
+//   |grad f(x)| <= |g| + |H|_F rho + W3 rho^2
+// and s = f / |grad f| >= f_lo / g_hi wherever f_lo > 0.  fp32 evaluation errors follow skin_bound_f32's model
+// (centre = an fp32 point); the n-term error sums are replaced by n * (largest term).  Returns -3e38 when nothing
+// can be certified.  One thread per ball (the cost kernel runs it once per group of its tile before the point
+// loop: inside the loop the extra code costs more instruction fetch than the skipped pre-filters save).
+FLASH_HD float skin_ball_lower_f32(const float* __restrict__ cw, int n, bool normalize, float cx, float cy, float cz, float rho) {
+  float v[11];   // f3, g[3], Hxx, Hyy, Hzz, Hxy, Hxz, Hyz, sum |k|
+  float m1 = 0.f, m2 = 0.f, m3 = 0.f;   // max |k|(r+p1), .. * r, .. * r^2
+#pragma unroll
+  for (int q = 0; q < 11; ++q) v[q] = 0.f;
+  const float p1 = fabsf(cx) + fabsf(cy) + fabsf(cz);
+  for (int i = 0; i < n; ++i) {
+    const F4 cc = reinterpret_cast<const F4*>(cw)[i];
+    const float ux = cx - cc.x, uy = cy - cc.y, uz = cz - cc.z, k = cc.w;
+    const float r2 = fmaf(ux, ux, fmaf(uy, uy, uz * uz));
+#ifdef __CUDA_ARCH__
+    const float ri = rsqrt_fast(fmaxf(r2, 1e-30f));
+#else
+    const float ri = 1.0f / sqrtf(fmaxf(r2, 1e-30f));
+#endif
+    const float r = r2 * ri, kr = k * r, ki = k * ri;
+    v[0] = fmaf(kr, r2, v[0]);
+    v[1] = fmaf(kr, ux, v[1]); v[2] = fmaf(kr, uy, v[2]); v[3] = fmaf(kr, uz, v[3]);
+    const float kx = ki * ux, ky = ki * uy, kz = ki * uz;
+    v[4] += fmaf(kx, ux, kr); v[5] += fmaf(ky, uy, kr); v[6] += fmaf(kz, uz, kr);
+    v[7] = fmaf(kx, uy, v[7]); v[8] = fmaf(kx, uz, v[8]); v[9] = fmaf(ky, uz, v[9]);
+    const float t = fabsf(k) * (r + p1);
+    v[10] += fabsf(k); m1 = fmaxf(m1, t); m2 = fmaxf(m2, t * r); m3 = fmaxf(m3, t * r2);
+  }
+  const float* a4 = cw + 4 * n;
+  const float third = 1.0f / 3.0f, nf = (float)n;
+  const float f = fmaf(v[0], third, fmaf(a4[1], cx, fmaf(a4[2], cy, fmaf(a4[3], cz, a4[0]))));
+  const float K = 1.1920929e-7f * (float)(2 * n + 40);
+  const float pa = fabsf(a4[0]) + fabsf(a4[1] * cx) + fabsf(a4[2] * cy) + fabsf(a4[3] * cz);
+  const float Ef = K * (nf * m3 * third + pa) + 1e-30f;
+  const float gx = v[1] + a4[1], gy = v[2] + a4[2], gz = v[3] + a4[3];
+  const float gn = sqrtf(fmaf(gx, gx, fmaf(gy, gy, gz * gz))) * (1.f + 1e-6f) + 2.f * K * (nf * m2 + fabsf(a4[1]) + fabsf(a4[2]) + fabsf(a4[3]));
+  const float hd = fmaf(v[4], v[4], fmaf(v[5], v[5], v[6] * v[6])), ho = fmaf(v[7], v[7], fmaf(v[8], v[8], v[9] * v[9]));
+  const float hn = sqrtf(fmaf(2.f, ho, hd)) * (1.f + 1e-6f) + 8.f * K * nf * m1;   // Frobenius norm + evaluation error
+  const float W3 = v[10] * (1.f + 1e-5f);   // >= sum |3 w_i|
+  const float rh = rho * (1.f + 1e-6f);
+  const float f_lo = (f - Ef - fabsf(f) * 1e-6f) - (rh * (gn + rh * (0.5f * hn + rh * third * W3))) * (1.f + 1e-5f);
+  if (!(f_lo > 0.f)) return -3.0e38f;
+  if (!normalize) return f_lo;
+  const float g_hi = (gn + rh * (hn + rh * W3)) * (1.f + 1e-5f) + 1e-30f;
+  return (f_lo / g_hi) * (1.f - 1e-6f);
+}
 // fp32 side table of one config: hull transforms (12 floats each) and the skin tables above
 FLASH_HD void tabf_fill(const HotModel& H, const double* __restrict__ tab, float* __restrict__ tabf, int tid, int nthreads) {
   for (int i = tid; i < 12 * H.n_convex; i += nthreads) tabf[i] = (float)tab[i];
@@ -888,7 +941,7 @@ FLASH_HD void hull_ball_bounds(const ConvexC& C, const float* __restrict__ T, fl
 // Hulls that can be the minimum for SOME point of the ball: lb_j <= min_k ub_k.  A culled hull is
 // strictly farther than hull argmin(ub) at every point of the ball, so neither the min nor the argmin
 // (first minimum) changes.  `first` = the most promising candidate (smallest lower bound).
-FLASH_HD unsigned group_candidates(const HotModel& M, const float* __restrict__ tabf, float cx, float cy, float cz, float rho, int& first) {
+FLASH_HD unsigned group_candidates(const HotModel& M, const float* __restrict__ tabf, float cx, float cy, float cz, float rho, int& first, float* min_ub_out = nullptr) {
   float lb[MAX_CONVEX];
   float min_ub = 3.0e38f;
   for (int j = 0; j < M.n_convex; ++j) {
@@ -896,10 +949,26 @@ FLASH_HD unsigned group_candidates(const HotModel& M, const float* __restrict__ 
     hull_ball_bounds(M.cvx[j], tabf + 12 * j, cx, cy, cz, rho, lb[j], ub);
     min_ub = fminf(min_ub, ub);
   }
+  if (min_ub_out) *min_ub_out = min_ub;
   unsigned mask = 0; float lb0 = 3.0e38f; first = -1;
   for (int j = 0; j < M.n_convex; ++j)
     if (lb[j] <= min_ub) { mask |= 1u << j; if (lb[j] < lb0) { lb0 = lb[j]; first = j; } }
   return mask;
+}
+
+// Skins that are the minimum for NO point of the ball (bit k set = skip skin k): their certified lower bound over
+// the ball exceeds min_ub, the smallest hull upper bound (group_candidates), by more than the fp32 rounding of
+// the final comparison.  `cut` receives an upper bound of the group's minimum to start the hull scans from.
+FLASH_HD float skin_cull_threshold(float min_ub) { return min_ub * (min_ub > 0.f ? 1.f + 2e-6f : 1.f - 2e-6f) + 2e-6f; }
+FLASH_HD unsigned group_skin_cull(const HotModel& M, const float* __restrict__ tabf, float cx, float cy, float cz, float rho, float min_ub, float& cut) {
+  unsigned skip = 0u;
+  const float thr = skin_cull_threshold(min_ub);
+  for (int k = 0; k < M.n_skins; ++k) {
+    const SkinC& K = M.skin[k];
+    if (skin_ball_lower_f32(tabf + K.tabf_off, K.npts, M.normalize != 0, cx, cy, cz, rho) > thr) skip |= 1u << k;
+  }
+  cut = skip ? thr : 3.0e38f;
+  return skip;
 }
 
 // Evaluates skin(x) = min over all surfaces for one world point under one configuration.
@@ -910,7 +979,8 @@ FLASH_HD unsigned group_candidates(const HotModel& M, const float* __restrict__ 
 // The point is passed in fp64: the cost path feeds fp32 points (exact in fp64), the ray marcher its
 // fp64 sample positions.
 FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __restrict__ tab, const float* __restrict__ tabf,
-                         double px, double py, double pz, unsigned cand, int first, bool use_grid, bool fp32_point, PointEval& out) {
+                         double px, double py, double pz, unsigned cand, int first, bool use_grid, bool fp32_point, PointEval& out,
+                         unsigned skin_skip = 0u, float cut0 = 3.0e38f) {
   const ConvexC* __restrict__ cvx = M.cvx;
   float best = 3.0e38f; int arg = 0x7fffffff; int slot = -1; int is_skin = 0;
   out.y = f3(0, 0, 0); out.n = f3(0, 0, 0);
@@ -924,9 +994,10 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
   // marcher passes fp64 sample positions and evaluates the skins directly.
   const bool defer = nc > 0 && fp32_point;
   float s_lo[MAX_SKINS];
-  float cut = 3.0e38f;   // an upper bound of the final minimum that no surface index is attached to
+  float cut = cut0;   // an upper bound of the final minimum that no surface index is attached to
   for (int k = 0; k < M.n_skins; ++k) {
     const SkinC& K = M.skin[k];
+    if (defer && ((skin_skip >> k) & 1u)) { s_lo[k] = 3.0e38f; continue; }   // group_skin_cull: never the minimum here
     if (defer) {
       const SkinBound sb = skin_bound_f32(tabf + K.tabf_off, K.npts, M.normalize != 0, fx, fy, fz);
       s_lo[k] = sb.lo;

@@ -337,6 +337,7 @@ __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayou
 #ifndef FLASH_MINB
 #define FLASH_MINB 1
 #endif
+#define FLASH_MAX_TILE_GROUPS 512   // choose_tile keeps tiles at <= 16384 points
 template <bool GRAD, bool ARGMIN, bool DIST>
 __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -378,6 +379,25 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   // which 11 warps waited for the slowest one, which is what the per-batch barrier of the static schedule was
   // (expensively) bounding; see DESIGN.md 5.
   const int ngroups = (int)((tile1 - tile0 + 31) >> 5);
+#ifndef FLASH_NO_SKIN_CULL
+  // Group-level skin cull, one thread per group of the tile, before the point loop: bit k of s_skip[g] = skin k is
+  // the minimum for no point of group g (certified lower bound over the group's ball > smallest hull upper bound),
+  // so the loop skips its fp32 pre-filter for all 32 points.
+  __shared__ unsigned char s_skip[FLASH_MAX_TILE_GROUPS];
+  const bool skin_pre = !DIST && p.grp != nullptr && n_convex > 1 && H.n_skins > 0 && H.n_skins <= 8 && ngroups <= FLASH_MAX_TILE_GROUPS;
+  if (skin_pre)
+    for (int gi = tid; gi < ngroups; gi += CBLOCK) {
+      const float4 gb = __ldg(p.grp + ((tile0 >> 5) + gi));
+      float min_ub = 3.0e38f;
+      for (int j = 0; j < n_convex; ++j) {
+        float lbv, ubv;
+        hull_ball_bounds(H.cvx[j], tabf + 12 * j, gb.x, gb.y, gb.z, gb.w, lbv, ubv);
+        min_ub = fminf(min_ub, ubv);
+      }
+      float cut_unused;
+      s_skip[gi] = (unsigned char)group_skin_cull(H, tabf, gb.x, gb.y, gb.z, gb.w, min_ub, cut_unused);
+    }
+#endif
   int g = 0;
   if (lane == 0) g = atomicAdd(s_next, 1);
   g = __shfl_sync(0xffffffffu, g, 0);
@@ -385,6 +405,7 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     __syncthreads();
     while (g < g_end && g < ngroups) {
     const long long wbase = tile0 + (long long)g * 32;
+    const int gcur = g; (void)gcur;
     if (lane == 0) g = atomicAdd(s_next, 1);
     g = __shfl_sync(0xffffffffu, g, 0);
 #else
@@ -409,6 +430,7 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     float px = 0.f, py = 0.f, pz = 0.f;
     // hulls that can be the minimum for some point of this warp's 32 Morton neighbours: lane j bounds hull j
     unsigned cand = all_convex; int first = -1;
+    unsigned skin_skip = 0u; float cut0 = 3.0e38f;
     if (!DIST && p.grp != nullptr && n_convex > 1 && wbase < tile1) {   // (a warp past the tile end has no points and no group)
       const float4 gb = __ldg(p.grp + (wbase >> 5));
       float lbv = 3.0e38f, ubv = 3.0e38f;
@@ -418,11 +440,14 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
       cand = __ballot_sync(0xffffffffu, is_cand);
       first = __reduce_min_sync(0xffffffffu, is_cand ? ((ordered_int(lbv) & ~31) | lane) : 0x7fffffff) & 31;
       if (cand == 0u) { cand = all_convex; first = -1; }   // only with non-finite bounds
+#if defined(FLASH_DYN_GROUPS) && !defined(FLASH_NO_SKIN_CULL)
+      else if (skin_pre) { skin_skip = s_skip[gcur]; if (skin_skip) cut0 = skin_cull_threshold(min_ub); }
+#endif
     }
     if (valid) {
       const float4 P = __ldg(p.pts + i);
       px = P.x; py = P.y; pz = P.z;
-      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, cand, first, p.use_grid != 0, true, e);
+      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, cand, first, p.use_grid != 0, true, e, skin_skip, cut0);
     }
     if (DIST) {
       if (valid) {

@@ -48,6 +48,9 @@ def lib():
         L.hc_support.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_int32_p, c_int32_p, c_float_p, c_float_p]; L.hc_support.restype = None
         L.hc_set_group_cull.argtypes = [C.c_int]; L.hc_set_group_cull.restype = None
         L.hc_group_stats.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_group_stats.restype = None
+        L.hc_set_skin_cull.argtypes = [C.c_int]; L.hc_set_skin_cull.restype = None
+        L.hc_skin_groups_skipped.argtypes = [C.c_int]; L.hc_skin_groups_skipped.restype = C.c_longlong
+        L.hc_skin_ball_lower.argtypes = [vp, c_double_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]; L.hc_skin_ball_lower.restype = C.c_float
         _lib = L
     return _lib
 
@@ -107,6 +110,10 @@ class HostCheck:
                             hi.ctypes.data_as(c_float_p), s.ctypes.data_as(c_double_p))
         return lo, hi, s
 
+    def skin_ball_lower(self, k, tab, centre, rho):
+        c = np.asarray(centre, np.float32)
+        return float(lib().hc_skin_ball_lower(self.h, tab.ctypes.data_as(c_double_p), k, float(c[0]), float(c[1]), float(c[2]), float(np.float32(rho))))
+
     def support(self, j, q):
         q = np.ascontiguousarray(q, np.float32).reshape(-1, 3)
         im = np.empty(len(q), np.int32); isc = np.empty(len(q), np.int32); vm = np.empty(len(q), np.float32); vs = np.empty(len(q), np.float32)
@@ -129,6 +136,14 @@ def counters(reset=True):
 
 def set_group_cull(on):
     lib().hc_set_group_cull(1 if on else 0)
+
+
+def set_skin_cull(on):
+    lib().hc_set_skin_cull(1 if on else 0)
+
+
+def skin_groups_skipped(reset=True):
+    return int(lib().hc_skin_groups_skipped(1 if reset else 0))
 
 
 def group_stats(reset=True):

@@ -154,6 +154,55 @@ def test_fp32_skin_interval_contains_fp64_value(name):
     assert np.median((hi - lo) / np.maximum(np.abs(s), 1e-9)) < 0.25
 
 
+@pytest.mark.parametrize("name", ["irb_and_squishable", "squishable", "two_link_arm", "beanbag"])
+def test_skin_ball_lower_bound_holds_at_every_point_of_the_ball(name):
+    """skin_ball_lower_f32 (group-level skin cull) is a CERTIFIED lower bound of the skin value over the whole
+    ball: checked against the fp64 value at 400 points of each ball (surface and interior), for balls of the
+    sizes the Morton groups have (millimetres to decimetres) near and far from the skin."""
+    rng = np.random.default_rng(11)
+    m = BUILDERS[name]()
+    h = hl.HostCheck(m)
+    tab, _ = h.prepare(GOLD[name + "/x"])
+    centre = GOLD[name + "/pts"].mean(0)
+    certified = 0
+    for scale in (0.1, 0.4, 1.5):
+        for rho in (0.002, 0.01, 0.05, 0.2):
+            for c in (centre + scale * rng.standard_normal((40, 3))).astype(np.float32):
+                lb = h.skin_ball_lower(0, tab, c, rho)
+                if lb < -1e37:
+                    continue
+                certified += 1
+                d = rng.standard_normal((400, 3)); d /= np.linalg.norm(d, axis=1)[:, None]
+                d *= rho * np.concatenate([np.ones(200), rng.uniform(0, 1, 200) ** (1 / 3)])[:, None]
+                pts = (c.astype(np.float64) + d).astype(np.float32)
+                pts = pts[np.linalg.norm(pts.astype(np.float64) - c, axis=1) <= rho]
+                _, _, s = h.skin_bound(0, tab, pts)
+                assert lb <= s.min(), (name, scale, rho, lb, s.min())
+    assert certified > 100   # and it does certify something
+
+
+def test_group_skin_cull_never_changes_the_result():
+    """Replay with and without the group-level skin cull: distances, argmins and accumulators are identical,
+    and the cull fires on most groups of a scene where the hulls dominate."""
+    m = flash.models.irb_and_squishable()
+    h = hl.HostCheck(m)
+    tab, _ = h.prepare(GOLD["irb_and_squishable/x"])
+    rng = np.random.default_rng(6)
+    # groups of 32 points as the Morton order makes them: 2000 clusters of 1.5 cm, plus the golden frame's points
+    ctr = rng.uniform([-0.8, -0.8, -0.3], [1.0, 0.8, 1.2], (2000, 1, 3))
+    pts = np.concatenate([(ctr + rng.uniform(-0.015, 0.015, (2000, 32, 3))).reshape(-1, 3), GOLD["irb_and_squishable/pts"]]).astype(np.float32)
+    try:
+        hl.set_skin_cull(True); hl.skin_groups_skipped()
+        a1, d1, g1 = h.accumulate(tab, pts)
+        skipped = hl.skin_groups_skipped()
+        hl.set_skin_cull(False)
+        a0, d0, g0 = h.accumulate(tab, pts)
+    finally:
+        hl.set_skin_cull(True)
+    assert np.array_equal(d0, d1) and np.array_equal(g0, g1) and np.array_equal(a0, a1)
+    assert skipped > 0.2 * len(pts) / 32
+
+
 def test_fp32_prefilter_defers_most_fp64_skin_evaluations():
     rng = np.random.default_rng(4)
     m = flash.models.irb_and_squishable()
