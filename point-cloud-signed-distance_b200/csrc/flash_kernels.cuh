@@ -379,13 +379,18 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   // which 11 warps waited for the slowest one, which is what the per-batch barrier of the static schedule was
   // (expensively) bounding; see DESIGN.md 5.
   const int ngroups = (int)((tile1 - tile0 + 31) >> 5);
-#ifndef FLASH_NO_SKIN_CULL
-  // Group-level skin cull, one thread per group of the tile, before the point loop: bit k of s_skip[g] = skin k is
-  // the minimum for no point of group g (certified lower bound over the group's ball > smallest hull upper bound),
-  // so the loop skips its fp32 pre-filter for all 32 points.
-  __shared__ unsigned char s_skip[FLASH_MAX_TILE_GROUPS];
-  const bool skin_pre = !DIST && p.grp != nullptr && n_convex > 1 && H.n_skins > 0 && H.n_skins <= 8 && ngroups <= FLASH_MAX_TILE_GROUPS;
-  if (skin_pre)
+#ifndef FLASH_NO_GROUP_PREPASS
+  // Group pre-pass, one thread per group of the tile, before the point loop (inside the loop the same code costs more
+  // instruction fetch than it saves):
+  //   s_cand / first : hulls that can be the minimum for some point of the group's ball, the most promising first
+  //   skip bits      : skin k is the minimum for NO point of the group (certified lower bound over the ball >
+  //                    smallest hull upper bound): the loop skips its fp32 pre-filter for all 32 points
+  //   s_thr          : upper bound of the group's minimum, the hull scans' cutoff when a skin is skipped
+  __shared__ unsigned s_cand[FLASH_MAX_TILE_GROUPS];
+  __shared__ float s_thr[FLASH_MAX_TILE_GROUPS];
+  __shared__ unsigned short s_meta[FLASH_MAX_TILE_GROUPS];   // first << 8 | skip bits (first = 255: none)
+  const bool grp_pre = !DIST && p.grp != nullptr && n_convex > 1 && ngroups <= FLASH_MAX_TILE_GROUPS;
+  if (grp_pre)
     for (int gi = tid; gi < ngroups; gi += CBLOCK) {
       const float4 gb = __ldg(p.grp + ((tile0 >> 5) + gi));
       float min_ub = 3.0e38f;
@@ -394,9 +399,21 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
         hull_ball_bounds(H.cvx[j], tabf + 12 * j, gb.x, gb.y, gb.z, gb.w, lbv, ubv);
         min_ub = fminf(min_ub, ubv);
       }
-      float cut_unused;
-      s_skip[gi] = (unsigned char)group_skin_cull(H, tabf, gb.x, gb.y, gb.z, gb.w, min_ub, cut_unused);
+      unsigned cm = 0u; int best = 0x7fffffff;
+      for (int j = 0; j < n_convex; ++j) {
+        float lbv, ubv;
+        hull_ball_bounds(H.cvx[j], tabf + 12 * j, gb.x, gb.y, gb.z, gb.w, lbv, ubv);
+        if (lbv <= min_ub) { cm |= 1u << j; best = min(best, (ordered_int(lbv) & ~31) | j); }
+      }
+      unsigned skip = 0u; float thr = 3.0e38f; int fi = best & 31;
+      if (cm == 0u) { cm = all_convex; fi = 255; }   // only with non-finite bounds
+#ifndef FLASH_NO_SKIN_CULL
+      else if (H.n_skins > 0 && H.n_skins <= 8) skip = group_skin_cull(H, tabf, gb.x, gb.y, gb.z, gb.w, min_ub, thr);
+#endif
+      s_cand[gi] = cm; s_thr[gi] = thr; s_meta[gi] = (unsigned short)((fi << 8) | skip);
     }
+#else
+  const bool grp_pre = false;
 #endif
   int g = 0;
   if (lane == 0) g = atomicAdd(s_next, 1);
@@ -431,6 +448,15 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     // hulls that can be the minimum for some point of this warp's 32 Morton neighbours: lane j bounds hull j
     unsigned cand = all_convex; int first = -1;
     unsigned skin_skip = 0u; float cut0 = 3.0e38f;
+#ifdef FLASH_DYN_GROUPS
+    if (grp_pre) {
+#ifndef FLASH_NO_GROUP_PREPASS
+      const unsigned m = s_meta[gcur];
+      cand = s_cand[gcur]; first = (m >> 8) == 255u ? -1 : (int)(m >> 8);
+      skin_skip = m & 255u; cut0 = s_thr[gcur];
+#endif
+    } else
+#endif
     if (!DIST && p.grp != nullptr && n_convex > 1 && wbase < tile1) {   // (a warp past the tile end has no points and no group)
       const float4 gb = __ldg(p.grp + (wbase >> 5));
       float lbv = 3.0e38f, ubv = 3.0e38f;
@@ -440,9 +466,6 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
       cand = __ballot_sync(0xffffffffu, is_cand);
       first = __reduce_min_sync(0xffffffffu, is_cand ? ((ordered_int(lbv) & ~31) | lane) : 0x7fffffff) & 31;
       if (cand == 0u) { cand = all_convex; first = -1; }   // only with non-finite bounds
-#if defined(FLASH_DYN_GROUPS) && !defined(FLASH_NO_SKIN_CULL)
-      else if (skin_pre) { skin_skip = s_skip[gcur]; if (skin_skip) cut0 = skin_cull_threshold(min_ub); }
-#endif
     }
     if (valid) {
       const float4 P = __ldg(p.pts + i);
