@@ -337,7 +337,10 @@ __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayou
 #ifndef FLASH_MINB
 #define FLASH_MINB 1
 #endif
-#define FLASH_MAX_TILE_GROUPS 512   // choose_tile keeps tiles at <= 16384 points
+#ifndef FLASH_MAX_TILE_GROUPS
+#define FLASH_MAX_TILE_GROUPS 1024   // choose_tile keeps tiles at <= 32768 points
+#endif
+constexpr size_t COST_STATIC_SMEM = (size_t)FLASH_MAX_TILE_GROUPS * 10 + 64;   // the group pre-pass tables of cost_kernel (static __shared__)
 template <bool GRAD, bool ARGMIN, bool DIST>
 __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
   extern __shared__ __align__(16) unsigned char smem[];

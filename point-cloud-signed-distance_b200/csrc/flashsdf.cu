@@ -172,7 +172,7 @@ int choose_tile(const flash_ctx* ctx, long long n, int C) {
   long long ppb = (n * C + target_blocks - 1) / target_blocks;
   ppb = ((ppb + CBLOCK - 1) / CBLOCK) * CBLOCK;
   if (ppb < CBLOCK) ppb = CBLOCK;
-  static const long long max_tile = [] { const char* e = getenv("FLASHSDF_TILE"); long long v = e ? atoll(e) : 0; return v >= CBLOCK ? v : (16384ll / CBLOCK) * CBLOCK; }();   // K5: 4032 -> 55.5 ms, 8064 -> 54.0, 16128 -> 53.5, 32256 -> 53.5
+  static const long long max_tile = [] { const char* e = getenv("FLASHSDF_TILE"); long long v = e ? atoll(e) : 0; return v >= CBLOCK ? v : (32768ll / CBLOCK) * CBLOCK; }();   // K5: 4032 -> 55.5 ms, 8064 -> 54.0, 16128 -> 53.5, 32256 -> 53.5; with the group pre-pass 16128 -> 45.4, 24576 -> 44.6, 32256 -> 44.5
   if (ppb > max_tile) ppb = max_tile;
   while ((n + ppb - 1) / ppb > 65535) ppb *= 2;
   return (int)ppb;
@@ -190,7 +190,7 @@ int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin) {
   if (ctx->n_pts == 0) return 0;
   const int tiles = (int)((ctx->n_pts + p.pts_per_block - 1) / p.pts_per_block);
   const size_t smem = cost_layout(ctx, grad).total;
-  if (smem > (size_t)ctx->smem_optin) return fail(ctx, FLASH_ERR_TOO_LARGE, "model geometry does not fit in shared memory (" + std::to_string(smem) + " bytes)");
+  if (smem + COST_STATIC_SMEM > (size_t)ctx->smem_optin) return fail(ctx, FLASH_ERR_TOO_LARGE, "model geometry does not fit in shared memory (" + std::to_string(smem) + " bytes)");
   if (grad) return d_argmin ? launch_cost_t<true, true, false>(ctx, p, C, tiles, smem) : launch_cost_t<true, false, false>(ctx, p, C, tiles, smem);
   return d_argmin ? launch_cost_t<false, true, false>(ctx, p, C, tiles, smem) : launch_cost_t<false, false, false>(ctx, p, C, tiles, smem);
 }
@@ -420,7 +420,7 @@ int flash_model_create(const flash_model_desc* desc, const flash_options* opt, f
   if (M.geo_f4) CUC(cudaMemcpy(ctx->d_geo_f4, ctx->hm.geo_f4.data(), M.geo_f4 * sizeof(F4), cudaMemcpyHostToDevice));
   if (M.geo_u32) CUC(cudaMemcpy(ctx->d_geo_u32, ctx->hm.geo_u32.data(), M.geo_u32 * sizeof(uint32_t), cudaMemcpyHostToDevice));
   const size_t smem = cost_layout(ctx, true).total;
-  if (smem > (size_t)ctx->smem_optin) { ctx->err = "model geometry does not fit in shared memory (" + std::to_string(smem) + " bytes)"; return bail(FLASH_ERR_TOO_LARGE); }
+  if (smem + COST_STATIC_SMEM > (size_t)ctx->smem_optin) { ctx->err = "model geometry does not fit in shared memory (" + std::to_string(smem) + " bytes)"; return bail(FLASH_ERR_TOO_LARGE); }
   if (ctx->hm.opt.sdf_mode == FLASH_SDF_GRID) { int rc = bake_grids(ctx); if (rc) return bail(rc); }
 #undef CUC
   *out = ctx;
