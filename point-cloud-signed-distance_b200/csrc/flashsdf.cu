@@ -172,7 +172,7 @@ int choose_tile(const flash_ctx* ctx, long long n, int C) {
   long long ppb = (n * C + target_blocks - 1) / target_blocks;
   ppb = ((ppb + CBLOCK - 1) / CBLOCK) * CBLOCK;
   if (ppb < CBLOCK) ppb = CBLOCK;
-  static const long long max_tile = [] { const char* e = getenv("FLASHSDF_TILE"); long long v = e ? atoll(e) : 0; return v >= CBLOCK ? v : (32768ll / CBLOCK) * CBLOCK; }();   // K5: 4032 -> 55.5 ms, 8064 -> 54.0, 16128 -> 53.5, 32256 -> 53.5; with the group pre-pass 16128 -> 45.4, 24576 -> 44.6, 32256 -> 44.5
+  static const long long max_tile = [] { const char* e = getenv("FLASHSDF_TILE"); long long v = e ? (atoll(e) / 32) * 32 : 0; return v >= CBLOCK ? v : (32768ll / CBLOCK) * CBLOCK; }();   // K5: 4032 -> 55.5 ms, 8064 -> 54.0, 16128 -> 53.5, 32256 -> 53.5; with the group pre-pass 16128 -> 45.4, 24576 -> 44.6, 32256 -> 44.5
   if (ppb > max_tile) ppb = max_tile;
   while ((n + ppb - 1) / ppb > 65535) ppb *= 2;
   return (int)ppb;
