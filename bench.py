@@ -345,6 +345,8 @@ def run_ours(args, rank, local_rank, world):
             line["grid_mode"] = grid_leg(args, flash, L, X, pts, n_local, cost.copy(), flush)
             line["tracking"] = tracking_leg(flash, L)
             line["other_configs"] = configs_leg(flash, L, args.steps)
+        if args.parity:
+            line["parity"] = parity_leg(flash, m, L, ctx, X, cost, grad, pts, n_local, N, rank, world)
         if args.cpu_baseline and world == 1:
             base = cpu_leg(args.ref_points, args.ref_configs, 1, 1)
             fast = cpu_leg(args.ref_points, args.ref_configs, 1, 0, method="adjoint")
@@ -355,6 +357,30 @@ def run_ours(args, rank, local_rank, world):
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def parity_leg(flash, m, L, ctx, X, cost, grad, pts_local, n_local, N, rank, world):
+    """Config 0 of the TIMED workload against the fp64 oracle (tests/oracle_lib, the checker -- never the thing
+    measured): cost and gradient over the whole global cloud, argmin over this rank's shard."""
+    import oracle_lib as ol
+    from flash._desc import c_double_p, c_int32_p
+    t0 = time.perf_counter()
+    o = ol.Oracle(m)
+    full = pts_local[:n_local] if world == 1 else scene_points(N)
+    co, go = o.cost_grad(X[0], full, method="adjoint", mode=ol.GJK)
+    arg = np.empty(n_local, np.int32)
+    c1 = np.empty(1)
+    m.check(L.flash_cost_grad(ctx, X[:1].ctypes.data_as(c_double_p), 1, 10.0, c1.ctypes.data_as(c_double_p), None, arg.ctypes.data_as(c_int32_p)))
+    _, ao = o.skin(X[0], pts_local[:n_local], mode=ol.GJK, argmin=True)
+    bad = np.nonzero(arg != ao)[0]
+    outside_band = 0
+    if len(bad):
+        per = np.sort(o.surfaces(X[0], pts_local[bad], mode=ol.GJK), axis=1)
+        outside_band = int(((per[:, 1] - per[:, 0]) > 2e-6 * np.maximum(1.0, np.abs(per[:, 0]))).sum())
+    return {"config": 0, "points": int(len(full)), "cost_rel": float(abs(cost[0] - co) / abs(co)), "grad_rel": float(np.abs(grad[0] - go).max() / np.abs(go).max()),
+            "argmin_flips": int(len(bad)), "argmin_flips_outside_2e-6_tie_band": outside_band, "argmin_points": int(n_local),
+            "oracle": "oracle/ fp64 C++ restatement, single-pass adjoint gradient, GJK distances, %d threads" % o.threads,
+            "seconds": time.perf_counter() - t0}
 
 
 def grid_leg(args, flash, L, X, pts, n_local, cost_exact, flush):
@@ -552,6 +578,7 @@ def main():
     ap.add_argument("--ref-points", type=int, default=1_000_000)
     ap.add_argument("--ref-configs", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
+    ap.add_argument("--no-parity", dest="parity", action="store_false", help="skip the oracle check of config 0 after the timed loops")
     ap.add_argument("--no-extras", dest="extras", action="store_false", help="skip the grid-mode and K3 tracking legs (N=1 only)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

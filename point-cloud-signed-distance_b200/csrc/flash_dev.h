@@ -22,8 +22,8 @@
 namespace flashdev {
 
 #if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
-struct Counters { long long points, narrow, inside, gjk_iters, plane_tests, vert_tests, lb_tests, skin64; unsigned exact_mask; };   // exact_mask: hulls whose narrow phase ran for the LAST point
-inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0, 0, 0, 0u}; return c; }
+struct Counters { long long points, narrow, inside, gjk_iters, plane_tests, vert_tests, lb_tests, skin64, feat_evals; unsigned exact_mask; };   // exact_mask: hulls whose narrow phase ran for the LAST point
+inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0u}; return c; }
 #define FLASH_COUNT(field, n) (flashdev::counters().field += (n))
 #else
 #define FLASH_COUNT(field, n) ((void)0)
@@ -624,8 +624,11 @@ FLASH_HD float hull_gjk_finish(const HullView& V, F3 q, float D, int fs, F3& nrm
   return dd * inv;
 }
 
-FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
+// kind_out (may be null): 0 = rejected by the cutoff, 1 = inside (fs = the plane of largest distance), 2 = outside with
+// the closest point interior to the start triangle of plane fs, 3 = outside with GJK's terminal simplex in S_out.
+FLASH_HD float hull_sd_ex(const HullView& V, F3 y, float cutoff, F3& nrm, int* kind_out, int* fs_out, Simplex* S_out) {
   float D = 0.f; int fs = 0;
+  if (kind_out) *kind_out = 0;
 #ifndef FLASH_NO_PLANEHINT
   const int hint = hull_plane_hint(V, y, cutoff, D, fs);
   FLASH_COUNT(plane_tests, 16);
@@ -639,7 +642,8 @@ FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
   FLASH_COUNT(plane_tests, V.np);
 #endif
   FLASH_COUNT(narrow, 1);
-  if (D <= 0.f) { FLASH_COUNT(inside, 1); nrm = plane_normal(V.planes, fs); return D; }
+  if (fs_out) *fs_out = fs;
+  if (D <= 0.f) { FLASH_COUNT(inside, 1); if (kind_out) *kind_out = 1; nrm = plane_normal(V.planes, fs); return D; }
   Simplex S;
   F3 q;
   const bool certified = hull_gjk_start(V, y, fs, S, q);
@@ -655,7 +659,116 @@ FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) {
 #endif
     if (!hull_gjk_update(V, y, iw, S, q)) break;
   }
+  if (kind_out) *kind_out = certified ? 2 : 3;
+  if (S_out) *S_out = S;
   return hull_gjk_finish(V, q, D, fs, nrm);
+}
+FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) { return hull_sd_ex(V, y, cutoff, nrm, nullptr, nullptr, nullptr); }
+
+// ---- group feature certification ---------------------------------------------------------------------------------
+// The 32 points one warp evaluates together are Morton neighbours inside a ball B(c, rho) (points_groups_kernel).
+// If the whole ball lies in the Voronoi region of ONE feature of the hull -- a face, an edge or a vertex -- every
+// point's distance is a closed form of that feature and the per-point narrow phase (plane hint, start triangle,
+// GJK iterations, support queries) is not needed at all.  The cost kernel's group pre-pass (one thread per group)
+// runs the narrow phase once at the ball centre, takes the closest feature from it and certifies it for the ball
+// by the projection theorem -- x* in H is the closest point of x iff (x - x*).(z - x*) <= 0 for every z in H -- whose
+// conditions are LINEAR in x for a fixed feature, so their maximum over a ball is the value at the centre plus rho
+// times a norm:
+//   vertex v        (x - v).(v_k - v) <= 0 for every hull vertex k
+//   edge (a, b)     0 <= (x - a).e <= |b - a| (e the unit direction), and (x - a).w_k <= 0 with w_k the part of
+//                   v_k - a orthogonal to e
+//   face f          the projection x' of x onto the plane of f lies in H: n_g.x' - o_g <= 0 for every plane g (points
+//                   outside), and f is the plane of largest distance: n_f.x - o_f >= n_g.x - o_g (points inside)
+// A feature is a u32: type (bits 0-1: 0 none, 1 vertex, 2 edge, 3 face) | ia << 8 | ib << 16 (vertices) or
+// plane slot << 8 (face).  All tests carry an absolute slack for the fp32 centre transform; a point that is outside
+// its certified region by a rounding error delta gets a distance that is wrong by O(delta^2 / d) only.
+enum { FEAT_NONE = 0, FEAT_VERTEX = 1, FEAT_EDGE = 2, FEAT_FACE = 3 };
+FLASH_HD unsigned hull_ball_feature(const HullView& V, F3 yc, float rho, float& d_centre) {
+  F3 n; int kind = 0, fs = 0; Simplex S;
+  S.ns = 0; S.ia = S.ib = S.ic = 0; S.a = S.b = S.c = f3(0.f, 0.f, 0.f);
+  const float D = hull_sd_ex(V, yc, 3.0e38f, n, &kind, &fs, &S);
+  d_centre = D;
+  const float r = rho * (1.f + 1e-5f) + 1e-5f;   // ball radius + slack for the fp32 transform of the centre
+  if (kind == 3 && S.ns == 3) {
+    // GJK ended in the interior of a triangle of hull vertices: it lies on a supporting plane, i.e. on the face
+    // whose plane is the farthest one from yc (every plane distance is a lower bound of the true distance)
+    float Dp; int fp;
+    if (!hull_plane_scan(V, yc, 3.0e38f, Dp, fp)) return FEAT_NONE;
+    fs = fp; kind = 2;
+  }
+  if (kind == 1 || kind == 2) {
+    // face fs
+    const F3 nf = plane_normal(V.planes, fs);
+    if (!(dot(nf, nf) > 0.5f)) return FEAT_NONE;
+    const float* pf = reinterpret_cast<const float*>(V.planes + (fs & ~1));
+    const float df = fmaf(nf.x, yc.x, fmaf(nf.y, yc.y, fmaf(nf.z, yc.z, pf[6 + (fs & 1)])));   // n_f.yc - o_f
+    const bool dips_inside = df - r < 0.f, pokes_outside = df + r > 0.f;
+    for (int g = 0; g < V.np; ++g) {
+      if (g == fs) continue;
+      const float* pg = reinterpret_cast<const float*>(V.planes + (g & ~1)); const int h = g & 1;
+      const F3 ng = f3(pg[h], pg[2 + h], pg[4 + h]);
+      const float dg = fmaf(ng.x, yc.x, fmaf(ng.y, yc.y, fmaf(ng.z, yc.z, pg[6 + h])));
+      const float c = dot(ng, nf);
+      // outside points: projection onto plane f stays inside plane g
+      if (pokes_outside && !(dg - df * c + r * sqrtf(fmaxf(1.f - c * c, 0.f) + 1e-6f) <= 0.f)) return FEAT_NONE;
+      // inside points: plane f has the largest distance
+      if (dips_inside && !(df - dg - r * sqrtf(fmaxf(2.f - 2.f * c, 0.f) + 1e-6f) >= 0.f)) return FEAT_NONE;
+    }
+    return FEAT_FACE | ((unsigned)fs << 8);
+  }
+  if (kind != 3 || !(D - r > 0.f)) return FEAT_NONE;   // vertex / edge regions: the ball must be outside the hull
+  if (S.ns == 1) {
+    const F3 v = S.a + yc;       // simplex coordinates are relative to the query point
+    const F3 u = yc - v;
+    for (int k = 0; k < V.nv; ++k) {
+      const F3 e = vert_at(V, k) - v;
+      const float ee = dot(e, e);
+      if (!(dot(u, e) + r * sqrtf(ee) <= 0.f)) return FEAT_NONE;
+    }
+    return FEAT_VERTEX | ((unsigned)S.ia << 8);
+  }
+  if (S.ns == 2) {
+    const F3 a = S.a + yc, b = S.b + yc;
+    F3 e = b - a;
+    const float len2 = dot(e, e);
+    if (!(len2 > 0.f)) return FEAT_NONE;
+    const float len = sqrtf(len2);
+    e = e * (1.f / len);
+    const F3 u = yc - a;
+    const float t = dot(u, e);
+    if (!(t - r >= 0.f && t + r <= len)) return FEAT_NONE;
+    for (int k = 0; k < V.nv; ++k) {
+      const F3 vk = vert_at(V, k) - a;
+      const F3 w = vk - e * dot(vk, e);
+      if (!(dot(u, w) + r * sqrtf(dot(w, w)) <= 0.f)) return FEAT_NONE;
+    }
+    return FEAT_EDGE | ((unsigned)S.ia << 8) | ((unsigned)S.ib << 16);
+  }
+  return FEAT_NONE;
+}
+// distance and gradient of y to a certified feature
+FLASH_HD float hull_feature_eval(const HullView& V, unsigned feat, F3 y, F3& nrm) {
+  const unsigned type = feat & 3u;
+  if (type == FEAT_FACE) {
+    const int fs = (int)(feat >> 8);
+    const float* pf = reinterpret_cast<const float*>(V.planes + (fs & ~1)); const int h = fs & 1;
+    nrm = f3(pf[h], pf[2 + h], pf[4 + h]);
+    return fmaf(nrm.x, y.x, fmaf(nrm.y, y.y, fmaf(nrm.z, y.z, pf[6 + h])));
+  }
+  F3 u = y - vert_at(V, (int)((feat >> 8) & 255u));
+  if (type == FEAT_EDGE) {
+    const F3 e = vert_at(V, (int)((feat >> 16) & 255u)) - vert_at(V, (int)((feat >> 8) & 255u));
+    u = u - e * (dot(u, e) / dot(e, e));
+  }
+  const float dd = dot(u, u);
+#ifdef __CUDA_ARCH__
+  float inv = rsqrtf(dd);
+  inv = inv * (1.5f - 0.5f * dd * inv * inv);
+#else
+  const float inv = 1.0f / sqrtf(dd);
+#endif
+  nrm = u * inv;
+  return dd * inv;
 }
 
 // conservative lower bound of the signed distance from the AABB of the hull
@@ -971,6 +1084,41 @@ FLASH_HD unsigned group_skin_cull(const HotModel& M, const float* __restrict__ t
   return skip;
 }
 
+// The whole group pre-pass of cost_kernel for one group (ball c, rho) of one configuration:
+//   cand / first   hulls that can be the minimum for some point of the ball, the most promising one
+//   feat           certified closest feature of `first` for the whole ball (hull_ball_feature), 0 if none
+//   skip / cut     skins that are the minimum for no point of the ball; upper bound of the group's minimum
+// The exact distance of `first` at the ball centre (a by-product of the feature search) tightens the upper bound
+// of the group's minimum from |c - centroid| - inradius + rho to d(c) + rho, which culls more hulls and skins.
+struct GroupPre { unsigned cand; int first; unsigned feat; unsigned skip; float cut; };
+FLASH_HD GroupPre group_prepass(const HotModel& M, const GeoView& G, const float* __restrict__ tabf, float cx, float cy, float cz, float rho,
+                                bool want_feat, bool want_skin_cull) {
+  GroupPre o; o.cand = 0u; o.first = -1; o.feat = 0u; o.skip = 0u; o.cut = 3.0e38f;
+  const int nc = M.n_convex;
+  float min_ub = 3.0e38f, lb0 = 3.0e38f;
+  for (int j = 0; j < nc; ++j) {
+    float lbv, ubv;
+    hull_ball_bounds(M.cvx[j], tabf + 12 * j, cx, cy, cz, rho, lbv, ubv);
+    min_ub = fminf(min_ub, ubv);
+    if (lbv < lb0) { lb0 = lbv; o.first = j; }
+  }
+  if (want_feat && o.first >= 0) {
+    const ConvexC& C = M.cvx[o.first];
+    float dc;
+    o.feat = hull_ball_feature(hull_view(G, C), to_geometry_f32(tabf + 12 * o.first, cx, cy, cz), rho, dc);
+    const float ub2 = dc + rho * (1.f + 1e-5f) + 1e-5f;   // 1-Lipschitz: d(x) <= d(c) + rho
+    if (dc < 3.0e37f) min_ub = fminf(min_ub, ub2);
+  }
+  for (int j = 0; j < nc; ++j) {
+    float lbv, ubv;
+    hull_ball_bounds(M.cvx[j], tabf + 12 * j, cx, cy, cz, rho, lbv, ubv);
+    if (lbv <= min_ub || j == o.first) o.cand |= 1u << j;
+  }
+  if (o.cand == 0u) { o.cand = nc >= 32 ? 0xffffffffu : ((1u << nc) - 1u); o.first = -1; o.feat = 0u; return o; }   // only with non-finite bounds
+  if (want_skin_cull && M.n_skins > 0 && M.n_skins <= 8) o.skip = group_skin_cull(M, tabf, cx, cy, cz, rho, min_ub, o.cut);
+  return o;
+}
+
 // Evaluates skin(x) = min over all surfaces for one world point under one configuration.
 // `cand` = bit mask of the convex slots to consider (group_candidates, or all ones), `first` = the
 // slot to evaluate first (-1: chosen here from the per-point bounds).  Within the candidates a body is
@@ -980,7 +1128,7 @@ FLASH_HD unsigned group_skin_cull(const HotModel& M, const float* __restrict__ t
 // fp64 sample positions.
 FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __restrict__ tab, const float* __restrict__ tabf,
                          double px, double py, double pz, unsigned cand, int first, bool use_grid, bool fp32_point, PointEval& out,
-                         unsigned skin_skip = 0u, float cut0 = 3.0e38f) {
+                         unsigned skin_skip = 0u, float cut0 = 3.0e38f, unsigned feat = 0u) {
   const ConvexC* __restrict__ cvx = M.cvx;
   float best = 3.0e38f; int arg = 0x7fffffff; int slot = -1; int is_skin = 0;
   out.y = f3(0, 0, 0); out.n = f3(0, 0, 0);
@@ -1034,6 +1182,16 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
       rest &= rest - 1u;
     }
     const ConvexC& C = cvx[j];
+    if ((feat & 3u) != 0u && j == first) {
+      // the group's ball lies in the Voronoi region of one feature of this hull (hull_ball_feature): closed form
+      FLASH_COUNT(feat_evals, 1);
+      const F3 y = to_geometry(tab + 12 * j, px, py, pz);
+      F3 n;
+      const float d = hull_feature_eval(hull_view(G, C), feat, y, n);
+      if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
+      j = -1;
+      continue;
+    }
     bool skip = false;
     if (!single) {
       FLASH_COUNT(lb_tests, 1);

@@ -340,7 +340,7 @@ __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayou
 #ifndef FLASH_MAX_TILE_GROUPS
 #define FLASH_MAX_TILE_GROUPS 1024   // choose_tile keeps tiles at <= 32768 points
 #endif
-constexpr size_t COST_STATIC_SMEM = (size_t)FLASH_MAX_TILE_GROUPS * 10 + 64;   // the group pre-pass tables of cost_kernel (static __shared__)
+constexpr size_t COST_STATIC_SMEM = (size_t)FLASH_MAX_TILE_GROUPS * 14 + 64;   // the group pre-pass tables of cost_kernel (static __shared__)
 template <bool GRAD, bool ARGMIN, bool DIST>
 __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -391,29 +391,25 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   //   s_thr          : upper bound of the group's minimum, the hull scans' cutoff when a skin is skipped
   __shared__ unsigned s_cand[FLASH_MAX_TILE_GROUPS];
   __shared__ float s_thr[FLASH_MAX_TILE_GROUPS];
+  __shared__ unsigned s_feat[FLASH_MAX_TILE_GROUPS];         // certified closest feature of hull `first` for the whole group (hull_ball_feature)
   __shared__ unsigned short s_meta[FLASH_MAX_TILE_GROUPS];   // first << 8 | skip bits (first = 255: none)
   const bool grp_pre = !DIST && p.grp != nullptr && n_convex > 1 && ngroups <= FLASH_MAX_TILE_GROUPS;
   if (grp_pre)
     for (int gi = tid; gi < ngroups; gi += CBLOCK) {
       const float4 gb = __ldg(p.grp + ((tile0 >> 5) + gi));
-      float min_ub = 3.0e38f;
-      for (int j = 0; j < n_convex; ++j) {
-        float lbv, ubv;
-        hull_ball_bounds(H.cvx[j], tabf + 12 * j, gb.x, gb.y, gb.z, gb.w, lbv, ubv);
-        min_ub = fminf(min_ub, ubv);
-      }
-      unsigned cm = 0u; int best = 0x7fffffff;
-      for (int j = 0; j < n_convex; ++j) {
-        float lbv, ubv;
-        hull_ball_bounds(H.cvx[j], tabf + 12 * j, gb.x, gb.y, gb.z, gb.w, lbv, ubv);
-        if (lbv <= min_ub) { cm |= 1u << j; best = min(best, (ordered_int(lbv) & ~31) | j); }
-      }
-      unsigned skip = 0u; float thr = 3.0e38f; int fi = best & 31;
-      if (cm == 0u) { cm = all_convex; fi = 255; }   // only with non-finite bounds
 #ifndef FLASH_NO_SKIN_CULL
-      else if (H.n_skins > 0 && H.n_skins <= 8) skip = group_skin_cull(H, tabf, gb.x, gb.y, gb.z, gb.w, min_ub, thr);
+      const bool want_cull = true;
+#else
+      const bool want_cull = false;
 #endif
-      s_cand[gi] = cm; s_thr[gi] = thr; s_meta[gi] = (unsigned short)((fi << 8) | skip);
+#ifndef FLASH_NO_FEATURES
+      const bool want_feat = p.use_grid == 0;
+#else
+      const bool want_feat = false;
+#endif
+      const GroupPre gp = group_prepass(H, G, tabf, gb.x, gb.y, gb.z, gb.w, want_feat, want_cull);
+      s_cand[gi] = gp.cand; s_thr[gi] = gp.cut; s_feat[gi] = gp.feat;
+      s_meta[gi] = (unsigned short)(((gp.first < 0 ? 255 : gp.first) << 8) | gp.skip);
     }
 #else
   const bool grp_pre = false;
@@ -450,13 +446,13 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     float px = 0.f, py = 0.f, pz = 0.f;
     // hulls that can be the minimum for some point of this warp's 32 Morton neighbours: lane j bounds hull j
     unsigned cand = all_convex; int first = -1;
-    unsigned skin_skip = 0u; float cut0 = 3.0e38f;
+    unsigned skin_skip = 0u; float cut0 = 3.0e38f; unsigned feat = 0u;
 #ifdef FLASH_DYN_GROUPS
     if (grp_pre) {
 #ifndef FLASH_NO_GROUP_PREPASS
       const unsigned m = s_meta[gcur];
       cand = s_cand[gcur]; first = (m >> 8) == 255u ? -1 : (int)(m >> 8);
-      skin_skip = m & 255u; cut0 = s_thr[gcur];
+      skin_skip = m & 255u; cut0 = s_thr[gcur]; feat = s_feat[gcur];
 #endif
     } else
 #endif
@@ -473,7 +469,7 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     if (valid) {
       const float4 P = __ldg(p.pts + i);
       px = P.x; py = P.y; pz = P.z;
-      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, cand, first, p.use_grid != 0, true, e, skin_skip, cut0);
+      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, cand, first, p.use_grid != 0, true, e, skin_skip, cut0, feat);
     }
     if (DIST) {
       if (valid) {

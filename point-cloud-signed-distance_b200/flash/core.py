@@ -92,6 +92,7 @@ class Manipulator:  # src/Flash.jl:62-65
         self.surfaces = list(surfaces)
         self._ctx = None
         self._packed = None
+        self._points_owner = None   # the CostFunctor whose cloud the ctx currently holds
         self._options = dict(sdf_mode=SDF_EXACT, grid_spacing=0.0, grid_margin=0.0,
                              rbf_normalize_by_gradient=1, rbf_polynomial_degree=1, device=-1)
 
@@ -111,6 +112,7 @@ class Manipulator:  # src/Flash.jl:62-65
             _lib.lib().flash_destroy(self._ctx)
         self._ctx = None
         self._packed = None
+        self._points_owner = None
 
     def packed(self):
         if self._packed is None:

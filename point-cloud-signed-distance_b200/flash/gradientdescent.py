@@ -29,8 +29,11 @@ def cost(state, sensed_points, deformation_cost_weight=default_deformation_cost_
 class CostFunctor:  # src/gradientdescent.jl:41-57
     """cost = CostFunctor(manipulator, sensed_points); cost(x) -> raw cost (not divided by N).
 
-    The points are uploaded once (the functor captures them, as in the reference); every call is one
-    flash_cost_grad launch.  Batched forms (`batch`) evaluate C candidate states at once.
+    The functor captures its points, as in the reference (src/gradientdescent.jl:41-47).  The manipulator's
+    flash_ctx holds ONE frame at a time, so the manipulator remembers which functor uploaded last
+    (`_points_owner`) and a functor whose cloud was displaced re-uploads it before its next call: two functors
+    on one manipulator never evaluate on each other's points.  Every call is one flash_cost_grad launch.
+    Batched forms (`batch`) evaluate C candidate states at once.
     """
 
     def __init__(self, manipulator, sensed_points):
@@ -42,6 +45,7 @@ class CostFunctor:  # src/gradientdescent.jl:41-57
     def upload(self):
         m = self.manipulator
         m.check(_lib.lib().flash_points_set(m.ctx(), self.sensed_points.ctypes.data_as(c_double_p), len(self.sensed_points)))
+        m._points_owner = self
 
     def batch(self, X, gradient=True, argmin=False, deformation_cost_weight=default_deformation_cost_weight):
         m = self.manipulator
@@ -52,6 +56,10 @@ class CostFunctor:  # src/gradientdescent.jl:41-57
         if X.shape[1] != nx:
             raise ValueError("state vector has %d entries, expected %d" % (X.shape[1], nx))
         Cn = X.shape[0]
+        if m._points_owner is not self or m._ctx is None:
+            self.upload()          # another functor (or a rebuilt ctx) replaced this functor's cloud
+        if _lib.lib().flash_num_points(m.ctx()) != len(self.sensed_points):
+            raise RuntimeError("flash ctx holds %d points, this functor %d" % (_lib.lib().flash_num_points(m.ctx()), len(self.sensed_points)))
         cost = np.empty(Cn)
         grad = np.empty((Cn, nx)) if gradient else None
         arg = np.empty((Cn, len(self.sensed_points)), dtype=np.int32) if argmin else None

@@ -16,6 +16,8 @@ using namespace flashhost;
 struct HC { HostModel hm; HotModel hot; };
 static int g_group_cull = 1;            // replay the warp-level hull culling of cost_kernel
 static int g_skin_cull = 1;             // ... and the group-level skin cull
+static int g_feat = 1;                  // ... and the group feature certification
+static long long g_feat_groups[4] = {0, 0, 0, 0};
 static long long g_skin_groups_skipped = 0;
 static long long g_cand_total = 0, g_groups = 0, g_rounds_or = 0, g_rounds_max = 0;
 static unsigned g_or = 0; static int g_max = 0;
@@ -85,7 +87,7 @@ void hc_accumulate(void* p, const double* tab, const float* pts, long long n, in
   tabf_fill(H, tab, tabf, 0, 1);
   const unsigned all_convex = H.n_convex >= 32 ? 0xffffffffu : ((1u << H.n_convex) - 1u);
   unsigned cand = all_convex; int first = -1;
-  unsigned skin_skip = 0u; float cut0 = 3.0e38f;
+  unsigned skin_skip = 0u; float cut0 = 3.0e38f; unsigned feat = 0u;
   for (long long i = 0; i < n; ++i) {
     if (g_group_cull && (i & 31) == 0 && H.n_convex > 1) {
       // the warp's 32 points: bounding ball as points_groups_kernel computes it, then the candidate hulls
@@ -95,18 +97,17 @@ void hc_accumulate(void* p, const double* tab, const float* pts, long long n, in
       const float cx = 0.5f * (lo[0] + hi[0]), cy = 0.5f * (lo[1] + hi[1]), cz = 0.5f * (lo[2] + hi[2]);
       const float ex = fmaxf(hi[0] - cx, cx - lo[0]), ey = fmaxf(hi[1] - cy, cy - lo[1]), ez = fmaxf(hi[2] - cz, cz - lo[2]);
       const float rho = sqrtf(ex * ex + ey * ey + ez * ez) * (1.f + 1e-6f) + 1e-30f;
-      float min_ub;
-      cand = group_candidates(H, tabf, cx, cy, cz, rho, first, &min_ub);
+      const GroupPre gp = group_prepass(H, G, tabf, cx, cy, cz, rho, g_feat != 0, g_skin_cull != 0);
+      cand = gp.cand; first = gp.first; skin_skip = gp.skip; cut0 = gp.cut; feat = gp.feat;
       g_cand_total += __builtin_popcount(cand); g_groups += 1;
-      skin_skip = 0u; cut0 = 3.0e38f;
-      if (g_skin_cull && H.n_skins > 0) skin_skip = group_skin_cull(H, tabf, cx, cy, cz, rho, min_ub, cut0);
       g_skin_groups_skipped += skin_skip ? 1 : 0;
+      g_feat_groups[feat & 3u] += 1;
     }
     PointEval e;
 #ifdef FLASH_COUNTERS
     counters().exact_mask = 0u;
 #endif
-    eval_point(H, G, tab, tabf, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], cand, first, use_grid != 0, true, e, skin_skip, cut0);
+    eval_point(H, G, tab, tabf, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], cand, first, use_grid != 0, true, e, skin_skip, cut0, feat);
 #ifdef FLASH_COUNTERS
     // exact narrow-phase rounds a warp of 32 consecutive points executes: one per hull ANY lane evaluates (the
     // kernel's candidate loop is warp-uniform) vs the most any single lane needs
@@ -146,6 +147,9 @@ void hc_epilogue(void* p, const double* x, const double* tab, const double* aux,
 
 void hc_set_group_cull(int on) { g_group_cull = on; }
 void hc_set_skin_cull(int on) { g_skin_cull = on; }
+void hc_set_feature(int on) { g_feat = on; }
+// groups by certified feature type: none, vertex, edge, face
+void hc_feature_stats(long long* out, int reset) { for (int k = 0; k < 4; ++k) { out[k] = g_feat_groups[k]; if (reset) g_feat_groups[k] = 0; } }
 long long hc_skin_groups_skipped(int reset) { long long v = g_skin_groups_skipped; if (reset) g_skin_groups_skipped = 0; return v; }
 // certified lower bound of skin k over a ball (tab = prepared fp64 table of one config)
 float hc_skin_ball_lower(void* p, const double* tab, int k, float cx, float cy, float cz, float rho) {
@@ -165,9 +169,10 @@ void hc_counters(long long* out, int reset) {
 #ifdef FLASH_COUNTERS
   Counters& c = counters();
   out[0] = c.points; out[1] = c.narrow; out[2] = c.inside; out[3] = c.gjk_iters; out[4] = c.plane_tests; out[5] = c.vert_tests; out[6] = c.lb_tests; out[7] = c.skin64;
-  if (reset) c = Counters{0, 0, 0, 0, 0, 0, 0, 0};
+  out[8] = c.feat_evals;
+  if (reset) c = Counters{0, 0, 0, 0, 0, 0, 0, 0, 0, 0u};
 #else
-  for (int i = 0; i < 8; ++i) out[i] = -1;
+  for (int i = 0; i < 9; ++i) out[i] = -1;
 #endif
 }
 

@@ -49,6 +49,8 @@ def lib():
         L.hc_set_group_cull.argtypes = [C.c_int]; L.hc_set_group_cull.restype = None
         L.hc_group_stats.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_group_stats.restype = None
         L.hc_set_skin_cull.argtypes = [C.c_int]; L.hc_set_skin_cull.restype = None
+        L.hc_set_feature.argtypes = [C.c_int]; L.hc_set_feature.restype = None
+        L.hc_feature_stats.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_feature_stats.restype = None
         L.hc_skin_groups_skipped.argtypes = [C.c_int]; L.hc_skin_groups_skipped.restype = C.c_longlong
         L.hc_skin_ball_lower.argtypes = [vp, c_double_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]; L.hc_skin_ball_lower.restype = C.c_float
         _lib = L
@@ -129,9 +131,9 @@ class HostCheck:
 
 
 def counters(reset=True):
-    out = (C.c_longlong * 8)()
+    out = (C.c_longlong * 9)()
     lib().hc_counters(out, 1 if reset else 0)
-    return dict(zip(("points", "narrow", "inside", "gjk_iters", "plane_tests", "vert_tests", "lb_tests", "skin64"), list(out)))
+    return dict(zip(("points", "narrow", "inside", "gjk_iters", "plane_tests", "vert_tests", "lb_tests", "skin64", "feat_evals"), list(out)))
 
 
 def set_group_cull(on):
@@ -140,6 +142,16 @@ def set_group_cull(on):
 
 def set_skin_cull(on):
     lib().hc_set_skin_cull(1 if on else 0)
+
+
+def set_feature(on):
+    lib().hc_set_feature(1 if on else 0)
+
+
+def feature_stats(reset=True):
+    out = (C.c_longlong * 4)()
+    lib().hc_feature_stats(out, 1 if reset else 0)
+    return dict(zip(("none", "vertex", "edge", "face"), list(out)))
 
 
 def skin_groups_skipped(reset=True):

@@ -405,3 +405,23 @@ def test_contour_mesh_lies_on_the_zero_level_set():
     m.check(_lib.lib().flash_contour_mesh(m.ctx(), x.ctypes.data_as(c_double_p), -1, lo.ctypes.data_as(c_double_p), hi.ctypes.data_as(c_double_p), 0.02, 0.0,
                                           None, 0, C.byref(n)))
     assert n.value == len(t3)
+
+
+def test_two_functors_on_one_manipulator_keep_their_own_points():
+    """The reference's CostFunctor captures its own sensed_points (src/gradientdescent.jl:41-47); the ctx holds
+    one frame, so a displaced functor must re-upload instead of evaluating on the other functor's cloud."""
+    rng = np.random.default_rng(21)
+    m = flash.models.irb140()
+    x = rng.uniform(-1, 1, 6)
+    pa = _points(rng, 5000, [-0.6, -0.7, -0.2], [0.9, 0.7, 1.1])
+    pb = _points(rng, 12000, [-0.6, -0.7, -0.2], [0.9, 0.7, 1.1])
+    fa = flash.gradientdescent.CostFunctor(m, pa)
+    ca = fa(x)
+    fb = flash.gradientdescent.CostFunctor(m, pb)      # replaces the ctx's cloud
+    cb = fb(x)
+    # (fp64 atomics: repeated calls agree to rounding unless the ctx is deterministic)
+    assert np.isclose(fa(x), ca, rtol=1e-12) and np.isclose(fb(x), cb, rtol=1e-12) and abs(ca - cb) > 1e-3 * ca
+    _, _, arg = fa.batch(x, argmin=True)                # sized from fa's own cloud
+    assert arg.shape == (1, 5000)
+    assert np.isclose(flash.gradientdescent.cost(flash.ManipulatorState(m), pb), fb(np.zeros(6)), rtol=1e-12)
+    assert np.isclose(fa(x), ca, rtol=1e-12)

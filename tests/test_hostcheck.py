@@ -125,13 +125,52 @@ def test_warp_group_culling_changes_nothing_and_culls():
     # a dense slab (K5 density: ~6,700 points per litre) so that 32 Morton neighbours span ~2 cm
     pts = rng.uniform([-0.4, -0.3, 0.0], [0.6, 0.3, 0.3], (1_200_000, 3)).astype(np.float32)
     pts = _morton_sorted(pts, bits=6)[: 32 * 3000]
-    hl.set_group_cull(False)
-    a0, d0, g0 = h.accumulate(tab, pts)
-    hl.set_group_cull(True); hl.group_stats()
-    a1, d1, g1 = h.accumulate(tab, pts)
-    st = hl.group_stats()
+    try:
+        hl.set_feature(False)                      # culling alone: bit-identical
+        hl.set_group_cull(False)
+        a0, d0, g0 = h.accumulate(tab, pts)
+        hl.set_group_cull(True); hl.group_stats()
+        a1, d1, g1 = h.accumulate(tab, pts)
+        st = hl.group_stats()
+    finally:
+        hl.set_feature(True); hl.set_group_cull(True)
     assert np.array_equal(d0, d1) and np.array_equal(g0, g1) and np.array_equal(a0, a1)
     assert st["groups"] == 3000 and st["candidates"] / st["groups"] < 5.0   # 8 hulls in the model
+
+
+def test_group_feature_certification_is_exact_and_fires():
+    """hull_ball_feature: groups whose bounding ball lies in the Voronoi region of one face / edge / vertex of the
+    nearest hull evaluate that hull by the feature's closed form.  Same distances as the GJK path to fp32 rounding
+    (and as the fp64 oracle), same argmin; the exact centre distance also tightens the group's hull and skin culls."""
+    rng = np.random.default_rng(12)
+    m = flash.models.irb_and_squishable()
+    h = hl.HostCheck(m)
+    x = GOLD["irb_and_squishable/x"]
+    tab, _ = h.prepare(x)
+    # tight clusters (1 cm) at all distances from the scene, plus clusters ON the hull surfaces (depth-frame regime)
+    ctr = rng.uniform([-0.8, -0.8, -0.3], [1.0, 0.8, 1.2], (3000, 1, 3))
+    pts = (ctr + rng.uniform(-0.01, 0.01, (3000, 32, 3))).reshape(-1, 3).astype(np.float32)
+    o = ol.Oracle(m)
+    d_or, a_or = o.skin(x, pts.astype(np.float64), mode=ol.GJK, argmin=True)
+    near = np.abs(d_or) < 0.01
+    pts = np.concatenate([pts, pts[near][: 32 * (near.sum() // 32)]])
+    d_or, a_or = o.skin(x, pts.astype(np.float64), mode=ol.GJK, argmin=True)
+    try:
+        hl.set_feature(False)
+        a0, d0, g0 = h.accumulate(tab, pts)
+        hl.set_feature(True); hl.feature_stats(); hl.counters()
+        a1, d1, g1 = h.accumulate(tab, pts)
+        fs = hl.feature_stats(); cn = hl.counters()
+    finally:
+        hl.set_feature(True)
+    assert np.abs(d1 - d0).max() < 3e-7 and np.abs(d1 - d_or).max() < 3e-7
+    flips = np.nonzero(g1 != a_or)[0]
+    per = np.sort(o.surfaces(x, pts[flips].astype(np.float64), mode=ol.GJK), axis=1) if len(flips) else np.zeros((0, 2))
+    assert len(flips) <= 4 and (per[:, 1] - per[:, 0] < 2e-6).all()
+    assert np.abs(a1 - a0).max() <= 1e-6 * np.abs(a0).max()
+    groups = sum(fs.values())
+    assert fs["vertex"] > 0 and fs["edge"] > 0 and fs["face"] > 0 and fs["none"] < 0.8 * groups
+    assert cn["feat_evals"] > 0.2 * cn["points"]
 
 
 @pytest.mark.parametrize("name", ["irb_and_squishable", "squishable", "two_link_arm", "beanbag"])
@@ -192,13 +231,14 @@ def test_group_skin_cull_never_changes_the_result():
     ctr = rng.uniform([-0.8, -0.8, -0.3], [1.0, 0.8, 1.2], (2000, 1, 3))
     pts = np.concatenate([(ctr + rng.uniform(-0.015, 0.015, (2000, 32, 3))).reshape(-1, 3), GOLD["irb_and_squishable/pts"]]).astype(np.float32)
     try:
+        hl.set_feature(False)
         hl.set_skin_cull(True); hl.skin_groups_skipped()
         a1, d1, g1 = h.accumulate(tab, pts)
         skipped = hl.skin_groups_skipped()
         hl.set_skin_cull(False)
         a0, d0, g0 = h.accumulate(tab, pts)
     finally:
-        hl.set_skin_cull(True)
+        hl.set_skin_cull(True); hl.set_feature(True)
     assert np.array_equal(d0, d1) and np.array_equal(g0, g1) and np.array_equal(a0, a1)
     assert skipped > 0.2 * len(pts) / 32
 
