@@ -134,9 +134,37 @@ int flash_num_surfaces(const flash_ctx* ctx);
  * rounded to fp32 on upload (stated in DESIGN.md). */
 int flash_points_set(flash_ctx* ctx, const double* xyz, int64_t n);
 int flash_points_set_f32(flash_ctx* ctx, const float* xyz, int64_t n);
-/* zero-copy: a device buffer of n float4 {x,y,z,unused} that stays valid until replaced */
+/* zero-copy: a device buffer of n float4 {x,y,z,unused}, evaluated in the caller's order (no sort; group balls only).
+ * The buffer must stay valid AND UNCHANGED until it is replaced by another flash_points_set* call: the group
+ * balls computed here bound its contents, and the producer's work must be complete before the call. */
 int flash_points_set_device(flash_ctx* ctx, const void* device_float4, int64_t n);
 int64_t flash_num_points(const flash_ctx* ctx);
+
+/*
+ * Frame pipelining (the live loop of examples/irb_and_squishable.ipynb:495-503 evaluates frame k while frame k+1
+ * arrives).  The ctx owns TWO point sets and a copy stream: flash_points_set_async uploads, Hilbert-sorts and groups
+ * the next frame into the back set while kernels issued on the compute stream keep reading the front set;
+ * flash_points_swap makes the back set current for every LATER call (stream-ordered, it does not block the host).
+ * Pageable caller memory is staged into a pinned ring inside the ctx before the call returns; pinned caller memory
+ * (cudaHostAlloc / cudaHostRegister) is read by DMA and must stay valid until the first compute call after the swap
+ * has returned (or flash_points_sync).
+ */
+int flash_points_set_async(flash_ctx* ctx, const double* xyz, int64_t n);
+int flash_points_set_async_f32(flash_ctx* ctx, const float* xyz, int64_t n);
+int flash_points_swap(flash_ctx* ctx);
+int flash_points_sync(flash_ctx* ctx);   /* host-blocks until every upload issued so far has finished */
+
+/*
+ * A batch of F frames (BASELINE.json configs[3]: 8 Kinect frames x 16 candidate configurations per frame).  Frame f is
+ * xyz[f][counts[f]][3]; all frames are uploaded, sorted and grouped in one pass (F <= FLASH_MAX_FRAMES).
+ * flash_cost_grad_frames then evaluates C candidate states PER FRAME in one launch: X is [F][C][nx], cost [F][C],
+ * grad [F][C][nx] (may be NULL); state X[f][c] sees frame f only.
+ */
+#define FLASH_MAX_FRAMES 64
+int flash_frames_set(flash_ctx* ctx, const double* const* xyz, const int64_t* counts, int32_t F);
+int flash_frames_set_async(flash_ctx* ctx, const double* const* xyz, const int64_t* counts, int32_t F);
+int flash_num_frames(const flash_ctx* ctx);
+int flash_cost_grad_frames(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad);
 
 /*
  * The hot path.  Replaces `(f::CostFunctor)(x)` + ForwardDiff's chunked gradient

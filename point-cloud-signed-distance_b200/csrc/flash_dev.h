@@ -22,8 +22,8 @@
 namespace flashdev {
 
 #if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
-struct Counters { long long points, narrow, inside, gjk_iters, plane_tests, vert_tests, lb_tests, skin64, feat_evals; unsigned exact_mask; };   // exact_mask: hulls whose narrow phase ran for the LAST point
-inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0u}; return c; }
+struct Counters { long long points, narrow, inside, gjk_iters, plane_tests, vert_tests, lb_tests, skin64, feat_evals, warm; unsigned exact_mask; };   // exact_mask: hulls whose narrow phase ran for the LAST point
+inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0u}; return c; }
 #define FLASH_COUNT(field, n) (flashdev::counters().field += (n))
 #else
 #define FLASH_COUNT(field, n) ((void)0)
@@ -679,27 +679,35 @@ FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) { return 
 //                   v_k - a orthogonal to e
 //   face f          the projection x' of x onto the plane of f lies in H: n_g.x' - o_g <= 0 for every plane g (points
 //                   outside), and f is the plane of largest distance: n_f.x - o_f >= n_g.x - o_g (points inside)
-// A feature is a u32: type (bits 0-1: 0 none, 1 vertex, 2 edge, 3 face) | ia << 8 | ib << 16 (vertices) or
+// A feature is a u32: type (bits 0-1: 0 none, 1 vertex, 2 edge, 3 face) | FEAT_CERT | ia << 8 | ib << 16 (vertices) or
 // plane slot << 8 (face).  All tests carry an absolute slack for the fp32 centre transform; a point that is outside
 // its certified region by a rounding error delta gets a distance that is wrong by O(delta^2 / d) only.
-enum { FEAT_NONE = 0, FEAT_VERTEX = 1, FEAT_EDGE = 2, FEAT_FACE = 3 };
+// Without FEAT_CERT the word is a HINT: the vertices (ia, ib, ic in bits 8-31, type = their number) of the simplex GJK
+// ended on at the ball centre.  The points of the group start their own GJK from it (hull_sd_warm): no plane hint, no
+// start triangle, and -- GJK's termination test being independent of the start -- the same exact distance.
+enum { FEAT_NONE = 0, FEAT_VERTEX = 1, FEAT_EDGE = 2, FEAT_FACE = 3, FEAT_CERT = 4 };
+FLASH_HD unsigned feat_hint(const Simplex& S) {
+  return (unsigned)S.ns | ((unsigned)S.ia << 8) | ((unsigned)(S.ns > 1 ? S.ib : 0) << 16) | ((unsigned)(S.ns > 2 ? S.ic : 0) << 24);
+}
 FLASH_HD unsigned hull_ball_feature(const HullView& V, F3 yc, float rho, float& d_centre) {
   F3 n; int kind = 0, fs = 0; Simplex S;
   S.ns = 0; S.ia = S.ib = S.ic = 0; S.a = S.b = S.c = f3(0.f, 0.f, 0.f);
   const float D = hull_sd_ex(V, yc, 3.0e38f, n, &kind, &fs, &S);
   d_centre = D;
   const float r = rho * (1.f + 1e-5f) + 1e-5f;   // ball radius + slack for the fp32 transform of the centre
+  // (a hint is only safe when the whole ball is outside the hull: GJK on the vertices cannot see penetration)
+  const unsigned hint = (kind == 2 || kind == 3) && S.ns >= 1 && S.ns <= 3 && D - r > 0.f ? feat_hint(S) : (unsigned)FEAT_NONE;
   if (kind == 3 && S.ns == 3) {
     // GJK ended in the interior of a triangle of hull vertices: it lies on a supporting plane, i.e. on the face
     // whose plane is the farthest one from yc (every plane distance is a lower bound of the true distance)
     float Dp; int fp;
-    if (!hull_plane_scan(V, yc, 3.0e38f, Dp, fp)) return FEAT_NONE;
+    if (!hull_plane_scan(V, yc, 3.0e38f, Dp, fp)) return hint;
     fs = fp; kind = 2;
   }
   if (kind == 1 || kind == 2) {
     // face fs
     const F3 nf = plane_normal(V.planes, fs);
-    if (!(dot(nf, nf) > 0.5f)) return FEAT_NONE;
+    if (!(dot(nf, nf) > 0.5f)) return hint;
     const float* pf = reinterpret_cast<const float*>(V.planes + (fs & ~1));
     const float df = fmaf(nf.x, yc.x, fmaf(nf.y, yc.y, fmaf(nf.z, yc.z, pf[6 + (fs & 1)])));   // n_f.yc - o_f
     const bool dips_inside = df - r < 0.f, pokes_outside = df + r > 0.f;
@@ -710,41 +718,56 @@ FLASH_HD unsigned hull_ball_feature(const HullView& V, F3 yc, float rho, float& 
       const float dg = fmaf(ng.x, yc.x, fmaf(ng.y, yc.y, fmaf(ng.z, yc.z, pg[6 + h])));
       const float c = dot(ng, nf);
       // outside points: projection onto plane f stays inside plane g
-      if (pokes_outside && !(dg - df * c + r * sqrtf(fmaxf(1.f - c * c, 0.f) + 1e-6f) <= 0.f)) return FEAT_NONE;
+      if (pokes_outside && !(dg - df * c + r * sqrtf(fmaxf(1.f - c * c, 0.f) + 1e-6f) <= 0.f)) return hint;
       // inside points: plane f has the largest distance
-      if (dips_inside && !(df - dg - r * sqrtf(fmaxf(2.f - 2.f * c, 0.f) + 1e-6f) >= 0.f)) return FEAT_NONE;
+      if (dips_inside && !(df - dg - r * sqrtf(fmaxf(2.f - 2.f * c, 0.f) + 1e-6f) >= 0.f)) return hint;
     }
-    return FEAT_FACE | ((unsigned)fs << 8);
+    return FEAT_FACE | FEAT_CERT | ((unsigned)fs << 8);
   }
-  if (kind != 3 || !(D - r > 0.f)) return FEAT_NONE;   // vertex / edge regions: the ball must be outside the hull
-  if (S.ns == 1) {
-    const F3 v = S.a + yc;       // simplex coordinates are relative to the query point
-    const F3 u = yc - v;
-    for (int k = 0; k < V.nv; ++k) {
-      const F3 e = vert_at(V, k) - v;
-      const float ee = dot(e, e);
-      if (!(dot(u, e) + r * sqrtf(ee) <= 0.f)) return FEAT_NONE;
-    }
-    return FEAT_VERTEX | ((unsigned)S.ia << 8);
+  // Vertex and edge regions are NOT certified: with the warm start their points cost one closest-point update and
+  // one support query, and the certificate (a pass over all vertices, or adjacency tables) costs the group kernel
+  // more than the closed form saves (measured: K5 group_kernel 4.7 ms with the certificates, 24 % of the groups
+  // certified).  Faces are: a patch of depth points lying ON a face straddles the surface, where GJK cannot start.
+  return hint;
+}
+// GJK started from the group's hint simplex.  Returns false when the point turns out to be on / inside the hull
+// (q = 0): the caller takes the regular path, whose plane scan gives the depth.
+FLASH_HD bool hull_sd_warm(const HullView& V, unsigned feat, F3 y, float& d, F3& nrm) {
+  const int ns = (int)(feat & 3u);
+  const int ia = (int)((feat >> 8) & 255u), ib = (int)((feat >> 16) & 255u), ic = (int)(feat >> 24);
+  Simplex S; F3 q;
+  const F3 pa = vert_at(V, ia) - y;
+  S.ns = 1; S.a = pa; S.ia = ia; S.b = pa; S.ib = ia; S.c = pa; S.ic = ia;
+  q = pa;
+  if (ns == 2) {
+    const F3 pb = vert_at(V, ib) - y;
+    float u0, u1;
+    q = seg_closest0(pa, pb, u0, u1);
+    simplex_from(S, pa, ia, u0, pb, ib, u1, pb, ib, 0.f);
+  } else if (ns == 3) {
+    const F3 pb = vert_at(V, ib) - y, pc = vert_at(V, ic) - y;
+    float u0, u1, u2;
+    q = tri_closest0(pa, pb, pc, u0, u1, u2);
+    simplex_from(S, pa, ia, u0, pb, ib, u1, pc, ic, u2);
   }
-  if (S.ns == 2) {
-    const F3 a = S.a + yc, b = S.b + yc;
-    F3 e = b - a;
-    const float len2 = dot(e, e);
-    if (!(len2 > 0.f)) return FEAT_NONE;
-    const float len = sqrtf(len2);
-    e = e * (1.f / len);
-    const F3 u = yc - a;
-    const float t = dot(u, e);
-    if (!(t - r >= 0.f && t + r <= len)) return FEAT_NONE;
-    for (int k = 0; k < V.nv; ++k) {
-      const F3 vk = vert_at(V, k) - a;
-      const F3 w = vk - e * dot(vk, e);
-      if (!(dot(u, w) + r * sqrtf(dot(w, w)) <= 0.f)) return FEAT_NONE;
-    }
-    return FEAT_EDGE | ((unsigned)S.ia << 8) | ((unsigned)S.ib << 16);
+  FLASH_COUNT(warm, 1);
+  for (int it = 0; it < GJK_MAX_ITER; ++it) {
+    if (!(dot(q, q) > 0.f)) return false;
+    FLASH_COUNT(gjk_iters, 1);
+    const int iw = hull_support_map(V, q);
+    if (!hull_gjk_update(V, y, iw, S, q)) break;
   }
-  return FEAT_NONE;
+  const float dd = dot(q, q);
+  if (!(dd > 0.f)) return false;
+#ifdef __CUDA_ARCH__
+  float inv = rsqrtf(dd);
+  inv = inv * (1.5f - 0.5f * dd * inv * inv);
+#else
+  const float inv = 1.0f / sqrtf(dd);
+#endif
+  nrm = q * (-inv);
+  d = dd * inv;
+  return true;
 }
 // distance and gradient of y to a certified feature
 FLASH_HD float hull_feature_eval(const HullView& V, unsigned feat, F3 y, F3& nrm) {
@@ -1096,11 +1119,12 @@ FLASH_HD GroupPre group_prepass(const HotModel& M, const GeoView& G, const float
   GroupPre o; o.cand = 0u; o.first = -1; o.feat = 0u; o.skip = 0u; o.cut = 3.0e38f;
   const int nc = M.n_convex;
   float min_ub = 3.0e38f, lb0 = 3.0e38f;
+  float lb[MAX_CONVEX];
   for (int j = 0; j < nc; ++j) {
-    float lbv, ubv;
-    hull_ball_bounds(M.cvx[j], tabf + 12 * j, cx, cy, cz, rho, lbv, ubv);
+    float ubv;
+    hull_ball_bounds(M.cvx[j], tabf + 12 * j, cx, cy, cz, rho, lb[j], ubv);
     min_ub = fminf(min_ub, ubv);
-    if (lbv < lb0) { lb0 = lbv; o.first = j; }
+    if (lb[j] < lb0) { lb0 = lb[j]; o.first = j; }
   }
   if (want_feat && o.first >= 0) {
     const ConvexC& C = M.cvx[o.first];
@@ -1109,11 +1133,8 @@ FLASH_HD GroupPre group_prepass(const HotModel& M, const GeoView& G, const float
     const float ub2 = dc + rho * (1.f + 1e-5f) + 1e-5f;   // 1-Lipschitz: d(x) <= d(c) + rho
     if (dc < 3.0e37f) min_ub = fminf(min_ub, ub2);
   }
-  for (int j = 0; j < nc; ++j) {
-    float lbv, ubv;
-    hull_ball_bounds(M.cvx[j], tabf + 12 * j, cx, cy, cz, rho, lbv, ubv);
-    if (lbv <= min_ub || j == o.first) o.cand |= 1u << j;
-  }
+  for (int j = 0; j < nc; ++j)
+    if (lb[j] <= min_ub || j == o.first) o.cand |= 1u << j;
   if (o.cand == 0u) { o.cand = nc >= 32 ? 0xffffffffu : ((1u << nc) - 1u); o.first = -1; o.feat = 0u; return o; }   // only with non-finite bounds
   if (want_skin_cull && M.n_skins > 0 && M.n_skins <= 8) o.skip = group_skin_cull(M, tabf, cx, cy, cz, rho, min_ub, o.cut);
   return o;
@@ -1183,14 +1204,18 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
     }
     const ConvexC& C = cvx[j];
     if ((feat & 3u) != 0u && j == first) {
-      // the group's ball lies in the Voronoi region of one feature of this hull (hull_ball_feature): closed form
-      FLASH_COUNT(feat_evals, 1);
       const F3 y = to_geometry(tab + 12 * j, px, py, pz);
-      F3 n;
-      const float d = hull_feature_eval(hull_view(G, C), feat, y, n);
-      if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
-      j = -1;
-      continue;
+      F3 n; float d; bool ok = true;
+      if (feat & FEAT_CERT) {
+        // the group's ball lies in the Voronoi region of one feature of this hull (hull_ball_feature): closed form
+        FLASH_COUNT(feat_evals, 1);
+        d = hull_feature_eval(hull_view(G, C), feat, y, n);
+      } else ok = hull_sd_warm(hull_view(G, C), feat, y, d, n);   // GJK from the simplex found at the ball centre
+      if (ok) {
+        if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
+        j = -1;
+        continue;
+      }
     }
     bool skip = false;
     if (!single) {

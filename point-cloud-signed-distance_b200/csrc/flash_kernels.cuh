@@ -47,6 +47,7 @@ constexpr int CBLOCK = FLASH_CBLOCK;
 #endif
 #endif
 constexpr int CWARPS = CBLOCK / 32;
+constexpr int FRAMES_MAX = 64;   // = MAX_FRAMES of flash_ingest.cuh
 constexpr int QENT = 8;  // doubles per skin-queue entry: x y z s ginv nhx nhy nhz (slot in a side array)
 
 struct CostParams {
@@ -62,7 +63,11 @@ struct CostParams {
   int32_t* argmin;     // [C][n_pts] or null
   const int* perm;     // sorted position -> caller index (null: identity)
   const float4* grp;   // per 32 consecutive points: bounding ball {cx, cy, cz, rho} (null: no group culling)
+  const uint4* rec;    // group records of group_kernel, [C][rec_stride] (null: per-warp hull cull inside the loop)
+  long long rec_stride;
   double* dist;        // [n_pts] (DIST mode, C == 1)
+  const long long* frames;   // null: one frame [0, n_pts); else off[0 .. FRAMES_MAX], cnt[FRAMES_MAX + 1 ..] and
+  int cfg_per_frame;         // configuration c evaluates frame c / cfg_per_frame only
   int pts_per_block;
   int use_grid;
 };
@@ -332,20 +337,81 @@ __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayou
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Group pre-pass as its own kernel: ONE THREAD per (configuration, group of 32 points).  Everything it decides is
+// decided once for 32 evaluations (flash_dev.h group_prepass): candidate hulls, the most promising one and -- from one
+// narrow phase at the ball centre -- its certified closest feature and a tight upper bound of the group's minimum,
+// which in turn culls more hulls and skins.  Inside cost_kernel (round 1: a phase in front of the point loop, one 768-
+// thread block per SM) the same code left two thirds of the block waiting at a barrier behind long serial threads; here
+// it runs at full occupancy and the point loop only loads a 16-byte record per group.
+struct GroupParams {
+  const HotModel* hot;
+  const F4* geo_f4;
+  const uint32_t* geo_u32;
+  int geo_f4_n, geo_u32_n;
+  const double* tab;       // [C][tab_len]
+  const float4* grp;       // group balls
+  const long long* frames; // as CostParams
+  int cfg_per_frame;
+  long long n_groups;      // groups of the (single) frame when frames == null
+  uint4* rec;              // [C][rec_stride]
+  long long rec_stride;
+  int groups_per_block;
+  int want_feat, want_cull;
+};
+constexpr int GBLOCK = 256;
+__host__ __device__ inline size_t group_smem(int geo_f4_n, int geo_u32_n, int tabf_len) {
+  return align16(sizeof(HotModel)) + align16(sizeof(F4) * (size_t)geo_f4_n) + align16(sizeof(uint32_t) * (size_t)geo_u32_n) + align16(sizeof(float) * (size_t)(tabf_len > 0 ? tabf_len : 4));
+}
+__global__ void __launch_bounds__(GBLOCK, 2) group_kernel(const GroupParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int tid = threadIdx.x, c = blockIdx.x;
+  long long g0 = 0, g1 = p.n_groups;
+  if (p.frames) { const int f = c / p.cfg_per_frame; g0 = p.frames[f] >> 5; g1 = g0 + ((p.frames[FRAMES_MAX + 1 + f] + 31) >> 5); }
+  const long long b0 = g0 + (long long)blockIdx.y * p.groups_per_block;
+  if (b0 >= g1) return;
+  long long b1 = b0 + p.groups_per_block; if (b1 > g1) b1 = g1;
+  const HotModel* hot_g = p.hot;
+  size_t o = 0;
+  HotModel* Hs = reinterpret_cast<HotModel*>(smem); o = align16(sizeof(HotModel));
+  F4* f4s = reinterpret_cast<F4*>(smem + o); o += align16(sizeof(F4) * (size_t)p.geo_f4_n);
+  uint32_t* u32s = reinterpret_cast<uint32_t*>(smem + o); o += align16(sizeof(uint32_t) * (size_t)p.geo_u32_n);
+  float* tabf = reinterpret_cast<float*>(smem + o);
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(hot_g);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(Hs);
+    for (int i = tid; i < (int)(sizeof(HotModel) / 4); i += GBLOCK) dst[i] = src[i];
+    const float4* s4 = reinterpret_cast<const float4*>(p.geo_f4);
+    float4* d4 = reinterpret_cast<float4*>(f4s);
+    for (int i = tid; i < p.geo_f4_n; i += GBLOCK) d4[i] = __ldg(s4 + i);
+    for (int i = tid; i < p.geo_u32_n; i += GBLOCK) u32s[i] = __ldg(p.geo_u32 + i);
+    tabf_fill(*hot_g, p.tab + (size_t)c * hot_g->tab_len, tabf, tid, GBLOCK);
+  }
+  __syncthreads();
+  const HotModel& H = *Hs;
+  GeoView G; G.f4 = f4s; G.u32 = u32s; G.grid_pool = nullptr;
+  uint4* out = p.rec + (size_t)c * p.rec_stride - g0;
+  for (long long g = b0 + tid; g < b1; g += GBLOCK) {
+    const float4 gb = __ldg(p.grp + g);
+    const GroupPre gp = group_prepass(H, G, tabf, gb.x, gb.y, gb.z, gb.w, p.want_feat != 0, p.want_cull != 0);
+    out[g] = make_uint4(gp.cand, __float_as_uint(gp.cut), gp.feat, (unsigned)(((gp.first < 0 ? 255 : gp.first) << 8) | gp.skip));
+  }
+}
+
 // GRAD: accumulate gradient terms; ARGMIN: write the argmin surface per point; DIST: write the
 // min distance per point (skin_eval entry) and skip all accumulation.
 #ifndef FLASH_MINB
 #define FLASH_MINB 1
 #endif
-#ifndef FLASH_MAX_TILE_GROUPS
-#define FLASH_MAX_TILE_GROUPS 1024   // choose_tile keeps tiles at <= 32768 points
-#endif
-constexpr size_t COST_STATIC_SMEM = (size_t)FLASH_MAX_TILE_GROUPS * 14 + 64;   // the group pre-pass tables of cost_kernel (static __shared__)
+constexpr size_t COST_STATIC_SMEM = 64;   // static __shared__ of cost_kernel (the group hand-out counter)
 template <bool GRAD, bool ARGMIN, bool DIST>
 __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int c = blockIdx.x;
+  long long range0 = 0, range1 = p.n_pts;
+  if (p.frames) { const int f = c / p.cfg_per_frame; range0 = p.frames[f]; range1 = range0 + p.frames[FRAMES_MAX + 1 + f]; }
+  if (range0 + (long long)blockIdx.y * p.pts_per_block >= range1) return;   // (block-uniform) a frame shorter than the longest one
   // every block re-derives the layout from the same numbers the host used
   const HotModel* hot_g = p.hot;
   const int tab_len = hot_g->tab_len, acc_len = hot_g->acc_len, n_convex = hot_g->n_convex;
@@ -370,9 +436,9 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   int* qslot = reinterpret_cast<int*>(smem + L.off_qslot) + warp * 32;
 
   const unsigned all_convex = n_convex >= 32 ? 0xffffffffu : ((1u << n_convex) - 1u);
-  const long long tile0 = (long long)blockIdx.y * p.pts_per_block;
+  const long long tile0 = range0 + (long long)blockIdx.y * p.pts_per_block;
   long long tile1 = tile0 + p.pts_per_block;
-  if (tile1 > p.n_pts) tile1 = p.n_pts;
+  if (tile1 > range1) tile1 = range1;
   double cost_local = 0.0;
 
 #ifdef FLASH_DYN_GROUPS
@@ -382,38 +448,13 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   // which 11 warps waited for the slowest one, which is what the per-batch barrier of the static schedule was
   // (expensively) bounding; see DESIGN.md 5.
   const int ngroups = (int)((tile1 - tile0 + 31) >> 5);
-#ifndef FLASH_NO_GROUP_PREPASS
-  // Group pre-pass, one thread per group of the tile, before the point loop (inside the loop the same code costs more
-  // instruction fetch than it saves):
-  //   s_cand / first : hulls that can be the minimum for some point of the group's ball, the most promising first
-  //   skip bits      : skin k is the minimum for NO point of the group (certified lower bound over the ball >
-  //                    smallest hull upper bound): the loop skips its fp32 pre-filter for all 32 points
-  //   s_thr          : upper bound of the group's minimum, the hull scans' cutoff when a skin is skipped
-  __shared__ unsigned s_cand[FLASH_MAX_TILE_GROUPS];
-  __shared__ float s_thr[FLASH_MAX_TILE_GROUPS];
-  __shared__ unsigned s_feat[FLASH_MAX_TILE_GROUPS];         // certified closest feature of hull `first` for the whole group (hull_ball_feature)
-  __shared__ unsigned short s_meta[FLASH_MAX_TILE_GROUPS];   // first << 8 | skip bits (first = 255: none)
-  const bool grp_pre = !DIST && p.grp != nullptr && n_convex > 1 && ngroups <= FLASH_MAX_TILE_GROUPS;
-  if (grp_pre)
-    for (int gi = tid; gi < ngroups; gi += CBLOCK) {
-      const float4 gb = __ldg(p.grp + ((tile0 >> 5) + gi));
-#ifndef FLASH_NO_SKIN_CULL
-      const bool want_cull = true;
-#else
-      const bool want_cull = false;
-#endif
-#ifndef FLASH_NO_FEATURES
-      const bool want_feat = p.use_grid == 0;
-#else
-      const bool want_feat = false;
-#endif
-      const GroupPre gp = group_prepass(H, G, tabf, gb.x, gb.y, gb.z, gb.w, want_feat, want_cull);
-      s_cand[gi] = gp.cand; s_thr[gi] = gp.cut; s_feat[gi] = gp.feat;
-      s_meta[gi] = (unsigned short)(((gp.first < 0 ? 255 : gp.first) << 8) | gp.skip);
-    }
-#else
-  const bool grp_pre = false;
-#endif
+  // Group records (group_kernel, one thread per group and configuration, run before this kernel):
+  //   x = cand    hulls that can be the minimum for some point of the group's ball
+  //   y = cut     upper bound of the group's minimum, the hull scans' cutoff when a skin is skipped
+  //   z = feat    certified closest feature of hull `first` for the whole ball (hull_ball_feature), 0 = none
+  //   w = first << 8 | skin skip bits   (first = 255: none)
+  const bool grp_pre = !DIST && p.rec != nullptr;
+  const uint4* rec = grp_pre ? p.rec + (size_t)c * p.rec_stride + ((tile0 - range0) >> 5) : nullptr;
   int g = 0;
   if (lane == 0) g = atomicAdd(s_next, 1);
   g = __shfl_sync(0xffffffffu, g, 0);
@@ -449,11 +490,10 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     unsigned skin_skip = 0u; float cut0 = 3.0e38f; unsigned feat = 0u;
 #ifdef FLASH_DYN_GROUPS
     if (grp_pre) {
-#ifndef FLASH_NO_GROUP_PREPASS
-      const unsigned m = s_meta[gcur];
-      cand = s_cand[gcur]; first = (m >> 8) == 255u ? -1 : (int)(m >> 8);
-      skin_skip = m & 255u; cut0 = s_thr[gcur]; feat = s_feat[gcur];
-#endif
+      const uint4 r = __ldg(rec + gcur);
+      cand = r.x; cut0 = __uint_as_float(r.y); feat = r.z;
+      first = (r.w >> 8) == 255u ? -1 : (int)(r.w >> 8);
+      skin_skip = r.w & 255u;
     } else
 #endif
     if (!DIST && p.grp != nullptr && n_convex > 1 && wbase < tile1) {   // (a warp past the tile end has no points and no group)

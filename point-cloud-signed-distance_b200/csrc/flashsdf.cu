@@ -13,6 +13,7 @@
 #include "../../include/flashsdf.h"
 #include "flash_host.h"
 #include "flash_kernels.cuh"
+#include "flash_ingest.cuh"
 
 using namespace flashdev;
 using namespace flashhost;
@@ -65,17 +66,36 @@ struct flash_ctx {
   size_t grid_pool_floats = 0;
   std::vector<double> grid_err;  // per convex slot
   bool use_grid = false;
-  // points
-  float4* d_pts = nullptr; long long n_pts = 0; long long cap_pts = 0; bool pts_external = false; bool pts_set = false;
-  void* d_stage = nullptr; size_t cap_stage = 0;
-  int* d_bins = nullptr; int* d_perm = nullptr; size_t cap_perm = 0; bool perm_on = false; bool sort_points = true;
-  float4* d_grp = nullptr; size_t cap_grp = 0; bool grp_on = false; bool group_cull = true;
+  // points: two sets (front = the frame(s) being evaluated, back = the one being uploaded / sorted on the copy stream)
+  struct PointSet {
+    float4* d_pts = nullptr; long long cap_pts = 0; bool external = false;
+    int* d_perm = nullptr; size_t cap_perm = 0; bool perm_on = false;
+    float4* d_grp = nullptr; size_t cap_grp = 0; bool grp_on = false;
+    long long* d_frames = nullptr;     // device: off[0 .. MAX_FRAMES], cnt[MAX_FRAMES + 1 ..]
+    FrameTable ft;                     // the same on the host (+ offsets in the caller-order staging buffer)
+    long long n = 0, max_cnt = 0;      // points of all frames; of the largest frame
+    bool set = false;
+    cudaEvent_t ready = nullptr;       // copy stream: upload + sort + group balls finished
+    cudaEvent_t retired = nullptr;     // compute stream: every kernel that read this set has been issued before this event
+    bool retired_valid = false;
+  };
+  PointSet ps[2];
+  int cur = 0;
+  bool back_pending = false;           // flash_points_set_async has filled the back set, flash_points_swap not yet called
+  cudaStream_t copy_stream = nullptr;
+  void* d_stage = nullptr; size_t cap_stage = 0;           // caller-order [n][3] as uploaded
+  void* h_ring[2] = {nullptr, nullptr}; size_t cap_ring[2] = {0, 0}; cudaEvent_t ring_done[2] = {nullptr, nullptr}; int ring_next = 0;   // pinned staging for pageable callers
+  unsigned* d_keys[2] = {nullptr, nullptr}; int* d_idx[2] = {nullptr, nullptr}; size_t cap_sort = 0;
+  int* d_table = nullptr; size_t cap_table = 0; int* d_sums = nullptr; unsigned* d_bounds = nullptr;   // [6 * MAX_FRAMES] bounds + [1] scan counter
+  bool sort_points = true; bool group_cull = true;
   // per-batch state
   int cap_C = 0;
   double *d_X = nullptr, *d_tab = nullptr, *d_aux = nullptr, *d_acc = nullptr, *d_cost = nullptr, *d_grad = nullptr, *d_div = nullptr;
   int *d_status = nullptr, *d_done = nullptr, *d_iters = nullptr;
   double* h_pin = nullptr; size_t cap_pin = 0;  // pinned staging for X / cost / grad
   int32_t* d_argmin = nullptr; size_t cap_argmin = 0;
+  uint4* d_rec = nullptr; size_t cap_rec = 0;   // group records of group_kernel, [C][rec_stride]
+  bool features = true;
   // query scratch (skin_eval / raycast)
   double* d_qd = nullptr; size_t cap_qd = 0;
   int* d_qi = nullptr; size_t cap_qi = 0;
@@ -178,17 +198,50 @@ int choose_tile(const flash_ctx* ctx, long long n, int C) {
   return (int)ppb;
 }
 
-int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin) {
+// group pre-pass (group_kernel) for C configurations of the current point set -> ctx->d_rec; *stride = records per config
+int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride) {
   const ModelC& M = ctx->hm.M;
+  const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
+  *stride = 0;
+  const long long n_tile = cfg_per_frame > 0 ? P.max_cnt : P.n;
+  if (!(P.grp_on && ctx->group_cull) || M.n_convex < 2 || n_tile == 0) return 0;
+  const long long G = (n_tile + 31) / 32;
+  int rc = ensure(ctx, ctx->d_rec, ctx->cap_rec, (size_t)C * (size_t)G); if (rc) return rc;
+  GroupParams g;
+  g.hot = ctx->d_hot; g.geo_f4 = ctx->d_geo_f4; g.geo_u32 = ctx->d_geo_u32; g.geo_f4_n = M.geo_f4; g.geo_u32_n = M.geo_u32;
+  g.tab = ctx->d_tab; g.grp = P.d_grp; g.frames = cfg_per_frame > 0 ? P.d_frames : nullptr; g.cfg_per_frame = cfg_per_frame > 0 ? cfg_per_frame : 1;
+  g.n_groups = G; g.rec = ctx->d_rec; g.rec_stride = G;
+  long long gpb = (G * C + (long long)ctx->sm_count * 4 - 1) / ((long long)ctx->sm_count * 4);
+  gpb = std::min<long long>(std::max<long long>(((gpb + GBLOCK - 1) / GBLOCK) * GBLOCK, GBLOCK), 8 * GBLOCK);
+  g.groups_per_block = (int)gpb;
+  g.want_feat = (ctx->features && !ctx->use_grid) ? 1 : 0; g.want_cull = 1;
+  const size_t smem = group_smem(M.geo_f4, M.geo_u32, M.tabf_len);
+  if (smem > 48 * 1024) CU(cudaFuncSetAttribute(group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  group_kernel<<<dim3((unsigned)C, (unsigned)((G + gpb - 1) / gpb)), GBLOCK, smem, ctx->stream>>>(g);
+  CU(cudaGetLastError());
+  ctx->launches++; ctx->last.launches++;
+  *stride = G;
+  return 0;
+}
+
+// C = total configurations of the launch; cfg_per_frame > 0: configuration c evaluates frame c / cfg_per_frame only
+int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin, int cfg_per_frame = 0) {
+  const ModelC& M = ctx->hm.M;
+  const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
+  long long rec_stride = 0;
+  { int rc = run_groups(ctx, C, cfg_per_frame, &rec_stride); if (rc) return rc; }
   CostParams p;
+  p.rec = rec_stride > 0 ? ctx->d_rec : nullptr; p.rec_stride = rec_stride;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
   p.geo_f4_n = M.geo_f4; p.geo_u32_n = M.geo_u32;
-  p.pts = ctx->d_pts; p.n_pts = ctx->n_pts; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = d_argmin; p.dist = nullptr; p.perm = ctx->perm_on ? ctx->d_perm : nullptr;
-  p.grp = ctx->grp_on && ctx->group_cull ? ctx->d_grp : nullptr;
-  p.pts_per_block = choose_tile(ctx, ctx->n_pts, C);
+  p.pts = P.d_pts; p.n_pts = P.n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = d_argmin; p.dist = nullptr; p.perm = P.perm_on ? P.d_perm : nullptr;
+  p.grp = P.grp_on && ctx->group_cull ? P.d_grp : nullptr;
+  p.frames = cfg_per_frame > 0 ? P.d_frames : nullptr; p.cfg_per_frame = cfg_per_frame > 0 ? cfg_per_frame : 1;
+  const long long n_tile = cfg_per_frame > 0 ? P.max_cnt : P.n;
+  p.pts_per_block = choose_tile(ctx, n_tile, C);
   p.use_grid = ctx->use_grid ? 1 : 0;
-  if (ctx->n_pts == 0) return 0;
-  const int tiles = (int)((ctx->n_pts + p.pts_per_block - 1) / p.pts_per_block);
+  if (P.n == 0 || n_tile == 0) return 0;
+  const int tiles = (int)((n_tile + p.pts_per_block - 1) / p.pts_per_block);
   const size_t smem = cost_layout(ctx, grad).total;
   if (smem + COST_STATIC_SMEM > (size_t)ctx->smem_optin) return fail(ctx, FLASH_ERR_TOO_LARGE, "model geometry does not fit in shared memory (" + std::to_string(smem) + " bytes)");
   if (grad) return d_argmin ? launch_cost_t<true, true, false>(ctx, p, C, tiles, smem) : launch_cost_t<true, false, false>(ctx, p, C, tiles, smem);
@@ -221,12 +274,12 @@ int run_allreduce(flash_ctx* ctx, int C) {
 }
 
 // prepare -> main -> (allreduce) -> epilogue on the ctx stream, X already on the device
-int pipeline(flash_ctx* ctx, int C, double w_def, bool grad, int32_t* d_argmin) {
+int pipeline(flash_ctx* ctx, int C, double w_def, bool grad, int32_t* d_argmin, int cfg_per_frame = 0) {
   int rc;
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[0], ctx->stream));
   if ((rc = run_prepare(ctx, C, true))) return rc;   // also zeroes the accumulators
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[1], ctx->stream));
-  if ((rc = run_cost(ctx, C, grad, d_argmin))) return rc;
+  if ((rc = run_cost(ctx, C, grad, d_argmin, cfg_per_frame))) return rc;
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
   if ((rc = run_allreduce(ctx, C))) return rc;
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[3], ctx->stream));
@@ -307,71 +360,166 @@ int bake_grids(flash_ctx* ctx) {
 
 }  // namespace
 
-// bounding balls of the 32-point groups the main kernel's warps evaluate together
-static int points_groups(flash_ctx* ctx) {
-  ctx->grp_on = false;
-  const long long n = ctx->n_pts;
-  if (n <= 0) return 0;
-  int rc = ensure(ctx, ctx->d_grp, ctx->cap_grp, (size_t)((n + 31) / 32)); if (rc) return rc;
-  points_groups_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_pts, n, ctx->d_grp);
-  CU(cudaGetLastError());
-  ctx->launches++;
-  ctx->grp_on = true;
-  return 0;
-}
-
-static int points_alloc(flash_ctx* ctx, int64_t n) {
-  if (ctx->pts_external) { ctx->d_pts = nullptr; ctx->cap_pts = 0; ctx->pts_external = false; }
-  if (n > ctx->cap_pts) {
-    if (ctx->d_pts) CU(cudaFree(ctx->d_pts));
-    ctx->d_pts = nullptr; ctx->cap_pts = 0;
-    CU(cudaMalloc((void**)&ctx->d_pts, (size_t)std::max<int64_t>(n, 1) * sizeof(float4)));
-    ctx->cap_pts = n;
+// ---- point sets: upload, Hilbert sort, group balls (flash_ingest.cuh), all on the copy stream -------------------
+static int set_alloc(flash_ctx* ctx, flash_ctx::PointSet& P, long long span) {
+  if (P.external) { P.d_pts = nullptr; P.cap_pts = 0; P.external = false; }
+  if (span > P.cap_pts) {
+    if (P.d_pts) CU(cudaFree(P.d_pts));
+    P.d_pts = nullptr; P.cap_pts = 0;
+    const long long want = span + span / 16 + 32;
+    CU(cudaMalloc((void**)&P.d_pts, (size_t)want * sizeof(float4)));
+    P.cap_pts = want;
   }
+  if (!P.d_frames) CU(cudaMalloc((void**)&P.d_frames, (size_t)(2 * MAX_FRAMES + 2) * sizeof(long long)));
+  if (!P.ready) { CU(cudaEventCreateWithFlags(&P.ready, cudaEventDisableTiming)); CU(cudaEventCreateWithFlags(&P.retired, cudaEventDisableTiming)); }
   return 0;
 }
 
-// H2D of the caller's AoS buffer, then convert + Morton-bin on the device (see flash_kernels.cuh)
+static bool host_pinned(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged;
+}
+
+// F frames ptrs[f][counts[f]][3] (host) -> set P.  Returns after ENQUEUEING the work on the copy stream; pageable
+// caller memory has been staged into the ctx's pinned ring by then, pinned caller memory is read by DMA until P.ready.
 template <class T>
-static int points_ingest(flash_ctx* ctx, const T* xyz, int64_t n) {
+static int ingest(flash_ctx* ctx, flash_ctx::PointSet& P, const T* const* ptrs, const int64_t* counts, int F) {
   CU(cudaSetDevice(ctx->device));
-  int rc = points_alloc(ctx, n); if (rc) return rc;
-  ctx->perm_on = false; ctx->grp_on = false;
-  if (n > 0) {
-    const size_t bytes = (size_t)n * 3 * sizeof(T);
-    if (bytes > ctx->cap_stage) { if (ctx->d_stage) CU(cudaFree(ctx->d_stage)); ctx->d_stage = nullptr; ctx->cap_stage = 0; CU(cudaMalloc(&ctx->d_stage, bytes)); ctx->cap_stage = bytes; }
-    CU(cudaMemcpyAsync(ctx->d_stage, xyz, bytes, cudaMemcpyHostToDevice, ctx->stream));
-    const T* src = (const T*)ctx->d_stage;
-    const unsigned nb = (unsigned)((n + 255) / 256);
-    if (ctx->sort_points && n >= 4096 && n < (1ll << 31)) {
-      if (!ctx->d_bins) CU(cudaMalloc((void**)&ctx->d_bins, (size_t)(SORT_BINS + 256 + 8) * sizeof(int)));
-      rc = ensure(ctx, ctx->d_perm, ctx->cap_perm, (size_t)n); if (rc) return rc;
-      int* bins = ctx->d_bins; int* sums = bins + SORT_BINS; unsigned* bounds = (unsigned*)(sums + 256);
-      CU(cudaMemsetAsync(bins, 0, (size_t)(SORT_BINS + 256) * sizeof(int), ctx->stream));
-      const unsigned init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
-      CU(cudaMemcpyAsync(bounds, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
-      const unsigned gb = (unsigned)std::min<long long>((n + 255) / 256, (long long)ctx->sm_count * 16);
-      points_bounds_kernel<T><<<gb, 256, 0, ctx->stream>>>(src, n, bounds);
-      points_hist_kernel<T><<<nb, 256, 0, ctx->stream>>>(src, n, bounds, bins);
-      bins_scan_local_kernel<<<SORT_BINS / 1024, 1024, 0, ctx->stream>>>(bins, sums);
-      bins_scan_add_kernel<<<SORT_BINS / 1024, 1024, 0, ctx->stream>>>(bins, sums);
-      points_scatter_kernel<T><<<nb, 256, 0, ctx->stream>>>(src, n, bounds, bins, ctx->d_pts, ctx->d_perm);
-      CU(cudaGetLastError());
-      ctx->launches += 5;
-      ctx->perm_on = true;
-    } else {
-      convert_points_kernel<T><<<nb, 256, 0, ctx->stream>>>(src, ctx->d_pts, n);
-      CU(cudaGetLastError());
-      ctx->launches++;
-    }
-    ctx->n_pts = n;
-    rc = points_groups(ctx); if (rc) return rc;
-    CU(cudaStreamSynchronize(ctx->stream));  // the caller may reuse xyz as soon as we return
+  FrameTable& ft = P.ft;
+  ft.n_frames = F;
+  long long n = 0, span = 0, max_cnt = 0;
+  for (int f = 0; f < F; ++f) {
+    ft.src_off[f] = n; ft.off[f] = span; ft.cnt[f] = counts[f];
+    n += counts[f]; span += (counts[f] + 31) & ~31ll; max_cnt = std::max<long long>(max_cnt, counts[f]);
   }
-  ctx->n_pts = n; ctx->pts_set = true;
+  ft.src_off[F] = n; ft.off[F] = span;
+  int rc = set_alloc(ctx, P, std::max<long long>(span, 32)); if (rc) return rc;
+  cudaStream_t cs = ctx->copy_stream;
+  if (P.retired_valid) { CU(cudaStreamWaitEvent(cs, P.retired, 0)); P.retired_valid = false; }
+  P.perm_on = false; P.grp_on = false; P.n = n; P.max_cnt = max_cnt; P.set = true;
+  {
+    long long h[2 * MAX_FRAMES + 2];
+    for (int f = 0; f <= F; ++f) h[f] = ft.off[f];
+    for (int f = 0; f < F; ++f) h[MAX_FRAMES + 1 + f] = ft.cnt[f];
+    // small and rare (once per frame batch): pageable source, synchronous staging by the driver
+    CU(cudaMemcpyAsync(P.d_frames, h, sizeof h, cudaMemcpyHostToDevice, cs));
+  }
+  if (n == 0) { CU(cudaEventRecord(P.ready, cs)); return FLASH_OK; }
+  // ---- upload into the caller-order staging buffer
+  const size_t bytes = (size_t)n * 3 * sizeof(T);
+  if (bytes > ctx->cap_stage) {
+    CU(cudaStreamSynchronize(cs));
+    if (ctx->d_stage) CU(cudaFree(ctx->d_stage));
+    ctx->d_stage = nullptr; ctx->cap_stage = 0;
+    CU(cudaMalloc(&ctx->d_stage, bytes + bytes / 16));
+    ctx->cap_stage = bytes + bytes / 16;
+  }
+  bool all_pinned = true;
+  for (int f = 0; f < F; ++f) if (counts[f] > 0 && !host_pinned(ptrs[f])) all_pinned = false;
+  if (all_pinned) {
+    for (int f = 0; f < F; ++f)
+      if (counts[f] > 0) CU(cudaMemcpyAsync((char*)ctx->d_stage + (size_t)ft.src_off[f] * 3 * sizeof(T), ptrs[f], (size_t)counts[f] * 3 * sizeof(T), cudaMemcpyHostToDevice, cs));
+  } else {
+    const int slot = ctx->ring_next; ctx->ring_next ^= 1;
+    if (!ctx->ring_done[slot]) CU(cudaEventCreateWithFlags(&ctx->ring_done[slot], cudaEventDisableTiming));
+    else CU(cudaEventSynchronize(ctx->ring_done[slot]));          // the DMA that last read this slot has finished
+    if (bytes > ctx->cap_ring[slot]) {
+      if (ctx->h_ring[slot]) CU(cudaFreeHost(ctx->h_ring[slot]));
+      ctx->h_ring[slot] = nullptr; ctx->cap_ring[slot] = 0;
+      CU(cudaHostAlloc(&ctx->h_ring[slot], bytes + bytes / 16, cudaHostAllocDefault));
+      ctx->cap_ring[slot] = bytes + bytes / 16;
+    }
+    for (int f = 0; f < F; ++f)
+      if (counts[f] > 0) std::memcpy((char*)ctx->h_ring[slot] + (size_t)ft.src_off[f] * 3 * sizeof(T), ptrs[f], (size_t)counts[f] * 3 * sizeof(T));
+    CU(cudaMemcpyAsync(ctx->d_stage, ctx->h_ring[slot], bytes, cudaMemcpyHostToDevice, cs));
+    CU(cudaEventRecord(ctx->ring_done[slot], cs));
+  }
+  const T* src = (const T*)ctx->d_stage;
+  const long long span_groups = span >> 5;
+  rc = ensure(ctx, P.d_grp, P.cap_grp, (size_t)span_groups); if (rc) return rc;
+  const unsigned gblocks = (unsigned)((span_groups * 32 + 255) / 256);
+  if (ctx->sort_points && n >= 4096 && n < (1ll << 31)) {
+    rc = ensure(ctx, P.d_perm, P.cap_perm, (size_t)span); if (rc) return rc;
+    if ((size_t)n > ctx->cap_sort) {
+      CU(cudaStreamSynchronize(cs));
+      for (int k = 0; k < 2; ++k) { if (ctx->d_keys[k]) CU(cudaFree(ctx->d_keys[k])); if (ctx->d_idx[k]) CU(cudaFree(ctx->d_idx[k])); ctx->d_keys[k] = nullptr; ctx->d_idx[k] = nullptr; }
+      const size_t want = (size_t)n + (size_t)n / 16;
+      for (int k = 0; k < 2; ++k) { CU(cudaMalloc((void**)&ctx->d_keys[k], want * sizeof(unsigned))); CU(cudaMalloc((void**)&ctx->d_idx[k], want * sizeof(int))); }
+      ctx->cap_sort = want;
+    }
+    if (!ctx->d_bounds) CU(cudaMalloc((void**)&ctx->d_bounds, (size_t)(6 * MAX_FRAMES + 1) * sizeof(unsigned)));
+    unsigned* scan_done = ctx->d_bounds + 6 * MAX_FRAMES;
+    // key layout: frame bits | 3 * hb Hilbert bits; the top `kb` bits are sorted (enough to order clouds of this size)
+    int fb = 0; while ((1 << fb) < F) ++fb;
+    const int hb = std::min(10, (32 - fb) / 3);
+    const int total_bits = fb + 3 * hb;
+    int lg = 0; while ((1ll << lg) < n) ++lg;
+    int kb = std::min(total_bits, std::max(16, lg + 5 + fb));
+    const int passes = (kb + 7) / 8;
+    kb = std::min(total_bits, passes * 8);
+    const int drop = total_bits - kb;
+    // chunk of keys per warp: a multiple of 32, about 4096 warps in flight for large clouds
+    long long E = ((n + 4095) / 4096 + 31) & ~31ll;
+    E = std::min<long long>(std::max<long long>(E, 512), 1 << 20);
+    const int nW = (int)((n + E - 1) / E);
+    const long long tlen = 256ll * nW;
+    const int sblocks = (int)((tlen + 1023) / 1024);
+    if ((size_t)tlen > ctx->cap_table) {
+      CU(cudaStreamSynchronize(cs));
+      if (ctx->d_table) CU(cudaFree(ctx->d_table));
+      if (ctx->d_sums) CU(cudaFree(ctx->d_sums));
+      ctx->d_table = nullptr; ctx->d_sums = nullptr; ctx->cap_table = 0;
+      CU(cudaMalloc((void**)&ctx->d_table, (size_t)tlen * 2 * sizeof(int)));
+      CU(cudaMalloc((void**)&ctx->d_sums, ((size_t)tlen * 2 / 1024 + 2) * sizeof(int)));
+      ctx->cap_table = (size_t)tlen * 2;
+    }
+    bounds_init_kernel<<<(6 * F + 255) / 256, 256, 0, cs>>>(ctx->d_bounds, F, scan_done);
+    const unsigned bb = (unsigned)std::min<long long>((max_cnt + 255) / 256, std::max(1, ctx->sm_count * 16 / F));
+    frames_bounds_kernel<T><<<dim3(std::max(bb, 1u), F), 256, 0, cs>>>(src, ft, ctx->d_bounds);
+    points_keys_kernel<T><<<dim3((unsigned)((max_cnt + 255) / 256), F), 256, 0, cs>>>(src, ft, ctx->d_bounds, hb, drop, ctx->d_keys[0], ctx->d_idx[0]);
+    const unsigned rblocks = (unsigned)((nW + RS_WARPS - 1) / RS_WARPS);
+    int in = 0;
+    for (int ps = 0; ps < passes; ++ps) {
+      radix_hist_kernel<<<rblocks, RS_BLOCK, 0, cs>>>(ctx->d_keys[in], n, 8 * ps, (int)E, nW, ctx->d_table);
+      radix_scan_kernel<<<sblocks, 1024, 0, cs>>>(ctx->d_table, tlen, ctx->d_sums, scan_done);
+      radix_scatter_kernel<<<rblocks, RS_BLOCK, 0, cs>>>(ctx->d_keys[in], ctx->d_idx[in], n, 8 * ps, (int)E, nW, ctx->d_table, ctx->d_sums, ctx->d_keys[in ^ 1], ctx->d_idx[in ^ 1]);
+      in ^= 1;
+    }
+    points_gather_kernel<T><<<gblocks, 256, 0, cs>>>(src, ctx->d_idx[in], ft, P.d_pts, P.d_perm, P.d_grp);
+    CU(cudaGetLastError());
+    ctx->launches += 4 + 3 * passes;
+    P.perm_on = true;
+  } else {
+    points_convert_kernel<T><<<gblocks, 256, 0, cs>>>(src, ft, P.d_pts, P.d_grp);
+    CU(cudaGetLastError());
+    ctx->launches++;
+  }
+  P.grp_on = true;
+  CU(cudaEventRecord(P.ready, cs));
   return FLASH_OK;
 }
 
+// back set -> front: kernels issued from now on read the new frame(s); the old front may be overwritten by the next
+// upload once everything already issued on the compute stream has run
+static int swap_sets(flash_ctx* ctx) {
+  flash_ctx::PointSet& old = ctx->ps[ctx->cur];
+  if (old.ready) { CU(cudaEventRecord(old.retired, ctx->stream)); old.retired_valid = true; }
+  ctx->cur ^= 1;
+  ctx->back_pending = false;
+  CU(cudaStreamWaitEvent(ctx->stream, ctx->ps[ctx->cur].ready, 0));
+  return FLASH_OK;
+}
+
+template <class T>
+static int points_set_sync(flash_ctx* ctx, const T* xyz, int64_t n) {
+  const T* ptrs[1] = {xyz};
+  const int64_t counts[1] = {n};
+  int rc = ingest<T>(ctx, ctx->ps[ctx->cur ^ 1], ptrs, counts, 1); if (rc) return rc;
+  rc = swap_sets(ctx); if (rc) return rc;
+  CU(cudaEventSynchronize(ctx->ps[ctx->cur].ready));   // the caller may reuse xyz as soon as we return
+  return FLASH_OK;
+}
 
 // ================================================================================================
 extern "C" {
@@ -389,6 +537,7 @@ int flash_model_create(const flash_model_desc* desc, const flash_options* opt, f
   make_hot(ctx->hm.M, ctx->hot);
   if (const char* e = getenv("FLASHSDF_NO_SORT")) ctx->sort_points = !(e[0] == '1');
   if (const char* e = getenv("FLASHSDF_NO_GROUP_CULL")) ctx->group_cull = !(e[0] == '1');
+  if (const char* e = getenv("FLASHSDF_NO_FEATURES")) ctx->features = !(e[0] == '1');
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0) {
@@ -407,6 +556,7 @@ int flash_model_create(const flash_model_desc* desc, const flash_options* opt, f
   ctx->sm_count = prop.multiProcessorCount; ctx->l2_bytes = prop.l2CacheSize; ctx->smem_optin = (int)prop.sharedMemPerBlockOptin;
   int khz = 0; cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev); ctx->clock_khz = khz;
   CUC(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  CUC(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
   for (auto& ev : ctx->ev) CUC(cudaEventCreate(&ev));
   const ModelC& M = ctx->hm.M;
   CUC(cudaMalloc((void**)&ctx->d_model, sizeof(ModelC)));
@@ -432,10 +582,21 @@ void flash_destroy(flash_ctx* ctx) {
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
-  void* frees[] = {ctx->d_model, ctx->d_hot, ctx->d_geo_f4, ctx->d_geo_u32, ctx->d_grid_pool, ctx->pts_external ? nullptr : (void*)ctx->d_pts, ctx->d_stage,
+  if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+  void* frees[] = {ctx->d_model, ctx->d_hot, ctx->d_geo_f4, ctx->d_geo_u32, ctx->d_grid_pool, ctx->d_stage,
                    ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, ctx->d_cost, ctx->d_grad, ctx->d_div, ctx->d_status, ctx->d_done, ctx->d_iters,
-                   ctx->d_argmin, ctx->d_qd, ctx->d_qi, ctx->d_bins, ctx->d_perm, ctx->d_grp};
+                   ctx->d_argmin, ctx->d_rec, ctx->d_qd, ctx->d_qi, ctx->d_keys[0], ctx->d_keys[1], ctx->d_idx[0], ctx->d_idx[1], ctx->d_table, ctx->d_sums, ctx->d_bounds};
   for (void* p : frees) if (p) cudaFree(p);
+  for (auto& P : ctx->ps) {
+    if (P.d_pts && !P.external) cudaFree(P.d_pts);
+    if (P.d_perm) cudaFree(P.d_perm);
+    if (P.d_grp) cudaFree(P.d_grp);
+    if (P.d_frames) cudaFree(P.d_frames);
+    if (P.ready) cudaEventDestroy(P.ready);
+    if (P.retired) cudaEventDestroy(P.retired);
+  }
+  for (int k = 0; k < 2; ++k) { if (ctx->h_ring[k]) cudaFreeHost(ctx->h_ring[k]); if (ctx->ring_done[k]) cudaEventDestroy(ctx->ring_done[k]); }
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   if (ctx->h_pin) cudaFreeHost(ctx->h_pin);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -445,36 +606,111 @@ void flash_destroy(flash_ctx* ctx) {
 int flash_num_positions(const flash_ctx* ctx) { return ctx ? ctx->hm.M.nq : FLASH_ERR_INVALID; }
 int flash_num_states(const flash_ctx* ctx) { return ctx ? ctx->hm.M.nx : FLASH_ERR_INVALID; }
 int flash_num_surfaces(const flash_ctx* ctx) { return ctx ? ctx->hm.M.n_surfaces : FLASH_ERR_INVALID; }
-int64_t flash_num_points(const flash_ctx* ctx) { return ctx ? ctx->n_pts : FLASH_ERR_INVALID; }
+int64_t flash_num_points(const flash_ctx* ctx) { return ctx ? ctx->ps[ctx->cur].n : FLASH_ERR_INVALID; }
 
 int flash_points_set(flash_ctx* ctx, const double* xyz, int64_t n) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set: bad arguments");
-  return points_ingest<double>(ctx, xyz, n);
+  return points_set_sync<double>(ctx, xyz, n);
 }
 
 int flash_points_set_f32(flash_ctx* ctx, const float* xyz, int64_t n) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_f32: bad arguments");
-  return points_ingest<float>(ctx, xyz, n);
+  return points_set_sync<float>(ctx, xyz, n);
 }
+
+int flash_points_set_async(flash_ctx* ctx, const double* xyz, int64_t n) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_async: bad arguments");
+  const double* ptrs[1] = {xyz};
+  const int64_t counts[1] = {n};
+  int rc = ingest<double>(ctx, ctx->ps[ctx->cur ^ 1], ptrs, counts, 1); if (rc) return rc;
+  ctx->back_pending = true;
+  return FLASH_OK;
+}
+
+int flash_points_set_async_f32(flash_ctx* ctx, const float* xyz, int64_t n) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_async_f32: bad arguments");
+  const float* ptrs[1] = {xyz};
+  const int64_t counts[1] = {n};
+  int rc = ingest<float>(ctx, ctx->ps[ctx->cur ^ 1], ptrs, counts, 1); if (rc) return rc;
+  ctx->back_pending = true;
+  return FLASH_OK;
+}
+
+int flash_points_swap(flash_ctx* ctx) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!ctx->back_pending) return fail(ctx, FLASH_ERR_STATE, "flash_points_swap: no flash_points_set_async / flash_frames_set_async pending");
+  CU(cudaSetDevice(ctx->device));
+  return swap_sets(ctx);
+}
+
+int flash_points_sync(flash_ctx* ctx) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->copy_stream));
+  return FLASH_OK;
+}
+
+static int frames_check(flash_ctx* ctx, const void* const* xyz, const int64_t* counts, int32_t F, const char* who) {
+  if (!xyz || !counts || F < 1 || F > MAX_FRAMES) return fail(ctx, FLASH_ERR_INVALID, std::string(who) + ": need 1.." + std::to_string(MAX_FRAMES) + " frames");
+  long long tot = 0;
+  for (int f = 0; f < F; ++f) { if (counts[f] < 0 || (counts[f] > 0 && !xyz[f])) return fail(ctx, FLASH_ERR_INVALID, std::string(who) + ": bad frame"); tot += counts[f]; }
+  if (tot >= (1ll << 31)) return fail(ctx, FLASH_ERR_TOO_LARGE, std::string(who) + ": more than 2^31 points in one batch of frames");
+  return 0;
+}
+
+int flash_frames_set(flash_ctx* ctx, const double* const* xyz, const int64_t* counts, int32_t F) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  int rc = frames_check(ctx, (const void* const*)xyz, counts, F, "flash_frames_set"); if (rc) return rc;
+  rc = ingest<double>(ctx, ctx->ps[ctx->cur ^ 1], xyz, counts, F); if (rc) return rc;
+  rc = swap_sets(ctx); if (rc) return rc;
+  CU(cudaEventSynchronize(ctx->ps[ctx->cur].ready));
+  return FLASH_OK;
+}
+
+int flash_frames_set_async(flash_ctx* ctx, const double* const* xyz, const int64_t* counts, int32_t F) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  int rc = frames_check(ctx, (const void* const*)xyz, counts, F, "flash_frames_set_async"); if (rc) return rc;
+  rc = ingest<double>(ctx, ctx->ps[ctx->cur ^ 1], xyz, counts, F); if (rc) return rc;
+  ctx->back_pending = true;
+  return FLASH_OK;
+}
+
+int flash_num_frames(const flash_ctx* ctx) { return ctx ? (ctx->ps[ctx->cur].set ? ctx->ps[ctx->cur].ft.n_frames : 0) : FLASH_ERR_INVALID; }
 
 int flash_points_set_device(flash_ctx* ctx, const void* device_float4, int64_t n) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (n < 0 || (n > 0 && !device_float4)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_device: bad arguments");
   if (((uintptr_t)device_float4 & 15) != 0) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_device: pointer must be 16-byte aligned");
   CU(cudaSetDevice(ctx->device));
-  if (!ctx->pts_external && ctx->d_pts) CU(cudaFree(ctx->d_pts));
-  ctx->d_pts = (float4*)device_float4; ctx->cap_pts = 0; ctx->pts_external = true; ctx->perm_on = false;
-  ctx->n_pts = n; ctx->pts_set = true;
-  return points_groups(ctx);
+  flash_ctx::PointSet& P = ctx->ps[ctx->cur ^ 1];
+  int rc = set_alloc(ctx, P, 32); if (rc) return rc;
+  cudaStream_t cs = ctx->copy_stream;
+  if (P.retired_valid) { CU(cudaStreamWaitEvent(cs, P.retired, 0)); P.retired_valid = false; }
+  if (!P.external && P.d_pts) { CU(cudaStreamSynchronize(cs)); CU(cudaFree(P.d_pts)); }
+  P.d_pts = (float4*)device_float4; P.cap_pts = 0; P.external = true; P.perm_on = false; P.grp_on = false;
+  P.n = n; P.max_cnt = n; P.set = true;
+  P.ft.n_frames = 1; P.ft.off[0] = 0; P.ft.off[1] = (n + 31) & ~31ll; P.ft.cnt[0] = n; P.ft.src_off[0] = 0; P.ft.src_off[1] = n;
+  if (n > 0) {
+    const long long groups = (n + 31) / 32;
+    rc = ensure(ctx, P.d_grp, P.cap_grp, (size_t)groups); if (rc) return rc;
+    groups_ball_kernel<<<(unsigned)((groups * 32 + 255) / 256), 256, 0, cs>>>(P.d_pts, n, P.d_grp);
+    CU(cudaGetLastError());
+    ctx->launches++;
+    P.grp_on = true;
+  }
+  CU(cudaEventRecord(P.ready, cs));
+  rc = swap_sets(ctx); if (rc) return rc;
+  CU(cudaEventSynchronize(ctx->ps[ctx->cur].ready));
+  return FLASH_OK;
 }
 
-int flash_cost_grad(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad, int32_t* argmin) {
-  if (!ctx) return FLASH_ERR_INVALID;
-  if (!X || C < 1 || !cost) return fail(ctx, FLASH_ERR_INVALID, "flash_cost_grad: bad arguments");
-  if (!ctx->pts_set) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad: call flash_points_set first");
+static int cost_grad_impl(flash_ctx* ctx, const double* X, int32_t C, int cfg_per_frame, double w_def, double* cost, double* grad, int32_t* argmin, const char* who) {
   const ModelC& M = ctx->hm.M;
+  const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
   CU(cudaSetDevice(ctx->device));
   int rc = ensure_batch(ctx, C); if (rc) return rc;
   ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
@@ -483,19 +719,39 @@ int flash_cost_grad(flash_ctx* ctx, const double* X, int32_t C, double w_def, do
   CU(cudaMemcpyAsync(ctx->d_X, ctx->h_pin, nX * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   int32_t* d_arg = nullptr;
   if (argmin) {
-    rc = ensure(ctx, ctx->d_argmin, ctx->cap_argmin, (size_t)C * (size_t)std::max<long long>(ctx->n_pts, 1)); if (rc) return rc;
+    rc = ensure(ctx, ctx->d_argmin, ctx->cap_argmin, (size_t)C * (size_t)std::max<long long>(P.n, 1)); if (rc) return rc;
     d_arg = ctx->d_argmin;
   }
-  rc = pipeline(ctx, C, w_def, grad != nullptr, d_arg); if (rc) return rc;
+  rc = pipeline(ctx, C, w_def, grad != nullptr, d_arg, cfg_per_frame); if (rc) return rc;
   double* h_cost = ctx->h_pin + nX;
   double* h_grad = h_cost + C;
   CU(cudaMemcpyAsync(h_cost, ctx->d_cost, (size_t)C * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
   if (grad) CU(cudaMemcpyAsync(h_grad, ctx->d_grad, nX * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-  if (argmin && ctx->n_pts > 0) CU(cudaMemcpyAsync(argmin, d_arg, (size_t)C * ctx->n_pts * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  if (argmin && P.n > 0) CU(cudaMemcpyAsync(argmin, d_arg, (size_t)C * P.n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
   rc = check_status(ctx); if (rc) return rc;   // synchronises the stream
   std::memcpy(cost, h_cost, (size_t)C * sizeof(double));
   if (grad) std::memcpy(grad, h_grad, nX * sizeof(double));
+  (void)who;
   return collect_timing(ctx);
+}
+
+int flash_cost_grad(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad, int32_t* argmin) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!X || C < 1 || !cost) return fail(ctx, FLASH_ERR_INVALID, "flash_cost_grad: bad arguments");
+  const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
+  if (!P.set) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad: call flash_points_set first");
+  if (P.ft.n_frames != 1) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad: the ctx holds a batch of frames, use flash_cost_grad_frames");
+  return cost_grad_impl(ctx, X, C, 0, w_def, cost, grad, argmin, "flash_cost_grad");
+}
+
+int flash_cost_grad_frames(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!X || C < 1 || !cost) return fail(ctx, FLASH_ERR_INVALID, "flash_cost_grad_frames: bad arguments");
+  const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
+  if (!P.set) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad_frames: call flash_frames_set first");
+  const long long tot = (long long)C * P.ft.n_frames;
+  if (tot > 65535 * 16) return fail(ctx, FLASH_ERR_TOO_LARGE, "flash_cost_grad_frames: frames x configs too large");
+  return cost_grad_impl(ctx, X, (int32_t)tot, C, w_def, cost, grad, nullptr, "flash_cost_grad_frames");
 }
 
 int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t n, double* dist, int32_t* argmin) {
@@ -521,7 +777,7 @@ int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t 
   CostParams p;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
   p.geo_f4_n = M.geo_f4; p.geo_u32_n = M.geo_u32;
-  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr;
+  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr; p.frames = nullptr; p.cfg_per_frame = 1; p.rec = nullptr; p.rec_stride = 0;
   p.pts_per_block = choose_tile(ctx, n, 1); p.use_grid = ctx->use_grid ? 1 : 0;
   const int tiles = (int)((n + p.pts_per_block - 1) / p.pts_per_block);
   const size_t smem = cost_layout(ctx, false).total;
@@ -584,7 +840,8 @@ int flash_raycast(flash_ctx* ctx, const double* x, const double* rays, int64_t R
 int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solver_params* sp, const double* divisors, double* cost_out, int32_t* iters_out) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (!X || C < 1 || !sp || sp->iteration_limit < 0) return fail(ctx, FLASH_ERR_INVALID, "flash_estimate_state: bad arguments");
-  if (!ctx->pts_set) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: call flash_points_set first");
+  if (!ctx->ps[ctx->cur].set) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: call flash_points_set first");
+  if (ctx->ps[ctx->cur].ft.n_frames != 1) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: the ctx holds a batch of frames");
   const ModelC& M = ctx->hm.M;
   CU(cudaSetDevice(ctx->device));
   int rc = ensure_batch(ctx, C); if (rc) return rc;
@@ -599,7 +856,7 @@ int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solve
     CU(cudaMemcpyAsync(ctx->d_div, divisors, (size_t)M.nx * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   }
   // total point count across ranks (the reference divides by length(sensed_points), src/tracking.jl:20)
-  double n_total = (double)ctx->n_pts;
+  double n_total = (double)ctx->ps[ctx->cur].n;
   if (ctx->comm) {
     double* d_n = ctx->d_cost;  // scratch
     CU(cudaMemcpyAsync(d_n, &n_total, sizeof(double), cudaMemcpyHostToDevice, ctx->stream));

@@ -19,6 +19,8 @@ SYMBOLS = [
     "flash_estimate_state", "flash_comm_unique_id", "flash_comm_init", "flash_comm_world",
     "flash_profiling", "flash_last_timing", "flash_launch_count", "flash_device_info",
     "flash_grid_report", "flash_grid_download", "flash_contour_mesh",
+    "flash_points_set_async", "flash_points_set_async_f32", "flash_points_swap", "flash_points_sync",
+    "flash_frames_set", "flash_frames_set_async", "flash_num_frames", "flash_cost_grad_frames",
 ]
 
 _lib = None
@@ -44,6 +46,14 @@ def lib():
     L.flash_points_set.argtypes = [vp, c_double_p, C.c_int64]
     L.flash_points_set_f32.argtypes = [vp, C.POINTER(C.c_float), C.c_int64]
     L.flash_points_set_device.argtypes = [vp, vp, C.c_int64]
+    L.flash_points_set_async.argtypes = [vp, c_double_p, C.c_int64]
+    L.flash_points_set_async_f32.argtypes = [vp, C.POINTER(C.c_float), C.c_int64]
+    L.flash_points_swap.argtypes = [vp]
+    L.flash_points_sync.argtypes = [vp]
+    L.flash_frames_set.argtypes = [vp, C.POINTER(c_double_p), C.POINTER(C.c_int64), C.c_int32]
+    L.flash_frames_set_async.argtypes = [vp, C.POINTER(c_double_p), C.POINTER(C.c_int64), C.c_int32]
+    L.flash_num_frames.argtypes = [vp]
+    L.flash_cost_grad_frames.argtypes = [vp, c_double_p, C.c_int32, C.c_double, c_double_p, c_double_p]
     L.flash_num_points.argtypes = [vp]; L.flash_num_points.restype = C.c_int64
     L.flash_cost_grad.argtypes = [vp, c_double_p, C.c_int32, C.c_double, c_double_p, c_double_p, c_int32_p]
     L.flash_skin_eval.argtypes = [vp, c_double_p, c_double_p, C.c_int64, c_double_p, c_int32_p]

@@ -81,3 +81,37 @@ def CostAndGradientFunctor(cost):  # src/gradientdescent.jl:59-65: (g, x) -> val
         g[:] = grad[0]
         return float(c[0])
     return f
+
+
+class FramesCostFunctor:
+    """A batch of F frames evaluated with C candidate states per frame in one launch (BASELINE.json configs[3]:
+    8 Kinect frames x 16 candidates): flash_frames_set + flash_cost_grad_frames.  X is [F][C][nx]."""
+
+    def __init__(self, manipulator, frames):
+        import ctypes as C
+        self.manipulator = manipulator
+        self.frames = [np.ascontiguousarray(f, dtype=np.float64).reshape(-1, 3) for f in frames]
+        self._ptrs = (c_double_p * len(self.frames))(*[f.ctypes.data_as(c_double_p) for f in self.frames])
+        self._counts = (C.c_int64 * len(self.frames))(*[len(f) for f in self.frames])
+        self.upload()
+
+    def upload(self):
+        m = self.manipulator
+        m.check(_lib.lib().flash_frames_set(m.ctx(), self._ptrs, self._counts, len(self.frames)))
+        m._points_owner = self
+
+    def batch(self, X, gradient=True, deformation_cost_weight=default_deformation_cost_weight):
+        m = self.manipulator
+        nx = num_states(m)
+        X = np.ascontiguousarray(X, dtype=np.float64)
+        F = len(self.frames)
+        if X.ndim != 3 or X.shape[0] != F or X.shape[2] != nx:
+            raise ValueError("X must be [%d frames][C][%d states]" % (F, nx))
+        if m._points_owner is not self or m._ctx is None:
+            self.upload()
+        Cn = X.shape[1]
+        cost = np.empty((F, Cn))
+        grad = np.empty((F, Cn, nx)) if gradient else None
+        m.check(_lib.lib().flash_cost_grad_frames(m.ctx(), X.ctypes.data_as(c_double_p), Cn, float(deformation_cost_weight),
+                                                  cost.ctypes.data_as(c_double_p), grad.ctypes.data_as(c_double_p) if gradient else None))
+        return cost, grad

@@ -17,6 +17,8 @@ struct HC { HostModel hm; HotModel hot; };
 static int g_group_cull = 1;            // replay the warp-level hull culling of cost_kernel
 static int g_skin_cull = 1;             // ... and the group-level skin cull
 static int g_feat = 1;                  // ... and the group feature certification
+static int g_warm = 1;                  // ... and the GJK warm start from the group's hint
+static int g_dbg = 0;
 static long long g_feat_groups[4] = {0, 0, 0, 0};
 static long long g_skin_groups_skipped = 0;
 static long long g_cand_total = 0, g_groups = 0, g_rounds_or = 0, g_rounds_max = 0;
@@ -90,18 +92,31 @@ void hc_accumulate(void* p, const double* tab, const float* pts, long long n, in
   unsigned skin_skip = 0u; float cut0 = 3.0e38f; unsigned feat = 0u;
   for (long long i = 0; i < n; ++i) {
     if (g_group_cull && (i & 31) == 0 && H.n_convex > 1) {
-      // the warp's 32 points: bounding ball as points_groups_kernel computes it, then the candidate hulls
-      float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
-      for (long long k = i; k < n && k < i + 32; ++k)
-        for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], pts[3 * k + a]); hi[a] = fmaxf(hi[a], pts[3 * k + a]); }
-      const float cx = 0.5f * (lo[0] + hi[0]), cy = 0.5f * (lo[1] + hi[1]), cz = 0.5f * (lo[2] + hi[2]);
-      const float ex = fmaxf(hi[0] - cx, cx - lo[0]), ey = fmaxf(hi[1] - cy, cy - lo[1]), ez = fmaxf(hi[2] - cz, cz - lo[2]);
-      const float rho = sqrtf(ex * ex + ey * ey + ez * ez) * (1.f + 1e-6f) + 1e-30f;
+      // the warp's 32 points: bounding ball as flash_ingest.cuh warp_ball computes it (Badoiu-Clarkson from the centroid)
+      const int cntp = (int)std::min<long long>(32, n - i);
+      float cx = 0.f, cy = 0.f, cz = 0.f;
+      for (int k = 0; k < cntp; ++k) { cx += pts[3 * (i + k)]; cy += pts[3 * (i + k) + 1]; cz += pts[3 * (i + k) + 2]; }
+      cx /= cntp; cy /= cntp; cz /= cntp;
+      float mm = 0.f;
+      for (int it = 0; it <= 10; ++it) {
+        int who = 0; mm = -1.f;
+        for (int k = 0; k < cntp; ++k) {
+          const float dx = pts[3 * (i + k)] - cx, dy = pts[3 * (i + k) + 1] - cy, dz = pts[3 * (i + k) + 2] - cz;
+          const float d2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+          if (d2 > mm) { mm = d2; who = k; }
+        }
+        if (it == 10) break;
+        const float sgl = 1.0f / (float)(it + 2);
+        cx = fmaf(pts[3 * (i + who)] - cx, sgl, cx); cy = fmaf(pts[3 * (i + who) + 1] - cy, sgl, cy); cz = fmaf(pts[3 * (i + who) + 2] - cz, sgl, cz);
+      }
+      const float rho = sqrtf(fmaxf(mm, 0.f)) * (1.f + 2e-6f) + 1e-30f;
       const GroupPre gp = group_prepass(H, G, tabf, cx, cy, cz, rho, g_feat != 0, g_skin_cull != 0);
       cand = gp.cand; first = gp.first; skin_skip = gp.skip; cut0 = gp.cut; feat = gp.feat;
       g_cand_total += __builtin_popcount(cand); g_groups += 1;
       g_skin_groups_skipped += skin_skip ? 1 : 0;
-      g_feat_groups[feat & 3u] += 1;
+      if (!g_warm && !(feat & FEAT_CERT)) feat = 0u;
+      g_feat_groups[(feat & FEAT_CERT) ? (feat & 3u) : 0u] += 1;
+      if (g_dbg) printf("group %lld first %d feat %08x cand %x rho %g c %g %g %g\n", i / 32, first, feat, cand, rho, cx, cy, cz);
     }
     PointEval e;
 #ifdef FLASH_COUNTERS
@@ -148,6 +163,8 @@ void hc_epilogue(void* p, const double* x, const double* tab, const double* aux,
 void hc_set_group_cull(int on) { g_group_cull = on; }
 void hc_set_skin_cull(int on) { g_skin_cull = on; }
 void hc_set_feature(int on) { g_feat = on; }
+void hc_set_warm(int on) { g_warm = on; }
+void hc_set_dbg(int on) { g_dbg = on; }
 // groups by certified feature type: none, vertex, edge, face
 void hc_feature_stats(long long* out, int reset) { for (int k = 0; k < 4; ++k) { out[k] = g_feat_groups[k]; if (reset) g_feat_groups[k] = 0; } }
 long long hc_skin_groups_skipped(int reset) { long long v = g_skin_groups_skipped; if (reset) g_skin_groups_skipped = 0; return v; }
@@ -169,10 +186,10 @@ void hc_counters(long long* out, int reset) {
 #ifdef FLASH_COUNTERS
   Counters& c = counters();
   out[0] = c.points; out[1] = c.narrow; out[2] = c.inside; out[3] = c.gjk_iters; out[4] = c.plane_tests; out[5] = c.vert_tests; out[6] = c.lb_tests; out[7] = c.skin64;
-  out[8] = c.feat_evals;
-  if (reset) c = Counters{0, 0, 0, 0, 0, 0, 0, 0, 0, 0u};
+  out[8] = c.feat_evals; out[9] = c.warm;
+  if (reset) c = Counters{0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0u};
 #else
-  for (int i = 0; i < 9; ++i) out[i] = -1;
+  for (int i = 0; i < 10; ++i) out[i] = -1;
 #endif
 }
 
@@ -217,3 +234,18 @@ void hc_hull_sd(void* p, int j, const float* y, long long n, float* d, float* nr
 }
 
 }  // extern "C"
+
+// GJK warm-started from every possible hint simplex of hull j against the cold start (debugging aid + test)
+extern "C" void hc_hull_warm(void* p, int j, const float* y, long long n, const int* ids /* [n][3], -1 = unused */, float* d, int* ok) {
+  HC* h = (HC*)p;
+  const ConvexC& C = h->hm.M.cvx[j];
+  GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
+  const HullView V = hull_view(G, C);
+  for (long long i = 0; i < n; ++i) {
+    Simplex S; S.ns = 0; S.ia = S.ib = S.ic = 0;
+    for (int k = 0; k < 3; ++k) if (ids[3 * i + k] >= 0) { if (S.ns == 0) S.ia = ids[3 * i + k]; else if (S.ns == 1) S.ib = ids[3 * i + k]; else S.ic = ids[3 * i + k]; ++S.ns; }
+    F3 nn; float dd = 0.f;
+    ok[i] = hull_sd_warm(V, feat_hint(S), f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]), dd, nn) ? 1 : 0;
+    d[i] = dd;
+  }
+}

@@ -131,9 +131,9 @@ class HostCheck:
 
 
 def counters(reset=True):
-    out = (C.c_longlong * 9)()
+    out = (C.c_longlong * 10)()
     lib().hc_counters(out, 1 if reset else 0)
-    return dict(zip(("points", "narrow", "inside", "gjk_iters", "plane_tests", "vert_tests", "lb_tests", "skin64", "feat_evals"), list(out)))
+    return dict(zip(("points", "narrow", "inside", "gjk_iters", "plane_tests", "vert_tests", "lb_tests", "skin64", "feat_evals", "warm"), list(out)))
 
 
 def set_group_cull(on):

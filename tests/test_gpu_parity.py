@@ -425,3 +425,46 @@ def test_two_functors_on_one_manipulator_keep_their_own_points():
     assert arg.shape == (1, 5000)
     assert np.isclose(flash.gradientdescent.cost(flash.ManipulatorState(m), pb), fb(np.zeros(6)), rtol=1e-12)
     assert np.isclose(fa(x), ca, rtol=1e-12)
+
+
+def test_frames_batch_equals_frame_by_frame_and_async_swap_pipelines():
+    """flash_frames_set + flash_cost_grad_frames (F frames x C candidates per frame, one launch) == one
+    flash_points_set + flash_cost_grad per frame; flash_points_set_async / flash_points_swap hand over the frames in
+    order while the previous one is still being evaluated."""
+    import ctypes as C
+    from flash import _lib
+    from flash._desc import c_double_p
+    rng = np.random.default_rng(31)
+    m = flash.models.irb_and_squishable()
+    nx = flash.num_states(m)
+    x0 = flash.gradientdescent.flatten(flash.ManipulatorState(m))
+    x0[4:7] = [0.0, 0.0, 0.75]; x0[17:20] = [0.55, 0.45, 0.8]; x0[24:27] = [0.4, 0.0, 0.6]
+    frames = [_points(rng, n, [-0.5, -0.5, 0.5], [1.0, 0.5, 2.0]) for n in (9000, 20011, 33, 15000)]
+    X = x0 + 0.03 * rng.standard_normal((4, 3, nx))
+    ff = flash.gradientdescent.FramesCostFunctor(m, frames)
+    cost, grad = ff.batch(X)
+    o = ol.Oracle(m)
+    for f, pts in enumerate(frames):
+        c1, g1, _ = flash.gradientdescent.CostFunctor(m, pts).batch(X[f])
+        # the batch sorts all frames in one pass (coarser keys): other groups of 32, so other points take the certified-
+        # feature path instead of GJK -- same distances to fp32 rounding (1e-7 m), not bit for bit
+        assert np.allclose(cost[f], c1, rtol=1e-7)
+        assert np.abs(grad[f] - g1).max() <= 1e-6 * np.abs(g1).max()
+        co, go = o.cost_grad(X[f, 1], pts, method="adjoint", mode=ol.GJK)
+        assert abs(cost[f, 1] - co) <= RTOL * abs(co) and np.abs(grad[f, 1] - go).max() <= RTOL * np.abs(go).max()
+    # async pipeline: upload frame k+1 while frame k is evaluated
+    L = _lib.lib(); ctx = m.ctx()
+    m.check(L.flash_points_set_async(ctx, frames[0].ctypes.data_as(c_double_p), len(frames[0])))
+    got = []
+    for k in range(4):
+        m.check(L.flash_points_swap(ctx))
+        if k + 1 < 4:
+            m.check(L.flash_points_set_async(ctx, frames[k + 1].ctypes.data_as(c_double_p), len(frames[k + 1])))
+        c = np.empty(3); g = np.empty((3, nx))
+        Xk = np.ascontiguousarray(X[k])
+        m.check(L.flash_cost_grad(ctx, Xk.ctypes.data_as(c_double_p), 3, 10.0, c.ctypes.data_as(c_double_p), g.ctypes.data_as(c_double_p), None))
+        assert L.flash_num_points(ctx) == len(frames[k])
+        got.append(c)
+    m._points_owner = None
+    assert np.allclose(np.array(got), cost, rtol=1e-7)
+    assert L.flash_points_swap(ctx) != 0          # nothing pending: FLASH_ERR_STATE, reported not thrown

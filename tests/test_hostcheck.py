@@ -139,9 +139,10 @@ def test_warp_group_culling_changes_nothing_and_culls():
 
 
 def test_group_feature_certification_is_exact_and_fires():
-    """hull_ball_feature: groups whose bounding ball lies in the Voronoi region of one face / edge / vertex of the
-    nearest hull evaluate that hull by the feature's closed form.  Same distances as the GJK path to fp32 rounding
-    (and as the fp64 oracle), same argmin; the exact centre distance also tightens the group's hull and skin culls."""
+    """hull_ball_feature: groups whose bounding ball lies in the Voronoi region of one FACE of the nearest hull
+    evaluate that hull by the plane's closed form; groups entirely outside it start every point's GJK from the simplex
+    found at the ball centre (hull_sd_warm).  Same distances as the cold GJK path to fp32 rounding (and as the fp64
+    oracle), same argmin; the exact centre distance also tightens the group's hull and skin culls."""
     rng = np.random.default_rng(12)
     m = flash.models.irb_and_squishable()
     h = hl.HostCheck(m)
@@ -168,9 +169,9 @@ def test_group_feature_certification_is_exact_and_fires():
     per = np.sort(o.surfaces(x, pts[flips].astype(np.float64), mode=ol.GJK), axis=1) if len(flips) else np.zeros((0, 2))
     assert len(flips) <= 4 and (per[:, 1] - per[:, 0] < 2e-6).all()
     assert np.abs(a1 - a0).max() <= 1e-6 * np.abs(a0).max()
-    groups = sum(fs.values())
-    assert fs["vertex"] > 0 and fs["edge"] > 0 and fs["face"] > 0 and fs["none"] < 0.8 * groups
-    assert cn["feat_evals"] > 0.2 * cn["points"]
+    assert fs["face"] > 0 and cn["feat_evals"] > 0.02 * cn["points"]
+    assert cn["warm"] > 0.4 * cn["points"]          # most groups are clear of the hulls: warm-started GJK
+    assert cn["narrow"] < 0.6 * cn["points"]        # ... and the cold narrow phase (plane hint, start triangle) is the exception
 
 
 @pytest.mark.parametrize("name", ["irb_and_squishable", "squishable", "two_link_arm", "beanbag"])
