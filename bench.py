@@ -342,9 +342,12 @@ def run_ours(args, rank, local_rank, world):
             "checksum_cost_sum": checksum,
         }
         if world == 1 and args.extras:
-            line["grid_mode"] = grid_leg(args, flash, L, X, pts, n_local, cost.copy(), flush)
-            line["tracking"] = tracking_leg(flash, L)
-            line["other_configs"] = configs_leg(flash, L, args.steps)
+            if args.grid_leg:
+                line["grid_mode"] = grid_leg(args, flash, L, X, pts, n_local, cost.copy(), flush)
+            if args.tracking_leg:
+                line["tracking"] = tracking_leg(flash, L)
+            if args.configs_leg:
+                line["other_configs"] = configs_leg(flash, L, args.steps)
         if args.parity:
             line["parity"] = parity_leg(flash, m, L, ctx, X, cost, grad, pts, n_local, N, rank, world)
         if args.cpu_baseline and world == 1:
@@ -580,6 +583,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
     ap.add_argument("--no-parity", dest="parity", action="store_false", help="skip the oracle check of config 0 after the timed loops")
     ap.add_argument("--no-extras", dest="extras", action="store_false", help="skip the grid-mode and K3 tracking legs (N=1 only)")
+    ap.add_argument("--no-grid", dest="grid_leg", action="store_false", help="skip the grid-mode leg")
+    ap.add_argument("--no-tracking", dest="tracking_leg", action="store_false", help="skip the K3 tracking leg")
+    ap.add_argument("--no-configs", dest="configs_leg", action="store_false", help="skip the K2 / K4 legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

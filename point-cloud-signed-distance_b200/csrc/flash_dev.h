@@ -1203,6 +1203,12 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
       rest &= rest - 1u;
     }
     const ConvexC& C = cvx[j];
+    // Per-point use of the group's certified feature / GJK warm start.  Compiled into the device loop only on request
+    // (-DFLASH_FEAT_PATH): measured on K5 it LOSES -- 54.9 ms with it, 49.0 with the code present but never taken,
+    // 42.2 ms without the code (round 2, B200; K2 0.110 / 0.088 / 0.080 ms, K4 4.65 / 4.41 / 3.97 ms): the point loop is
+    // instruction-fetch and register bound (80 registers: 460 B of spills with the path, 216 B without).  The host
+    // replay (tests/hostcheck) keeps it, so the certificates stay tested.
+#if !defined(__CUDA_ARCH__) || defined(FLASH_FEAT_PATH)
     if ((feat & 3u) != 0u && j == first) {
       const F3 y = to_geometry(tab + 12 * j, px, py, pz);
       F3 n; float d; bool ok = true;
@@ -1217,6 +1223,7 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
         continue;
       }
     }
+#endif
     bool skip = false;
     if (!single) {
       FLASH_COUNT(lb_tests, 1);

@@ -95,7 +95,7 @@ struct flash_ctx {
   double* h_pin = nullptr; size_t cap_pin = 0;  // pinned staging for X / cost / grad
   int32_t* d_argmin = nullptr; size_t cap_argmin = 0;
   uint4* d_rec = nullptr; size_t cap_rec = 0;   // group records of group_kernel, [C][rec_stride]
-  bool features = true;
+  bool features = false;   // exact narrow phase at the ball centre in group_kernel (tighter group bound): off by default, see flash_dev.h eval_point
   // query scratch (skin_eval / raycast)
   double* d_qd = nullptr; size_t cap_qd = 0;
   int* d_qi = nullptr; size_t cap_qi = 0;
@@ -537,7 +537,7 @@ int flash_model_create(const flash_model_desc* desc, const flash_options* opt, f
   make_hot(ctx->hm.M, ctx->hot);
   if (const char* e = getenv("FLASHSDF_NO_SORT")) ctx->sort_points = !(e[0] == '1');
   if (const char* e = getenv("FLASHSDF_NO_GROUP_CULL")) ctx->group_cull = !(e[0] == '1');
-  if (const char* e = getenv("FLASHSDF_NO_FEATURES")) ctx->features = !(e[0] == '1');
+  if (const char* e = getenv("FLASHSDF_FEATURES")) ctx->features = (e[0] == '1');
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0) {
