@@ -10,6 +10,7 @@
 #pragma once
 #include <math.h>
 #include <stdint.h>
+#include <string.h>
 
 #ifdef __CUDACC__
 #define FLASH_HD __host__ __device__ __forceinline__
@@ -64,6 +65,8 @@ struct ConvexC {
   double frame[12];                          // geometry frame -> body frame
   // grid mode (body-frame SDF grid): origin, spacing, dims, offset into the grid pool (floats)
   float g_org[3]; float g_inv_h; int g_dim[3]; int g_on; long long g_off;
+  // closest-feature BSP tree (flash_bsp.h): node planes / plain plane table / vertices / edges (F4 indices), child words (u32 index)
+  int bsp_on, off_bn, off_bk, off_bp, off_bv, off_be;
 };
 
 struct SkinC {
@@ -411,7 +414,8 @@ FLASH_HD int dir_cell(F3 d) {
 // counts are padded to a multiple of 8; padding planes can never be the maximum, padding vertices are
 // copies of vertex 0 (never a strictly better support).
 struct HullView { const F4* planes; const uint32_t* ptri; const F4* va; const float* vz; int np, nv;
-                  const unsigned short* voff; const unsigned char* vlist; const unsigned short* pgrp; };
+                  const unsigned short* voff; const unsigned char* vlist; const unsigned short* pgrp;
+                  const F4* bn; const uint32_t* bk; const F4* bp; const F4* bv; const F4* be; int bsp_on; };
 FLASH_HD F3 plane_normal(const F4* P, int f) { const float* a = reinterpret_cast<const float*>(P + (f & ~1)); const int h = f & 1; return f3(a[h], a[2 + h], a[4 + h]); }
 FLASH_HD F3 vert_at(const HullView& V, int j) { const float* a = reinterpret_cast<const float*>(V.va + (j >> 1)); const int h = j & 1; return f3(a[h], a[2 + h], V.vz[j]); }
 
@@ -664,6 +668,61 @@ FLASH_HD float hull_sd_ex(const HullView& V, F3 y, float cutoff, F3& nrm, int* k
   return hull_gjk_finish(V, q, D, fs, nrm);
 }
 FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) { return hull_sd_ex(V, y, cutoff, nrm, nullptr, nullptr, nullptr); }
+
+// ---- closest-feature BSP (flash_bsp.h): one plane test per level locates the cell of y, whose feature gives the
+// signed distance and its gradient in closed form.  Leaf word: 0x8000 | kind << 13 | index, kind 0 = face (plane
+// index), 1 = vertex, 2 = edge (edge table: unit direction + first vertex).  Lane-uniform: every lane runs the same
+// ~9 instructions per level, whatever its path.
+FLASH_HD unsigned bsp_locate(const F4* __restrict__ nodes, const uint32_t* __restrict__ kids, F3 y) {
+  unsigned k = 0u;
+  do {
+#ifdef __CUDA_ARCH__
+    const float4 pp = __ldg(reinterpret_cast<const float4*>(nodes) + k);
+    F4 p; p.x = pp.x; p.y = pp.y; p.z = pp.z; p.w = pp.w;
+    const uint32_t w = __ldg(kids + k);
+#else
+    const F4 p = nodes[k];
+    const uint32_t w = kids[k];
+#endif
+    const float s = fmaf(p.x, y.x, fmaf(p.y, y.y, fmaf(p.z, y.z, p.w)));
+    k = s > 0.f ? (w >> 16) : (w & 0xffffu);
+  } while (!(k & 0x8000u));
+  return k;
+}
+FLASH_HD float bsp_feature_sd(const HullView& V, unsigned leaf, F3 y, F3& nrm) {
+  const unsigned kind = (leaf >> 13) & 3u, idx = leaf & 0x1fffu;
+  if (kind == 0u) {
+    const F4 p = V.bp[idx];
+    nrm = f3(p.x, p.y, p.z);
+    return fmaf(p.x, y.x, fmaf(p.y, y.y, fmaf(p.z, y.z, p.w)));
+  }
+  F3 u = f3(0.f, 0.f, 0.f);
+  unsigned ia = idx;
+  if (kind == 2u) {
+    const F4 e = V.be[idx];
+    u = f3(e.x, e.y, e.z);
+#ifdef __CUDA_ARCH__
+    ia = __float_as_uint(e.w);
+#else
+    memcpy(&ia, &e.w, 4);
+#endif
+  }
+  const F4 a = V.bv[ia];
+  F3 r = y - f3(a.x, a.y, a.z);
+  const float t = dot(r, u);
+  r = f3(fmaf(-t, u.x, r.x), fmaf(-t, u.y, r.y), fmaf(-t, u.z, r.z));   // vertex: u = 0
+  const float dd = dot(r, r);
+  if (!(dd > 0.f)) { nrm = f3(0.f, 0.f, 0.f); return 0.f; }                // on the feature itself
+#ifdef __CUDA_ARCH__
+  float inv = rsqrtf(dd);
+  inv = inv * (1.5f - 0.5f * dd * inv * inv);   // one Newton step: ~1 ulp
+#else
+  const float inv = 1.0f / sqrtf(dd);
+#endif
+  nrm = r * inv;
+  return dd * inv;
+}
+FLASH_HD float hull_sd_bsp(const HullView& V, F3 y, F3& nrm) { return bsp_feature_sd(V, bsp_locate(V.bn, V.bk, y), y, nrm); }
 
 // ---- group feature certification ---------------------------------------------------------------------------------
 // The 32 points one warp evaluates together are Morton neighbours inside a ball B(c, rho) (points_groups_kernel).
@@ -1049,6 +1108,7 @@ FLASH_HD HullView hull_view(const GeoView& G, const ConvexC& C) {
   V.voff = reinterpret_cast<const unsigned short*>(G.u32 + C.off_voff);
   V.vlist = reinterpret_cast<const unsigned char*>(G.u32 + C.off_vlist);
   V.pgrp = reinterpret_cast<const unsigned short*>(G.u32 + C.off_pgrp);
+  V.bn = G.f4 + C.off_bn; V.bk = G.u32 + C.off_bk; V.bp = G.f4 + C.off_bp; V.bv = G.f4 + C.off_bv; V.be = G.f4 + C.off_be; V.bsp_on = C.bsp_on;
   return V;
 }
 
@@ -1238,7 +1298,11 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
 #if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
       const long long narrow0 = flashdev::counters().narrow;
 #endif
+#ifdef FLASH_GJK_PATH
       if (!done) d = hull_sd(hull_view(G, C), y, fminf(best, cut), n);
+#else
+      if (!done) { FLASH_COUNT(narrow, 1); d = hull_sd_bsp(hull_view(G, C), y, n); }
+#endif
 #if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
       if (flashdev::counters().narrow != narrow0) flashdev::counters().exact_mask |= 1u << j;
 #endif

@@ -15,6 +15,7 @@
 
 #include "../../include/flashsdf.h"
 #include "flash_dev.h"
+#include "flash_bsp.h"
 
 namespace flashhost {
 
@@ -25,6 +26,7 @@ struct HostModel {
   std::vector<F4> geo_f4;
   std::vector<uint32_t> geo_u32;
   flash_options opt;
+  std::vector<std::array<double, 5>> bsp_stats;   // per convex slot: nodes, max depth, mean leaf depth, cells, dropped slivers
 };
 
 struct HullOut {
@@ -381,6 +383,25 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
         db = std::min(db, w);
       }
       C.depth_bound = (float)(db * 1.0001 + 1e-6);
+      {
+        // closest-feature BSP tree (flash_bsp.h) -> blob: node planes, plain plane table {n, -o}, vertices {x, y, z, 0}, edges
+        flashbsp::BspHull bh; std::string berr;
+        C.bsp_on = 0; C.off_bn = C.off_bk = C.off_bp = C.off_bv = C.off_be = 0;
+        if (opt.reserved[0] != 1 && flashbsp::build_bsp(H.verts, H.planes, bh, berr)) {
+          C.bsp_on = 1;
+          C.off_bn = (int)out.geo_f4.size();
+          for (auto& p : bh.node_plane) out.geo_f4.push_back(F4{p[0], p[1], p[2], p[3]});
+          C.off_bp = (int)out.geo_f4.size();
+          for (auto& p : H.planes) out.geo_f4.push_back(F4{(float)p[0], (float)p[1], (float)p[2], -(float)p[3]});
+          C.off_bv = (int)out.geo_f4.size();
+          for (auto& v : H.verts) out.geo_f4.push_back(F4{(float)v.x, (float)v.y, (float)v.z, 0.f});
+          C.off_be = (int)out.geo_f4.size();
+          for (auto& e : bh.edges) out.geo_f4.push_back(F4{e[0], e[1], e[2], e[3]});
+          C.off_bk = (int)out.geo_u32.size();
+          for (uint32_t w : bh.node_kids) out.geo_u32.push_back(w);
+          out.bsp_stats.push_back({(double)bh.node_plane.size(), (double)bh.max_depth, bh.mean_depth, (double)bh.n_regions, (double)bh.n_dropped});
+        } else out.bsp_stats.push_back({0, 0, 0, 0, 0});
+      }
       // geometry frame = surface frame shifted to the centroid
       double fr[12], sh[12] = {1, 0, 0, 0, 1, 0, 0, 0, 1, H.centroid.x, H.centroid.y, H.centroid.z};
       xf_from_rowmajor34(d->surface_frame + 12 * s, fr);

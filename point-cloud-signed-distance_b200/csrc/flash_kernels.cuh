@@ -36,8 +36,10 @@ constexpr int WARPS = BLOCK / 32;
 // 62.5: one barrier over 24 warps waits too long); barrier every 2nd batch 55.4; dynamic hand-out of the groups
 // with no barrier at all 54.2 (384 x 2), 16128-point tiles 53.5, 768 x 1 52.5 (640 x 1, 96 regs: 53.1; 512 x 1,
 // 120 regs, no spills: 55.4; 256 x 3: 57.0).
+// Round 2, with the closest-feature BSP narrow phase (no GJK code in the loop: 64 registers, no spills, geometry in L1
+// instead of shared memory): 768 x 1 31.2 ms, 384 x 2 30.5, 1024 x 1 28.4, 384 x 3 28.2, 512 x 2 28.1 (K4: 2.94 ms).
 #ifndef FLASH_CBLOCK
-#define FLASH_CBLOCK 768
+#define FLASH_CBLOCK 512
 #endif
 constexpr int CBLOCK = FLASH_CBLOCK;
 // groups of 32 points per barrier interval of the dynamic hand-out (cost_kernel); FLASH_STATIC_GROUPS = the static schedule
@@ -389,7 +391,7 @@ __global__ void __launch_bounds__(GBLOCK, 2) group_kernel(const GroupParams p) {
   }
   __syncthreads();
   const HotModel& H = *Hs;
-  GeoView G; G.f4 = f4s; G.u32 = u32s; G.grid_pool = nullptr;
+  GeoView G; G.f4 = p.geo_f4_n > 0 ? f4s : p.geo_f4; G.u32 = p.geo_u32_n > 0 ? u32s : p.geo_u32; G.grid_pool = nullptr;
   uint4* out = p.rec + (size_t)c * p.rec_stride - g0;
   for (long long g = b0 + tid; g < b1; g += GBLOCK) {
     const float4 gb = __ldg(p.grp + g);
@@ -401,7 +403,7 @@ __global__ void __launch_bounds__(GBLOCK, 2) group_kernel(const GroupParams p) {
 // GRAD: accumulate gradient terms; ARGMIN: write the argmin surface per point; DIST: write the
 // min distance per point (skin_eval entry) and skip all accumulation.
 #ifndef FLASH_MINB
-#define FLASH_MINB 1
+#define FLASH_MINB 2
 #endif
 constexpr size_t COST_STATIC_SMEM = 64;   // static __shared__ of cost_kernel (the group hand-out counter)
 template <bool GRAD, bool ARGMIN, bool DIST>
@@ -427,8 +429,8 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   __syncthreads();
   const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
   GeoView G;
-  G.f4 = reinterpret_cast<const F4*>(smem + L.off_f4);
-  G.u32 = reinterpret_cast<const uint32_t*>(smem + L.off_u32);
+  G.f4 = p.geo_f4_n > 0 ? reinterpret_cast<const F4*>(smem + L.off_f4) : p.geo_f4;
+  G.u32 = p.geo_u32_n > 0 ? reinterpret_cast<const uint32_t*>(smem + L.off_u32) : p.geo_u32;
   G.grid_pool = p.grid_pool;
   const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
   const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
@@ -973,8 +975,8 @@ __global__ void __launch_bounds__(BLOCK, 2) raycast_kernel(const RayParams p) {
   __syncthreads();
   const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
   GeoView G;
-  G.f4 = reinterpret_cast<const F4*>(smem + L.off_f4);
-  G.u32 = reinterpret_cast<const uint32_t*>(smem + L.off_u32);
+  G.f4 = p.geo_f4_n > 0 ? reinterpret_cast<const F4*>(smem + L.off_f4) : p.geo_f4;
+  G.u32 = p.geo_u32_n > 0 ? reinterpret_cast<const uint32_t*>(smem + L.off_u32) : p.geo_u32;
   G.grid_pool = p.grid_pool;
   const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
   const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
@@ -1204,8 +1206,8 @@ __global__ void __launch_bounds__(BLOCK, 2) field_grid_kernel(const GridParams p
   __syncthreads();
   const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
   GeoView G;
-  G.f4 = reinterpret_cast<const F4*>(smem + L.off_f4);
-  G.u32 = reinterpret_cast<const uint32_t*>(smem + L.off_u32);
+  G.f4 = p.geo_f4_n > 0 ? reinterpret_cast<const F4*>(smem + L.off_f4) : p.geo_f4;
+  G.u32 = p.geo_u32_n > 0 ? reinterpret_cast<const uint32_t*>(smem + L.off_u32) : p.geo_u32;
   G.grid_pool = nullptr;
   const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
   const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);

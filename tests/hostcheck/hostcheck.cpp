@@ -233,6 +233,43 @@ void hc_hull_sd(void* p, int j, const float* y, long long n, float* d, float* nr
   }
 }
 
+// the same through the closest-feature BSP tree (flash_bsp.h / hull_sd_bsp); leaf[] receives the leaf words
+int hc_hull_sd_bsp(void* p, int j, const float* y, long long n, float* d, float* nrm, int* leaf) {
+  HC* h = (HC*)p;
+  const ConvexC& C = h->hm.M.cvx[j];
+  if (!C.bsp_on) return 0;
+  GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
+  const HullView V = hull_view(G, C);
+  for (long long i = 0; i < n; ++i) {
+    F3 nn; const F3 yy = f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]);
+    const unsigned k = bsp_locate(V.bn, V.bk, yy);
+    d[i] = bsp_feature_sd(V, k, yy, nn);
+    nrm[3 * i] = nn.x; nrm[3 * i + 1] = nn.y; nrm[3 * i + 2] = nn.z;
+    if (leaf) leaf[i] = (int)k;
+  }
+  return 1;
+}
+// out[5]: nodes, max depth, mean leaf depth, cells, dropped slivers
+void hc_bsp_stats(void* p, int j, double* out) {
+  HC* h = (HC*)p;
+  for (int k = 0; k < 5; ++k) out[k] = j < (int)h->hm.bsp_stats.size() ? h->hm.bsp_stats[j][k] : 0.0;
+}
+// depth of the leaf each query reaches
+void hc_bsp_depth(void* p, int j, const float* y, long long n, int* depth) {
+  HC* h = (HC*)p;
+  const ConvexC& C = h->hm.M.cvx[j];
+  const F4* nodes = h->hm.geo_f4.data() + C.off_bn; const uint32_t* kids = h->hm.geo_u32.data() + C.off_bk;
+  for (long long i = 0; i < n; ++i) {
+    unsigned k = 0u; int dep = 0;
+    do {
+      const F4 q = nodes[k]; const uint32_t w = kids[k];
+      const float s = fmaf(q.x, y[3 * i], fmaf(q.y, y[3 * i + 1], fmaf(q.z, y[3 * i + 2], q.w)));
+      k = s > 0.f ? (w >> 16) : (w & 0xffffu); ++dep;
+    } while (!(k & 0x8000u));
+    depth[i] = dep;
+  }
+}
+
 }  // extern "C"
 
 // GJK warm-started from every possible hint simplex of hull j against the cold start (debugging aid + test)

@@ -20,7 +20,7 @@ c_float_p = C.POINTER(C.c_float)
 
 
 def build():
-    srcs = [os.path.join(HC_DIR, "hostcheck.cpp"), os.path.join(CSRC, "flash_dev.h"), os.path.join(CSRC, "flash_host.h"),
+    srcs = [os.path.join(HC_DIR, "hostcheck.cpp"), os.path.join(CSRC, "flash_dev.h"), os.path.join(CSRC, "flash_host.h"), os.path.join(CSRC, "flash_bsp.h"),
             os.path.join(ROOT, "include", "flashsdf.h")]
     if os.path.exists(LIB) and all(os.path.getmtime(LIB) >= os.path.getmtime(s) for s in srcs):
         return
@@ -44,6 +44,9 @@ def lib():
         L.hc_epilogue.argtypes = [vp, c_double_p, c_double_p, c_double_p, c_double_p, C.c_double, c_double_p, c_double_p]; L.hc_epilogue.restype = None
         L.hc_counters.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_counters.restype = None
         L.hc_hull_sd.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_float_p, c_float_p]; L.hc_hull_sd.restype = None
+        L.hc_hull_sd_bsp.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_float_p, c_float_p, c_int32_p]; L.hc_hull_sd_bsp.restype = C.c_int
+        L.hc_bsp_stats.argtypes = [vp, C.c_int, c_double_p]; L.hc_bsp_stats.restype = None
+        L.hc_bsp_depth.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_int32_p]; L.hc_bsp_depth.restype = None
         L.hc_skin_bound.argtypes = [vp, C.c_int, c_double_p, c_float_p, C.c_longlong, c_float_p, c_float_p, c_double_p]; L.hc_skin_bound.restype = None
         L.hc_support.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_int32_p, c_int32_p, c_float_p, c_float_p]; L.hc_support.restype = None
         L.hc_set_group_cull.argtypes = [C.c_int]; L.hc_set_group_cull.restype = None
@@ -128,6 +131,24 @@ class HostCheck:
         d = np.empty(len(y), np.float32); n = np.empty((len(y), 3), np.float32)
         lib().hc_hull_sd(self.h, j, y.ctypes.data_as(c_float_p), len(y), d.ctypes.data_as(c_float_p), n.ctypes.data_as(c_float_p))
         return d, n
+
+    def hull_sd_bsp(self, j, y):
+        """signed distance through the closest-feature BSP tree; returns d, n, leaf words (None if the hull has no tree)"""
+        y = np.ascontiguousarray(y, np.float32).reshape(-1, 3)
+        d = np.empty(len(y), np.float32); n = np.empty((len(y), 3), np.float32); leaf = np.empty(len(y), np.int32)
+        ok = lib().hc_hull_sd_bsp(self.h, j, y.ctypes.data_as(c_float_p), len(y), d.ctypes.data_as(c_float_p), n.ctypes.data_as(c_float_p), leaf.ctypes.data_as(c_int32_p))
+        return (d, n, leaf) if ok else None
+
+    def bsp_stats(self, j):
+        out = np.zeros(5)
+        lib().hc_bsp_stats(self.h, j, out.ctypes.data_as(c_double_p))
+        return dict(zip(("nodes", "max_depth", "mean_leaf_depth", "cells", "dropped"), out.tolist()))
+
+    def bsp_depth(self, j, y):
+        y = np.ascontiguousarray(y, np.float32).reshape(-1, 3)
+        dep = np.empty(len(y), np.int32)
+        lib().hc_bsp_depth(self.h, j, y.ctypes.data_as(c_float_p), len(y), dep.ctypes.data_as(c_int32_p))
+        return dep
 
 
 def counters(reset=True):
