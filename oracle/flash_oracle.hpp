@@ -169,15 +169,26 @@ inline void build_hull(const std::vector<V3d>& in, Hull& h) {
     std::vector<int> on;
     for (int m = 0; m < n; ++m) if (std::fabs(dot(nn, h.verts[m]) - p[3]) <= 10 * eps + 1e-7 * diam * 1e-2) on.push_back(m);
     if (on.size() < 3) continue;
-    V3d c{0, 0, 0};
-    for (int m : on) c = c + h.verts[m];
-    c = scale(c, 1.0 / on.size());
-    V3d e1 = h.verts[on[0]] - c; e1 = scale(e1, 1.0 / norm(e1));
+    // corners of the face polygon: 2-D convex hull (monotone chain) of the vertices on the plane, so that vertices
+    // inside the face or on its edges (legal input, not corners) cannot spoil the fan
+    V3d e1 = std::fabs(nn.x) < 0.9 ? cross(nn, V3d{1, 0, 0}) : cross(nn, V3d{0, 1, 0});
+    e1 = scale(e1, 1.0 / norm(e1));
     V3d e2 = cross(nn, e1);
-    std::vector<std::pair<double, int>> ang;
-    for (int m : on) { V3d r = h.verts[m] - c; ang.push_back({std::atan2(dot(r, e2), dot(r, e1)), m}); }
-    std::sort(ang.begin(), ang.end());
-    for (size_t t = 1; t + 1 < ang.size(); ++t) h.tris.push_back({ang[0].second, ang[t].second, ang[t + 1].second});
+    std::vector<std::array<double, 3>> q;
+    for (int m : on) q.push_back({dot(h.verts[m], e1), dot(h.verts[m], e2), (double)m});
+    std::sort(q.begin(), q.end());
+    auto turn = [](const std::array<double, 3>& a, const std::array<double, 3>& b, const std::array<double, 3>& c) { return (b[0] - a[0]) * (c[1] - a[1]) - (b[1] - a[1]) * (c[0] - a[0]); };
+    std::vector<std::array<double, 3>> ch;
+    for (int pass = 0; pass < 2; ++pass) {
+      const size_t start = ch.size();
+      for (size_t i = 0; i < q.size(); ++i) {
+        const auto& pt = pass == 0 ? q[i] : q[q.size() - 1 - i];
+        while (ch.size() >= start + 2 && turn(ch[ch.size() - 2], ch[ch.size() - 1], pt) <= 1e-12 * diam * diam) ch.pop_back();
+        ch.push_back(pt);
+      }
+      ch.pop_back();
+    }
+    for (size_t t = 1; t + 1 < ch.size(); ++t) h.tris.push_back({(int)ch[0][2], (int)ch[t][2], (int)ch[t + 1][2]});
   }
 }
 

@@ -23,8 +23,8 @@
 namespace flashdev {
 
 #if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
-struct Counters { long long points, narrow, inside, gjk_iters, plane_tests, vert_tests, lb_tests, skin64, feat_evals, warm; unsigned exact_mask; };   // exact_mask: hulls whose narrow phase ran for the LAST point
-inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0u}; return c; }
+struct Counters { long long points, narrow, lb_tests, skin64, bsp_levels; unsigned exact_mask; };   // exact_mask: hulls whose narrow phase ran for the LAST point
+inline Counters& counters() { static Counters c = {0, 0, 0, 0, 0, 0u}; return c; }
 #define FLASH_COUNT(field, n) (flashdev::counters().field += (n))
 #else
 #define FLASH_COUNT(field, n) ((void)0)
@@ -37,7 +37,6 @@ constexpr int MAX_SKINS = 4;
 constexpr int MAX_SKIN_PTS = 64;           // control points per skin (two_link_arm has 46)
 constexpr int MAX_SKIN_M = MAX_SKIN_PTS + 4;
 constexpr int MAX_HULL_VERTS = 255;        // vertex ids are packed in 8 bits
-constexpr int GJK_MAX_ITER = 24;
 
 enum { JOINT_FIXED = 0, JOINT_REVOLUTE = 1, JOINT_QUAT = 2 };
 enum { SURF_CONVEX = 0, SURF_RIGID_SKIN = 1, SURF_DEFORMABLE_SKIN = 2 };
@@ -56,17 +55,14 @@ struct BodyC {
 // per convex surface; the geometry frame is the surface frame re-centred on the hull centroid
 struct ConvexC {
   int surface, body, nverts, nplanes;
-  int off_planes, off_tris, off_verts, off_vz;  // indices into the geometry blob (units: F4 / u32 / F4 / F4)
-  int nplanes_pad, nverts_pad;               // counts rounded up to a multiple of 8 (padding is inert)
-  int off_voff, off_vlist;                   // support direction map (u32 indices into the blob), see dir_cell()
-  int off_pgrp, pgrp_pad;                    // plane-group hint map (u32 index into the blob; u16 per direction cell), see hull_plane_hint()
+  // closest-feature BSP tree (flash_bsp.h) in the geometry blob: node planes / plane table / vertices / edges (F4
+  // indices), child words (u32 index); node count
+  int off_bn, off_bk, off_bp, off_bv, off_be, n_nodes;
   float lo[3], hi[3];                        // AABB of the vertices, geometry frame
   float depth_bound, r_in;                   // >= max penetration depth; <= inradius about the geometry origin
   double frame[12];                          // geometry frame -> body frame
   // grid mode (body-frame SDF grid): origin, spacing, dims, offset into the grid pool (floats)
   float g_org[3]; float g_inv_h; int g_dim[3]; int g_on; long long g_off;
-  // closest-feature BSP tree (flash_bsp.h): node planes / plain plane table / vertices / edges (F4 indices), child words (u32 index)
-  int bsp_on, off_bn, off_bk, off_bp, off_bv, off_be;
 };
 
 struct SkinC {
@@ -317,376 +313,50 @@ FLASH_HD void skin_solve(const ModelC& M, const SkinC& K, const double* LU, cons
 }
 
 // ------------------------------------------------------------------ convex signed distance (row A8)
-// Closest point to the ORIGIN on segment / triangle given in coordinates relative to the query
-// point (Ericson, Real-Time Collision Detection 5.1.2 / 5.1.5), with barycentric weights whose
-// exact zeros identify the supporting sub-simplex.
-FLASH_HD F3 seg_closest0(F3 a, F3 b, float& wa, float& wb) {
-  F3 ab = b - a;
-  float den = dot(ab, ab);
-  float t = den > 0.f ? -dot(a, ab) / den : 0.f;
-  if (t <= 0.f) { wa = 1.f; wb = 0.f; return a; }
-  if (t >= 1.f) { wa = 0.f; wb = 1.f; return b; }
-  wa = 1.f - t; wb = t;
-  return a + ab * t;
-}
-// cold path of tri_closest0 (collinear triangle: best of the three edges), kept out of line so that the five
-// inlined copies of the triangle solver do not each carry three segment solvers (instruction-cache footprint)
-#if defined(FLASH_COLD_NOINLINE)
-FLASH_HDN
-#else
-FLASH_HD
-#endif
-F3 tri_degenerate0(F3 a, F3 b, F3 c, float& wa, float& wb, float& wc) {
-  float u0, u1, v0, v1, w0, w1;
-  F3 q0 = seg_closest0(a, b, u0, u1), q1 = seg_closest0(a, c, v0, v1), q2 = seg_closest0(b, c, w0, w1);
-  float e0 = dot(q0, q0), e1 = dot(q1, q1), e2 = dot(q2, q2);
-  if (e0 <= e1 && e0 <= e2) { wa = u0; wb = u1; wc = 0.f; return q0; }
-  if (e1 <= e2) { wa = v0; wb = 0.f; wc = v1; return q1; }
-  wa = 0.f; wb = w0; wc = w1; return q2;
-}
-FLASH_HD F3 tri_closest0(F3 a, F3 b, F3 c, float& wa, float& wb, float& wc) {
-  F3 ab = b - a, ac = c - a;
-  float d1 = -dot(ab, a), d2 = -dot(ac, a);
-  if (d1 <= 0.f && d2 <= 0.f) { wa = 1.f; wb = 0.f; wc = 0.f; return a; }
-  float d3 = -dot(ab, b), d4 = -dot(ac, b);
-  if (d3 >= 0.f && d4 <= d3) { wa = 0.f; wb = 1.f; wc = 0.f; return b; }
-  float vc = d1 * d4 - d3 * d2;
-  if (vc <= 0.f && d1 >= 0.f && d3 <= 0.f) { float v = d1 / (d1 - d3); wa = 1.f - v; wb = v; wc = 0.f; return a + ab * v; }
-  float d5 = -dot(ab, c), d6 = -dot(ac, c);
-  if (d6 >= 0.f && d5 <= d6) { wa = 0.f; wb = 0.f; wc = 1.f; return c; }
-  float vb = d5 * d2 - d1 * d6;
-  if (vb <= 0.f && d2 >= 0.f && d6 <= 0.f) { float w = d2 / (d2 - d6); wa = 1.f - w; wb = 0.f; wc = w; return a + ac * w; }
-  float va = d3 * d6 - d5 * d4;
-  if (va <= 0.f && (d4 - d3) >= 0.f && (d5 - d6) >= 0.f) { float w = (d4 - d3) / ((d4 - d3) + (d5 - d6)); wa = 0.f; wb = 1.f - w; wc = w; return b + (c - b) * w; }
-  float den = va + vb + vc;
-  if (!(den > 0.f)) return tri_degenerate0(a, b, c, wa, wb, wc);   // degenerate (collinear) triangle: best of the three edges
-  float inv = 1.f / den;
-  float v = vb * inv, w = vc * inv;
-  wa = 1.f - v - w; wb = v; wc = w;
-  return a + ab * v + ac * w;
-}
-
-// GJK working simplex: up to three hull vertices (coordinates relative to the query point).
-struct Simplex { F3 a, b, c; int ia, ib, ic, ns; };
-FLASH_HD void simplex_push(Simplex& S, F3 p, int j) {
-  if (S.ns == 0) { S.a = p; S.ia = j; } else if (S.ns == 1) { S.b = p; S.ib = j; } else { S.c = p; S.ic = j; }
-  ++S.ns;
-}
-// keep the vertices with non-zero barycentric weight (at least one)
-FLASH_HD void simplex_from(Simplex& S, F3 p0, int j0, float u0, F3 p1, int j1, float u1, F3 p2, int j2, float u2) {
-  S.ns = 0;
-  if (u0 > 0.f) simplex_push(S, p0, j0);
-  if (u1 > 0.f) simplex_push(S, p1, j1);
-  if (u2 > 0.f) simplex_push(S, p2, j2);
-  if (S.ns == 0) simplex_push(S, p2, j2);
-}
-
-// ---- support direction map (per hull): a cube map of DIRMAP_R x DIRMAP_R cells per face over directions d.
-//   voff/vlist  (u16 offsets / u8 lists)  EVERY vertex that is the support vertex for SOME direction of
-//                      the cell (host: normal-cone / cell clipping with margins) -- the support query over
-//                      the list (2-3 vertices on the IRB140 hulls) is exact and replaces the 56-vertex scan.
-// (A face table of the same shape that replaced the 100-plane scan by one plane test was measured and
-//  dropped: the most-violated plane is a much better GJK start -- 1.0 vs 1.3 iterations per point, and the
-//  iterations, not the scan, are what costs)
-constexpr int DIRMAP_R = 8;
-constexpr int DIRMAP_CELLS = 6 * DIRMAP_R * DIRMAP_R;
-FLASH_HD int dir_cell(F3 d) {
-  // branch-free: major axis by selects, one (approximate on the device: 2 ulp, far inside the margin the
-  // host grows every cell by) reciprocal, clamps in floating point
-  const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
-  const bool X = ax >= ay && ax >= az, Y = !X && ay >= az;
-  const float m = X ? d.x : (Y ? d.y : d.z), u = X ? d.y : (Y ? d.z : d.x), v = X ? d.z : (Y ? d.x : d.y);
-  const int face = (X ? 0 : (Y ? 2 : 4)) + (m < 0.f ? 1 : 0);
-#ifdef __CUDA_ARCH__
-  const float inv = __fdividef(0.5f * DIRMAP_R, fmaxf(fabsf(m), 1e-30f));
-#else
-  const float inv = (0.5f * DIRMAP_R) / fmaxf(fabsf(m), 1e-30f);
-#endif
-  // (u/|m| + 1) R/2 in [0, R] -> cell
-  const float fu = fminf(fmaxf(fmaf(u, inv, 0.5f * DIRMAP_R), 0.f), DIRMAP_R - 0.5f);
-  const float fv = fminf(fmaxf(fmaf(v, inv, 0.5f * DIRMAP_R), 0.f), DIRMAP_R - 0.5f);
-  return (face * DIRMAP_R + (int)fv) * DIRMAP_R + (int)fu;
-}
-
-// ---- geometry blob layout (per hull), chosen so that the scans run on packed fp32 FMAs (FFMA2, sm_100):
-//   planes, pair k = planes 2k, 2k+1:  F4 {nx0, nx1, ny0, ny1}, F4 {nz0, nz1, -o0, -o1}
-//   vertices, pair k:                  F4 {x0, x1, y0, y1} (VA) and float2 {z0, z1} (VZ, a flat float array)
-// counts are padded to a multiple of 8; padding planes can never be the maximum, padding vertices are
-// copies of vertex 0 (never a strictly better support).
-struct HullView { const F4* planes; const uint32_t* ptri; const F4* va; const float* vz; int np, nv;
-                  const unsigned short* voff; const unsigned char* vlist; const unsigned short* pgrp;
-                  const F4* bn; const uint32_t* bk; const F4* bp; const F4* bv; const F4* be; int bsp_on; };
-FLASH_HD F3 plane_normal(const F4* P, int f) { const float* a = reinterpret_cast<const float*>(P + (f & ~1)); const int h = f & 1; return f3(a[h], a[2 + h], a[4 + h]); }
-FLASH_HD F3 vert_at(const HullView& V, int j) { const float* a = reinterpret_cast<const float*>(V.va + (j >> 1)); const int h = j & 1; return f3(a[h], a[2 + h], V.vz[j]); }
-
-// eight plane distances n.y - o / eight support values q.v; the device versions issue one FFMA2 per
-// two lanes of work, the host versions are the same fused multiply-adds one at a time (bit-identical).
-#ifdef __CUDA_ARCH__
-__device__ __forceinline__ unsigned long long pk2(float lo, float hi) { unsigned long long r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
-__device__ __forceinline__ void upk2(unsigned long long v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
-  unsigned long long r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r;
-}
-__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) {
-  unsigned long long r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r;
-}
-#endif
-FLASH_HD void planes8(const F4* __restrict__ P, F3 y, float sv[8]) {
-#if defined(__CUDA_ARCH__) && !defined(FLASH_NO_FFMA2)
-  const unsigned long long yx = pk2(y.x, y.x), yy = pk2(y.y, y.y), yz = pk2(y.z, y.z);
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const F4 a = P[2 * k], b = P[2 * k + 1];
-    unsigned long long r = fma2(pk2(b.x, b.y), yz, pk2(b.z, b.w));
-    r = fma2(pk2(a.z, a.w), yy, r);
-    r = fma2(pk2(a.x, a.y), yx, r);
-    upk2(r, sv[2 * k], sv[2 * k + 1]);
-  }
-#else
-  for (int k = 0; k < 4; ++k) {
-    const F4 a = P[2 * k], b = P[2 * k + 1];
-    sv[2 * k] = fmaf(a.x, y.x, fmaf(a.z, y.y, fmaf(b.x, y.z, b.z)));
-    sv[2 * k + 1] = fmaf(a.y, y.x, fmaf(a.w, y.y, fmaf(b.y, y.z, b.w)));
-  }
-#endif
-}
-FLASH_HD void verts8(const F4* __restrict__ VA, const float* __restrict__ VZ, F3 q, float sv[8]) {
-#if defined(__CUDA_ARCH__) && !defined(FLASH_NO_FFMA2)
-  const unsigned long long qx = pk2(q.x, q.x), qy = pk2(q.y, q.y), qz = pk2(q.z, q.z);
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const F4 a = VA[k];
-    const float2 z = *reinterpret_cast<const float2*>(VZ + 2 * k);
-    unsigned long long r = mul2(pk2(z.x, z.y), qz);
-    r = fma2(pk2(a.z, a.w), qy, r);
-    r = fma2(pk2(a.x, a.y), qx, r);
-    upk2(r, sv[2 * k], sv[2 * k + 1]);
-  }
-#else
-  for (int k = 0; k < 4; ++k) {
-    const F4 a = VA[k];
-    sv[2 * k] = fmaf(q.x, a.x, fmaf(q.y, a.z, q.z * VZ[2 * k]));
-    sv[2 * k + 1] = fmaf(q.x, a.y, fmaf(q.y, a.w, q.z * VZ[2 * k + 1]));
-  }
-#endif
-}
-
-// Signed distance from y (geometry frame) to the convex hull given by its supporting planes and
-// vertices.  Inside (all plane distances <= 0): the largest plane distance, normal = that plane's.
-// Outside: exact Euclidean distance by GJK on the vertex set, started from a triangle of the
-// most-violated face (EnhancedGJK `gjk!` is the reference algorithm, src/Flash.jl:238-243; its
-// inside value is iteration-path dependent and replaced by the exact depth -- DESIGN.md).
-// nrm receives grad_y(distance).
+// Signed distance from y (geometry frame) to a convex hull through its closest-feature BSP tree (flash_bsp.h):
+// one plane test per level locates the cell of y, whose feature -- a face, an edge or a vertex -- gives the distance
+// and its gradient in closed form.  Inside the hull the cell's face is the plane of largest (least negative)
+// distance: the exact depth.  (EnhancedGJK `gjk!` is the reference algorithm, src/Flash.jl:238-243; outside it
+// converges to the same number, inside its value is iteration-path dependent -- DESIGN.md 2.)
+// Every lane of a warp runs the same ~11 instructions per level whatever its path; round 1's per-point GJK (plane
+// hint, start triangle, support queries, simplex updates) was 45 % of cost_kernel's instructions at 17-23 of 32
+// active lanes.
 //
-// The function is split into the two scans (plane maximum, support vertex) and the per-point pieces
-// between them, because the main kernel runs the scans warp-cooperatively (lanes = planes / vertices,
-// flash_kernels.cuh hull_sd_warp) around the SAME per-point pieces; this serial composition is what
-// the ray marcher, skin_eval, grid baking and the host replay use.
+// Per hull in the geometry blob: node planes F4 {n, -o} + child words u32 (lo | hi << 16; s = n.y - o > 0 -> hi);
+// a child with bit 15 set is a leaf: 0x8000 | kind << 13 | index, kind 0 = face (index into the plane table
+// F4 {n, -o}), 1 = vertex (vertex table F4 {x, y, z, 0}), 2 = edge (edge table F4 {unit direction, bits(first vertex)}).
+struct HullView { const F4* bn; const uint32_t* bk; const F4* bp; const F4* bv; const F4* be; };
 
-// [region: plane scan] largest plane distance D and the lowest plane index attaining it.  Returns false
-// (and leaves fs undefined) as soon as D exceeds `cutoff`: D is a lower bound of the distance.
-FLASH_HD bool hull_plane_scan(const HullView& V, F3 y, float cutoff, float& D_out, int& fs_out) {
-  const F4* __restrict__ planes = V.planes;
-  float D = -3.0e38f; int fg = 0;
-  int f = 0;
-  for (; f < V.np; f += 8) {
-    float sv[8];
-    planes8(planes + f, y, sv);
-    const float m = fmaxf(fmaxf(fmaxf(sv[0], sv[1]), fmaxf(sv[2], sv[3])), fmaxf(fmaxf(sv[4], sv[5]), fmaxf(sv[6], sv[7])));
-    fg = m > D ? f : fg;
-    D = fmaxf(D, m);
-    if (D > cutoff) { D_out = D; return false; }
-  }
-  float sv[8];                // index inside the winning group: recomputed once instead of tracked per group
-  planes8(planes + fg, y, sv);
-  int k = 7;
-#pragma unroll
-  for (int t = 6; t >= 0; --t) k = (sv[t] == D) ? t : k;
-  D_out = D; fs_out = fg + k;
-  return true;
-}
-// [region: plane hint] The host clusters the planes into groups of 8 by normal direction and records,
-// per direction cell of y (geometry origin = hull centroid), the two groups that hold the most-violated
-// plane for (nearly) every OUTSIDE point of that cell (flash_host.h build_plane_hints: upper envelopes of
-// the plane distances along sampled rays).  The map is a HINT, never trusted for the result:
-//   * any plane with n.y - o > 0 proves y outside, and its distance is a lower bound of the true one
-//     (valid for the cutoff test and as the "certified face" shortcut of hull_gjk_start);
-//   * the distance itself comes from GJK, which terminates on its own exact criterion whatever face it
-//     started from (a missed most-violated plane costs an extra iteration, not accuracy);
-//   * if no hinted plane is violated the point is inside or the hint failed: the full scan decides.
-// Returns 0: D > cutoff (cannot be the minimum), 1: outside with (D, fs), 2: undecided.
-FLASH_HD float max8(const float sv[8]) { return fmaxf(fmaxf(fmaxf(sv[0], sv[1]), fmaxf(sv[2], sv[3])), fmaxf(fmaxf(sv[4], sv[5]), fmaxf(sv[6], sv[7]))); }
-FLASH_HD int hull_plane_hint(const HullView& V, F3 y, float cutoff, float& D_out, int& fs_out) {
-  const unsigned gg = V.pgrp[dir_cell(y)];
-  const int g0 = (int)(gg & 255u) * 8, g1 = (int)(gg >> 8) * 8;
-  float sv[8];
-  planes8(V.planes + g0, y, sv);
-  float D = max8(sv);
-  int gw = g0;
-  if (D > cutoff) { D_out = D; return 0; }        // most rejections need the first group only
-  if (g1 != g0) {
-    planes8(V.planes + g1, y, sv);
-    const float m = max8(sv);
-    gw = m > D ? g1 : g0;
-    D = fmaxf(D, m);
-    if (D > cutoff) { D_out = D; return 0; }
-  }
-  D_out = D;
-  if (!(D > 0.f)) return 2;
-  planes8(V.planes + gw, y, sv);                   // index inside the winning group: recomputed for the accepted points only
-  int k = 7;
-#pragma unroll
-  for (int t = 6; t >= 0; --t) k = (sv[t] == D) ? t : k;
-  fs_out = gw + k;
-  return 1;
-}
-// [region: support scan] lowest vertex index minimising q.v
-FLASH_HD int hull_support_scan(const HullView& V, F3 q) {
-  float best = 3.0e38f; int vg = 0;
-  for (int v = 0; v < V.nv; v += 8) {   // groups of 8 (padded with copies of vertex 0)
-    float sv[8];
-    verts8(V.va + (v >> 1), V.vz + v, q, sv);
-    const float m = fminf(fminf(fminf(sv[0], sv[1]), fminf(sv[2], sv[3])), fminf(fminf(sv[4], sv[5]), fminf(sv[6], sv[7])));
-    vg = m < best ? v : vg;
-    best = fminf(best, m);
-  }
-  float sv[8];
-  verts8(V.va + (vg >> 1), V.vz + vg, q, sv);
-  int k = 7;
-#pragma unroll
-  for (int t = 6; t >= 0; --t) k = (sv[t] == best) ? t : k;
-  return vg + k;
-}
-// [region: support map] exact support vertex (lowest index minimising q.v) from the direction map: only
-// the vertices whose normal cone meets the cell of -q can be the support (host: build_dirmaps)
-FLASH_HD int hull_support_map(const HullView& V, F3 q) {
-  const int cell = dir_cell(f3(-q.x, -q.y, -q.z));
-  const int b = V.voff[cell], e = V.voff[cell + 1];
-  float best = 3.0e38f; int iw = 0;
-  for (int t = b; t < e; ++t) {       // lists are in increasing vertex order: strict < keeps the lowest index on ties
-    const int j = V.vlist[t];
-    const F3 p = vert_at(V, j);
-    const float sv = fmaf(q.x, p.x, fmaf(q.y, p.y, q.z * p.z));
-    if (sv < best) { best = sv; iw = j; }
-  }
-  return iw;
-}
-// [region: start triangle] closest point of face fs's triangle; true = it is interior to the triangle,
-// i.e. the orthogonal projection of y onto the supporting plane, which lies on the hull: it IS the
-// closest point (no tolerance involved) and no support scan is needed to certify it.
-FLASH_HD bool hull_gjk_start(const HullView& V, F3 y, int fs, Simplex& S, F3& q) {
-  const uint32_t t = V.ptri[fs];
-  const int j0 = t & 255, j1 = (t >> 8) & 255, j2 = (t >> 16) & 255;
-  F3 p0 = vert_at(V, j0) - y, p1 = vert_at(V, j1) - y, p2 = vert_at(V, j2) - y;
-  float u0, u1, u2;
-  q = tri_closest0(p0, p1, p2, u0, u1, u2);
-  simplex_from(S, p0, j0, u0, p1, j1, u1, p2, j2, u2);
-  return S.ns == 3;
-}
-// [region: simplex update] one GJK step after the support scan returned vertex iw for direction q.
-// Returns false when q is already the closest point (iw supports the simplex / no descent left).
-FLASH_HD bool hull_gjk_update(const HullView& V, F3 y, int iw, Simplex& S, F3& q) {
-  if (iw == S.ia || (S.ns > 1 && iw == S.ib) || (S.ns > 2 && iw == S.ic)) return false;  // already supporting
-  const float dd = dot(q, q);
-  F3 w = vert_at(V, iw) - y;
-  if (dd - dot(q, w) <= 1e-7f * dd) return false;                                          // no descent left
-  float u0, u1, u2;
-  if (S.ns == 1) {
-    q = seg_closest0(S.a, w, u0, u1);
-    simplex_from(S, S.a, S.ia, u0, w, iw, u1, w, iw, 0.f);
-  } else if (S.ns == 2) {
-    q = tri_closest0(S.a, S.b, w, u0, u1, u2);
-    simplex_from(S, S.a, S.ia, u0, S.b, S.ib, u1, w, iw, u2);
-  } else {
-    // tetrahedron (a,b,c,w): y is outside the hull, so the closest point lies on one of the
-    // three faces that contain the new vertex.  (A rolled loop over the faces -- one copy of the triangle
-    // solver instead of four, 5088 instead of 6072 instructions -- was measured 10% SLOWER: the dynamic
-    // indexing of the simplex spills.)
-    float x0, x1, x2, y0, y1, y2, z0, z1, z2;
-    F3 q0 = tri_closest0(S.a, S.b, w, x0, x1, x2);
-    F3 q1 = tri_closest0(S.a, S.c, w, y0, y1, y2);
-    F3 q2 = tri_closest0(S.b, S.c, w, z0, z1, z2);
-    float e0 = dot(q0, q0), e1 = dot(q1, q1), e2 = dot(q2, q2);
-    Simplex T = S;
-    if (e0 <= e1 && e0 <= e2) { q = q0; simplex_from(S, T.a, T.ia, x0, T.b, T.ib, x1, w, iw, x2); }
-    else if (e1 <= e2) { q = q1; simplex_from(S, T.a, T.ia, y0, T.c, T.ic, y1, w, iw, y2); }
-    else { q = q2; simplex_from(S, T.b, T.ib, z0, T.c, T.ic, z1, w, iw, z2); }
-  }
-  return true;
-}
-// distance and its gradient from the converged q (closest point - y)
-FLASH_HD float hull_gjk_finish(const HullView& V, F3 q, float D, int fs, F3& nrm) {
-  const float dd = dot(q, q);
-  if (!(dd > 0.f)) { nrm = plane_normal(V.planes, fs); return D; }   // numerically on the surface
+// descend from `start` (a node index, or already a leaf word) to the leaf of y
+FLASH_HD unsigned bsp_locate(const HullView& V, unsigned start, F3 y) {
+  unsigned k = start;
+  while (!(k & 0x8000u)) {
+    FLASH_COUNT(bsp_levels, 1);
 #ifdef __CUDA_ARCH__
-  float inv = rsqrtf(dd);
-  inv = inv * (1.5f - 0.5f * dd * inv * inv);   // one Newton step: ~1 ulp
-#else
-  float inv = 1.0f / sqrtf(dd);
-#endif
-  nrm = q * (-inv);
-  return dd * inv;
-}
-
-// kind_out (may be null): 0 = rejected by the cutoff, 1 = inside (fs = the plane of largest distance), 2 = outside with
-// the closest point interior to the start triangle of plane fs, 3 = outside with GJK's terminal simplex in S_out.
-FLASH_HD float hull_sd_ex(const HullView& V, F3 y, float cutoff, F3& nrm, int* kind_out, int* fs_out, Simplex* S_out) {
-  float D = 0.f; int fs = 0;
-  if (kind_out) *kind_out = 0;
-#ifndef FLASH_NO_PLANEHINT
-  const int hint = hull_plane_hint(V, y, cutoff, D, fs);
-  FLASH_COUNT(plane_tests, 16);
-  if (hint == 0) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }
-  if (hint == 2) {
-    FLASH_COUNT(plane_tests, V.np);
-    if (!hull_plane_scan(V, y, cutoff, D, fs)) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }
-  }
-#else
-  if (!hull_plane_scan(V, y, cutoff, D, fs)) { nrm = f3(0.f, 0.f, 0.f); return 3.0e38f; }   // cannot be the minimum: never a candidate value
-  FLASH_COUNT(plane_tests, V.np);
-#endif
-  FLASH_COUNT(narrow, 1);
-  if (fs_out) *fs_out = fs;
-  if (D <= 0.f) { FLASH_COUNT(inside, 1); if (kind_out) *kind_out = 1; nrm = plane_normal(V.planes, fs); return D; }
-  Simplex S;
-  F3 q;
-  const bool certified = hull_gjk_start(V, y, fs, S, q);
-  for (int it = 0; it < GJK_MAX_ITER && !certified; ++it) {
-    if (!(dot(q, q) > 0.f)) break;
-    // support vertex towards the query point: minimise q.(v - y)  <=>  minimise q.v
-    FLASH_COUNT(gjk_iters, 1);
-#ifndef FLASH_NO_DIRMAP
-    const int iw = hull_support_map(V, q);
-#else
-    FLASH_COUNT(vert_tests, V.nv);
-    const int iw = hull_support_scan(V, q);
-#endif
-    if (!hull_gjk_update(V, y, iw, S, q)) break;
-  }
-  if (kind_out) *kind_out = certified ? 2 : 3;
-  if (S_out) *S_out = S;
-  return hull_gjk_finish(V, q, D, fs, nrm);
-}
-FLASH_HD float hull_sd(const HullView& V, F3 y, float cutoff, F3& nrm) { return hull_sd_ex(V, y, cutoff, nrm, nullptr, nullptr, nullptr); }
-
-// ---- closest-feature BSP (flash_bsp.h): one plane test per level locates the cell of y, whose feature gives the
-// signed distance and its gradient in closed form.  Leaf word: 0x8000 | kind << 13 | index, kind 0 = face (plane
-// index), 1 = vertex, 2 = edge (edge table: unit direction + first vertex).  Lane-uniform: every lane runs the same
-// ~9 instructions per level, whatever its path.
-FLASH_HD unsigned bsp_locate(const F4* __restrict__ nodes, const uint32_t* __restrict__ kids, F3 y) {
-  unsigned k = 0u;
-  do {
-#ifdef __CUDA_ARCH__
-    const float4 pp = __ldg(reinterpret_cast<const float4*>(nodes) + k);
+    const float4 pp = __ldg(reinterpret_cast<const float4*>(V.bn) + k);
     F4 p; p.x = pp.x; p.y = pp.y; p.z = pp.z; p.w = pp.w;
-    const uint32_t w = __ldg(kids + k);
+    const uint32_t w = __ldg(V.bk + k);
 #else
-    const F4 p = nodes[k];
-    const uint32_t w = kids[k];
+    const F4 p = V.bn[k];
+    const uint32_t w = V.bk[k];
 #endif
     const float s = fmaf(p.x, y.x, fmaf(p.y, y.y, fmaf(p.z, y.z, p.w)));
     k = s > 0.f ? (w >> 16) : (w & 0xffffu);
-  } while (!(k & 0x8000u));
+  }
+  return k;
+}
+// Descend with a whole ball B(yc, r): as long as the ball lies on one side of the node's plane every point of it
+// takes the same child.  Returns the first node the ball straddles (or the leaf that contains it): the start word
+// from which the points of the ball finish their own descent (cost_kernel's group records).  A point within
+// rounding distance of a plane may end up on either side: the distance is continuous across every cell boundary.
+FLASH_HD unsigned bsp_descend_ball(const HullView& V, F3 yc, float r) {
+  unsigned k = 0u;
+  while (!(k & 0x8000u)) {
+    const F4 p = V.bn[k];
+    const uint32_t w = V.bk[k];
+    const float s = fmaf(p.x, yc.x, fmaf(p.y, yc.y, fmaf(p.z, yc.z, p.w)));
+    if (s > r) k = w >> 16; else if (s < -r) k = w & 0xffffu; else break;
+  }
   return k;
 }
 FLASH_HD float bsp_feature_sd(const HullView& V, unsigned leaf, F3 y, F3& nrm) {
@@ -722,135 +392,9 @@ FLASH_HD float bsp_feature_sd(const HullView& V, unsigned leaf, F3 y, F3& nrm) {
   nrm = r * inv;
   return dd * inv;
 }
-FLASH_HD float hull_sd_bsp(const HullView& V, F3 y, F3& nrm) { return bsp_feature_sd(V, bsp_locate(V.bn, V.bk, y), y, nrm); }
-
-// ---- group feature certification ---------------------------------------------------------------------------------
-// The 32 points one warp evaluates together are Morton neighbours inside a ball B(c, rho) (points_groups_kernel).
-// If the whole ball lies in the Voronoi region of ONE feature of the hull -- a face, an edge or a vertex -- every
-// point's distance is a closed form of that feature and the per-point narrow phase (plane hint, start triangle,
-// GJK iterations, support queries) is not needed at all.  The cost kernel's group pre-pass (one thread per group)
-// runs the narrow phase once at the ball centre, takes the closest feature from it and certifies it for the ball
-// by the projection theorem -- x* in H is the closest point of x iff (x - x*).(z - x*) <= 0 for every z in H -- whose
-// conditions are LINEAR in x for a fixed feature, so their maximum over a ball is the value at the centre plus rho
-// times a norm:
-//   vertex v        (x - v).(v_k - v) <= 0 for every hull vertex k
-//   edge (a, b)     0 <= (x - a).e <= |b - a| (e the unit direction), and (x - a).w_k <= 0 with w_k the part of
-//                   v_k - a orthogonal to e
-//   face f          the projection x' of x onto the plane of f lies in H: n_g.x' - o_g <= 0 for every plane g (points
-//                   outside), and f is the plane of largest distance: n_f.x - o_f >= n_g.x - o_g (points inside)
-// A feature is a u32: type (bits 0-1: 0 none, 1 vertex, 2 edge, 3 face) | FEAT_CERT | ia << 8 | ib << 16 (vertices) or
-// plane slot << 8 (face).  All tests carry an absolute slack for the fp32 centre transform; a point that is outside
-// its certified region by a rounding error delta gets a distance that is wrong by O(delta^2 / d) only.
-// Without FEAT_CERT the word is a HINT: the vertices (ia, ib, ic in bits 8-31, type = their number) of the simplex GJK
-// ended on at the ball centre.  The points of the group start their own GJK from it (hull_sd_warm): no plane hint, no
-// start triangle, and -- GJK's termination test being independent of the start -- the same exact distance.
-enum { FEAT_NONE = 0, FEAT_VERTEX = 1, FEAT_EDGE = 2, FEAT_FACE = 3, FEAT_CERT = 4 };
-FLASH_HD unsigned feat_hint(const Simplex& S) {
-  return (unsigned)S.ns | ((unsigned)S.ia << 8) | ((unsigned)(S.ns > 1 ? S.ib : 0) << 16) | ((unsigned)(S.ns > 2 ? S.ic : 0) << 24);
-}
-FLASH_HD unsigned hull_ball_feature(const HullView& V, F3 yc, float rho, float& d_centre) {
-  F3 n; int kind = 0, fs = 0; Simplex S;
-  S.ns = 0; S.ia = S.ib = S.ic = 0; S.a = S.b = S.c = f3(0.f, 0.f, 0.f);
-  const float D = hull_sd_ex(V, yc, 3.0e38f, n, &kind, &fs, &S);
-  d_centre = D;
-  const float r = rho * (1.f + 1e-5f) + 1e-5f;   // ball radius + slack for the fp32 transform of the centre
-  // (a hint is only safe when the whole ball is outside the hull: GJK on the vertices cannot see penetration)
-  const unsigned hint = (kind == 2 || kind == 3) && S.ns >= 1 && S.ns <= 3 && D - r > 0.f ? feat_hint(S) : (unsigned)FEAT_NONE;
-  if (kind == 3 && S.ns == 3) {
-    // GJK ended in the interior of a triangle of hull vertices: it lies on a supporting plane, i.e. on the face
-    // whose plane is the farthest one from yc (every plane distance is a lower bound of the true distance)
-    float Dp; int fp;
-    if (!hull_plane_scan(V, yc, 3.0e38f, Dp, fp)) return hint;
-    fs = fp; kind = 2;
-  }
-  if (kind == 1 || kind == 2) {
-    // face fs
-    const F3 nf = plane_normal(V.planes, fs);
-    if (!(dot(nf, nf) > 0.5f)) return hint;
-    const float* pf = reinterpret_cast<const float*>(V.planes + (fs & ~1));
-    const float df = fmaf(nf.x, yc.x, fmaf(nf.y, yc.y, fmaf(nf.z, yc.z, pf[6 + (fs & 1)])));   // n_f.yc - o_f
-    const bool dips_inside = df - r < 0.f, pokes_outside = df + r > 0.f;
-    for (int g = 0; g < V.np; ++g) {
-      if (g == fs) continue;
-      const float* pg = reinterpret_cast<const float*>(V.planes + (g & ~1)); const int h = g & 1;
-      const F3 ng = f3(pg[h], pg[2 + h], pg[4 + h]);
-      const float dg = fmaf(ng.x, yc.x, fmaf(ng.y, yc.y, fmaf(ng.z, yc.z, pg[6 + h])));
-      const float c = dot(ng, nf);
-      // outside points: projection onto plane f stays inside plane g
-      if (pokes_outside && !(dg - df * c + r * sqrtf(fmaxf(1.f - c * c, 0.f) + 1e-6f) <= 0.f)) return hint;
-      // inside points: plane f has the largest distance
-      if (dips_inside && !(df - dg - r * sqrtf(fmaxf(2.f - 2.f * c, 0.f) + 1e-6f) >= 0.f)) return hint;
-    }
-    return FEAT_FACE | FEAT_CERT | ((unsigned)fs << 8);
-  }
-  // Vertex and edge regions are NOT certified: with the warm start their points cost one closest-point update and
-  // one support query, and the certificate (a pass over all vertices, or adjacency tables) costs the group kernel
-  // more than the closed form saves (measured: K5 group_kernel 4.7 ms with the certificates, 24 % of the groups
-  // certified).  Faces are: a patch of depth points lying ON a face straddles the surface, where GJK cannot start.
-  return hint;
-}
-// GJK started from the group's hint simplex.  Returns false when the point turns out to be on / inside the hull
-// (q = 0): the caller takes the regular path, whose plane scan gives the depth.
-FLASH_HD bool hull_sd_warm(const HullView& V, unsigned feat, F3 y, float& d, F3& nrm) {
-  const int ns = (int)(feat & 3u);
-  const int ia = (int)((feat >> 8) & 255u), ib = (int)((feat >> 16) & 255u), ic = (int)(feat >> 24);
-  Simplex S; F3 q;
-  const F3 pa = vert_at(V, ia) - y;
-  S.ns = 1; S.a = pa; S.ia = ia; S.b = pa; S.ib = ia; S.c = pa; S.ic = ia;
-  q = pa;
-  if (ns == 2) {
-    const F3 pb = vert_at(V, ib) - y;
-    float u0, u1;
-    q = seg_closest0(pa, pb, u0, u1);
-    simplex_from(S, pa, ia, u0, pb, ib, u1, pb, ib, 0.f);
-  } else if (ns == 3) {
-    const F3 pb = vert_at(V, ib) - y, pc = vert_at(V, ic) - y;
-    float u0, u1, u2;
-    q = tri_closest0(pa, pb, pc, u0, u1, u2);
-    simplex_from(S, pa, ia, u0, pb, ib, u1, pc, ic, u2);
-  }
-  FLASH_COUNT(warm, 1);
-  for (int it = 0; it < GJK_MAX_ITER; ++it) {
-    if (!(dot(q, q) > 0.f)) return false;
-    FLASH_COUNT(gjk_iters, 1);
-    const int iw = hull_support_map(V, q);
-    if (!hull_gjk_update(V, y, iw, S, q)) break;
-  }
-  const float dd = dot(q, q);
-  if (!(dd > 0.f)) return false;
-#ifdef __CUDA_ARCH__
-  float inv = rsqrtf(dd);
-  inv = inv * (1.5f - 0.5f * dd * inv * inv);
-#else
-  const float inv = 1.0f / sqrtf(dd);
-#endif
-  nrm = q * (-inv);
-  d = dd * inv;
-  return true;
-}
-// distance and gradient of y to a certified feature
-FLASH_HD float hull_feature_eval(const HullView& V, unsigned feat, F3 y, F3& nrm) {
-  const unsigned type = feat & 3u;
-  if (type == FEAT_FACE) {
-    const int fs = (int)(feat >> 8);
-    const float* pf = reinterpret_cast<const float*>(V.planes + (fs & ~1)); const int h = fs & 1;
-    nrm = f3(pf[h], pf[2 + h], pf[4 + h]);
-    return fmaf(nrm.x, y.x, fmaf(nrm.y, y.y, fmaf(nrm.z, y.z, pf[6 + h])));
-  }
-  F3 u = y - vert_at(V, (int)((feat >> 8) & 255u));
-  if (type == FEAT_EDGE) {
-    const F3 e = vert_at(V, (int)((feat >> 16) & 255u)) - vert_at(V, (int)((feat >> 8) & 255u));
-    u = u - e * (dot(u, e) / dot(e, e));
-  }
-  const float dd = dot(u, u);
-#ifdef __CUDA_ARCH__
-  float inv = rsqrtf(dd);
-  inv = inv * (1.5f - 0.5f * dd * inv * inv);
-#else
-  const float inv = 1.0f / sqrtf(dd);
-#endif
-  nrm = u * inv;
-  return dd * inv;
+FLASH_HD float hull_sd(const HullView& V, F3 y, F3& nrm, unsigned start = 0u) {
+  FLASH_COUNT(narrow, 1);
+  return bsp_feature_sd(V, bsp_locate(V, start, y), y, nrm);
 }
 
 // conservative lower bound of the signed distance from the AABB of the hull
@@ -1096,19 +640,14 @@ FLASH_HD void skin_adjoint_term(const double* __restrict__ c, const double* __re
 }
 
 // ------------------------------------------------------------------ min over surfaces (row A6)
-struct GeoView {            // geometry blob (shared memory in the main kernel)
-  const F4* f4;             // plane pairs, vertex pairs
-  const uint32_t* u32;      // per-plane start triangle
+struct GeoView {            // geometry blob (global memory, read through L1)
+  const F4* f4;             // BSP node planes, plane / vertex / edge tables
+  const uint32_t* u32;      // BSP child words
   const float* grid_pool;   // grid mode
 };
 FLASH_HD HullView hull_view(const GeoView& G, const ConvexC& C) {
   HullView V;
-  V.planes = G.f4 + C.off_planes; V.ptri = G.u32 + C.off_tris; V.va = G.f4 + C.off_verts;
-  V.vz = reinterpret_cast<const float*>(G.f4 + C.off_vz); V.np = C.nplanes_pad; V.nv = C.nverts_pad;
-  V.voff = reinterpret_cast<const unsigned short*>(G.u32 + C.off_voff);
-  V.vlist = reinterpret_cast<const unsigned char*>(G.u32 + C.off_vlist);
-  V.pgrp = reinterpret_cast<const unsigned short*>(G.u32 + C.off_pgrp);
-  V.bn = G.f4 + C.off_bn; V.bk = G.u32 + C.off_bk; V.bp = G.f4 + C.off_bp; V.bv = G.f4 + C.off_bv; V.be = G.f4 + C.off_be; V.bsp_on = C.bsp_on;
+  V.bn = G.f4 + C.off_bn; V.bk = G.u32 + C.off_bk; V.bp = G.f4 + C.off_bp; V.bv = G.f4 + C.off_bv; V.be = G.f4 + C.off_be;
   return V;
 }
 
@@ -1134,24 +673,6 @@ FLASH_HD void hull_ball_bounds(const ConvexC& C, const float* __restrict__ T, fl
   lb = aabb_lower_bound(C.lo, C.hi, C.depth_bound, y) - r - 4e-6f;
   ub = sqrtf(dot(y, y)) * (1.f + 4e-6f) + 8e-6f - C.r_in + r;
 }
-// Hulls that can be the minimum for SOME point of the ball: lb_j <= min_k ub_k.  A culled hull is
-// strictly farther than hull argmin(ub) at every point of the ball, so neither the min nor the argmin
-// (first minimum) changes.  `first` = the most promising candidate (smallest lower bound).
-FLASH_HD unsigned group_candidates(const HotModel& M, const float* __restrict__ tabf, float cx, float cy, float cz, float rho, int& first, float* min_ub_out = nullptr) {
-  float lb[MAX_CONVEX];
-  float min_ub = 3.0e38f;
-  for (int j = 0; j < M.n_convex; ++j) {
-    float ub;
-    hull_ball_bounds(M.cvx[j], tabf + 12 * j, cx, cy, cz, rho, lb[j], ub);
-    min_ub = fminf(min_ub, ub);
-  }
-  if (min_ub_out) *min_ub_out = min_ub;
-  unsigned mask = 0; float lb0 = 3.0e38f; first = -1;
-  for (int j = 0; j < M.n_convex; ++j)
-    if (lb[j] <= min_ub) { mask |= 1u << j; if (lb[j] < lb0) { lb0 = lb[j]; first = j; } }
-  return mask;
-}
-
 // Skins that are the minimum for NO point of the ball (bit k set = skip skin k): their certified lower bound over
 // the ball exceeds min_ub, the smallest hull upper bound (group_candidates), by more than the fp32 rounding of
 // the final comparison.  `cut` receives an upper bound of the group's minimum to start the hull scans from.
@@ -1167,49 +688,69 @@ FLASH_HD unsigned group_skin_cull(const HotModel& M, const float* __restrict__ t
   return skip;
 }
 
-// The whole group pre-pass of cost_kernel for one group (ball c, rho) of one configuration:
-//   cand / first   hulls that can be the minimum for some point of the ball, the most promising one
-//   feat           certified closest feature of `first` for the whole ball (hull_ball_feature), 0 if none
+// The group pre-pass of cost_kernel (group_kernel: one thread per group of 32 points and configuration; ball c, rho):
+//   cand / first   hulls that can be the minimum for some point of the ball, the nearest one at the centre
 //   skip / cut     skins that are the minimum for no point of the ball; upper bound of the group's minimum
-// The exact distance of `first` at the ball centre (a by-product of the feature search) tightens the upper bound
-// of the group's minimum from |c - centroid| - inradius + rho to d(c) + rho, which culls more hulls and skins.
-struct GroupPre { unsigned cand; int first; unsigned feat; unsigned skip; float cut; };
+//   starts         per candidate, in evaluation order (first, then the others by index; three at most): the BSP node
+//                  from which the points of the ball finish their descent (bsp_descend_ball), or already their leaf
+// Bounds: the cheap AABB / inradius bounds of hull_ball_bounds first; with `exact`, every hull they keep is evaluated
+// exactly at the ball centre (one BSP descent), and the distance being 1-Lipschitz, d_j(c) -+ rho bounds it over
+// the ball far more tightly (K5: 3.0 candidates per group from the AABB bounds).  Hulls with lb_j > min_k ub_k are
+// strictly farther than hull argmin(ub) at every point of the ball, so neither the min nor the argmin changes.
+// Not with grid mode, whose per-point values deviate from the exact distance by the grid error.
+struct GroupPre { unsigned cand; int first; unsigned skip; float cut; unsigned long long starts; };
 FLASH_HD GroupPre group_prepass(const HotModel& M, const GeoView& G, const float* __restrict__ tabf, float cx, float cy, float cz, float rho,
-                                bool want_feat, bool want_skin_cull) {
-  GroupPre o; o.cand = 0u; o.first = -1; o.feat = 0u; o.skip = 0u; o.cut = 3.0e38f;
+                                bool exact, bool want_skin_cull) {
+  GroupPre o; o.cand = 0u; o.first = -1; o.skip = 0u; o.cut = 3.0e38f; o.starts = 0ull;
   const int nc = M.n_convex;
-  float min_ub = 3.0e38f, lb0 = 3.0e38f;
+  float min_ub = 3.0e38f;
   float lb[MAX_CONVEX];
+  unsigned short st[MAX_CONVEX];
   for (int j = 0; j < nc; ++j) {
     float ubv;
     hull_ball_bounds(M.cvx[j], tabf + 12 * j, cx, cy, cz, rho, lb[j], ubv);
     min_ub = fminf(min_ub, ubv);
-    if (lb[j] < lb0) { lb0 = lb[j]; o.first = j; }
+    st[j] = 0;
   }
-  if (want_feat && o.first >= 0) {
-    const ConvexC& C = M.cvx[o.first];
-    float dc;
-    o.feat = hull_ball_feature(hull_view(G, C), to_geometry_f32(tabf + 12 * o.first, cx, cy, cz), rho, dc);
-    const float ub2 = dc + rho * (1.f + 1e-5f) + 1e-5f;   // 1-Lipschitz: d(x) <= d(c) + rho
-    if (dc < 3.0e37f) min_ub = fminf(min_ub, ub2);
+  if (exact) {
+    const float r = rho * (1.f + 1e-5f) + 1e-5f;   // ball radius + slack for the fp32 transform of the centre
+    for (int j = 0; j < nc; ++j) {
+      if (lb[j] > min_ub) continue;
+      const HullView V = hull_view(G, M.cvx[j]);
+      const F3 yc = to_geometry_f32(tabf + 12 * j, cx, cy, cz);
+      const unsigned s0 = bsp_descend_ball(V, yc, r);
+      F3 nn;
+      const float dc = bsp_feature_sd(V, bsp_locate(V, s0, yc), yc, nn);
+      st[j] = (unsigned short)s0;
+      lb[j] = fmaxf(lb[j], dc - r);
+      min_ub = fminf(min_ub, dc + r);
+    }
   }
+  float lb0 = 3.0e38f;
   for (int j = 0; j < nc; ++j)
-    if (lb[j] <= min_ub || j == o.first) o.cand |= 1u << j;
-  if (o.cand == 0u) { o.cand = nc >= 32 ? 0xffffffffu : ((1u << nc) - 1u); o.first = -1; o.feat = 0u; return o; }   // only with non-finite bounds
+    if (lb[j] <= min_ub) { o.cand |= 1u << j; if (lb[j] < lb0) { lb0 = lb[j]; o.first = j; } }
+  if (o.cand == 0u) { o.cand = nc >= 32 ? 0xffffffffu : ((1u << nc) - 1u); o.first = -1; return o; }   // only with non-finite bounds
+  {
+    int t = 1;
+    o.starts = (unsigned long long)st[o.first];
+    for (int j = 0; j < nc && t < 4; ++j)
+      if (j != o.first && ((o.cand >> j) & 1u)) { o.starts |= (unsigned long long)st[j] << (16 * t); ++t; }
+  }
   if (want_skin_cull && M.n_skins > 0 && M.n_skins <= 8) o.skip = group_skin_cull(M, tabf, cx, cy, cz, rho, min_ub, o.cut);
   return o;
 }
 
 // Evaluates skin(x) = min over all surfaces for one world point under one configuration.
-// `cand` = bit mask of the convex slots to consider (group_candidates, or all ones), `first` = the
-// slot to evaluate first (-1: chosen here from the per-point bounds).  Within the candidates a body is
-// evaluated exactly only if its per-point AABB lower bound can still beat the best value so far,
-// which cannot change the min or the argmin.
+// `cand` = bit mask of the convex slots to consider (group_prepass, or all ones), `first` = the
+// slot to evaluate first (-1: chosen here from the per-point bounds), `starts` = the BSP start words of the
+// candidates in evaluation order, 16 bits each (0 = the root).  Within the candidates a body is evaluated
+// exactly only if its per-point AABB lower bound can still beat the best value so far, which cannot change
+// the min or the argmin.
 // The point is passed in fp64: the cost path feeds fp32 points (exact in fp64), the ray marcher its
 // fp64 sample positions.
 FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __restrict__ tab, const float* __restrict__ tabf,
                          double px, double py, double pz, unsigned cand, int first, bool use_grid, bool fp32_point, PointEval& out,
-                         unsigned skin_skip = 0u, float cut0 = 3.0e38f, unsigned feat = 0u) {
+                         unsigned skin_skip = 0u, float cut0 = 3.0e38f, unsigned long long starts = 0ull) {
   const ConvexC* __restrict__ cvx = M.cvx;
   float best = 3.0e38f; int arg = 0x7fffffff; int slot = -1; int is_skin = 0;
   out.y = f3(0, 0, 0); out.n = f3(0, 0, 0);
@@ -1217,7 +758,7 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
   const int nc = M.n_convex;
   const float fx = (float)px, fy = (float)py, fz = (float)pz;
   // Skins.  With convex bodies in the model the fp64 evaluation is deferred: a certified fp32 interval
-  // [lo, hi] of each skin's value is enough to (a) give the hull scans a cutoff (hi) and (b) decide
+  // [lo, hi] of each skin's value is enough to (a) give the hull tests a cutoff (hi) and (b) decide
   // afterwards whether the skin can still be the minimum (lo <= best hull); only then is it evaluated
   // in fp64.  The point must be fp32-representable for the interval to be valid (cost path); the ray
   // marcher passes fp64 sample positions and evaluates the skins directly.
@@ -1247,6 +788,7 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
       const float l = aabb_lower_bound(cvx[j].lo, cvx[j].hi, cvx[j].depth_bound, to_geometry_f32(tabf + 12 * j, fx, fy, fz));
       if (l < lb0) { lb0 = l; first = j; }
     }
+    starts = 0ull;
   }
   // `first`, then the remaining candidates in surface order
   const bool single = (cand & (cand - 1u)) == 0u;
@@ -1263,27 +805,8 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
       rest &= rest - 1u;
     }
     const ConvexC& C = cvx[j];
-    // Per-point use of the group's certified feature / GJK warm start.  Compiled into the device loop only on request
-    // (-DFLASH_FEAT_PATH): measured on K5 it LOSES -- 54.9 ms with it, 49.0 with the code present but never taken,
-    // 42.2 ms without the code (round 2, B200; K2 0.110 / 0.088 / 0.080 ms, K4 4.65 / 4.41 / 3.97 ms): the point loop is
-    // instruction-fetch and register bound (80 registers: 460 B of spills with the path, 216 B without).  The host
-    // replay (tests/hostcheck) keeps it, so the certificates stay tested.
-#if !defined(__CUDA_ARCH__) || defined(FLASH_FEAT_PATH)
-    if ((feat & 3u) != 0u && j == first) {
-      const F3 y = to_geometry(tab + 12 * j, px, py, pz);
-      F3 n; float d; bool ok = true;
-      if (feat & FEAT_CERT) {
-        // the group's ball lies in the Voronoi region of one feature of this hull (hull_ball_feature): closed form
-        FLASH_COUNT(feat_evals, 1);
-        d = hull_feature_eval(hull_view(G, C), feat, y, n);
-      } else ok = hull_sd_warm(hull_view(G, C), feat, y, d, n);   // GJK from the simplex found at the ball centre
-      if (ok) {
-        if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
-        j = -1;
-        continue;
-      }
-    }
-#endif
+    const unsigned start = (unsigned)(starts & 0xffffull);
+    starts >>= 16;
     bool skip = false;
     if (!single) {
       FLASH_COUNT(lb_tests, 1);
@@ -1296,16 +819,9 @@ FLASH_HD void eval_point(const HotModel& M, const GeoView& G, const double* __re
       bool done = false;
       if (use_grid && C.g_on) done = grid_sd(C, G.grid_pool, y, d, n);
 #if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
-      const long long narrow0 = flashdev::counters().narrow;
+      if (!done) flashdev::counters().exact_mask |= 1u << j;
 #endif
-#ifdef FLASH_GJK_PATH
-      if (!done) d = hull_sd(hull_view(G, C), y, fminf(best, cut), n);
-#else
-      if (!done) { FLASH_COUNT(narrow, 1); d = hull_sd_bsp(hull_view(G, C), y, n); }
-#endif
-#if defined(FLASH_COUNTERS) && !defined(__CUDA_ARCH__)
-      if (flashdev::counters().narrow != narrow0) flashdev::counters().exact_mask |= 1u << j;
-#endif
+      if (!done) d = hull_sd(hull_view(G, C), y, n, start);
       if (lex_less(d, C.surface, best, arg)) { best = d; arg = C.surface; slot = j; is_skin = 0; out.y = y; out.n = n; }
     }
     j = -1;

@@ -1,6 +1,6 @@
 // flash_host.h -- host-side model ingestion for libflashsdf: validates a flash_model_desc, builds
-// the convex hulls (supporting planes + GJK start triangles), re-centres their geometry frames and
-// packs everything into the device layout of flash_dev.h.  Plain C++17 (no CUDA), so the same code
+// the convex hulls (supporting planes) and their closest-feature BSP trees (flash_bsp.h), re-centres
+// their geometry frames and packs everything into the device layout of flash_dev.h.  Plain C++17 (no CUDA), so the same code
 // is exercised by the CPU-only tests.
 //
 // Replaces, for the hot path, what the Julia side holds in `Manipulator` / `ConvexGeometry` /
@@ -33,7 +33,6 @@ struct HullOut {
   std::vector<D3> verts;                        // welded, re-centred
   D3 centroid;                                  // removed offset
   std::vector<std::array<double, 4>> planes;    // n.x - o <= 0 inside
-  std::vector<std::array<int, 3>> ptri;         // per plane: the largest-area vertex triple on it
 };
 
 inline double nrm(D3 a) { return std::sqrt(dot(a, a)); }
@@ -95,152 +94,7 @@ inline bool build_hull(const std::vector<D3>& in, HullOut& H, std::string& err) 
   if (planes.size() > 1024) { err = "convex surface has more than 1024 faces"; return false; }
   H.verts = v;
   H.planes = planes;
-  for (auto& p : planes) {
-    std::vector<int> on;
-    for (int m = 0; m < n; ++m) if (std::fabs(p[0] * v[m].x + p[1] * v[m].y + p[2] * v[m].z - p[3]) <= 1e-7 * diam) on.push_back(m);
-    std::array<int, 3> best = {on.size() > 0 ? on[0] : 0, on.size() > 1 ? on[1] : 0, on.size() > 2 ? on[2] : 0};
-    double ba = -1;
-    for (size_t a = 0; a < on.size(); ++a)
-      for (size_t b = a + 1; b < on.size(); ++b)
-        for (size_t d = b + 1; d < on.size(); ++d) {
-          double ar = nrm(cross(v[on[b]] - v[on[a]], v[on[d]] - v[on[a]]));
-          if (ar > ba) { ba = ar; best = {on[a], on[b], on[d]}; }
-        }
-    H.ptri.push_back(best);
-  }
   return true;
-}
-
-// Support direction map of one hull (flash_dev.h dir_cell): the exact support-candidate lists.  Vertex k is a candidate of a cell iff its normal cone
-// {d : d.(v_k - v_j) >= 0 for all j} meets the cell (grown by a margin that covers the fp32 cell
-// lookup on the device): the cell's quad in face coordinates is clipped by every half-plane
-// (Sutherland-Hodgman); what survives is the set of directions v_k supports.
-struct DirMaps { std::vector<unsigned short> voff; std::vector<unsigned char> vlist; };
-inline void build_dirmaps(const std::vector<std::array<float, 3>>& v, int nverts, DirMaps& out) {
-  const int R = DIRMAP_R;
-  out.voff.assign(DIRMAP_CELLS + 1, 0); out.vlist.clear();
-  double rout = 0;
-  for (int k = 0; k < nverts; ++k) rout = std::max(rout, std::sqrt((double)v[k][0] * v[k][0] + (double)v[k][1] * v[k][1] + (double)v[k][2] * v[k][2]));
-  const double margin = 2e-3, eps = 1e-9 * std::max(rout, 1e-30);
-  typedef std::array<double, 2> P2;
-  for (int face = 0; face < 6; ++face) {
-    const int ax = face / 2; const double sg = (face % 2 == 0) ? 1.0 : -1.0;
-    const int e1 = (ax + 1) % 3, e2 = (ax + 2) % 3;   // dir_cell: u = next axis, v = the one after
-    for (int iv = 0; iv < R; ++iv)
-      for (int iu = 0; iu < R; ++iu) {
-        const int cell = (face * R + iv) * R + iu;
-        const double u0 = -1.0 + 2.0 * iu / R - margin, u1 = -1.0 + 2.0 * (iu + 1) / R + margin;
-        const double v0 = -1.0 + 2.0 * iv / R - margin, v1 = -1.0 + 2.0 * (iv + 1) / R + margin;
-        for (int k = 0; k < nverts; ++k) {
-          std::vector<P2> poly = {{u0, v0}, {u1, v0}, {u1, v1}, {u0, v1}}, nxt;
-          for (int j = 0; j < nverts && !poly.empty(); ++j) {
-            if (j == k) continue;
-            const double w[3] = {(double)v[k][0] - v[j][0], (double)v[k][1] - v[j][1], (double)v[k][2] - v[j][2]};
-            const double a = w[e1], b = w[e2], c = sg * w[ax] + eps;   // keep a*u + b*v + c >= 0
-            nxt.clear();
-            const size_t n = poly.size();
-            for (size_t i = 0; i < n; ++i) {
-              const P2 p = poly[i], q = poly[(i + 1) % n];
-              const double fp = a * p[0] + b * p[1] + c, fq = a * q[0] + b * q[1] + c;
-              if (fp >= 0) nxt.push_back(p);
-              if ((fp >= 0) != (fq >= 0)) { const double t = fp / (fp - fq); nxt.push_back({p[0] + t * (q[0] - p[0]), p[1] + t * (q[1] - p[1])}); }
-            }
-            poly.swap(nxt);
-          }
-          if (!poly.empty()) out.vlist.push_back((unsigned char)k);
-        }
-        out.voff[cell + 1] = (unsigned short)out.vlist.size();
-      }
-  }
-}
-
-// Plane groups for hull_plane_hint (flash_dev.h).  (1) The planes are clustered into groups of 8 by normal
-// direction (balanced k-means on the unit sphere, farthest-point seeds): `order` lists, slot by slot, the
-// plane stored there (-1 = inert padding); group g = slots [8g, 8g+8).
-inline void cluster_planes(const std::vector<std::array<double, 4>>& planes, std::vector<int>& order) {
-  const int n = (int)planes.size(), K = (n + 7) / 8;
-  std::vector<D3> nv(n), cen(K);
-  for (int f = 0; f < n; ++f) nv[f] = d3(planes[f][0], planes[f][1], planes[f][2]);
-  std::vector<int> grp(n, 0);
-  {  // farthest-point seeds
-    std::vector<double> best(n, -2.0);
-    int cur = 0;
-    for (int k = 0; k < K; ++k) {
-      cen[k] = nv[cur];
-      int nxt = 0; double lo = 3.0;
-      for (int f = 0; f < n; ++f) { best[f] = std::max(best[f], dot(nv[f], cen[k])); if (best[f] < lo) { lo = best[f]; nxt = f; } }
-      cur = nxt;
-    }
-  }
-  for (int it = 0; it < 12; ++it) {
-    // balanced assignment: (plane, centre) pairs by decreasing similarity, capacity 8 per centre
-    std::vector<std::array<double, 3>> pr;
-    pr.reserve((size_t)n * K);
-    for (int f = 0; f < n; ++f) for (int k = 0; k < K; ++k) pr.push_back({-dot(nv[f], cen[k]), (double)f, (double)k});
-    std::sort(pr.begin(), pr.end());
-    std::vector<int> cnt(K, 0); std::vector<char> done(n, 0);
-    for (auto& e : pr) {
-      const int f = (int)e[1], k = (int)e[2];
-      if (done[f] || cnt[k] >= 8) continue;
-      grp[f] = k; done[f] = 1; ++cnt[k];
-    }
-    for (int k = 0; k < K; ++k) {
-      D3 c = d3(0, 0, 0);
-      for (int f = 0; f < n; ++f) if (grp[f] == k) c = c + nv[f];
-      const double l = nrm(c);
-      if (l > 1e-12) cen[k] = c * (1.0 / l);
-    }
-  }
-  order.assign((size_t)8 * K, -1);
-  std::vector<int> fill(K, 0);
-  for (int f = 0; f < n; ++f) order[(size_t)8 * grp[f] + fill[grp[f]]++] = f;
-}
-// (2) Per direction cell: the two groups that most often hold the most-violated plane of an outside point
-// y = t d of the cell.  Along a ray the plane distances t (n_f.d) - o_f are lines in t; outside the hull
-// (t > t_exit) the most-violated plane runs through their upper envelope, which is walked exactly; every
-// plane on it is weighted by the log-length of its stretch (clipped to 20 t_exit).  5 x 5 rays per cell.
-inline void build_plane_hints(const std::vector<std::array<double, 4>>& planes, const std::vector<int>& order, std::vector<unsigned short>& pgrp) {
-  const int R = DIRMAP_R, n = (int)planes.size(), K = (int)order.size() / 8;
-  std::vector<int> grp_of(n, 0);
-  for (size_t s = 0; s < order.size(); ++s) if (order[s] >= 0) grp_of[order[s]] = (int)(s / 8);
-  pgrp.assign(DIRMAP_CELLS, 0);
-  std::vector<double> a(n), wgt(K);
-  for (int face = 0; face < 6; ++face) {
-    const int ax = face / 2; const double sg = (face % 2 == 0) ? 1.0 : -1.0;
-    const int e1 = (ax + 1) % 3, e2 = (ax + 2) % 3;
-    for (int iv = 0; iv < R; ++iv)
-      for (int iu = 0; iu < R; ++iu) {
-        std::fill(wgt.begin(), wgt.end(), 0.0);
-        for (int sv = 0; sv < 5; ++sv)
-          for (int su = 0; su < 5; ++su) {
-            double d[3];
-            d[ax] = sg; d[e1] = -1.0 + 2.0 * (iu + 0.05 + 0.225 * su) / R; d[e2] = -1.0 + 2.0 * (iv + 0.05 + 0.225 * sv) / R;
-            int f = -1; double t = 1e300;
-            for (int g = 0; g < n; ++g) {
-              a[g] = planes[g][0] * d[0] + planes[g][1] * d[1] + planes[g][2] * d[2];
-              if (a[g] > 0 && planes[g][3] / a[g] < t) { t = planes[g][3] / a[g]; f = g; }
-            }
-            if (f < 0) continue;
-            const double t_end = 20.0 * t;
-            for (int guard = 0; guard < n && t < t_end; ++guard) {
-              int nf = -1; double tn = t_end;
-              for (int g = 0; g < n; ++g) {
-                if (!(a[g] > a[f])) continue;
-                const double tc = (planes[g][3] - planes[f][3]) / (a[g] - a[f]);
-                if (tc < tn) { tn = tc; nf = g; }
-              }
-              wgt[grp_of[f]] += std::log(std::max(tn, t * (1 + 1e-12)) / t) + 1e-3;
-              if (nf < 0) break;
-              f = nf; t = std::max(tn, t);
-            }
-          }
-        int b0 = 0, b1 = -1;
-        for (int k = 1; k < K; ++k) if (wgt[k] > wgt[b0]) b0 = k;
-        for (int k = 0; k < K; ++k) if (k != b0 && wgt[k] > 0 && (b1 < 0 || wgt[k] > wgt[b1])) b1 = k;
-        if (b1 < 0) b1 = b0;
-        pgrp[(face * R + iv) * R + iu] = (unsigned short)(b0 | (b1 << 8));
-      }
-  }
 }
 
 inline void options_default(flash_options* o) {
@@ -311,65 +165,11 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
       HullOut H;
       if (!build_hull(pts, H, err)) { err = "surface " + std::to_string(s) + ": " + err; return false; }
       C.nverts = (int)H.verts.size(); C.nplanes = (int)H.planes.size();
-      C.off_planes = (int)out.geo_f4.size(); C.off_tris = (int)out.geo_u32.size();
-      // planes: padded to a multiple of 8 with planes that can never be the maximum, stored as pairs
-      // {nx0,nx1,ny0,ny1}{nz0,nz1,-o0,-o1} for the packed-FMA scan (flash_dev.h "geometry blob layout")
-      // slot order: groups of 8 planes with neighbouring normals (cluster_planes); padding slots are inert
-      std::vector<int> order;
-      std::vector<unsigned short> pgrp;
-      if (C.nplanes <= 8 * 255) {
-        cluster_planes(H.planes, order);
-        build_plane_hints(H.planes, order, pgrp);
-      } else {   // more groups than a byte can name: no hint (every cell points at group 0; the full scan decides)
-        for (int f = 0; f < ((C.nplanes + 7) & ~7); ++f) order.push_back(f < C.nplanes ? f : -1);
-        pgrp.assign(DIRMAP_CELLS, 0);
-      }
-      C.nplanes_pad = (int)order.size();
-      {
-        std::vector<std::array<float, 4>> pl;
-        uint32_t any_tri = (uint32_t)H.ptri[0][0] | ((uint32_t)H.ptri[0][1] << 8) | ((uint32_t)H.ptri[0][2] << 16);
-        for (int slot = 0; slot < C.nplanes_pad; ++slot) {
-          const int f = order[slot];
-          if (f < 0) { pl.push_back({0.f, 0.f, 0.f, -1.0e30f}); out.geo_u32.push_back(any_tri); continue; }
-          pl.push_back({(float)H.planes[f][0], (float)H.planes[f][1], (float)H.planes[f][2], -(float)H.planes[f][3]});
-          out.geo_u32.push_back((uint32_t)H.ptri[f][0] | ((uint32_t)H.ptri[f][1] << 8) | ((uint32_t)H.ptri[f][2] << 16));
-        }
-        for (int f = 0; f < C.nplanes_pad; f += 2) {
-          out.geo_f4.push_back(F4{pl[f][0], pl[f + 1][0], pl[f][1], pl[f + 1][1]});
-          out.geo_f4.push_back(F4{pl[f][2], pl[f + 1][2], pl[f][3], pl[f + 1][3]});
-        }
-      }
-      // vertices: padded with copies of vertex 0 (never a strictly better support); pairs {x0,x1,y0,y1}
-      // followed by the flat z array
-      C.nverts_pad = (C.nverts + 7) & ~7;
-      std::vector<std::array<float, 3>> vf;
       for (int k = 0; k < 3; ++k) { C.lo[k] = 3e38f; C.hi[k] = -3e38f; }
       for (auto& v : H.verts) {
-        std::array<float, 3> f = {(float)v.x, (float)v.y, (float)v.z};
-        vf.push_back(f);
+        const float f[3] = {(float)v.x, (float)v.y, (float)v.z};
         // bounds must contain the fp32 vertices (nextafter outward)
         for (int k = 0; k < 3; ++k) { C.lo[k] = std::min(C.lo[k], std::nextafterf(f[k], -3e38f)); C.hi[k] = std::max(C.hi[k], std::nextafterf(f[k], 3e38f)); }
-      }
-      for (int v = C.nverts; v < C.nverts_pad; ++v) vf.push_back(vf[0]);
-      C.off_verts = (int)out.geo_f4.size();
-      for (int v = 0; v < C.nverts_pad; v += 2) out.geo_f4.push_back(F4{vf[v][0], vf[v + 1][0], vf[v][1], vf[v + 1][1]});
-      C.off_vz = (int)out.geo_f4.size();
-      for (int v = 0; v < C.nverts_pad; v += 4) out.geo_f4.push_back(F4{vf[v][2], vf[v + 1][2], vf[v + 2][2], vf[v + 3][2]});
-      {
-        // support direction map -> blob (u32 words): voff u16 | vlist bytes
-        DirMaps dm;
-        build_dirmaps(vf, C.nverts, dm);
-        auto push_bytes = [&](const void* src, size_t nbytes) {
-          const size_t words = (nbytes + 3) / 4, at = out.geo_u32.size();
-          out.geo_u32.resize(at + words, 0u);
-          std::memcpy(out.geo_u32.data() + at, src, nbytes);
-          return (int)at;
-        };
-        C.off_voff = push_bytes(dm.voff.data(), dm.voff.size() * sizeof(unsigned short));
-        if (dm.vlist.empty()) dm.vlist.push_back(0);
-        C.off_vlist = push_bytes(dm.vlist.data(), dm.vlist.size());
-        C.off_pgrp = push_bytes(pgrp.data(), pgrp.size() * sizeof(unsigned short));
-        C.pgrp_pad = 0;
       }
       {
         double rin = 1e300;   // the geometry origin is the vertex centroid: strictly inside
@@ -384,23 +184,21 @@ inline bool build_model(const flash_model_desc* d, const flash_options* opt_in, 
       }
       C.depth_bound = (float)(db * 1.0001 + 1e-6);
       {
-        // closest-feature BSP tree (flash_bsp.h) -> blob: node planes, plain plane table {n, -o}, vertices {x, y, z, 0}, edges
+        // closest-feature BSP tree (flash_bsp.h) -> blob: node planes, plane table {n, -o}, vertices {x, y, z, 0}, edges; child words
         flashbsp::BspHull bh; std::string berr;
-        C.bsp_on = 0; C.off_bn = C.off_bk = C.off_bp = C.off_bv = C.off_be = 0;
-        if (opt.reserved[0] != 1 && flashbsp::build_bsp(H.verts, H.planes, bh, berr)) {
-          C.bsp_on = 1;
-          C.off_bn = (int)out.geo_f4.size();
-          for (auto& p : bh.node_plane) out.geo_f4.push_back(F4{p[0], p[1], p[2], p[3]});
-          C.off_bp = (int)out.geo_f4.size();
-          for (auto& p : H.planes) out.geo_f4.push_back(F4{(float)p[0], (float)p[1], (float)p[2], -(float)p[3]});
-          C.off_bv = (int)out.geo_f4.size();
-          for (auto& v : H.verts) out.geo_f4.push_back(F4{(float)v.x, (float)v.y, (float)v.z, 0.f});
-          C.off_be = (int)out.geo_f4.size();
-          for (auto& e : bh.edges) out.geo_f4.push_back(F4{e[0], e[1], e[2], e[3]});
-          C.off_bk = (int)out.geo_u32.size();
-          for (uint32_t w : bh.node_kids) out.geo_u32.push_back(w);
-          out.bsp_stats.push_back({(double)bh.node_plane.size(), (double)bh.max_depth, bh.mean_depth, (double)bh.n_regions, (double)bh.n_dropped});
-        } else out.bsp_stats.push_back({0, 0, 0, 0, 0});
+        if (!flashbsp::build_bsp(H.verts, H.planes, bh, berr)) { err = "surface " + std::to_string(s) + ": " + berr; return false; }
+        C.n_nodes = (int)bh.node_plane.size();
+        C.off_bn = (int)out.geo_f4.size();
+        for (auto& p : bh.node_plane) out.geo_f4.push_back(F4{p[0], p[1], p[2], p[3]});
+        C.off_bp = (int)out.geo_f4.size();
+        for (auto& p : H.planes) out.geo_f4.push_back(F4{(float)p[0], (float)p[1], (float)p[2], -(float)p[3]});
+        C.off_bv = (int)out.geo_f4.size();
+        for (auto& v : H.verts) out.geo_f4.push_back(F4{(float)v.x, (float)v.y, (float)v.z, 0.f});
+        C.off_be = (int)out.geo_f4.size();
+        for (auto& e : bh.edges) out.geo_f4.push_back(F4{e[0], e[1], e[2], e[3]});
+        C.off_bk = (int)out.geo_u32.size();
+        for (uint32_t w : bh.node_kids) out.geo_u32.push_back(w);
+        out.bsp_stats.push_back({(double)bh.node_plane.size(), (double)bh.max_depth, bh.mean_depth, (double)bh.n_regions, (double)bh.n_dropped});
       }
       // geometry frame = surface frame shifted to the centroid
       double fr[12], sh[12] = {1, 0, 0, 0, 1, 0, 0, 0, 1, H.centroid.x, H.centroid.y, H.centroid.z};

@@ -12,9 +12,9 @@
 //   grid kernels     SDF grid baking / error sampling for FLASH_SDF_GRID
 //
 // Design notes (B200): tensor cores are not used (no dense contraction on this path).  Points are
-// read as coalesced float4; hull geometry, the config's transforms and RBF tables are staged in
-// shared memory once per block; reductions are warp shuffles -> per-warp shared accumulators ->
-// one fp64 atomicAdd per accumulator per block.
+// read as coalesced float4; the config's transforms and RBF tables are staged in shared memory once
+// per block, the hulls' closest-feature BSP trees are read from global memory through L1; reductions
+// are warp shuffles -> per-warp shared accumulators -> one fp64 atomicAdd per accumulator per block.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -57,7 +57,6 @@ struct CostParams {
   const F4* geo_f4;
   const uint32_t* geo_u32;
   const float* grid_pool;
-  int geo_f4_n, geo_u32_n;
   const float4* pts;
   long long n_pts;
   const double* tab;   // [C][tab_len]
@@ -78,14 +77,12 @@ __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t
 
 // dynamic shared memory layout of cost_kernel / raycast_kernel
 struct SmemLayout {
-  size_t off_hot, off_f4, off_u32, off_tab, off_tabf, off_acc, off_queue, off_qslot, total;
+  size_t off_hot, off_tab, off_tabf, off_acc, off_queue, off_qslot, total;
 };
-__host__ __device__ inline SmemLayout smem_layout(int geo_f4_n, int geo_u32_n, int tab_len, int acc_len, int tabf_len, bool grad_skins, int warps = WARPS) {
+__host__ __device__ inline SmemLayout smem_layout(int tab_len, int acc_len, int tabf_len, bool grad_skins, int warps = WARPS) {
   SmemLayout L;
   size_t o = 0;
   L.off_hot = o; o = align16(o + sizeof(HotModel));
-  L.off_f4 = o; o = align16(o + sizeof(F4) * (size_t)geo_f4_n);
-  L.off_u32 = o; o = align16(o + sizeof(uint32_t) * (size_t)geo_u32_n);
   L.off_tab = o; o = align16(o + sizeof(double) * (size_t)tab_len);
   L.off_tabf = o; o = align16(o + sizeof(float) * (size_t)(tabf_len > 0 ? tabf_len : 4));
   L.off_acc = o; o = align16(o + sizeof(double) * (size_t)acc_len * warps);
@@ -313,23 +310,13 @@ __global__ void __launch_bounds__(PREP_T) prepare_kernel(const ModelC* __restric
 }
 
 // ------------------------------------------------------------------------------------------------
-// stage model + geometry + this config's table in shared memory
-__device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayout& L, const HotModel* hot, const F4* geo_f4, int nf4,
-                                            const uint32_t* geo_u32, int nu32, const double* tab, int tab_len, int nthreads = BLOCK) {
+// stage the model and this config's tables in shared memory
+__device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayout& L, const HotModel* hot, const double* tab, int tab_len, int nthreads = BLOCK) {
   const int tid = threadIdx.x;
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(hot);
     uint32_t* dst = reinterpret_cast<uint32_t*>(smem + L.off_hot);
     for (int i = tid; i < (int)(sizeof(HotModel) / 4); i += nthreads) dst[i] = src[i];
-  }
-  {
-    const float4* src = reinterpret_cast<const float4*>(geo_f4);
-    float4* dst = reinterpret_cast<float4*>(smem + L.off_f4);
-    for (int i = tid; i < nf4; i += nthreads) dst[i] = __ldg(src + i);
-  }
-  {
-    uint32_t* dst = reinterpret_cast<uint32_t*>(smem + L.off_u32);
-    for (int i = tid; i < nu32; i += nthreads) dst[i] = __ldg(geo_u32 + i);
   }
   {
     double* dst = reinterpret_cast<double*>(smem + L.off_tab);
@@ -341,16 +328,16 @@ __device__ __forceinline__ void stage_block(unsigned char* smem, const SmemLayou
 
 // ------------------------------------------------------------------------------------------------
 // Group pre-pass as its own kernel: ONE THREAD per (configuration, group of 32 points).  Everything it decides is
-// decided once for 32 evaluations (flash_dev.h group_prepass): candidate hulls, the most promising one and -- from one
-// narrow phase at the ball centre -- its certified closest feature and a tight upper bound of the group's minimum,
-// which in turn culls more hulls and skins.  Inside cost_kernel (round 1: a phase in front of the point loop, one 768-
-// thread block per SM) the same code left two thirds of the block waiting at a barrier behind long serial threads; here
-// it runs at full occupancy and the point loop only loads a 16-byte record per group.
+// decided once for 32 evaluations (flash_dev.h group_prepass): the candidate hulls from exact distances at the ball
+// centre, the nearest one, the BSP nodes from which the group's points finish their descent, the skins that cannot be
+// the minimum and an upper bound of the group's minimum.  Inside cost_kernel (round 1: a phase in front of the point
+// loop, one 768-thread block per SM) the same code left two thirds of the block waiting at a barrier behind long
+// serial threads; here it runs at full occupancy and the point loop only loads a 16-byte record per group:
+//   x = cand (bits 0-23) | skin skip bits << 24      y = cut      z, w = starts (3 x 16 bits) | first << 16 in w
 struct GroupParams {
   const HotModel* hot;
   const F4* geo_f4;
   const uint32_t* geo_u32;
-  int geo_f4_n, geo_u32_n;
   const double* tab;       // [C][tab_len]
   const float4* grp;       // group balls
   const long long* frames; // as CostParams
@@ -359,12 +346,10 @@ struct GroupParams {
   uint4* rec;              // [C][rec_stride]
   long long rec_stride;
   int groups_per_block;
-  int want_feat, want_cull;
+  int exact, want_cull;
 };
 constexpr int GBLOCK = 256;
-__host__ __device__ inline size_t group_smem(int geo_f4_n, int geo_u32_n, int tabf_len) {
-  return align16(sizeof(HotModel)) + align16(sizeof(F4) * (size_t)geo_f4_n) + align16(sizeof(uint32_t) * (size_t)geo_u32_n) + align16(sizeof(float) * (size_t)(tabf_len > 0 ? tabf_len : 4));
-}
+__host__ __device__ inline size_t group_smem(int tabf_len) { return align16(sizeof(HotModel)) + align16(sizeof(float) * (size_t)(tabf_len > 0 ? tabf_len : 4)); }
 __global__ void __launch_bounds__(GBLOCK, 2) group_kernel(const GroupParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x, c = blockIdx.x;
@@ -374,29 +359,23 @@ __global__ void __launch_bounds__(GBLOCK, 2) group_kernel(const GroupParams p) {
   if (b0 >= g1) return;
   long long b1 = b0 + p.groups_per_block; if (b1 > g1) b1 = g1;
   const HotModel* hot_g = p.hot;
-  size_t o = 0;
-  HotModel* Hs = reinterpret_cast<HotModel*>(smem); o = align16(sizeof(HotModel));
-  F4* f4s = reinterpret_cast<F4*>(smem + o); o += align16(sizeof(F4) * (size_t)p.geo_f4_n);
-  uint32_t* u32s = reinterpret_cast<uint32_t*>(smem + o); o += align16(sizeof(uint32_t) * (size_t)p.geo_u32_n);
-  float* tabf = reinterpret_cast<float*>(smem + o);
+  HotModel* Hs = reinterpret_cast<HotModel*>(smem);
+  float* tabf = reinterpret_cast<float*>(smem + align16(sizeof(HotModel)));
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(hot_g);
     uint32_t* dst = reinterpret_cast<uint32_t*>(Hs);
     for (int i = tid; i < (int)(sizeof(HotModel) / 4); i += GBLOCK) dst[i] = src[i];
-    const float4* s4 = reinterpret_cast<const float4*>(p.geo_f4);
-    float4* d4 = reinterpret_cast<float4*>(f4s);
-    for (int i = tid; i < p.geo_f4_n; i += GBLOCK) d4[i] = __ldg(s4 + i);
-    for (int i = tid; i < p.geo_u32_n; i += GBLOCK) u32s[i] = __ldg(p.geo_u32 + i);
     tabf_fill(*hot_g, p.tab + (size_t)c * hot_g->tab_len, tabf, tid, GBLOCK);
   }
   __syncthreads();
   const HotModel& H = *Hs;
-  GeoView G; G.f4 = p.geo_f4_n > 0 ? f4s : p.geo_f4; G.u32 = p.geo_u32_n > 0 ? u32s : p.geo_u32; G.grid_pool = nullptr;
+  GeoView G; G.f4 = p.geo_f4; G.u32 = p.geo_u32; G.grid_pool = nullptr;
   uint4* out = p.rec + (size_t)c * p.rec_stride - g0;
   for (long long g = b0 + tid; g < b1; g += GBLOCK) {
     const float4 gb = __ldg(p.grp + g);
-    const GroupPre gp = group_prepass(H, G, tabf, gb.x, gb.y, gb.z, gb.w, p.want_feat != 0, p.want_cull != 0);
-    out[g] = make_uint4(gp.cand, __float_as_uint(gp.cut), gp.feat, (unsigned)(((gp.first < 0 ? 255 : gp.first) << 8) | gp.skip));
+    const GroupPre gp = group_prepass(H, G, tabf, gb.x, gb.y, gb.z, gb.w, p.exact != 0, p.want_cull != 0);
+    out[g] = make_uint4((gp.cand & 0xffffffu) | (gp.skip << 24), __float_as_uint(gp.cut), (unsigned)(gp.starts & 0xffffffffull),
+                        (unsigned)((gp.starts >> 32) & 0xffffull) | ((unsigned)(gp.first < 0 ? 255 : gp.first) << 16));
   }
 }
 
@@ -417,8 +396,8 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   // every block re-derives the layout from the same numbers the host used
   const HotModel* hot_g = p.hot;
   const int tab_len = hot_g->tab_len, acc_len = hot_g->acc_len, n_convex = hot_g->n_convex;
-  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, tab_len, acc_len, hot_g->tabf_len, GRAD && hot_g->n_skins > 0, CWARPS);
-  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab + (size_t)c * tab_len, tab_len, CBLOCK);
+  const SmemLayout L = smem_layout(tab_len, acc_len, hot_g->tabf_len, GRAD && hot_g->n_skins > 0, CWARPS);
+  stage_block(smem, L, hot_g, p.tab + (size_t)c * tab_len, tab_len, CBLOCK);
   double* acc_w = reinterpret_cast<double*>(smem + L.off_acc) + (size_t)warp * acc_len;
 #ifdef FLASH_DYN_GROUPS
   __shared__ int s_next_v;
@@ -429,8 +408,8 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   __syncthreads();
   const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
   GeoView G;
-  G.f4 = p.geo_f4_n > 0 ? reinterpret_cast<const F4*>(smem + L.off_f4) : p.geo_f4;
-  G.u32 = p.geo_u32_n > 0 ? reinterpret_cast<const uint32_t*>(smem + L.off_u32) : p.geo_u32;
+  G.f4 = p.geo_f4;
+  G.u32 = p.geo_u32;
   G.grid_pool = p.grid_pool;
   const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
   const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
@@ -450,11 +429,7 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   // which 11 warps waited for the slowest one, which is what the per-batch barrier of the static schedule was
   // (expensively) bounding; see DESIGN.md 5.
   const int ngroups = (int)((tile1 - tile0 + 31) >> 5);
-  // Group records (group_kernel, one thread per group and configuration, run before this kernel):
-  //   x = cand    hulls that can be the minimum for some point of the group's ball
-  //   y = cut     upper bound of the group's minimum, the hull scans' cutoff when a skin is skipped
-  //   z = feat    certified closest feature of hull `first` for the whole ball (hull_ball_feature), 0 = none
-  //   w = first << 8 | skin skip bits   (first = 255: none)
+  // group records (group_kernel, run before this kernel; layout there)
   const bool grp_pre = !DIST && p.rec != nullptr;
   const uint4* rec = grp_pre ? p.rec + (size_t)c * p.rec_stride + ((tile0 - range0) >> 5) : nullptr;
   int g = 0;
@@ -487,31 +462,21 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     e.d = 0.f; e.arg = -1; e.slot = -1; e.is_skin = 0;
     e.y = f3(0.f, 0.f, 0.f); e.n = f3(0.f, 0.f, 0.f);   // lanes past the tile end must contribute exact zeros
     float px = 0.f, py = 0.f, pz = 0.f;
-    // hulls that can be the minimum for some point of this warp's 32 Morton neighbours: lane j bounds hull j
+    // hulls that can be the minimum for some point of this warp's 32 neighbours, from the group's record
     unsigned cand = all_convex; int first = -1;
-    unsigned skin_skip = 0u; float cut0 = 3.0e38f; unsigned feat = 0u;
+    unsigned skin_skip = 0u; float cut0 = 3.0e38f; unsigned long long starts = 0ull;
 #ifdef FLASH_DYN_GROUPS
     if (grp_pre) {
       const uint4 r = __ldg(rec + gcur);
-      cand = r.x; cut0 = __uint_as_float(r.y); feat = r.z;
-      first = (r.w >> 8) == 255u ? -1 : (int)(r.w >> 8);
-      skin_skip = r.w & 255u;
-    } else
-#endif
-    if (!DIST && p.grp != nullptr && n_convex > 1 && wbase < tile1) {   // (a warp past the tile end has no points and no group)
-      const float4 gb = __ldg(p.grp + (wbase >> 5));
-      float lbv = 3.0e38f, ubv = 3.0e38f;
-      if (lane < n_convex) hull_ball_bounds(H.cvx[lane], tabf + 12 * lane, gb.x, gb.y, gb.z, gb.w, lbv, ubv);
-      const float min_ub = from_ordered_int(__reduce_min_sync(0xffffffffu, ordered_int(ubv)));
-      const bool is_cand = lane < n_convex && lbv <= min_ub;
-      cand = __ballot_sync(0xffffffffu, is_cand);
-      first = __reduce_min_sync(0xffffffffu, is_cand ? ((ordered_int(lbv) & ~31) | lane) : 0x7fffffff) & 31;
-      if (cand == 0u) { cand = all_convex; first = -1; }   // only with non-finite bounds
+      cand = r.x & 0xffffffu; skin_skip = r.x >> 24; cut0 = __uint_as_float(r.y);
+      starts = (unsigned long long)r.z | ((unsigned long long)(r.w & 0xffffu) << 32);
+      first = (r.w >> 16) == 255u ? -1 : (int)(r.w >> 16);
     }
+#endif
     if (valid) {
       const float4 P = __ldg(p.pts + i);
       px = P.x; py = P.y; pz = P.z;
-      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, cand, first, p.use_grid != 0, true, e, skin_skip, cut0, feat);
+      eval_point(H, G, tab, tabf, (double)px, (double)py, (double)pz, cand, first, p.use_grid != 0, true, e, skin_skip, cut0, starts);
     }
     if (DIST) {
       if (valid) {
@@ -949,7 +914,6 @@ struct RayParams {
   const F4* geo_f4;
   const uint32_t* geo_u32;
   const float* grid_pool;
-  int geo_f4_n, geo_u32_n;
   const double* tab;      // config 0
   const double* rays;     // [R][3]
   long long R;
@@ -970,13 +934,13 @@ __global__ void __launch_bounds__(BLOCK, 2) raycast_kernel(const RayParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x;
   const HotModel* hot_g = p.hot;
-  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, hot_g->tab_len, 0, hot_g->tabf_len, false);
-  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab, hot_g->tab_len);
+  const SmemLayout L = smem_layout(hot_g->tab_len, 0, hot_g->tabf_len, false);
+  stage_block(smem, L, hot_g, p.tab, hot_g->tab_len);
   __syncthreads();
   const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
   GeoView G;
-  G.f4 = p.geo_f4_n > 0 ? reinterpret_cast<const F4*>(smem + L.off_f4) : p.geo_f4;
-  G.u32 = p.geo_u32_n > 0 ? reinterpret_cast<const uint32_t*>(smem + L.off_u32) : p.geo_u32;
+  G.f4 = p.geo_f4;
+  G.u32 = p.geo_u32;
   G.grid_pool = p.grid_pool;
   const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
   const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
@@ -1154,7 +1118,7 @@ __global__ void bake_grid_kernel(const HotModel* __restrict__ hot, const F4* __r
   F3 y = f3(C.g_org[0] + ix * h, C.g_org[1] + iy * h, C.g_org[2] + iz * h);
   F3 n3;
   GeoView G; G.f4 = geo_f4; G.u32 = geo_u32; G.grid_pool = nullptr;
-  pool[C.g_off + i] = hull_sd(hull_view(G, C), y, 3.0e38f, n3);
+  pool[C.g_off + i] = hull_sd(hull_view(G, C), y, n3);
 }
 // max |trilinear - exact| over cell centres (the worst place for trilinear interpolation)
 __global__ void grid_error_kernel(const HotModel* __restrict__ hot, const F4* __restrict__ geo_f4, const uint32_t* __restrict__ geo_u32, int j,
@@ -1170,7 +1134,7 @@ __global__ void grid_error_kernel(const HotModel* __restrict__ hot, const F4* __
     F3 y = f3(C.g_org[0] + (ix + 0.5f) * h, C.g_org[1] + (iy + 0.5f) * h, C.g_org[2] + (iz + 0.5f) * h);
     F3 n3, n4; float dg;
     GeoView G; G.f4 = geo_f4; G.u32 = geo_u32; G.grid_pool = nullptr;
-    float de = hull_sd(hull_view(G, C), y, 3.0e38f, n3);
+    float de = hull_sd(hull_view(G, C), y, n3);
     if (grid_sd(C, pool, y, dg, n4)) err = fabsf(dg - de);
   }
   err = fmaxf(err, __shfl_xor_sync(0xffffffffu, err, 16));
@@ -1192,7 +1156,6 @@ struct GridParams {
   const HotModel* hot;
   const F4* geo_f4;
   const uint32_t* geo_u32;
-  int geo_f4_n, geo_u32_n;
   const double* tab;      // config 0
   double org[3]; double h; int dim[3];
   int surface;            // surface index, or < 0 for skin(state) = min over all
@@ -1201,13 +1164,13 @@ struct GridParams {
 __global__ void __launch_bounds__(BLOCK, 2) field_grid_kernel(const GridParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const HotModel* hot_g = p.hot;
-  const SmemLayout L = smem_layout(p.geo_f4_n, p.geo_u32_n, hot_g->tab_len, 0, hot_g->tabf_len, false);
-  stage_block(smem, L, hot_g, p.geo_f4, p.geo_f4_n, p.geo_u32, p.geo_u32_n, p.tab, hot_g->tab_len);
+  const SmemLayout L = smem_layout(hot_g->tab_len, 0, hot_g->tabf_len, false);
+  stage_block(smem, L, hot_g, p.tab, hot_g->tab_len);
   __syncthreads();
   const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
   GeoView G;
-  G.f4 = p.geo_f4_n > 0 ? reinterpret_cast<const F4*>(smem + L.off_f4) : p.geo_f4;
-  G.u32 = p.geo_u32_n > 0 ? reinterpret_cast<const uint32_t*>(smem + L.off_u32) : p.geo_u32;
+  G.f4 = p.geo_f4;
+  G.u32 = p.geo_u32;
   G.grid_pool = nullptr;
   const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
   const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
@@ -1230,7 +1193,7 @@ __global__ void __launch_bounds__(BLOCK, 2) field_grid_kernel(const GridParams p
         v = skin_eval(c, c + 3 * H.skin[k].npts, H.skin[k].npts, H.normalize != 0, px, py, pz).s;
       }
     for (int j = 0; j < H.n_convex; ++j)
-      if (H.cvx[j].surface == p.surface) { F3 nn; v = (double)hull_sd(hull_view(G, H.cvx[j]), to_geometry(tab + 12 * j, px, py, pz), 3.0e38f, nn); }
+      if (H.cvx[j].surface == p.surface) { F3 nn; v = (double)hull_sd(hull_view(G, H.cvx[j]), to_geometry(tab + 12 * j, px, py, pz), nn); }
   }
   p.field[i] = (float)v;
 }

@@ -95,7 +95,7 @@ struct flash_ctx {
   double* h_pin = nullptr; size_t cap_pin = 0;  // pinned staging for X / cost / grad
   int32_t* d_argmin = nullptr; size_t cap_argmin = 0;
   uint4* d_rec = nullptr; size_t cap_rec = 0;   // group records of group_kernel, [C][rec_stride]
-  bool features = false;   // exact narrow phase at the ball centre in group_kernel (tighter group bound): off by default, see flash_dev.h eval_point
+  bool exact_groups = true;   // group_kernel evaluates the candidate hulls exactly at the ball centre (flash_dev.h group_prepass)
   // query scratch (skin_eval / raycast)
   double* d_qd = nullptr; size_t cap_qd = 0;
   int* d_qi = nullptr; size_t cap_qi = 0;
@@ -111,16 +111,6 @@ struct flash_ctx {
 };
 
 namespace {
-
-// geometry blob elements the kernels copy into shared memory: everything for the GJK path (plane hints, support maps),
-// nothing for the BSP path (the closest-feature trees are read from global memory through L1)
-#ifdef FLASH_GJK_PATH
-#define STAGE_F4(M) ((M).geo_f4)
-#define STAGE_U32(M) ((M).geo_u32)
-#else
-#define STAGE_F4(M) 0
-#define STAGE_U32(M) 0
-#endif
 
 #define CU(call)                                                                                   \
   do {                                                                                             \
@@ -173,7 +163,7 @@ int ensure_batch(flash_ctx* ctx, int C) {
 
 SmemLayout cost_layout(const flash_ctx* ctx, bool grad) {
   const ModelC& M = ctx->hm.M;
-  return smem_layout(STAGE_F4(M), STAGE_U32(M), M.tab_len, M.acc_len, M.tabf_len, grad && M.n_skins > 0, CWARPS);
+  return smem_layout(M.tab_len, M.acc_len, M.tabf_len, grad && M.n_skins > 0, CWARPS);
 }
 
 template <bool G, bool A, bool D>
@@ -218,14 +208,14 @@ int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride) {
   const long long G = (n_tile + 31) / 32;
   int rc = ensure(ctx, ctx->d_rec, ctx->cap_rec, (size_t)C * (size_t)G); if (rc) return rc;
   GroupParams g;
-  g.hot = ctx->d_hot; g.geo_f4 = ctx->d_geo_f4; g.geo_u32 = ctx->d_geo_u32; g.geo_f4_n = STAGE_F4(M); g.geo_u32_n = STAGE_U32(M);
+  g.hot = ctx->d_hot; g.geo_f4 = ctx->d_geo_f4; g.geo_u32 = ctx->d_geo_u32;
   g.tab = ctx->d_tab; g.grp = P.d_grp; g.frames = cfg_per_frame > 0 ? P.d_frames : nullptr; g.cfg_per_frame = cfg_per_frame > 0 ? cfg_per_frame : 1;
   g.n_groups = G; g.rec = ctx->d_rec; g.rec_stride = G;
   long long gpb = (G * C + (long long)ctx->sm_count * 4 - 1) / ((long long)ctx->sm_count * 4);
   gpb = std::min<long long>(std::max<long long>(((gpb + GBLOCK - 1) / GBLOCK) * GBLOCK, GBLOCK), 8 * GBLOCK);
   g.groups_per_block = (int)gpb;
-  g.want_feat = (ctx->features && !ctx->use_grid) ? 1 : 0; g.want_cull = 1;
-  const size_t smem = group_smem(STAGE_F4(M), STAGE_U32(M), M.tabf_len);
+  g.exact = (ctx->exact_groups && !ctx->use_grid) ? 1 : 0; g.want_cull = 1;
+  const size_t smem = group_smem(M.tabf_len);
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   group_kernel<<<dim3((unsigned)C, (unsigned)((G + gpb - 1) / gpb)), GBLOCK, smem, ctx->stream>>>(g);
   CU(cudaGetLastError());
@@ -243,7 +233,6 @@ int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin, int cfg_per_fr
   CostParams p;
   p.rec = rec_stride > 0 ? ctx->d_rec : nullptr; p.rec_stride = rec_stride;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
-  p.geo_f4_n = STAGE_F4(M); p.geo_u32_n = STAGE_U32(M);
   p.pts = P.d_pts; p.n_pts = P.n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = d_argmin; p.dist = nullptr; p.perm = P.perm_on ? P.d_perm : nullptr;
   p.grp = P.grp_on && ctx->group_cull ? P.d_grp : nullptr;
   p.frames = cfg_per_frame > 0 ? P.d_frames : nullptr; p.cfg_per_frame = cfg_per_frame > 0 ? cfg_per_frame : 1;
@@ -547,7 +536,7 @@ int flash_model_create(const flash_model_desc* desc, const flash_options* opt, f
   make_hot(ctx->hm.M, ctx->hot);
   if (const char* e = getenv("FLASHSDF_NO_SORT")) ctx->sort_points = !(e[0] == '1');
   if (const char* e = getenv("FLASHSDF_NO_GROUP_CULL")) ctx->group_cull = !(e[0] == '1');
-  if (const char* e = getenv("FLASHSDF_FEATURES")) ctx->features = (e[0] == '1');
+  if (const char* e = getenv("FLASHSDF_NO_EXACT_GROUPS")) ctx->exact_groups = !(e[0] == '1');
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0) {
@@ -786,7 +775,6 @@ int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t 
   ctx->launches++; ctx->last.launches++;
   CostParams p;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
-  p.geo_f4_n = STAGE_F4(M); p.geo_u32_n = STAGE_U32(M);
   p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr; p.frames = nullptr; p.cfg_per_frame = 1; p.rec = nullptr; p.rec_stride = 0;
   p.pts_per_block = choose_tile(ctx, n, 1); p.use_grid = ctx->use_grid ? 1 : 0;
   const int tiles = (int)((n + p.pts_per_block - 1) / p.pts_per_block);
@@ -822,10 +810,10 @@ int flash_raycast(flash_ctx* ctx, const double* x, const double* rays, int64_t R
   CU(cudaMemcpyAsync(d_rays, rays, (size_t)R * 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   RayParams p;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
-  p.geo_f4_n = STAGE_F4(M); p.geo_u32_n = STAGE_U32(M); p.tab = ctx->d_tab; p.rays = d_rays; p.R = R;
+  p.tab = ctx->d_tab; p.rays = d_rays; p.R = R;
   for (int i = 0; i < 12; ++i) p.cam[i] = cam[i];
   p.depths = d_depths; p.block_hits = ctx->d_qi; p.use_grid = ctx->use_grid ? 1 : 0;
-  const size_t smem = smem_layout(STAGE_F4(M), STAGE_U32(M), M.tab_len, 0, M.tabf_len, false).total;
+  const size_t smem = smem_layout(M.tab_len, 0, M.tabf_len, false).total;
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(raycast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[1], ctx->stream));
   raycast_kernel<<<nblocks, BLOCK, smem, ctx->stream>>>(p);
@@ -935,9 +923,9 @@ int flash_contour_mesh(flash_ctx* ctx, const double* x, int32_t surface, const d
   float* d_field = (float*)ctx->d_qd;
   unsigned long long* d_cnt = (unsigned long long*)(ctx->d_qd + off_cnt);
   float* d_tri = (float*)(ctx->d_qd + off_tri);
-  g.hot = ctx->d_hot; g.geo_f4 = ctx->d_geo_f4; g.geo_u32 = ctx->d_geo_u32; g.geo_f4_n = STAGE_F4(M); g.geo_u32_n = STAGE_U32(M);
+  g.hot = ctx->d_hot; g.geo_f4 = ctx->d_geo_f4; g.geo_u32 = ctx->d_geo_u32;
   g.tab = ctx->d_tab; g.h = spacing; g.surface = surface; g.field = d_field;
-  const size_t smem = smem_layout(STAGE_F4(M), STAGE_U32(M), M.tab_len, 0, M.tabf_len, false).total;
+  const size_t smem = smem_layout(M.tab_len, 0, M.tabf_len, false).total;
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(field_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   field_grid_kernel<<<(unsigned)((nodes + BLOCK - 1) / BLOCK), BLOCK, smem, ctx->stream>>>(g);
   CU(cudaGetLastError());

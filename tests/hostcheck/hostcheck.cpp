@@ -16,10 +16,8 @@ using namespace flashhost;
 struct HC { HostModel hm; HotModel hot; };
 static int g_group_cull = 1;            // replay the warp-level hull culling of cost_kernel
 static int g_skin_cull = 1;             // ... and the group-level skin cull
-static int g_feat = 1;                  // ... and the group feature certification
-static int g_warm = 1;                  // ... and the GJK warm start from the group's hint
+static int g_exact = 1;                 // ... with exact centre distances and BSP start nodes (group_prepass)
 static int g_dbg = 0;
-static long long g_feat_groups[4] = {0, 0, 0, 0};
 static long long g_skin_groups_skipped = 0;
 static long long g_cand_total = 0, g_groups = 0, g_rounds_or = 0, g_rounds_max = 0;
 static unsigned g_or = 0; static int g_max = 0;
@@ -48,21 +46,6 @@ void hc_convex_info(void* p, int j, int* nverts, int* nplanes, float* lo, float*
   for (int k = 0; k < 3; ++k) { lo[k] = C.lo[k]; hi[k] = C.hi[k]; }
 }
 
-// plane slots of hull j: nplanes_pad floats[4] {nx, ny, nz, -o} (inert padding: n = 0, -o = -1e30) and the
-// hint map (DIRMAP_CELLS entries: group0 | group1 << 8)
-int hc_plane_table(void* p, int j, float* planes /* [nplanes_pad][4] or null */, unsigned short* pgrp /* [DIRMAP_CELLS] or null */) {
-  HC* h = (HC*)p;
-  const ConvexC& C = h->hm.M.cvx[j];
-  const F4* P = h->hm.geo_f4.data() + C.off_planes;
-  if (planes)
-    for (int f = 0; f < C.nplanes_pad; ++f) {
-      const float* a = reinterpret_cast<const float*>(P + (f & ~1)); const int hh = f & 1;
-      planes[4 * f] = a[hh]; planes[4 * f + 1] = a[2 + hh]; planes[4 * f + 2] = a[4 + hh]; planes[4 * f + 3] = a[6 + hh];
-    }
-  if (pgrp) std::memcpy(pgrp, h->hm.geo_u32.data() + C.off_pgrp, DIRMAP_CELLS * sizeof(unsigned short));
-  return C.nplanes_pad;
-}
-
 // prepare kernel, one config
 void hc_prepare(void* p, const double* x, double* tab, double* aux) {
   ModelC& M = ((HC*)p)->hm.M;
@@ -89,7 +72,7 @@ void hc_accumulate(void* p, const double* tab, const float* pts, long long n, in
   tabf_fill(H, tab, tabf, 0, 1);
   const unsigned all_convex = H.n_convex >= 32 ? 0xffffffffu : ((1u << H.n_convex) - 1u);
   unsigned cand = all_convex; int first = -1;
-  unsigned skin_skip = 0u; float cut0 = 3.0e38f; unsigned feat = 0u;
+  unsigned skin_skip = 0u; float cut0 = 3.0e38f; unsigned long long starts = 0ull;
   for (long long i = 0; i < n; ++i) {
     if (g_group_cull && (i & 31) == 0 && H.n_convex > 1) {
       // the warp's 32 points: bounding ball as flash_ingest.cuh warp_ball computes it (Badoiu-Clarkson from the centroid)
@@ -110,19 +93,17 @@ void hc_accumulate(void* p, const double* tab, const float* pts, long long n, in
         cx = fmaf(pts[3 * (i + who)] - cx, sgl, cx); cy = fmaf(pts[3 * (i + who) + 1] - cy, sgl, cy); cz = fmaf(pts[3 * (i + who) + 2] - cz, sgl, cz);
       }
       const float rho = sqrtf(fmaxf(mm, 0.f)) * (1.f + 2e-6f) + 1e-30f;
-      const GroupPre gp = group_prepass(H, G, tabf, cx, cy, cz, rho, g_feat != 0, g_skin_cull != 0);
-      cand = gp.cand; first = gp.first; skin_skip = gp.skip; cut0 = gp.cut; feat = gp.feat;
+      const GroupPre gp = group_prepass(H, G, tabf, cx, cy, cz, rho, g_exact != 0 && !use_grid, g_skin_cull != 0);
+      cand = gp.cand; first = gp.first; skin_skip = gp.skip; cut0 = gp.cut; starts = gp.starts;
       g_cand_total += __builtin_popcount(cand); g_groups += 1;
       g_skin_groups_skipped += skin_skip ? 1 : 0;
-      if (!g_warm && !(feat & FEAT_CERT)) feat = 0u;
-      g_feat_groups[(feat & FEAT_CERT) ? (feat & 3u) : 0u] += 1;
-      if (g_dbg) printf("group %lld first %d feat %08x cand %x rho %g c %g %g %g\n", i / 32, first, feat, cand, rho, cx, cy, cz);
+      if (g_dbg) printf("group %lld first %d starts %llx cand %x rho %g c %g %g %g\n", i / 32, first, starts, cand, rho, cx, cy, cz);
     }
     PointEval e;
 #ifdef FLASH_COUNTERS
     counters().exact_mask = 0u;
 #endif
-    eval_point(H, G, tab, tabf, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], cand, first, use_grid != 0, true, e, skin_skip, cut0, feat);
+    eval_point(H, G, tab, tabf, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2], cand, first, use_grid != 0, true, e, skin_skip, cut0, starts);
 #ifdef FLASH_COUNTERS
     // exact narrow-phase rounds a warp of 32 consecutive points executes: one per hull ANY lane evaluates (the
     // kernel's candidate loop is warp-uniform) vs the most any single lane needs
@@ -162,11 +143,8 @@ void hc_epilogue(void* p, const double* x, const double* tab, const double* aux,
 
 void hc_set_group_cull(int on) { g_group_cull = on; }
 void hc_set_skin_cull(int on) { g_skin_cull = on; }
-void hc_set_feature(int on) { g_feat = on; }
-void hc_set_warm(int on) { g_warm = on; }
+void hc_set_exact(int on) { g_exact = on; }
 void hc_set_dbg(int on) { g_dbg = on; }
-// groups by certified feature type: none, vertex, edge, face
-void hc_feature_stats(long long* out, int reset) { for (int k = 0; k < 4; ++k) { out[k] = g_feat_groups[k]; if (reset) g_feat_groups[k] = 0; } }
 long long hc_skin_groups_skipped(int reset) { long long v = g_skin_groups_skipped; if (reset) g_skin_groups_skipped = 0; return v; }
 // certified lower bound of skin k over a ball (tab = prepared fp64 table of one config)
 float hc_skin_ball_lower(void* p, const double* tab, int k, float cx, float cy, float cz, float rho) {
@@ -185,11 +163,10 @@ void hc_round_stats(long long* out, int reset) { out[0] = g_rounds_or; out[1] = 
 void hc_counters(long long* out, int reset) {
 #ifdef FLASH_COUNTERS
   Counters& c = counters();
-  out[0] = c.points; out[1] = c.narrow; out[2] = c.inside; out[3] = c.gjk_iters; out[4] = c.plane_tests; out[5] = c.vert_tests; out[6] = c.lb_tests; out[7] = c.skin64;
-  out[8] = c.feat_evals; out[9] = c.warm;
-  if (reset) c = Counters{0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0u};
+  out[0] = c.points; out[1] = c.narrow; out[2] = c.lb_tests; out[3] = c.skin64; out[4] = c.bsp_levels;
+  if (reset) c = Counters{0, 0, 0, 0, 0, 0u};
 #else
-  for (int i = 0; i < 10; ++i) out[i] = -1;
+  for (int i = 0; i < 5; ++i) out[i] = -1;
 #endif
 }
 
@@ -208,19 +185,6 @@ void hc_skin_bound(void* p, int k, const double* tab, const float* pts, long lon
   }
 }
 
-// support vertex for directions q[n][3] of convex slot j: from the direction map and from the full scan
-void hc_support(void* p, int j, const float* q, long long n, int* iw_map, int* iw_scan, float* val_map, float* val_scan) {
-  HC* h = (HC*)p;
-  const ConvexC& C = h->hm.M.cvx[j];
-  GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
-  const HullView V = hull_view(G, C);
-  for (long long i = 0; i < n; ++i) {
-    const F3 d = f3(q[3 * i], q[3 * i + 1], q[3 * i + 2]);
-    iw_map[i] = hull_support_map(V, d); iw_scan[i] = hull_support_scan(V, d);
-    val_map[i] = dot(d, vert_at(V, iw_map[i])); val_scan[i] = dot(d, vert_at(V, iw_scan[i]));
-  }
-}
-
 // signed distance of geometry-frame points y[n][3] to convex slot j
 void hc_hull_sd(void* p, int j, const float* y, long long n, float* d, float* nrm) {
   HC* h = (HC*)p;
@@ -228,7 +192,7 @@ void hc_hull_sd(void* p, int j, const float* y, long long n, float* d, float* nr
   GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
   for (long long i = 0; i < n; ++i) {
     F3 nn;
-    d[i] = hull_sd(hull_view(G, C), f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]), 3.0e38f, nn);
+    d[i] = hull_sd(hull_view(G, C), f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]), nn);
     nrm[3 * i] = nn.x; nrm[3 * i + 1] = nn.y; nrm[3 * i + 2] = nn.z;
   }
 }
@@ -237,12 +201,11 @@ void hc_hull_sd(void* p, int j, const float* y, long long n, float* d, float* nr
 int hc_hull_sd_bsp(void* p, int j, const float* y, long long n, float* d, float* nrm, int* leaf) {
   HC* h = (HC*)p;
   const ConvexC& C = h->hm.M.cvx[j];
-  if (!C.bsp_on) return 0;
   GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
   const HullView V = hull_view(G, C);
   for (long long i = 0; i < n; ++i) {
     F3 nn; const F3 yy = f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]);
-    const unsigned k = bsp_locate(V.bn, V.bk, yy);
+    const unsigned k = bsp_locate(V, 0u, yy);
     d[i] = bsp_feature_sd(V, k, yy, nn);
     nrm[3 * i] = nn.x; nrm[3 * i + 1] = nn.y; nrm[3 * i + 2] = nn.z;
     if (leaf) leaf[i] = (int)k;
@@ -272,17 +235,3 @@ void hc_bsp_depth(void* p, int j, const float* y, long long n, int* depth) {
 
 }  // extern "C"
 
-// GJK warm-started from every possible hint simplex of hull j against the cold start (debugging aid + test)
-extern "C" void hc_hull_warm(void* p, int j, const float* y, long long n, const int* ids /* [n][3], -1 = unused */, float* d, int* ok) {
-  HC* h = (HC*)p;
-  const ConvexC& C = h->hm.M.cvx[j];
-  GeoView G; G.f4 = h->hm.geo_f4.data(); G.u32 = h->hm.geo_u32.data(); G.grid_pool = nullptr;
-  const HullView V = hull_view(G, C);
-  for (long long i = 0; i < n; ++i) {
-    Simplex S; S.ns = 0; S.ia = S.ib = S.ic = 0;
-    for (int k = 0; k < 3; ++k) if (ids[3 * i + k] >= 0) { if (S.ns == 0) S.ia = ids[3 * i + k]; else if (S.ns == 1) S.ib = ids[3 * i + k]; else S.ic = ids[3 * i + k]; ++S.ns; }
-    F3 nn; float dd = 0.f;
-    ok[i] = hull_sd_warm(V, feat_hint(S), f3(y[3 * i], y[3 * i + 1], y[3 * i + 2]), dd, nn) ? 1 : 0;
-    d[i] = dd;
-  }
-}

@@ -48,12 +48,10 @@ def lib():
         L.hc_bsp_stats.argtypes = [vp, C.c_int, c_double_p]; L.hc_bsp_stats.restype = None
         L.hc_bsp_depth.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_int32_p]; L.hc_bsp_depth.restype = None
         L.hc_skin_bound.argtypes = [vp, C.c_int, c_double_p, c_float_p, C.c_longlong, c_float_p, c_float_p, c_double_p]; L.hc_skin_bound.restype = None
-        L.hc_support.argtypes = [vp, C.c_int, c_float_p, C.c_longlong, c_int32_p, c_int32_p, c_float_p, c_float_p]; L.hc_support.restype = None
         L.hc_set_group_cull.argtypes = [C.c_int]; L.hc_set_group_cull.restype = None
         L.hc_group_stats.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_group_stats.restype = None
         L.hc_set_skin_cull.argtypes = [C.c_int]; L.hc_set_skin_cull.restype = None
-        L.hc_set_feature.argtypes = [C.c_int]; L.hc_set_feature.restype = None
-        L.hc_feature_stats.argtypes = [C.POINTER(C.c_longlong), C.c_int]; L.hc_feature_stats.restype = None
+        L.hc_set_exact.argtypes = [C.c_int]; L.hc_set_exact.restype = None
         L.hc_skin_groups_skipped.argtypes = [C.c_int]; L.hc_skin_groups_skipped.restype = C.c_longlong
         L.hc_skin_ball_lower.argtypes = [vp, c_double_p, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float]; L.hc_skin_ball_lower.restype = C.c_float
         _lib = L
@@ -119,13 +117,6 @@ class HostCheck:
         c = np.asarray(centre, np.float32)
         return float(lib().hc_skin_ball_lower(self.h, tab.ctypes.data_as(c_double_p), k, float(c[0]), float(c[1]), float(c[2]), float(np.float32(rho))))
 
-    def support(self, j, q):
-        q = np.ascontiguousarray(q, np.float32).reshape(-1, 3)
-        im = np.empty(len(q), np.int32); isc = np.empty(len(q), np.int32); vm = np.empty(len(q), np.float32); vs = np.empty(len(q), np.float32)
-        lib().hc_support(self.h, j, q.ctypes.data_as(c_float_p), len(q), im.ctypes.data_as(c_int32_p), isc.ctypes.data_as(c_int32_p),
-                         vm.ctypes.data_as(c_float_p), vs.ctypes.data_as(c_float_p))
-        return im, isc, vm, vs
-
     def hull_sd(self, j, y):
         y = np.ascontiguousarray(y, np.float32).reshape(-1, 3)
         d = np.empty(len(y), np.float32); n = np.empty((len(y), 3), np.float32)
@@ -152,9 +143,9 @@ class HostCheck:
 
 
 def counters(reset=True):
-    out = (C.c_longlong * 10)()
+    out = (C.c_longlong * 5)()
     lib().hc_counters(out, 1 if reset else 0)
-    return dict(zip(("points", "narrow", "inside", "gjk_iters", "plane_tests", "vert_tests", "lb_tests", "skin64", "feat_evals", "warm"), list(out)))
+    return dict(zip(("points", "narrow", "lb_tests", "skin64", "bsp_levels"), list(out)))
 
 
 def set_group_cull(on):
@@ -165,14 +156,9 @@ def set_skin_cull(on):
     lib().hc_set_skin_cull(1 if on else 0)
 
 
-def set_feature(on):
-    lib().hc_set_feature(1 if on else 0)
-
-
-def feature_stats(reset=True):
-    out = (C.c_longlong * 4)()
-    lib().hc_feature_stats(out, 1 if reset else 0)
-    return dict(zip(("none", "vertex", "edge", "face"), list(out)))
+def set_exact(on):
+    """exact centre distances + BSP start nodes in the group pre-pass (group_prepass) on / off"""
+    lib().hc_set_exact(1 if on else 0)
 
 
 def skin_groups_skipped(reset=True):

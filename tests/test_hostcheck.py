@@ -126,23 +126,23 @@ def test_warp_group_culling_changes_nothing_and_culls():
     pts = rng.uniform([-0.4, -0.3, 0.0], [0.6, 0.3, 0.3], (1_200_000, 3)).astype(np.float32)
     pts = _morton_sorted(pts, bits=6)[: 32 * 3000]
     try:
-        hl.set_feature(False)                      # culling alone: bit-identical
+        hl.set_exact(False)                        # culling alone (no start nodes): bit-identical
         hl.set_group_cull(False)
         a0, d0, g0 = h.accumulate(tab, pts)
         hl.set_group_cull(True); hl.group_stats()
         a1, d1, g1 = h.accumulate(tab, pts)
         st = hl.group_stats()
     finally:
-        hl.set_feature(True); hl.set_group_cull(True)
+        hl.set_exact(True); hl.set_group_cull(True)
     assert np.array_equal(d0, d1) and np.array_equal(g0, g1) and np.array_equal(a0, a1)
     assert st["groups"] == 3000 and st["candidates"] / st["groups"] < 5.0   # 8 hulls in the model
 
 
-def test_group_feature_certification_is_exact_and_fires():
-    """hull_ball_feature: groups whose bounding ball lies in the Voronoi region of one FACE of the nearest hull
-    evaluate that hull by the plane's closed form; groups entirely outside it start every point's GJK from the simplex
-    found at the ball centre (hull_sd_warm).  Same distances as the cold GJK path to fp32 rounding (and as the fp64
-    oracle), same argmin; the exact centre distance also tightens the group's hull and skin culls."""
+def test_group_exact_prepass_and_bsp_start_nodes_change_nothing():
+    """group_prepass with exact centre distances: tighter candidate sets than the AABB bounds, and every point
+    finishes its BSP descent from the group's start node (bsp_descend_ball) -- same distances as a descent from the
+    root to fp32 rounding (a point within rounding distance of a cell boundary may take the neighbouring cell), same
+    argmin as the fp64 oracle, far fewer levels per point."""
     rng = np.random.default_rng(12)
     m = flash.models.irb_and_squishable()
     h = hl.HostCheck(m)
@@ -157,21 +157,25 @@ def test_group_feature_certification_is_exact_and_fires():
     pts = np.concatenate([pts, pts[near][: 32 * (near.sum() // 32)]])
     d_or, a_or = o.skin(x, pts.astype(np.float64), mode=ol.GJK, argmin=True)
     try:
-        hl.set_feature(False)
+        hl.set_exact(False); hl.counters(); hl.group_stats()
         a0, d0, g0 = h.accumulate(tab, pts)
-        hl.set_feature(True); hl.feature_stats(); hl.counters()
+        c0 = hl.counters(); s0 = hl.group_stats()
+        hl.set_exact(True)
         a1, d1, g1 = h.accumulate(tab, pts)
-        fs = hl.feature_stats(); cn = hl.counters()
+        c1 = hl.counters(); s1 = hl.group_stats()
     finally:
-        hl.set_feature(True)
+        hl.set_exact(True)
     assert np.abs(d1 - d0).max() < 3e-7 and np.abs(d1 - d_or).max() < 3e-7
     flips = np.nonzero(g1 != a_or)[0]
     per = np.sort(o.surfaces(x, pts[flips].astype(np.float64), mode=ol.GJK), axis=1) if len(flips) else np.zeros((0, 2))
     assert len(flips) <= 4 and (per[:, 1] - per[:, 0] < 2e-6).all()
     assert np.abs(a1 - a0).max() <= 1e-6 * np.abs(a0).max()
-    assert fs["face"] > 0 and cn["feat_evals"] > 0.02 * cn["points"]
-    assert cn["warm"] > 0.4 * cn["points"]          # most groups are clear of the hulls: warm-started GJK
-    assert cn["narrow"] < 0.6 * cn["points"]        # ... and the cold narrow phase (plane hint, start triangle) is the exception
+    assert s1["candidates"] < 0.8 * s0["candidates"]                  # exact bounds cull more hulls than the AABB bounds
+    assert c1["narrow"] <= c0["narrow"]
+    assert c1["bsp_levels"] / c1["narrow"] < 0.5 * c0["bsp_levels"] / c0["narrow"]   # ... and the descents start deep in the tree
+    print("candidates/group %.2f -> %.2f, narrow/point %.2f -> %.2f, BSP levels/narrow %.1f -> %.1f" % (
+        s0["candidates"] / s0["groups"], s1["candidates"] / s1["groups"], c0["narrow"] / c0["points"], c1["narrow"] / c1["points"],
+        c0["bsp_levels"] / c0["narrow"], c1["bsp_levels"] / c1["narrow"]))
 
 
 @pytest.mark.parametrize("name", ["irb_and_squishable", "squishable", "two_link_arm", "beanbag"])
@@ -232,14 +236,13 @@ def test_group_skin_cull_never_changes_the_result():
     ctr = rng.uniform([-0.8, -0.8, -0.3], [1.0, 0.8, 1.2], (2000, 1, 3))
     pts = np.concatenate([(ctr + rng.uniform(-0.015, 0.015, (2000, 32, 3))).reshape(-1, 3), GOLD["irb_and_squishable/pts"]]).astype(np.float32)
     try:
-        hl.set_feature(False)
         hl.set_skin_cull(True); hl.skin_groups_skipped()
         a1, d1, g1 = h.accumulate(tab, pts)
         skipped = hl.skin_groups_skipped()
         hl.set_skin_cull(False)
         a0, d0, g0 = h.accumulate(tab, pts)
     finally:
-        hl.set_skin_cull(True); hl.set_feature(True)
+        hl.set_skin_cull(True)
     assert np.array_equal(d0, d1) and np.array_equal(g0, g1) and np.array_equal(a0, a1)
     assert skipped > 0.2 * len(pts) / 32
 
@@ -259,28 +262,10 @@ def test_fp32_prefilter_defers_most_fp64_skin_evaluations():
     assert winners <= c["skin64"] <= winners + 0.1 * len(pts)
 
 
-def test_support_direction_map_is_exact():
-    """The cube-map candidate lists must contain the true support vertex for EVERY direction (also on cell
-    borders and cube edges): the map query has to return the same support value as the 56-vertex scan."""
-    rng = np.random.default_rng(8)
-    m = flash.models.irb_and_squishable()
-    h = hl.HostCheck(m)
-    q = rng.standard_normal((200000, 3)).astype(np.float32)
-    # directions exactly on cell borders / cube edges / axes
-    g = np.linspace(-1, 1, 17)
-    U, V = np.meshgrid(g, g)
-    border = np.concatenate([np.stack([np.ones_like(U), U, V], -1).reshape(-1, 3)[:, p] * s for p in ([0, 1, 2], [1, 2, 0], [2, 0, 1]) for s in (1, -1)])
-    q = np.concatenate([q, border.astype(np.float32), np.eye(3, dtype=np.float32), -np.eye(3, dtype=np.float32)])
-    for j in range(h.n_convex):
-        im, isc, vm, vs = h.support(j, q)
-        assert np.array_equal(vm, vs), (j, np.abs(vm - vs).max())
-        assert (im == isc).mean() > 0.999      # differ only on exact ties
-
-
-def test_plane_hint_map_never_changes_the_distance():
-    """hull_plane_hint (flash_dev.h) only picks GJK's start face and rejects by a valid lower bound; the
-    distance must equal the oracle's brute-force point-polytope distance everywhere: hugging the surfaces
-    (ray-cast hits pushed out / in by 1 mm and 1 cm), mid range, and far outside the scene."""
+def test_bsp_distance_equals_brute_force_everywhere():
+    """The closest-feature BSP descent (flash_dev.h hull_sd, trees of flash_bsp.h) must equal the oracle's
+    brute-force point-polytope distance everywhere: hugging the surfaces (points walked onto the zero level set and
+    pushed out / in by 1 mm and 1 cm), mid range, and far outside the scene."""
     rng = np.random.default_rng(12)
     m = flash.models.irb_and_squishable()
     h, o = hl.HostCheck(m), ol.Oracle(m)
@@ -303,45 +288,52 @@ def test_plane_hint_map_never_changes_the_distance():
     per = o.surfaces(x, pts, mode=ol.BRUTE)
     for i in np.nonzero(arg != ao)[0]:
         s = np.sort(per[i]); assert s[1] - s[0] < 4e-6
-    # and it does its job: far fewer plane tests than one full 100-plane scan per narrow-phase evaluation
-    assert cn["plane_tests"] < 45 * cn["narrow"]
+    # one descent costs ~12 plane tests on the 100-face IRB140 hulls
+    assert cn["bsp_levels"] < 16 * cn["narrow"]
 
 
-def test_plane_groups_and_hint_tables_are_well_formed():
-    """flash_host.h cluster_planes / build_plane_hints: every plane sits in exactly one slot, padding slots are
-    inert, the groups are tight clusters of normals, and every hint names existing groups; for a direction cell's
-    centre ray the most-violated plane just outside the hull and one hull radius away is in a hinted group."""
-    import ctypes as C
-    m = flash.models.irb_and_squishable()
-    h = hl.HostCheck(m)
-    L = hl.lib()
-    L.hc_plane_table.restype = C.c_int
-    L.hc_plane_table.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
-    R = 8
-    for j in range(h.n_convex):
-        nv, npl, lo, hi, depth = h.convex_info(j)
-        npad = L.hc_plane_table(h.h, j, None, None)
-        assert npad % 8 == 0 and npl <= npad < npl + 8 * ((npl + 7) // 8)
-        P = np.zeros((npad, 4), np.float32); G = np.zeros(6 * R * R, np.uint16)
-        L.hc_plane_table(h.h, j, P.ctypes.data, G.ctypes.data)
-        real = np.linalg.norm(P[:, :3], axis=1) > 0.5
-        assert real.sum() == npl and (P[~real, 3] < -1e29).all()
-        assert np.allclose(np.linalg.norm(P[real, :3], axis=1), 1.0, atol=1e-5) and (P[real, 3] < 0).all()   # -o < 0: centroid inside
-        ng = npad // 8
-        assert ((G & 255) < ng).all() and ((G >> 8) < ng).all()
-        if npl >= 32:   # clustered: normals of a group lie within a cap much smaller than the sphere
-            spread = [np.min(P[g * 8:(g + 1) * 8][real[g * 8:(g + 1) * 8], :3] @ P[g * 8:(g + 1) * 8][real[g * 8:(g + 1) * 8], :3].mean(0)) for g in range(ng) if real[g * 8:(g + 1) * 8].any()]
-            assert np.median(spread) > 0.6
-        # the cell centres of the +x face
-        hits = 0
-        for iv in range(R):
-            for iu in range(R):
-                d = np.array([1.0, -1 + (2 * iu + 1) / R, -1 + (2 * iv + 1) / R]); d /= np.linalg.norm(d)
-                a = P[:, :3].astype(np.float64) @ d
-                t_exit = np.min(np.where(real & (a > 0), -P[:, 3] / np.maximum(a, 1e-30), np.inf))
-                g = G[(0 * R + iv) * R + iu]
-                for scale in (1.05, 2.0):       # just outside the hull and one hull radius away, along the cell's centre ray
-                    y = scale * t_exit * d
-                    f = int(np.argmax(np.where(real, P[:, :3] @ y + P[:, 3], -np.inf)))
-                    hits += (f // 8) in (int(g & 255), int(g >> 8))
-        assert hits >= 0.6 * 2 * R * R       # a hint, not a guarantee: a miss costs a GJK iteration, never accuracy (70-100 % on these hulls)
+def _one_hull_model(verts):
+    """a convex body fixed to the world (body -1): its geometry frame is the world frame shifted to the centroid"""
+    from flash.core import Mechanism
+    return flash.Manipulator(Mechanism([]), [flash.ConvexGeometry(np.asarray(verts, float), -1)])
+
+
+def test_bsp_trees_on_awkward_hulls():
+    """flash_bsp.h on hulls that stress the builder: coplanar many-vertex faces (prism caps), collinear and interior
+    input points, duplicates, a tetrahedron, a thin slab, a sliver-faced random hull.  Signed distance and gradient
+    from the tree against the oracle's brute-force distance; the trees stay small and shallow."""
+    rng = np.random.default_rng(21)
+    th = np.linspace(0, 2 * np.pi, 24, endpoint=False)
+    ring = np.stack([0.2 * np.cos(th), 0.2 * np.sin(th)], 1)
+    sph = rng.standard_normal((60, 3)); sph /= np.linalg.norm(sph, axis=1, keepdims=True)
+    box = np.array([[x, y, z] for x in (-0.3, 0.3) for y in (-0.2, 0.2) for z in (-0.1, 0.1)])
+    hulls = {
+        "prism24": np.concatenate([np.c_[ring, np.full(24, -0.15)], np.c_[ring, np.full(24, 0.15)]]),
+        "box+interior+collinear": np.concatenate([box, 0.5 * box, [[0.0, 0.2, 0.1], [0.3, 0.0, 0.1], [0.0, 0.0, 0.1]], box[:3]]),
+        "tetrahedron": np.array([[0, 0, 0], [0.4, 0, 0], [0, 0.3, 0], [0, 0, 0.2]]),
+        "slab": np.array([[x, y, z] for x in (-0.5, 0.5) for y in (-0.4, 0.4) for z in (-0.002, 0.002)]),
+        "sphere60": sph * np.array([0.3, 0.2, 0.1]),
+        "cone": np.concatenate([np.c_[ring, np.zeros(24)], [[0, 0, 0.5]]]),
+    }
+    for name, v in hulls.items():
+        m = _one_hull_model(v)
+        h, o = hl.HostCheck(m), ol.Oracle(m)
+        st = h.bsp_stats(0)
+        assert 0 < st["nodes"] < 20000 and st["max_depth"] <= 40, (name, st)
+        ext = np.abs(v).max()
+        pts = np.concatenate([rng.uniform(-1.5, 1.5, (6000, 3)) * ext, rng.uniform(-3, 3, (2000, 3)), v + 1e-3 * rng.standard_normal(v.shape),
+                              (v[rng.integers(0, len(v), 4000)] + v[rng.integers(0, len(v), 4000)]) / 2 + 2e-3 * rng.standard_normal((4000, 3))]).astype(np.float32)
+        x = np.zeros(0)
+        do = o.skin(x, pts.astype(np.float64), mode=ol.BRUTE)
+        nv, npl, lo, hi, db = h.convex_info(0)
+        cen = np.unique(np.round(v, 12), axis=0).mean(0)             # geometry frame = input frame shifted to the vertex centroid
+        d, n, leaf = h.hull_sd_bsp(0, (pts.astype(np.float64) - cen).astype(np.float32))
+        assert np.abs(d - do).max() < 1e-6 * (1 + np.abs(do).max()), (name, np.abs(d - do).max())
+        # gradient: unit length off the surface, and consistent with central differences of the oracle away from the
+        # feature boundaries
+        far = np.abs(do) > 1e-3
+        assert np.allclose(np.linalg.norm(n[far], axis=1), 1.0, atol=1e-4), name
+        eps = 1e-4
+        fd = np.stack([(o.skin(x, pts + eps * e, mode=ol.BRUTE) - o.skin(x, pts - eps * e, mode=ol.BRUTE)) / (2 * eps) for e in np.eye(3)], 1)
+        ok = np.abs(fd - n).max(1) < 2e-2
+        assert ok[far].mean() > 0.95, (name, ok[far].mean())
