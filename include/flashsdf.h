@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define FLASHSDF_ABI_VERSION 1
+#define FLASHSDF_ABI_VERSION 2
 
 typedef struct flash_ctx flash_ctx;
 
@@ -111,7 +111,18 @@ typedef struct flash_options {
   int32_t sdf_mode;                 /* FLASH_SDF_EXACT (default) or FLASH_SDF_GRID */
   double  grid_spacing;             /* metres, grid mode; <=0 -> 0.004 */
   double  grid_margin;              /* metres around each hull's AABB covered by its grid; <=0 -> 0.10 */
-  int32_t reserved[8];
+  /* 1: run-to-run bit-identical results (the reference sums the points in one fixed order, src/gradientdescent.jl:32):
+   * static group -> warp schedule, per-tile partial sums combined in tile order instead of fp64 atomics.  0 (default):
+   * dynamic schedule + atomics, a few per cent faster, sums in a different order every run. */
+  int32_t deterministic;
+  /* Single-process multi-GPU context (the reference's estimate_state is called from ONE Julia process,
+   * src/tracking.jl:8-27): n_devices > 1 makes flash_model_create build one sub-context per entry of devices[]
+   * (CUDA ordinals), each with its own streams, joined by an in-process NCCL communicator.  flash_points_set /
+   * flash_frames_set shard the cloud (frames) over the devices, flash_cost_grad / flash_estimate_state return the
+   * global result, flash_raycast shards the rays.  0 or 1: one device (`device`). */
+  int32_t n_devices;
+  int32_t devices[16];
+  int32_t reserved[6];
 } flash_options;
 
 void flash_options_default(flash_options* opt);

@@ -714,7 +714,11 @@ FLASH_HD GroupPre group_prepass(const HotModel& M, const GeoView& G, const float
   }
   if (exact) {
     const float r = rho * (1.f + 1e-5f) + 1e-5f;   // ball radius + slack for the fp32 transform of the centre
-    for (int j = 0; j < nc; ++j) {
+    // the hull with the smallest AABB bound first: its exact distance usually rules out all the others
+    int j0 = 0;
+    for (int j = 1; j < nc; ++j) if (lb[j] < lb[j0]) j0 = j;
+    for (int t = 0; t < nc; ++t) {
+      const int j = t == 0 ? j0 : (t <= j0 ? t - 1 : t);
       if (lb[j] > min_ub) continue;
       const HullView V = hull_view(G, M.cvx[j]);
       const F3 yc = to_geometry_f32(tabf + 12 * j, cx, cy, cz);

@@ -42,13 +42,10 @@ constexpr int WARPS = BLOCK / 32;
 #define FLASH_CBLOCK 512
 #endif
 constexpr int CBLOCK = FLASH_CBLOCK;
-// groups of 32 points per barrier interval of the dynamic hand-out (cost_kernel); FLASH_STATIC_GROUPS = the static schedule
-#ifndef FLASH_STATIC_GROUPS
-#ifndef FLASH_DYN_GROUPS
-#define FLASH_DYN_GROUPS 1000000   // K5, ms per launch: 24 -> 55.6, 48 -> 55.1, 96 -> 54.7, 252 (= the whole 8064-point tile) -> 54.2; static 55.4-57.4
-#endif
-#endif
 constexpr int CWARPS = CBLOCK / 32;
+#ifndef FLASH_GRAB
+#define FLASH_GRAB 2
+#endif
 constexpr int FRAMES_MAX = 64;   // = MAX_FRAMES of flash_ingest.cuh
 constexpr int QENT = 8;  // doubles per skin-queue entry: x y z s ginv nhx nhy nhz (slot in a side array)
 
@@ -71,6 +68,7 @@ struct CostParams {
   int cfg_per_frame;         // configuration c evaluates frame c / cfg_per_frame only
   int pts_per_block;
   int use_grid;
+  double* part;        // deterministic mode: per-tile partial sums [C][gridDim.y][acc_len] (null: fp64 atomics into acc)
 };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
@@ -385,7 +383,9 @@ __global__ void __launch_bounds__(GBLOCK, 2) group_kernel(const GroupParams p) {
 #define FLASH_MINB 2
 #endif
 constexpr size_t COST_STATIC_SMEM = 64;   // static __shared__ of cost_kernel (the group hand-out counter)
-template <bool GRAD, bool ARGMIN, bool DIST>
+// DET: deterministic mode as a template parameter -- as a run-time branch on p.part it cost the default kernel 6 % (the
+// initial `g = warp` keeps one more value live across the prologue: 104 B of spills at the 64-register cap).
+template <bool GRAD, bool ARGMIN, bool DIST, bool DET = false>
 __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -399,11 +399,8 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   const SmemLayout L = smem_layout(tab_len, acc_len, hot_g->tabf_len, GRAD && hot_g->n_skins > 0, CWARPS);
   stage_block(smem, L, hot_g, p.tab + (size_t)c * tab_len, tab_len, CBLOCK);
   double* acc_w = reinterpret_cast<double*>(smem + L.off_acc) + (size_t)warp * acc_len;
-#ifdef FLASH_DYN_GROUPS
-  __shared__ int s_next_v;
-  int* s_next = &s_next_v;
-  if (tid == 0) s_next_v = 0;
-#endif
+  __shared__ int s_next;
+  if (tid == 0) s_next = 0;
   if (!DIST) for (int i = lane; i < acc_len; i += 32) acc_w[i] = 0.0;
   __syncthreads();
   const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
@@ -422,40 +419,32 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   if (tile1 > range1) tile1 = range1;
   double cost_local = 0.0;
 
-#ifdef FLASH_DYN_GROUPS
-  // Groups of 32 points are handed to the warps dynamically WITHIN an interval of FLASH_DYN_GROUPS groups; a block
-  // barrier separates the intervals and the hand-out evens out the warps' unequal work between two barriers.
-  // Measured best with ONE interval (no barrier after the first): the hand-out removes the end-of-block tail in
-  // which 11 warps waited for the slowest one, which is what the per-batch barrier of the static schedule was
-  // (expensively) bounding; see DESIGN.md 5.
+  // Groups of 32 points are handed to the block's warps dynamically (FLASH_GRAB consecutive groups per shared-memory
+  // atomic): the cost per group varies several-fold (candidate hulls, skin winners) and with a static schedule every
+  // block ended with most warps waiting for the slowest one.  Deterministic mode
+  // (flash_options.deterministic) uses the static schedule -- warp w takes chunks w, w + CWARPS, ... -- so that every
+  // accumulator sees its terms in one fixed order.
   const int ngroups = (int)((tile1 - tile0 + 31) >> 5);
   // group records (group_kernel, run before this kernel; layout there)
   const bool grp_pre = !DIST && p.rec != nullptr;
   const uint4* rec = grp_pre ? p.rec + (size_t)c * p.rec_stride + ((tile0 - range0) >> 5) : nullptr;
+  // chunks of FLASH_GRAB (a power of two) groups start at multiples of FLASH_GRAB: the end of a chunk is a bit test
   int g = 0;
-  if (lane == 0) g = atomicAdd(s_next, 1);
-  g = __shfl_sync(0xffffffffu, g, 0);
-  for (int g_end = FLASH_DYN_GROUPS; ; g_end += FLASH_DYN_GROUPS) {
-    __syncthreads();
-    while (g < g_end && g < ngroups) {
-    const long long wbase = tile0 + (long long)g * 32;
-    const int gcur = g; (void)gcur;
-    if (lane == 0) g = atomicAdd(s_next, 1);
+  if (DET) g = warp * FLASH_GRAB;
+  else {
+    if (lane == 0) g = atomicAdd(&s_next, FLASH_GRAB);
     g = __shfl_sync(0xffffffffu, g, 0);
-#else
-  for (long long base = tile0; base < tile1; base += CBLOCK) {
-    {
-#ifndef FLASH_NO_BATCH_SYNC
-#ifndef FLASH_SYNC_EVERY
-#define FLASH_SYNC_EVERY 2   // K5: every batch 56.2 ms, every 2nd 55.4, every 3rd 55.4
-#endif
-#if FLASH_SYNC_EVERY > 1
-    if ((((base - tile0) / CBLOCK) % FLASH_SYNC_EVERY) == 0)
-#endif
-    __syncthreads();   // keep the block's warps in the same code region (instruction-cache locality, see CBLOCK)
-#endif
-    const long long wbase = base + warp * 32;
-#endif
+  }
+  while (g < ngroups) {
+    const long long wbase = tile0 + (long long)g * 32;
+    const int gcur = g;
+    if (((++g) & (FLASH_GRAB - 1)) == 0) {
+      if (DET) g += (CWARPS - 1) * FLASH_GRAB;
+      else {
+        if (lane == 0) g = atomicAdd(&s_next, FLASH_GRAB);
+        g = __shfl_sync(0xffffffffu, g, 0);
+      }
+    }
     const long long i = wbase + lane;
     const bool valid = i < tile1;
     PointEval e;
@@ -465,14 +454,12 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     // hulls that can be the minimum for some point of this warp's 32 neighbours, from the group's record
     unsigned cand = all_convex; int first = -1;
     unsigned skin_skip = 0u; float cut0 = 3.0e38f; unsigned long long starts = 0ull;
-#ifdef FLASH_DYN_GROUPS
     if (grp_pre) {
       const uint4 r = __ldg(rec + gcur);
       cand = r.x & 0xffffffu; skin_skip = r.x >> 24; cut0 = __uint_as_float(r.y);
       starts = (unsigned long long)r.z | ((unsigned long long)(r.w & 0xffffu) << 32);
       first = (r.w >> 16) == 255u ? -1 : (int)(r.w >> 16);
     }
-#endif
     if (valid) {
       const float4 P = __ldg(p.pts + i);
       px = P.x; py = P.y; pz = P.z;
@@ -580,10 +567,6 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
         __syncwarp();
       }
     }
-    }
-#ifdef FLASH_DYN_GROUPS
-    if (g_end >= ngroups) break;
-#endif
   }
   if (DIST) return;
   cost_local = warp_sum(cost_local);
@@ -595,7 +578,22 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     double s = 0;
 #pragma unroll
     for (int w = 0; w < CWARPS; ++w) s += acc_all[(size_t)w * acc_len + l];
-    if (s != 0.0) atomicAdd(p.acc + (size_t)c * acc_len + l, s);
+    if (DET) p.part[((size_t)c * gridDim.y + blockIdx.y) * acc_len + l] = s;
+    else if (s != 0.0) atomicAdd(p.acc + (size_t)c * acc_len + l, s);
+  }
+}
+
+// deterministic mode: acc[c][l] = sum over the tiles of configuration c, in tile order
+__global__ void __launch_bounds__(128) reduce_partials_kernel(const double* __restrict__ part, double* __restrict__ acc, int acc_len, int tiles_max,
+                                                              const long long* __restrict__ frames, int cfg_per_frame, long long n_pts, int pts_per_block, int nacc) {
+  const int c = blockIdx.x;
+  long long cnt = n_pts;
+  if (frames) cnt = frames[FRAMES_MAX + 1 + c / cfg_per_frame];
+  const int tiles = (int)((cnt + pts_per_block - 1) / pts_per_block);
+  for (int l = threadIdx.x; l < nacc; l += 128) {
+    double s = 0.0;
+    for (int t = 0; t < tiles && t < tiles_max; ++t) s += part[((size_t)c * tiles_max + t) * acc_len + l];
+    acc[(size_t)c * acc_len + l] = s;
   }
 }
 

@@ -95,6 +95,7 @@ struct flash_ctx {
   double* h_pin = nullptr; size_t cap_pin = 0;  // pinned staging for X / cost / grad
   int32_t* d_argmin = nullptr; size_t cap_argmin = 0;
   uint4* d_rec = nullptr; size_t cap_rec = 0;   // group records of group_kernel, [C][rec_stride]
+  double* d_part = nullptr; size_t cap_part = 0; bool deterministic = false;   // per-tile partial sums [C][tiles][acc_len]
   bool exact_groups = true;   // group_kernel evaluates the candidate hulls exactly at the ball centre (flash_dev.h group_prepass)
   // query scratch (skin_eval / raycast)
   double* d_qd = nullptr; size_t cap_qd = 0;
@@ -166,9 +167,9 @@ SmemLayout cost_layout(const flash_ctx* ctx, bool grad) {
   return smem_layout(M.tab_len, M.acc_len, M.tabf_len, grad && M.n_skins > 0, CWARPS);
 }
 
-template <bool G, bool A, bool D>
+template <bool G, bool A, bool D, bool DET = false>
 int launch_cost_t(flash_ctx* ctx, const CostParams& p, int C, int tiles, size_t smem) {
-  auto k = cost_kernel<G, A, D>;
+  auto k = cost_kernel<G, A, D, DET>;
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((unsigned)C, (unsigned)tiles);
   k<<<grid, CBLOCK, smem, ctx->stream>>>(p);
@@ -214,7 +215,10 @@ int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride) {
   long long gpb = (G * C + (long long)ctx->sm_count * 4 - 1) / ((long long)ctx->sm_count * 4);
   gpb = std::min<long long>(std::max<long long>(((gpb + GBLOCK - 1) / GBLOCK) * GBLOCK, GBLOCK), 8 * GBLOCK);
   g.groups_per_block = (int)gpb;
-  g.exact = (ctx->exact_groups && !ctx->use_grid) ? 1 : 0; g.want_cull = 1;
+  // exact centre distances pay when there are enough (group, configuration) pairs to fill the GPU with one thread each:
+  // K5 (2e7 pairs) 28.6 -> 22.0 ms; on a single depth frame (K2: 9,600 pairs) the longer serial threads cost more than
+  // the tighter candidate sets save (0.069 -> 0.088 ms)
+  g.exact = (ctx->exact_groups && !ctx->use_grid && G * C >= 262144) ? 1 : 0; g.want_cull = 1;
   const size_t smem = group_smem(M.tabf_len);
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   group_kernel<<<dim3((unsigned)C, (unsigned)((G + gpb - 1) / gpb)), GBLOCK, smem, ctx->stream>>>(g);
@@ -242,9 +246,23 @@ int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin, int cfg_per_fr
   if (P.n == 0 || n_tile == 0) return 0;
   const int tiles = (int)((n_tile + p.pts_per_block - 1) / p.pts_per_block);
   const size_t smem = cost_layout(ctx, grad).total;
-  if (smem + COST_STATIC_SMEM > (size_t)ctx->smem_optin) return fail(ctx, FLASH_ERR_TOO_LARGE, "model geometry does not fit in shared memory (" + std::to_string(smem) + " bytes)");
-  if (grad) return d_argmin ? launch_cost_t<true, true, false>(ctx, p, C, tiles, smem) : launch_cost_t<true, false, false>(ctx, p, C, tiles, smem);
-  return d_argmin ? launch_cost_t<false, true, false>(ctx, p, C, tiles, smem) : launch_cost_t<false, false, false>(ctx, p, C, tiles, smem);
+  if (smem + COST_STATIC_SMEM > (size_t)ctx->smem_optin) return fail(ctx, FLASH_ERR_TOO_LARGE, "model tables do not fit in shared memory (" + std::to_string(smem) + " bytes)");
+  p.part = nullptr;
+  if (ctx->deterministic) {
+    int rc = ensure(ctx, ctx->d_part, ctx->cap_part, (size_t)C * (size_t)tiles * (size_t)M.acc_len); if (rc) return rc;
+    p.part = ctx->d_part;
+  }
+  int rc;
+  if (ctx->deterministic) {
+    if (grad) rc = d_argmin ? launch_cost_t<true, true, false, true>(ctx, p, C, tiles, smem) : launch_cost_t<true, false, false, true>(ctx, p, C, tiles, smem);
+    else rc = d_argmin ? launch_cost_t<false, true, false, true>(ctx, p, C, tiles, smem) : launch_cost_t<false, false, false, true>(ctx, p, C, tiles, smem);
+  } else if (grad) rc = d_argmin ? launch_cost_t<true, true, false>(ctx, p, C, tiles, smem) : launch_cost_t<true, false, false>(ctx, p, C, tiles, smem);
+  else rc = d_argmin ? launch_cost_t<false, true, false>(ctx, p, C, tiles, smem) : launch_cost_t<false, false, false>(ctx, p, C, tiles, smem);
+  if (rc || !ctx->deterministic) return rc;
+  reduce_partials_kernel<<<C, 128, 0, ctx->stream>>>(ctx->d_part, ctx->d_acc, M.acc_len, tiles, p.frames, p.cfg_per_frame, P.n, p.pts_per_block, grad ? M.acc_len : 1);
+  CU(cudaGetLastError());
+  ctx->launches++; ctx->last.launches++;
+  return 0;
 }
 
 int run_prepare(flash_ctx* ctx, int C, bool zero_acc = false) {
@@ -537,6 +555,8 @@ int flash_model_create(const flash_model_desc* desc, const flash_options* opt, f
   if (const char* e = getenv("FLASHSDF_NO_SORT")) ctx->sort_points = !(e[0] == '1');
   if (const char* e = getenv("FLASHSDF_NO_GROUP_CULL")) ctx->group_cull = !(e[0] == '1');
   if (const char* e = getenv("FLASHSDF_NO_EXACT_GROUPS")) ctx->exact_groups = !(e[0] == '1');
+  ctx->deterministic = ctx->hm.opt.deterministic != 0;
+  if (const char* e = getenv("FLASHSDF_DETERMINISTIC")) ctx->deterministic = (e[0] == '1');
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess || ndev == 0) {
@@ -584,7 +604,7 @@ void flash_destroy(flash_ctx* ctx) {
   if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
   void* frees[] = {ctx->d_model, ctx->d_hot, ctx->d_geo_f4, ctx->d_geo_u32, ctx->d_grid_pool, ctx->d_stage,
                    ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, ctx->d_cost, ctx->d_grad, ctx->d_div, ctx->d_status, ctx->d_done, ctx->d_iters,
-                   ctx->d_argmin, ctx->d_rec, ctx->d_qd, ctx->d_qi, ctx->d_keys[0], ctx->d_keys[1], ctx->d_idx[0], ctx->d_idx[1], ctx->d_table, ctx->d_sums, ctx->d_bounds};
+                   ctx->d_argmin, ctx->d_rec, ctx->d_part, ctx->d_qd, ctx->d_qi, ctx->d_keys[0], ctx->d_keys[1], ctx->d_idx[0], ctx->d_idx[1], ctx->d_table, ctx->d_sums, ctx->d_bounds};
   for (void* p : frees) if (p) cudaFree(p);
   for (auto& P : ctx->ps) {
     if (P.d_pts && !P.external) cudaFree(P.d_pts);
@@ -775,7 +795,7 @@ int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t 
   ctx->launches++; ctx->last.launches++;
   CostParams p;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
-  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr; p.frames = nullptr; p.cfg_per_frame = 1; p.rec = nullptr; p.rec_stride = 0;
+  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr; p.frames = nullptr; p.cfg_per_frame = 1; p.rec = nullptr; p.rec_stride = 0; p.part = nullptr;
   p.pts_per_block = choose_tile(ctx, n, 1); p.use_grid = ctx->use_grid ? 1 : 0;
   const int tiles = (int)((n + p.pts_per_block - 1) / p.pts_per_block);
   const size_t smem = cost_layout(ctx, false).total;

@@ -2,7 +2,7 @@
 import ctypes as C
 import numpy as np
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 c_double_p = C.POINTER(C.c_double)
 c_int32_p = C.POINTER(C.c_int32)
 
@@ -24,7 +24,8 @@ class Options(C.Structure):
         ("abi_version", C.c_int32), ("device", C.c_int32),
         ("rbf_normalize_by_gradient", C.c_int32), ("rbf_polynomial_degree", C.c_int32),
         ("sdf_mode", C.c_int32), ("grid_spacing", C.c_double), ("grid_margin", C.c_double),
-        ("reserved", C.c_int32 * 8),
+        ("deterministic", C.c_int32), ("n_devices", C.c_int32), ("devices", C.c_int32 * 16),
+        ("reserved", C.c_int32 * 6),
     ]
 
 

@@ -94,7 +94,7 @@ class Manipulator:  # src/Flash.jl:62-65
         self._packed = None
         self._points_owner = None   # the CostFunctor whose cloud the ctx currently holds
         self._options = dict(sdf_mode=SDF_EXACT, grid_spacing=0.0, grid_margin=0.0,
-                             rbf_normalize_by_gradient=1, rbf_polynomial_degree=1, device=-1)
+                             rbf_normalize_by_gradient=1, rbf_polynomial_degree=1, device=-1, deterministic=0, devices=())
 
     def __repr__(self):  # src/Flash.jl:67
         return "Manipulator with %d links and %d surfaces" % (len(self.mechanism.bodies) + 1, len(self.surfaces))
@@ -128,6 +128,10 @@ class Manipulator:  # src/Flash.jl:62-65
                 if k in ("grid_spacing", "grid_margin"):
                     if v > 0:
                         setattr(opt, k, v)
+                elif k == "devices":
+                    opt.n_devices = len(v)
+                    for i, dv in enumerate(v):
+                        opt.devices[i] = int(dv)
                 else:
                     setattr(opt, k, v)
             out = C.c_void_p()

@@ -31,7 +31,7 @@ def test_header_symbols_all_exported():
     missing = [s for s in declared if not hasattr(L, s)]
     assert not missing, missing
     assert sorted(_lib.SYMBOLS) == declared
-    assert L.flash_abi_version() == 1
+    assert L.flash_abi_version() == 2
 
 
 def test_library_has_no_torch_or_nccl_link_dependency():

@@ -468,3 +468,37 @@ def test_frames_batch_equals_frame_by_frame_and_async_swap_pipelines():
     m._points_owner = None
     assert np.allclose(np.array(got), cost, rtol=1e-7)
     assert L.flash_points_swap(ctx) != 0          # nothing pending: FLASH_ERR_STATE, reported not thrown
+
+
+def test_deterministic_mode_is_bit_reproducible():
+    """flash_options.deterministic = 1: static group -> warp schedule and per-tile partial sums combined in tile order
+    instead of fp64 atomics.  Two flash_cost_grad calls, and two whole on-device estimate_state loops with the
+    notebook's (chaotic) squishable solver settings on the real Kinect cloud, are bit-identical; the default mode
+    agrees to rounding."""
+    rng = np.random.default_rng(41)
+    m = flash.models.irb_and_squishable()
+    nx = flash.num_states(m)
+    x0 = flash.gradientdescent.flatten(flash.ManipulatorState(m))
+    x0[4:7] = [0.0, 0.0, 0.75]; x0[17:20] = [0.55, 0.45, 0.8]; x0[24:27] = [0.4, 0.0, 0.6]
+    X = x0 + 0.03 * rng.standard_normal((3, nx))
+    pts = _points(rng, 400_000, [-0.5, -0.5, 0.5], [1.0, 0.5, 2.0])
+    c_def, g_def, _ = flash.gradientdescent.CostFunctor(m, pts).batch(X)
+    m.set_options(deterministic=1)
+    f = flash.gradientdescent.CostFunctor(m, pts)
+    runs = [f.batch(X) for _ in range(3)]
+    for c, g, _ in runs[1:]:
+        assert np.array_equal(c, runs[0][0]) and np.array_equal(g, runs[0][1])
+    assert np.allclose(runs[0][0], c_def, rtol=1e-12) and np.abs(runs[0][1] - g_def).max() <= 1e-10 * np.abs(g_def).max()
+    m.set_options(deterministic=0)
+    # the tracking loop: 50 iterations of the squishable notebook's solver on the real cloud (DESIGN.md 5: chaotic --
+    # the default mode's fp64 atomics make the final cost differ from run to run)
+    real = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "squishable_unsquished_xyz.npy")
+    cloud = np.load(real).astype(np.float64)
+    ms = flash.models.squishable()
+    ms.set_options(deterministic=1)
+    solver = flash.tracking.NaiveSolver(flash.num_states(ms), rate=0.01, max_step=0.1, iteration_limit=50,
+                                        precondition_divisors=np.r_[np.ones(7), 1e-3 * np.ones(36)])
+    xs = flash.gradientdescent.flatten(flash.ManipulatorState(ms))
+    xs[4:7] = cloud.mean(0)
+    ends = [flash.tracking.estimate_state(ms, cloud, xs, solver=solver, on_device=True) for _ in range(3)]
+    assert np.array_equal(ends[0], ends[1]) and np.array_equal(ends[0], ends[2])
