@@ -248,6 +248,14 @@ def run_ours(args, rank, local_rank, world):
         m.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
 
     def e2e_step():
+        # the live loop of examples/irb_and_squishable.ipynb:495-503: frame k is evaluated while frame k+1 uploads.
+        # Every step hands the library one frame of HOST points (24 B x N, pinned) and reads cost/grad back on the host;
+        # the upload of the next step's frame is issued first and overlaps this step's kernels (copy stream + DMA).
+        m.check(L.flash_points_swap(ctx))                          # the frame uploaded during the previous step
+        m.check(L.flash_points_set_async(ctx, pp, n_local))        # the next one
+        m.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
+
+    def e2e_step_serial():
         m.check(L.flash_points_set(ctx, pp, n_local))
         m.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
 
@@ -258,7 +266,7 @@ def run_ours(args, rank, local_rank, world):
         step()
     launches0 = L.flash_launch_count(ctx)
     first_sample = sampler.mark() if rank == 0 else 0
-    t_steps, k_main, k_total = [], [], []
+    t_steps, k_main, k_total, k_group = [], [], [], []
     tm = Timing()
     for _ in range(args.steps):
         flush.zero_()
@@ -268,14 +276,23 @@ def run_ours(args, rank, local_rank, world):
         torch.cuda.synchronize()
         t_steps.append(time.perf_counter() - t0)
         L.flash_last_timing(ctx, C.byref(tm))
-        k_main.append(tm.ms_main); k_total.append(tm.ms_total)
+        k_main.append(tm.ms_main); k_total.append(tm.ms_total); k_group.append(tm.ms_group)
     barrier()
     launches = L.flash_launch_count(ctx) - launches0
     checksum = float(cost.sum())
 
     # end-to-end: host (pinned) points -> device every step, results back on the host
-    for _ in range(1):
-        e2e_step()
+    t_ser = []
+    for k in range(1 + min(args.steps, 3)):
+        flush.zero_()
+        barrier()
+        t0 = time.perf_counter()
+        e2e_step_serial()
+        torch.cuda.synchronize()
+        if k:
+            t_ser.append(time.perf_counter() - t0)
+    m.check(L.flash_points_set_async(ctx, pp, n_local))
+    e2e_step()
     t_e2e = []
     for _ in range(args.steps):
         flush.zero_()
@@ -284,13 +301,14 @@ def run_ours(args, rank, local_rank, world):
         e2e_step()
         torch.cuda.synchronize()
         t_e2e.append(time.perf_counter() - t0)
+    m.check(L.flash_points_swap(ctx))   # retire the last upload
     barrier()
     clocks = sampler.stop(first_sample) if rank == 0 else None
 
-    tt = torch.tensor([sum(t_steps), sum(t_e2e), sum(k_main) / 1e3, sum(k_total) / 1e3], dtype=torch.float64, device="cuda")
+    tt = torch.tensor([sum(t_steps), sum(t_e2e), sum(k_main) / 1e3, sum(k_total) / 1e3, sum(t_ser) / len(t_ser) * args.steps, sum(k_group) / 1e3], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    T, Te, Tk, Tkt = [float(v) for v in tt.cpu()]
+    T, Te, Tk, Tkt, Tser, Tg = [float(v) for v in tt.cpu()]
     units = float(N) * Cn * args.steps
     if rank == 0:
         peaks, peak_src = measured_peaks()
@@ -300,27 +318,46 @@ def run_ours(args, rank, local_rank, world):
         # config pass it is not L2-resident for; the algorithmic minimum is one read per launch per rank
         # plus the per-config tables -- the kernel is ALU-bound, see DESIGN.md.
         n_rank = (N + world - 1) // world
-        alg_bytes = 16.5 * n_rank + 8.0 * Cn * 400   # float4 point + 16 B bounding ball per 32 points
-        kernel_s = Tk / args.steps
+        alg_bytes = 16.5 * n_rank + 8.0 * Cn * 400 + 2 * 16.0 * Cn * n_rank / 32   # float4 point + 16 B bounding ball per 32 points; group records
+        kernel_s = (Tk - Tg) / args.steps     # cost_kernel alone (CUDA events on the library's stream); group_kernel = Tg
+        group_s = Tg / args.steps
         achieved = alg_bytes / kernel_s / 1e9
-        # per-launch DRAM traffic and warp instructions from the committed ncu capture, scaled to this launch
+        # instruction and DRAM counts per evaluation come from the `ncu --set full` capture of THIS kernel build
+        # (profiles/r02_ncu_constants.json, written by tools/refresh_profiles.sh from the capture of the same bench
+        # command; "kernel_sha" = hash of csrc/ at capture time), scaled to this launch and divided by this run's
+        # CUDA-event kernel time
         ncu = {}
         try:
-            ncu = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_constants.json")))
+            ncu = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_constants.json")))
         except Exception:
             pass
         traffic = None
-        issue = None
+        roof = {"bound": "issue", "achieved": None, "peak": None, "unit": "warp-instr/s", "frac": None, "traffic": None, "kernel": "cost_kernel<GRAD>",
+                "kernel_ms": 1e3 * kernel_s, "group_kernel_ms": 1e3 * group_s, "note": "profiles/r02_ncu_constants.json missing"}
+        sm_clock = (clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)) * 1e6
+        fp32_peak = sm.value * 128 * 2 * sm_clock / 1e12
         if ncu:
-            traffic = (ncu["dram_bytes_read"] + ncu["dram_bytes_write"]) * (n_rank / ncu["points"])
-            winst = ncu["warp_instructions"] * (n_rank * Cn) / (ncu["points"] * ncu["configs"])
-            sm_clock = (clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)) * 1e6
+            import hashlib
+            sha = hashlib.sha1()
+            for fn in ("flash_dev.h", "flash_kernels.cuh"):
+                sha.update(open(os.path.join(ROOT, "point-cloud-signed-distance_b200", "csrc", fn), "rb").read())
+            sha_ok = sha.hexdigest()[:12] == ncu.get("kernel_sha")
+            scale = (n_rank * Cn) / (ncu["points"] * ncu["configs"])
+            traffic = (ncu["dram_bytes_read"] + ncu["dram_bytes_write"]) * scale
+            winst = ncu["warp_instructions"] * scale
             peak_issue = sm.value * 4 * sm_clock
-            issue = {"bound": "issue slots (4 warp-instructions/clk/SM)", "achieved": winst / kernel_s, "peak": peak_issue, "unit": "warp-instr/s",
-                     "frac": winst / kernel_s / peak_issue, "warp_instr_per_eval": ncu["warp_instructions"] / (ncu["points"] * ncu["configs"]),
-                     "source": "instruction count per evaluation from profiles/r01_cost_kernel_ncu_full.txt (refreshed by tools/refresh_profiles.sh) x this run's evaluations / this run's kernel time"}
-        # ALU roofline (the binding one in exact mode): issue slots per second
-        fp32_peak = sm.value * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12
+            roof = {"bound": "issue", "achieved": winst / kernel_s, "peak": peak_issue, "unit": "warp-instr/s", "frac": winst / kernel_s / peak_issue,
+                    "traffic": traffic, "kernel": "cost_kernel<GRAD>", "kernel_ms": 1e3 * kernel_s, "group_kernel_ms": 1e3 * group_s,
+                    "kernel_share_of_step": kernel_s / (Tkt / args.steps),
+                    "warp_instr_per_eval": ncu["warp_instructions"] / (ncu["points"] * ncu["configs"]),
+                    "lanes_active": ncu.get("lanes_active"), "warps_active_pct": ncu.get("warps_active_pct"), "registers": ncu.get("registers"),
+                    "spill_bytes": ncu.get("spill_bytes"), "issue_active_pct_under_ncu": ncu.get("issue_active_pct"),
+                    "fp32_flops_frac": (ncu["fp32_flops"] * scale / kernel_s / 1e12 / fp32_peak) if "fp32_flops" in ncu else None,
+                    "fp64_flops_tflops": (ncu["fp64_flops"] * scale / kernel_s / 1e12) if "fp64_flops" in ncu else None,
+                    "peak_source": "4 warp-instructions/clk/SM x %d SMs x SM clock sampled during the run" % sm.value,
+                    "source": "profiles/r02_ncu_constants.json (ncu --set full of this kernel build, %s) x this run's evaluations / this run's kernel time" % ("device code hash %s %s the sources of this run" % (ncu.get("kernel_sha", "?"), "MATCHES" if sha_ok else "DOES NOT MATCH")),
+                    "profile_matches_this_build": sha_ok,
+                    "note": "exact mode is instruction-issue bound (BSP descents, certified culls, fp64 RBF adjoints), not memory bound: HBM figures in hbm_roofline"}
         line = {
             "metric": METRIC, "value": units / T, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": 1e3 * T / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -329,15 +366,17 @@ def run_ours(args, rank, local_rank, world):
                        "points": N, "configs": Cn, "sdf_mode": args.mode, "l2": "L2 flushed (512 MiB memset) between timed steps; inputs %s L2" % ("exceed" if 16 * n_rank > l2.value else "fit"),
                        "parallelism": "points sharded x%d by interleaved x-slabs (40 slabs, rank r owns slabs r mod %d), one ncclAllReduce of [%d][%d] fp64 per step" % (world, world, Cn, acc_len)},
             "device_ms_per_step": 1e3 * Tkt / args.steps,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
-                         "traffic": traffic, "peak_source": peak_src, "kernel": "cost_kernel<GRAD>", "kernel_ms": 1e3 * kernel_s,
-                         "note": "exact mode is ALU-bound (GJK + fp64 RBF), not HBM-bound: see alu"},
-            "issue_roofline": issue,
-            "alu": {"evals_per_sm_clock": (units / world / args.steps) / kernel_s / (sm.value * (clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)) * 1e6),
-                    "fp32_peak_tflops_nominal": fp32_peak},
+            "roofline": roof,
+            "hbm_roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
+                             "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes": alg_bytes,
+                             "note": "16.5 B per point per launch (float4 + its share of the group ball) + 16 B group record per (group, config) written and read once; the path is not HBM-bound"},
+            "alu": {"evals_per_sm_clock": (units / world / args.steps) / kernel_s / (sm.value * sm_clock), "fp32_peak_tflops_nominal": fp32_peak},
             "clocks": clocks,
             "e2e": {"value": units / Te, "unit": UNIT, "h2d_bytes_per_step": int(n_local * 24 + X.nbytes), "d2h_bytes_per_step": int(cost.nbytes + grad.nbytes),
-                    "ms_per_step": 1e3 * Te / args.steps},
+                    "ms_per_step": 1e3 * Te / args.steps,
+                    "how": "flash_points_swap + flash_points_set_async(next frame) + flash_cost_grad per step: the upload, Hilbert sort and grouping of frame k+1 overlap the kernels of frame k",
+                    "serial_value": units / Tser, "serial_ms_per_step": 1e3 * Tser / args.steps,
+                    "serial_how": "flash_points_set (blocking) + flash_cost_grad per step, nothing overlapped"},
             "gpu_launches": int(launches),
             "checksum_cost_sum": checksum,
         }
@@ -451,7 +490,6 @@ def frame_cloud(flash, state, cam, rows=480, cols=640, ground_z=0.0, far=3.0):
 def configs_leg(flash, L, steps):
     """BASELINE.json configs[1] (K2) and configs[3] (K4) as SURVEY 8(d) defines them: depth frames of the
     models themselves (points ON the surfaces -- the tracking regime, unlike K5's uniform cloud)."""
-    from flash._desc import Timing, c_double_p
     out = {}
     rng = np.random.default_rng(2)
     # K2: IRB140, one 640x480 frame from (0, 1.5, 0.5) looking along -y, one candidate configuration
@@ -459,9 +497,9 @@ def configs_leg(flash, L, steps):
     st = flash.ManipulatorState(m)
     cam = flash.depthsensors.affine((0, 1.5, 0.5), (1, 0, 0), np.pi / 2)
     pts, hits = frame_cloud(flash, st, cam)
-    X = rng.uniform(-np.pi / 2, np.pi / 2, (1, 6))
-    out["k2_irb140_one_frame_one_config"] = _time_batches(flash, L, m, [pts], X, steps, hits)
-    # K4: IRB140(floating)+squishable+table, 8 frames x 16 configs per frame
+    X = rng.uniform(-np.pi / 2, np.pi / 2, (1, 1, 6))
+    out["k2_irb140_one_frame_one_config"] = _time_frames(flash, L, m, [pts], X, steps, hits)
+    # K4: IRB140(floating)+squishable+table, 8 frames x 16 configs per frame, ONE flash_cost_grad_frames launch per batch
     m4 = scene_model(flash)
     X4 = scene_states(flash, m4, 16)
     st4 = flash.ManipulatorState(m4)
@@ -474,47 +512,72 @@ def configs_leg(flash, L, steps):
         cam4 = flash.depthsensors.affine((0.3 + 0.05 * k, 1.8, 1.0), (1, 0, 0), np.pi / 2 + 0.25)
         p, h = frame_cloud(flash, st4, cam4)
         frames.append(p); hits4 += h
-    out["k4_combined_8_frames_x_16_configs"] = _time_batches(flash, L, m4, frames, X4, steps, hits4)
+    out["k4_combined_8_frames_x_16_configs"] = _time_frames(flash, L, m4, frames, np.repeat(X4[None], 8, 0), steps, hits4)
     return out
 
 
-def _time_batches(flash, L, m, clouds, X, steps, hits):
+def _time_frames(flash, L, m, clouds, X, steps, hits):
+    """A batch of F frames x C candidate states per frame through flash_frames_set(_async) + flash_cost_grad_frames
+    (the batch entry points of include/flashsdf.h).  device = CUDA-event time of one flash_cost_grad_frames call with
+    the frames resident; e2e = per batch, the F frames from pinned HOST memory (upload + Hilbert sort + grouping on the
+    copy stream, overlapping the previous batch's kernels) + the call + cost/grad back on the host."""
     import torch
     from flash._desc import Timing, c_double_p
     ctx = m.ctx()
-    Cn, nx = X.shape
+    F, Cn, nx = X.shape
     X = np.ascontiguousarray(X)
-    cost = np.empty(Cn); grad = np.empty((Cn, nx))
+    cost = np.empty((F, Cn)); grad = np.empty((F, Cn, nx))
     pX, pc, pg = X.ctypes.data_as(c_double_p), cost.ctypes.data_as(c_double_p), grad.ctypes.data_as(c_double_p)
     m.check(L.flash_profiling(ctx, 1))
     tm = Timing()
-    # frames live in pinned host memory, as the K5 leg's points do (bench contract: H2D from pinned memory)
-    keep = []
-    pinned = []
-    for p in clouds:
+    keep, ptr_list = [], []
+    for p in clouds:   # frames live in pinned host memory (bench contract: H2D from pinned memory)
         t = torch.empty(p.shape, dtype=torch.float64, pin_memory=True)
         a = t.numpy(); a[:] = p
-        keep.append(t); pinned.append(a)
-    clouds = pinned
-    def run():
-        k_ms = 0.0
-        for p in clouds:
-            m.check(L.flash_points_set(ctx, p.ctypes.data_as(c_double_p), len(p)))
-            m.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
-            L.flash_last_timing(ctx, C.byref(tm)); k_ms += tm.ms_total
-        return k_ms
-    for _ in range(2):
-        run()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter(); k = 0.0
-    for _ in range(steps):
-        k += run()
-    torch.cuda.synchronize()
-    dt = time.perf_counter() - t0
+        keep.append(t); ptr_list.append(a.ctypes.data_as(c_double_p))
+    ptrs = (c_double_p * F)(*ptr_list)
+    counts = (C.c_int64 * F)(*[len(p) for p in clouds])
     n = sum(len(p) for p in clouds)
-    return {"points": n, "ray_hits_on_model": hits, "configs": Cn, "frames": len(clouds), "e2e_ms_per_batch": 1e3 * dt / steps,
-            "e2e_evals_per_sec": n * Cn * steps / dt, "device_ms_per_batch": k / steps, "device_evals_per_sec": n * Cn * steps / (k / 1e3),
-            "note": "e2e = flash_points_set (H2D + Morton binning) + flash_cost_grad per frame, host buffers; device = CUDA-event time of prepare+cost+epilogue"}
+    m.check(L.flash_frames_set(ctx, ptrs, counts, F))
+    k_ms = []
+    for k in range(2 + steps):
+        m.check(L.flash_cost_grad_frames(ctx, pX, Cn, 10.0, pc, pg))
+        L.flash_last_timing(ctx, C.byref(tm))
+        if k >= 2:
+            k_ms.append((tm.ms_total, tm.ms_main, tm.ms_group))
+    torch.cuda.synchronize()
+    # serial end to end
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        m.check(L.flash_frames_set(ctx, ptrs, counts, F))
+        m.check(L.flash_cost_grad_frames(ctx, pX, Cn, 10.0, pc, pg))
+    torch.cuda.synchronize()
+    t_serial = (time.perf_counter() - t0) / steps
+    # pipelined end to end: batch k+1 uploads while batch k is evaluated
+    m.check(L.flash_frames_set_async(ctx, ptrs, counts, F))
+    def step():
+        m.check(L.flash_points_swap(ctx))
+        m.check(L.flash_frames_set_async(ctx, ptrs, counts, F))
+        m.check(L.flash_cost_grad_frames(ctx, pX, Cn, 10.0, pc, pg))
+    step()
+    torch.cuda.synchronize()
+    reps = max(steps, 10)
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        step()
+    torch.cuda.synchronize()
+    t_pipe = (time.perf_counter() - t0) / reps
+    m.check(L.flash_points_swap(ctx))
+    m._points_owner = None
+    dev = float(np.mean([k[0] for k in k_ms]))
+    return {"points": n, "ray_hits_on_model": hits, "configs": Cn, "frames": F,
+            "device_ms_per_batch": dev, "device_evals_per_sec": n * Cn / (dev / 1e3),
+            "cost_kernel_ms": float(np.mean([k[1] - k[2] for k in k_ms])), "group_kernel_ms": float(np.mean([k[2] for k in k_ms])),
+            "e2e_ms_per_batch": 1e3 * t_pipe, "e2e_evals_per_sec": n * Cn / t_pipe,
+            "e2e_serial_ms_per_batch": 1e3 * t_serial, "e2e_serial_evals_per_sec": n * Cn / t_serial,
+            "h2d_bytes_per_batch": int(24 * n + X.nbytes), "d2h_bytes_per_batch": int(cost.nbytes + grad.nbytes),
+            "note": "flash_frames_set(_async) + flash_cost_grad_frames, one launch per batch; device = CUDA-event time of prepare + group + cost + epilogue with "
+                    "the frames resident; e2e = frames from pinned host memory every batch, pipelined (batch k+1 uploads while batch k runs); e2e_serial = nothing overlapped"}
 
 
 def tracking_leg(flash, L):
@@ -552,14 +615,19 @@ def tracking_leg(flash, L):
             ends.append(float(cost[0]))
         t = min(times[1:])
         # end to end per frame: the frame's points from host memory (upload + Morton binning) + the whole solver loop
+        # (the live loop: frame k+1 uploads on the copy stream while frame k is being solved)
         cl = np.ascontiguousarray(cloud)
         te = []
-        for _ in range(4):
+        m.check(L.flash_points_set_async(m.ctx(), cl.ctypes.data_as(c_double_p), len(cl)))
+        for _ in range(6):
             X = x0.reshape(1, -1).copy()
             t0 = time.perf_counter()
-            m.check(L.flash_points_set(m.ctx(), cl.ctypes.data_as(c_double_p), len(cl)))
+            m.check(L.flash_points_swap(m.ctx()))
+            m.check(L.flash_points_set_async(m.ctx(), cl.ctypes.data_as(c_double_p), len(cl)))
             m.check(L.flash_estimate_state(m.ctx(), X.ctypes.data_as(c_double_p), 1, C.byref(sp), div.ctypes.data_as(c_double_p), cost.ctypes.data_as(c_double_p), None))
             te.append(time.perf_counter() - t0)
+        m.check(L.flash_points_swap(m.ctx()))
+        m._points_owner = None
         out[name] = {"points": int(len(cloud)), "iterations": 50, "ms_per_frame": 1e3 * t, "frames_per_sec": 1.0 / t,
                      "frames_per_sec_with_upload": 1.0 / min(te[1:]),
                      "evals_per_sec": len(cloud) * 51 / t, "cost_start": float(c0), "cost_end": float(ends[-1]), "cost_end_of_each_repeat": ends}

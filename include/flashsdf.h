@@ -245,6 +245,7 @@ typedef struct flash_timing {
   float ms_epilogue;   /* adjoint solve + joint projection  */
   float ms_total;      /* first launch -> last kernel end   */
   int32_t launches;    /* kernels launched by the last call */
+  float ms_group;      /* group pre-pass kernel (part of ms_main) */
 } flash_timing;
 int flash_profiling(flash_ctx* ctx, int32_t enable);
 int flash_last_timing(const flash_ctx* ctx, flash_timing* t);

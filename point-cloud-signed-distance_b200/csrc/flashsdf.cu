@@ -104,8 +104,8 @@ struct flash_ctx {
   nccl_comm comm = nullptr; int rank = 0, world = 1;
   // measurement
   bool profiling = false;
-  cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-  flash_timing last = {0, 0, 0, 0, 0, 0};
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [5]: between group_kernel and cost_kernel
+  flash_timing last = {0, 0, 0, 0, 0, 0, 0};
   long long launches = 0;
   int sm_count = 0, clock_khz = 0; long long l2_bytes = 0; int smem_optin = 0;
   std::string err;
@@ -156,9 +156,23 @@ int ensure_batch(flash_ctx* ctx, int C) {
   CU(cudaMalloc((void**)&ctx->d_grad, c * M.nx * sizeof(double)));
   CU(cudaMalloc((void**)&ctx->d_done, c * sizeof(int)));
   CU(cudaMalloc((void**)&ctx->d_iters, c * sizeof(int)));
-  ctx->cap_pin = c * (2 * (size_t)M.nx + 2);
+  ctx->cap_pin = c * (2 * (size_t)M.nx + 2) + (size_t)M.nx;   // X, cost, grad (+ the solver's divisors)
   CU(cudaHostAlloc((void**)&ctx->h_pin, ctx->cap_pin * sizeof(double), cudaHostAllocDefault));
   ctx->cap_C = C;
+  return 0;
+}
+
+// Small host -> device uploads (the candidate states, the solver's divisors) are PULLED by a kernel from the ctx's
+// pinned staging buffer (mapped into the device's address space by UVA) instead of going through the copy engine:
+// a cudaMemcpyAsync would queue behind a frame upload in flight on the copy stream (240 MB = 4.5 ms on K5) and hold
+// back every kernel of the call -- measured: flash_cost_grad 21.9 ms alone, 26.7 ms with the next frame uploading.
+__global__ void pull_doubles_kernel(double* __restrict__ dst, const double* __restrict__ src, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+int pull_pinned(flash_ctx* ctx, double* dst, const double* src_pinned, size_t n) {
+  if (n == 0) return 0;
+  pull_doubles_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 64), 256, 0, ctx->stream>>>(dst, src_pinned, n);
+  CU(cudaGetLastError());
   return 0;
 }
 
@@ -234,6 +248,7 @@ int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin, int cfg_per_fr
   const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
   long long rec_stride = 0;
   { int rc = run_groups(ctx, C, cfg_per_frame, &rec_stride); if (rc) return rc; }
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[5], ctx->stream));
   CostParams p;
   p.rec = rec_stride > 0 ? ctx->d_rec : nullptr; p.rec_stride = rec_stride;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
@@ -310,6 +325,7 @@ int collect_timing(flash_ctx* ctx) {
   CU(cudaEventSynchronize(ctx->ev[4]));
   CU(cudaEventElapsedTime(&ctx->last.ms_prepare, ctx->ev[0], ctx->ev[1]));
   CU(cudaEventElapsedTime(&ctx->last.ms_main, ctx->ev[1], ctx->ev[2]));
+  CU(cudaEventElapsedTime(&ctx->last.ms_group, ctx->ev[1], ctx->ev[5]));
   CU(cudaEventElapsedTime(&ctx->last.ms_allreduce, ctx->ev[2], ctx->ev[3]));
   CU(cudaEventElapsedTime(&ctx->last.ms_epilogue, ctx->ev[3], ctx->ev[4]));
   CU(cudaEventElapsedTime(&ctx->last.ms_total, ctx->ev[0], ctx->ev[4]));
@@ -732,10 +748,10 @@ static int cost_grad_impl(flash_ctx* ctx, const double* X, int32_t C, int cfg_pe
   const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
   CU(cudaSetDevice(ctx->device));
   int rc = ensure_batch(ctx, C); if (rc) return rc;
-  ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0, 0};
   const size_t nX = (size_t)C * M.nx;
   std::memcpy(ctx->h_pin, X, nX * sizeof(double));
-  CU(cudaMemcpyAsync(ctx->d_X, ctx->h_pin, nX * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  rc = pull_pinned(ctx, ctx->d_X, ctx->h_pin, nX); if (rc) return rc;
   int32_t* d_arg = nullptr;
   if (argmin) {
     rc = ensure(ctx, ctx->d_argmin, ctx->cap_argmin, (size_t)C * (size_t)std::max<long long>(P.n, 1)); if (rc) return rc;
@@ -780,7 +796,7 @@ int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t 
   const ModelC& M = ctx->hm.M;
   CU(cudaSetDevice(ctx->device));
   int rc = ensure_batch(ctx, 1); if (rc) return rc;
-  ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0, 0};
   CU(cudaMemcpyAsync(ctx->d_X, x, (size_t)M.nx * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   if ((rc = run_prepare(ctx, 1))) return rc;
   // query points: [n][3] doubles -> float4 (own scratch; the frame's points stay untouched)
@@ -819,7 +835,7 @@ int flash_raycast(flash_ctx* ctx, const double* x, const double* rays, int64_t R
   const ModelC& M = ctx->hm.M;
   CU(cudaSetDevice(ctx->device));
   int rc = ensure_batch(ctx, 1); if (rc) return rc;
-  ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0, 0};
   CU(cudaMemcpyAsync(ctx->d_X, x, (size_t)M.nx * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   if ((rc = run_prepare(ctx, 1))) return rc;
   const int nblocks = (int)((R + BLOCK - 1) / BLOCK);
@@ -863,15 +879,17 @@ int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solve
   const ModelC& M = ctx->hm.M;
   CU(cudaSetDevice(ctx->device));
   int rc = ensure_batch(ctx, C); if (rc) return rc;
-  ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0, 0};
   const size_t nX = (size_t)C * M.nx;
   std::memcpy(ctx->h_pin, X, nX * sizeof(double));
-  CU(cudaMemcpyAsync(ctx->d_X, ctx->h_pin, nX * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  rc = pull_pinned(ctx, ctx->d_X, ctx->h_pin, nX); if (rc) return rc;
   CU(cudaMemsetAsync(ctx->d_done, 0, (size_t)C * sizeof(int), ctx->stream));
   CU(cudaMemsetAsync(ctx->d_iters, 0, (size_t)C * sizeof(int), ctx->stream));
   if (divisors) {
     if (!ctx->d_div) CU(cudaMalloc((void**)&ctx->d_div, (size_t)M.nx * sizeof(double)));
-    CU(cudaMemcpyAsync(ctx->d_div, divisors, (size_t)M.nx * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    double* h_div = ctx->h_pin + (size_t)C * (2 * (size_t)M.nx + 2);
+    std::memcpy(h_div, divisors, (size_t)M.nx * sizeof(double));
+    rc = pull_pinned(ctx, ctx->d_div, h_div, (size_t)M.nx); if (rc) return rc;
   }
   // total point count across ranks (the reference divides by length(sensed_points), src/tracking.jl:20)
   double n_total = (double)ctx->ps[ctx->cur].n;
@@ -934,7 +952,7 @@ int flash_contour_mesh(flash_ctx* ctx, const double* x, int32_t surface, const d
   if (nodes > (1ll << 30)) return fail(ctx, FLASH_ERR_TOO_LARGE, "flash_contour_mesh: more than 2^30 grid nodes; increase spacing");
   CU(cudaSetDevice(ctx->device));
   int rc = ensure_batch(ctx, 1); if (rc) return rc;
-  ctx->last = flash_timing{0, 0, 0, 0, 0, 0};
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0, 0};
   CU(cudaMemcpyAsync(ctx->d_X, x, (size_t)M.nx * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
   if ((rc = run_prepare(ctx, 1))) return rc;
   // scratch (in doubles): field[nodes] floats | counter | triangles[cap][9] floats

@@ -39,7 +39,7 @@ class SolverParams(C.Structure):
 class Timing(C.Structure):
     _fields_ = [
         ("ms_prepare", C.c_float), ("ms_main", C.c_float), ("ms_allreduce", C.c_float),
-        ("ms_epilogue", C.c_float), ("ms_total", C.c_float), ("launches", C.c_int32),
+        ("ms_epilogue", C.c_float), ("ms_total", C.c_float), ("launches", C.c_int32), ("ms_group", C.c_float),
     ]
 
 

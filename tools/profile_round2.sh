@@ -12,9 +12,9 @@ $CMD > gpurun_out/${tag}_plain.json 2> gpurun_out/${tag}_plain.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv $CMD > gpurun_out/${tag}_ncu1.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:cost_kernel -s 1 -c 1 -o gpurun_out/${tag}_cost $CMD > gpurun_out/${tag}_ncu2.log 2>&1
 tail -2 gpurun_out/${tag}_ncu2.log
-# K4: tools/configs_bench.py launches cost_kernel 5 times for K2 (2 warm-up + 3), then the K4 frames
+# K4: tools/configs_bench.py launches cost_kernel 19 times for K2 (5 resident + 3 serial + 11 pipelined), then the K4 batches
 python tools/configs_bench.py > gpurun_out/${tag}_configs.json 2> gpurun_out/${tag}_configs.err
-ncu --set full --clock-control none --import-source on -k regex:cost_kernel -s 6 -c 1 -o gpurun_out/${tag}_cost_k4 python tools/configs_bench.py > gpurun_out/${tag}_ncu3.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:cost_kernel -s 21 -c 1 -o gpurun_out/${tag}_cost_k4 python tools/configs_bench.py > gpurun_out/${tag}_ncu3.log 2>&1
 tail -2 gpurun_out/${tag}_ncu3.log
 ncu --set full --clock-control none --import-source on -k regex:cost_kernel -s 1 -c 1 -o gpurun_out/${tag}_cost_grid $CMD --mode grid > gpurun_out/${tag}_ncu4.log 2>&1
 tail -2 gpurun_out/${tag}_ncu4.log
