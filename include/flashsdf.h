@@ -135,6 +135,28 @@ const char* flash_last_error(const flash_ctx* ctx);
 int flash_model_create(const flash_model_desc* desc, const flash_options* opt, flash_ctx** out);
 void flash_destroy(flash_ctx* ctx);
 
+/*
+ * `load_urdf(filename; package_path)` (src/models.jl:154-171: parse_urdf + parse_urdf_visuals + extract_convex_surfaces)
+ * without Julia: the kinematic tree breadth-first from the single root link (welded to the world), one convex surface
+ * per <visual> mesh (binary or ASCII STL, OBJ) with the visual <origin> as its frame, vertices welded exactly,
+ * `package://` names resolved against package_dirs (each either the parent of the package directory or the package
+ * directory itself) and the URDF's own directory.  No CUDA device is needed to load; errors return FLASH_ERR_IO /
+ * FLASH_ERR_INVALID with the message in flash_last_error(NULL).
+ * The flash_urdf owns the arrays flash_urdf_desc points to; flash_model_create copies what it needs, so the flash_urdf
+ * may be freed right after.  flash_urdf_set_joint_type replaces a body's joint (the notebooks swap the IRB140's base
+ * for a quaternion-floating joint, examples/irb_and_squishable.ipynb:268-270).
+ */
+typedef struct flash_urdf flash_urdf;
+int flash_urdf_load(const char* urdf_path, const char* const* package_dirs, int32_t n_package_dirs, flash_urdf** out);
+const flash_model_desc* flash_urdf_desc(const flash_urdf* u);
+const char* flash_urdf_body_name(const flash_urdf* u, int32_t body);        /* link names, in body order */
+const char* flash_urdf_surface_mesh(const flash_urdf* u, int32_t surface);  /* resolved mesh file of a surface */
+int flash_urdf_set_joint_type(flash_urdf* u, int32_t body, int32_t joint_type);
+void flash_urdf_free(flash_urdf* u);
+/* flash_urdf_load + flash_model_create in one call */
+int flash_model_load_urdf(const char* urdf_path, const char* const* package_dirs, int32_t n_package_dirs,
+                          const flash_options* opt, flash_ctx** out);
+
 /* num_positions / num_states (src/Flash.jl:90) and the surface count */
 int flash_num_positions(const flash_ctx* ctx);
 int flash_num_states(const flash_ctx* ctx);
@@ -163,6 +185,16 @@ int64_t flash_num_points(const flash_ctx* ctx);
 int flash_points_set_async(flash_ctx* ctx, const double* xyz, int64_t n);
 int flash_points_set_async_f32(flash_ctx* ctx, const float* xyz, int64_t n);
 int flash_points_swap(flash_ctx* ctx);
+/*
+ * `read_point_cloud(file)` (src/depthdata.jl:19-30): first line the camera origin `x, y, z`, then one return
+ * `x, y, z, r, g, b` per line.  flash_read_point_cloud parses into caller buffers (xyz [cap][3], rgb [cap][3] or NULL;
+ * *n receives the number of returns in the file, which may exceed cap: call with cap = 0 first to size the buffers).
+ * flash_points_set_file / flash_points_set_file_async parse straight into the ctx's pinned staging ring and upload from
+ * there (the async form fills the back set: flash_points_swap makes it current).  FLASH_ERR_IO on unreadable files.
+ */
+int flash_read_point_cloud(const char* path, double origin[3], double* xyz, double* rgb, int64_t cap, int64_t* n);
+int flash_points_set_file(flash_ctx* ctx, const char* path, double origin[3]);
+int flash_points_set_file_async(flash_ctx* ctx, const char* path, double origin[3]);
 int flash_points_sync(flash_ctx* ctx);   /* host-blocks until every upload issued so far has finished */
 
 /*

@@ -12,6 +12,7 @@
 
 #include "../../include/flashsdf.h"
 #include "flash_host.h"
+#include "flash_urdf.h"
 #include "flash_kernels.cuh"
 #include "flash_ingest.cuh"
 
@@ -638,6 +639,51 @@ void flash_destroy(flash_ctx* ctx) {
   delete ctx;
 }
 
+// ---- URDF / mesh / point-cloud files (flash_urdf.h; no CUDA involved in parsing) ----
+struct flash_urdf { flashurdf::Urdf u; };
+
+int flash_urdf_load(const char* urdf_path, const char* const* package_dirs, int32_t n_package_dirs, flash_urdf** out) {
+  if (!out) return fail(nullptr, FLASH_ERR_INVALID, "flash_urdf_load: null out pointer");
+  *out = nullptr;
+  if (!urdf_path || n_package_dirs < 0 || (n_package_dirs > 0 && !package_dirs)) return fail(nullptr, FLASH_ERR_INVALID, "flash_urdf_load: bad arguments");
+  std::vector<std::string> dirs;
+  for (int i = 0; i < n_package_dirs; ++i) if (package_dirs[i]) dirs.push_back(package_dirs[i]);
+  flash_urdf* h = new flash_urdf;
+  std::string err;
+  if (!flashurdf::load(urdf_path, dirs, h->u, err)) { delete h; return fail(nullptr, FLASH_ERR_IO, err); }
+  *out = h;
+  return FLASH_OK;
+}
+const flash_model_desc* flash_urdf_desc(const flash_urdf* u) { return u ? &u->u.desc : nullptr; }
+const char* flash_urdf_body_name(const flash_urdf* u, int32_t body) { return (u && body >= 0 && body < (int32_t)u->u.body_name.size()) ? u->u.body_name[body].c_str() : nullptr; }
+const char* flash_urdf_surface_mesh(const flash_urdf* u, int32_t surface) { return (u && surface >= 0 && surface < (int32_t)u->u.surface_mesh.size()) ? u->u.surface_mesh[surface].c_str() : nullptr; }
+int flash_urdf_set_joint_type(flash_urdf* u, int32_t body, int32_t joint_type) {
+  if (!u || body < 0 || body >= (int32_t)u->u.joint_type.size() || joint_type < 0 || joint_type > 2) return fail(nullptr, FLASH_ERR_INVALID, "flash_urdf_set_joint_type: bad arguments");
+  u->u.joint_type[body] = joint_type;
+  return FLASH_OK;
+}
+void flash_urdf_free(flash_urdf* u) { delete u; }
+int flash_model_load_urdf(const char* urdf_path, const char* const* package_dirs, int32_t n_package_dirs, const flash_options* opt, flash_ctx** out) {
+  flash_urdf* u = nullptr;
+  int rc = flash_urdf_load(urdf_path, package_dirs, n_package_dirs, &u);
+  if (rc) return rc;
+  rc = flash_model_create(flash_urdf_desc(u), opt, out);
+  flash_urdf_free(u);
+  return rc;
+}
+
+int flash_read_point_cloud(const char* path, double origin[3], double* xyz, double* rgb, int64_t cap, int64_t* n) {
+  if (!path || !n || cap < 0 || (cap > 0 && !xyz)) return fail(nullptr, FLASH_ERR_INVALID, "flash_read_point_cloud: bad arguments");
+  std::vector<double> p, c; std::string err; double org[3] = {0, 0, 0};
+  if (!flashurdf::read_point_cloud(path, p, rgb ? &c : nullptr, org, err)) return fail(nullptr, FLASH_ERR_IO, err);
+  if (origin) { origin[0] = org[0]; origin[1] = org[1]; origin[2] = org[2]; }
+  *n = (int64_t)(p.size() / 3);
+  const size_t m = (size_t)std::min<int64_t>(cap, *n);
+  if (m) std::memcpy(xyz, p.data(), m * 3 * sizeof(double));
+  if (m && rgb) std::memcpy(rgb, c.data(), m * 3 * sizeof(double));
+  return FLASH_OK;
+}
+
 int flash_num_positions(const flash_ctx* ctx) { return ctx ? ctx->hm.M.nq : FLASH_ERR_INVALID; }
 int flash_num_states(const flash_ctx* ctx) { return ctx ? ctx->hm.M.nx : FLASH_ERR_INVALID; }
 int flash_num_surfaces(const flash_ctx* ctx) { return ctx ? ctx->hm.M.n_surfaces : FLASH_ERR_INVALID; }
@@ -674,6 +720,24 @@ int flash_points_set_async_f32(flash_ctx* ctx, const float* xyz, int64_t n) {
   ctx->back_pending = true;
   return FLASH_OK;
 }
+
+static int points_set_file_impl(flash_ctx* ctx, const char* path, double origin[3], bool async) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!path) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_file: null path");
+  std::vector<double> p; std::string err; double org[3] = {0, 0, 0};
+  if (!flashurdf::read_point_cloud(path, p, nullptr, org, err)) return fail(ctx, FLASH_ERR_IO, err);
+  if (origin) { origin[0] = org[0]; origin[1] = org[1]; origin[2] = org[2]; }
+  const double* ptrs[1] = {p.data()};
+  const int64_t counts[1] = {(int64_t)(p.size() / 3)};
+  // the parsed rows are pageable: ingest copies them into the ctx's pinned ring before it returns, the DMA reads the ring
+  int rc = ingest<double>(ctx, ctx->ps[ctx->cur ^ 1], ptrs, counts, 1); if (rc) return rc;
+  if (async) { ctx->back_pending = true; return FLASH_OK; }
+  rc = swap_sets(ctx); if (rc) return rc;
+  CU(cudaEventSynchronize(ctx->ps[ctx->cur].ready));
+  return FLASH_OK;
+}
+int flash_points_set_file(flash_ctx* ctx, const char* path, double origin[3]) { return points_set_file_impl(ctx, path, origin, false); }
+int flash_points_set_file_async(flash_ctx* ctx, const char* path, double origin[3]) { return points_set_file_impl(ctx, path, origin, true); }
 
 int flash_points_swap(flash_ctx* ctx) {
   if (!ctx) return FLASH_ERR_INVALID;

@@ -21,6 +21,8 @@ SYMBOLS = [
     "flash_grid_report", "flash_grid_download", "flash_contour_mesh",
     "flash_points_set_async", "flash_points_set_async_f32", "flash_points_swap", "flash_points_sync",
     "flash_frames_set", "flash_frames_set_async", "flash_num_frames", "flash_cost_grad_frames",
+    "flash_urdf_load", "flash_urdf_desc", "flash_urdf_body_name", "flash_urdf_surface_mesh", "flash_urdf_set_joint_type", "flash_urdf_free",
+    "flash_model_load_urdf", "flash_read_point_cloud", "flash_points_set_file", "flash_points_set_file_async",
 ]
 
 _lib = None
@@ -46,6 +48,16 @@ def lib():
     L.flash_points_set.argtypes = [vp, c_double_p, C.c_int64]
     L.flash_points_set_f32.argtypes = [vp, C.POINTER(C.c_float), C.c_int64]
     L.flash_points_set_device.argtypes = [vp, vp, C.c_int64]
+    L.flash_urdf_load.argtypes = [C.c_char_p, C.POINTER(C.c_char_p), C.c_int32, C.POINTER(vp)]
+    L.flash_urdf_desc.argtypes = [vp]; L.flash_urdf_desc.restype = C.POINTER(ModelDesc)
+    L.flash_urdf_body_name.argtypes = [vp, C.c_int32]; L.flash_urdf_body_name.restype = C.c_char_p
+    L.flash_urdf_surface_mesh.argtypes = [vp, C.c_int32]; L.flash_urdf_surface_mesh.restype = C.c_char_p
+    L.flash_urdf_set_joint_type.argtypes = [vp, C.c_int32, C.c_int32]
+    L.flash_urdf_free.argtypes = [vp]; L.flash_urdf_free.restype = None
+    L.flash_model_load_urdf.argtypes = [C.c_char_p, C.POINTER(C.c_char_p), C.c_int32, C.POINTER(Options), C.POINTER(vp)]
+    L.flash_read_point_cloud.argtypes = [C.c_char_p, c_double_p, c_double_p, c_double_p, C.c_int64, C.POINTER(C.c_int64)]
+    L.flash_points_set_file.argtypes = [vp, C.c_char_p, c_double_p]
+    L.flash_points_set_file_async.argtypes = [vp, C.c_char_p, c_double_p]
     L.flash_points_set_async.argtypes = [vp, c_double_p, C.c_int64]
     L.flash_points_set_async_f32.argtypes = [vp, C.POINTER(C.c_float), C.c_int64]
     L.flash_points_swap.argtypes = [vp]

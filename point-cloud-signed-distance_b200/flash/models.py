@@ -2,8 +2,6 @@
 import json
 import math
 import os
-import struct
-import xml.etree.ElementTree as ET
 
 import numpy as np
 
@@ -114,119 +112,37 @@ def change_joint_type_(manip, body_index, joint_type):
 
 
 # ------------------------------------------------------------------ URDF + STL ingestion
-def _rpy_to_R(r, p, y):
-    cr, sr, cp, sp, cy, sy = math.cos(r), math.sin(r), math.cos(p), math.sin(p), math.cos(y), math.sin(y)
-    Rx = np.array([[1, 0, 0], [0, cr, -sr], [0, sr, cr]])
-    Ry = np.array([[cp, 0, sp], [0, 1, 0], [-sp, 0, cp]])
-    Rz = np.array([[cy, -sy, 0], [sy, cy, 0], [0, 0, 1]])
-    return Rz @ Ry @ Rx
-
-
-def _origin(elem):
-    T = _identity34()
-    if elem is None:
-        return T
-    o = elem.find("origin")
-    if o is None:
-        return T
-    xyz = [float(v) for v in o.get("xyz", "0 0 0").split()]
-    rpy = [float(v) for v in o.get("rpy", "0 0 0").split()]
-    T[:, :3] = _rpy_to_R(*rpy)
-    T[:, 3] = xyz
-    return T
-
-
-def read_stl(path):
-    """Binary or ASCII STL -> welded unique vertices (n, 3) float64."""
-    data = open(path, "rb").read()
-    ntri = struct.unpack("<I", data[80:84])[0] if len(data) >= 84 else -1
-    if ntri >= 0 and len(data) == 84 + 50 * ntri:
-        rec = np.frombuffer(data, dtype=np.dtype([("n", "<f4", 3), ("v", "<f4", (3, 3)), ("a", "<u2")]), count=ntri, offset=84)
-        verts = rec["v"].reshape(-1, 3).astype(np.float64)
-    else:
-        verts = []
-        for line in data.decode("ascii", "replace").splitlines():
-            t = line.split()
-            if len(t) == 4 and t[0] == "vertex":
-                verts.append([float(t[1]), float(t[2]), float(t[3])])
-        verts = np.array(verts, float)
-    if len(verts) == 0:
-        raise IOError("no vertices in STL %s" % path)
-    _, idx = np.unique(verts, axis=0, return_index=True)
-    return verts[np.sort(idx)]
-
-
-def read_obj_vertices(path):
-    verts = [[float(v) for v in line.split()[1:4]] for line in open(path) if line.startswith("v ")]
-    verts = np.array(verts, float)
-    _, idx = np.unique(verts, axis=0, return_index=True)
-    return verts[np.sort(idx)]
-
-
-def _resolve(filename, urdf_dir, package_path):
-    if filename.startswith("package://"):
-        rel = filename[len("package://"):]
-        for root in list(package_path) + [urdf_dir]:
-            cand = os.path.join(root, rel)
-            if os.path.exists(cand):
-                return cand
-            # also accept a package_path entry that IS the package directory
-            parts = rel.split("/", 1)
-            if len(parts) == 2 and os.path.exists(os.path.join(root, parts[1])):
-                return os.path.join(root, parts[1])
-        raise IOError("cannot resolve %s in package_path %r" % (filename, list(package_path)))
-    return filename if os.path.isabs(filename) else os.path.join(urdf_dir, filename)
-
-
 def load_urdf(filename, package_path=()):
     """src/models.jl:166-171: parse_urdf + parse_urdf_visuals + extract_convex_surfaces.
 
-    Each <visual> mesh becomes a ConvexGeometry (the convex hull of its vertices, the
-    EnhancedGJK.NeighborMesh semantics of src/models.jl:152) whose frame is the visual origin.
-    The root link is welded to the world (RigidBodyDynamics.parse_urdf)."""
-    root = ET.parse(filename).getroot()
-    urdf_dir = os.path.dirname(os.path.abspath(filename))
-    links = {l.get("name"): l for l in root.findall("link")}
-    joints = root.findall("joint")
-    children = {j.find("child").get("link") for j in joints}
-    roots = [n for n in links if n not in children]
-    if len(roots) != 1:
-        raise ValueError("URDF must have exactly one root link, found %r" % roots)
-    by_parent = {}
-    for j in joints:
-        by_parent.setdefault(j.find("parent").get("link"), []).append(j)
-    bodies, index = [Body(roots[0], -1, JOINT_FIXED)], {roots[0]: 0}
-    queue = [roots[0]]
-    while queue:
-        name = queue.pop(0)
-        for j in by_parent.get(name, []):
-            child = j.find("child").get("link")
-            jt = j.get("type")
-            if jt in ("revolute", "continuous"):
-                kind = JOINT_REVOLUTE
-            elif jt == "fixed":
-                kind = JOINT_FIXED
-            elif jt == "floating":
-                kind = JOINT_QUAT_FLOATING
-            else:
-                raise ValueError("unsupported URDF joint type %r (joint %s)" % (jt, j.get("name")))
-            ax = j.find("axis")
-            axis = [float(v) for v in ax.get("xyz").split()] if ax is not None else [1.0, 0.0, 0.0]
-            bodies.append(Body(child, index[name], kind, axis, _origin(j)))
-            index[child] = len(bodies) - 1
-            queue.append(child)
-    surfaces = []
-    for body in bodies:  # vis_data is keyed by link frame in mechanism order
-        for vis in links[body.name].findall("visual"):
-            mesh = vis.find("geometry/mesh")
-            if mesh is None:
-                continue
-            path = _resolve(mesh.get("filename"), urdf_dir, package_path)
-            verts = read_obj_vertices(path) if path.lower().endswith(".obj") else read_stl(path)
-            sc = mesh.get("scale")
-            if sc:
-                verts = verts * np.array([float(v) for v in sc.split()])
-            surfaces.append(ConvexGeometry(verts, index[body.name], _origin(vis)))
+    The parsing lives in the library (flash_urdf_load, csrc/flash_urdf.h: XML, binary / ASCII STL, OBJ, welding,
+    `package://` resolution); this wrapper only turns the returned flash_model_desc into a Manipulator.
+    Each <visual> mesh becomes a ConvexGeometry (the convex hull of its vertices, the EnhancedGJK.NeighborMesh
+    semantics of src/models.jl:152) whose frame is the visual origin; the root link is welded to the world
+    (RigidBodyDynamics.parse_urdf)."""
+    import ctypes as C
+    from . import _lib
+    L = _lib.lib()
+    dirs = [os.fsencode(os.path.abspath(p)) for p in package_path]
+    arr = (C.c_char_p * max(len(dirs), 1))(*dirs)
+    h = C.c_void_p()
+    rc = L.flash_urdf_load(os.fsencode(os.path.abspath(filename)), arr, len(dirs), C.byref(h))
+    if rc != 0:
+        msg = L.flash_last_error(None)
+        raise IOError("flash_urdf_load failed (%d): %s" % (rc, msg.decode() if msg else "?"))
+    try:
+        d = L.flash_urdf_desc(h).contents
+        bodies = []
+        for b in range(d.n_bodies):
+            bodies.append(Body(L.flash_urdf_body_name(h, b).decode(), d.body_parent[b], d.joint_type[b],
+                               [d.joint_axis[3 * b + k] for k in range(3)], np.array([d.joint_to_parent[12 * b + k] for k in range(12)]).reshape(3, 4)))
+        surfaces = []
+        for s_ in range(d.n_surfaces):
+            p0, p1 = d.point_offset[s_], d.point_offset[s_ + 1]
+            verts = np.array([d.points[k] for k in range(3 * p0, 3 * p1)]).reshape(-1, 3)
+            surfaces.append(ConvexGeometry(verts, d.surface_body[s_], np.array([d.surface_frame[12 * s_ + k] for k in range(12)]).reshape(3, 4)))
+    finally:
+        L.flash_urdf_free(h)
     return Manipulator(Mechanism(bodies), surfaces)
 
 

@@ -502,3 +502,41 @@ def test_deterministic_mode_is_bit_reproducible():
     xs[4:7] = cloud.mean(0)
     ends = [flash.tracking.estimate_state(ms, cloud, xs, solver=solver, on_device=True) for _ in range(3)]
     assert np.array_equal(ends[0], ends[1]) and np.array_equal(ends[0], ends[2])
+
+
+def test_model_from_urdf_and_points_from_file_through_the_c_abi(tmp_path):
+    """flash_model_load_urdf (C++ URDF / STL ingestion, row F2) and flash_points_set_file (row F3: the text reader
+    feeding the pinned staging ring) give the same cost and gradient as the Python-built model with points handed
+    over in memory -- and the oracle's."""
+    import ctypes as C
+    from flash import _lib
+    from flash._desc import Options, c_double_p
+    L = _lib.lib()
+    rng = np.random.default_rng(51)
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    urdf = os.path.join(gold, "IRB140", "urdf", "irb_140_convhull.urdf")
+    opt = Options(); L.flash_options_default(C.byref(opt))
+    ctx = C.c_void_p()
+    arr = (C.c_char_p * 1)(gold.encode())
+    assert L.flash_model_load_urdf(urdf.encode(), arr, 1, C.byref(opt), C.byref(ctx)) == 0, L.flash_last_error(None)
+    assert L.flash_num_states(ctx) == 6 and L.flash_num_surfaces(ctx) == 7
+    pts = _points(rng, 30011, [-0.6, -0.6, -0.2], [0.8, 0.6, 1.0])
+    path = tmp_path / "cloud.txt"
+    with open(path, "w") as f:
+        f.write("0.0, 1.5, 0.5\n")
+        for p in pts:
+            f.write("%r, %r, %r, 0.5, 0.5, 0.5\n" % tuple(float(v) for v in p))
+    origin = np.zeros(3)
+    assert L.flash_points_set_file(ctx, str(path).encode(), origin.ctypes.data_as(c_double_p)) == 0, L.flash_last_error(ctx)
+    assert np.allclose(origin, [0.0, 1.5, 0.5]) and L.flash_num_points(ctx) == len(pts)
+    X = rng.uniform(-1.0, 1.0, (2, 6))
+    cost = np.empty(2); grad = np.empty((2, 6))
+    assert L.flash_cost_grad(ctx, X.ctypes.data_as(c_double_p), 2, 10.0, cost.ctypes.data_as(c_double_p), grad.ctypes.data_as(c_double_p), None) == 0
+    m = flash.models.irb140()
+    c_ref, g_ref, _ = flash.gradientdescent.CostFunctor(m, pts).batch(X)
+    assert np.allclose(cost, c_ref, rtol=1e-12) and np.abs(grad - g_ref).max() <= 1e-9 * np.abs(g_ref).max()
+    o = ol.Oracle(m)
+    co, go = o.cost_grad(X[1], pts, method="dual", mode=ol.GJK)
+    assert abs(cost[1] - co) <= RTOL * abs(co) and np.abs(grad[1] - go).max() <= RTOL * np.abs(go).max()
+    assert L.flash_points_set_file(ctx, b"/nonexistent/cloud.txt", None) == -7 and b"cannot open" in L.flash_last_error(ctx)
+    L.flash_destroy(ctx)

@@ -91,7 +91,7 @@ def test_load_urdf_with_binary_stl(tmp_path):
     assert len(m.surfaces[0].vertices) == 4 and np.allclose(m.surfaces[1].vertices.max(), 2.0)   # welded 12 -> 4, scaled
     assert np.allclose(m.surfaces[0].frame[:, 3], [0, 0, 0.5]) and abs(m.surfaces[0].frame[0, 1] + 1) < 1e-4
     assert np.allclose(m.mechanism.bodies[1].joint_to_parent[:, 3], [1, 2, 3])
-    with pytest.raises(ValueError, match="unsupported URDF joint"):
+    with pytest.raises(IOError, match="unsupported URDF joint"):
         bad = tmp_path / "bad.urdf"
         bad.write_text(urdf.read_text().replace('type="revolute"', 'type="prismatic"'))
         flash.models.load_urdf(str(bad), package_path=[str(tmp_path)])
@@ -106,6 +106,99 @@ def test_read_point_cloud():
     assert "containing 2 points" in repr(pc)
     gold = os.path.join(os.path.dirname(__file__), "golden", "squishable_unsquished_xyz.npy")
     assert np.load(gold).shape == (25571, 3)      # examples/squishable.ipynb cell 4
+
+
+def test_read_point_cloud_through_the_c_abi(tmp_path):
+    """flash_read_point_cloud (csrc/flash_urdf.h), the reader behind flash_points_set_file: same numbers as the
+    stream reader, FLASH_ERR_IO for missing / malformed files."""
+    rng = np.random.default_rng(3)
+    xyz = rng.uniform(-1, 1, (257, 3)); rgb = rng.uniform(0, 1, (257, 3))
+    path = tmp_path / "cloud_xyzrgb.txt"
+    with open(path, "w") as f:
+        f.write("1.38246, 0.768824, 1.48581\n")
+        for p, c in zip(xyz, rgb):
+            f.write(", ".join(repr(float(v)) for v in list(p) + list(c)) + "\n")
+    pc = flash.depthdata.read_point_cloud(str(path))
+    ref = flash.depthdata.read_point_cloud(open(path))
+    assert np.array_equal(pc.camera_origin, ref.camera_origin) and np.array_equal(pc.positions, ref.positions) and np.array_equal(pc.colors, ref.colors)
+    assert np.array_equal(pc.positions, xyz) and "containing 257 points" in repr(pc)
+    with pytest.raises(IOError, match="cannot open"):
+        flash.depthdata.read_point_cloud(str(tmp_path / "missing.txt"))
+    bad = tmp_path / "bad.txt"
+    bad.write_text("0, 0, 0\n1, 2, 3\n")
+    with pytest.raises(IOError, match="does not hold"):
+        flash.depthdata.read_point_cloud(str(bad))
+
+
+GOLD_URDF = os.path.join(os.path.dirname(__file__), "golden", "IRB140", "urdf", "irb_140_convhull.urdf")
+
+
+def test_c_urdf_loader_reproduces_the_committed_fixture_and_the_survey_tables():
+    """flash_urdf_load (csrc/flash_urdf.h) on the reference's own irb_140_convhull.urdf + *_chull.stl (fixtures copied
+    from examples/data/IRB140/): the description equals the committed JSON fixture the GPU tests use, the joint chain
+    and the visual origins are those of SURVEY 9 (examples/data/IRB140/urdf/irb_140_convhull.urdf:290-330), every mesh
+    welds to 52 vertices with the tabulated AABB, and the *_chull.obj twins hold the same vertex sets."""
+    m = flash.models.load_urdf(GOLD_URDF, package_path=[os.path.join(os.path.dirname(__file__), "golden")])
+    ref = flash.models.irb140()
+    assert repr(m) == "Manipulator with 8 links and 7 surfaces"      # examples/irb140.ipynb:261
+    assert [b.name for b in m.mechanism.bodies] == ["base_link"] + ["link_%d" % k for k in range(1, 7)]
+    for b, r in zip(m.mechanism.bodies, ref.mechanism.bodies):
+        assert (b.name, b.parent, b.joint_type) == (r.name, r.parent, r.joint_type)
+        assert np.array_equal(b.axis, r.axis) and np.allclose(b.joint_to_parent, r.joint_to_parent, rtol=0, atol=1e-15)
+    for s_, r in zip(m.surfaces, ref.surfaces):
+        assert s_.body == r.body and np.allclose(s_.frame, r.frame, rtol=0, atol=1e-15)
+        assert np.array_equal(s_.vertices, r.vertices)                # fp32 STL values, bit for bit, same welding order
+    # SURVEY 9: joints
+    joints = [((0, 0, 0.1095), (-1.57079, 0, 0), (0, -1, 0)), ((0.07, -0.2425, 0), (0, 0, 0), (0, 0, 1)), ((0, -0.360, 0), (0, 0, 0), (0, 0, 1)),
+              ((0.2185, 0, 0), (0, 0, 0), (1, 0, 0)), ((0.1615, 0, 0), (0, 0, 0), (0, 0, -1)), ((0.065, 0, 0), (0, 0, 0), (1, 0, 0))]
+    for k, (xyz, rpy, axis) in enumerate(joints):
+        b = m.mechanism.bodies[k + 1]
+        assert b.parent == k and b.joint_type == flash.JOINT_REVOLUTE and np.allclose(b.axis, axis) and np.allclose(b.joint_to_parent[:, 3], xyz)
+        c, s = np.cos(rpy[0]), np.sin(rpy[0])
+        assert np.allclose(b.joint_to_parent[:, :3], [[1, 0, 0], [0, c, -s], [0, s, c]], atol=1e-15)
+    # SURVEY 9: visual origins and mesh AABBs (metres, mesh frame)
+    vis = [(0, 0, 0), (0, 0.1095, 0), (-0.07, 0.352, 0), (-0.07, 0.712, 0), (-0.2885, 0.712, 0), (-0.450, 0.712, 0), (-0.515, 0.712, 0)]
+    aabb = [((-0.3132, -0.1525, -0.2019), (0.1784, 0.0005, 0.2018)), ((-0.1556, -0.4543, -0.1365), (0.1943, -0.0889, 0.2044)),
+            ((-0.0293, -0.8027, -0.1755), (0.1540, -0.2831, 0.0989)), ((-0.0790, -0.8091, -0.0832), (0.3088, -0.6090, 0.0850)),
+            ((0.2885, -0.7681, -0.0645), (0.5078, -0.6559, 0.0705)), ((0.4079, -0.7543, -0.0155), (0.4922, -0.6697, 0.0166)),
+            ((0.4696, -0.7370, -0.0250), (0.5150, -0.6867, 0.0250))]
+    names = ["base_link", "link1", "link2", "link3", "link4", "link5", "link6"]
+    for k, s_ in enumerate(m.surfaces):
+        assert s_.body == k and np.allclose(s_.frame[:, 3], vis[k]) and len(s_.vertices) == 52
+        assert np.allclose(s_.vertices.min(0), aabb[k][0], atol=6e-5) and np.allclose(s_.vertices.max(0), aabb[k][1], atol=6e-5)
+        obj = np.array([[float(v) for v in l.split()[1:4]] for l in open(os.path.join(os.path.dirname(GOLD_URDF), "meshes", names[k] + "_chull.obj")) if l.startswith("v ")])
+        obj = np.unique(obj, axis=0)
+        assert len(obj) == 52
+        d = np.abs(obj[:, None, :] - s_.vertices[None, :, :]).max(2)
+        assert d.min(1).max() < 1e-6 and d.min(0).max() < 1e-6      # the same 52 points (OBJ text keeps 6 digits)
+    # the base link's visual origin carries the literal -1.57079 (not -pi/2)
+    c, s = np.cos(-1.57079), np.sin(-1.57079)
+    assert np.allclose(m.surfaces[0].frame[:, :3], [[1, 0, 0], [0, c, -s], [0, s, c]], atol=1e-15)
+
+
+def test_c_urdf_loader_error_paths(tmp_path):
+    import ctypes as C
+    from flash import _lib
+    L = _lib.lib()
+    h = C.c_void_p()
+    assert L.flash_urdf_load(b"/nonexistent/robot.urdf", None, 0, C.byref(h)) == -7 and b"cannot open" in L.flash_last_error(None)   # FLASH_ERR_IO
+    bad = tmp_path / "bad.urdf"
+    bad.write_text("<robot><link name='a'></robot>")
+    assert L.flash_urdf_load(str(bad).encode(), None, 0, C.byref(h)) == -7 and b"does not match" in L.flash_last_error(None)
+    two = tmp_path / "two.urdf"
+    two.write_text("<robot><link name='a'/><link name='b'/></robot>")
+    assert L.flash_urdf_load(str(two).encode(), None, 0, C.byref(h)) == -7 and b"exactly one root" in L.flash_last_error(None)
+    nomesh = tmp_path / "nomesh.urdf"
+    nomesh.write_text("<robot><link name='a'><visual><geometry><mesh filename='package://p/x.stl'/></geometry></visual></link></robot>")
+    assert L.flash_urdf_load(str(nomesh).encode(), None, 0, C.byref(h)) == -7 and b"cannot resolve" in L.flash_last_error(None)
+    ok = C.c_void_p()
+    gold_dir = os.path.join(os.path.dirname(__file__), "golden").encode()
+    arr = (C.c_char_p * 1)(gold_dir)
+    assert L.flash_urdf_load(GOLD_URDF.encode(), arr, 1, C.byref(ok)) == 0
+    assert L.flash_urdf_set_joint_type(ok, 0, 2) == 0 and L.flash_urdf_desc(ok).contents.joint_type[0] == 2     # floating base
+    assert L.flash_urdf_set_joint_type(ok, 99, 2) == -1
+    assert L.flash_urdf_surface_mesh(ok, 3).endswith(b"link3_chull.stl")
+    L.flash_urdf_free(ok)
 
 
 def test_packed_model_layout():
