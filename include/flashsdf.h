@@ -268,6 +268,8 @@ int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solve
 int flash_comm_unique_id(void* id128);             /* rank 0 creates, caller broadcasts */
 int flash_comm_init(flash_ctx* ctx, int32_t rank, int32_t world, const void* id128);
 int flash_comm_world(const flash_ctx* ctx);
+/* devices of a single-process multi-GPU context (flash_options.n_devices); 1 for an ordinary context */
+int flash_num_devices(const flash_ctx* ctx);
 
 /* ---- measurement hooks (CUDA events on the ctx stream) ---- */
 typedef struct flash_timing {

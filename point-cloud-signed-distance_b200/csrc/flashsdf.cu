@@ -103,6 +103,15 @@ struct flash_ctx {
   int* d_qi = nullptr; size_t cap_qi = 0;
   // comm
   nccl_comm comm = nullptr; int rank = 0, world = 1;
+  double n_global = -1.0;   // points of all ranks in the current set (flash_estimate_state divides by it); < 0: not reduced yet
+  // single-process multi-GPU context (flash_options.n_devices > 1): the parent owns one full sub-context per device and no
+  // device state of its own; subs[0] additionally owns the table of every sub's accumulator pointer for the peer reduction
+  std::vector<flash_ctx*> subs;
+  flash_ctx* parent = nullptr;
+  double** d_peer_acc = nullptr; int peer_acc_C = 0;
+  cudaEvent_t ev_cost = nullptr, ev_red = nullptr;   // sub: cost kernel done; subs[0]: peer reduction done
+  std::vector<long long> shard_off;                  // parent: first point of every sub's shard (+ total), caller order
+  std::vector<int> frame_sub, frame_slot;            // parent: owner and local index of every frame of the current batch
   // measurement
   bool profiling = false;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // [5]: between group_kernel and cost_kernel
@@ -303,21 +312,6 @@ int run_allreduce(flash_ctx* ctx, int C) {
   if (!ctx->comm) return 0;
   int rc = g_nccl.AllReduce(ctx->d_acc, ctx->d_acc, (size_t)C * ctx->hm.M.acc_len, NCCL_FLOAT64, NCCL_SUM, ctx->comm, ctx->stream);
   if (rc != 0) return fail(ctx, FLASH_ERR_NCCL, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"));
-  return 0;
-}
-
-// prepare -> main -> (allreduce) -> epilogue on the ctx stream, X already on the device
-int pipeline(flash_ctx* ctx, int C, double w_def, bool grad, int32_t* d_argmin, int cfg_per_frame = 0) {
-  int rc;
-  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[0], ctx->stream));
-  if ((rc = run_prepare(ctx, C, true))) return rc;   // also zeroes the accumulators
-  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[1], ctx->stream));
-  if ((rc = run_cost(ctx, C, grad, d_argmin, cfg_per_frame))) return rc;
-  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
-  if ((rc = run_allreduce(ctx, C))) return rc;
-  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[3], ctx->stream));
-  if ((rc = run_epilogue(ctx, C, w_def, grad))) return rc;
-  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[4], ctx->stream));
   return 0;
 }
 
@@ -541,6 +535,7 @@ static int swap_sets(flash_ctx* ctx) {
   if (old.ready) { CU(cudaEventRecord(old.retired, ctx->stream)); old.retired_valid = true; }
   ctx->cur ^= 1;
   ctx->back_pending = false;
+  ctx->n_global = -1.0;
   CU(cudaStreamWaitEvent(ctx->stream, ctx->ps[ctx->cur].ready, 0));
   return FLASH_OK;
 }
@@ -555,6 +550,12 @@ static int points_set_sync(flash_ctx* ctx, const T* xyz, int64_t n) {
   return FLASH_OK;
 }
 
+// multi-device forms (defined further down, next to the staged cost_grad they are built from)
+template <class T> static int multi_points_set(flash_ctx* ctx, const T* xyz, int64_t n, bool async);
+static int multi_swap(flash_ctx* ctx);
+static int multi_frames_set(flash_ctx* ctx, const double* const* xyz, const int64_t* counts, int32_t F, bool async);
+static int multi_create(const flash_model_desc* desc, const flash_options* opt, flash_ctx** out);
+
 // ================================================================================================
 extern "C" {
 
@@ -565,6 +566,7 @@ const char* flash_last_error(const flash_ctx* ctx) { return ctx ? ctx->err.c_str
 int flash_model_create(const flash_model_desc* desc, const flash_options* opt, flash_ctx** out) {
   if (!out) return fail(nullptr, FLASH_ERR_INVALID, "null out pointer");
   *out = nullptr;
+  if (opt && opt->abi_version == FLASHSDF_ABI_VERSION && opt->n_devices > 1) return multi_create(desc, opt, out);
   flash_ctx* ctx = new flash_ctx;
   std::string err;
   if (!build_model(desc, opt, ctx->hm, err)) { delete ctx; return fail(nullptr, FLASH_ERR_INVALID, err); }
@@ -615,6 +617,14 @@ int flash_model_create(const flash_model_desc* desc, const flash_options* opt, f
 
 void flash_destroy(flash_ctx* ctx) {
   if (!ctx) return;
+  if (!ctx->subs.empty()) {
+    for (flash_ctx* sub : ctx->subs) flash_destroy(sub);
+    delete ctx;
+    return;
+  }
+  if (ctx->d_peer_acc) { cudaSetDevice(ctx->device); cudaFree(ctx->d_peer_acc); }
+  if (ctx->ev_cost) cudaEventDestroy(ctx->ev_cost);
+  if (ctx->ev_red) cudaEventDestroy(ctx->ev_red);
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
@@ -687,23 +697,32 @@ int flash_read_point_cloud(const char* path, double origin[3], double* xyz, doub
 int flash_num_positions(const flash_ctx* ctx) { return ctx ? ctx->hm.M.nq : FLASH_ERR_INVALID; }
 int flash_num_states(const flash_ctx* ctx) { return ctx ? ctx->hm.M.nx : FLASH_ERR_INVALID; }
 int flash_num_surfaces(const flash_ctx* ctx) { return ctx ? ctx->hm.M.n_surfaces : FLASH_ERR_INVALID; }
-int64_t flash_num_points(const flash_ctx* ctx) { return ctx ? ctx->ps[ctx->cur].n : FLASH_ERR_INVALID; }
+int64_t flash_num_points(const flash_ctx* ctx) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (ctx->subs.empty()) return ctx->ps[ctx->cur].n;
+  int64_t n = 0;
+  for (const flash_ctx* sub : ctx->subs) n += sub->ps[sub->cur].n;
+  return n;
+}
 
 int flash_points_set(flash_ctx* ctx, const double* xyz, int64_t n) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set: bad arguments");
+  if (!ctx->subs.empty()) return multi_points_set<double>(ctx, xyz, n, false);
   return points_set_sync<double>(ctx, xyz, n);
 }
 
 int flash_points_set_f32(flash_ctx* ctx, const float* xyz, int64_t n) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_f32: bad arguments");
+  if (!ctx->subs.empty()) return multi_points_set<float>(ctx, xyz, n, false);
   return points_set_sync<float>(ctx, xyz, n);
 }
 
 int flash_points_set_async(flash_ctx* ctx, const double* xyz, int64_t n) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_async: bad arguments");
+  if (!ctx->subs.empty()) return multi_points_set<double>(ctx, xyz, n, true);
   const double* ptrs[1] = {xyz};
   const int64_t counts[1] = {n};
   int rc = ingest<double>(ctx, ctx->ps[ctx->cur ^ 1], ptrs, counts, 1); if (rc) return rc;
@@ -714,6 +733,7 @@ int flash_points_set_async(flash_ctx* ctx, const double* xyz, int64_t n) {
 int flash_points_set_async_f32(flash_ctx* ctx, const float* xyz, int64_t n) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (n < 0 || (n > 0 && !xyz)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_async_f32: bad arguments");
+  if (!ctx->subs.empty()) return multi_points_set<float>(ctx, xyz, n, true);
   const float* ptrs[1] = {xyz};
   const int64_t counts[1] = {n};
   int rc = ingest<float>(ctx, ctx->ps[ctx->cur ^ 1], ptrs, counts, 1); if (rc) return rc;
@@ -727,6 +747,7 @@ static int points_set_file_impl(flash_ctx* ctx, const char* path, double origin[
   std::vector<double> p; std::string err; double org[3] = {0, 0, 0};
   if (!flashurdf::read_point_cloud(path, p, nullptr, org, err)) return fail(ctx, FLASH_ERR_IO, err);
   if (origin) { origin[0] = org[0]; origin[1] = org[1]; origin[2] = org[2]; }
+  if (!ctx->subs.empty()) return multi_points_set<double>(ctx, p.data(), (int64_t)(p.size() / 3), async);
   const double* ptrs[1] = {p.data()};
   const int64_t counts[1] = {(int64_t)(p.size() / 3)};
   // the parsed rows are pageable: ingest copies them into the ctx's pinned ring before it returns, the DMA reads the ring
@@ -741,6 +762,7 @@ int flash_points_set_file_async(flash_ctx* ctx, const char* path, double origin[
 
 int flash_points_swap(flash_ctx* ctx) {
   if (!ctx) return FLASH_ERR_INVALID;
+  if (!ctx->subs.empty()) return multi_swap(ctx);
   if (!ctx->back_pending) return fail(ctx, FLASH_ERR_STATE, "flash_points_swap: no flash_points_set_async / flash_frames_set_async pending");
   CU(cudaSetDevice(ctx->device));
   return swap_sets(ctx);
@@ -748,6 +770,7 @@ int flash_points_swap(flash_ctx* ctx) {
 
 int flash_points_sync(flash_ctx* ctx) {
   if (!ctx) return FLASH_ERR_INVALID;
+  if (!ctx->subs.empty()) { for (flash_ctx* sub : ctx->subs) { int rc = flash_points_sync(sub); if (rc) { ctx->err = sub->err; return rc; } } return FLASH_OK; }
   CU(cudaSetDevice(ctx->device));
   CU(cudaStreamSynchronize(ctx->copy_stream));
   return FLASH_OK;
@@ -764,6 +787,7 @@ static int frames_check(flash_ctx* ctx, const void* const* xyz, const int64_t* c
 int flash_frames_set(flash_ctx* ctx, const double* const* xyz, const int64_t* counts, int32_t F) {
   if (!ctx) return FLASH_ERR_INVALID;
   int rc = frames_check(ctx, (const void* const*)xyz, counts, F, "flash_frames_set"); if (rc) return rc;
+  if (!ctx->subs.empty()) return multi_frames_set(ctx, xyz, counts, F, false);
   rc = ingest<double>(ctx, ctx->ps[ctx->cur ^ 1], xyz, counts, F); if (rc) return rc;
   rc = swap_sets(ctx); if (rc) return rc;
   CU(cudaEventSynchronize(ctx->ps[ctx->cur].ready));
@@ -773,17 +797,23 @@ int flash_frames_set(flash_ctx* ctx, const double* const* xyz, const int64_t* co
 int flash_frames_set_async(flash_ctx* ctx, const double* const* xyz, const int64_t* counts, int32_t F) {
   if (!ctx) return FLASH_ERR_INVALID;
   int rc = frames_check(ctx, (const void* const*)xyz, counts, F, "flash_frames_set_async"); if (rc) return rc;
+  if (!ctx->subs.empty()) return multi_frames_set(ctx, xyz, counts, F, true);
   rc = ingest<double>(ctx, ctx->ps[ctx->cur ^ 1], xyz, counts, F); if (rc) return rc;
   ctx->back_pending = true;
   return FLASH_OK;
 }
 
-int flash_num_frames(const flash_ctx* ctx) { return ctx ? (ctx->ps[ctx->cur].set ? ctx->ps[ctx->cur].ft.n_frames : 0) : FLASH_ERR_INVALID; }
+int flash_num_frames(const flash_ctx* ctx) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!ctx->subs.empty()) return ctx->frame_sub.empty() ? (ctx->shard_off.empty() ? 0 : 1) : (int)ctx->frame_sub.size();
+  return ctx->ps[ctx->cur].set ? ctx->ps[ctx->cur].ft.n_frames : 0;
+}
 
 int flash_points_set_device(flash_ctx* ctx, const void* device_float4, int64_t n) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (n < 0 || (n > 0 && !device_float4)) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_device: bad arguments");
   if (((uintptr_t)device_float4 & 15) != 0) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_device: pointer must be 16-byte aligned");
+  if (!ctx->subs.empty()) return fail(ctx, FLASH_ERR_INVALID, "flash_points_set_device: a multi-device context shards host points; give each device its own single-device context for device-resident clouds");
   CU(cudaSetDevice(ctx->device));
   flash_ctx::PointSet& P = ctx->ps[ctx->cur ^ 1];
   int rc = set_alloc(ctx, P, 32); if (rc) return rc;
@@ -807,7 +837,12 @@ int flash_points_set_device(flash_ctx* ctx, const void* device_float4, int64_t n
   return FLASH_OK;
 }
 
-static int cost_grad_impl(flash_ctx* ctx, const double* X, int32_t C, int cfg_per_frame, double w_def, double* cost, double* grad, int32_t* argmin, const char* who) {
+// flash_cost_grad in stages, so that a multi-device parent can run them device by device around one reduction:
+//   cg_begin   X -> device, prepare, group pre-pass, cost kernel (all enqueued, nothing waits)
+//   (reduction: ncclAllReduce across processes, or the peer reduction across the parent's devices)
+//   cg_end     epilogue + results into the pinned staging buffer (enqueued)
+//   cg_finish  wait, hand the results to the caller
+static int cg_begin(flash_ctx* ctx, const double* X, int32_t C, int cfg_per_frame, bool grad, bool want_argmin) {
   const ModelC& M = ctx->hm.M;
   const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
   CU(cudaSetDevice(ctx->device));
@@ -817,26 +852,239 @@ static int cost_grad_impl(flash_ctx* ctx, const double* X, int32_t C, int cfg_pe
   std::memcpy(ctx->h_pin, X, nX * sizeof(double));
   rc = pull_pinned(ctx, ctx->d_X, ctx->h_pin, nX); if (rc) return rc;
   int32_t* d_arg = nullptr;
-  if (argmin) {
+  if (want_argmin) {
     rc = ensure(ctx, ctx->d_argmin, ctx->cap_argmin, (size_t)C * (size_t)std::max<long long>(P.n, 1)); if (rc) return rc;
     d_arg = ctx->d_argmin;
   }
-  rc = pipeline(ctx, C, w_def, grad != nullptr, d_arg, cfg_per_frame); if (rc) return rc;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[0], ctx->stream));
+  if ((rc = run_prepare(ctx, C, true))) return rc;   // also zeroes the accumulators
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[1], ctx->stream));
+  if ((rc = run_cost(ctx, C, grad, d_arg, cfg_per_frame))) return rc;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[2], ctx->stream));
+  return 0;
+}
+static int cg_end(flash_ctx* ctx, int32_t C, double w_def, bool grad) {
+  const ModelC& M = ctx->hm.M;
+  CU(cudaSetDevice(ctx->device));
+  int rc;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[3], ctx->stream));
+  if ((rc = run_epilogue(ctx, C, w_def, grad))) return rc;
+  if (ctx->profiling) CU(cudaEventRecord(ctx->ev[4], ctx->stream));
+  const size_t nX = (size_t)C * M.nx;
   double* h_cost = ctx->h_pin + nX;
   double* h_grad = h_cost + C;
   CU(cudaMemcpyAsync(h_cost, ctx->d_cost, (size_t)C * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
   if (grad) CU(cudaMemcpyAsync(h_grad, ctx->d_grad, nX * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-  if (argmin && P.n > 0) CU(cudaMemcpyAsync(argmin, d_arg, (size_t)C * P.n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
-  rc = check_status(ctx); if (rc) return rc;   // synchronises the stream
-  std::memcpy(cost, h_cost, (size_t)C * sizeof(double));
-  if (grad) std::memcpy(grad, h_grad, nX * sizeof(double));
-  (void)who;
+  return 0;
+}
+static int cg_finish(flash_ctx* ctx, int32_t C, double* cost, double* grad) {
+  const ModelC& M = ctx->hm.M;
+  CU(cudaSetDevice(ctx->device));
+  int rc = check_status(ctx); if (rc) return rc;   // synchronises the stream
+  const size_t nX = (size_t)C * M.nx;
+  if (cost) std::memcpy(cost, ctx->h_pin + nX, (size_t)C * sizeof(double));
+  if (grad) std::memcpy(grad, ctx->h_pin + nX + C, nX * sizeof(double));
   return collect_timing(ctx);
 }
+static int cost_grad_impl(flash_ctx* ctx, const double* X, int32_t C, int cfg_per_frame, double w_def, double* cost, double* grad, int32_t* argmin, const char* who) {
+  const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
+  int rc = cg_begin(ctx, X, C, cfg_per_frame, grad != nullptr, argmin != nullptr); if (rc) return rc;
+  if ((rc = run_allreduce(ctx, C))) return rc;
+  if ((rc = cg_end(ctx, C, w_def, grad != nullptr))) return rc;
+  if (argmin && P.n > 0) CU(cudaMemcpyAsync(argmin, ctx->d_argmin, (size_t)C * P.n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  (void)who;
+  return cg_finish(ctx, C, cost, grad);
+}
+
+
+}  // extern "C" (templates below)
+
+// ================================================================================================
+// Single-process multi-GPU context (flash_options.n_devices > 1).  The reference's estimate_state is called from ONE
+// Julia process (src/tracking.jl:8-27), so the library shards inside: points in contiguous ranges of the caller's
+// order, frames round-robin, rays in contiguous ranges.  The accumulators (cost, wrenches, RBF adjoint sums: a few
+// KB per configuration) are combined by ONE kernel on the first device that reads every device's buffer through
+// NVLink peer memory in a fixed order and writes the sum back to all of them -- deterministic, no NCCL in this mode
+// (the process-per-GPU mode keeps ncclAllReduce, flash_comm_init).
+__global__ void reduce_peers_kernel(double* const* __restrict__ accs, int G, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    double s = 0.0;
+    for (int g = 0; g < G; ++g) s += accs[g][i];
+    for (int g = 0; g < G; ++g) accs[g][i] = s;
+  }
+}
+static int multi_fail(flash_ctx* P, flash_ctx* sub, int rc) { P->err = "device " + std::to_string(sub->device) + ": " + sub->err; return rc; }
+#define MSUB(call) do { int rc_ = (call); if (rc_) return multi_fail(ctx, sub, rc_); } while (0)
+
+// every sub's cost kernel has been enqueued: sum the accumulators over the devices
+static int multi_reduce(flash_ctx* ctx, int C) {
+  flash_ctx* s0 = ctx->subs[0];
+  const int G = (int)ctx->subs.size();
+  const size_t n = (size_t)C * s0->hm.M.acc_len;
+  if (s0->peer_acc_C != s0->cap_C) {   // (re)built whenever ensure_batch reallocated the accumulators
+    std::vector<double*> h(G);
+    for (int g = 0; g < G; ++g) h[g] = ctx->subs[g]->d_acc;
+    { flash_ctx* ctx = s0; CU(cudaSetDevice(s0->device)); if (!s0->d_peer_acc) CU(cudaMalloc((void**)&s0->d_peer_acc, 64 * sizeof(double*)));
+      CU(cudaMemcpyAsync(s0->d_peer_acc, h.data(), G * sizeof(double*), cudaMemcpyHostToDevice, s0->stream)); CU(cudaStreamSynchronize(s0->stream)); }
+    s0->peer_acc_C = s0->cap_C;
+  }
+  for (flash_ctx* sub : ctx->subs) { flash_ctx* ctx = sub; CU(cudaSetDevice(sub->device)); CU(cudaEventRecord(sub->ev_cost, sub->stream)); }
+  {
+    flash_ctx* ctx = s0;
+    CU(cudaSetDevice(s0->device));
+    for (int g = 1; g < G; ++g) CU(cudaStreamWaitEvent(s0->stream, s0->parent->subs[g]->ev_cost, 0));
+    reduce_peers_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 64), 256, 0, s0->stream>>>(s0->d_peer_acc, G, n);
+    CU(cudaGetLastError());
+    s0->launches++; s0->last.launches++;
+    CU(cudaEventRecord(s0->ev_red, s0->stream));
+  }
+  for (int g = 1; g < G; ++g) { flash_ctx* ctx = s0->parent->subs[g]; CU(cudaSetDevice(ctx->device)); CU(cudaStreamWaitEvent(ctx->stream, s0->ev_red, 0)); }
+  return 0;
+}
+
+template <class T>
+static int multi_points_set(flash_ctx* ctx, const T* xyz, int64_t n, bool async) {
+  const int G = (int)ctx->subs.size();
+  ctx->shard_off.assign(G + 1, 0);
+  for (int g = 0; g <= G; ++g) ctx->shard_off[g] = (long long)((__int128)n * g / G);
+  ctx->frame_sub.clear();
+  for (int g = 0; g < G; ++g) {
+    flash_ctx* sub = ctx->subs[g];
+    const T* ptrs[1] = {xyz + 3 * ctx->shard_off[g]};
+    const int64_t counts[1] = {ctx->shard_off[g + 1] - ctx->shard_off[g]};
+    MSUB(ingest<T>(sub, sub->ps[sub->cur ^ 1], ptrs, counts, 1));
+    sub->back_pending = true;
+  }
+  if (async) { ctx->back_pending = true; return FLASH_OK; }
+  for (flash_ctx* sub : ctx->subs) { MSUB(swap_sets(sub)); }
+  for (flash_ctx* sub : ctx->subs) { flash_ctx* ctx = sub; CU(cudaSetDevice(sub->device)); CU(cudaEventSynchronize(sub->ps[sub->cur].ready)); }
+  return FLASH_OK;
+}
+static int multi_swap(flash_ctx* ctx) {
+  if (!ctx->back_pending) return fail(ctx, FLASH_ERR_STATE, "flash_points_swap: no flash_points_set_async / flash_frames_set_async pending");
+  for (flash_ctx* sub : ctx->subs) { flash_ctx* ctx = sub; CU(cudaSetDevice(sub->device)); if (sub->back_pending) { int rc = swap_sets(sub); if (rc) return rc; } }
+  ctx->back_pending = false;
+  return FLASH_OK;
+}
+// frames round-robin over the devices (K4: 8 frames on 8 GPUs, one each); a device without a frame holds an empty set
+static int multi_frames_set(flash_ctx* ctx, const double* const* xyz, const int64_t* counts, int32_t F, bool async) {
+  const int G = (int)ctx->subs.size();
+  ctx->frame_sub.assign(F, 0); ctx->frame_slot.assign(F, 0);
+  std::vector<std::vector<const double*>> ptrs(G);
+  std::vector<std::vector<int64_t>> cnts(G);
+  for (int f = 0; f < F; ++f) { const int g = f % G; ctx->frame_sub[f] = g; ctx->frame_slot[f] = (int)ptrs[g].size(); ptrs[g].push_back(xyz[f]); cnts[g].push_back(counts[f]); }
+  ctx->shard_off.clear();
+  for (int g = 0; g < G; ++g) {
+    flash_ctx* sub = ctx->subs[g];
+    if (ptrs[g].empty()) { sub->back_pending = false; continue; }
+    MSUB(ingest<double>(sub, sub->ps[sub->cur ^ 1], ptrs[g].data(), cnts[g].data(), (int)ptrs[g].size()));
+    sub->back_pending = true;
+  }
+  if (async) { ctx->back_pending = true; return FLASH_OK; }
+  for (flash_ctx* sub : ctx->subs) if (sub->back_pending) { MSUB(swap_sets(sub)); }
+  for (flash_ctx* sub : ctx->subs) { flash_ctx* ctx = sub; CU(cudaSetDevice(sub->device)); if (sub->ps[sub->cur].ready) CU(cudaEventSynchronize(sub->ps[sub->cur].ready)); }
+  return FLASH_OK;
+}
+static void multi_timing(flash_ctx* ctx) {
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0, 0};
+  for (flash_ctx* sub : ctx->subs) {
+    ctx->last.ms_prepare = std::max(ctx->last.ms_prepare, sub->last.ms_prepare); ctx->last.ms_main = std::max(ctx->last.ms_main, sub->last.ms_main);
+    ctx->last.ms_allreduce = std::max(ctx->last.ms_allreduce, sub->last.ms_allreduce); ctx->last.ms_epilogue = std::max(ctx->last.ms_epilogue, sub->last.ms_epilogue);
+    ctx->last.ms_total = std::max(ctx->last.ms_total, sub->last.ms_total); ctx->last.ms_group = std::max(ctx->last.ms_group, sub->last.ms_group);
+    ctx->last.launches += sub->last.launches;
+  }
+}
+static int multi_cost_grad(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad, int32_t* argmin) {
+  if (ctx->shard_off.empty()) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad: call flash_points_set first (the ctx holds a batch of frames: use flash_cost_grad_frames)");
+  const long long N = ctx->shard_off.back();
+  for (flash_ctx* sub : ctx->subs) { sub->profiling = ctx->profiling; MSUB(cg_begin(sub, X, C, 0, grad != nullptr, argmin != nullptr)); }
+  int rc = multi_reduce(ctx, C); if (rc) return rc;
+  for (size_t g = 0; g < ctx->subs.size(); ++g) {
+    flash_ctx* sub = ctx->subs[g];
+    MSUB(cg_end(sub, C, w_def, grad != nullptr));
+    const long long n_g = sub->ps[sub->cur].n;
+    if (argmin && n_g > 0) {   // this shard's columns of argmin[C][N]
+      flash_ctx* ctx2 = ctx; flash_ctx* ctx = sub;
+      CU(cudaMemcpy2DAsync(argmin + ctx2->shard_off[g], (size_t)N * sizeof(int32_t), sub->d_argmin, (size_t)n_g * sizeof(int32_t), (size_t)n_g * sizeof(int32_t), (size_t)C,
+                           cudaMemcpyDeviceToHost, sub->stream));
+    }
+  }
+  for (size_t g = 0; g < ctx->subs.size(); ++g) { flash_ctx* sub = ctx->subs[g]; MSUB(cg_finish(sub, C, g == 0 ? cost : nullptr, g == 0 ? grad : nullptr)); }
+  multi_timing(ctx);
+  return FLASH_OK;
+}
+static int multi_cost_grad_frames(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad) {
+  const int F = (int)ctx->frame_sub.size(), G = (int)ctx->subs.size();
+  if (F == 0) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad_frames: call flash_frames_set first");
+  const int nx = ctx->hm.M.nx;
+  std::vector<std::vector<double>> Xg(G), cg(G), gg(G);
+  std::vector<int> nf(G, 0);
+  for (int f = 0; f < F; ++f) { const int g = ctx->frame_sub[f]; Xg[g].insert(Xg[g].end(), X + (size_t)f * C * nx, X + (size_t)(f + 1) * C * nx); nf[g]++; }
+  for (int g = 0; g < G; ++g) {
+    if (!nf[g]) continue;
+    flash_ctx* sub = ctx->subs[g];
+    sub->profiling = ctx->profiling;
+    if ((long long)C * nf[g] > 65535 * 16) return fail(ctx, FLASH_ERR_TOO_LARGE, "flash_cost_grad_frames: frames x configs too large");
+    MSUB(cg_begin(sub, Xg[g].data(), C * nf[g], C, grad != nullptr, false));
+    MSUB(cg_end(sub, C * nf[g], w_def, grad != nullptr));      // frames are independent: no reduction
+  }
+  for (int g = 0; g < G; ++g) {
+    if (!nf[g]) continue;
+    flash_ctx* sub = ctx->subs[g];
+    cg[g].resize((size_t)C * nf[g]); if (grad) gg[g].resize((size_t)C * nf[g] * nx);
+    MSUB(cg_finish(sub, C * nf[g], cg[g].data(), grad ? gg[g].data() : nullptr));
+  }
+  for (int f = 0; f < F; ++f) {
+    const int g = ctx->frame_sub[f], k = ctx->frame_slot[f];
+    std::memcpy(cost + (size_t)f * C, cg[g].data() + (size_t)k * C, (size_t)C * sizeof(double));
+    if (grad) std::memcpy(grad + (size_t)f * C * nx, gg[g].data() + (size_t)k * C * nx, (size_t)C * nx * sizeof(double));
+  }
+  multi_timing(ctx);
+  return FLASH_OK;
+}
+
+static int multi_create(const flash_model_desc* desc, const flash_options* opt, flash_ctx** out) {
+  const int G = opt->n_devices;
+  if (G > 16) return fail(nullptr, FLASH_ERR_INVALID, "flash_options.n_devices > 16");
+  flash_ctx* P = new flash_ctx;
+  std::string err;
+  if (!build_model(desc, opt, P->hm, err)) { delete P; return fail(nullptr, FLASH_ERR_INVALID, err); }
+  P->device = opt->devices[0];
+  for (int g = 0; g < G; ++g) {
+    flash_options o = *opt;
+    o.n_devices = 0; o.device = opt->devices[g];
+    flash_ctx* sub = nullptr;
+    const int rc = flash_model_create(desc, &o, &sub);
+    if (rc) { const std::string msg = "device " + std::to_string(opt->devices[g]) + ": " + g_create_err; flash_destroy(P); return fail(nullptr, rc, msg); }
+    sub->parent = P;
+    P->subs.push_back(sub);
+    if (cudaEventCreateWithFlags(&sub->ev_cost, cudaEventDisableTiming) != cudaSuccess || cudaEventCreateWithFlags(&sub->ev_red, cudaEventDisableTiming) != cudaSuccess) {
+      flash_destroy(P); return fail(nullptr, FLASH_ERR_CUDA, "cudaEventCreate failed");
+    }
+  }
+  // the reduction kernel runs on the first device and touches every other device's accumulators through peer memory
+  flash_ctx* s0 = P->subs[0];
+  cudaSetDevice(s0->device);
+  for (int g = 1; g < G; ++g) {
+    const int dev = P->subs[g]->device;
+    if (dev == s0->device) continue;   // (the same device listed twice: legal, used by the single-GPU tests)
+    int can = 0;
+    cudaDeviceCanAccessPeer(&can, s0->device, dev);
+    if (!can) { flash_destroy(P); return fail(nullptr, FLASH_ERR_CUDA, "device " + std::to_string(s0->device) + " cannot access device " + std::to_string(dev) + " as a peer (NVLink / PCIe P2P required)"); }
+    const cudaError_t e = cudaDeviceEnablePeerAccess(dev, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { flash_destroy(P); return fail(nullptr, FLASH_ERR_CUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e)); }
+    cudaGetLastError();
+  }
+  *out = P;
+  return FLASH_OK;
+}
+
+extern "C" {
 
 int flash_cost_grad(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad, int32_t* argmin) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (!X || C < 1 || !cost) return fail(ctx, FLASH_ERR_INVALID, "flash_cost_grad: bad arguments");
+  if (!ctx->subs.empty()) return multi_cost_grad(ctx, X, C, w_def, cost, grad, argmin);
   const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
   if (!P.set) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad: call flash_points_set first");
   if (P.ft.n_frames != 1) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad: the ctx holds a batch of frames, use flash_cost_grad_frames");
@@ -846,6 +1094,7 @@ int flash_cost_grad(flash_ctx* ctx, const double* X, int32_t C, double w_def, do
 int flash_cost_grad_frames(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (!X || C < 1 || !cost) return fail(ctx, FLASH_ERR_INVALID, "flash_cost_grad_frames: bad arguments");
+  if (!ctx->subs.empty()) return multi_cost_grad_frames(ctx, X, C, w_def, cost, grad);
   const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
   if (!P.set) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad_frames: call flash_frames_set first");
   const long long tot = (long long)C * P.ft.n_frames;
@@ -856,6 +1105,7 @@ int flash_cost_grad_frames(flash_ctx* ctx, const double* X, int32_t C, double w_
 int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t n, double* dist, int32_t* argmin) {
   if (!ctx) return FLASH_ERR_INVALID;
   if (!x || n < 0 || (n > 0 && (!xyz || !dist))) return fail(ctx, FLASH_ERR_INVALID, "flash_skin_eval: bad arguments");
+  if (!ctx->subs.empty()) { int rc = flash_skin_eval(ctx->subs[0], x, xyz, n, dist, argmin); if (rc) ctx->err = ctx->subs[0]->err; return rc; }
   if (n == 0) return FLASH_OK;
   const ModelC& M = ctx->hm.M;
   CU(cudaSetDevice(ctx->device));
@@ -891,11 +1141,8 @@ int flash_kinect_rays(int32_t rows, int32_t cols, double vertical_fov, double ho
   return FLASH_OK;
 }
 
-int flash_raycast(flash_ctx* ctx, const double* x, const double* rays, int64_t R, const double cam[12], double* depths, double* hits, int64_t* nhits) {
-  if (!ctx) return FLASH_ERR_INVALID;
-  if (!x || R < 0 || !cam || (R > 0 && (!rays || !depths))) return fail(ctx, FLASH_ERR_INVALID, "flash_raycast: bad arguments");
-  if (nhits) *nhits = 0;
-  if (R == 0) return FLASH_OK;
+// ray casting in two halves so that a multi-device parent can start every device before it waits for any
+static int raycast_launch(flash_ctx* ctx, const double* x, const double* rays, int64_t R, const double cam[12]) {
   const ModelC& M = ctx->hm.M;
   CU(cudaSetDevice(ctx->device));
   int rc = ensure_batch(ctx, 1); if (rc) return rc;
@@ -925,21 +1172,63 @@ int flash_raycast(flash_ctx* ctx, const double* x, const double* rays, int64_t R
                                                           cam[7], cam[8], cam[9], cam[10], cam[11]);
   CU(cudaGetLastError());
   ctx->launches += 3; ctx->last.launches += 3;
+  return 0;
+}
+static int raycast_collect(flash_ctx* ctx, int64_t R, double* depths, double* hits, int64_t* nhits) {
+  CU(cudaSetDevice(ctx->device));
+  double* d_rays = ctx->d_qd; double* d_depths = d_rays + 3 * R; double* d_hits = d_depths + R; long long* d_total = (long long*)(d_hits + 3 * R);
   long long total = 0;
   CU(cudaMemcpyAsync(depths, d_depths, (size_t)R * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaMemcpyAsync(&total, d_total, sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream));
-  rc = check_status(ctx); if (rc) return rc;
+  int rc = check_status(ctx); if (rc) return rc;
   if (hits && total > 0) { CU(cudaMemcpyAsync(hits, d_hits, (size_t)total * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream)); CU(cudaStreamSynchronize(ctx->stream)); }
   if (nhits) *nhits = total;
   if (ctx->profiling) { CU(cudaEventElapsedTime(&ctx->last.ms_main, ctx->ev[1], ctx->ev[2])); ctx->last.ms_total = ctx->last.ms_main; }
   return FLASH_OK;
 }
 
-int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solver_params* sp, const double* divisors, double* cost_out, int32_t* iters_out) {
+int flash_raycast(flash_ctx* ctx, const double* x, const double* rays, int64_t R, const double cam[12], double* depths, double* hits, int64_t* nhits) {
   if (!ctx) return FLASH_ERR_INVALID;
-  if (!X || C < 1 || !sp || sp->iteration_limit < 0) return fail(ctx, FLASH_ERR_INVALID, "flash_estimate_state: bad arguments");
-  if (!ctx->ps[ctx->cur].set) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: call flash_points_set first");
-  if (ctx->ps[ctx->cur].ft.n_frames != 1) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: the ctx holds a batch of frames");
+  if (!x || R < 0 || !cam || (R > 0 && (!rays || !depths))) return fail(ctx, FLASH_ERR_INVALID, "flash_raycast: bad arguments");
+  if (nhits) *nhits = 0;
+  if (R == 0) return FLASH_OK;
+  if (!ctx->subs.empty()) {
+    // rays sharded in contiguous ranges (image row bands for a row-major sensor): depths land at their ray's index, hits are
+    // concatenated in device order = ray order (raycast_points, src/depthsensors.jl:99-113)
+    const int G = (int)ctx->subs.size();
+    std::vector<int64_t> off(G + 1);
+    for (int g = 0; g <= G; ++g) off[g] = (int64_t)((__int128)R * g / G);
+    for (int g = 0; g < G; ++g) {
+      flash_ctx* sub = ctx->subs[g];
+      sub->profiling = ctx->profiling;
+      if (off[g + 1] > off[g]) MSUB(raycast_launch(sub, x, rays + 3 * off[g], off[g + 1] - off[g], cam));
+    }
+    int64_t total = 0;
+    for (int g = 0; g < G; ++g) {
+      flash_ctx* sub = ctx->subs[g];
+      if (off[g + 1] == off[g]) continue;
+      int64_t nh = 0;
+      MSUB(raycast_collect(sub, off[g + 1] - off[g], depths + off[g], hits ? hits + 3 * total : nullptr, &nh));
+      total += nh;
+    }
+    if (nhits) *nhits = total;
+    multi_timing(ctx);
+    return FLASH_OK;
+  }
+  int rc = raycast_launch(ctx, x, rays, R, cam); if (rc) return rc;
+  return raycast_collect(ctx, R, depths, hits, nhits);
+}
+
+static int run_iterate(flash_ctx* ctx, int C, const flash_solver_params* sp, double n_total, bool have_div, size_t it_smem) {
+  iterate_kernel<<<C, PREP_T, it_smem, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, C, sp->deformation_cost_weight, ctx->d_cost,
+                                                  ctx->d_grad, n_total > 0 ? 1.0 / n_total : 0.0, sp->rate, sp->max_step, sp->gradient_convergence_tolerance,
+                                                  have_div ? ctx->d_div : nullptr, ctx->d_done, ctx->d_iters, ctx->d_status);
+  CU(cudaGetLastError());
+  ctx->launches++; ctx->last.launches++;
+  return 0;
+}
+// state upload of flash_estimate_state (one device)
+static int es_begin(flash_ctx* ctx, const double* X, int32_t C, const double* divisors, size_t it_smem) {
   const ModelC& M = ctx->hm.M;
   CU(cudaSetDevice(ctx->device));
   int rc = ensure_batch(ctx, C); if (rc) return rc;
@@ -955,30 +1244,75 @@ int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solve
     std::memcpy(h_div, divisors, (size_t)M.nx * sizeof(double));
     rc = pull_pinned(ctx, ctx->d_div, h_div, (size_t)M.nx); if (rc) return rc;
   }
+  if (it_smem > 48 * 1024) CU(cudaFuncSetAttribute(iterate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)it_smem));
+  return 0;
+}
+// The solver loop on every device of a multi-device parent: each device evaluates its shard, the peer reduction hands
+// all of them the same sums, and every device then takes the same NaiveSolver step on its own copy of the state.
+static int multi_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solver_params* sp, const double* divisors, double* cost_out, int32_t* iters_out) {
+  if (ctx->shard_off.empty()) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: call flash_points_set first");
+  const ModelC& M = ctx->hm.M;
+  const size_t it_smem = std::max(prepare_smem_doubles(M), epilogue_smem_doubles(M)) * sizeof(double);
+  const double n_total = (double)ctx->shard_off.back();
+  for (flash_ctx* sub : ctx->subs) { sub->profiling = false; MSUB(es_begin(sub, X, C, divisors, it_smem)); MSUB(run_prepare(sub, C, true)); }
+  for (int it = 0; it < sp->iteration_limit; ++it) {
+    for (flash_ctx* sub : ctx->subs) { flash_ctx* ctx = sub; CU(cudaSetDevice(sub->device)); int rc = run_cost(sub, C, true, nullptr); if (rc) return rc; }
+    int rc = multi_reduce(ctx, C); if (rc) return rc;
+    for (flash_ctx* sub : ctx->subs) { flash_ctx* ctx = sub; CU(cudaSetDevice(sub->device)); rc = run_iterate(sub, C, sp, n_total, divisors != nullptr, it_smem); if (rc) return rc; }
+  }
+  if (cost_out) {
+    for (flash_ctx* sub : ctx->subs) { flash_ctx* ctx = sub; CU(cudaSetDevice(sub->device)); int rc = run_cost(sub, C, false, nullptr); if (rc) return rc; }
+    int rc = multi_reduce(ctx, C); if (rc) return rc;
+    { flash_ctx* sub = ctx->subs[0]; flash_ctx* ctx = sub; CU(cudaSetDevice(sub->device)); rc = run_epilogue(sub, C, sp->deformation_cost_weight, false); if (rc) return rc; }
+  }
+  const size_t nX = (size_t)C * M.nx;
+  for (size_t g = 0; g < ctx->subs.size(); ++g) {
+    flash_ctx* sub = ctx->subs[g];
+    flash_ctx* ctx = sub;
+    CU(cudaSetDevice(sub->device));
+    if (g == 0) {
+      CU(cudaMemcpyAsync(sub->h_pin, sub->d_X, nX * sizeof(double), cudaMemcpyDeviceToHost, sub->stream));
+      if (cost_out) CU(cudaMemcpyAsync(sub->h_pin + nX, sub->d_cost, (size_t)C * sizeof(double), cudaMemcpyDeviceToHost, sub->stream));
+      if (iters_out) CU(cudaMemcpyAsync(iters_out, sub->d_iters, (size_t)C * sizeof(int), cudaMemcpyDeviceToHost, sub->stream));
+    }
+    int rc = check_status(sub); if (rc) return rc;
+  }
+  std::memcpy(X, ctx->subs[0]->h_pin, nX * sizeof(double));
+  if (cost_out) std::memcpy(cost_out, ctx->subs[0]->h_pin + nX, (size_t)C * sizeof(double));
+  multi_timing(ctx);
+  return FLASH_OK;
+}
+
+int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solver_params* sp, const double* divisors, double* cost_out, int32_t* iters_out) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!X || C < 1 || !sp || sp->iteration_limit < 0) return fail(ctx, FLASH_ERR_INVALID, "flash_estimate_state: bad arguments");
+  if (!ctx->subs.empty()) return multi_estimate_state(ctx, X, C, sp, divisors, cost_out, iters_out);
+  if (!ctx->ps[ctx->cur].set) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: call flash_points_set first");
+  if (ctx->ps[ctx->cur].ft.n_frames != 1) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: the ctx holds a batch of frames");
+  const ModelC& M = ctx->hm.M;
+  const size_t it_smem = std::max(prepare_smem_doubles(M), epilogue_smem_doubles(M)) * sizeof(double);
+  const size_t nX = (size_t)C * M.nx;
+  int rc = es_begin(ctx, X, C, divisors, it_smem); if (rc) return rc;
   // total point count across ranks (the reference divides by length(sensed_points), src/tracking.jl:20)
   double n_total = (double)ctx->ps[ctx->cur].n;
-  if (ctx->comm) {
+  if (ctx->comm && ctx->n_global >= 0) n_total = ctx->n_global;   // reduced once per point set, not once per call
+  else if (ctx->comm) {
     double* d_n = ctx->d_cost;  // scratch
     CU(cudaMemcpyAsync(d_n, &n_total, sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     int nrc = g_nccl.AllReduce(d_n, d_n, 1, NCCL_FLOAT64, NCCL_SUM, ctx->comm, ctx->stream);
     if (nrc != 0) return fail(ctx, FLASH_ERR_NCCL, "ncclAllReduce(point count) failed");
     CU(cudaMemcpyAsync(&n_total, d_n, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
+    ctx->n_global = n_total;
   }
   const bool prof = ctx->profiling; ctx->profiling = false;
   cudaEvent_t e0 = ctx->ev[0], e1 = ctx->ev[4];
   if (prof) CU(cudaEventRecord(e0, ctx->stream));
   // per iteration: cost_kernel -> [allreduce] -> iterate_kernel (epilogue + NaiveSolver step + prepare of the next pass)
-  const size_t it_smem = std::max(prepare_smem_doubles(M), epilogue_smem_doubles(M)) * sizeof(double);
-  if (it_smem > 48 * 1024) CU(cudaFuncSetAttribute(iterate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)it_smem));
   if ((rc = run_prepare(ctx, C, true))) { ctx->profiling = prof; return rc; }
   for (int it = 0; it < sp->iteration_limit; ++it) {
     if ((rc = run_cost(ctx, C, true, nullptr)) || (rc = run_allreduce(ctx, C))) { ctx->profiling = prof; return rc; }
-    iterate_kernel<<<C, PREP_T, it_smem, ctx->stream>>>(ctx->d_model, ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, C, sp->deformation_cost_weight, ctx->d_cost,
-                                                    ctx->d_grad, n_total > 0 ? 1.0 / n_total : 0.0, sp->rate, sp->max_step, sp->gradient_convergence_tolerance,
-                                                    divisors ? ctx->d_div : nullptr, ctx->d_done, ctx->d_iters, ctx->d_status);
-    CU(cudaGetLastError());
-    ctx->launches++; ctx->last.launches++;
+    if ((rc = run_iterate(ctx, C, sp, n_total, divisors != nullptr, it_smem))) { ctx->profiling = prof; return rc; }
   }
   if (cost_out) {   // cost at the final state: the last iterate_kernel already prepared it
     if ((rc = run_cost(ctx, C, false, nullptr)) || (rc = run_allreduce(ctx, C)) || (rc = run_epilogue(ctx, C, sp->deformation_cost_weight, false))) { ctx->profiling = prof; return rc; }
@@ -999,6 +1333,7 @@ int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solve
 int flash_contour_mesh(flash_ctx* ctx, const double* x, int32_t surface, const double lo[3], const double hi[3], double spacing, double iso,
                        float* triangles, int64_t cap, int64_t* n_triangles) {
   if (!ctx) return FLASH_ERR_INVALID;
+  if (!ctx->subs.empty()) { int rc = flash_contour_mesh(ctx->subs[0], x, surface, lo, hi, spacing, iso, triangles, cap, n_triangles); if (rc) ctx->err = ctx->subs[0]->err; return rc; }
   const ModelC& M = ctx->hm.M;
   if (!x || !lo || !hi || !n_triangles || !(spacing > 0) || cap < 0 || surface >= M.n_surfaces)
     return fail(ctx, FLASH_ERR_INVALID, "flash_contour_mesh: bad arguments");
@@ -1061,6 +1396,7 @@ int flash_comm_unique_id(void* id128) {
 }
 
 int flash_comm_init(flash_ctx* ctx, int32_t rank, int32_t world, const void* id128) {
+  if (ctx && !ctx->subs.empty()) return fail(ctx, FLASH_ERR_INVALID, "flash_comm_init: a multi-device context already spans its devices");
   if (!ctx) return FLASH_ERR_INVALID;
   if (world < 1 || rank < 0 || rank >= world || !id128) return fail(ctx, FLASH_ERR_INVALID, "flash_comm_init: bad arguments");
   std::string err;
@@ -1077,11 +1413,18 @@ int flash_comm_init(flash_ctx* ctx, int32_t rank, int32_t world, const void* id1
 int flash_comm_world(const flash_ctx* ctx) { return ctx ? ctx->world : FLASH_ERR_INVALID; }
 
 // ---- measurement
-int flash_profiling(flash_ctx* ctx, int32_t enable) { if (!ctx) return FLASH_ERR_INVALID; ctx->profiling = enable != 0; return FLASH_OK; }
+int flash_profiling(flash_ctx* ctx, int32_t enable) { if (!ctx) return FLASH_ERR_INVALID; ctx->profiling = enable != 0; for (flash_ctx* sub : ctx->subs) sub->profiling = enable != 0; return FLASH_OK; }
 int flash_last_timing(const flash_ctx* ctx, flash_timing* t) { if (!ctx || !t) return FLASH_ERR_INVALID; *t = ctx->last; return FLASH_OK; }
-int64_t flash_launch_count(const flash_ctx* ctx) { return ctx ? ctx->launches : FLASH_ERR_INVALID; }
+int64_t flash_launch_count(const flash_ctx* ctx) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  int64_t n = ctx->launches;
+  for (const flash_ctx* sub : ctx->subs) n += sub->launches;
+  return n;
+}
+int flash_num_devices(const flash_ctx* ctx) { return ctx ? (ctx->subs.empty() ? 1 : (int)ctx->subs.size()) : FLASH_ERR_INVALID; }
 int flash_device_info(const flash_ctx* ctx, int32_t* sm_count, int32_t* clock_khz, int64_t* l2_bytes) {
   if (!ctx) return FLASH_ERR_INVALID;
+  if (!ctx->subs.empty()) return flash_device_info(ctx->subs[0], sm_count, clock_khz, l2_bytes);
   if (sm_count) *sm_count = ctx->sm_count;
   if (clock_khz) *clock_khz = ctx->clock_khz;
   if (l2_bytes) *l2_bytes = ctx->l2_bytes;
@@ -1089,6 +1432,7 @@ int flash_device_info(const flash_ctx* ctx, int32_t* sm_count, int32_t* clock_kh
 }
 int flash_grid_report(const flash_ctx* ctx, int32_t surface, int32_t dims[3], double* spacing, double* max_abs_err) {
   if (!ctx) return FLASH_ERR_INVALID;
+  if (!ctx->subs.empty()) return flash_grid_report(ctx->subs[0], surface, dims, spacing, max_abs_err);
   const ModelC& M = ctx->hm.M;
   if (surface < 0 || surface >= M.n_surfaces || M.surf_kind[surface] != SURF_CONVEX || !ctx->use_grid) return FLASH_ERR_INVALID;
   const ConvexC& C = M.cvx[M.surf_slot[surface]];
@@ -1100,6 +1444,7 @@ int flash_grid_report(const flash_ctx* ctx, int32_t surface, int32_t dims[3], do
 
 int flash_grid_download(const flash_ctx* ctx, int32_t surface, double origin[3], double geometry_to_body[12], float* values) {
   if (!ctx) return FLASH_ERR_INVALID;
+  if (!ctx->subs.empty()) return flash_grid_download(ctx->subs[0], surface, origin, geometry_to_body, values);
   const ModelC& M = ctx->hm.M;
   if (surface < 0 || surface >= M.n_surfaces || M.surf_kind[surface] != SURF_CONVEX || !ctx->use_grid) return FLASH_ERR_INVALID;
   const ConvexC& C = M.cvx[M.surf_slot[surface]];

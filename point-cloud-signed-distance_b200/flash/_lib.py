@@ -22,7 +22,7 @@ SYMBOLS = [
     "flash_points_set_async", "flash_points_set_async_f32", "flash_points_swap", "flash_points_sync",
     "flash_frames_set", "flash_frames_set_async", "flash_num_frames", "flash_cost_grad_frames",
     "flash_urdf_load", "flash_urdf_desc", "flash_urdf_body_name", "flash_urdf_surface_mesh", "flash_urdf_set_joint_type", "flash_urdf_free",
-    "flash_model_load_urdf", "flash_read_point_cloud", "flash_points_set_file", "flash_points_set_file_async",
+    "flash_model_load_urdf", "flash_read_point_cloud", "flash_points_set_file", "flash_points_set_file_async", "flash_num_devices",
 ]
 
 _lib = None
@@ -43,7 +43,7 @@ def lib():
     L.flash_last_error.argtypes = [vp]; L.flash_last_error.restype = C.c_char_p
     L.flash_model_create.argtypes = [C.POINTER(ModelDesc), C.POINTER(Options), C.POINTER(vp)]
     L.flash_destroy.argtypes = [vp]; L.flash_destroy.restype = None
-    for f in ("flash_num_positions", "flash_num_states", "flash_num_surfaces", "flash_comm_world"):
+    for f in ("flash_num_positions", "flash_num_states", "flash_num_surfaces", "flash_comm_world", "flash_num_devices"):
         getattr(L, f).argtypes = [vp]; getattr(L, f).restype = C.c_int
     L.flash_points_set.argtypes = [vp, c_double_p, C.c_int64]
     L.flash_points_set_f32.argtypes = [vp, C.POINTER(C.c_float), C.c_int64]

@@ -540,3 +540,63 @@ def test_model_from_urdf_and_points_from_file_through_the_c_abi(tmp_path):
     assert abs(cost[1] - co) <= RTOL * abs(co) and np.abs(grad[1] - go).max() <= RTOL * np.abs(go).max()
     assert L.flash_points_set_file(ctx, b"/nonexistent/cloud.txt", None) == -7 and b"cannot open" in L.flash_last_error(ctx)
     L.flash_destroy(ctx)
+
+
+def _multi_devices():
+    """two sub-contexts: on two GPUs when the box has them, else twice on device 0 (the sharding, the peer reduction and the
+    gathers run all the same)"""
+    import torch
+    return (0, 1) if torch.cuda.device_count() >= 2 else (0, 0)
+
+
+def test_single_process_multi_device_context_matches_one_device():
+    """flash_options.n_devices: ONE context that shards points (contiguous ranges), frames (round-robin) and rays
+    (contiguous ranges) over its devices and reduces the accumulators over peer memory -- the form the reference's
+    single Julia process needs (src/tracking.jl:8-27).  Cost, gradient, argmin, frame batches, the on-device solver
+    loop and ray casting against the same calls on one device, and the cost against the oracle."""
+    rng = np.random.default_rng(61)
+    devs = _multi_devices()
+    m1 = flash.models.irb_and_squishable()
+    m2 = flash.models.irb_and_squishable()
+    m2.set_options(devices=devs)
+    from flash import _lib
+    assert _lib.lib().flash_num_devices(m2.ctx()) == 2 and _lib.lib().flash_num_devices(m1.ctx()) == 1
+    nx = flash.num_states(m1)
+    x0 = flash.gradientdescent.flatten(flash.ManipulatorState(m1))
+    x0[4:7] = [0.0, 0.0, 0.75]; x0[17:20] = [0.55, 0.45, 0.8]; x0[24:27] = [0.4, 0.0, 0.6]
+    X = x0 + 0.03 * rng.standard_normal((3, nx))
+    pts = _points(rng, 200_003, [-0.5, -0.5, 0.5], [1.0, 0.5, 2.0])
+    c1, g1, a1 = flash.gradientdescent.CostFunctor(m1, pts).batch(X, argmin=True)
+    c2, g2, a2 = flash.gradientdescent.CostFunctor(m2, pts).batch(X, argmin=True)
+    # (the shards are sorted and grouped on their own: other groups of 32, so the fp32 warp sums of the hull wrenches round differently)
+    assert np.allclose(c2, c1, rtol=1e-9) and np.abs(g2 - g1).max() <= 1e-7 * np.abs(g1).max()
+    assert np.array_equal(a1, a2)                      # per-point results do not depend on the shard a point lands in
+    o = ol.Oracle(m1)
+    co, go = o.cost_grad(X[2], pts, method="adjoint", mode=ol.GJK)
+    assert abs(c2[2] - co) <= RTOL * abs(co) and np.abs(g2[2] - go).max() <= RTOL * np.abs(go).max()
+    # frames: 5 frames over 2 devices (3 + 2), 2 candidates each
+    frames = [_points(rng, n, [-0.5, -0.5, 0.5], [1.0, 0.5, 2.0]) for n in (9000, 20011, 33, 15000, 4096)]
+    XF = x0 + 0.03 * rng.standard_normal((5, 2, nx))
+    cf1, gf1 = flash.gradientdescent.FramesCostFunctor(m1, frames).batch(XF)
+    cf2, gf2 = flash.gradientdescent.FramesCostFunctor(m2, frames).batch(XF)
+    assert np.allclose(cf2, cf1, rtol=1e-9) and np.abs(gf2 - gf1).max() <= 1e-7 * np.abs(gf1).max()
+    # the solver loop: every device takes the same steps on the same sums
+    ms1, ms2 = flash.models.squishable(), flash.models.squishable()
+    ms2.set_options(devices=devs)
+    cloud = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "squishable_unsquished_xyz.npy")).astype(np.float64)
+    xs = flash.gradientdescent.flatten(flash.ManipulatorState(ms1)); xs[4:7] = cloud.mean(0)
+    solver = flash.tracking.NaiveSolver(flash.num_states(ms1), rate=0.1, max_step=0.05, iteration_limit=8)
+    e1 = flash.tracking.estimate_state(ms1, cloud, xs, solver=solver, on_device=True)
+    e2 = flash.tracking.estimate_state(ms2, cloud, xs, solver=solver, on_device=True)
+    assert np.abs(e2 - e1).max() < 1e-9
+    # ray casting: rays in contiguous ranges, depths in place, hits concatenated in ray order
+    sensor = flash.depthsensors.Kinect(60, 80)
+    cam = flash.depthsensors.affine((0, 1.5, 0.5), (1, 0, 0), np.pi / 2)
+    mi1, mi2 = flash.models.irb140(), flash.models.irb140()
+    mi2.set_options(devices=devs)
+    d1 = flash.depthsensors.raycast_depths(flash.skin(flash.ManipulatorState(mi1)), sensor, cam)
+    d2 = flash.depthsensors.raycast_depths(flash.skin(flash.ManipulatorState(mi2)), sensor, cam)
+    assert np.array_equal(np.isnan(d1), np.isnan(d2)) and np.array_equal(d1[~np.isnan(d1)], d2[~np.isnan(d2)])
+    h1 = flash.depthsensors.raycast(flash.ManipulatorState(mi1), sensor, cam)
+    h2 = flash.depthsensors.raycast(flash.ManipulatorState(mi2), sensor, cam)
+    assert h1.shape == h2.shape and len(h1) > 100 and np.array_equal(h1, h2)
