@@ -205,6 +205,20 @@ def run_ours(args, rank, local_rank, world):
         dist = dist_
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     L = _lib.lib()
+    single_proc = None
+    if world > 1 and args.extras:
+        # The same box through ONE process and ONE multi-device context (flash_options.n_devices -- what a single Julia
+        # process uses), measured BEFORE the ranks touch their GPUs: rank 0 runs it in a child process (bounded by a
+        # timeout) while the other ranks wait on a CPU (gloo) barrier, so no NCCL kernel spins on the devices meanwhile.
+        gl = dist.new_group(backend="gloo")
+        if rank == 0:
+            try:
+                r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "multi_bench.py"), str(world), str(args.points), str(args.configs)],
+                                   capture_output=True, text=True, timeout=300)
+                single_proc = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else {"error": r.stderr[-400:]}
+            except Exception as e:   # reported, never fatal for the headline
+                single_proc = {"error": repr(e)}
+        dist.barrier(group=gl)
     m = scene_model(flash)
     m.set_options(device=local_rank, sdf_mode=1 if args.mode == "grid" else 0, grid_spacing=args.grid_spacing)
     ctx = m.ctx()
@@ -305,6 +319,14 @@ def run_ours(args, rank, local_rank, world):
     barrier()
     clocks = sampler.stop(first_sample) if rank == 0 else None
 
+    arg0 = None
+    if args.parity:
+        # argmin of config 0 over this rank's shard: a COLLECTIVE call when a communicator is attached (every rank makes it);
+        # rank 0 checks its shard against the oracle in parity_leg
+        from flash._desc import c_int32_p
+        arg0 = np.empty(n_local, np.int32)
+        c1 = np.empty(1)
+        m.check(L.flash_cost_grad(ctx, X[:1].ctypes.data_as(c_double_p), 1, 10.0, c1.ctypes.data_as(c_double_p), None, arg0.ctypes.data_as(c_int32_p)))
     tt = torch.tensor([sum(t_steps), sum(t_e2e), sum(k_main) / 1e3, sum(k_total) / 1e3, sum(t_ser) / len(t_ser) * args.steps, sum(k_group) / 1e3], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -387,8 +409,10 @@ def run_ours(args, rank, local_rank, world):
                 line["tracking"] = tracking_leg(flash, L)
             if args.configs_leg:
                 line["other_configs"] = configs_leg(flash, L, args.steps)
+        if single_proc is not None:
+            line["single_process_ctx"] = single_proc
         if args.parity:
-            line["parity"] = parity_leg(flash, m, L, ctx, X, cost, grad, pts, n_local, N, rank, world)
+            line["parity"] = parity_leg(flash, m, L, ctx, X, cost, grad, pts, n_local, N, rank, world, arg0)
         if args.cpu_baseline and world == 1:
             base = cpu_leg(args.ref_points, args.ref_configs, 1, 1)
             fast = cpu_leg(args.ref_points, args.ref_configs, 1, 0, method="adjoint")
@@ -401,7 +425,7 @@ def run_ours(args, rank, local_rank, world):
         dist.destroy_process_group()
 
 
-def parity_leg(flash, m, L, ctx, X, cost, grad, pts_local, n_local, N, rank, world):
+def parity_leg(flash, m, L, ctx, X, cost, grad, pts_local, n_local, N, rank, world, arg):
     """Config 0 of the TIMED workload against the fp64 oracle (tests/oracle_lib, the checker -- never the thing
     measured): cost and gradient over the whole global cloud, argmin over this rank's shard."""
     import oracle_lib as ol
@@ -410,9 +434,6 @@ def parity_leg(flash, m, L, ctx, X, cost, grad, pts_local, n_local, N, rank, wor
     o = ol.Oracle(m)
     full = pts_local[:n_local] if world == 1 else scene_points(N)
     co, go = o.cost_grad(X[0], full, method="adjoint", mode=ol.GJK)
-    arg = np.empty(n_local, np.int32)
-    c1 = np.empty(1)
-    m.check(L.flash_cost_grad(ctx, X[:1].ctypes.data_as(c_double_p), 1, 10.0, c1.ctypes.data_as(c_double_p), None, arg.ctypes.data_as(c_int32_p)))
     _, ao = o.skin(X[0], pts_local[:n_local], mode=ol.GJK, argmin=True)
     bad = np.nonzero(arg != ao)[0]
     outside_band = 0
@@ -578,6 +599,78 @@ def _time_frames(flash, L, m, clouds, X, steps, hits):
             "h2d_bytes_per_batch": int(24 * n + X.nbytes), "d2h_bytes_per_batch": int(cost.nbytes + grad.nbytes),
             "note": "flash_frames_set(_async) + flash_cost_grad_frames, one launch per batch; device = CUDA-event time of prepare + group + cost + epilogue with "
                     "the frames resident; e2e = frames from pinned host memory every batch, pipelined (batch k+1 uploads while batch k runs); e2e_serial = nothing overlapped"}
+
+
+def single_process_leg(flash, L, devices, steps, n_points=10_000_000, n_configs=64):
+    """The same workloads through ONE multi-device context (flash_options.n_devices: the form a single Julia process
+    uses): K5 with the cloud handed over whole -- in slab order (contiguous index ranges are compact x-slabs) and
+    shuffled (index ranges thin the cloud: the case a caller who shards naively hits) -- and K4's 8 frames x 16
+    candidates with the frames round-robin over the devices."""
+    import torch
+    from flash._desc import Timing, c_double_p
+    out = {"devices": list(devices)}
+    m = scene_model(flash)
+    m.set_options(devices=tuple(devices))
+    ctx = m.ctx()
+    nx = flash.num_states(m)
+    X = np.ascontiguousarray(scene_states(flash, m, n_configs))
+    cost = np.empty(n_configs); grad = np.empty((n_configs, nx))
+    pX, pc, pg = X.ctypes.data_as(c_double_p), cost.ctypes.data_as(c_double_p), grad.ctypes.data_as(c_double_p)
+    m.check(L.flash_profiling(ctx, 1))
+    tm = Timing()
+    pin = torch.empty((n_points, 3), dtype=torch.float64, pin_memory=True)
+    pts = pin.numpy()
+    for order in ("slab_order", "shuffled"):
+        pts[:] = scene_points(n_points)
+        if order == "shuffled":
+            pts[:] = pts[np.random.default_rng(9).permutation(n_points)]
+        pp = pts.ctypes.data_as(c_double_p)
+        m.check(L.flash_points_set(ctx, pp, n_points))
+        for _ in range(3):
+            m.check(L.flash_cost_grad(ctx, pX, n_configs, 10.0, pc, pg, None))
+        ts, km = [], []
+        for _ in range(steps):
+            for d in set(devices):
+                torch.cuda.synchronize(d)
+            t0 = time.perf_counter()
+            m.check(L.flash_cost_grad(ctx, pX, n_configs, 10.0, pc, pg, None))
+            ts.append(time.perf_counter() - t0)
+            L.flash_last_timing(ctx, C.byref(tm)); km.append(tm.ms_main)
+        # end to end, pipelined as the N=1 leg: every device uploads and sorts its shard of the next frame while it evaluates the current one
+        m.check(L.flash_points_set_async(ctx, pp, n_points))
+        te = []
+        for k in range(steps + 1):
+            t0 = time.perf_counter()
+            m.check(L.flash_points_swap(ctx))
+            m.check(L.flash_points_set_async(ctx, pp, n_points))
+            m.check(L.flash_cost_grad(ctx, pX, n_configs, 10.0, pc, pg, None))
+            if k:
+                te.append(time.perf_counter() - t0)
+        m.check(L.flash_points_swap(ctx))
+        out["k5_" + order] = {"value": n_points * n_configs / np.mean(ts), "unit": UNIT, "ms_per_step": 1e3 * float(np.mean(ts)), "kernel_ms_max_over_devices": float(np.mean(km)),
+                              "e2e_value": n_points * n_configs / np.mean(te), "e2e_ms_per_step": 1e3 * float(np.mean(te)), "checksum_cost_sum": float(cost.sum())}
+    m._points_owner = None
+    m.invalidate()
+    del pin
+    # K4
+    rng = np.random.default_rng(2)
+    m4 = scene_model(flash)
+    X4 = scene_states(flash, m4, 16)
+    st4 = flash.ManipulatorState(m4)
+    frames = []
+    for k in range(8):
+        x = X4[0].copy()
+        x[:flash.num_positions(m4)] += 0.02 * rng.standard_normal(flash.num_positions(m4))
+        flash.gradientdescent.unflatten_(st4, x)
+        cam4 = flash.depthsensors.affine((0.3 + 0.05 * k, 1.8, 1.0), (1, 0, 0), np.pi / 2 + 0.25)
+        p, _ = frame_cloud(flash, st4, cam4)
+        frames.append(p)
+    m4.set_options(devices=tuple(devices))
+    r = _time_frames(flash, L, m4, frames, np.repeat(X4[None], 8, 0), steps, 0)
+    r.pop("ray_hits_on_model", None)
+    out["k4_combined_8_frames_x_16_configs"] = r
+    m4.invalidate()
+    return out
 
 
 def tracking_leg(flash, L):

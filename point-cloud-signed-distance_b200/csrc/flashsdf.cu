@@ -110,7 +110,8 @@ struct flash_ctx {
   flash_ctx* parent = nullptr;
   double** d_peer_acc = nullptr; int peer_acc_C = 0;
   cudaEvent_t ev_cost = nullptr, ev_red = nullptr;   // sub: cost kernel done; subs[0]: peer reduction done
-  std::vector<long long> shard_off;                  // parent: first point of every sub's shard (+ total), caller order
+  std::vector<std::vector<long long>> seg_off, seg_len;   // parent: per sub, the chunks of the caller's cloud it holds (first point, length)
+  long long n_points = 0; bool have_points = false;       // parent: size of the current cloud (false: a batch of frames)
   std::vector<int> frame_sub, frame_slot;            // parent: owner and local index of every frame of the current batch
   // measurement
   bool profiling = false;
@@ -411,25 +412,35 @@ static bool host_pinned(const void* p) {
 
 // F frames ptrs[f][counts[f]][3] (host) -> set P.  Returns after ENQUEUEING the work on the copy stream; pageable
 // caller memory has been staged into the ctx's pinned ring by then, pinned caller memory is read by DMA until P.ready.
+// segments = true: the F inputs are pieces of ONE frame (a multi-device parent hands every device several chunks of the
+// caller's cloud), concatenated in the staging buffer.
 template <class T>
-static int ingest(flash_ctx* ctx, flash_ctx::PointSet& P, const T* const* ptrs, const int64_t* counts, int F) {
+static int ingest(flash_ctx* ctx, flash_ctx::PointSet& P, const T* const* ptrs, const int64_t* counts, int F, bool segments = false) {
   CU(cudaSetDevice(ctx->device));
   FrameTable& ft = P.ft;
-  ft.n_frames = F;
   long long n = 0, span = 0, max_cnt = 0;
-  for (int f = 0; f < F; ++f) {
-    ft.src_off[f] = n; ft.off[f] = span; ft.cnt[f] = counts[f];
-    n += counts[f]; span += (counts[f] + 31) & ~31ll; max_cnt = std::max<long long>(max_cnt, counts[f]);
+  std::vector<long long> in_off((size_t)F + 1, 0);   // offset of every input in the caller-order staging buffer
+  for (int f = 0; f < F; ++f) { in_off[f] = n; n += counts[f]; }
+  in_off[F] = n;
+  const int NF = segments ? 1 : F;
+  ft.n_frames = NF;
+  if (segments) {
+    ft.src_off[0] = 0; ft.off[0] = 0; ft.cnt[0] = n; span = (n + 31) & ~31ll; max_cnt = n;
+  } else {
+    for (int f = 0; f < F; ++f) {
+      ft.src_off[f] = in_off[f]; ft.off[f] = span; ft.cnt[f] = counts[f];
+      span += (counts[f] + 31) & ~31ll; max_cnt = std::max<long long>(max_cnt, counts[f]);
+    }
   }
-  ft.src_off[F] = n; ft.off[F] = span;
+  ft.src_off[NF] = n; ft.off[NF] = span;
   int rc = set_alloc(ctx, P, std::max<long long>(span, 32)); if (rc) return rc;
   cudaStream_t cs = ctx->copy_stream;
   if (P.retired_valid) { CU(cudaStreamWaitEvent(cs, P.retired, 0)); P.retired_valid = false; }
   P.perm_on = false; P.grp_on = false; P.n = n; P.max_cnt = max_cnt; P.set = true;
   {
     long long h[2 * MAX_FRAMES + 2];
-    for (int f = 0; f <= F; ++f) h[f] = ft.off[f];
-    for (int f = 0; f < F; ++f) h[MAX_FRAMES + 1 + f] = ft.cnt[f];
+    for (int f = 0; f <= NF; ++f) h[f] = ft.off[f];
+    for (int f = 0; f < NF; ++f) h[MAX_FRAMES + 1 + f] = ft.cnt[f];
     // small and rare (once per frame batch): pageable source, synchronous staging by the driver
     CU(cudaMemcpyAsync(P.d_frames, h, sizeof h, cudaMemcpyHostToDevice, cs));
   }
@@ -447,7 +458,7 @@ static int ingest(flash_ctx* ctx, flash_ctx::PointSet& P, const T* const* ptrs, 
   for (int f = 0; f < F; ++f) if (counts[f] > 0 && !host_pinned(ptrs[f])) all_pinned = false;
   if (all_pinned) {
     for (int f = 0; f < F; ++f)
-      if (counts[f] > 0) CU(cudaMemcpyAsync((char*)ctx->d_stage + (size_t)ft.src_off[f] * 3 * sizeof(T), ptrs[f], (size_t)counts[f] * 3 * sizeof(T), cudaMemcpyHostToDevice, cs));
+      if (counts[f] > 0) CU(cudaMemcpyAsync((char*)ctx->d_stage + (size_t)in_off[f] * 3 * sizeof(T), ptrs[f], (size_t)counts[f] * 3 * sizeof(T), cudaMemcpyHostToDevice, cs));
   } else {
     const int slot = ctx->ring_next; ctx->ring_next ^= 1;
     if (!ctx->ring_done[slot]) CU(cudaEventCreateWithFlags(&ctx->ring_done[slot], cudaEventDisableTiming));
@@ -459,7 +470,7 @@ static int ingest(flash_ctx* ctx, flash_ctx::PointSet& P, const T* const* ptrs, 
       ctx->cap_ring[slot] = bytes + bytes / 16;
     }
     for (int f = 0; f < F; ++f)
-      if (counts[f] > 0) std::memcpy((char*)ctx->h_ring[slot] + (size_t)ft.src_off[f] * 3 * sizeof(T), ptrs[f], (size_t)counts[f] * 3 * sizeof(T));
+      if (counts[f] > 0) std::memcpy((char*)ctx->h_ring[slot] + (size_t)in_off[f] * 3 * sizeof(T), ptrs[f], (size_t)counts[f] * 3 * sizeof(T));
     CU(cudaMemcpyAsync(ctx->d_stage, ctx->h_ring[slot], bytes, cudaMemcpyHostToDevice, cs));
     CU(cudaEventRecord(ctx->ring_done[slot], cs));
   }
@@ -479,7 +490,7 @@ static int ingest(flash_ctx* ctx, flash_ctx::PointSet& P, const T* const* ptrs, 
     if (!ctx->d_bounds) CU(cudaMalloc((void**)&ctx->d_bounds, (size_t)(6 * MAX_FRAMES + 1) * sizeof(unsigned)));
     unsigned* scan_done = ctx->d_bounds + 6 * MAX_FRAMES;
     // key layout: frame bits | 3 * hb Hilbert bits; the top `kb` bits are sorted (enough to order clouds of this size)
-    int fb = 0; while ((1 << fb) < F) ++fb;
+    int fb = 0; while ((1 << fb) < NF) ++fb;
     const int hb = std::min(10, (32 - fb) / 3);
     const int total_bits = fb + 3 * hb;
     int lg = 0; while ((1ll << lg) < n) ++lg;
@@ -502,10 +513,10 @@ static int ingest(flash_ctx* ctx, flash_ctx::PointSet& P, const T* const* ptrs, 
       CU(cudaMalloc((void**)&ctx->d_sums, ((size_t)tlen * 2 / 1024 + 2) * sizeof(int)));
       ctx->cap_table = (size_t)tlen * 2;
     }
-    bounds_init_kernel<<<(6 * F + 255) / 256, 256, 0, cs>>>(ctx->d_bounds, F, scan_done);
-    const unsigned bb = (unsigned)std::min<long long>((max_cnt + 255) / 256, std::max(1, ctx->sm_count * 16 / F));
-    frames_bounds_kernel<T><<<dim3(std::max(bb, 1u), F), 256, 0, cs>>>(src, ft, ctx->d_bounds);
-    points_keys_kernel<T><<<dim3((unsigned)((max_cnt + 255) / 256), F), 256, 0, cs>>>(src, ft, ctx->d_bounds, hb, drop, ctx->d_keys[0], ctx->d_idx[0]);
+    bounds_init_kernel<<<(6 * NF + 255) / 256, 256, 0, cs>>>(ctx->d_bounds, NF, scan_done);
+    const unsigned bb = (unsigned)std::min<long long>((max_cnt + 255) / 256, std::max(1, ctx->sm_count * 16 / NF));
+    frames_bounds_kernel<T><<<dim3(std::max(bb, 1u), NF), 256, 0, cs>>>(src, ft, ctx->d_bounds);
+    points_keys_kernel<T><<<dim3((unsigned)((max_cnt + 255) / 256), NF), 256, 0, cs>>>(src, ft, ctx->d_bounds, hb, drop, ctx->d_keys[0], ctx->d_idx[0]);
     const unsigned rblocks = (unsigned)((nW + RS_WARPS - 1) / RS_WARPS);
     int in = 0;
     for (int ps = 0; ps < passes; ++ps) {
@@ -805,7 +816,7 @@ int flash_frames_set_async(flash_ctx* ctx, const double* const* xyz, const int64
 
 int flash_num_frames(const flash_ctx* ctx) {
   if (!ctx) return FLASH_ERR_INVALID;
-  if (!ctx->subs.empty()) return ctx->frame_sub.empty() ? (ctx->shard_off.empty() ? 0 : 1) : (int)ctx->frame_sub.size();
+  if (!ctx->subs.empty()) return ctx->frame_sub.empty() ? (ctx->have_points ? 1 : 0) : (int)ctx->frame_sub.size();
   return ctx->ps[ctx->cur].set ? ctx->ps[ctx->cur].ft.n_frames : 0;
 }
 
@@ -901,7 +912,7 @@ static int cost_grad_impl(flash_ctx* ctx, const double* X, int32_t C, int cfg_pe
 
 // ================================================================================================
 // Single-process multi-GPU context (flash_options.n_devices > 1).  The reference's estimate_state is called from ONE
-// Julia process (src/tracking.jl:8-27), so the library shards inside: points in contiguous ranges of the caller's
+// Julia process (src/tracking.jl:8-27), so the library shards inside: points in round-robin chunks of the caller's
 // order, frames round-robin, rays in contiguous ranges.  The accumulators (cost, wrenches, RBF adjoint sums: a few
 // KB per configuration) are combined by ONE kernel on the first device that reads every device's buffer through
 // NVLink peer memory in a fixed order and writes the sum back to all of them -- deterministic, no NCCL in this mode
@@ -942,17 +953,29 @@ static int multi_reduce(flash_ctx* ctx, int C) {
   return 0;
 }
 
+// Points are dealt to the devices in chunks, round-robin: every device sees the whole scene (a contiguous split of a
+// spatially ordered cloud gave one of two GPUs all the points near the robot: 14.6 ms against 11.9 ms for a shuffled
+// cloud on K5), and a chunk is a contiguous piece of host memory, i.e. one DMA.  About 8 chunks per device, 1,024 to
+// 65,536 points each.
 template <class T>
 static int multi_points_set(flash_ctx* ctx, const T* xyz, int64_t n, bool async) {
   const int G = (int)ctx->subs.size();
-  ctx->shard_off.assign(G + 1, 0);
-  for (int g = 0; g <= G; ++g) ctx->shard_off[g] = (long long)((__int128)n * g / G);
+  long long chunk = (n / ((long long)G * 8) + 31) & ~31ll;
+  chunk = std::min<long long>(std::max<long long>(chunk, 1024), 65536);
+  ctx->seg_off.assign(G, {}); ctx->seg_len.assign(G, {});
+  std::vector<std::vector<const T*>> ptrs(G);
+  std::vector<std::vector<int64_t>> cnts(G);
+  int g = 0;
+  for (long long at = 0; at < n; at += chunk, g = (g + 1) % G) {
+    const long long len = std::min<long long>(chunk, n - at);
+    ctx->seg_off[g].push_back(at); ctx->seg_len[g].push_back(len);
+    ptrs[g].push_back(xyz + 3 * at); cnts[g].push_back(len);
+  }
+  ctx->n_points = n; ctx->have_points = true;
   ctx->frame_sub.clear();
-  for (int g = 0; g < G; ++g) {
+  for (g = 0; g < G; ++g) {
     flash_ctx* sub = ctx->subs[g];
-    const T* ptrs[1] = {xyz + 3 * ctx->shard_off[g]};
-    const int64_t counts[1] = {ctx->shard_off[g + 1] - ctx->shard_off[g]};
-    MSUB(ingest<T>(sub, sub->ps[sub->cur ^ 1], ptrs, counts, 1));
+    MSUB(ingest<T>(sub, sub->ps[sub->cur ^ 1], ptrs[g].data(), cnts[g].data(), (int)ptrs[g].size(), true));
     sub->back_pending = true;
   }
   if (async) { ctx->back_pending = true; return FLASH_OK; }
@@ -973,7 +996,7 @@ static int multi_frames_set(flash_ctx* ctx, const double* const* xyz, const int6
   std::vector<std::vector<const double*>> ptrs(G);
   std::vector<std::vector<int64_t>> cnts(G);
   for (int f = 0; f < F; ++f) { const int g = f % G; ctx->frame_sub[f] = g; ctx->frame_slot[f] = (int)ptrs[g].size(); ptrs[g].push_back(xyz[f]); cnts[g].push_back(counts[f]); }
-  ctx->shard_off.clear();
+  ctx->have_points = false;
   for (int g = 0; g < G; ++g) {
     flash_ctx* sub = ctx->subs[g];
     if (ptrs[g].empty()) { sub->back_pending = false; continue; }
@@ -995,18 +1018,23 @@ static void multi_timing(flash_ctx* ctx) {
   }
 }
 static int multi_cost_grad(flash_ctx* ctx, const double* X, int32_t C, double w_def, double* cost, double* grad, int32_t* argmin) {
-  if (ctx->shard_off.empty()) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad: call flash_points_set first (the ctx holds a batch of frames: use flash_cost_grad_frames)");
-  const long long N = ctx->shard_off.back();
+  if (!ctx->have_points) return fail(ctx, FLASH_ERR_STATE, "flash_cost_grad: call flash_points_set first (the ctx holds a batch of frames: use flash_cost_grad_frames)");
+  const long long N = ctx->n_points;
   for (flash_ctx* sub : ctx->subs) { sub->profiling = ctx->profiling; MSUB(cg_begin(sub, X, C, 0, grad != nullptr, argmin != nullptr)); }
   int rc = multi_reduce(ctx, C); if (rc) return rc;
   for (size_t g = 0; g < ctx->subs.size(); ++g) {
     flash_ctx* sub = ctx->subs[g];
     MSUB(cg_end(sub, C, w_def, grad != nullptr));
     const long long n_g = sub->ps[sub->cur].n;
-    if (argmin && n_g > 0) {   // this shard's columns of argmin[C][N]
-      flash_ctx* ctx2 = ctx; flash_ctx* ctx = sub;
-      CU(cudaMemcpy2DAsync(argmin + ctx2->shard_off[g], (size_t)N * sizeof(int32_t), sub->d_argmin, (size_t)n_g * sizeof(int32_t), (size_t)n_g * sizeof(int32_t), (size_t)C,
-                           cudaMemcpyDeviceToHost, sub->stream));
+    if (argmin && n_g > 0) {   // this device's chunks: columns of argmin[C][N]
+      flash_ctx* par = ctx; flash_ctx* ctx = sub;
+      long long at = 0;
+      for (size_t k = 0; k < par->seg_off[g].size(); ++k) {
+        const long long len = par->seg_len[g][k];
+        CU(cudaMemcpy2DAsync(argmin + par->seg_off[g][k], (size_t)N * sizeof(int32_t), sub->d_argmin + at, (size_t)n_g * sizeof(int32_t), (size_t)len * sizeof(int32_t), (size_t)C,
+                             cudaMemcpyDeviceToHost, sub->stream));
+        at += len;
+      }
     }
   }
   for (size_t g = 0; g < ctx->subs.size(); ++g) { flash_ctx* sub = ctx->subs[g]; MSUB(cg_finish(sub, C, g == 0 ? cost : nullptr, g == 0 ? grad : nullptr)); }
@@ -1250,10 +1278,10 @@ static int es_begin(flash_ctx* ctx, const double* X, int32_t C, const double* di
 // The solver loop on every device of a multi-device parent: each device evaluates its shard, the peer reduction hands
 // all of them the same sums, and every device then takes the same NaiveSolver step on its own copy of the state.
 static int multi_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solver_params* sp, const double* divisors, double* cost_out, int32_t* iters_out) {
-  if (ctx->shard_off.empty()) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: call flash_points_set first");
+  if (!ctx->have_points) return fail(ctx, FLASH_ERR_STATE, "flash_estimate_state: call flash_points_set first");
   const ModelC& M = ctx->hm.M;
   const size_t it_smem = std::max(prepare_smem_doubles(M), epilogue_smem_doubles(M)) * sizeof(double);
-  const double n_total = (double)ctx->shard_off.back();
+  const double n_total = (double)ctx->n_points;
   for (flash_ctx* sub : ctx->subs) { sub->profiling = false; MSUB(es_begin(sub, X, C, divisors, it_smem)); MSUB(run_prepare(sub, C, true)); }
   for (int it = 0; it < sp->iteration_limit; ++it) {
     for (flash_ctx* sub : ctx->subs) { flash_ctx* ctx = sub; CU(cudaSetDevice(sub->device)); int rc = run_cost(sub, C, true, nullptr); if (rc) return rc; }
