@@ -5,8 +5,8 @@ Workload (BASELINE.json configs[4], "K5"): the IRB140(floating base)+squishable+
 examples/irb_and_squishable.ipynb (63 states, 9 surfaces), 10,000,000 synthetic points uniform in the
 scene AABB [-0.5,1]x[-0.5,0.5]x[0.5,2], 64 candidate configurations (warm start + N(0,0.05)).
 One "step" = one flash_cost_grad call: cost[64] + grad[64][63] over all points.
-With N GPUs the POINTS are sharded across ranks by interleaved x-slabs of the same global cloud (total work
-fixed -> "strong" scaling; scene_points); each rank's
+With N GPUs the POINTS of the same global cloud are sharded across ranks (total work fixed -> "strong" scaling;
+scene_points: Morton-ordered blobs dealt round-robin by default); each rank's
 partial accumulators are summed by one ncclAllReduce inside the library before the epilogue.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode exact|grid]
@@ -61,28 +61,64 @@ def slab_counts(n_total):
     return [base + (1 if s < rem else 0) for s in range(SLABS)]
 
 
-def scene_points(n_total, rank=0, world=1, seed=1000):
-    """The global seeded cloud of n_total points, fp32-representable and uniform in the scene AABB, generated as
-    SLABS equal-count slabs along x (stratified uniform sampling: slab s is uniform in its x-range, drawn from its
-    own generator (seed, s)), so that every rank count sees the SAME cloud.  Returns the points of `rank`:
-    the slabs s with s % world == rank -- a spatial domain decomposition (interleaved, so that every rank samples
-    the whole scene) that keeps a rank's points as dense as the full cloud; sharding a randomly ordered cloud by
-    index instead thins every shard to 1/world of the density and costs the kernel's warp-level culling
-    15 % at world = 8."""
+def _global_cloud(n_total, seed):
+    """The global seeded cloud: fp32-representable points uniform in the scene AABB, generated as SLABS equal-count
+    slabs along x (stratified uniform sampling: slab s is uniform in its x-range, drawn from its own generator
+    (seed, s)) -- the same cloud at every rank count."""
     counts = slab_counts(n_total)
-    mine = [s_ for s_ in range(SLABS) if s_ % world == rank]
-    pts = np.empty((sum(counts[s_] for s_ in mine), 3), np.float64)
+    pts = np.empty((n_total, 3), np.float64)
     at = 0
     w = (SCENE_HI[0] - SCENE_LO[0]) / SLABS
-    for s_ in mine:
+    for s_ in range(SLABS):
         rng = np.random.default_rng([seed, s_])
         u = rng.random((counts[s_], 3), dtype=np.float32)
         lo = np.array([SCENE_LO[0] + s_ * w, SCENE_LO[1], SCENE_LO[2]])
         ext = np.array([w, SCENE_HI[1] - SCENE_LO[1], SCENE_HI[2] - SCENE_LO[2]])
-        chunk = (lo + ext * u).astype(np.float32)
-        pts[at:at + counts[s_]] = chunk
+        pts[at:at + counts[s_]] = (lo + ext * u).astype(np.float32)
         at += counts[s_]
     return pts
+
+
+BLOB = 8192   # points per blob of the "blobs" sharding rule (a multiple of the kernels' 32-point groups)
+
+
+def _morton_order(pts):
+    """argsort by a 30-bit Morton key over the scene AABB (host side, numpy): spatial neighbours become index neighbours"""
+    q = np.clip(((pts - SCENE_LO) / (SCENE_HI - SCENE_LO) * 1024).astype(np.int64), 0, 1023)
+    key = np.zeros(len(pts), np.int64)
+    for b_ in range(10):
+        for a_ in range(3):
+            key |= ((q[:, a_] >> b_) & 1) << (3 * b_ + a_)
+    return np.argsort(key, kind="stable")
+
+
+def scene_points(n_total, rank=0, world=1, seed=1000, shard="blobs"):
+    """The points of `rank` out of `world` of the global seeded cloud (_global_cloud), by one of three sharding rules:
+
+      blobs   (default) the cloud in Morton order is cut into blobs of BLOB consecutive points -- compact lumps a few
+              centimetres across -- dealt to the ranks round-robin: every rank holds points as DENSE as the full
+              cloud (the kernels' 32-point groups keep their small bounding balls) from ALL OVER the scene (the ranks'
+              work is balanced).  What a caller who splits a frame into image tiles gets.
+      slabs   rank r owns the x-slabs s with s % world == r: dense, but the ranks whose slabs cut through the robot work
+              17 % longer than the others at world = 8 (round-2 measurement, per_rank in the bench line).
+      index   contiguous index ranges of the cloud in random order: balanced, but every shard is a thin sample of the
+              whole scene -- 1/world of the density, bounding balls world^(1/3) times wider: +28 % kernel time per
+              evaluation at world = 8 (tools/density_probe.py).
+    world = 1 returns the whole cloud in generation order under every rule."""
+    pts = _global_cloud(n_total, seed)
+    if world == 1:
+        return pts
+    if shard == "slabs":
+        counts = slab_counts(n_total)
+        offs = np.concatenate([[0], np.cumsum(counts)])
+        return np.concatenate([pts[offs[s_]:offs[s_ + 1]] for s_ in range(SLABS) if s_ % world == rank]) if n_total else pts
+    if shard == "index":
+        perm = np.random.default_rng([seed, 12345]).permutation(n_total)
+        return pts[perm[(n_total * rank) // world:(n_total * (rank + 1)) // world]]
+    order = _morton_order(pts)
+    nblob = (n_total + BLOB - 1) // BLOB
+    mine = [order[b_ * BLOB:(b_ + 1) * BLOB] for b_ in range(rank, nblob, world)]
+    return pts[np.concatenate(mine)] if mine else pts[:0]
 
 
 class ClockSampler:
@@ -230,7 +266,7 @@ def run_ours(args, rank, local_rank, world):
 
     # shard the points: rank r owns the x-slabs s with s % world == r of the global cloud (scene_points)
     N = args.points
-    shard = scene_points(N, rank, world)
+    shard = scene_points(N, rank, world, shard=args.shard)
     n_local = len(shard)
     pin = torch.empty((n_local, 3), dtype=torch.float64, pin_memory=True)
     pts = pin.numpy()
@@ -331,6 +367,16 @@ def run_ours(args, rank, local_rank, world):
     if dist is not None:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     T, Te, Tk, Tkt, Tser, Tg = [float(v) for v in tt.cpu()]
+    per_rank = None
+    if dist is not None:   # where the time goes on every rank: cost kernel, group kernel, whole device step (ms, mean over the timed steps)
+        mine = torch.tensor([(sum(k_main) - sum(k_group)) / args.steps, sum(k_group) / args.steps, sum(k_total) / args.steps, 1e3 * sum(t_steps) / args.steps],
+                            dtype=torch.float64, device="cuda")
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        a = np.array([t.cpu().numpy() for t in allr])
+        per_rank = {"cost_kernel_ms": [round(float(v), 4) for v in a[:, 0]], "group_kernel_ms": [round(float(v), 4) for v in a[:, 1]],
+                    "device_step_ms": [round(float(v), 4) for v in a[:, 2]], "host_step_ms": [round(float(v), 4) for v in a[:, 3]],
+                    "cost_kernel_min_median_max": [float(np.min(a[:, 0])), float(np.median(a[:, 0])), float(np.max(a[:, 0]))]}
     units = float(N) * Cn * args.steps
     if rank == 0:
         peaks, peak_src = measured_peaks()
@@ -386,7 +432,8 @@ def run_ours(args, rank, local_rank, world):
             "dtype": "f32 distances / f64 RBF + accumulation", "data": "synthetic",
             "config": {"workload": "K5: IRB140(floating)+squishable+table (63 states, 9 surfaces), %d points x %d configs, points sharded over %d GPU(s)" % (N, Cn, world),
                        "points": N, "configs": Cn, "sdf_mode": args.mode, "l2": "L2 flushed (512 MiB memset) between timed steps; inputs %s L2" % ("exceed" if 16 * n_rank > l2.value else "fit"),
-                       "parallelism": "points sharded x%d by interleaved x-slabs (40 slabs, rank r owns slabs r mod %d), one ncclAllReduce of [%d][%d] fp64 per step" % (world, world, Cn, acc_len)},
+                       "parallelism": "points sharded x%d (rule '%s': %s), one ncclAllReduce of [%d][%d] fp64 per step" % (
+                           world, args.shard, {"blobs": "Morton-ordered blobs of %d points dealt round-robin" % BLOB, "slabs": "interleaved x-slabs", "index": "index ranges of the shuffled cloud"}[args.shard], Cn, acc_len)},
             "device_ms_per_step": 1e3 * Tkt / args.steps,
             "roofline": roof,
             "hbm_roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"],
@@ -409,6 +456,8 @@ def run_ours(args, rank, local_rank, world):
                 line["tracking"] = tracking_leg(flash, L)
             if args.configs_leg:
                 line["other_configs"] = configs_leg(flash, L, args.steps)
+        if per_rank is not None:
+            line["per_rank"] = per_rank
         if single_proc is not None:
             line["single_process_ctx"] = single_proc
         if args.parity:
@@ -739,6 +788,7 @@ def main():
     ap.add_argument("--points", type=int, default=10_000_000)
     ap.add_argument("--configs", type=int, default=64)
     ap.add_argument("--grid-spacing", type=float, default=0.004)
+    ap.add_argument("--shard", default="blobs", choices=["blobs", "slabs", "index"], help="how the global cloud is dealt to the ranks (scene_points)")
     ap.add_argument("--ref-points", type=int, default=1_000_000)
     ap.add_argument("--ref-configs", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")

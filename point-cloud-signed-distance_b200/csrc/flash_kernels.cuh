@@ -348,7 +348,7 @@ struct GroupParams {
 };
 constexpr int GBLOCK = 256;
 __host__ __device__ inline size_t group_smem(int tabf_len) { return align16(sizeof(HotModel)) + align16(sizeof(float) * (size_t)(tabf_len > 0 ? tabf_len : 4)); }
-__global__ void __launch_bounds__(GBLOCK, 2) group_kernel(const GroupParams p) {
+__global__ void __launch_bounds__(GBLOCK, 4) group_kernel(const GroupParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x, c = blockIdx.x;
   long long g0 = 0, g1 = p.n_groups;

@@ -237,7 +237,10 @@ int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride) {
   g.hot = ctx->d_hot; g.geo_f4 = ctx->d_geo_f4; g.geo_u32 = ctx->d_geo_u32;
   g.tab = ctx->d_tab; g.grp = P.d_grp; g.frames = cfg_per_frame > 0 ? P.d_frames : nullptr; g.cfg_per_frame = cfg_per_frame > 0 ? cfg_per_frame : 1;
   g.n_groups = G; g.rec = ctx->d_rec; g.rec_stride = G;
-  long long gpb = (G * C + (long long)ctx->sm_count * 4 - 1) / ((long long)ctx->sm_count * 4);
+  // groups per block: >= 16 waves of blocks when there is that much work (one thread per group: a block's cost varies with
+  // the groups' candidate counts, so few big blocks end in a long tail -- 1,280 blocks of 2,048 groups cost K5 at 1.25 M
+  // points 0.35 ms against 0.25 ms pro rata), never less than one group per thread
+  long long gpb = (G * C + (long long)ctx->sm_count * 8 * 16 - 1) / ((long long)ctx->sm_count * 8 * 16);
   gpb = std::min<long long>(std::max<long long>(((gpb + GBLOCK - 1) / GBLOCK) * GBLOCK, GBLOCK), 8 * GBLOCK);
   g.groups_per_block = (int)gpb;
   // exact centre distances pay when there are enough (group, configuration) pairs to fill the GPU with one thread each:

@@ -59,26 +59,32 @@ def test_sharded_points_allreduce_matches_single_rank():
 
 
 def test_shard_rule_covers_all_points_once():
-    """bench.scene_points: the union of the ranks' slabs is the N = 1 cloud (same points, every one once), the
-    shards are balanced, each shard spans the whole scene, and the cloud is uniform in the scene box."""
+    """bench.scene_points: under every sharding rule the union of the ranks' shards is the N = 1 cloud (same points,
+    every one once), the shards are balanced and each spans the whole scene; blobs are spatially compact; the cloud is
+    uniform in the scene box."""
     sys.path.insert(0, os.path.dirname(HERE))
     import bench
     key = lambda a: np.sort(a.view([("x", "f8"), ("y", "f8"), ("z", "f8")]).ravel())
     for n in (0, 1, 7, 100_003):
         whole = bench.scene_points(n)
         assert whole.shape == (n, 3)
-        for world in (1, 2, 4, 8):
-            parts = [bench.scene_points(n, r, world) for r in range(world)]
-            assert sum(len(p) for p in parts) == n
-            if n:
-                assert np.array_equal(key(np.concatenate(parts)), key(whole))
-            if n > 1000:
-                sizes = [len(p) for p in parts]
-                assert max(sizes) - min(sizes) <= bench.SLABS // world + 1
-                for p in parts:      # interleaved slabs: every rank sees (nearly) the full x-extent of the scene
-                    assert p[:, 0].max() - p[:, 0].min() > 0.75 * (bench.SCENE_HI[0] - bench.SCENE_LO[0])
+        for rule in ("blobs", "slabs", "index"):
+            for world in (1, 2, 4, 8):
+                parts = [np.ascontiguousarray(bench.scene_points(n, r, world, shard=rule)) for r in range(world)]
+                assert sum(len(p) for p in parts) == n
+                if n:
+                    assert np.array_equal(key(np.concatenate(parts)), key(whole))
+                if n > 1000:
+                    sizes = [len(p) for p in parts]
+                    assert max(sizes) - min(sizes) <= max(bench.SLABS // world + 1, bench.BLOB)
+                    for p in parts:      # every rank sees (nearly) the full x-extent of the scene
+                        assert p[:, 0].max() - p[:, 0].min() > 0.75 * (bench.SCENE_HI[0] - bench.SCENE_LO[0])
     big = bench.scene_points(100_003)
     assert (big >= bench.SCENE_LO).all() and (big <= bench.SCENE_HI).all()
     assert np.array_equal(big, big.astype(np.float32).astype(np.float64))          # fp32-representable
     h = np.histogram(big[:, 0], bins=10, range=(bench.SCENE_LO[0], bench.SCENE_HI[0]))[0]
     assert h.max() - h.min() < 0.05 * h.mean()
+    # a blob is a compact lump: its extent is far below the scene's
+    part = bench.scene_points(400_000, 3, 8)
+    blob = part[: bench.BLOB]
+    assert (blob.max(0) - blob.min(0)).max() < 0.5
