@@ -4,9 +4,10 @@
 # the build image (SURVEY 0.7).  The Python package `flash/` is the tested caller of the same ABI.
 #
 # What changes on the Julia side: nothing in src/tracking.jl, src/models.jl or the notebooks.
-# `Flash.GradientDescent.CostFunctor` gains a Float64 fast path that calls the library, and
-# `estimate_state` asks for cost AND gradient in one call instead of letting ForwardDiff push
-# ceil(nx/10) dual passes through `cost`.
+# `estimate_state` here has the reference's signature and defaults; it hands the solver the same
+# `(g, x) -> value` closure shape as `CostAndGradientFunctor` (src/gradientdescent.jl:59-65), with cost AND gradient
+# from one library call instead of ForwardDiff's ceil(nx/10) dual passes through `cost`, and it honours every field of
+# the solver object (rate, max_step, iteration_limit, gradient_convergence_tolerance, precondition_divisors).
 module FlashCUDA
 
 import Flash
@@ -14,6 +15,8 @@ import Flash: Manipulator, ManipulatorState, BodyGeometry, ConvexGeometry, Rigid
               DeformableInterpolatingSkin, num_states
 using RigidBodyDynamics
 import StaticArrays: SVector
+import SimpleGradientDescent
+import MathProgBase
 
 const lib = "libflashsdf"   # point-cloud-signed-distance_b200/lib must be on LD_LIBRARY_PATH
 
@@ -98,7 +101,7 @@ function Context(manip::Manipulator)
         push!(offs, div(length(pts), 3))
     end
     keep = Any[parent, jtype, axis, j2p, kind, sbody, sframe, offs, nsurf, pts, pbody]
-    desc = ModelDesc(1, length(verts), pointer(parent), pointer(jtype), pointer(axis), pointer(j2p),
+    desc = ModelDesc(2, length(verts), pointer(parent), pointer(jtype), pointer(axis), pointer(j2p),
                      length(kind), pointer(kind), pointer(sbody), pointer(sframe), pointer(offs),
                      pointer(nsurf), pointer(pts), pointer(pbody))
     out = Ref{Ptr{Void}}(C_NULL)
@@ -136,27 +139,115 @@ function cost_and_gradient!(ctx::Context, G::Matrix{Float64}, X::Matrix{Float64}
     costs
 end
 
+# ---- contexts are cached per manipulator: building one uploads the model and builds the hulls' BSP trees
+const contexts = ObjectIdDict()
+context(manip::Manipulator) = get!(() -> Context(manip), contexts, manip)::Context
+
 """
-Drop-in for `Flash.Tracking.estimate_state` (src/tracking.jl:8-27) with the same signature.  The loop,
-the callback (called with the RAW cost, as in the reference) and the solver object stay in Julia.
+The closure `src/tracking.jl:16-21` builds, with the gradient: `(g, x) -> value` in the shape of
+`CostAndGradientFunctor` (src/gradientdescent.jl:59-65).  As `wrapped_cost` does, it calls `callback(x, c)` with the
+RAW cost and returns `c / length(sensed_points)`; `g` receives the gradient of that returned value.
 """
-function estimate_state(manipulator::Manipulator, sensed_points::Vector{SVector{3, Float64}}, x_estimated::Vector{Float64};
-                        callback::Function=(x, c) -> (), solver=nothing, ctx::Context=Context(manipulator))
-    set_points!(ctx, sensed_points)
-    n = length(sensed_points)
-    rate = solver === nothing ? 0.1 : solver.rate
-    max_step = solver === nothing ? 0.5 : solver.max_step
-    iters = solver === nothing ? 30 : solver.iteration_limit
-    x = copy(x_estimated); g = similar(x)
-    for i in 1:iters
+function wrapped_cost_and_gradient(ctx::Context, n_points::Int, callback::Function)
+    (g, x) -> begin
         c = cost_and_gradient!(ctx, g, x)
         callback(x, c)
-        step = -rate .* g ./ n
+        scale!(g, 1 / n_points)
+        c / n_points
+    end
+end
+
+# mirror of flash_solver_params (include/flashsdf.h)
+immutable SolverParams
+    rate::Float64
+    max_step::Float64
+    iteration_limit::Int32
+    gradient_convergence_tolerance::Float64
+    deformation_cost_weight::Float64
+end
+
+field_or(solver, name::Symbol, default) = name in fieldnames(solver) ? getfield(solver, name) : default
+
+"""
+`optimize!` of a `SimpleGradientDescent.NaiveSolver` model with an analytic gradient.  SimpleGradientDescent
+(@0fcc1f9, REQUIRE.dev:24) is not in the reference tree; the step is the one its keyword names describe
+(src/tracking.jl:12-15, examples/irb140.ipynb cell 9, examples/squishable.ipynb cell 9) and the one
+flash_estimate_state runs on the device:  g = grad(cost / N);  stop when |g| < gradient_convergence_tolerance;
+step = -rate * g ./ precondition_divisors, rescaled so that |step| <= max_step;  x += step.
+EVERY field of the solver is honoured; `fg!` is the closure above, so the callback sees every evaluation.
+"""
+function naive_optimize!(fg!::Function, solver, x0::Vector{Float64})
+    x = copy(x0); g = similar(x)
+    rate = field_or(solver, :rate, 0.1)
+    max_step = field_or(solver, :max_step, 0.5)
+    iters = field_or(solver, :iteration_limit, 30)
+    tol = field_or(solver, :gradient_convergence_tolerance, 0.0)
+    div = field_or(solver, :precondition_divisors, nothing)
+    divisors = div === nothing ? ones(length(x)) : Float64[d for d in div]
+    for i in 1:iters
+        fg!(g, x)
+        (tol > 0 && norm(g) < tol) && break
+        step = -rate .* g ./ divisors
         s = norm(step)
-        s > max_step && (step .*= max_step / s)
+        s > max_step && scale!(step, max_step / s)
         x .+= step
     end
     x
+end
+
+"""
+A `MathProgBase.AbstractNLPEvaluator` over the same closure, for solvers that go through MathProgBase
+(`IpoptSolver(print_level=1, max_iter=50)`, examples/squishable.ipynb:344): objective and gradient from the library,
+no constraints, no Hessian (Ipopt then runs its limited-memory quasi-Newton mode, as it does for the reference's
+ForwardDiff gradient).
+"""
+type FlashEvaluator <: MathProgBase.AbstractNLPEvaluator
+    fg!::Function
+    scratch::Vector{Float64}
+end
+MathProgBase.initialize(::FlashEvaluator, requested_features::Vector{Symbol}) =
+    all(f -> f in (:Grad,), requested_features) || error("FlashEvaluator provides :Grad only")
+MathProgBase.features_available(::FlashEvaluator) = [:Grad]
+MathProgBase.eval_f(e::FlashEvaluator, x) = e.fg!(e.scratch, x)
+MathProgBase.eval_grad_f(e::FlashEvaluator, g, x) = (e.fg!(g, x); nothing)
+MathProgBase.eval_g(::FlashEvaluator, g, x) = nothing
+MathProgBase.jac_structure(::FlashEvaluator) = Int[], Int[]
+MathProgBase.eval_jac_g(::FlashEvaluator, J, x) = nothing
+
+"""
+Drop-in for `Flash.Tracking.estimate_state` (src/tracking.jl:8-27), same signature, same defaults.
+ * NaiveSolver with a callback: the loop stays in Julia (`naive_optimize!`), one flash_cost_grad per iteration.
+ * NaiveSolver without a callback: the whole loop runs on the device (flash_estimate_state), all solver fields passed.
+ * any MathProgBase solver (IpoptSolver): driven through `FlashEvaluator`.
+The context of a manipulator is built once and cached (`context`).
+"""
+function estimate_state(manipulator::Manipulator, sensed_points::Vector{SVector{3, Float64}}, x_estimated::Vector{Float64};
+                        callback::Union{Function, Void}=nothing,
+                        solver=SimpleGradientDescent.NaiveSolver(num_states(manipulator), rate=0.1, max_step=0.5, iteration_limit=30),
+                        ctx::Context=context(manipulator))
+    set_points!(ctx, sensed_points)
+    n = length(sensed_points)
+    if isa(solver, SimpleGradientDescent.NaiveSolver)
+        if callback === nothing
+            x = copy(x_estimated)
+            div = field_or(solver, :precondition_divisors, nothing)
+            divisors = div === nothing ? ones(length(x)) : Float64[d for d in div]   # (a named array: ccall roots it for the call)
+            sp = SolverParams(solver.rate, solver.max_step, solver.iteration_limit,
+                              field_or(solver, :gradient_convergence_tolerance, 0.0), Flash.GradientDescent.default_deformation_cost_weight)
+            check(ctx.ptr, ccall((:flash_estimate_state, lib), Cint,
+                                 (Ptr{Void}, Ptr{Float64}, Int32, Ptr{SolverParams}, Ptr{Float64}, Ptr{Float64}, Ptr{Int32}),
+                                 ctx.ptr, x, 1, &sp, divisors, C_NULL, C_NULL))
+            return x
+        end
+        return naive_optimize!(wrapped_cost_and_gradient(ctx, n, callback), solver, x_estimated)
+    end
+    fg! = wrapped_cost_and_gradient(ctx, n, callback === nothing ? (x, c) -> () : callback)
+    nvars = num_states(manipulator)
+    model = MathProgBase.NonlinearModel(solver)
+    MathProgBase.loadproblem!(model, nvars, 0, fill(-Inf, nvars), fill(Inf, nvars), Float64[], Float64[], :Min, FlashEvaluator(fg!, zeros(nvars)))
+    MathProgBase.setwarmstart!(model, x_estimated)
+    MathProgBase.optimize!(model)
+    MathProgBase.getsolution(model)
 end
 
 "`DepthSensors.raycast_depths` (src/depthsensors.jl:88-97) on the device; NaN marks a miss."

@@ -63,3 +63,38 @@ def test_bad_descriptions_are_rejected_before_touching_the_device():
     assert b"abi_version" in L.flash_last_error(None)
     assert L.flash_model_create(None, None, C.byref(out)) == -1
     assert L.flash_num_states(None) == -1
+
+
+def _driver():
+    """tests/abi_driver: the plain-C caller of every ABI entry point (built by __graft_entry__.build())"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "tests", "abi_driver")
+    src = os.path.join(root, "tests", "abi_driver.c")
+    libdir = os.path.join(root, "point-cloud-signed-distance_b200", "lib")
+    if not os.path.exists(exe) or os.path.getmtime(exe) < os.path.getmtime(src):
+        subprocess.check_call(["gcc", "-O1", "-std=c99", "-Wall", "-o", exe, src, "-L" + libdir, "-lflashsdf", "-lm", "-Wl,-rpath," + libdir])
+    gold = os.path.join(root, "tests", "golden")
+    return [exe, os.path.join(gold, "IRB140", "urdf", "irb_140_convhull.urdf"), gold]
+
+
+def test_plain_c_driver_host_side(tmp_path):
+    """Every header symbol is callable from C; without a device the file-ingestion entry points work and every compute
+    entry point fails loudly (FLASH_ERR_NO_DEVICE) -- there is no CPU path to fall back to."""
+    import subprocess
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by test_plain_c_driver_on_the_gpu")
+    r = subprocess.run(_driver() + [str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 0 and "FAIL " not in r.stdout and "PASSED (host-side checks only" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_plain_c_driver_on_the_gpu(tmp_path):
+    """The same driver on a GPU box: cost / gradient / argmin against the closed form of a box, the beanbag known answer
+    of test/runtests.jl:17, frames, async upload + swap, files, ray casting, the on-device solver, iso-surface
+    extraction, grid mode, deterministic + multi-device contexts, URDF loading -- all from plain C."""
+    import subprocess
+    r = subprocess.run(_driver() + [str(tmp_path)], capture_output=True, text=True)
+    print(r.stdout)
+    assert r.returncode == 0 and "FAIL " not in r.stdout and r.stdout.strip().endswith("PASSED"), r.stdout + r.stderr
