@@ -13,8 +13,34 @@ ORACLE_DIR = os.path.join(ROOT, "oracle")
 LIB = os.path.join(ORACLE_DIR, "liboracle.so")
 
 import sys
-sys.path.insert(0, os.path.join(ROOT, "point-cloud-signed-distance_b200"))
-from flash._desc import ModelDesc, PackedModel, SolverParams, c_double_p, c_int32_p  # noqa: E402
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import indep  # noqa: E402  (the oracle's model description is packed by the independent restatement, not by the product's flash._desc)
+from indep import ModelDesc  # noqa: E402
+
+c_double_p = C.POINTER(C.c_double)
+c_int32_p = C.POINTER(C.c_int32)
+
+
+class SolverParams(C.Structure):   # flash_solver_params of include/flashsdf.h
+    _fields_ = [("rate", C.c_double), ("max_step", C.c_double), ("iteration_limit", C.c_int32),
+                ("gradient_convergence_tolerance", C.c_double), ("deformation_cost_weight", C.c_double)]
+
+
+def model_dict(manipulator):
+    """A product-side Manipulator (duck-typed: nothing of `flash` is imported here) as the dict form of tests/indep.py.
+    Tests that want the oracle independent of the product's model BUILDERS too pass indep.MODELS[...]() instead."""
+    if isinstance(manipulator, dict):
+        return manipulator
+    bodies = [dict(parent=b.parent, jtype=b.joint_type, axis=tuple(float(v) for v in b.axis), j2p=np.asarray(b.joint_to_parent, float).reshape(3, 4), name=getattr(b, "name", ""))
+              for b in manipulator.mechanism.bodies]
+    surfaces = []
+    for s_ in manipulator.surfaces:
+        if hasattr(s_, "vertices"):
+            surfaces.append(dict(kind="convex", body=s_.body, frame=np.asarray(s_.frame, float).reshape(3, 4), verts=np.asarray(s_.vertices, float).reshape(-1, 3)))
+        else:
+            surfaces.append(dict(kind="deformable" if type(s_).__name__.startswith("Deformable") else "rigid",
+                                 surface=[(int(b), tuple(p)) for b, p in s_.surface_points], skeleton=[(int(b), tuple(p)) for b, p in s_.skeleton_points]))
+    return dict(bodies=bodies, surfaces=surfaces)
 
 BRUTE, GJK = 0, 1
 _lib = None
@@ -57,13 +83,13 @@ def _p(a):
 class Oracle:
     def __init__(self, manipulator, normalize_by_gradient=1, poly_degree=1, threads=None):
         L = lib()
-        self.packed = PackedModel(manipulator)
+        self.packed = indep.Packed(model_dict(manipulator))
         self.h = L.fo_model_create(C.byref(self.packed.desc), normalize_by_gradient, poly_degree)
         if not self.h:
             raise RuntimeError("oracle: " + L.fo_last_error().decode())
         self.nx = L.fo_num_states(self.h)
         self.nq = L.fo_num_positions(self.h)
-        self.n_surfaces = len(manipulator.surfaces)
+        self.n_surfaces = self.packed.n_surfaces
         self.threads = threads or L.fo_max_threads()
 
     def __del__(self):
