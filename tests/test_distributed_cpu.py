@@ -87,6 +87,6 @@ def test_shard_rule_covers_all_points_once():
     h = np.histogram(big[:, 0], bins=10, range=(bench.SCENE_LO[0], bench.SCENE_HI[0]))[0]
     assert h.max() - h.min() < 0.05 * h.mean()
     # a blob is a compact lump: its extent is far below the scene's
-    part = bench.scene_points(400_000, 3, 8)
+    part = bench.scene_points(2_000_000, 3, 8)
     blob = part[: bench.BLOB]
-    assert (blob.max(0) - blob.min(0)).max() < 0.5
+    assert (blob.max(0) - blob.min(0)).max() < 0.6     # a piece of the Z-curve: ~20 cm of the 1.5 m scene at this density
