@@ -218,7 +218,7 @@ def run_reference(args, rank, world):
     line = {"metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * base["seconds"] / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "impl": "reference",
-            "config": {"workload": "K5: IRB140(floating)+squishable+table, 63 states, 9 surfaces; bounded sample of 10M points x 64 configs",
+            "config": {"workload": "K5: IRB140(floating)+squishable+table, 63 states, 9 surfaces; bounded sample of 10M points x 64 configs: ALL %d configurations, %d of the points (uniform in the same scene box; the rate is per evaluation)" % (args.ref_configs, args.ref_points),
                        "points": args.ref_points, "configs": args.ref_configs},
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -789,8 +789,8 @@ def main():
     ap.add_argument("--configs", type=int, default=64)
     ap.add_argument("--grid-spacing", type=float, default=0.004)
     ap.add_argument("--shard", default="blobs", choices=["blobs", "slabs", "index"], help="how the global cloud is dealt to the ranks (scene_points)")
-    ap.add_argument("--ref-points", type=int, default=1_000_000)
-    ap.add_argument("--ref-configs", type=int, default=4)
+    ap.add_argument("--ref-points", type=int, default=100_000)
+    ap.add_argument("--ref-configs", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
     ap.add_argument("--no-parity", dest="parity", action="store_false", help="skip the oracle check of config 0 after the timed loops")
     ap.add_argument("--no-extras", dest="extras", action="store_false", help="skip the grid-mode and K3 tracking legs (N=1 only)")
