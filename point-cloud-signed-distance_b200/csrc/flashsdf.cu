@@ -214,7 +214,10 @@ int choose_tile(const flash_ctx* ctx, long long n, int C) {
     ppb = std::max<long long>(32, ((ppb + 31) / 32) * 32);
     return (int)ppb;
   }
-  const long long target_blocks = (long long)ctx->sm_count * 2 * 4;
+  // >= 20 waves of blocks (2 per SM) where there is that much work (swept 4 .. 64 on K4 and on K5 at the per-rank size of 8 GPUs): the blocks' durations differ several-fold (tiles near the
+  // bodies), so few waves end in a long tail -- K4's 8 x 16 batch ran as 1,280 blocks = 4.3 waves with 32,768-point tiles
+  static const long long waves = [] { const char* e = getenv("FLASHSDF_WAVES"); long long v = e ? atoll(e) : 0; return v > 0 ? v : 20ll; }();
+  const long long target_blocks = (long long)ctx->sm_count * 2 * waves;
   long long ppb = (n * C + target_blocks - 1) / target_blocks;
   ppb = ((ppb + CBLOCK - 1) / CBLOCK) * CBLOCK;
   if (ppb < CBLOCK) ppb = CBLOCK;
