@@ -6,7 +6,7 @@
 // bounding ball drives every group-level cull and certificate (flash_dev.h group_prepass).  The tighter the balls, the
 // more the kernel can decide once per group instead of once per point.  Pipeline, all on the ctx's copy stream:
 //
-//   points_bounds_kernel   AABB of each frame (ordered-integer atomics)
+//   frames_bounds_kernel   AABB of each frame (ordered-integer atomics)
 //   points_keys_kernel     key = frame << hb*3 | Hilbert index of the point's cell in a 2^hb-per-axis CUBIC grid over the
 //                          frame's AABB (hb = 10 bits per axis for up to 4 frames)
 //   radix_*_kernel         stable LSD radix sort of (key, index), 8 bits per pass, 2-4 passes: per-warp digit histograms,

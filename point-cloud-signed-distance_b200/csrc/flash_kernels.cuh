@@ -90,10 +90,6 @@ __host__ __device__ inline SmemLayout smem_layout(int tab_len, int acc_len, int 
   return L;
 }
 
-// monotone float <-> int maps, so that REDUX.MIN (integer) reduces floats
-__device__ __forceinline__ int ordered_int(float f) { const int i = __float_as_int(f); return i ^ ((i >> 31) & 0x7fffffff); }
-__device__ __forceinline__ float from_ordered_int(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
-
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -772,11 +768,8 @@ __global__ void __launch_bounds__(32) epilogue_kernel(const ModelC* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------------
-// Point ingestion: fp64 or fp32 [n][3] AoS (the memory of a Julia Vector{SVector{3,Float64}}) ->
-// float4 rounded once, and re-ordered into Morton order of a 64^3 cell grid over the cloud's AABB
-// so that the 32 points of a warp lie within ~one cell: all lanes then cull the same bodies and run
-// the same GJK iterations (measured: 9.4 -> ~25 active lanes per instruction).  The cost is a sum
-// over points, so the order is free; `perm` maps sorted position -> caller's index for argmin.
+// Point ingestion helpers shared with flash_ingest.cuh (which holds the pipeline: bounds, Hilbert keys, radix sort,
+// gather + group balls): fp64 or fp32 [n][3] AoS (the memory of a Julia Vector{SVector{3,Float64}}) -> float4 rounded once.
 template <class T>
 __device__ __forceinline__ float3 load_xyz(const T* __restrict__ src, long long i) {
   return make_float3((float)src[3 * i], (float)src[3 * i + 1], (float)src[3 * i + 2]);
@@ -790,114 +783,7 @@ __host__ __device__ inline float from_ordered_bits(unsigned u) {
   float f; memcpy(&f, &u, 4); return f;
 #endif
 }
-// bounds[0..2] = min (ordered bits), bounds[3..5] = max
-template <class T>
-__global__ void points_bounds_kernel(const T* __restrict__ src, long long n, unsigned* __restrict__ bounds) {
-  float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    float3 p = load_xyz(src, i);
-    if (p.x == p.x && p.y == p.y && p.z == p.z && fabsf(p.x) < 1e30f && fabsf(p.y) < 1e30f && fabsf(p.z) < 1e30f) {
-      lo[0] = fminf(lo[0], p.x); lo[1] = fminf(lo[1], p.y); lo[2] = fminf(lo[2], p.z);
-      hi[0] = fmaxf(hi[0], p.x); hi[1] = fmaxf(hi[1], p.y); hi[2] = fmaxf(hi[2], p.z);
-    }
-  }
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o)); hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o)); }
-  }
-  if ((threadIdx.x & 31) == 0) {
-#pragma unroll
-    for (int k = 0; k < 3; ++k) { atomicMin(bounds + k, ordered_bits(lo[k])); atomicMax(bounds + 3 + k, ordered_bits(hi[k])); }
-  }
-}
-constexpr int SORT_BITS = 6;                       // 64 cells per axis
-constexpr int SORT_BINS = 1 << (3 * SORT_BITS);    // 262,144
-__device__ __forceinline__ unsigned spread3(unsigned v) {  // 6 bits -> every third bit
-  v &= 0x3f;
-  v = (v | (v << 8)) & 0x300f;
-  v = (v | (v << 4)) & 0x30c3;
-  v = (v | (v << 2)) & 0x9249;
-  return v;
-}
-__device__ __forceinline__ unsigned cell_of(float3 p, const unsigned* __restrict__ bounds) {
-  unsigned key = 0;
-  const float v[3] = {p.x, p.y, p.z};
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    const float lo = from_ordered_bits(bounds[k]), hi = from_ordered_bits(bounds[3 + k]);
-    const float ext = hi - lo;
-    float t = ext > 0.f ? (v[k] - lo) / ext : 0.f;
-    int c = (int)(t * (float)(1 << SORT_BITS));
-    c = c < 0 ? 0 : (c > (1 << SORT_BITS) - 1 ? (1 << SORT_BITS) - 1 : c);   // NaN -> 0
-    key |= spread3((unsigned)c) << k;
-  }
-  return key;
-}
-template <class T>
-__global__ void points_hist_kernel(const T* __restrict__ src, long long n, const unsigned* __restrict__ bounds, int* __restrict__ bins) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) atomicAdd(bins + cell_of(load_xyz(src, i), bounds), 1);
-}
-// exclusive scan of SORT_BINS counters: per-1024 local scan, scan of the 256 block sums, add back
-__global__ void __launch_bounds__(1024) bins_scan_local_kernel(int* __restrict__ bins, int* __restrict__ block_sums) {
-  __shared__ int wsum[32];
-  const int i = blockIdx.x * 1024 + threadIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int v = bins[i];
-  int x = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-  if (lane == 31) wsum[w] = x;
-  __syncthreads();
-  if (w == 0) {
-    int s = wsum[lane];
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
-    wsum[lane] = s;
-  }
-  __syncthreads();
-  const int incl = x + (w > 0 ? wsum[w - 1] : 0);
-  bins[i] = incl - v;
-  if (threadIdx.x == 1023) block_sums[blockIdx.x] = incl;
-}
-__global__ void __launch_bounds__(1024) bins_scan_add_kernel(int* __restrict__ bins, const int* __restrict__ block_sums) {
-  __shared__ int base;
-  if (threadIdx.x == 0) { int s = 0; for (int b = 0; b < (int)blockIdx.x; ++b) s += block_sums[b]; base = s; }
-  __syncthreads();
-  bins[blockIdx.x * 1024 + threadIdx.x] += base;
-}
-template <class T>
-__global__ void points_scatter_kernel(const T* __restrict__ src, long long n, const unsigned* __restrict__ bounds, int* __restrict__ cursor,
-                                      float4* __restrict__ dst, int* __restrict__ perm) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const float3 p = load_xyz(src, i);
-  const int pos = atomicAdd(cursor + cell_of(p, bounds), 1);
-  dst[pos] = make_float4(p.x, p.y, p.z, 0.f);
-  perm[pos] = (int)i;
-}
-// bounding ball of every 32 consecutive (Morton-neighbouring) points: one warp per group
-__global__ void __launch_bounds__(256) points_groups_kernel(const float4* __restrict__ pts, long long n, float4* __restrict__ grp) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long g = i >> 5;
-  if (g * 32 >= n) return;
-  float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
-  if (i < n) { const float4 p = __ldg(pts + i); lo[0] = hi[0] = p.x; lo[1] = hi[1] = p.y; lo[2] = hi[2] = p.z; }
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o)); hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o)); }
-  }
-  if ((threadIdx.x & 31) == 0) {
-    const float cx = 0.5f * (lo[0] + hi[0]), cy = 0.5f * (lo[1] + hi[1]), cz = 0.5f * (lo[2] + hi[2]);
-    const float ex = fmaxf(hi[0] - cx, cx - lo[0]), ey = fmaxf(hi[1] - cy, cy - lo[1]), ez = fmaxf(hi[2] - cz, cz - lo[2]);
-    float rho = sqrtf(ex * ex + ey * ey + ez * ez) * (1.f + 1e-6f) + 1e-30f;
-    float4 o = make_float4(cx, cy, cz, rho);
-    if (!(rho < 3e37f) || !(fabsf(cx) < 3e37f) || !(fabsf(cy) < 3e37f) || !(fabsf(cz) < 3e37f)) o = make_float4(0.f, 0.f, 0.f, 1e30f);  // NaN / inf: no culling
-    grp[g] = o;
-  }
-}
-// unsorted conversion (clouds too small to be worth sorting, or > 2^31 points)
+// plain conversion of query points (flash_skin_eval)
 template <class T>
 __global__ void convert_points_kernel(const T* __restrict__ src, float4* __restrict__ dst, long long n) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
