@@ -39,8 +39,10 @@ def consts(full, opc):
            "warp_instructions": int(g("smsp__inst_executed.sum")), "issue_active_pct": round(g("smsp__issue_active.avg.pct_of_peak_sustained_active"), 2),
            "kernel_ms_under_ncu": round(g("gpu__time_duration.sum"), 3), "lanes_active": round(g("smsp__thread_inst_executed_per_inst_executed.ratio"), 2),
            "warps_active_pct": round(g("sm__warps_active.avg.pct_of_peak_sustained_active"), 1), "registers": int(g("launch__registers_per_thread"))}
-    try:
-        out["lts_bytes"] = int(g("lts__t_bytes.sum"))
+    try:                                                  # L2 traffic: sectors of 32 B (lts__t_bytes is not in every ncu section set)
+        out["lts_bytes"] = int(g("lts__t_sectors.sum")) * 32
+        out["l2_hit_pct"] = round(g("lts__t_sector_hit_rate.pct"), 1)
+        out["l1_hit_pct"] = round(g("l1tex__t_sector_hit_rate.pct"), 1)
     except Exception:
         pass
     # executed floating-point work from the opcode roll-up (thread-level: warp instructions x active lanes)
