@@ -229,6 +229,31 @@ int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t 
                     double* dist, int32_t* argmin);
 
 /*
+ * flash_skin_eval for callers that may not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * flash_skin_eval, but the call allocates nothing, on the device or on the host side of the CUDA
+ * runtime: every device temporary (the state, the kinematics / RBF tables prepare_kernel
+ * derives from it, the query points as doubles and as float4, the distances, the argmin, the
+ * status word) lives in ONE file-scope `static __device__` array of
+ * FLASH_STATIC_SCRATCH_BYTES (4 MiB) that every GPU which loads the library holds until exit.
+ * Limits, checked before anything is launched (FLASH_ERR_TOO_LARGE with a message naming them):
+ *   n <= FLASH_STATIC_MAX_QUERY (65,536 query points per call), and
+ *   8 * (num_states + the model's table lengths) <= FLASH_STATIC_STATE_BYTES (512 KiB).
+ * x, xyz, dist and argmin may be host or device pointers (copied with cudaMemcpyDefault).
+ * The array is shared by every context on a device and keeps the last call's contents; the call
+ * clears what must start at zero (the status word), holds a process-wide lock and returns only
+ * when its stream has drained, so calls made through this entry point never overlap -- any two
+ * users of the array that DID overlap on the GPU would race.  A multi-device context
+ * evaluates on its first device, as flash_skin_eval does.
+ */
+#define FLASH_STATIC_MAX_QUERY 65536
+#define FLASH_STATIC_STATE_BYTES (512 * 1024)
+#define FLASH_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int flash_skin_eval_static(flash_ctx* ctx, const double* x, const double* xyz, int64_t n,
+                           double* dist, int32_t* argmin);
+
+/*
  * `DepthSensors.raycast_depths` / `raycast_points` (src/depthsensors.jl:56-113).
  * rays [R][3] are the SENSOR-frame unit rays (generateKinectRays, :10-30) in row-major order,
  * cam[12] the row-major [R|t] sensor->world transform.  depths[R] receives the marching distance

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1167,6 +1168,80 @@ int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t 
   CU(cudaMemcpyAsync(dist, d_dist, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
   if (argmin) CU(cudaMemcpyAsync(argmin, ctx->d_qi, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
   return check_status(ctx);
+}
+
+// ---- flash_skin_eval without any allocation (include/flashsdf.h: no counterpart in the reference) ----
+// The scratch of the call: a file-scope device array, FLASH_STATIC_SCRATCH_BYTES on every GPU that loads the library.
+//   [0, 256)                               status word of prepare_kernel (cleared by every call)
+//   [256, FLASH_STATIC_STATE_BYTES)        x[nx] | tab[tab_len] | aux[aux_len]   (doubles, each rounded up to 256 B)
+//   then, at fixed offsets sized for FLASH_STATIC_MAX_QUERY points: xyz (3 doubles) | float4 | dist (double) | argmin (int)
+// In HOST code `g_static_scratch` is the host-side stand-in of the symbol, not a device address: the address a kernel may
+// be given comes from cudaGetSymbolAddress, looked up once per device with that device current (static_scratch_base).
+static __device__ __align__(256) unsigned char g_static_scratch[FLASH_STATIC_SCRATCH_BYTES];
+static_assert((size_t)FLASH_STATIC_STATE_BYTES + (size_t)FLASH_STATIC_MAX_QUERY * (24 + 16 + 8 + 4) <= (size_t)FLASH_STATIC_SCRATCH_BYTES, "static scratch layout");
+static std::mutex g_static_mu;                 // held for a whole call: the array is shared by every context of the process
+static unsigned char* g_static_base[64] = {};  // per device ordinal
+
+static int static_scratch_base(flash_ctx* ctx, unsigned char** base) {   // ctx->device is current; g_static_mu is held
+  const int dev = ctx->device;
+  if (dev >= 0 && dev < 64 && g_static_base[dev]) { *base = g_static_base[dev]; return 0; }
+  void* p = nullptr;
+  CU(cudaGetSymbolAddress(&p, g_static_scratch));
+  if (!p) return fail(ctx, FLASH_ERR_CUDA, "cudaGetSymbolAddress(g_static_scratch) returned a null address");
+  if (dev >= 0 && dev < 64) g_static_base[dev] = (unsigned char*)p;
+  *base = (unsigned char*)p;
+  return 0;
+}
+
+int flash_skin_eval_static(flash_ctx* ctx, const double* x, const double* xyz, int64_t n, double* dist, int32_t* argmin) {
+  if (!ctx) return FLASH_ERR_INVALID;
+  if (!x || n < 0 || (n > 0 && (!xyz || !dist))) return fail(ctx, FLASH_ERR_INVALID, "flash_skin_eval_static: bad arguments");
+  if (!ctx->subs.empty()) { int rc = flash_skin_eval_static(ctx->subs[0], x, xyz, n, dist, argmin); if (rc) ctx->err = ctx->subs[0]->err; return rc; }
+  if (n > FLASH_STATIC_MAX_QUERY)
+    return fail(ctx, FLASH_ERR_TOO_LARGE, "flash_skin_eval_static: " + std::to_string((long long)n) + " query points exceed FLASH_STATIC_MAX_QUERY = " +
+                                              std::to_string(FLASH_STATIC_MAX_QUERY) + " (split the call, or use flash_skin_eval)");
+  const ModelC& M = ctx->hm.M;
+  auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+  const size_t off_x = 256, off_tab = off_x + up((size_t)M.nx * 8), off_aux = off_tab + up((size_t)std::max(M.tab_len, 1) * 8),
+               end_state = off_aux + up((size_t)std::max(M.aux_len, 1) * 8);
+  if (end_state > (size_t)FLASH_STATIC_STATE_BYTES)
+    return fail(ctx, FLASH_ERR_TOO_LARGE, "flash_skin_eval_static: the model's state and tables (" + std::to_string(end_state) +
+                                              " bytes) exceed FLASH_STATIC_STATE_BYTES = " + std::to_string(FLASH_STATIC_STATE_BYTES));
+  if (n == 0) return FLASH_OK;
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  CU(cudaSetDevice(ctx->device));
+  unsigned char* base = nullptr;
+  int rc = static_scratch_base(ctx, &base); if (rc) return rc;
+  const size_t Q = (size_t)FLASH_STATIC_MAX_QUERY, off_xyz = (size_t)FLASH_STATIC_STATE_BYTES, off_f4 = off_xyz + 24 * Q, off_dist = off_f4 + 16 * Q, off_arg = off_dist + 8 * Q;
+  int* d_status = (int*)base;
+  double *d_x = (double*)(base + off_x), *d_tab = (double*)(base + off_tab), *d_aux = (double*)(base + off_aux);
+  double *d_xyz = (double*)(base + off_xyz), *d_dist = (double*)(base + off_dist);
+  float4* d_f4 = (float4*)(base + off_f4);
+  int32_t* d_arg = (int32_t*)(base + off_arg);
+  ctx->last = flash_timing{0, 0, 0, 0, 0, 0, 0};
+  CU(cudaMemsetAsync(d_status, 0, sizeof(int), ctx->stream));   // the array keeps the last call's contents: the flag must start at zero
+  CU(cudaMemcpyAsync(d_x, x, (size_t)M.nx * sizeof(double), cudaMemcpyDefault, ctx->stream));
+  CU(cudaMemcpyAsync(d_xyz, xyz, (size_t)n * 3 * sizeof(double), cudaMemcpyDefault, ctx->stream));
+  const size_t psmem = prepare_smem_doubles(M) * sizeof(double);
+  if (psmem > 48 * 1024) CU(cudaFuncSetAttribute(prepare_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem));
+  prepare_kernel<<<1, PREP_T, psmem, ctx->stream>>>(ctx->d_model, d_x, d_tab, d_aux, nullptr, d_status);
+  CU(cudaGetLastError());
+  convert_points_kernel<double><<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d_xyz, d_f4, n);
+  CU(cudaGetLastError());
+  ctx->launches += 2; ctx->last.launches += 2;
+  CostParams p;
+  p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
+  p.pts = d_f4; p.n_pts = n; p.tab = d_tab; p.acc = nullptr; p.argmin = d_arg; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr; p.frames = nullptr; p.cfg_per_frame = 1; p.rec = nullptr; p.rec_stride = 0; p.part = nullptr;
+  p.pts_per_block = choose_tile(ctx, n, 1); p.use_grid = ctx->use_grid ? 1 : 0;
+  const int tiles = (int)((n + p.pts_per_block - 1) / p.pts_per_block);
+  if ((rc = launch_cost_t<false, true, true>(ctx, p, 1, tiles, cost_layout(ctx, false).total))) return rc;
+  int st = 0;
+  CU(cudaMemcpyAsync(dist, d_dist, (size_t)n * sizeof(double), cudaMemcpyDefault, ctx->stream));
+  if (argmin) CU(cudaMemcpyAsync(argmin, d_arg, (size_t)n * sizeof(int32_t), cudaMemcpyDefault, ctx->stream));
+  CU(cudaMemcpyAsync(&st, d_status, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  if (st != 0) return fail(ctx, FLASH_ERR_INVALID, "singular RBF system (coincident skin control points)");
+  return FLASH_OK;
 }
 
 int flash_kinect_rays(int32_t rows, int32_t cols, double vertical_fov, double horizontal_fov, double* rays) {

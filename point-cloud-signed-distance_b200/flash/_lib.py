@@ -23,6 +23,7 @@ SYMBOLS = [
     "flash_frames_set", "flash_frames_set_async", "flash_num_frames", "flash_cost_grad_frames",
     "flash_urdf_load", "flash_urdf_desc", "flash_urdf_body_name", "flash_urdf_surface_mesh", "flash_urdf_set_joint_type", "flash_urdf_free",
     "flash_model_load_urdf", "flash_read_point_cloud", "flash_points_set_file", "flash_points_set_file_async", "flash_num_devices",
+    "flash_skin_eval_static",
 ]
 
 _lib = None
@@ -69,6 +70,7 @@ def lib():
     L.flash_num_points.argtypes = [vp]; L.flash_num_points.restype = C.c_int64
     L.flash_cost_grad.argtypes = [vp, c_double_p, C.c_int32, C.c_double, c_double_p, c_double_p, c_int32_p]
     L.flash_skin_eval.argtypes = [vp, c_double_p, c_double_p, C.c_int64, c_double_p, c_int32_p]
+    L.flash_skin_eval_static.argtypes = [vp, vp, vp, C.c_int64, vp, vp]   # host or device addresses
     L.flash_raycast.argtypes = [vp, c_double_p, c_double_p, C.c_int64, c_double_p, c_double_p, c_double_p, C.POINTER(C.c_int64)]
     L.flash_kinect_rays.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_double, c_double_p]
     L.flash_estimate_state.argtypes = [vp, c_double_p, C.c_int32, C.POINTER(SolverParams), c_double_p, c_double_p, c_int32_p]

@@ -136,6 +136,9 @@ int main(int argc, char** argv) {
   { /* skin_eval: beanbag known answer (test/runtests.jl:17: skin(100,0,0) ~ 99 within 2 %) with the bag at the origin */
     double xb[14] = {1, 0, 0, 0, 500, 500, 500, 1, 0, 0, 0, 0, 0, 0}, q[3] = {100, 0, 0}, dist = 0; int32_t a = -1;
     CHECK(flash_skin_eval(ctx, xb, q, 1, &dist, &a) == FLASH_OK && fabs(dist - 99.0) < 0.02 * 99.0 && a == 1, "flash_skin_eval: beanbag skin(100,0,0) = %.4f (reference test: 99 +- 2 %%)", dist);
+    double d2 = 0; int32_t a2 = -1;
+    CHECK(flash_skin_eval_static(ctx, xb, q, 1, &d2, &a2) == FLASH_OK && d2 == dist && a2 == a, "flash_skin_eval_static (no allocation): the same value, %.4f", d2);
+    CHECK(flash_skin_eval_static(ctx, xb, q, FLASH_STATIC_MAX_QUERY + 1, &d2, &a2) == FLASH_ERR_TOO_LARGE && strstr(flash_last_error(ctx), "FLASH_STATIC_MAX_QUERY"), "flash_skin_eval_static: beyond its maximum -> FLASH_ERR_TOO_LARGE");
   }
   { /* float, file, async + swap entry points give the same cost (to rounding: the default mode sums in a different order every run) */
     static float cf[N][3];
