@@ -378,41 +378,13 @@ __global__ void __launch_bounds__(GBLOCK, 4) group_kernel(const GroupParams p) {
 #ifndef FLASH_MINB
 #define FLASH_MINB 2
 #endif
-constexpr size_t COST_STATIC_SMEM = 64;   // static __shared__ of cost_kernel (the group hand-out counter)
-// DET: deterministic mode as a template parameter -- as a run-time branch on p.part it cost the default kernel 6 % (the
-// initial `g = warp` keeps one more value live across the prologue: 104 B of spills at the 64-register cap).
-template <bool GRAD, bool ARGMIN, bool DIST, bool DET = false>
-__global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int c = blockIdx.x;
-  long long range0 = 0, range1 = p.n_pts;
-  if (p.frames) { const int f = c / p.cfg_per_frame; range0 = p.frames[f]; range1 = range0 + p.frames[FRAMES_MAX + 1 + f]; }
-  if (range0 + (long long)blockIdx.y * p.pts_per_block >= range1) return;   // (block-uniform) a frame shorter than the longest one
-  // every block re-derives the layout from the same numbers the host used
-  const HotModel* hot_g = p.hot;
-  const int tab_len = hot_g->tab_len, acc_len = hot_g->acc_len, n_convex = hot_g->n_convex;
-  const SmemLayout L = smem_layout(tab_len, acc_len, hot_g->tabf_len, GRAD && hot_g->n_skins > 0, CWARPS);
-  stage_block(smem, L, hot_g, p.tab + (size_t)c * tab_len, tab_len, CBLOCK);
-  double* acc_w = reinterpret_cast<double*>(smem + L.off_acc) + (size_t)warp * acc_len;
-  __shared__ int s_next;
-  if (tid == 0) s_next = 0;
-  if (!DIST) for (int i = lane; i < acc_len; i += 32) acc_w[i] = 0.0;
-  __syncthreads();
-  const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
-  GeoView G;
-  G.f4 = p.geo_f4;
-  G.u32 = p.geo_u32;
-  G.grid_pool = p.grid_pool;
-  const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
-  const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
-  double* queue = reinterpret_cast<double*>(smem + L.off_queue) + (size_t)warp * 32 * QENT;
-  int* qslot = reinterpret_cast<int*>(smem + L.off_qslot) + warp * 32;
-
+// The point loop of cost_kernel (and of track_kernel): the warps of one block work through the groups of the tile
+// [tile0, tile1) of configuration c and add into their own accumulators acc_w; returns this lane's part of the cost.
+template <bool GRAD, bool ARGMIN, bool DIST, bool DET, int GRAB = FLASH_GRAB>
+__device__ __forceinline__ double cost_groups(const CostParams& p, const HotModel& H, const GeoView& G, const double* tab, const float* tabf, double* acc_w,
+                                              double* queue, int* qslot, int* s_next, int c, int n_convex, long long range0, long long tile0, long long tile1,
+                                              int lane, int warp) {
   const unsigned all_convex = n_convex >= 32 ? 0xffffffffu : ((1u << n_convex) - 1u);
-  const long long tile0 = range0 + (long long)blockIdx.y * p.pts_per_block;
-  long long tile1 = tile0 + p.pts_per_block;
-  if (tile1 > range1) tile1 = range1;
   double cost_local = 0.0;
 
   // Groups of 32 points are handed to the block's warps dynamically (FLASH_GRAB consecutive groups per shared-memory
@@ -426,18 +398,18 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   const uint4* rec = grp_pre ? p.rec + (size_t)c * p.rec_stride + ((tile0 - range0) >> 5) : nullptr;
   // chunks of FLASH_GRAB (a power of two) groups start at multiples of FLASH_GRAB: the end of a chunk is a bit test
   int g = 0;
-  if (DET) g = warp * FLASH_GRAB;
+  if (DET) g = warp * GRAB;
   else {
-    if (lane == 0) g = atomicAdd(&s_next, FLASH_GRAB);
+    if (lane == 0) g = atomicAdd(s_next, GRAB);
     g = __shfl_sync(0xffffffffu, g, 0);
   }
   while (g < ngroups) {
     const long long wbase = tile0 + (long long)g * 32;
     const int gcur = g;
-    if (((++g) & (FLASH_GRAB - 1)) == 0) {
-      if (DET) g += (CWARPS - 1) * FLASH_GRAB;
+    if (((++g) & (GRAB - 1)) == 0) {
+      if (DET) g += (CWARPS - 1) * GRAB;
       else {
-        if (lane == 0) g = atomicAdd(&s_next, FLASH_GRAB);
+        if (lane == 0) g = atomicAdd(s_next, GRAB);
         g = __shfl_sync(0xffffffffu, g, 0);
       }
     }
@@ -564,6 +536,44 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
       }
     }
   }
+  return cost_local;
+}
+
+constexpr size_t COST_STATIC_SMEM = 64;   // static __shared__ of cost_kernel (the group hand-out counter)
+// DET: deterministic mode as a template parameter -- as a run-time branch on p.part it cost the default kernel 6 % (the
+// initial `g = warp` keeps one more value live across the prologue: 104 B of spills at the 64-register cap).
+template <bool GRAD, bool ARGMIN, bool DIST, bool DET = false>
+__global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostParams p) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int c = blockIdx.x;
+  long long range0 = 0, range1 = p.n_pts;
+  if (p.frames) { const int f = c / p.cfg_per_frame; range0 = p.frames[f]; range1 = range0 + p.frames[FRAMES_MAX + 1 + f]; }
+  if (range0 + (long long)blockIdx.y * p.pts_per_block >= range1) return;   // (block-uniform) a frame shorter than the longest one
+  // every block re-derives the layout from the same numbers the host used
+  const HotModel* hot_g = p.hot;
+  const int tab_len = hot_g->tab_len, acc_len = hot_g->acc_len, n_convex = hot_g->n_convex;
+  const SmemLayout L = smem_layout(tab_len, acc_len, hot_g->tabf_len, GRAD && hot_g->n_skins > 0, CWARPS);
+  stage_block(smem, L, hot_g, p.tab + (size_t)c * tab_len, tab_len, CBLOCK);
+  double* acc_w = reinterpret_cast<double*>(smem + L.off_acc) + (size_t)warp * acc_len;
+  __shared__ int s_next;
+  if (tid == 0) s_next = 0;
+  if (!DIST) for (int i = lane; i < acc_len; i += 32) acc_w[i] = 0.0;
+  __syncthreads();
+  const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
+  GeoView G;
+  G.f4 = p.geo_f4;
+  G.u32 = p.geo_u32;
+  G.grid_pool = p.grid_pool;
+  const double* tab = reinterpret_cast<const double*>(smem + L.off_tab);
+  const float* tabf = reinterpret_cast<const float*>(smem + L.off_tabf);
+  double* queue = reinterpret_cast<double*>(smem + L.off_queue) + (size_t)warp * 32 * QENT;
+  int* qslot = reinterpret_cast<int*>(smem + L.off_qslot) + warp * 32;
+
+  const long long tile0 = range0 + (long long)blockIdx.y * p.pts_per_block;
+  long long tile1 = tile0 + p.pts_per_block;
+  if (tile1 > range1) tile1 = range1;
+  double cost_local = cost_groups<GRAD, ARGMIN, DIST, DET>(p, H, G, tab, tabf, acc_w, queue, qslot, &s_next, c, n_convex, range0, tile0, tile1, lane, warp);
   if (DIST) return;
   cost_local = warp_sum(cost_local);
   if (lane == 0) acc_w[0] += cost_local;
@@ -919,6 +929,37 @@ __global__ void __launch_bounds__(BLOCK) compact_hits_kernel(const double* __res
   }
 }
 
+// One NaiveSolver update on one warp (flash_estimate_state in flashsdf.h): step = -rate * (g / N) ./ divisors, its norm
+// clamped to max_step; returns true (and leaves x alone) when |g / N| < tol.
+__device__ __forceinline__ bool naive_step_warp(int nx, const double* g, double* x, double inv_n, double rate, double max_step, double tol,
+                                                const double* divisors, int lane) {
+  double gn = 0, sn = 0;
+  double stv[8];                       // this lane's step components (nx <= 256): divided once, applied below
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const int k = lane + 32 * q;
+    stv[q] = 0.0;
+    if (k < nx) {
+      const double gk = g[k] * inv_n;
+      const double st = -rate * gk / (divisors ? divisors[k] : 1.0);
+      stv[q] = st;
+      gn += gk * gk; sn += st * st;
+    }
+  }
+  for (int k = lane + 256; k < nx; k += 32) {   // states beyond the register window (up to 64 + 3 * 4 * 64)
+    const double gk = g[k] * inv_n;
+    const double st = -rate * gk / (divisors ? divisors[k] : 1.0);
+    gn += gk * gk; sn += st * st;
+  }
+  gn = warp_sum(gn); sn = sqrt(warp_sum(sn));
+  if (tol > 0 && sqrt(gn) < tol) return true;
+  const double sc = sn > max_step ? max_step / sn : 1.0;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) { const int k = lane + 32 * q; if (k < nx) x[k] += sc * stv[q]; }
+  for (int k = lane + 256; k < nx; k += 32) x[k] += sc * (-rate * g[k] * inv_n / (divisors ? divisors[k] : 1.0));
+  return false;
+}
+
 // ------------------------------------------------------------------------------------------------
 // Tracking iteration tail in ONE launch, one block per config: epilogue (cost + gradient of the pass the cost
 // kernel just finished; warp 0) -> NaiveSolver step (flash_estimate_state in flashsdf.h; warp 0) -> prepare of
@@ -950,34 +991,8 @@ __global__ void __launch_bounds__(PREP_T) iterate_kernel(const ModelC* Mp, doubl
     t1 = clock64();
 #endif
     if (!done[c]) {
-      const int nx = M.nx;
-      double gn = 0, sn = 0;
-      double stv[8];                       // this lane's step components (nx <= 256): divided once, applied below
-#pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        const int k = lane + 32 * q;
-        stv[q] = 0.0;
-        if (k < nx) {
-          const double gk = g[k] * inv_n;
-          const double st = -rate * gk / (divisors ? divisors[k] : 1.0);
-          stv[q] = st;
-          gn += gk * gk; sn += st * st;
-        }
-      }
-      for (int k = lane + 256; k < nx; k += 32) {   // states beyond the register window (up to 64 + 3 * 4 * 64)
-        const double gk = g[k] * inv_n;
-        const double st = -rate * gk / (divisors ? divisors[k] : 1.0);
-        gn += gk * gk; sn += st * st;
-      }
-      gn = warp_sum(gn); sn = sqrt(warp_sum(sn));
-      if (tol > 0 && sqrt(gn) < tol) { if (lane == 0) done[c] = 1; }
-      else {
-        const double sc = sn > max_step ? max_step / sn : 1.0;
-#pragma unroll
-        for (int q = 0; q < 8; ++q) { const int k = lane + 32 * q; if (k < nx) x[k] += sc * stv[q]; }
-        for (int k = lane + 256; k < nx; k += 32) x[k] += sc * (-rate * g[k] * inv_n / (divisors ? divisors[k] : 1.0));
-        if (lane == 0) iters[c] += 1;
-      }
+      if (naive_step_warp(M.nx, g, x, inv_n, rate, max_step, tol, divisors, lane)) { if (lane == 0) done[c] = 1; }
+      else if (lane == 0) iters[c] += 1;
     }
   }
 #ifdef FLASH_ITER_TIMING
@@ -988,6 +1003,193 @@ __global__ void __launch_bounds__(PREP_T) iterate_kernel(const ModelC* Mp, doubl
 #ifdef FLASH_ITER_TIMING
   if (tid == 0 && c == 0 && iters[0] >= 20 && iters[0] < 23) printf("iterate_kernel cycles: epilogue %lld step %lld prepare %lld\n", t1 - t0, t2 - t1, clock64() - t2);
 #endif
+}
+
+// ------------------------------------------------------------------------------------------------
+// The whole solver loop of one frame in ONE launch (flash_estimate_state: one configuration, a model whose point loop
+// needs no group records, one device).  A persistent grid of at most one block per SM, all co-resident (cooperative
+// launch).  Per iteration:
+//   cost pass   every block runs cost_groups over its own tile out of tables in ITS shared memory and adds the sums of its
+//               warps to the pass's totals (fp64 atomics; deterministic mode: stores them per block)
+//   barrier     one grid-wide barrier (arrive counter + spin; bounded, so a lost block ends the call instead of hanging)
+//   tail        EVERY block reads the totals (deterministic mode: adds the blocks' sums in a fixed order), then runs the epilogue, the NaiveSolver
+//               step and the prepare of the next pass redundantly on its own copy of the state: the other SMs would only
+//               wait, and what the next pass reads (centres, weights, inverse) is already where it is needed.
+// The two-kernel loop it replaces (cost_kernel, iterate_kernel per iteration) spent ~9 us per iteration on launches and on
+// moving tables, inverse and sums through global memory.  Same arithmetic in the same order per block
+// as the two-kernel loop in deterministic mode, except that the sums over the points are grouped by tile.
+struct TrackParams {
+  CostParams cp;            // hot, geometry, pts, n_pts, pts_per_block, use_grid (tab / acc / rec / part unused)
+  const ModelC* model;
+  double* X;                // [nx]  in: start, out: estimate
+  double* part;             // deterministic: [2][acc_len][gridDim.x] block sums; else [3][acc_len] totals, zero at launch
+  unsigned* bar;            // grid barrier counter, zero at launch
+  double* cost;             // [1] cost at the final state (want_cost)
+  int* iters; int* done; int* status;
+  const double* divisors;   // may be null
+  double w_def, inv_n, rate, max_step, tol;
+  int iteration_limit, want_cost;
+};
+struct TrackLayout { SmemLayout L; size_t off_x, off_aux, off_grad, off_sum, off_scr, total; };
+__host__ __device__ inline TrackLayout track_layout(const ModelC& M) {
+  TrackLayout T;
+  T.L = smem_layout(M.tab_len, M.acc_len, M.tabf_len, M.n_skins > 0, CWARPS);
+  size_t o = T.L.total;
+  T.off_x = o; o = align16(o + sizeof(double) * (size_t)M.nx);
+  T.off_aux = o; o = align16(o + sizeof(double) * (size_t)(M.aux_len > 0 ? M.aux_len : 1));
+  T.off_grad = o; o = align16(o + sizeof(double) * (size_t)M.nx);
+  T.off_sum = o; o = align16(o + sizeof(double) * (size_t)M.acc_len);
+  const size_t a = prepare_smem_doubles(M), b = epilogue_smem_doubles(M);
+  T.off_scr = o; o = align16(o + sizeof(double) * (a > b ? a : b));
+  T.total = o;
+  return T;
+}
+constexpr unsigned TRACK_SPIN_LIMIT = 1u << 22;   // seconds of polling: far beyond any pass; a grid that is not co-resident gives up
+__device__ __forceinline__ bool track_grid_barrier(unsigned* bar, unsigned target, int* s_lost) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(bar, 1u);
+    unsigned spins = 0;
+    while (*(volatile unsigned*)bar < target) { if (++spins > TRACK_SPIN_LIMIT) { *s_lost = 1; break; } __nanosleep(32); }
+    __threadfence();
+  }
+  __syncthreads();
+  return *s_lost == 0;
+}
+template <bool DET>
+__global__ void __launch_bounds__(CBLOCK, 1) track_kernel(const TrackParams t) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const ModelC& M = *t.model;
+  const TrackLayout T = track_layout(M);
+  const SmemLayout& L = T.L;
+  const int acc_len = M.acc_len, nx = M.nx, nblk = gridDim.x;
+  __shared__ int s_next, s_lost, s_done;
+  double* s_x = reinterpret_cast<double*>(smem + T.off_x);
+  double* s_aux = reinterpret_cast<double*>(smem + T.off_aux);
+  double* s_grad = reinterpret_cast<double*>(smem + T.off_grad);
+  double* s_sum = reinterpret_cast<double*>(smem + T.off_sum);
+  double* s_scr = reinterpret_cast<double*>(smem + T.off_scr);
+  double* tab = reinterpret_cast<double*>(smem + L.off_tab);
+  float* tabf = reinterpret_cast<float*>(smem + L.off_tabf);
+  double* acc_all = reinterpret_cast<double*>(smem + L.off_acc);
+  double* acc_w = acc_all + (size_t)warp * acc_len;
+  double* queue = reinterpret_cast<double*>(smem + L.off_queue) + (size_t)warp * 32 * QENT;
+  int* qslot = reinterpret_cast<int*>(smem + L.off_qslot) + warp * 32;
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(t.cp.hot);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(smem + L.off_hot);
+    for (int i = tid; i < (int)(sizeof(HotModel) / 4); i += CBLOCK) dst[i] = src[i];
+    for (int i = tid; i < nx; i += CBLOCK) s_x[i] = t.X[i];
+    if (tid == 0) { s_lost = 0; s_done = 0; }
+  }
+  __syncthreads();
+  const HotModel& H = *reinterpret_cast<const HotModel*>(smem + L.off_hot);
+  GeoView G;
+  G.f4 = t.cp.geo_f4; G.u32 = t.cp.geo_u32; G.grid_pool = t.cp.grid_pool;
+  const long long n = t.cp.n_pts;
+  const long long tile0 = (long long)blockIdx.x * t.cp.pts_per_block;
+  long long tile1 = tile0 + t.cp.pts_per_block;
+  if (tile1 > n) tile1 = n;
+  int iters = 0;
+  unsigned passes = 0;
+  const int last = t.iteration_limit + (t.want_cost ? 1 : 0);   // the extra pass is the cost at the final state
+#ifdef FLASH_TRACK_TIMING
+  long long tk[8];
+#define FLASH_TK(i) tk[i] = clock64()
+#else
+#define FLASH_TK(i) ((void)0)
+#endif
+  for (int it = 0; it < last; ++it) {
+    const bool final_pass = it == t.iteration_limit;
+    FLASH_TK(0);
+    // ---- tables of this pass from this block's copy of the state
+    prepare_block(M, s_x, tab, s_aux, nullptr, t.status, s_scr, tid, CBLOCK);
+    __syncthreads();
+    tabf_fill(H, tab, tabf, tid, CBLOCK);
+    for (int i = tid; i < acc_len * CWARPS; i += CBLOCK) acc_all[i] = 0.0;
+    if (tid == 0) s_next = 0;
+    __syncthreads();
+    FLASH_TK(1);
+    // ---- cost pass over this block's tile
+    double cost_local = 0.0;
+    if (tile0 < tile1) cost_local = cost_groups<true, false, false, DET, 1>(t.cp, H, G, tab, tabf, acc_w, queue, qslot, &s_next, 0, H.n_convex, 0ll, tile0, tile1, lane, warp);
+    cost_local = warp_sum(cost_local);
+    if (lane == 0) acc_w[0] += cost_local;
+#ifdef FLASH_TRACK_TIMING
+    __shared__ long long s_wclk[CWARPS];
+    if (lane == 0) s_wclk[warp] = clock64();
+#endif
+    __syncthreads();
+    FLASH_TK(2);
+#ifdef FLASH_TRACK_TIMING
+    if (tid == 0) { long long mx = 0; for (int w = 0; w < CWARPS; ++w) mx = s_wclk[w] > mx ? s_wclk[w] : mx; tk[7] = mx - tk[1]; }
+#endif
+    if (DET) {      // this block's sums, layout [pass & 1][accumulator][block]: the gather below reads whole rows
+      double* mine = t.part + (size_t)(passes & 1u) * nblk * acc_len + blockIdx.x;
+      for (int l = tid; l < acc_len; l += CBLOCK) {
+        double s = 0;
+#pragma unroll
+        for (int w = 0; w < CWARPS; ++w) s += acc_all[(size_t)w * acc_len + l];
+        __stcg(mine + (size_t)l * nblk, s);
+      }
+    } else {        // fp64 atomics into one of three rotating totals (zeroed two barriers ahead of their next use)
+      double* tot = t.part + (size_t)(passes % 3u) * acc_len;
+      for (int l = tid; l < acc_len; l += CBLOCK) {
+        double s = 0;
+#pragma unroll
+        for (int w = 0; w < CWARPS; ++w) s += acc_all[(size_t)w * acc_len + l];
+        if (s != 0.0) atomicAdd(tot + l, s);
+      }
+    }
+    ++passes;
+    if (!track_grid_barrier(t.bar, passes * (unsigned)nblk, &s_lost)) break;
+    FLASH_TK(3);
+    if (DET) {      // sums over the blocks in a fixed order: warp w takes accumulators w, w + 16, ..., four at a time
+      const double* all = t.part + (size_t)((passes - 1u) & 1u) * nblk * acc_len;
+      for (int l0 = 0; l0 < acc_len; l0 += 4 * CWARPS) {
+        double s[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int l = l0 + warp + k * CWARPS;
+          if (l < acc_len) for (int b = lane; b < nblk; b += 32) s[k] += __ldcg(all + (size_t)l * nblk + b);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int l = l0 + warp + k * CWARPS;
+          const double v = warp_sum(s[k]);
+          if (l < acc_len && lane == 0) s_sum[l] = v;
+        }
+      }
+    } else {
+      const double* tot = t.part + (size_t)((passes - 1u) % 3u) * acc_len;
+      for (int l = tid; l < acc_len; l += CBLOCK) s_sum[l] = __ldcg(tot + l);
+      if (blockIdx.x == 0) { double* z = t.part + (size_t)((passes + 1u) % 3u) * acc_len; for (int l = tid; l < acc_len; l += CBLOCK) z[l] = 0.0; }
+    }
+    __syncthreads();
+    FLASH_TK(4);
+    // ---- epilogue and solver step on warp 0
+    if (tid < 32) {
+      double cst = 0.0;
+      epilogue_warp(M, s_x, tab, s_aux, s_sum, t.w_def, &cst, final_pass ? nullptr : s_grad, s_scr, lane, false);
+      __syncwarp();
+      if (final_pass) { if (blockIdx.x == 0 && lane == 0) t.cost[0] = cst; }
+      else if (naive_step_warp(nx, s_grad, s_x, t.inv_n, t.rate, t.max_step, t.tol, t.divisors, lane)) {   // converged: x stays, and cst is the cost there
+        if (lane == 0) { s_done = 1; if (blockIdx.x == 0 && t.want_cost) t.cost[0] = cst; }
+      } else ++iters;
+    }
+    __syncthreads();
+#ifdef FLASH_TRACK_TIMING
+    if (tid == 0 && it == 20)
+      printf("track_kernel block %d cycles: prepare %lld cost %lld (slowest warp %lld) sums+barrier %lld gather %lld epilogue+step %lld\n", (int)blockIdx.x, tk[1] - tk[0], tk[2] - tk[1], tk[7], tk[3] - tk[2], tk[4] - tk[3], clock64() - tk[4]);
+#endif
+    if (final_pass || s_done) break;
+  }
+  if (blockIdx.x == 0) {
+    for (int i = tid; i < nx; i += CBLOCK) t.X[i] = s_x[i];
+    if (tid == 0) { t.iters[0] += iters; t.done[0] = s_done; if (s_lost) atomicExch(t.status, 2); }
+  } else if (tid == 0 && s_lost) atomicExch(t.status, 2);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -98,6 +98,7 @@ struct flash_ctx {
   int32_t* d_argmin = nullptr; size_t cap_argmin = 0;
   uint4* d_rec = nullptr; size_t cap_rec = 0;   // group records of group_kernel, [C][rec_stride]
   double* d_part = nullptr; size_t cap_part = 0; bool deterministic = false;   // per-tile partial sums [C][tiles][acc_len]
+  unsigned* d_bar = nullptr;   // grid barrier counter of track_kernel
   bool exact_groups = true;   // group_kernel evaluates the candidate hulls exactly at the ball centre (flash_dev.h group_prepass)
   // query scratch (skin_eval / raycast)
   double* d_qd = nullptr; size_t cap_qd = 0;
@@ -341,6 +342,7 @@ int check_status(flash_ctx* ctx) {
   CU(cudaStreamSynchronize(ctx->stream));
   if (st != 0) {
     CU(cudaMemsetAsync(ctx->d_status, 0, sizeof(int), ctx->stream));
+    if (st == 2) return fail(ctx, FLASH_ERR_CUDA, "track_kernel: the grid barrier timed out (blocks not co-resident); set FLASHSDF_NO_TRACK_KERNEL=1");
     return fail(ctx, FLASH_ERR_INVALID, "singular RBF system (coincident skin control points)");
   }
   return 0;
@@ -649,7 +651,7 @@ void flash_destroy(flash_ctx* ctx) {
   if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
   void* frees[] = {ctx->d_model, ctx->d_hot, ctx->d_geo_f4, ctx->d_geo_u32, ctx->d_grid_pool, ctx->d_stage,
                    ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, ctx->d_cost, ctx->d_grad, ctx->d_div, ctx->d_status, ctx->d_done, ctx->d_iters,
-                   ctx->d_argmin, ctx->d_rec, ctx->d_part, ctx->d_qd, ctx->d_qi, ctx->d_keys[0], ctx->d_keys[1], ctx->d_idx[0], ctx->d_idx[1], ctx->d_table, ctx->d_sums, ctx->d_bounds};
+                   ctx->d_argmin, ctx->d_rec, ctx->d_part, ctx->d_bar, ctx->d_qd, ctx->d_qi, ctx->d_keys[0], ctx->d_keys[1], ctx->d_idx[0], ctx->d_idx[1], ctx->d_table, ctx->d_sums, ctx->d_bounds};
   for (void* p : frees) if (p) cudaFree(p);
   for (auto& P : ctx->ps) {
     if (P.d_pts && !P.external) cudaFree(P.d_pts);
@@ -1356,6 +1358,43 @@ static int es_begin(flash_ctx* ctx, const double* X, int32_t C, const double* di
   if (it_smem > 48 * 1024) CU(cudaFuncSetAttribute(iterate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)it_smem));
   return 0;
 }
+// The solver loop as ONE persistent kernel (track_kernel): one configuration, no communicator, and a model whose point
+// loop takes no group records (run_groups would be a no-op).  Anything else runs the two-kernel loop below.
+static bool track_kernel_applies(const flash_ctx* ctx, int C) {
+  static const bool off = [] { const char* e = getenv("FLASHSDF_NO_TRACK_KERNEL"); return e && e[0] == '1'; }();
+  const ModelC& M = ctx->hm.M;
+  const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
+  if (off || C != 1 || ctx->comm || P.n <= 0) return false;
+  if (P.grp_on && ctx->group_cull && M.n_convex >= 2) return false;
+  return track_layout(M).total + 64 <= (size_t)ctx->smem_optin;
+}
+static int run_track(flash_ctx* ctx, const flash_solver_params* sp, double n_total, bool have_div, bool want_cost) {
+  const ModelC& M = ctx->hm.M;
+  const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
+  long long nblk = std::min<long long>(ctx->sm_count, (P.n + 31) / 32);
+  long long ppb = (((P.n + nblk - 1) / nblk + 31) / 32) * 32;
+  nblk = (P.n + ppb - 1) / ppb;
+  int rc = ensure(ctx, ctx->d_part, ctx->cap_part, std::max<size_t>((size_t)2 * (size_t)nblk, 3) * (size_t)M.acc_len); if (rc) return rc;
+  if (!ctx->deterministic) CU(cudaMemsetAsync(ctx->d_part, 0, (size_t)3 * M.acc_len * sizeof(double), ctx->stream));
+  if (!ctx->d_bar) CU(cudaMalloc((void**)&ctx->d_bar, 64 * sizeof(unsigned)));
+  CU(cudaMemsetAsync(ctx->d_bar, 0, 64 * sizeof(unsigned), ctx->stream));
+  TrackParams t;
+  CostParams& p = t.cp;
+  p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
+  p.pts = P.d_pts; p.n_pts = P.n; p.tab = nullptr; p.acc = nullptr; p.argmin = nullptr; p.dist = nullptr; p.perm = nullptr; p.grp = nullptr;
+  p.rec = nullptr; p.rec_stride = 0; p.frames = nullptr; p.cfg_per_frame = 1; p.pts_per_block = (int)ppb; p.use_grid = ctx->use_grid ? 1 : 0; p.part = nullptr;
+  t.model = ctx->d_model; t.X = ctx->d_X; t.part = ctx->d_part; t.bar = ctx->d_bar; t.cost = ctx->d_cost; t.iters = ctx->d_iters; t.done = ctx->d_done; t.status = ctx->d_status;
+  t.divisors = have_div ? ctx->d_div : nullptr;
+  t.w_def = sp->deformation_cost_weight; t.inv_n = n_total > 0 ? 1.0 / n_total : 0.0; t.rate = sp->rate; t.max_step = sp->max_step; t.tol = sp->gradient_convergence_tolerance;
+  t.iteration_limit = sp->iteration_limit; t.want_cost = want_cost ? 1 : 0;
+  const size_t smem = track_layout(M).total;
+  const void* k = ctx->deterministic ? (const void*)track_kernel<true> : (const void*)track_kernel<false>;
+  if (smem > 48 * 1024) CU(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  void* args[] = {&t};
+  CU(cudaLaunchCooperativeKernel(k, dim3((unsigned)nblk), dim3(CBLOCK), args, smem, ctx->stream));
+  ctx->launches++; ctx->last.launches++;
+  return 0;
+}
 // The solver loop on every device of a multi-device parent: each device evaluates its shard, the peer reduction hands
 // all of them the same sums, and every device then takes the same NaiveSolver step on its own copy of the state.
 static int multi_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solver_params* sp, const double* divisors, double* cost_out, int32_t* iters_out) {
@@ -1418,13 +1457,17 @@ int flash_estimate_state(flash_ctx* ctx, double* X, int32_t C, const flash_solve
   cudaEvent_t e0 = ctx->ev[0], e1 = ctx->ev[4];
   if (prof) CU(cudaEventRecord(e0, ctx->stream));
   // per iteration: cost_kernel -> [allreduce] -> iterate_kernel (epilogue + NaiveSolver step + prepare of the next pass)
-  if ((rc = run_prepare(ctx, C, true))) { ctx->profiling = prof; return rc; }
-  for (int it = 0; it < sp->iteration_limit; ++it) {
-    if ((rc = run_cost(ctx, C, true, nullptr)) || (rc = run_allreduce(ctx, C))) { ctx->profiling = prof; return rc; }
-    if ((rc = run_iterate(ctx, C, sp, n_total, divisors != nullptr, it_smem))) { ctx->profiling = prof; return rc; }
-  }
-  if (cost_out) {   // cost at the final state: the last iterate_kernel already prepared it
-    if ((rc = run_cost(ctx, C, false, nullptr)) || (rc = run_allreduce(ctx, C)) || (rc = run_epilogue(ctx, C, sp->deformation_cost_weight, false))) { ctx->profiling = prof; return rc; }
+  if (track_kernel_applies(ctx, C)) {
+    if ((rc = run_track(ctx, sp, n_total, divisors != nullptr, cost_out != nullptr))) { ctx->profiling = prof; return rc; }
+  } else {
+    if ((rc = run_prepare(ctx, C, true))) { ctx->profiling = prof; return rc; }
+    for (int it = 0; it < sp->iteration_limit; ++it) {
+      if ((rc = run_cost(ctx, C, true, nullptr)) || (rc = run_allreduce(ctx, C))) { ctx->profiling = prof; return rc; }
+      if ((rc = run_iterate(ctx, C, sp, n_total, divisors != nullptr, it_smem))) { ctx->profiling = prof; return rc; }
+    }
+    if (cost_out) {   // cost at the final state: the last iterate_kernel already prepared it
+      if ((rc = run_cost(ctx, C, false, nullptr)) || (rc = run_allreduce(ctx, C)) || (rc = run_epilogue(ctx, C, sp->deformation_cost_weight, false))) { ctx->profiling = prof; return rc; }
+    }
   }
   if (prof) CU(cudaEventRecord(e1, ctx->stream));
   ctx->profiling = prof;
