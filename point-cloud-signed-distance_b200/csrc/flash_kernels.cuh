@@ -111,7 +111,7 @@ __host__ __device__ inline size_t prepare_smem_doubles(const ModelC& M) {
   size_t need = 8;
   for (int k = 0; k < M.n_skins; ++k) {
     const size_t m = (size_t)M.skin[k].M, n = (size_t)M.skin[k].npts;
-    const size_t v = m * m + 3 * n + 3 * m + 4;   // A, centres, pivots, pivot row, pivot column, 2 scratch
+    const size_t v = m * m + 3 * n + 3 * m + 4 + (m * m <= 1024 ? m * m : 0);   // A, centres, pivots, pivot row, pivot column, 2 scratch (+2 pad), second matrix of the fast path
     if (v > need) need = v;
   }
   const size_t fk = 25 * MAX_BODIES + 64 + (MAX_BODIES * sizeof(BodyC) + 7) / 8;   // FK staging (reused by the skins afterwards)
@@ -196,35 +196,43 @@ __device__ __forceinline__ void prepare_block(const ModelC& M, const double* x, 
     bool ok = true;
     if (Mm * Mm <= T) {
       // Fast path (K3: 17 x 17 <= 320 threads): thread e owns element (i0, j0) in a register, the matrix in shared
-      // memory is only the exchange medium.  Per pivot TWO barriers: every thread scans the pivot column itself
-      // (broadcast loads, no shuffle search, no broadcast phase), the row exchange is done by addressing (row bi
-      // "holds" old row kk) instead of a swap phase, and the reciprocal of every pivot candidate was computed by
-      // the thread that produced it during the previous update, so no division sits on the critical path.
+      // memory is only the exchange medium.  Per pivot ONE barrier: the matrix (and the reciprocals) alternate between
+      // two buffers, so a step reads the buffer the previous step wrote and writes the other one; every thread scans
+      // the pivot column itself (broadcast loads, no shuffle search, no broadcast phase), the row exchange is done by
+      // addressing (row bi "holds" old row kk) instead of a swap phase, and the reciprocal of every pivot candidate was
+      // computed by the thread that produced it during the previous update, so no division sits on the critical path.
       // Same operations on the same numbers as the generic path below except for the reciprocal (rcp_newton, ~1 ulp).
+      // (Tried: the whole inversion on ONE warp, a column per lane in registers, multipliers by shuffles, no barrier --
+      // 3x slower, 51 k cycles against 17 k: ~400 dependent instructions per pivot on a single warp issue at ~5 cycles each.
+      // Tried in track_kernel: Newton-Schulz refinement of the previous iteration's inverse with a residual certificate --
+      // never accepted on K3: one solver step moves the system further than |I - A X| < 1/4 allows.)
       const bool act = tid < Mm * Mm;
       const int i = i0, j = j0;
-      double* rcp = prow;                       // [Mm] reciprocals of the next pivot column (prow/pcol are unused here)
+      const double* cur = A; double* nxt = scr + 4;          // [Mm][Mm] each
+      const double* rcp = prow; double* rcn = pcol;          // [Mm] reciprocals of the next pivot column (prow/pcol are unused here)
       double a = act ? A[tid] : 0.0;
-      if (act && j == 0) rcp[i] = rcp_newton(a);
+      if (act && j == 0) prow[i] = rcp_newton(a);
       __syncthreads();
       for (int kk = 0; kk < Mm; ++kk) {
         double best = -1.0; int bi = kk;   // (comparing the bit patterns as 64-bit integers instead: 5 % slower end to end)
 #pragma unroll 4
-        for (int r = kk; r < Mm; ++r) { const double v = fabs(A[r * Mm + kk]); if (v > best) { best = v; bi = r; } }   // lowest row on ties
+        for (int r = kk; r < Mm; ++r) { const double v = fabs(cur[r * Mm + kk]); if (v > best) { best = v; bi = r; } }   // lowest row on ties
         if (!(best > 0.0)) ok = false;
         const double inv = rcp[bi];
         if (tid == 0) piv[kk] = (double)bi;
-        double nv = 0.0;
         if (act) {
-          const double pr = A[bi * Mm + j];
-          const double f = (i == bi) ? A[kk * Mm + kk] : A[i * Mm + kk];
-          const double own = (i == bi) ? A[kk * Mm + j] : a;
+          const double pr = cur[bi * Mm + j];
+          const double f = (i == bi) ? cur[kk * Mm + kk] : cur[i * Mm + kk];
+          const double own = (i == bi) ? cur[kk * Mm + j] : a;
+          double nv;
           if (i == kk) nv = (j == kk) ? inv : pr * inv;
           else nv = (j == kk) ? -f * inv : fma(-f, pr * inv, own);
+          nxt[tid] = nv; a = nv;
+          if (j == kk + 1) rcn[i] = rcp_newton(nv);
         }
-        __syncthreads();                         // every read of the old matrix is done
-        if (act) { A[tid] = nv; a = nv; if (j == kk + 1) rcp[i] = rcp_newton(nv); }
-        __syncthreads();
+        __syncthreads();                         // the new matrix is complete; nobody reads the old one any more
+        { const double* t0 = cur; cur = nxt; nxt = const_cast<double*>(t0); }
+        { const double* t1 = rcp; rcp = rcn; rcn = const_cast<double*>(t1); }
       }
       FLASH_TS(4);
       // undo the row exchanges on the columns: the exchanges (kk, piv[kk]), kk = Mm-1 .. 0, move this thread's
@@ -380,7 +388,7 @@ __global__ void __launch_bounds__(GBLOCK, 4) group_kernel(const GroupParams p) {
 #endif
 // The point loop of cost_kernel (and of track_kernel): the warps of one block work through the groups of the tile
 // [tile0, tile1) of configuration c and add into their own accumulators acc_w; returns this lane's part of the cost.
-template <bool GRAD, bool ARGMIN, bool DIST, bool DET, int GRAB = FLASH_GRAB>
+template <bool GRAD, bool ARGMIN, bool DIST, bool DET, int GRAB = FLASH_GRAB, bool ILP2 = false>
 __device__ __forceinline__ double cost_groups(const CostParams& p, const HotModel& H, const GeoView& G, const double* tab, const float* tabf, double* acc_w,
                                               double* queue, int* qslot, int* s_next, int c, int n_convex, long long range0, long long tile0, long long tile1,
                                               int lane, int warp) {
@@ -513,12 +521,28 @@ __device__ __forceinline__ double cost_groups(const CostParams& p, const HotMode
             const int ci = cb + ci0;
             double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
             if (ci <= n) {
-              for (int qe = sub; qe < cnt; qe += E) {
-                if (qslot[qe] != k) continue;
-                const double* q = queue + qe * QENT;
-                double o[4];
-                skin_adjoint_term(cc, cc + 3 * n, n, H.normalize != 0, ci, q[0], q[1], q[2], q[3], q[4], d3(q[5], q[6], q[7]), o);
-                a0 += o[0]; a1 += o[1]; a2 += o[2]; a3 += o[3];
+              if (ILP2) {
+                // two queue entries per trip in straight-line code (track_kernel: a handful of warps per SM, nothing else
+                // to hide the fp64 latency behind); same terms added in the same order
+                for (int qe = sub; qe < cnt; qe += 2 * E) {
+                  const int qb = qe + E < cnt ? qe + E : qe;
+                  const bool u0 = qslot[qe] == k, u1 = qe + E < cnt && qslot[qb] == k;
+                  const double* q = queue + qe * QENT;
+                  const double* r = queue + qb * QENT;
+                  double o[4], o2[4];
+                  skin_adjoint_term(cc, cc + 3 * n, n, H.normalize != 0, ci, q[0], q[1], q[2], q[3], q[4], d3(q[5], q[6], q[7]), o);
+                  skin_adjoint_term(cc, cc + 3 * n, n, H.normalize != 0, ci, r[0], r[1], r[2], r[3], r[4], d3(r[5], r[6], r[7]), o2);
+                  if (u0) { a0 += o[0]; a1 += o[1]; a2 += o[2]; a3 += o[3]; }
+                  if (u1) { a0 += o2[0]; a1 += o2[1]; a2 += o2[2]; a3 += o2[3]; }
+                }
+              } else {
+                for (int qe = sub; qe < cnt; qe += E) {
+                  if (qslot[qe] != k) continue;
+                  const double* q = queue + qe * QENT;
+                  double o[4];
+                  skin_adjoint_term(cc, cc + 3 * n, n, H.normalize != 0, ci, q[0], q[1], q[2], q[3], q[4], d3(q[5], q[6], q[7]), o);
+                  a0 += o[0]; a1 += o[1]; a2 += o[2]; a3 += o[3];
+                }
               }
             }
             for (int o = G; o < 32; o <<= 1) {
@@ -632,7 +656,7 @@ __device__ __forceinline__ void epilogue_preload(const ModelC& M, const double* 
   for (int e = tid; e < 4 * n + 4; e += T) cc[e] = ct[e];
 }
 __device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, const double* tab, const double* aux, const double* acc, double w_def,
-                                              double* cost_c, double* grad, double* sm, int lane, bool preloaded = false) {
+                                              double* cost_c, double* grad, double* sm, int lane, bool preloaded = false, bool direct = false) {
   double* F = sm;                                // [nb][3]
   double* Mo = F + 3 * MAX_BODIES;               // [nb][3]
   double* sk = Mo + 3 * MAX_BODIES;              // per-skin scratch
@@ -662,18 +686,19 @@ __device__ __forceinline__ void epilogue_warp(const ModelC& M, const double* x, 
     for (int k = 0; k < M.n_skins; ++k) {
       const SkinC& K = M.skin[k];
       const int n = K.npts, Mm = K.M;
-      double* Ainv = sk;               // [Mm][Mm]
-      double* cc = Ainv + Mm * Mm;     // [n][3]
-      double* w = cc + 3 * n;          // [n + 4]
-      double* lam = w + n + 4;         // [Mm]
+      // direct: tab and aux are already in shared memory (track_kernel) -- no copy, only lam needs scratch
+      const double* Ainv = direct ? aux + aux_skin0(M) + K.aux_off : sk;   // [Mm][Mm]
+      const double* cc = direct ? tab + K.tab_off : sk + Mm * Mm;          // [n][3]
+      const double* w = cc + 3 * n;                                         // [n + 4]
+      double* lam = direct ? sk : sk + Mm * Mm + 4 * n + 4;                 // [Mm]
       const double* gY = acc + K.acc_off;
       const double* gC = gY + n + 4;
       __syncwarp();
-      if (!(preloaded && k == 0)) {
+      if (!direct && !(preloaded && k == 0)) {
         const double* src = aux + aux_skin0(M) + K.aux_off;
-        for (int e = lane; e < Mm * Mm; e += 32) Ainv[e] = src[e];
+        for (int e = lane; e < Mm * Mm; e += 32) sk[e] = src[e];
         const double* ct = tab + K.tab_off;
-        for (int e = lane; e < 4 * n + 4; e += 32) cc[e] = ct[e];   // centres then (w, a0, a): contiguous in tab
+        for (int e = lane; e < 4 * n + 4; e += 32) sk[Mm * Mm + e] = ct[e];   // centres then (w, a0, a): contiguous in tab
       }
       __syncwarp();
       FLASH_ES(1);
@@ -1057,7 +1082,10 @@ __device__ __forceinline__ bool track_grid_barrier(unsigned* bar, unsigned targe
   __syncthreads();
   return *s_lost == 0;
 }
-template <bool DET>
+// DET: deterministic mode (static schedule, block sums gathered in a fixed order).  STATIC: static schedule only -- chosen
+// when a block has at most one group per warp: warps 0 .. g-1 then sit evenly on the four schedulers (9 groups: 3+2+2+2),
+// while the first g warps to win the hand-out race may not (the pass is bound by the fp64 pipe of the fullest scheduler).
+template <bool DET, bool STATIC>
 __global__ void __launch_bounds__(CBLOCK, 1) track_kernel(const TrackParams t) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1114,7 +1142,7 @@ __global__ void __launch_bounds__(CBLOCK, 1) track_kernel(const TrackParams t) {
     FLASH_TK(1);
     // ---- cost pass over this block's tile
     double cost_local = 0.0;
-    if (tile0 < tile1) cost_local = cost_groups<true, false, false, DET, 1>(t.cp, H, G, tab, tabf, acc_w, queue, qslot, &s_next, 0, H.n_convex, 0ll, tile0, tile1, lane, warp);
+    if (tile0 < tile1) cost_local = cost_groups<true, false, false, DET || STATIC, 1, true>(t.cp, H, G, tab, tabf, acc_w, queue, qslot, &s_next, 0, H.n_convex, 0ll, tile0, tile1, lane, warp);
     cost_local = warp_sum(cost_local);
     if (lane == 0) acc_w[0] += cost_local;
 #ifdef FLASH_TRACK_TIMING
@@ -1172,7 +1200,7 @@ __global__ void __launch_bounds__(CBLOCK, 1) track_kernel(const TrackParams t) {
     // ---- epilogue and solver step on warp 0
     if (tid < 32) {
       double cst = 0.0;
-      epilogue_warp(M, s_x, tab, s_aux, s_sum, t.w_def, &cst, final_pass ? nullptr : s_grad, s_scr, lane, false);
+      epilogue_warp(M, s_x, tab, s_aux, s_sum, t.w_def, &cst, final_pass ? nullptr : s_grad, s_scr, lane, false, true);
       __syncwarp();
       if (final_pass) { if (blockIdx.x == 0 && lane == 0) t.cost[0] = cst; }
       else if (naive_step_warp(nx, s_grad, s_x, t.inv_n, t.rate, t.max_step, t.tol, t.divisors, lane)) {   // converged: x stays, and cst is the cost there

@@ -1388,7 +1388,7 @@ static int run_track(flash_ctx* ctx, const flash_solver_params* sp, double n_tot
   t.w_def = sp->deformation_cost_weight; t.inv_n = n_total > 0 ? 1.0 / n_total : 0.0; t.rate = sp->rate; t.max_step = sp->max_step; t.tol = sp->gradient_convergence_tolerance;
   t.iteration_limit = sp->iteration_limit; t.want_cost = want_cost ? 1 : 0;
   const size_t smem = track_layout(M).total;
-  const void* k = ctx->deterministic ? (const void*)track_kernel<true> : (const void*)track_kernel<false>;
+  const void* k = ctx->deterministic ? (const void*)track_kernel<true, true> : (ppb <= 32 * CWARPS ? (const void*)track_kernel<false, true> : (const void*)track_kernel<false, false>);
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   void* args[] = {&t};
   CU(cudaLaunchCooperativeKernel(k, dim3((unsigned)nblk), dim3(CBLOCK), args, smem, ctx->stream));
