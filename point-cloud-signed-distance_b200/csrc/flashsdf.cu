@@ -1358,14 +1358,17 @@ static int es_begin(flash_ctx* ctx, const double* X, int32_t C, const double* di
   if (it_smem > 48 * 1024) CU(cudaFuncSetAttribute(iterate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)it_smem));
   return 0;
 }
-// The solver loop as ONE persistent kernel (track_kernel): one configuration, no communicator, and a model whose point
-// loop takes no group records (run_groups would be a no-op).  Anything else runs the two-kernel loop below.
+// The solver loop as ONE persistent kernel (track_kernel): one configuration, no communicator; models with hulls only on
+// frame-sized clouds.  Anything else runs the two-kernel loop below.
 static bool track_kernel_applies(const flash_ctx* ctx, int C) {
   static const bool off = [] { const char* e = getenv("FLASHSDF_NO_TRACK_KERNEL"); return e && e[0] == '1'; }();
   const ModelC& M = ctx->hm.M;
   const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
   if (off || C != 1 || ctx->comm || P.n <= 0) return false;
-  if (P.grp_on && ctx->group_cull && M.n_convex >= 2) return false;
+  // models with hulls: the persistent loop runs without group records (every warp culls the hulls for its own 32 points),
+  // which beats group_kernel + cost_kernel + two launches per iteration on a depth frame (IRB140, 307,200 points, 30
+  // iterations: 1.64 ms against 1.90 ms; the K4 scene: 2.51 against 2.62) but not on a large cloud (K5: +22 % per pass)
+  if (P.grp_on && ctx->group_cull && M.n_convex >= 2 && P.n > 524288) return false;
   return track_layout(M).total + 64 <= (size_t)ctx->smem_optin;
 }
 static int run_track(flash_ctx* ctx, const flash_solver_params* sp, double n_total, bool have_div, bool want_cost) {

@@ -314,6 +314,47 @@ def test_on_device_estimate_state_batched_with_tolerance():
     assert np.allclose(c1, cost, rtol=1e-9)
 
 
+def test_on_device_estimate_state_models_with_hulls_single_config():
+    """One configuration of a model WITH hulls takes the persistent loop (track_kernel) without group records, and a
+    tolerance ends it early: host loop (one flash_cost_grad per iteration), device loop and the oracle's loop agree,
+    for the IRB140 and for the IRB140 + squishable + table scene (hulls and an RBF skin in one loop)."""
+    import ctypes as C
+    from flash import _lib
+    from flash._desc import SolverParams, c_double_p, c_int32_p
+    rng = np.random.default_rng(13)
+    m = flash.models.irb140()
+    sensor = flash.depthsensors.Kinect(60, 80)
+    cam = flash.depthsensors.affine((0, 1.5, 0.5), (1, 0, 0), np.pi / 2)
+    pts = flash.depthsensors.raycast(flash.ManipulatorState(m), sensor, cam)
+    x0 = 0.15 * rng.standard_normal(6)
+    solver = flash.tracking.NaiveSolver(6, rate=20.0, max_step=0.5, iteration_limit=25)
+    xh = flash.tracking.estimate_state(m, pts, x0, solver=solver)
+    xd = flash.tracking.estimate_state(m, pts, x0, solver=solver, on_device=True)
+    xo, co, it = ol.Oracle(m).estimate_state(x0, pts, rate=20.0, max_step=0.5, iteration_limit=25, mode=ol.GJK)
+    assert np.abs(xh - xd).max() < 1e-7
+    assert np.abs(xd - xo).max() < 1e-4
+    # early exit on the gradient tolerance: iterations reported, cost is the cost at the returned state
+    X = x0.reshape(1, 6).copy(); cost = np.zeros(1); iters = np.zeros(1, np.int32)
+    sp = SolverParams(20.0, 0.5, 200, 1e-3, 10.0)
+    m.check(_lib.lib().flash_estimate_state(m.ctx(), X.ctypes.data_as(c_double_p), 1, C.byref(sp), None, cost.ctypes.data_as(c_double_p), iters.ctypes.data_as(c_int32_p)))
+    f = flash.gradientdescent.CostFunctor(m, pts)
+    c1, g1, _ = f.batch(X, gradient=True)
+    assert 0 < iters[0] < 200 and np.linalg.norm(g1[0] / len(pts)) < 1e-3
+    assert abs(c1[0] - cost[0]) <= 1e-9 * abs(c1[0])
+    # the combined scene: 63 states, 8 hulls + a deformable skin
+    import bench
+    ms = bench.scene_model(flash)
+    xs = bench.scene_states(flash, ms, 1)[0]
+    st = flash.ManipulatorState(ms)
+    flash.gradientdescent.unflatten_(st, xs)
+    cloud = flash.depthsensors.raycast(st, flash.depthsensors.Kinect(60, 80), flash.depthsensors.affine((0.3, 1.8, 1.0), (1, 0, 0), np.pi / 2 + 0.25))
+    xs0 = xs.copy(); xs0[:flash.num_positions(ms)] += 0.01 * rng.standard_normal(flash.num_positions(ms))
+    solver = flash.tracking.NaiveSolver(len(xs), rate=0.01, max_step=0.1, iteration_limit=15)
+    xh = flash.tracking.estimate_state(ms, cloud, xs0, solver=solver)
+    xd = flash.tracking.estimate_state(ms, cloud, xs0, solver=solver, on_device=True)
+    assert np.abs(xh - xd).max() < 1e-6 * max(1.0, np.abs(xh).max())
+
+
 # ------------------------------------------------------------------ grid mode (north_star's gather design)
 def _trilinear_f64(vals, org, h, y):
     g = (y - org) / h
