@@ -117,7 +117,8 @@ typedef struct flash_options {
   int32_t deterministic;
   /* Single-process multi-GPU context (the reference's estimate_state is called from ONE Julia process,
    * src/tracking.jl:8-27): n_devices > 1 makes flash_model_create build one sub-context per entry of devices[]
-   * (CUDA ordinals), each with its own streams, joined by an in-process NCCL communicator.  flash_points_set /
+   * (CUDA ordinals), each with its own streams; the devices' sums are added by one kernel on devices[0] that reads
+   * the others' accumulators over NVLink peer memory, in a fixed order (no NCCL in this mode).  flash_points_set /
    * flash_frames_set shard the cloud (frames) over the devices, flash_cost_grad / flash_estimate_state return the
    * global result, flash_raycast shards the rays.  0 or 1: one device (`device`). */
   int32_t n_devices;
