@@ -69,6 +69,7 @@ struct CostParams {
   int pts_per_block;
   int use_grid;
   double* part;        // deterministic mode: per-tile partial sums [C][gridDim.y][acc_len] (null: fp64 atomics into acc)
+  const int* tile_order;   // block row -> tile (null: identity): expensive tiles first, so that the kernel does not end on them
 };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
@@ -349,6 +350,8 @@ struct GroupParams {
   long long rec_stride;
   int groups_per_block;
   int exact, want_cull;
+  unsigned* tile_w;        // [tiles] work estimate of every tile of cost_kernel, summed over configurations (null: not wanted)
+  int groups_per_tile;
 };
 constexpr int GBLOCK = 256;
 __host__ __device__ inline size_t group_smem(int tabf_len) { return align16(sizeof(HotModel)) + align16(sizeof(float) * (size_t)(tabf_len > 0 ? tabf_len : 4)); }
@@ -373,12 +376,49 @@ __global__ void __launch_bounds__(GBLOCK, 4) group_kernel(const GroupParams p) {
   const HotModel& H = *Hs;
   GeoView G; G.f4 = p.geo_f4; G.u32 = p.geo_u32; G.grid_pool = nullptr;
   uint4* out = p.rec + (size_t)c * p.rec_stride - g0;
-  for (long long g = b0 + tid; g < b1; g += GBLOCK) {
-    const float4 gb = __ldg(p.grp + g);
-    const GroupPre gp = group_prepass(H, G, tabf, gb.x, gb.y, gb.z, gb.w, p.exact != 0, p.want_cull != 0);
-    out[g] = make_uint4((gp.cand & 0xffffffu) | (gp.skip << 24), __float_as_uint(gp.cut), (unsigned)(gp.starts & 0xffffffffull),
-                        (unsigned)((gp.starts >> 32) & 0xffffull) | ((unsigned)(gp.first < 0 ? 255 : gp.first) << 16));
+  const unsigned all_skins = H.n_skins >= 32 ? 0xffffffffu : ((1u << H.n_skins) - 1u);
+  for (long long base = b0; base < b1; base += GBLOCK) {   // block-uniform trip count: the warps vote below
+    const long long g = base + tid;
+    const bool on = g < b1;
+    unsigned w = 0u;
+    if (on) {
+      const float4 gb = __ldg(p.grp + g);
+      const GroupPre gp = group_prepass(H, G, tabf, gb.x, gb.y, gb.z, gb.w, p.exact != 0, p.want_cull != 0);
+      out[g] = make_uint4((gp.cand & 0xffffffu) | (gp.skip << 24), __float_as_uint(gp.cut), (unsigned)(gp.starts & 0xffffffffull),
+                          (unsigned)((gp.starts >> 32) & 0xffffull) | ((unsigned)(gp.first < 0 ? 255 : gp.first) << 16));
+      // work estimate of the group in cost_kernel: one descent per candidate hull, several times that per skin still in play
+      w = 1u + (unsigned)__popc(gp.cand & 0xffffffu) + 6u * (unsigned)__popc(all_skins & ~gp.skip);
+    }
+    if (p.tile_w) {   // (block-uniform) consecutive lanes hold consecutive groups: one atomic per tile and warp
+      const int tl = on ? (int)((g - g0) / p.groups_per_tile) : -1;
+      const unsigned peers = __match_any_sync(0xffffffffu, tl);
+      const unsigned sum = __reduce_add_sync(peers, w);
+      if (on && (__ffs(peers) - 1) == (tid & 31)) atomicAdd(p.tile_w + tl, sum);
+    }
   }
+}
+
+// Order of the tiles of cost_kernel: heaviest first (longest-processing-time-first), from the estimates of group_kernel.
+// The cloud is in Hilbert order and its last tiles are often the expensive ones (near the bodies); launched last, their
+// blocks run on while most SMs have gone idle (K5 shard of 1.25 M points: 2.62 ms in Hilbert order, 2.50 ms reversed).
+// One block; tiles <= 1024.  Leaves the estimates zeroed for the next launch.
+__global__ void __launch_bounds__(1024) tile_order_kernel(unsigned* __restrict__ tile_w, int tiles, int* __restrict__ order) {
+  __shared__ unsigned long long key[1024];
+  const int t = threadIdx.x;
+  key[t] = t < tiles ? (((unsigned long long)tile_w[t] << 32) | (unsigned)(0xffffffffu - (unsigned)t)) : 0ull;
+  if (t < tiles) tile_w[t] = 0u;
+  __syncthreads();
+  for (int k = 2; k <= 1024; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      const int x = t ^ j;
+      if (x > t) {
+        const unsigned long long a = key[t], b = key[x];
+        const bool desc = (t & k) == 0;       // descending overall
+        if (desc ? a < b : a > b) { key[t] = b; key[x] = a; }
+      }
+      __syncthreads();
+    }
+  if (t < tiles) order[t] = (int)(0xffffffffu - (unsigned)(key[t] & 0xffffffffull));
 }
 
 // GRAD: accumulate gradient terms; ARGMIN: write the argmin surface per point; DIST: write the
@@ -573,7 +613,8 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   const int c = blockIdx.x;
   long long range0 = 0, range1 = p.n_pts;
   if (p.frames) { const int f = c / p.cfg_per_frame; range0 = p.frames[f]; range1 = range0 + p.frames[FRAMES_MAX + 1 + f]; }
-  if (range0 + (long long)blockIdx.y * p.pts_per_block >= range1) return;   // (block-uniform) a frame shorter than the longest one
+  const int ty = p.tile_order ? __ldg(p.tile_order + blockIdx.y) : (int)blockIdx.y;
+  if (range0 + (long long)ty * p.pts_per_block >= range1) return;   // (block-uniform) a frame shorter than the longest one
   // every block re-derives the layout from the same numbers the host used
   const HotModel* hot_g = p.hot;
   const int tab_len = hot_g->tab_len, acc_len = hot_g->acc_len, n_convex = hot_g->n_convex;
@@ -594,7 +635,7 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   double* queue = reinterpret_cast<double*>(smem + L.off_queue) + (size_t)warp * 32 * QENT;
   int* qslot = reinterpret_cast<int*>(smem + L.off_qslot) + warp * 32;
 
-  const long long tile0 = range0 + (long long)blockIdx.y * p.pts_per_block;
+  const long long tile0 = range0 + (long long)ty * p.pts_per_block;
   long long tile1 = tile0 + p.pts_per_block;
   if (tile1 > range1) tile1 = range1;
   double cost_local = cost_groups<GRAD, ARGMIN, DIST, DET>(p, H, G, tab, tabf, acc_w, queue, qslot, &s_next, c, n_convex, range0, tile0, tile1, lane, warp);
@@ -608,7 +649,7 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
     double s = 0;
 #pragma unroll
     for (int w = 0; w < CWARPS; ++w) s += acc_all[(size_t)w * acc_len + l];
-    if (DET) p.part[((size_t)c * gridDim.y + blockIdx.y) * acc_len + l] = s;
+    if (DET) p.part[((size_t)c * gridDim.y + ty) * acc_len + l] = s;
     else if (s != 0.0) atomicAdd(p.acc + (size_t)c * acc_len + l, s);
   }
 }

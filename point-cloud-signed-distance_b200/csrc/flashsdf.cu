@@ -99,6 +99,7 @@ struct flash_ctx {
   uint4* d_rec = nullptr; size_t cap_rec = 0;   // group records of group_kernel, [C][rec_stride]
   double* d_part = nullptr; size_t cap_part = 0; bool deterministic = false;   // per-tile partial sums [C][tiles][acc_len]
   unsigned* d_bar = nullptr;   // grid barrier counter of track_kernel
+  int* d_order = nullptr; size_t cap_order = 0; unsigned* d_tile_w = nullptr;   // block row -> tile of cost_kernel (tile_order_kernel), work estimates
   bool exact_groups = true;   // group_kernel evaluates the candidate hulls exactly at the ball centre (flash_dev.h group_prepass)
   // query scratch (skin_eval / raycast)
   double* d_qd = nullptr; size_t cap_qd = 0;
@@ -206,7 +207,7 @@ int launch_cost_t(flash_ctx* ctx, const CostParams& p, int C, int tiles, size_t 
 }
 
 // points per block: enough blocks for >= ~4 waves, at most 4096 points, at least one batch
-int choose_tile(const flash_ctx* ctx, long long n, int C) {
+int choose_tile(const flash_ctx* ctx, long long n, int C, bool lpt = false) {
   // small problems (tracking: one config, one depth frame): fewer full-size blocks than SMs would leave SMs idle
   // while the others queue 12 warps on their fp64 pipe; spread the points over one block per SM instead, in whole
   // warp groups of 32 (a block's last batch is then partial)
@@ -218,19 +219,30 @@ int choose_tile(const flash_ctx* ctx, long long n, int C) {
   }
   // >= 20 waves of blocks (2 per SM) where there is that much work (swept 4 .. 64 on K4 and on K5 at the per-rank size of 8 GPUs): the blocks' durations differ several-fold (tiles near the
   // bodies), so few waves end in a long tail -- K4's 8 x 16 batch ran as 1,280 blocks = 4.3 waves with 32,768-point tiles
-  static const long long waves = [] { const char* e = getenv("FLASHSDF_WAVES"); long long v = e ? atoll(e) : 0; return v > 0 ? v : 20ll; }();
+  // With the heaviest tiles launched first (tile_order_kernel) the tail is short anyway: half as many, larger blocks (K5 shard of
+  // 1.25 M points: 20 waves 2.520 ms, 10 waves 2.496; full cloud, 65,536-point tiles: 19.52 against 19.66 ms)
+  static const long long waves_env = [] { const char* e = getenv("FLASHSDF_WAVES"); long long v = e ? atoll(e) : 0; return v > 0 ? v : 0ll; }();
+  const long long waves = waves_env ? waves_env : (lpt ? 10ll : 20ll);
   const long long target_blocks = (long long)ctx->sm_count * 2 * waves;
   long long ppb = (n * C + target_blocks - 1) / target_blocks;
   ppb = ((ppb + CBLOCK - 1) / CBLOCK) * CBLOCK;
   if (ppb < CBLOCK) ppb = CBLOCK;
   static const long long max_tile = [] { const char* e = getenv("FLASHSDF_TILE"); long long v = e ? (atoll(e) / 32) * 32 : 0; return v >= CBLOCK ? v : (32768ll / CBLOCK) * CBLOCK; }();   // K5: 4032 -> 55.5 ms, 8064 -> 54.0, 16128 -> 53.5, 32256 -> 53.5; with the group pre-pass 16128 -> 45.4, 24576 -> 44.6, 32256 -> 44.5
-  if (ppb > max_tile) ppb = max_tile;
+  if (ppb > (lpt ? 2 * max_tile : max_tile)) ppb = lpt ? 2 * max_tile : max_tile;
   while ((n + ppb - 1) / ppb > 65535) ppb *= 2;
   return (int)ppb;
 }
 
+// cost_kernel's tiles are launched heaviest first where group_kernel runs anyway (its records give the estimates), on ONE frame
+// (a batch of frames shares its block rows between frames: the estimates of a row then mix places, and K4 measured 3 % slower
+// with it) with enough (group, configuration) pairs for a tail to matter
+static bool lpt_applies(const flash_ctx* ctx, int C, int cfg_per_frame) {
+  static const bool no_order = [] { const char* e = getenv("FLASHSDF_NO_TILE_ORDER"); return e && e[0] == '1'; }();
+  const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
+  return !no_order && cfg_per_frame == 0 && P.grp_on && ctx->group_cull && ctx->hm.M.n_convex >= 2 && ((P.n + 31) / 32) * C >= 262144;
+}
 // group pre-pass (group_kernel) for C configurations of the current point set -> ctx->d_rec; *stride = records per config
-int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride) {
+int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride, int pts_per_block = 0, bool* ordered = nullptr) {
   const ModelC& M = ctx->hm.M;
   const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
   *stride = 0;
@@ -252,11 +264,25 @@ int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride) {
   // K5 (2e7 pairs) 28.6 -> 22.0 ms; on a single depth frame (K2: 9,600 pairs) the longer serial threads cost more than
   // the tighter candidate sets save (0.069 -> 0.088 ms)
   g.exact = (ctx->exact_groups && !ctx->use_grid && G * C >= 262144) ? 1 : 0; g.want_cull = 1;
+  // tile order of cost_kernel (heaviest first) where there are enough blocks for a tail to matter and few enough tiles to sort
+  const long long tiles = pts_per_block > 0 ? (n_tile + pts_per_block - 1) / pts_per_block : 0;
+  g.tile_w = nullptr; g.groups_per_tile = 1;
+  if (lpt_applies(ctx, C, cfg_per_frame) && tiles >= 8 && tiles <= 1024) {
+    if (!ctx->d_tile_w) { CU(cudaMalloc((void**)&ctx->d_tile_w, 1024 * sizeof(unsigned))); CU(cudaMemsetAsync(ctx->d_tile_w, 0, 1024 * sizeof(unsigned), ctx->stream)); }
+    rc = ensure(ctx, ctx->d_order, ctx->cap_order, 1024); if (rc) return rc;
+    g.tile_w = ctx->d_tile_w; g.groups_per_tile = pts_per_block / 32;
+  }
   const size_t smem = group_smem(M.tabf_len);
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   group_kernel<<<dim3((unsigned)C, (unsigned)((G + gpb - 1) / gpb)), GBLOCK, smem, ctx->stream>>>(g);
   CU(cudaGetLastError());
   ctx->launches++; ctx->last.launches++;
+  if (g.tile_w) {
+    tile_order_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->d_tile_w, (int)tiles, ctx->d_order);
+    CU(cudaGetLastError());
+    ctx->launches++; ctx->last.launches++;
+    if (ordered) *ordered = true;
+  }
   *stride = G;
   return 0;
 }
@@ -266,7 +292,9 @@ int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin, int cfg_per_fr
   const ModelC& M = ctx->hm.M;
   const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
   long long rec_stride = 0;
-  { int rc = run_groups(ctx, C, cfg_per_frame, &rec_stride); if (rc) return rc; }
+  bool ordered = false;
+  const int ppb = choose_tile(ctx, cfg_per_frame > 0 ? P.max_cnt : P.n, C, lpt_applies(ctx, C, cfg_per_frame));
+  { int rc = run_groups(ctx, C, cfg_per_frame, &rec_stride, ppb, &ordered); if (rc) return rc; }
   if (ctx->profiling) CU(cudaEventRecord(ctx->ev[5], ctx->stream));
   CostParams p;
   p.rec = rec_stride > 0 ? ctx->d_rec : nullptr; p.rec_stride = rec_stride;
@@ -275,13 +303,14 @@ int run_cost(flash_ctx* ctx, int C, bool grad, int32_t* d_argmin, int cfg_per_fr
   p.grp = P.grp_on && ctx->group_cull ? P.d_grp : nullptr;
   p.frames = cfg_per_frame > 0 ? P.d_frames : nullptr; p.cfg_per_frame = cfg_per_frame > 0 ? cfg_per_frame : 1;
   const long long n_tile = cfg_per_frame > 0 ? P.max_cnt : P.n;
-  p.pts_per_block = choose_tile(ctx, n_tile, C);
+  p.pts_per_block = ppb;
   p.use_grid = ctx->use_grid ? 1 : 0;
   if (P.n == 0 || n_tile == 0) return 0;
   const int tiles = (int)((n_tile + p.pts_per_block - 1) / p.pts_per_block);
   const size_t smem = cost_layout(ctx, grad).total;
   if (smem + COST_STATIC_SMEM > (size_t)ctx->smem_optin) return fail(ctx, FLASH_ERR_TOO_LARGE, "model tables do not fit in shared memory (" + std::to_string(smem) + " bytes)");
-  p.part = nullptr;
+  p.part = nullptr; p.tile_order = nullptr;
+  if (ordered) p.tile_order = ctx->d_order;
   if (ctx->deterministic) {
     int rc = ensure(ctx, ctx->d_part, ctx->cap_part, (size_t)C * (size_t)tiles * (size_t)M.acc_len); if (rc) return rc;
     p.part = ctx->d_part;
@@ -651,7 +680,7 @@ void flash_destroy(flash_ctx* ctx) {
   if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
   void* frees[] = {ctx->d_model, ctx->d_hot, ctx->d_geo_f4, ctx->d_geo_u32, ctx->d_grid_pool, ctx->d_stage,
                    ctx->d_X, ctx->d_tab, ctx->d_aux, ctx->d_acc, ctx->d_cost, ctx->d_grad, ctx->d_div, ctx->d_status, ctx->d_done, ctx->d_iters,
-                   ctx->d_argmin, ctx->d_rec, ctx->d_part, ctx->d_bar, ctx->d_qd, ctx->d_qi, ctx->d_keys[0], ctx->d_keys[1], ctx->d_idx[0], ctx->d_idx[1], ctx->d_table, ctx->d_sums, ctx->d_bounds};
+                   ctx->d_argmin, ctx->d_rec, ctx->d_part, ctx->d_bar, ctx->d_order, ctx->d_tile_w, ctx->d_qd, ctx->d_qi, ctx->d_keys[0], ctx->d_keys[1], ctx->d_idx[0], ctx->d_idx[1], ctx->d_table, ctx->d_sums, ctx->d_bounds};
   for (void* p : frees) if (p) cudaFree(p);
   for (auto& P : ctx->ps) {
     if (P.d_pts && !P.external) cudaFree(P.d_pts);
@@ -1162,7 +1191,7 @@ int flash_skin_eval(flash_ctx* ctx, const double* x, const double* xyz, int64_t 
   ctx->launches++; ctx->last.launches++;
   CostParams p;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
-  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr; p.frames = nullptr; p.cfg_per_frame = 1; p.rec = nullptr; p.rec_stride = 0; p.part = nullptr;
+  p.pts = d_f4; p.n_pts = n; p.tab = ctx->d_tab; p.acc = ctx->d_acc; p.argmin = ctx->d_qi; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr; p.frames = nullptr; p.cfg_per_frame = 1; p.rec = nullptr; p.rec_stride = 0; p.part = nullptr; p.tile_order = nullptr;
   p.pts_per_block = choose_tile(ctx, n, 1); p.use_grid = ctx->use_grid ? 1 : 0;
   const int tiles = (int)((n + p.pts_per_block - 1) / p.pts_per_block);
   const size_t smem = cost_layout(ctx, false).total;
@@ -1233,7 +1262,7 @@ int flash_skin_eval_static(flash_ctx* ctx, const double* x, const double* xyz, i
   ctx->launches += 2; ctx->last.launches += 2;
   CostParams p;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
-  p.pts = d_f4; p.n_pts = n; p.tab = d_tab; p.acc = nullptr; p.argmin = d_arg; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr; p.frames = nullptr; p.cfg_per_frame = 1; p.rec = nullptr; p.rec_stride = 0; p.part = nullptr;
+  p.pts = d_f4; p.n_pts = n; p.tab = d_tab; p.acc = nullptr; p.argmin = d_arg; p.dist = d_dist; p.perm = nullptr; p.grp = nullptr; p.frames = nullptr; p.cfg_per_frame = 1; p.rec = nullptr; p.rec_stride = 0; p.part = nullptr; p.tile_order = nullptr;
   p.pts_per_block = choose_tile(ctx, n, 1); p.use_grid = ctx->use_grid ? 1 : 0;
   const int tiles = (int)((n + p.pts_per_block - 1) / p.pts_per_block);
   if ((rc = launch_cost_t<false, true, true>(ctx, p, 1, tiles, cost_layout(ctx, false).total))) return rc;
@@ -1385,7 +1414,7 @@ static int run_track(flash_ctx* ctx, const flash_solver_params* sp, double n_tot
   CostParams& p = t.cp;
   p.hot = ctx->d_hot; p.geo_f4 = ctx->d_geo_f4; p.geo_u32 = ctx->d_geo_u32; p.grid_pool = ctx->d_grid_pool;
   p.pts = P.d_pts; p.n_pts = P.n; p.tab = nullptr; p.acc = nullptr; p.argmin = nullptr; p.dist = nullptr; p.perm = nullptr; p.grp = nullptr;
-  p.rec = nullptr; p.rec_stride = 0; p.frames = nullptr; p.cfg_per_frame = 1; p.pts_per_block = (int)ppb; p.use_grid = ctx->use_grid ? 1 : 0; p.part = nullptr;
+  p.rec = nullptr; p.rec_stride = 0; p.frames = nullptr; p.cfg_per_frame = 1; p.pts_per_block = (int)ppb; p.use_grid = ctx->use_grid ? 1 : 0; p.part = nullptr; p.tile_order = nullptr;
   t.model = ctx->d_model; t.X = ctx->d_X; t.part = ctx->d_part; t.bar = ctx->d_bar; t.cost = ctx->d_cost; t.iters = ctx->d_iters; t.done = ctx->d_done; t.status = ctx->d_status;
   t.divisors = have_div ? ctx->d_div : nullptr;
   t.w_def = sp->deformation_cost_weight; t.inv_n = n_total > 0 ? 1.0 / n_total : 0.0; t.rate = sp->rate; t.max_step = sp->max_step; t.tol = sp->gradient_convergence_tolerance;
