@@ -195,45 +195,81 @@ __device__ __forceinline__ void prepare_block(const ModelC& M, const double* x, 
     __syncthreads();
     FLASH_TS(3);
     bool ok = true;
-    if (Mm * Mm <= T) {
-      // Fast path (K3: 17 x 17 <= 320 threads): thread e owns element (i0, j0) in a register, the matrix in shared
+    if (Mm * Mm <= T && Mm <= 22) {
+      // Fast path (K3: 17 x 17 <= 320 threads): every thread owns one element in a register, the matrix in shared
       // memory is only the exchange medium.  Per pivot ONE barrier: the matrix (and the reciprocals) alternate between
-      // two buffers, so a step reads the buffer the previous step wrote and writes the other one; every thread scans
-      // the pivot column itself (broadcast loads, no shuffle search, no broadcast phase), the row exchange is done by
-      // addressing (row bi "holds" old row kk) instead of a swap phase, and the reciprocal of every pivot candidate was
+      // two buffers, so a step reads the buffer the previous step wrote and writes the other one; the row exchange is done
+      // by addressing (row bi "holds" old row kk) instead of a swap phase, and the reciprocal of every pivot candidate was
       // computed by the thread that produced it during the previous update, so no division sits on the critical path.
-      // Same operations on the same numbers as the generic path below except for the reciprocal (rcp_newton, ~1 ulp).
+      // Same update formulas as the generic path below; the reciprocal (rcp_newton, ~1 ulp) and the choice among
+      // near-equal pivot candidates (below) differ.
       // (Tried: the whole inversion on ONE warp, a column per lane in registers, multipliers by shuffles, no barrier --
       // 3x slower, 51 k cycles against 17 k: ~400 dependent instructions per pivot on a single warp issue at ~5 cycles each.
       // Tried in track_kernel: Newton-Schulz refinement of the previous iteration's inverse with a residual certificate --
       // never accepted on K3: one solver step moves the system further than |I - A X| < 1/4 allows.)
+      // The pivot search is not a scan either: a thread owns element (i, j) with tid = j * Mm + i, so the Mm threads that
+      // produce column kk + 1 during step kk sit in one warp (or two), and each such warp finds its largest candidate with
+      // ONE redux on a 32-bit key -- the magnitude rounded to fp32 with its low five bits replaced by 31 - row (largest
+      // magnitude first, lowest row on ties) -- and leaves it in shared memory; step kk + 1 reads two words.  The pivot is
+      // then the largest candidate up to 2^-19 relative, which is all partial pivoting needs (K3: the 17 broadcast loads
+      // and dependent fp64 compares per thread and pivot were ~1/3 of the inversion's 16 k cycles).
       const bool act = tid < Mm * Mm;
-      const int i = i0, j = j0;
+      const int j = tid / Mm, i = tid - j * Mm;
+      const int e = i * Mm + j;                               // where this thread's element lives in the row-major matrices
       const double* cur = A; double* nxt = scr + 4;          // [Mm][Mm] each
       const double* rcp = prow; double* rcn = pcol;          // [Mm] reciprocals of the next pivot column (prow/pcol are unused here)
-      double a = act ? A[tid] : 0.0;
-      if (act && j == 0) prow[i] = rcp_newton(a);
+      unsigned* pk = reinterpret_cast<unsigned*>(scr);        // [2][2] pivot keys of the next column: per buffer, one word per warp that holds it
+      unsigned* pkc = pk; unsigned* pkn = pk + 2;
+      double a = act ? A[e] : 0.0;
+      {
+        const bool cand = act && j == 0;
+        const unsigned mask = __ballot_sync(0xffffffffu, cand);
+        if (cand) {
+          const float mg = (float)fabs(a);
+          const unsigned key = ((mg == mg ? __float_as_uint(mg) : 0u) & ~31u) | (unsigned)(31 - i);   // NaN: never the pivot
+          const unsigned m = __reduce_max_sync(mask, key);
+          prow[i] = rcp_newton(a);
+          if (lane == __ffs(mask) - 1) { pkc[0] = m; pkc[1] = 0u; }   // column 0 = threads 0 .. Mm-1: one warp
+        }
+      }
       __syncthreads();
       for (int kk = 0; kk < Mm; ++kk) {
-        double best = -1.0; int bi = kk;   // (comparing the bit patterns as 64-bit integers instead: 5 % slower end to end)
-#pragma unroll 4
-        for (int r = kk; r < Mm; ++r) { const double v = fabs(cur[r * Mm + kk]); if (v > best) { best = v; bi = r; } }   // lowest row on ties
-        if (!(best > 0.0)) ok = false;
+        const unsigned k0 = pkc[0], k1 = pkc[1];
+        const unsigned km = k0 > k1 ? k0 : k1;
+        const int bi = 31 - (int)(km & 31u);
+        if ((km >> 5) == 0u) ok = false;         // every candidate is zero (or below the fp32 range)
         const double inv = rcp[bi];
         if (tid == 0) piv[kk] = (double)bi;
+        double nv = 0.0;
         if (act) {
           const double pr = cur[bi * Mm + j];
           const double f = (i == bi) ? cur[kk * Mm + kk] : cur[i * Mm + kk];
           const double own = (i == bi) ? cur[kk * Mm + j] : a;
-          double nv;
           if (i == kk) nv = (j == kk) ? inv : pr * inv;
           else nv = (j == kk) ? -f * inv : fma(-f, pr * inv, own);
-          nxt[tid] = nv; a = nv;
-          if (j == kk + 1) rcn[i] = rcp_newton(nv);
+          nxt[e] = nv; a = nv;
+        }
+        {   // the candidates of the next pivot: column kk + 1, rows below kk
+          const int lo = (kk + 1) * Mm;                                   // first thread of that column
+          const bool col = act && j == kk + 1;
+          const bool cand = col && i > kk;
+          const unsigned mask = __ballot_sync(0xffffffffu, cand);
+          if (col) rcn[i] = rcp_newton(nv);
+          if (cand) {
+            const float mg = (float)fabs(nv);
+            const unsigned key = ((mg == mg ? __float_as_uint(mg) : 0u) & ~31u) | (unsigned)(31 - i);
+            const unsigned m = __reduce_max_sync(mask, key);
+            if (lane == __ffs(mask) - 1) {
+              const int slot = warp - ((lo + kk + 1) >> 5);              // warps of the candidates: that of thread lo + kk + 1, and maybe the next
+              pkn[slot] = m;
+              if (((lo + Mm - 1) >> 5) == ((lo + kk + 1) >> 5)) pkn[1] = 0u;   // all in one warp: the other word is empty
+            }
+          }
         }
         __syncthreads();                         // the new matrix is complete; nobody reads the old one any more
         { const double* t0 = cur; cur = nxt; nxt = const_cast<double*>(t0); }
         { const double* t1 = rcp; rcp = rcn; rcn = const_cast<double*>(t1); }
+        { unsigned* t2 = pkc; pkc = pkn; pkn = t2; }
       }
       FLASH_TS(4);
       // undo the row exchanges on the columns: the exchanges (kk, piv[kk]), kk = Mm-1 .. 0, move this thread's
@@ -401,14 +437,14 @@ __global__ void __launch_bounds__(GBLOCK, 4) group_kernel(const GroupParams p) {
 // Order of the tiles of cost_kernel: heaviest first (longest-processing-time-first), from the estimates of group_kernel.
 // The cloud is in Hilbert order and its last tiles are often the expensive ones (near the bodies); launched last, their
 // blocks run on while most SMs have gone idle (K5 shard of 1.25 M points: 2.62 ms in Hilbert order, 2.50 ms reversed).
-// One block; tiles <= 1024.  Leaves the estimates zeroed for the next launch.
+// One block of blockDim.x = the power of two >= tiles (<= 1024) threads.  Leaves the estimates zeroed for the next launch.
 __global__ void __launch_bounds__(1024) tile_order_kernel(unsigned* __restrict__ tile_w, int tiles, int* __restrict__ order) {
   __shared__ unsigned long long key[1024];
   const int t = threadIdx.x;
   key[t] = t < tiles ? (((unsigned long long)tile_w[t] << 32) | (unsigned)(0xffffffffu - (unsigned)t)) : 0ull;
   if (t < tiles) tile_w[t] = 0u;
   __syncthreads();
-  for (int k = 2; k <= 1024; k <<= 1)
+  for (int k = 2; k <= (int)blockDim.x; k <<= 1)
     for (int j = k >> 1; j > 0; j >>= 1) {
       const int x = t ^ j;
       if (x > t) {

@@ -278,7 +278,8 @@ int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride, int 
   CU(cudaGetLastError());
   ctx->launches++; ctx->last.launches++;
   if (g.tile_w) {
-    tile_order_kernel<<<1, 1024, 0, ctx->stream>>>(ctx->d_tile_w, (int)tiles, ctx->d_order);
+    int nt = 32; while (nt < tiles) nt <<= 1;
+    tile_order_kernel<<<1, nt, 0, ctx->stream>>>(ctx->d_tile_w, (int)tiles, ctx->d_order);
     CU(cudaGetLastError());
     ctx->launches++; ctx->last.launches++;
     if (ordered) *ordered = true;
