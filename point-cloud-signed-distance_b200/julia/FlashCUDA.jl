@@ -263,4 +263,50 @@ function raycast_depths(ctx::Context, x::Vector{Float64}, sensor::Flash.DepthSen
     permutedims(reshape(depths, size(rays, 2), size(rays, 1)), (2, 1))
 end
 
+"`DepthSensors.raycast_points` (src/depthsensors.jl:99-113): the world points of the rays that hit, in row-major ray order."
+function raycast_points(ctx::Context, x::Vector{Float64}, sensor::Flash.DepthSensors.DepthSensor, R::Matrix{Float64}, t::Vector{Float64})
+    rm = permutedims(sensor.rays, (2, 1))
+    nr = length(rm)
+    depths = Array{Float64}(nr)
+    hits = Array{Float64}(3nr)
+    nh = Ref{Int64}(0)
+    check(ctx.ptr, ccall((:flash_raycast, lib), Cint,
+                         (Ptr{Void}, Ptr{Float64}, Ptr{Float64}, Int64, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Ptr{Int64}),
+                         ctx.ptr, x, pointer(reinterpret(Float64, vec(rm), (3nr,))), nr, rowmajor34(R, t), depths, hits, nh))
+    [SVector{3, Float64}(hits[3k - 2], hits[3k - 1], hits[3k]) for k in 1:nh[]]
+end
+
+"`Flash.skin(state)` (src/Flash.jl:265-268) as a closure over the device field: `skin(ctx, x)(p)` for one point or a vector of points."
+function skin(ctx::Context, x::Vector{Float64})
+    function field(points::Vector{SVector{3, Float64}})
+        n = length(points)
+        dist = Array{Float64}(n)
+        check(ctx.ptr, ccall((:flash_skin_eval, lib), Cint, (Ptr{Void}, Ptr{Float64}, Ptr{Float64}, Int64, Ptr{Float64}, Ptr{Int32}),
+                             ctx.ptr, x, pointer(reinterpret(Float64, points, (3n,))), n, dist, C_NULL))
+        dist
+    end
+    field(p::SVector{3, Float64}) = field([p])[1]
+    field
+end
+
+# ---- a live stream (examples/irb_and_squishable.ipynb:495-503): frame k+1 uploads and sorts while frame k is tracked
+"Start the upload of the NEXT frame; `swap_points!` makes it current.  `sensed_points` must stay alive until then."
+function set_points_async!(ctx::Context, sensed_points::Vector{SVector{3, Float64}})
+    check(ctx.ptr, ccall((:flash_points_set_async, lib), Cint, (Ptr{Void}, Ptr{Float64}, Int64),
+          ctx.ptr, pointer(reinterpret(Float64, sensed_points, (3 * length(sensed_points),))), length(sensed_points)))
+end
+swap_points!(ctx::Context) = check(ctx.ptr, ccall((:flash_points_swap, lib), Cint, (Ptr{Void},), ctx.ptr))
+
+# ---- `Models.load_urdf` without the Julia mesh packages: URDF + STL / OBJ are read by the library (src/models.jl:154-171)
+"A context for the URDF's manipulator (one convex surface per visual mesh); `package_path` as in `Models.load_urdf`."
+function Context(urdf::String; package_path::Vector{String}=String[])
+    out = Ref{Ptr{Void}}(C_NULL)
+    rc = ccall((:flash_model_load_urdf, lib), Cint, (Cstring, Ptr{Cstring}, Int32, Ptr{Void}, Ptr{Ptr{Void}}),
+               urdf, package_path, length(package_path), C_NULL, out)
+    check(C_NULL, rc)
+    ctx = Context(out[], Any[])
+    finalizer(ctx, c -> ccall((:flash_destroy, lib), Void, (Ptr{Void},), c.ptr))
+    ctx
+end
+
 end # module
