@@ -355,6 +355,38 @@ def test_on_device_estimate_state_models_with_hulls_single_config():
     assert np.abs(xh - xd).max() < 1e-6 * max(1.0, np.abs(xh).max())
 
 
+def test_on_device_estimate_state_edge_cases_of_the_persistent_loop():
+    """track_kernel's corners: no iterations at all (cost at the start state, state untouched); a full-resolution frame
+    on a skin-only model (65 groups per block: the dynamic hand-out instantiation) against the host loop; the same
+    context re-used on a smaller frame afterwards; a cloud smaller than one group."""
+    import ctypes as C
+    from flash import _lib
+    from flash._desc import SolverParams, c_double_p, c_int32_p
+    rng = np.random.default_rng(14)
+    m = flash.models.squishable()
+    L = _lib.lib()
+    x0 = _state(m, rng, qs=0.05, ds=0.005)
+    big = _points(rng, 307200, [-0.35, -0.35, -0.3], [0.35, 0.35, 0.3])
+    small = big[:1000]
+    div = np.r_[np.ones(7), 1e-3 * np.ones(36)]
+    # (1) iteration_limit = 0
+    f = flash.gradientdescent.CostFunctor(m, small)
+    c_ref = f(x0)
+    X = x0.reshape(1, -1).copy(); cost = np.zeros(1); iters = np.full(1, -1, np.int32)
+    sp = SolverParams(0.01, 0.1, 0, 0.0, 10.0)
+    m.check(L.flash_estimate_state(m.ctx(), X.ctypes.data_as(c_double_p), 1, C.byref(sp), div.ctypes.data_as(c_double_p), cost.ctypes.data_as(c_double_p), iters.ctypes.data_as(c_int32_p)))
+    assert np.array_equal(X[0], x0) and iters[0] == 0 and abs(cost[0] - c_ref) <= 1e-9 * abs(c_ref)
+    # (2) a full frame, then (3) the small one again on the same context
+    # (4 iterations: on a cloud that is no surface the iteration is unstable -- host and device loops, identical to 1e-15 after
+    # one step, are 1e-13 apart after 4 and 1e-3 after 12, with the two-kernel device loop just the same: tools/track_diff_probe.py)
+    solver = flash.tracking.NaiveSolver(43, rate=0.01, max_step=0.1, iteration_limit=4, precondition_divisors=div)
+    for cloud in (big, small, big[:20]):
+        xh = flash.tracking.estimate_state(m, cloud, x0, solver=solver)
+        xd = flash.tracking.estimate_state(m, cloud, x0, solver=solver, on_device=True)
+        assert np.isfinite(xd).all() and np.abs(xh - xd).max() < 1e-10, (len(cloud), np.abs(xh - xd).max())
+        assert np.abs(xd - x0).max() > 1e-3
+
+
 # ------------------------------------------------------------------ grid mode (north_star's gather design)
 def _trilinear_f64(vals, org, h, y):
     g = (y - org) / h
