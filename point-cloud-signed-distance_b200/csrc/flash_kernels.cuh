@@ -69,7 +69,7 @@ struct CostParams {
   int pts_per_block;
   int use_grid;
   double* part;        // deterministic mode: per-tile partial sums [C][gridDim.y][acc_len] (null: fp64 atomics into acc)
-  const int* tile_order;   // block row -> tile (null: identity): expensive tiles first, so that the kernel does not end on them
+  const int* tile_order;   // [frames][gridDim.y] block row -> tile (null: identity): expensive tiles first, so that the kernel does not end on them
 };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
@@ -386,8 +386,8 @@ struct GroupParams {
   long long rec_stride;
   int groups_per_block;
   int exact, want_cull;
-  unsigned* tile_w;        // [tiles] work estimate of every tile of cost_kernel, summed over configurations (null: not wanted)
-  int groups_per_tile;
+  unsigned* tile_w;        // [frames][tiles] work estimate of every tile of cost_kernel, summed over the frame's configurations (null: not wanted)
+  int groups_per_tile, tiles;
 };
 constexpr int GBLOCK = 256;
 __host__ __device__ inline size_t group_smem(int tabf_len) { return align16(sizeof(HotModel)) + align16(sizeof(float) * (size_t)(tabf_len > 0 ? tabf_len : 4)); }
@@ -395,7 +395,8 @@ __global__ void __launch_bounds__(GBLOCK, 4) group_kernel(const GroupParams p) {
   extern __shared__ __align__(16) unsigned char smem[];
   const int tid = threadIdx.x, c = blockIdx.x;
   long long g0 = 0, g1 = p.n_groups;
-  if (p.frames) { const int f = c / p.cfg_per_frame; g0 = p.frames[f] >> 5; g1 = g0 + ((p.frames[FRAMES_MAX + 1 + f] + 31) >> 5); }
+  int frame = 0;
+  if (p.frames) { frame = c / p.cfg_per_frame; g0 = p.frames[frame] >> 5; g1 = g0 + ((p.frames[FRAMES_MAX + 1 + frame] + 31) >> 5); }
   const long long b0 = g0 + (long long)blockIdx.y * p.groups_per_block;
   if (b0 >= g1) return;
   long long b1 = b0 + p.groups_per_block; if (b1 > g1) b1 = g1;
@@ -429,7 +430,7 @@ __global__ void __launch_bounds__(GBLOCK, 4) group_kernel(const GroupParams p) {
       const int tl = on ? (int)((g - g0) / p.groups_per_tile) : -1;
       const unsigned peers = __match_any_sync(0xffffffffu, tl);
       const unsigned sum = __reduce_add_sync(peers, w);
-      if (on && (__ffs(peers) - 1) == (tid & 31)) atomicAdd(p.tile_w + tl, sum);
+      if (on && (__ffs(peers) - 1) == (tid & 31)) atomicAdd(p.tile_w + (size_t)frame * p.tiles + tl, sum);
     }
   }
 }
@@ -437,10 +438,11 @@ __global__ void __launch_bounds__(GBLOCK, 4) group_kernel(const GroupParams p) {
 // Order of the tiles of cost_kernel: heaviest first (longest-processing-time-first), from the estimates of group_kernel.
 // The cloud is in Hilbert order and its last tiles are often the expensive ones (near the bodies); launched last, their
 // blocks run on while most SMs have gone idle (K5 shard of 1.25 M points: 2.62 ms in Hilbert order, 2.50 ms reversed).
-// One block of blockDim.x = the power of two >= tiles (<= 1024) threads.  Leaves the estimates zeroed for the next launch.
+// One block per frame of blockDim.x = the power of two >= tiles (<= 1024) threads.  Leaves the estimates zeroed for the next launch.
 __global__ void __launch_bounds__(1024) tile_order_kernel(unsigned* __restrict__ tile_w, int tiles, int* __restrict__ order) {
   __shared__ unsigned long long key[1024];
   const int t = threadIdx.x;
+  tile_w += (size_t)blockIdx.x * tiles; order += (size_t)blockIdx.x * tiles;   // one block per frame
   key[t] = t < tiles ? (((unsigned long long)tile_w[t] << 32) | (unsigned)(0xffffffffu - (unsigned)t)) : 0ull;
   if (t < tiles) tile_w[t] = 0u;
   __syncthreads();
@@ -648,8 +650,9 @@ __global__ void __launch_bounds__(CBLOCK, FLASH_MINB) cost_kernel(const CostPara
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int c = blockIdx.x;
   long long range0 = 0, range1 = p.n_pts;
-  if (p.frames) { const int f = c / p.cfg_per_frame; range0 = p.frames[f]; range1 = range0 + p.frames[FRAMES_MAX + 1 + f]; }
-  const int ty = p.tile_order ? __ldg(p.tile_order + blockIdx.y) : (int)blockIdx.y;
+  int frame = 0;
+  if (p.frames) { frame = c / p.cfg_per_frame; range0 = p.frames[frame]; range1 = range0 + p.frames[FRAMES_MAX + 1 + frame]; }
+  const int ty = p.tile_order ? __ldg(p.tile_order + (size_t)frame * gridDim.y + blockIdx.y) : (int)blockIdx.y;   // one order per frame
   if (range0 + (long long)ty * p.pts_per_block >= range1) return;   // (block-uniform) a frame shorter than the longest one
   // every block re-derives the layout from the same numbers the host used
   const HotModel* hot_g = p.hot;

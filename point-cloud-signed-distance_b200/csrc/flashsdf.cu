@@ -233,13 +233,14 @@ int choose_tile(const flash_ctx* ctx, long long n, int C, bool lpt = false) {
   return (int)ppb;
 }
 
-// cost_kernel's tiles are launched heaviest first where group_kernel runs anyway (its records give the estimates), on ONE frame
-// (a batch of frames shares its block rows between frames: the estimates of a row then mix places, and K4 measured 3 % slower
-// with it) with enough (group, configuration) pairs for a tail to matter
+// cost_kernel's tiles are launched heaviest first where group_kernel runs anyway (its records give the estimates) and there
+// are enough (group, configuration) pairs for a tail to matter.  A batch of frames gets one order per frame (one order for
+// all frames mixes places in a block row: K4 measured 3 % slower with that, 2 % faster with its own order per frame).
 static bool lpt_applies(const flash_ctx* ctx, int C, int cfg_per_frame) {
-  static const bool no_order = [] { const char* e = getenv("FLASHSDF_NO_TILE_ORDER"); return e && e[0] == '1'; }();
+  static const int mode = [] { const char* e = getenv("FLASHSDF_TILE_ORDER"); return e ? atoi(e) : 2; }();   // 0: off, 1: single frames only, 2: batches of frames too
   const flash_ctx::PointSet& P = ctx->ps[ctx->cur];
-  return !no_order && cfg_per_frame == 0 && P.grp_on && ctx->group_cull && ctx->hm.M.n_convex >= 2 && ((P.n + 31) / 32) * C >= 262144;
+  const long long n_tile = cfg_per_frame > 0 ? P.max_cnt : P.n;
+  return mode > 0 && (cfg_per_frame == 0 || mode > 1) && P.grp_on && ctx->group_cull && ctx->hm.M.n_convex >= 2 && ((n_tile + 31) / 32) * C >= 262144;
 }
 // group pre-pass (group_kernel) for C configurations of the current point set -> ctx->d_rec; *stride = records per config
 int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride, int pts_per_block = 0, bool* ordered = nullptr) {
@@ -266,11 +267,12 @@ int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride, int 
   g.exact = (ctx->exact_groups && !ctx->use_grid && G * C >= 262144) ? 1 : 0; g.want_cull = 1;
   // tile order of cost_kernel (heaviest first) where there are enough blocks for a tail to matter and few enough tiles to sort
   const long long tiles = pts_per_block > 0 ? (n_tile + pts_per_block - 1) / pts_per_block : 0;
-  g.tile_w = nullptr; g.groups_per_tile = 1;
+  g.tile_w = nullptr; g.groups_per_tile = 1; g.tiles = 0;
   if (lpt_applies(ctx, C, cfg_per_frame) && tiles >= 8 && tiles <= 1024) {
-    if (!ctx->d_tile_w) { CU(cudaMalloc((void**)&ctx->d_tile_w, 1024 * sizeof(unsigned))); CU(cudaMemsetAsync(ctx->d_tile_w, 0, 1024 * sizeof(unsigned), ctx->stream)); }
-    rc = ensure(ctx, ctx->d_order, ctx->cap_order, 1024); if (rc) return rc;
-    g.tile_w = ctx->d_tile_w; g.groups_per_tile = pts_per_block / 32;
+    const size_t slots = (size_t)MAX_FRAMES * 1024;
+    if (!ctx->d_tile_w) { CU(cudaMalloc((void**)&ctx->d_tile_w, slots * sizeof(unsigned))); CU(cudaMemsetAsync(ctx->d_tile_w, 0, slots * sizeof(unsigned), ctx->stream)); }
+    rc = ensure(ctx, ctx->d_order, ctx->cap_order, slots); if (rc) return rc;
+    g.tile_w = ctx->d_tile_w; g.groups_per_tile = pts_per_block / 32; g.tiles = (int)tiles;
   }
   const size_t smem = group_smem(M.tabf_len);
   if (smem > 48 * 1024) CU(cudaFuncSetAttribute(group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -279,7 +281,7 @@ int run_groups(flash_ctx* ctx, int C, int cfg_per_frame, long long* stride, int 
   ctx->launches++; ctx->last.launches++;
   if (g.tile_w) {
     int nt = 32; while (nt < tiles) nt <<= 1;
-    tile_order_kernel<<<1, nt, 0, ctx->stream>>>(ctx->d_tile_w, (int)tiles, ctx->d_order);
+    tile_order_kernel<<<cfg_per_frame > 0 ? P.ft.n_frames : 1, nt, 0, ctx->stream>>>(ctx->d_tile_w, (int)tiles, ctx->d_order);
     CU(cudaGetLastError());
     ctx->launches++; ctx->last.launches++;
     if (ordered) *ordered = true;
