@@ -309,6 +309,8 @@ def run_ours(args, rank, local_rank, world):
         m.check(L.flash_points_set(ctx, pp, n_local))
         m.check(L.flash_cost_grad(ctx, pX, Cn, 10.0, pc, pg, None))
 
+    import gc
+    gc.collect(); gc.disable()   # as timeit does: a collection inside one of the few timed steps of one rank would be charged to all of them
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()      # sampling starts before the warm-up and ends after the end-to-end loop
@@ -354,6 +356,7 @@ def run_ours(args, rank, local_rank, world):
     m.check(L.flash_points_swap(ctx))   # retire the last upload
     barrier()
     clocks = sampler.stop(first_sample) if rank == 0 else None
+    gc.enable()
 
     arg0 = None
     if args.parity:
