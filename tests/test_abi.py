@@ -98,3 +98,19 @@ def test_plain_c_driver_on_the_gpu(tmp_path):
     r = subprocess.run(_driver() + [str(tmp_path)], capture_output=True, text=True)
     print(r.stdout)
     assert r.returncode == 0 and "FAIL " not in r.stdout and r.stdout.strip().endswith("PASSED"), r.stdout + r.stderr
+
+
+def test_documented_limits_match_the_sources():
+    """INTEGRATION.md's table of compiled-in limits quotes the constants of the sources."""
+    src = open(os.path.join(ROOT, "point-cloud-signed-distance_b200", "csrc", "flash_dev.h")).read()
+    ing = open(os.path.join(ROOT, "point-cloud-signed-distance_b200", "csrc", "flash_ingest.cuh")).read()
+    hdr = open(os.path.join(ROOT, "include", "flashsdf.h")).read()
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    const = lambda text, name: int(re.search(r"constexpr int %s = (\d+);" % name, text).group(1))
+    assert "| bodies / surfaces per model | %d / %d |" % (const(src, "MAX_BODIES"), const(src, "MAX_SURFACES")) in doc
+    assert "| convex surfaces | %d |" % const(src, "MAX_CONVEX") in doc
+    assert "| RBF skins; control points per skin | %d; %d |" % (const(src, "MAX_SKINS"), const(src, "MAX_SKIN_PTS")) in doc
+    assert "| frames per batch | %d |" % const(ing, "MAX_FRAMES") in doc
+    assert int(re.search(r"#define FLASH_MAX_FRAMES (\d+)", hdr).group(1)) == const(ing, "MAX_FRAMES")
+    q = int(re.search(r"#define FLASH_STATIC_MAX_QUERY (\d+)", hdr).group(1))
+    assert "{:,} query points".format(q) in doc and "devices[16]" in hdr and "| devices per context | 16 |" in doc
